@@ -1,0 +1,264 @@
+/*
+ * rfgpu.h — C ABI of the B200-native quad-pattern scan / filter / SPARQL-join path.
+ *
+ * This is the drop-in boundary a Rust `rdf-fusion-cuda` crate binds with `extern "C"`
+ * (see INTEGRATION.md for the bindgen-style stub).  Every entry point cites the
+ * reference interface (tobixdev/rdf-fusion, paths relative to the reference root) it
+ * replaces.  No torch / C++ types cross this boundary: plain pointers and sizes only.
+ *
+ * Conventions
+ *  - every function returning int32_t returns RFGPU_OK (0) or a negative RFGPU_E_* code;
+ *    the message is available through rfgpu_last_error(ctx) (thread-local copy when ctx
+ *    is NULL).  No exceptions or longjmp cross the boundary (DFResult<T> on the Rust side:
+ *    lib/storage/src/memory/storage/pattern_data_source.rs:47-55).
+ *  - object ids are uint32_t (lib/encoding/src/object_id/encoding.rs:131-133).  Id 0 is
+ *    DEFAULT_GRAPH_ID and is surfaced as Arrow NULL (lib/storage/src/memory/object_id.rs:21-27,
+ *    quad_index_data.rs:437-440).  On the device 0 *is* the NULL sentinel for every column;
+ *    validity bitmaps are synthesised on export and folded in on import.
+ *  - a ctx owns one CUDA device + one stream; calls on one ctx must be serialised by the
+ *    caller (one ctx per tokio worker / per DataFusion partition); stores and tables are
+ *    reference counted and may be shared between ctxs of the same device.
+ */
+#ifndef RFGPU_H
+#define RFGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RFGPU_OK 0
+#define RFGPU_E_INVALID (-1)     /* plan_err!: malformed argument / plan            */
+#define RFGPU_E_CUDA (-2)        /* CUDA runtime failure (message has the cudaError) */
+#define RFGPU_E_EXEC (-3)        /* exec_err!: runtime failure of a valid plan       */
+#define RFGPU_E_UNSUPPORTED (-4) /* shape not handled by the GPU node: keep the CPU node */
+#define RFGPU_E_NOGPU (-5)       /* no usable CUDA device: there is no CPU fallback  */
+
+typedef struct rfgpu_ctx rfgpu_ctx;
+typedef struct rfgpu_store rfgpu_store; /* IndexPermutations<MemQuadIndex> on the device */
+typedef struct rfgpu_table rfgpu_table; /* a device-resident set of solution mappings    */
+typedef struct rfgpu_scan_plan rfgpu_scan_plan; /* PlannedPatternScan                     */
+
+/* ---- index components / permutations: lib/storage/src/index/components.rs:62-84 ---- */
+enum { RFGPU_G = 0, RFGPU_S = 1, RFGPU_P = 2, RFGPU_O = 3 };
+/* a permutation is 4 components packed 2 bits each, level 0 in the low bits */
+#define RFGPU_PERM(a, b, c, d) ((uint32_t)((a) | ((b) << 2) | ((c) << 4) | ((d) << 6)))
+#define RFGPU_GSPO RFGPU_PERM(RFGPU_G, RFGPU_S, RFGPU_P, RFGPU_O)
+#define RFGPU_GPOS RFGPU_PERM(RFGPU_G, RFGPU_P, RFGPU_O, RFGPU_S)
+#define RFGPU_GOSP RFGPU_PERM(RFGPU_G, RFGPU_O, RFGPU_S, RFGPU_P)
+/* extra G-leading orders the reference does not keep but the store may */
+#define RFGPU_GPSO RFGPU_PERM(RFGPU_G, RFGPU_P, RFGPU_S, RFGPU_O)
+#define RFGPU_GSOP RFGPU_PERM(RFGPU_G, RFGPU_S, RFGPU_O, RFGPU_P)
+#define RFGPU_GOPS RFGPU_PERM(RFGPU_G, RFGPU_O, RFGPU_P, RFGPU_S)
+
+/* ---- context ---- */
+/* One CUDA device + stream + stream-ordered memory pool.  Fails with RFGPU_E_NOGPU when
+ * the device cannot be opened: the product path has no CPU fallback. */
+int32_t rfgpu_ctx_create(int32_t device, rfgpu_ctx** out);
+void rfgpu_ctx_destroy(rfgpu_ctx* ctx);
+const char* rfgpu_last_error(const rfgpu_ctx* ctx);
+/* the ctx's cudaStream_t (as void*), so a host can order its own work / events on it */
+void* rfgpu_ctx_stream(rfgpu_ctx* ctx);
+int32_t rfgpu_ctx_synchronize(rfgpu_ctx* ctx);
+const char* rfgpu_version(void);
+
+/* ---- scan instructions: lib/storage/src/memory/storage/scan_instructions.rs ---- */
+typedef enum {
+  RFGPU_PRED_NONE = 0,
+  RFGPU_PRED_FALSE = 1,    /* MemIndexScanPredicate::False   :159 */
+  RFGPU_PRED_IN = 2,       /* MemIndexScanPredicate::In      :161 */
+  RFGPU_PRED_BETWEEN = 3,  /* MemIndexScanPredicate::Between :163 (inclusive) */
+  RFGPU_PRED_EQUAL_TO = 4  /* MemIndexScanPredicate::EqualTo :165 (repeated variable) */
+} rfgpu_pred_kind;
+
+typedef struct {
+  int32_t kind;           /* rfgpu_pred_kind */
+  const uint32_t* ids;    /* IN: the id set (any order, duplicates tolerated) */
+  uint32_t n_ids;
+  uint32_t lo, hi;        /* BETWEEN: inclusive bounds */
+  const char* equal_to;   /* EQUAL_TO: variable name scanned at another level */
+} rfgpu_scan_pred;
+
+typedef enum { RFGPU_TRAVERSE = 0, RFGPU_SCAN = 1 } rfgpu_scan_action;
+
+typedef struct {
+  int32_t action;         /* Traverse(pred) | Scan(var, pred) — scan_instructions.rs:247-252 */
+  const char* var;        /* SCAN: variable (= output column) name */
+  rfgpu_scan_pred pred;
+} rfgpu_scan_instruction;
+
+/* comparison operators of pushed-down filters: predicate_pushdown.rs:24-58 */
+typedef enum { RFGPU_OP_EQ = 0, RFGPU_OP_GT = 1, RFGPU_OP_GTEQ = 2, RFGPU_OP_LT = 3, RFGPU_OP_LTEQ = 4 } rfgpu_cmp_op;
+
+/* ---- store: IndexPermutations (lib/storage/src/index/permutations.rs:54-128) ---- */
+int32_t rfgpu_store_create(rfgpu_ctx* ctx, rfgpu_store** out);
+rfgpu_store* rfgpu_store_retain(rfgpu_store* s); /* one read snapshot per plan: snapshot.rs:35-37 */
+void rfgpu_store_release(rfgpu_store* s);
+/* Adds one permutation from columns already sorted (and de-duplicated) in `perm` order;
+ * cols[i] is the column of level i.  `on_device` != 0: the pointers are device pointers on
+ * the ctx's device and are copied device-to-device.  Sortedness/uniqueness is verified by a
+ * kernel; violation → RFGPU_E_INVALID.  Replaces MemQuadIndex::insert (quad_index.rs:132-143)
+ * + MemIndexData::insert (quad_index_data.rs:287-332) for bulk load. */
+int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm,
+                              const uint32_t* const cols[4], uint64_t n_rows, int32_t on_device);
+uint64_t rfgpu_store_len(const rfgpu_store* s);
+int32_t rfgpu_store_num_indexes(const rfgpu_store* s);
+uint32_t rfgpu_store_index_perm(const rfgpu_store* s, int32_t i);
+
+/* ---- scan planning: PlannedPatternScan (scan.rs:414-513) ---- */
+/* `gspo` = the four instructions in G,S,P,O order (MemIndexScanInstructions::new_gspo,
+ * scan_instructions.rs:19-51: a variable scanned twice becomes Traverse(EqualTo(var))).
+ * The permutation is picked by IndexPermutations::choose_index (permutations.rs:81-96). */
+int32_t rfgpu_scan_plan_create(rfgpu_ctx* ctx, rfgpu_store* s,
+                               const rfgpu_scan_instruction gspo[4], rfgpu_scan_plan** out);
+void rfgpu_scan_plan_destroy(rfgpu_scan_plan* p);
+/* PlannedPatternScan::apply_filter (scan.rs:469-480) for `column <op> value`; re-chooses the
+ * index afterwards (try_find_better_index, scan.rs:483-486). */
+int32_t rfgpu_scan_plan_apply_filter(rfgpu_ctx* ctx, rfgpu_scan_plan* p, const char* column,
+                                     int32_t op /*rfgpu_cmp_op*/, uint32_t value);
+/* same for an already-combined Between (dynamic join filters: predicate_pushdown.rs:253-268) */
+int32_t rfgpu_scan_plan_apply_between(rfgpu_ctx* ctx, rfgpu_scan_plan* p, const char* column,
+                                      uint32_t lo, uint32_t hi);
+/* force a permutation (tests / benchmarks); RFGPU_E_INVALID if the store does not hold it */
+int32_t rfgpu_scan_plan_set_index(rfgpu_ctx* ctx, rfgpu_scan_plan* p, uint32_t perm);
+uint32_t rfgpu_scan_plan_index(const rfgpu_scan_plan* p);
+/* "[GPOS] subject=?subject, ..., additional_filters=[object in (2..9)]"-style text of the
+ * instructions in GSPO order (pattern_data_source.rs:89-104 fmt_as); returns bytes needed. */
+size_t rfgpu_scan_plan_describe(const rfgpu_scan_plan* p, char* buf, size_t cap);
+
+#define RFGPU_SCAN_ALLOW_VIEW 1u /* unfiltered ranges come back as zero-copy views (scan.rs:146-170) */
+/* MemQuadIndexScanIterator (scan.rs:101-213) + prune_relevant_row_groups
+ * (quad_index_data.rs:155-284) + compute_selection_vector (scan.rs:264-340), whole range in
+ * one pass.  Output columns: scanned variables in first-occurrence G,S,P,O order
+ * (lib/logical/src/patterns/mod.rs:68-107); graph column nullable, others not. */
+int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t flags, rfgpu_table** out);
+/* the contiguous index range pruning narrowed to, and rows kept by the residual predicates */
+int32_t rfgpu_scan_last_range(const rfgpu_ctx* ctx, uint64_t* from, uint64_t* to);
+
+/* ---- tables (solution mappings on the device) ---- */
+rfgpu_table* rfgpu_table_retain(rfgpu_table* t);
+void rfgpu_table_release(rfgpu_table* t);
+uint64_t rfgpu_table_num_rows(const rfgpu_table* t);
+int32_t rfgpu_table_num_cols(const rfgpu_table* t);
+const char* rfgpu_table_col_name(const rfgpu_table* t, int32_t col);
+int32_t rfgpu_table_col_nullable(const rfgpu_table* t, int32_t col);
+/* device pointer of a column (uint32_t[num_rows], 0 = NULL), valid while the table lives */
+const uint32_t* rfgpu_table_col_device_ptr(const rfgpu_table* t, int32_t col);
+/* Import host columns (an Arrow RecordBatch's UInt32 value buffers + optional validity
+ * bitmaps, LSB-first as in Arrow).  `pinned` != 0 promises page-locked buffers. */
+int32_t rfgpu_table_import(rfgpu_ctx* ctx, int32_t n_cols, const char* const* names,
+                           const uint8_t* nullable, const uint32_t* const* values,
+                           const uint8_t* const* validity, uint64_t n_rows, rfgpu_table** out);
+/* Export rows [row_off, row_off+n_rows) into caller buffers; validity[i] may be NULL (then
+ * nothing is written for it), else receives an Arrow bitmap (bit = value != 0).  Returns the
+ * null count per column in null_counts when non-NULL. */
+int32_t rfgpu_table_export(rfgpu_ctx* ctx, const rfgpu_table* t, uint64_t row_off, uint64_t n_rows,
+                           uint32_t* const* values, uint8_t* const* validity, uint64_t* null_counts);
+/* zero-copy projection / rename (DataFusion ProjectionExec over plain columns) */
+int32_t rfgpu_table_project(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t n_cols,
+                            const int32_t* cols, const char* const* new_names, rfgpu_table** out);
+/* override schema nullability (a field's is_nullable is a schema property: join/rewrite.rs:131-139) */
+int32_t rfgpu_table_set_nullable(rfgpu_table* t, int32_t col, int32_t nullable);
+
+/* ---- Arrow C Data Interface (what arrow-rs `arrow::ffi` speaks) ---- */
+struct ArrowSchema;
+struct ArrowArray;
+/* struct-typed array (a RecordBatch) of UInt32 children → table; does not take ownership
+ * of the input (caller still calls release). */
+int32_t rfgpu_table_import_arrow(rfgpu_ctx* ctx, const struct ArrowArray* array,
+                                 const struct ArrowSchema* schema, rfgpu_table** out);
+/* rows [row_off,row_off+n_rows) → newly allocated host buffers owned by the returned
+ * ArrowArray (release callback frees them); one struct array with one UInt32 child per column. */
+int32_t rfgpu_table_export_arrow(rfgpu_ctx* ctx, const rfgpu_table* t, uint64_t row_off,
+                                 uint64_t n_rows, struct ArrowArray* out_array,
+                                 struct ArrowSchema* out_schema);
+
+/* ---- ID-level filters: DataFusion FilterExec over object-id columns ---- */
+typedef enum {
+  RFGPU_F_EQ_CONST = 0,   /* col = c      (lib/logical/src/patterns/rewrite.rs:68-110)   */
+  RFGPU_F_NE_CONST = 1,   /* col != c     (BSBM explore Q5 `product@0 != <oid>`)          */
+  RFGPU_F_EQ_COL = 2,     /* col = col2   (sameTerm / filter_same_variable :112-148)      */
+  RFGPU_F_NE_COL = 3,     /* col != col2                                                  */
+  RFGPU_F_BETWEEN = 4,    /* lo <= col <= hi                                              */
+  RFGPU_F_IN = 5,         /* col IN ids                                                   */
+  RFGPU_F_IS_NULL = 6,    /* NOT BOUND(col)  (lib/logical/src/expr_builder.rs:58-60)      */
+  RFGPU_F_IS_NOT_NULL = 7 /* BOUND(col)                                                   */
+} rfgpu_filter_op;
+
+typedef struct {
+  int32_t op;           /* rfgpu_filter_op */
+  int32_t col, col2;    /* column indexes in the input table */
+  uint32_t value, hi;   /* EQ/NE const: value; BETWEEN: [value, hi] */
+  const uint32_t* ids;  /* IN */
+  uint32_t n_ids;
+} rfgpu_filter_pred;
+
+/* Conjunction of `n` predicates under SQL three-valued logic (a NULL comparison drops the
+ * row), order-preserving compaction of all columns. */
+int32_t rfgpu_filter(rfgpu_ctx* ctx, const rfgpu_table* in, const rfgpu_filter_pred* preds,
+                     int32_t n, rfgpu_table** out);
+
+/* ---- SPARQL join: SparqlJoinNode + SparqlJoinLoweringRule ---- */
+typedef enum { RFGPU_JOIN_INNER = 0, RFGPU_JOIN_LEFT = 1 } rfgpu_join_type;
+typedef enum {
+  RFGPU_JOIN_ALGO_CROSS = 0,     /* disjoint schemas: join/rewrite.rs:76-96                 */
+  RFGPU_JOIN_ALGO_EQUI = 1,      /* try_build_regular_join :126-168 (NullEqualsNothing)     */
+  RFGPU_JOIN_ALGO_COMPATIBLE = 2 /* build_join_with_is_compatible :183-221 (+COALESCE)      */
+} rfgpu_join_algo;
+
+/* Joins on the variables both schemas share (get_join_keys, join/rewrite.rs:363-379).
+ * Lowering follows rewrite_sparql_join (:71-111): no shared variable → cross / keyless left;
+ * no shared column nullable by schema → equi hash join; otherwise compatible-mapping join
+ * with COALESCE(lhs.k, rhs.k).  Output schema: all lhs columns, then rhs-only columns
+ * (join/logical.rs:251-279; rhs-only columns nullable for Left).  The multiset of rows is
+ * what DataFusion's HashJoinExec / NestedLoopJoinExec / CrossJoinExec would produce. */
+int32_t rfgpu_sparql_join(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_table* rhs,
+                          int32_t join_type, rfgpu_table** out);
+/* which lowering the last rfgpu_sparql_join on this ctx took (rfgpu_join_algo) */
+int32_t rfgpu_last_join_algo(const rfgpu_ctx* ctx);
+
+/* ---- multi-GPU: one process (ctx) per GPU, NCCL over NVLink ---- */
+#define RFGPU_UNIQUE_ID_BYTES 128
+int32_t rfgpu_comm_unique_id(uint8_t id[RFGPU_UNIQUE_ID_BYTES]);
+int32_t rfgpu_comm_init(rfgpu_ctx* ctx, int32_t rank, int32_t n_ranks,
+                        const uint8_t id[RFGPU_UNIQUE_ID_BYTES]);
+int32_t rfgpu_comm_rank(const rfgpu_ctx* ctx);
+int32_t rfgpu_comm_size(const rfgpu_ctx* ctx);
+/* Hash-partition `in` on column `key_col` (dest = mix32(id) mod n_ranks; NULL keys stay
+ * local... see DESIGN.md) and exchange with a grouped ncclSend/ncclRecv all-to-all: the
+ * exchange DataFusion's RepartitionExec(Hash) does between tokio tasks. */
+int32_t rfgpu_shuffle(rfgpu_ctx* ctx, const rfgpu_table* in, int32_t key_col, rfgpu_table** out);
+/* the destination rank of an id under the shuffle's hash (host mirror, for tests) */
+uint32_t rfgpu_shuffle_dest(uint32_t id, uint32_t n_ranks);
+/* partition only (no communication): rows grouped by destination, counts[n_parts] filled */
+int32_t rfgpu_partition(rfgpu_ctx* ctx, const rfgpu_table* in, int32_t key_col, uint32_t n_parts,
+                        rfgpu_table** out, uint64_t* counts);
+
+/* ---- metrics: the BaselineMetrics analogue (stream.rs:43-61) + kernel evidence ---- */
+typedef struct {
+  uint64_t kernel_launches;   /* launches of rfgpu's own kernels since the last reset */
+  uint64_t h2d_bytes, d2h_bytes;
+  uint64_t scan_rows_in, scan_rows_out;
+  uint64_t filter_rows_in, filter_rows_out;
+  uint64_t join_build_rows, join_probe_rows, join_rows_out;
+  uint64_t algorithmic_bytes; /* SURVEY §8(d) formulas, summed over operators */
+} rfgpu_metrics;
+int32_t rfgpu_metrics_get(const rfgpu_ctx* ctx, rfgpu_metrics* out);
+int32_t rfgpu_metrics_reset(rfgpu_ctx* ctx);
+/* per-kernel device time (CUDA events on the ctx stream) — off by default */
+int32_t rfgpu_profile_enable(rfgpu_ctx* ctx, int32_t on);
+int32_t rfgpu_profile_num_kernels(rfgpu_ctx* ctx);
+int32_t rfgpu_profile_get(rfgpu_ctx* ctx, int32_t i, const char** name, uint64_t* launches,
+                          double* total_ms, uint64_t* algorithmic_bytes);
+/* stream-ordered stopwatch on the ctx stream (bench.py times steps with it) */
+int32_t rfgpu_timer_start(rfgpu_ctx* ctx);
+int32_t rfgpu_timer_stop(rfgpu_ctx* ctx, double* elapsed_ms);
+/* write a buffer larger than L2 (flush between timed iterations) */
+int32_t rfgpu_flush_l2(rfgpu_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RFGPU_H */

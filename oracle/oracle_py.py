@@ -1,0 +1,278 @@
+"""ctypes wrapper of the CPU oracle (oracle/_build/librf_oracle.so).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs.  The product package (rdf_fusion_b200/) never imports this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+
+from rdf_fusion_b200 import _ffi as F
+from rdf_fusion_b200.api import FPred, Instr, make_filter_preds, make_instructions
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_build", "librf_oracle.so")
+_lib = None
+
+
+def build(force=False):
+    if force or not os.path.exists(LIB_PATH):
+        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        l = C.CDLL(LIB_PATH)
+        vp, u32p, u64p = C.c_void_p, F.u32p, F.u64p
+        sig = {
+            "orc_last_error": (C.c_char_p, []),
+            "orc_store_new": (vp, [C.c_uint64, C.c_int, u32p]),
+            "orc_store_free": (None, [vp]),
+            "orc_store_insert": (C.c_uint64, [vp, u32p, C.c_uint64]),
+            "orc_store_remove": (C.c_uint64, [vp, u32p, C.c_uint64]),
+            "orc_store_len": (C.c_uint64, [vp]),
+            "orc_store_load_sorted": (C.c_int, [vp, C.c_uint32, C.POINTER(vp), C.c_uint64]),
+            "orc_store_group_lens": (C.c_uint64, [vp, C.c_uint32, u64p, C.c_uint64]),
+            "orc_plan_new": (vp, [vp, C.POINTER(F.ScanInstruction)]),
+            "orc_plan_free": (None, [vp]),
+            "orc_plan_index": (C.c_uint32, [vp]),
+            "orc_plan_set_index": (C.c_int, [vp, C.c_uint32]),
+            "orc_plan_apply_filter": (C.c_int, [vp, C.c_char_p, C.c_int, C.c_uint32]),
+            "orc_plan_apply_between": (C.c_int, [vp, C.c_char_p, C.c_uint32, C.c_uint32]),
+            "orc_plan_describe": (C.c_uint64, [vp, C.c_char_p, C.c_uint64]),
+            "orc_plan_scan": (vp, [vp]),
+            "orc_plan_pruned_rows": (C.c_int64, [vp, u64p]),
+            "orc_result_free": (None, [vp]),
+            "orc_result_rows": (C.c_uint64, [vp]),
+            "orc_result_cols": (C.c_int, [vp]),
+            "orc_result_col_name": (C.c_char_p, [vp, C.c_int]),
+            "orc_result_col_nullable": (C.c_int, [vp, C.c_int]),
+            "orc_result_col": (u32p, [vp, C.c_int]),
+            "orc_result_num_batches": (C.c_uint64, [vp]),
+            "orc_result_batch_rows": (u64p, [vp]),
+            "orc_try_and_with": (C.c_int, [C.POINTER(F.ScanPred), C.POINTER(F.ScanPred), C.POINTER(C.c_int), u32p, u32p,
+                                           u32p, u32p, C.c_uint32]),
+            "orc_find_range": (C.c_int, [u32p, C.c_uint64, C.c_uint32, C.c_uint32, u64p, u64p]),
+            "orc_filter": (vp, [C.c_int, C.POINTER(C.c_char_p), F.u8p, C.POINTER(vp), C.c_uint64,
+                                C.POINTER(F.FilterPred), C.c_int]),
+            "orc_sparql_join": (vp, [C.c_int, C.POINTER(C.c_char_p), F.u8p, C.POINTER(vp), C.c_uint64,
+                                     C.c_int, C.POINTER(C.c_char_p), F.u8p, C.POINTER(vp), C.c_uint64,
+                                     C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]),
+        }
+        for n, (r, a) in sig.items():
+            fn = getattr(l, n)
+            fn.restype, fn.argtypes = r, a
+        _lib = l
+    return _lib
+
+
+class OracleError(RuntimeError):
+    pass
+
+
+def _err():
+    return OracleError((lib().orc_last_error() or b"").decode())
+
+
+class OTable:
+    """Plain host table: names, nullable flags, uint32 columns (0 = NULL)."""
+
+    def __init__(self, names, nullable, cols, batch_rows=None):
+        self.names = list(names)
+        self.nullable = [bool(x) for x in nullable]
+        self.cols = [np.ascontiguousarray(c, dtype=np.uint32) for c in cols]
+        self.batch_rows = batch_rows or []
+
+    @property
+    def num_rows(self):
+        return len(self.cols[0]) if self.cols else 0
+
+    @staticmethod
+    def from_result(r) -> "OTable":
+        l = lib()
+        try:
+            n = l.orc_result_rows(r)
+            nc = l.orc_result_cols(r)
+            names = [l.orc_result_col_name(r, c).decode() for c in range(nc)]
+            nullable = [l.orc_result_col_nullable(r, c) for c in range(nc)]
+            cols = [np.ctypeslib.as_array(l.orc_result_col(r, c), shape=(n,)).copy() if n else np.zeros(0, np.uint32)
+                    for c in range(nc)]
+            nb = l.orc_result_num_batches(r)
+            br = list(np.ctypeslib.as_array(l.orc_result_batch_rows(r), shape=(nb,))) if nb else []
+            t = OTable(names, nullable, cols, [int(x) for x in br])
+            t._rows = int(n)
+            return t
+        finally:
+            l.orc_result_free(r)
+
+    def _c(self):
+        nc = len(self.names)
+        names = (C.c_char_p * max(1, nc))(*[n.encode() for n in self.names])
+        nl = (C.c_uint8 * max(1, nc))(*[1 if x else 0 for x in self.nullable])
+        vals = (C.c_void_p * max(1, nc))(*[c.ctypes.data for c in self.cols])
+        return nc, names, C.cast(nl, F.u8p), vals, self.num_rows
+
+
+class OracleStore:
+    def __init__(self, batch_size=8192, perms: Sequence[int] = (F.GSPO, F.GPOS, F.GOSP)):
+        p = (C.c_uint32 * len(perms))(*perms)
+        self.h = lib().orc_store_new(batch_size, len(perms), C.cast(p, F.u32p))
+        self.perms = list(perms)
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().orc_store_free(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def insert(self, quads) -> int:
+        q = np.ascontiguousarray(quads, dtype=np.uint32).reshape(-1, 4)
+        return int(lib().orc_store_insert(self.h, q.ctypes.data_as(F.u32p), len(q)))
+
+    def remove(self, quads) -> int:
+        q = np.ascontiguousarray(quads, dtype=np.uint32).reshape(-1, 4)
+        return int(lib().orc_store_remove(self.h, q.ctypes.data_as(F.u32p), len(q)))
+
+    def load_quads(self, quads):
+        """fast bulk load: numpy sort per permutation, row groups of batch_size"""
+        quads = np.ascontiguousarray(quads, dtype=np.uint32).reshape(-1, 4)
+        quads = np.unique(quads, axis=0) if len(quads) else quads
+        for p in self.perms:
+            comps = [(p >> (2 * i)) & 3 for i in range(4)]
+            cols = [quads[:, c] for c in comps]
+            order = np.lexsort(tuple(reversed(cols))) if len(quads) else np.zeros(0, dtype=np.int64)
+            sc = [np.ascontiguousarray(c[order]) for c in cols]
+            arr = (C.c_void_p * 4)(*[x.ctypes.data for x in sc])
+            if lib().orc_store_load_sorted(self.h, p, arr, len(quads)) != 0:
+                raise _err()
+        return self
+
+    def __len__(self):
+        return int(lib().orc_store_len(self.h))
+
+    def group_lens(self, perm=F.GSPO) -> List[int]:
+        buf = (C.c_uint64 * 65536)()
+        n = lib().orc_store_group_lens(self.h, perm, buf, 65536)
+        return [int(buf[i]) for i in range(n)]
+
+    def plan(self, gspo: Sequence[Instr]) -> "OraclePlan":
+        return OraclePlan(self, gspo)
+
+
+class OraclePlan:
+    def __init__(self, store: OracleStore, gspo):
+        self.store = store
+        arr, keep = make_instructions(gspo)
+        self.h = lib().orc_plan_new(store.h, arr)
+        if not self.h:
+            raise _err()
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().orc_plan_free(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def apply_filter(self, column, op, value):
+        if lib().orc_plan_apply_filter(self.h, column.encode(), op, value) != 0:
+            raise _err()
+        return self
+
+    def apply_between(self, column, lo, hi):
+        if lib().orc_plan_apply_between(self.h, column.encode(), lo, hi) != 0:
+            raise _err()
+        return self
+
+    def set_index(self, perm):
+        if lib().orc_plan_set_index(self.h, perm) != 0:
+            raise _err()
+        return self
+
+    @property
+    def index(self):
+        return int(lib().orc_plan_index(self.h))
+
+    def describe(self) -> str:
+        n = lib().orc_plan_describe(self.h, None, 0)
+        buf = C.create_string_buffer(n)
+        lib().orc_plan_describe(self.h, buf, n)
+        return buf.value.decode()
+
+    def pruned_rows(self):
+        ns = C.c_uint64()
+        n = lib().orc_plan_pruned_rows(self.h, C.byref(ns))
+        return int(n), int(ns.value)
+
+    def execute(self) -> OTable:
+        r = lib().orc_plan_scan(self.h)
+        if not r:
+            raise _err()
+        return OTable.from_result(r)
+
+
+def try_and_with(a, b):
+    """a, b: api.Pred → None (not combinable) or (kind, lo, hi, ids)"""
+    def conv(p):
+        arr, keep = make_instructions([Instr(F.TRAVERSE, None, p)] + [Instr(F.TRAVERSE)] * 3)
+        return arr, keep
+    aa, ka = conv(a)
+    bb, kb = conv(b)
+    kind, lo, hi, n = C.c_int(), C.c_uint32(), C.c_uint32(), C.c_uint32()
+    ids = (C.c_uint32 * 256)()
+    ok = lib().orc_try_and_with(C.byref(aa[0].pred), C.byref(bb[0].pred), C.byref(kind), C.byref(lo), C.byref(hi),
+                                C.cast(ids, F.u32p), C.byref(n), 256)
+    if not ok:
+        return None
+    return kind.value, lo.value, hi.value, [int(ids[i]) for i in range(n.value)]
+
+
+def find_range(values, lo, hi):
+    v = np.ascontiguousarray(values, dtype=np.uint32)
+    a, b = C.c_uint64(), C.c_uint64()
+    k = lib().orc_find_range(v.ctypes.data_as(F.u32p), len(v), lo, hi, C.byref(a), C.byref(b))
+    return ["Before", "NotContained", "Contained", "After"][k], int(a.value), int(b.value)
+
+
+def filter_table(t: OTable, preds: Sequence[FPred]) -> OTable:
+    nc, names, nl, vals, n = t._c()
+    arr, keep = make_filter_preds(preds)
+    r = lib().orc_filter(nc, names, nl, vals, n, arr, len(preds))
+    if not r:
+        raise _err()
+    return OTable.from_result(r)
+
+
+def sparql_join(l: OTable, r: OTable, join_type=F.JOIN_INNER, impl="nested", threads=1):
+    """-> (OTable, algo, seconds).  impl: "nested" (definition) or "hash"."""
+    a = l._c()
+    b = r._c()
+    algo = C.c_int()
+    secs = C.c_double()
+    res = lib().orc_sparql_join(a[0], a[1], a[2], a[3], a[4], b[0], b[1], b[2], b[3], b[4], join_type,
+                                0 if impl == "nested" else 1, threads, C.byref(algo), C.byref(secs))
+    if not res:
+        raise _err()
+    return OTable.from_result(res), algo.value, secs.value
+
+
+def canonical_rows(cols: Sequence[np.ndarray]) -> np.ndarray:
+    """multiset comparison helper: rows sorted lexicographically (NULL = 0 sorts first), shape (rows, cols)"""
+    if not cols:
+        return np.zeros((0, 0), dtype=np.uint32)
+    m = np.stack([np.asarray(c, dtype=np.uint32) for c in cols], axis=1)
+    if len(m) == 0:
+        return m
+    order = np.lexsort(tuple(m[:, i] for i in reversed(range(m.shape[1]))))
+    return m[order]

@@ -1,0 +1,140 @@
+"""ctypes binding of include/rfgpu.h (librfgpu.so).
+
+This is the same surface a Rust `extern "C"` block would declare.  There is no fallback:
+if the CUDA library is missing the import raises, and if no GPU is present `rfgpu_ctx_create` fails with
+RFGPU_E_NOGPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librfgpu.so")
+
+OK, E_INVALID, E_CUDA, E_EXEC, E_UNSUPPORTED, E_NOGPU = 0, -1, -2, -3, -4, -5
+
+G, S, P, O = 0, 1, 2, 3
+
+
+def perm(a, b, c, d):
+    return a | (b << 2) | (c << 4) | (d << 6)
+
+
+GSPO, GPOS, GOSP = perm(G, S, P, O), perm(G, P, O, S), perm(G, O, S, P)
+GPSO, GSOP, GOPS = perm(G, P, S, O), perm(G, S, O, P), perm(G, O, P, S)
+PERM_NAMES = {GSPO: "GSPO", GPOS: "GPOS", GOSP: "GOSP", GPSO: "GPSO", GSOP: "GSOP", GOPS: "GOPS"}
+
+PRED_NONE, PRED_FALSE, PRED_IN, PRED_BETWEEN, PRED_EQUAL_TO = 0, 1, 2, 3, 4
+TRAVERSE, SCAN = 0, 1
+OP_EQ, OP_GT, OP_GTEQ, OP_LT, OP_LTEQ = 0, 1, 2, 3, 4
+F_EQ_CONST, F_NE_CONST, F_EQ_COL, F_NE_COL, F_BETWEEN, F_IN, F_IS_NULL, F_IS_NOT_NULL = range(8)
+JOIN_INNER, JOIN_LEFT = 0, 1
+ALGO_CROSS, ALGO_EQUI, ALGO_COMPATIBLE = 0, 1, 2
+SCAN_ALLOW_VIEW = 1
+UNIQUE_ID_BYTES = 128
+
+u32p = C.POINTER(C.c_uint32)
+u8p = C.POINTER(C.c_uint8)
+u64p = C.POINTER(C.c_uint64)
+
+
+class ScanPred(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("ids", u32p), ("n_ids", C.c_uint32), ("lo", C.c_uint32), ("hi", C.c_uint32),
+                ("equal_to", C.c_char_p)]
+
+
+class ScanInstruction(C.Structure):
+    _fields_ = [("action", C.c_int32), ("var", C.c_char_p), ("pred", ScanPred)]
+
+
+class FilterPred(C.Structure):
+    _fields_ = [("op", C.c_int32), ("col", C.c_int32), ("col2", C.c_int32), ("value", C.c_uint32), ("hi", C.c_uint32),
+                ("ids", u32p), ("n_ids", C.c_uint32)]
+
+
+class Metrics(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in (
+        "kernel_launches", "h2d_bytes", "d2h_bytes", "scan_rows_in", "scan_rows_out", "filter_rows_in",
+        "filter_rows_out", "join_build_rows", "join_probe_rows", "join_rows_out", "algorithmic_bytes")]
+
+
+# name -> (restype, argtypes); every symbol include/rfgpu.h declares
+SIGNATURES = {
+    "rfgpu_ctx_create": (C.c_int32, [C.c_int32, C.POINTER(C.c_void_p)]),
+    "rfgpu_ctx_destroy": (None, [C.c_void_p]),
+    "rfgpu_last_error": (C.c_char_p, [C.c_void_p]),
+    "rfgpu_ctx_stream": (C.c_void_p, [C.c_void_p]),
+    "rfgpu_ctx_synchronize": (C.c_int32, [C.c_void_p]),
+    "rfgpu_version": (C.c_char_p, []),
+    "rfgpu_store_create": (C.c_int32, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "rfgpu_store_retain": (C.c_void_p, [C.c_void_p]),
+    "rfgpu_store_release": (None, [C.c_void_p]),
+    "rfgpu_store_add_index": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p), C.c_uint64, C.c_int32]),
+    "rfgpu_store_len": (C.c_uint64, [C.c_void_p]),
+    "rfgpu_store_num_indexes": (C.c_int32, [C.c_void_p]),
+    "rfgpu_store_index_perm": (C.c_uint32, [C.c_void_p, C.c_int32]),
+    "rfgpu_scan_plan_create": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(ScanInstruction), C.POINTER(C.c_void_p)]),
+    "rfgpu_scan_plan_destroy": (None, [C.c_void_p]),
+    "rfgpu_scan_plan_apply_filter": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32, C.c_uint32]),
+    "rfgpu_scan_plan_apply_between": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_char_p, C.c_uint32, C.c_uint32]),
+    "rfgpu_scan_plan_set_index": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32]),
+    "rfgpu_scan_plan_index": (C.c_uint32, [C.c_void_p]),
+    "rfgpu_scan_plan_describe": (C.c_size_t, [C.c_void_p, C.c_char_p, C.c_size_t]),
+    "rfgpu_scan_execute": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "rfgpu_scan_last_range": (C.c_int32, [C.c_void_p, u64p, u64p]),
+    "rfgpu_table_retain": (C.c_void_p, [C.c_void_p]),
+    "rfgpu_table_release": (None, [C.c_void_p]),
+    "rfgpu_table_num_rows": (C.c_uint64, [C.c_void_p]),
+    "rfgpu_table_num_cols": (C.c_int32, [C.c_void_p]),
+    "rfgpu_table_col_name": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "rfgpu_table_col_nullable": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "rfgpu_table_col_device_ptr": (C.c_void_p, [C.c_void_p, C.c_int32]),
+    "rfgpu_table_import": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), u8p, C.POINTER(C.c_void_p),
+                                       C.POINTER(C.c_void_p), C.c_uint64, C.POINTER(C.c_void_p)]),
+    "rfgpu_table_export": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_void_p),
+                                       C.POINTER(C.c_void_p), u64p]),
+    "rfgpu_table_project": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_char_p),
+                                        C.POINTER(C.c_void_p)]),
+    "rfgpu_table_set_nullable": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32]),
+    "rfgpu_table_import_arrow": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]),
+    "rfgpu_table_export_arrow": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]),
+    "rfgpu_filter": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(FilterPred), C.c_int32, C.POINTER(C.c_void_p)]),
+    "rfgpu_sparql_join": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]),
+    "rfgpu_last_join_algo": (C.c_int32, [C.c_void_p]),
+    "rfgpu_comm_unique_id": (C.c_int32, [u8p]),
+    "rfgpu_comm_init": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, u8p]),
+    "rfgpu_comm_rank": (C.c_int32, [C.c_void_p]),
+    "rfgpu_comm_size": (C.c_int32, [C.c_void_p]),
+    "rfgpu_shuffle": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]),
+    "rfgpu_shuffle_dest": (C.c_uint32, [C.c_uint32, C.c_uint32]),
+    "rfgpu_partition": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_uint32, C.POINTER(C.c_void_p), u64p]),
+    "rfgpu_metrics_get": (C.c_int32, [C.c_void_p, C.POINTER(Metrics)]),
+    "rfgpu_metrics_reset": (C.c_int32, [C.c_void_p]),
+    "rfgpu_profile_enable": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "rfgpu_profile_num_kernels": (C.c_int32, [C.c_void_p]),
+    "rfgpu_profile_get": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), u64p, C.POINTER(C.c_double), u64p]),
+    "rfgpu_timer_start": (C.c_int32, [C.c_void_p]),
+    "rfgpu_timer_stop": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
+    "rfgpu_flush_l2": (C.c_int32, [C.c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """Load librfgpu.so; raises if it has not been built (python __graft_entry__.py or make -C rdf_fusion_b200/csrc)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build the CUDA library first (make -C rdf_fusion_b200/csrc). "
+            "rdf_fusion_b200 has no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib

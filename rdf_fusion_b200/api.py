@@ -1,0 +1,437 @@
+"""Host-side mirror of the reference's operator interface for the hot path, over the C ABI (librfgpu.so).
+
+Names follow the reference (tobixdev/rdf-fusion): `MemIndexScanInstruction::{Traverse,Scan}`,
+`MemIndexScanPredicate::{In,Between,EqualTo,False}` (lib/storage/src/memory/storage/scan_instructions.rs),
+`PlannedPatternScan::{apply_filter, create_stream}` (scan.rs:414-513), `SparqlJoinNode` Inner/Left
+(lib/logical/src/join/logical.rs).  Python is only the harness language here (no Rust toolchain in this image);
+all logic lives behind the C ABI so a Rust crate binds the same entry points.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+
+from . import _ffi as F
+
+
+class RfgpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"rfgpu error {code}: {msg}")
+        self.code = code
+        self.message = msg
+
+
+# ---- scan instruction builders (MemIndexScanInstruction / MemIndexScanPredicate) ----
+@dataclass
+class Pred:
+    kind: int = F.PRED_NONE
+    ids: Sequence[int] = ()
+    lo: int = 0
+    hi: int = 0
+    var: Optional[str] = None
+
+
+def In(*ids) -> Pred:
+    if len(ids) == 1 and not isinstance(ids[0], (int, np.integer)):
+        ids = tuple(ids[0])
+    return Pred(F.PRED_IN, ids=tuple(int(i) for i in ids))
+
+
+def Between(lo, hi) -> Pred:
+    return Pred(F.PRED_BETWEEN, lo=int(lo), hi=int(hi))
+
+
+def EqualTo(var) -> Pred:
+    return Pred(F.PRED_EQUAL_TO, var=var)
+
+
+FALSE = Pred(F.PRED_FALSE)
+
+
+@dataclass
+class Instr:
+    action: int
+    var: Optional[str] = None
+    pred: Optional[Pred] = None
+
+
+def traverse(pred=None) -> Instr:
+    if isinstance(pred, (int, np.integer)):
+        pred = In(int(pred))
+    return Instr(F.TRAVERSE, None, pred)
+
+
+def scan(var, pred=None) -> Instr:
+    return Instr(F.SCAN, var, pred)
+
+
+def make_instructions(gspo: Sequence[Instr]):
+    """-> (ctypes array of 4 rfgpu_scan_instruction, keepalive list)"""
+    assert len(gspo) == 4
+    arr = (F.ScanInstruction * 4)()
+    keep = []
+    for i, ins in enumerate(gspo):
+        arr[i].action = ins.action
+        arr[i].var = ins.var.encode() if ins.var is not None else None
+        p = ins.pred or Pred()
+        arr[i].pred.kind = p.kind
+        if p.kind == F.PRED_IN:
+            ids = (C.c_uint32 * len(p.ids))(*p.ids)
+            keep.append(ids)
+            arr[i].pred.ids = C.cast(ids, F.u32p)
+            arr[i].pred.n_ids = len(p.ids)
+        arr[i].pred.lo = p.lo
+        arr[i].pred.hi = p.hi
+        arr[i].pred.equal_to = p.var.encode() if p.var is not None else None
+    return arr, keep
+
+
+@dataclass
+class FPred:
+    """ID-level FilterExec predicate (rfgpu_filter_pred)."""
+    op: int
+    col: int
+    col2: int = 0
+    value: int = 0
+    hi: int = 0
+    ids: Sequence[int] = ()
+
+
+def make_filter_preds(preds: Sequence[FPred]):
+    arr = (F.FilterPred * max(1, len(preds)))()
+    keep = []
+    for i, p in enumerate(preds):
+        arr[i].op, arr[i].col, arr[i].col2, arr[i].value, arr[i].hi = p.op, p.col, p.col2, p.value, p.hi
+        if p.ids:
+            ids = (C.c_uint32 * len(p.ids))(*p.ids)
+            keep.append(ids)
+            arr[i].ids = C.cast(ids, F.u32p)
+            arr[i].n_ids = len(p.ids)
+    return arr, keep
+
+
+def _u32(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.uint32)
+
+
+class Context:
+    """One CUDA device + stream (rfgpu_ctx)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = F.load()
+        h = C.c_void_p()
+        rc = self.lib.rfgpu_ctx_create(device, C.byref(h))
+        if rc != F.OK:
+            raise RfgpuError(rc, (self.lib.rfgpu_last_error(None) or b"").decode())
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if self.h:
+            self.lib.rfgpu_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def check(self, rc):
+        if rc != F.OK:
+            raise RfgpuError(rc, (self.lib.rfgpu_last_error(self.h) or b"").decode())
+
+    def synchronize(self):
+        self.check(self.lib.rfgpu_ctx_synchronize(self.h))
+
+    # ---- store ----
+    def store(self) -> "Store":
+        return Store(self)
+
+    # ---- tables ----
+    def import_table(self, cols: Dict[str, np.ndarray], nullable: Optional[Dict[str, bool]] = None,
+                     validity: Optional[Dict[str, np.ndarray]] = None) -> "Table":
+        names = list(cols)
+        n = len(next(iter(cols.values()))) if cols else 0
+        arrs = [_u32(cols[k]) for k in names]
+        cn = (C.c_char_p * max(1, len(names)))(*[k.encode() for k in names])
+        nl = (C.c_uint8 * max(1, len(names)))(*[1 if (nullable or {}).get(k, False) else 0 for k in names])
+        vals = (C.c_void_p * max(1, len(names)))(*[a.ctypes.data for a in arrs])
+        vbufs = [np.ascontiguousarray((validity or {}).get(k)) if (validity or {}).get(k) is not None else None for k in names]
+        vptr = (C.c_void_p * max(1, len(names)))(*[(v.ctypes.data if v is not None else None) for v in vbufs])
+        out = C.c_void_p()
+        self.check(self.lib.rfgpu_table_import(self.h, len(names), cn, C.cast(nl, F.u8p), vals, vptr, n, C.byref(out)))
+        return Table(self, out)
+
+    def import_arrow(self, batch) -> "Table":
+        """pyarrow.RecordBatch of UInt32 columns → Table, through the Arrow C Data Interface."""
+        import pyarrow as pa
+        from pyarrow.cffi import ffi
+        c_schema = ffi.new("struct ArrowSchema*")
+        c_array = ffi.new("struct ArrowArray*")
+        sa = pa.StructArray.from_arrays(batch.columns, fields=list(batch.schema))
+        sa._export_to_c(int(ffi.cast("uintptr_t", c_array)), int(ffi.cast("uintptr_t", c_schema)))
+        out = C.c_void_p()
+        try:
+            self.check(self.lib.rfgpu_table_import_arrow(self.h, int(ffi.cast("uintptr_t", c_array)),
+                                                         int(ffi.cast("uintptr_t", c_schema)), C.byref(out)))
+        finally:
+            if c_array.release != ffi.NULL:
+                c_array.release(c_array)
+            if c_schema.release != ffi.NULL:
+                c_schema.release(c_schema)
+        return Table(self, out)
+
+    # ---- metrics / timing ----
+    def metrics(self) -> Dict[str, int]:
+        m = F.Metrics()
+        self.check(self.lib.rfgpu_metrics_get(self.h, C.byref(m)))
+        return {n: int(getattr(m, n)) for n, _ in F.Metrics._fields_}
+
+    def metrics_reset(self):
+        self.check(self.lib.rfgpu_metrics_reset(self.h))
+
+    def profile_enable(self, on=True):
+        self.check(self.lib.rfgpu_profile_enable(self.h, 1 if on else 0))
+
+    def profile(self) -> Dict[str, Dict[str, float]]:
+        out = {}
+        for i in range(self.lib.rfgpu_profile_num_kernels(self.h)):
+            name = C.c_char_p()
+            launches, nbytes = C.c_uint64(), C.c_uint64()
+            ms = C.c_double()
+            self.lib.rfgpu_profile_get(self.h, i, C.byref(name), C.byref(launches), C.byref(ms), C.byref(nbytes))
+            out[name.value.decode()] = {"launches": launches.value, "ms": ms.value, "bytes": nbytes.value}
+        return out
+
+    def timer_start(self):
+        self.check(self.lib.rfgpu_timer_start(self.h))
+
+    def timer_stop(self) -> float:
+        ms = C.c_double()
+        self.check(self.lib.rfgpu_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def flush_l2(self):
+        self.check(self.lib.rfgpu_flush_l2(self.h))
+
+    # ---- multi-GPU ----
+    def comm_unique_id(self) -> bytes:
+        buf = (C.c_uint8 * F.UNIQUE_ID_BYTES)()
+        self.check(self.lib.rfgpu_comm_unique_id(buf))
+        return bytes(buf)
+
+    def comm_init(self, rank: int, n_ranks: int, uid: bytes):
+        buf = (C.c_uint8 * F.UNIQUE_ID_BYTES)(*uid)
+        self.check(self.lib.rfgpu_comm_init(self.h, rank, n_ranks, buf))
+
+
+class Store:
+    """IndexPermutations on the device (rfgpu_store)."""
+
+    def __init__(self, ctx: Context):
+        self.ctx = ctx
+        h = C.c_void_p()
+        ctx.check(ctx.lib.rfgpu_store_create(ctx.h, C.byref(h)))
+        self.h = h
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.ctx.lib.rfgpu_store_release(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def __len__(self):
+        return int(self.ctx.lib.rfgpu_store_len(self.h))
+
+    def add_index(self, perm: int, cols: Sequence, on_device: bool = False):
+        """cols: 4 sorted columns in `perm` level order — numpy arrays, or integer device pointers with `n`."""
+        if on_device:
+            ptrs, n = cols
+            arr = (C.c_void_p * 4)(*ptrs)
+        else:
+            a = [_u32(c) for c in cols]
+            n = len(a[0])
+            arr = (C.c_void_p * 4)(*[x.ctypes.data for x in a])
+        self.ctx.check(self.ctx.lib.rfgpu_store_add_index(self.ctx.h, self.h, perm, arr, n, 1 if on_device else 0))
+
+    def load_quads(self, quads: np.ndarray, perms=(F.GSPO, F.GPOS, F.GOSP)):
+        """Bulk-load an (n,4) array of g,s,p,o ids: host sort + de-duplication per permutation (index build is
+        host-side in the reference too: quad_index.rs:132-143), then upload."""
+        quads = np.ascontiguousarray(quads, dtype=np.uint32).reshape(-1, 4)
+        quads = np.unique(quads, axis=0) if len(quads) else quads
+        for p in perms:
+            comps = [(p >> (2 * i)) & 3 for i in range(4)]
+            cols = [quads[:, c] for c in comps]
+            order = np.lexsort(tuple(reversed(cols))) if len(quads) else np.zeros(0, dtype=np.int64)
+            self.add_index(p, [c[order] for c in cols])
+        return self
+
+    @property
+    def perms(self) -> List[int]:
+        return [int(self.ctx.lib.rfgpu_store_index_perm(self.h, i))
+                for i in range(self.ctx.lib.rfgpu_store_num_indexes(self.h))]
+
+    def plan(self, gspo: Sequence[Instr]) -> "ScanPlan":
+        return ScanPlan(self, gspo)
+
+
+class ScanPlan:
+    """PlannedPatternScan (scan.rs:414-513)."""
+
+    def __init__(self, store: Store, gspo: Sequence[Instr]):
+        self.store = store
+        self.ctx = store.ctx
+        arr, keep = make_instructions(gspo)
+        h = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_scan_plan_create(self.ctx.h, store.h, arr, C.byref(h)))
+        self.h = h
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.ctx.lib.rfgpu_scan_plan_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def apply_filter(self, column: str, op: int, value: int):
+        self.ctx.check(self.ctx.lib.rfgpu_scan_plan_apply_filter(self.ctx.h, self.h, column.encode(), op, value))
+        return self
+
+    def apply_between(self, column: str, lo: int, hi: int):
+        self.ctx.check(self.ctx.lib.rfgpu_scan_plan_apply_between(self.ctx.h, self.h, column.encode(), lo, hi))
+        return self
+
+    def set_index(self, perm: int):
+        self.ctx.check(self.ctx.lib.rfgpu_scan_plan_set_index(self.ctx.h, self.h, perm))
+        return self
+
+    @property
+    def index(self) -> int:
+        return int(self.ctx.lib.rfgpu_scan_plan_index(self.h))
+
+    def describe(self) -> str:
+        n = self.ctx.lib.rfgpu_scan_plan_describe(self.h, None, 0)
+        buf = C.create_string_buffer(n)
+        self.ctx.lib.rfgpu_scan_plan_describe(self.h, buf, n)
+        return buf.value.decode()
+
+    def execute(self, allow_view: bool = False) -> "Table":
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_scan_execute(self.ctx.h, self.h, F.SCAN_ALLOW_VIEW if allow_view else 0,
+                                                       C.byref(out)))
+        return Table(self.ctx, out)
+
+    def last_range(self):
+        a, b = C.c_uint64(), C.c_uint64()
+        self.ctx.lib.rfgpu_scan_last_range(self.ctx.h, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+
+class Table:
+    """Device-resident solution mappings (rfgpu_table): UInt32 columns, 0 = NULL."""
+
+    def __init__(self, ctx: Context, h):
+        self.ctx = ctx
+        self.h = h
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.ctx.lib.rfgpu_table_release(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    @property
+    def num_rows(self) -> int:
+        return int(self.ctx.lib.rfgpu_table_num_rows(self.h))
+
+    @property
+    def names(self) -> List[str]:
+        return [self.ctx.lib.rfgpu_table_col_name(self.h, i).decode()
+                for i in range(self.ctx.lib.rfgpu_table_num_cols(self.h))]
+
+    @property
+    def nullable(self) -> List[bool]:
+        return [bool(self.ctx.lib.rfgpu_table_col_nullable(self.h, i))
+                for i in range(self.ctx.lib.rfgpu_table_num_cols(self.h))]
+
+    def set_nullable(self, col, nullable=True):
+        i = self.names.index(col) if isinstance(col, str) else col
+        self.ctx.check(self.ctx.lib.rfgpu_table_set_nullable(self.h, i, 1 if nullable else 0))
+        return self
+
+    def to_numpy(self, row_off=0, n_rows=None, out: Optional[List[np.ndarray]] = None,
+                 with_validity=False):
+        """-> list of uint32 arrays in column order (0 = NULL) [, validity bitmaps, null counts]"""
+        nc = len(self.names)
+        n = self.num_rows - row_off if n_rows is None else n_rows
+        arrs = out if out is not None else [np.empty(n, dtype=np.uint32) for _ in range(nc)]
+        vals = (C.c_void_p * max(1, nc))(*[a.ctypes.data for a in arrs])
+        if with_validity:
+            bits = [np.zeros((n + 7) // 8, dtype=np.uint8) for _ in range(nc)]
+            vptr = (C.c_void_p * max(1, nc))(*[b.ctypes.data for b in bits])
+            nulls = (C.c_uint64 * max(1, nc))()
+            self.ctx.check(self.ctx.lib.rfgpu_table_export(self.ctx.h, self.h, row_off, n, vals, vptr, nulls))
+            return arrs, bits, list(nulls)[:nc]
+        self.ctx.check(self.ctx.lib.rfgpu_table_export(self.ctx.h, self.h, row_off, n, vals, None, None))
+        return arrs
+
+    def to_arrow(self, row_off=0, n_rows=None):
+        """-> pyarrow.RecordBatch through the Arrow C Data Interface (what arrow-rs `ffi` would import)."""
+        import pyarrow as pa
+        from pyarrow.cffi import ffi
+        n = self.num_rows - row_off if n_rows is None else n_rows
+        c_schema = ffi.new("struct ArrowSchema*")
+        c_array = ffi.new("struct ArrowArray*")
+        self.ctx.check(self.ctx.lib.rfgpu_table_export_arrow(self.ctx.h, self.h, row_off, n,
+                                                             int(ffi.cast("uintptr_t", c_array)),
+                                                             int(ffi.cast("uintptr_t", c_schema))))
+        sa = pa.Array._import_from_c(int(ffi.cast("uintptr_t", c_array)), int(ffi.cast("uintptr_t", c_schema)))
+        return pa.RecordBatch.from_struct_array(sa)
+
+    def filter(self, preds: Sequence[FPred]) -> "Table":
+        arr, keep = make_filter_preds(preds)
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_filter(self.ctx.h, self.h, arr, len(preds), C.byref(out)))
+        return Table(self.ctx, out)
+
+    def join(self, rhs: "Table", join_type: int = F.JOIN_INNER) -> "Table":
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_sparql_join(self.ctx.h, self.h, rhs.h, join_type, C.byref(out)))
+        return Table(self.ctx, out)
+
+    def project(self, cols: Sequence, new_names: Optional[Sequence[str]] = None) -> "Table":
+        names = self.names
+        idx = [names.index(c) if isinstance(c, str) else int(c) for c in cols]
+        ci = (C.c_int32 * max(1, len(idx)))(*idx)
+        nn = None
+        if new_names is not None:
+            nn = (C.c_char_p * max(1, len(idx)))(*[s.encode() if s is not None else None for s in new_names])
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_table_project(self.ctx.h, self.h, len(idx), ci, nn, C.byref(out)))
+        return Table(self.ctx, out)
+
+    def partition(self, key_col, n_parts: int):
+        i = self.names.index(key_col) if isinstance(key_col, str) else key_col
+        counts = (C.c_uint64 * 64)()
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_partition(self.ctx.h, self.h, i, n_parts, C.byref(out), counts))
+        return Table(self.ctx, out), [int(counts[k]) for k in range(n_parts)]
+
+    def shuffle(self, key_col) -> "Table":
+        i = self.names.index(key_col) if isinstance(key_col, str) else key_col
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_shuffle(self.ctx.h, self.h, i, C.byref(out)))
+        return Table(self.ctx, out)
+
+    @property
+    def last_join_algo(self) -> int:
+        return int(self.ctx.lib.rfgpu_last_join_algo(self.ctx.h))

@@ -1,0 +1,334 @@
+// ctx.cu — context, device buffers, metrics/profiling, store (index permutations) of librfgpu.
+#include <cstring>
+#include <mutex>
+
+#include "rf_common.hpp"
+
+namespace rf {
+
+static thread_local std::string g_tls_err;
+
+void set_error(const rfgpu_ctx* ctx, const std::string& msg) {
+  g_tls_err = msg;
+  if (ctx) const_cast<rfgpu_ctx*>(ctx)->err = msg;
+}
+
+Core::~Core() {
+  if (stream) {
+    cudaSetDevice(device);
+    cudaStreamSynchronize(stream);
+    cudaStreamDestroy(stream);
+  }
+}
+
+DevBuf::DevBuf(std::shared_ptr<Core> c, size_t n) : core(std::move(c)), bytes(n) {
+  size_t padded = ((n + kPad - 1) / kPad) * kPad + kPad;
+  RF_CUDA(cudaSetDevice(core->device));
+  RF_CUDA(cudaMallocAsync(&ptr, padded, core->stream));
+}
+
+DevBuf::~DevBuf() {
+  if (ptr) {
+    cudaSetDevice(core->device);
+    cudaFreeAsync(ptr, core->stream);
+  }
+}
+
+KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes) : ctx(c) {
+  ctx->m.kernel_launches++;
+  idx = ctx->kstat_index(name);
+  ctx->kstats[idx].second.launches++;
+  ctx->kstats[idx].second.bytes += bytes;
+  if (ctx->profiling) {
+    RF_CUDA(cudaEventCreate(&a));
+    RF_CUDA(cudaEventCreate(&b));
+    RF_CUDA(cudaEventRecord(a, ctx->stream()));
+  }
+}
+
+KernelScope::~KernelScope() noexcept(false) {
+  cudaError_t e = cudaGetLastError();
+  if (a) {
+    cudaEventRecord(b, ctx->stream());
+    ctx->pending.push_back({idx, a, b});
+  }
+  if (e != cudaSuccess && !std::uncaught_exceptions())
+    throw Error(RFGPU_E_CUDA, std::string("kernel launch failed: ") + ctx->kstats[idx].first + ": " +
+                                  cudaGetErrorString(e));
+}
+
+rfgpu_table* new_table() { return new rfgpu_table(); }
+
+BufRef alloc_col(rfgpu_ctx* ctx, uint64_t rows) { return ctx->alloc(rows * sizeof(uint32_t)); }
+
+int find_col(const rfgpu_table* t, const std::string& name) {
+  for (size_t i = 0; i < t->cols.size(); i++)
+    if (t->cols[i].name == name) return (int)i;
+  return -1;
+}
+
+}  // namespace rf
+
+int rfgpu_ctx::kstat_index(const char* name) {
+  for (size_t i = 0; i < kstats.size(); i++)
+    if (kstats[i].first == name) return (int)i;
+  kstats.push_back({name, rf::KernelStat{}});
+  return (int)kstats.size() - 1;
+}
+
+void rfgpu_ctx::collect_profile() {
+  if (pending.empty()) return;
+  RF_CUDA(cudaStreamSynchronize(core->stream));
+  for (auto& p : pending) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, p.a, p.b);
+    kstats[p.idx].second.ms += ms;
+    cudaEventDestroy(p.a);
+    cudaEventDestroy(p.b);
+  }
+  pending.clear();
+}
+
+// ---- sortedness / uniqueness check of an index permutation ----
+__global__ void k_check_sorted(const uint32_t* __restrict__ c0, const uint32_t* __restrict__ c1,
+                               const uint32_t* __restrict__ c2, const uint32_t* __restrict__ c3, uint64_t n,
+                               unsigned long long* __restrict__ first_bad) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x + 1;
+  uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    uint32_t a0 = c0[i - 1], b0 = c0[i];
+    bool ok;
+    if (a0 != b0) {
+      ok = a0 < b0;
+    } else {
+      uint32_t a1 = c1[i - 1], b1 = c1[i];
+      if (a1 != b1) {
+        ok = a1 < b1;
+      } else {
+        uint32_t a2 = c2[i - 1], b2 = c2[i];
+        if (a2 != b2)
+          ok = a2 < b2;
+        else
+          ok = c3[i - 1] < c3[i];  // strict: the store is a set
+      }
+    }
+    if (!ok) atomicMin(first_bad, (unsigned long long)i);
+  }
+}
+
+extern "C" {
+
+const char* rfgpu_version(void) { return "rfgpu 0.1 (sm_100a)"; }
+
+const char* rfgpu_last_error(const rfgpu_ctx* ctx) { return ctx ? ctx->err.c_str() : rf::g_tls_err.c_str(); }
+
+int32_t rfgpu_ctx_create(int32_t device, rfgpu_ctx** out) {
+  rfgpu_ctx* ctx = nullptr;
+  try {
+    RF_REQUIRE(out != nullptr, RFGPU_E_INVALID, "out is NULL");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+      throw rf::Error(RFGPU_E_NOGPU, std::string("no CUDA device available (") +
+                                         (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0") +
+                                         "); rfgpu has no CPU fallback");
+    RF_REQUIRE(device >= 0 && device < n, RFGPU_E_INVALID, "device index out of range");
+    ctx = new rfgpu_ctx();
+    ctx->core = std::make_shared<rf::Core>();
+    ctx->core->device = device;
+    RF_CUDA(cudaSetDevice(device));
+    RF_CUDA(cudaStreamCreateWithFlags(&ctx->core->stream, cudaStreamNonBlocking));
+    cudaDeviceProp prop;
+    RF_CUDA(cudaGetDeviceProperties(&prop, device));
+    ctx->core->num_sms = prop.multiProcessorCount;
+    // keep freed blocks cached in the stream-ordered pool: operators allocate per call
+    cudaMemPool_t pool;
+    RF_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+    uint64_t thr = UINT64_MAX;
+    RF_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    RF_CUDA(cudaHostAlloc((void**)&ctx->h_scratch, 64 * sizeof(uint64_t), cudaHostAllocDefault));
+    RF_CUDA(cudaEventCreate(&ctx->t0));
+    RF_CUDA(cudaEventCreate(&ctx->t1));
+    *out = ctx;
+    return RFGPU_OK;
+  } catch (const rf::Error& e) {
+    rf::set_error(nullptr, e.what());
+    delete ctx;
+    return e.code;
+  } catch (const std::exception& e) {
+    rf::set_error(nullptr, e.what());
+    delete ctx;
+    return RFGPU_E_EXEC;
+  }
+}
+
+void rfgpu_ctx_destroy(rfgpu_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->core->device);
+  cudaStreamSynchronize(ctx->core->stream);
+  for (auto& p : ctx->pending) {
+    cudaEventDestroy(p.a);
+    cudaEventDestroy(p.b);
+  }
+  if (ctx->t0) cudaEventDestroy(ctx->t0);
+  if (ctx->t1) cudaEventDestroy(ctx->t1);
+  if (ctx->h_scratch) cudaFreeHost(ctx->h_scratch);
+  if (ctx->flush_buf) cudaFree(ctx->flush_buf);
+  ctx->comm.reset();
+  delete ctx;
+}
+
+void* rfgpu_ctx_stream(rfgpu_ctx* ctx) { return ctx ? (void*)ctx->core->stream : nullptr; }
+
+int32_t rfgpu_ctx_synchronize(rfgpu_ctx* ctx) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
+  ctx->sync();
+  RF_API_END(ctx)
+}
+
+// ---- store ----
+int32_t rfgpu_store_create(rfgpu_ctx* ctx, rfgpu_store** out) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx && out, RFGPU_E_INVALID, "NULL argument");
+  *out = new rfgpu_store();
+  RF_API_END(ctx)
+}
+
+rfgpu_store* rfgpu_store_retain(rfgpu_store* s) {
+  if (s) s->refs++;
+  return s;
+}
+
+void rfgpu_store_release(rfgpu_store* s) {
+  if (s && --s->refs == 0) delete s;
+}
+
+int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm, const uint32_t* const cols[4],
+                              uint64_t n_rows, int32_t on_device) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx && s && cols, RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(perm < 256, RFGPU_E_INVALID, "bad permutation code");
+  int seen = 0;
+  for (int i = 0; i < 4; i++) seen |= 1 << ((perm >> (2 * i)) & 3);
+  RF_REQUIRE(seen == 15, RFGPU_E_INVALID, "permutation must name each of G,S,P,O once");
+  RF_REQUIRE(n_rows < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "an index holds at most 2^32-2 rows per GPU");
+  for (auto& ix : s->indexes) RF_REQUIRE(ix.perm != perm, RFGPU_E_INVALID, "permutation already present");
+  if (!s->indexes.empty())
+    RF_REQUIRE(s->indexes[0].rows == n_rows, RFGPU_E_INVALID, "all permutations must hold the same quads");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  rfgpu_index_t ix;
+  ix.perm = perm;
+  ix.rows = n_rows;
+  for (int i = 0; i < 4; i++) {
+    RF_REQUIRE(cols[i] || n_rows == 0, RFGPU_E_INVALID, "NULL column");
+    ix.col[i] = rf::alloc_col(ctx, n_rows);
+    if (n_rows) {
+      RF_CUDA(cudaMemcpyAsync(ix.col[i]->ptr, cols[i], n_rows * 4, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                              ctx->stream()));
+      if (!on_device) ctx->m.h2d_bytes += n_rows * 4;
+    }
+  }
+  if (n_rows > 1) {
+    unsigned long long* bad = (unsigned long long*)ctx->h_scratch;
+    auto d_bad = ctx->alloc(8);
+    RF_CUDA(cudaMemsetAsync(d_bad->ptr, 0xFF, 8, ctx->stream()));
+    {
+      rf::KernelScope ks(ctx, "k_check_sorted");
+      uint32_t blocks = std::min<uint64_t>(rf::div_up(n_rows, 256), (uint64_t)ctx->core->num_sms * 8);
+      k_check_sorted<<<blocks, 256, 0, ctx->stream()>>>(ix.col[0]->as<uint32_t>(), ix.col[1]->as<uint32_t>(),
+                                                        ix.col[2]->as<uint32_t>(), ix.col[3]->as<uint32_t>(), n_rows,
+                                                        d_bad->as<unsigned long long>());
+    }
+    RF_CUDA(cudaMemcpyAsync(bad, d_bad->ptr, 8, cudaMemcpyDeviceToHost, ctx->stream()));
+    ctx->sync();
+    if (*bad != ~0ull)
+      throw rf::Error(RFGPU_E_INVALID, "index columns are not strictly sorted in permutation order at row " +
+                                           std::to_string(*bad));
+  } else {
+    ctx->sync();
+  }
+  s->indexes.push_back(std::move(ix));
+  RF_API_END(ctx)
+}
+
+uint64_t rfgpu_store_len(const rfgpu_store* s) { return s && !s->indexes.empty() ? s->indexes[0].rows : 0; }
+int32_t rfgpu_store_num_indexes(const rfgpu_store* s) { return s ? (int32_t)s->indexes.size() : 0; }
+uint32_t rfgpu_store_index_perm(const rfgpu_store* s, int32_t i) {
+  return s && i >= 0 && i < (int32_t)s->indexes.size() ? s->indexes[i].perm : 0xFFFFFFFFu;
+}
+
+// ---- metrics / profiling / timing ----
+int32_t rfgpu_metrics_get(const rfgpu_ctx* ctx, rfgpu_metrics* out) {
+  if (!ctx || !out) return RFGPU_E_INVALID;
+  *out = ctx->m;
+  return RFGPU_OK;
+}
+
+int32_t rfgpu_metrics_reset(rfgpu_ctx* ctx) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
+  ctx->collect_profile();
+  ctx->m = rfgpu_metrics{};
+  ctx->kstats.clear();
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_profile_enable(rfgpu_ctx* ctx, int32_t on) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
+  ctx->collect_profile();
+  ctx->profiling = on != 0;
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_profile_num_kernels(rfgpu_ctx* ctx) {
+  if (!ctx) return 0;
+  try {
+    ctx->collect_profile();
+  } catch (...) {
+  }
+  return (int32_t)ctx->kstats.size();
+}
+
+int32_t rfgpu_profile_get(rfgpu_ctx* ctx, int32_t i, const char** name, uint64_t* launches, double* total_ms,
+                          uint64_t* algorithmic_bytes) {
+  if (!ctx || i < 0 || i >= (int32_t)ctx->kstats.size()) return RFGPU_E_INVALID;
+  if (name) *name = ctx->kstats[i].first.c_str();
+  if (launches) *launches = ctx->kstats[i].second.launches;
+  if (total_ms) *total_ms = ctx->kstats[i].second.ms;
+  if (algorithmic_bytes) *algorithmic_bytes = ctx->kstats[i].second.bytes;
+  return RFGPU_OK;
+}
+
+int32_t rfgpu_timer_start(rfgpu_ctx* ctx) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
+  RF_CUDA(cudaEventRecord(ctx->t0, ctx->stream()));
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_timer_stop(rfgpu_ctx* ctx, double* elapsed_ms) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx && elapsed_ms, RFGPU_E_INVALID, "NULL argument");
+  RF_CUDA(cudaEventRecord(ctx->t1, ctx->stream()));
+  RF_CUDA(cudaEventSynchronize(ctx->t1));
+  float ms = 0;
+  RF_CUDA(cudaEventElapsedTime(&ms, ctx->t0, ctx->t1));
+  *elapsed_ms = ms;
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_flush_l2(rfgpu_ctx* ctx) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
+  if (!ctx->flush_buf) {
+    ctx->flush_bytes = 256ull << 20;  // 2x the 126 MB L2
+    RF_CUDA(cudaSetDevice(ctx->core->device));
+    RF_CUDA(cudaMalloc(&ctx->flush_buf, ctx->flush_bytes));
+  }
+  RF_CUDA(cudaMemsetAsync(ctx->flush_buf, 0x5A, ctx->flush_bytes, ctx->stream()));
+  RF_API_END(ctx)
+}
+
+}  // extern "C"

@@ -1,0 +1,323 @@
+// filter.cu — kernel 2: fused predicate evaluation + order-preserving stream compaction, and the device-wide scan.
+//
+// Replaces (a) the selection-vector path of the scan — compute_selection_vector / apply_predicate + arrow `filter`
+// per column (lib/storage/src/memory/storage/scan.rs:171-204,264-340) — and (b) DataFusion's FilterExec over
+// object-id columns (predicates built by lib/logical/src/patterns/rewrite.rs:68-148 and
+// lib/logical/src/expr_builder.rs:58-60,931-959).  One pass: every predicate column and every output column is read
+// once, the surviving rows are written once, in input order.
+//
+// Shape: tile = 4096 rows per CTA (256 threads x 16 rows, warp-striped so loads coalesce); __ballot_sync/__popc give the
+// rank inside a warp, a shared-memory scan over the 8 warp totals the rank inside the CTA, a decoupled look-back over
+// tile aggregates the global rank; survivors are staged in shared memory per column and written out coalesced.
+#include <algorithm>
+
+#include "rf_common.hpp"
+#include "rf_device.cuh"
+
+namespace rf {
+
+constexpr int kFThreads = 256;
+constexpr int kFItems = 16;
+constexpr int kFTile = kFThreads * kFItems;  // 4096 rows
+
+struct FilterArgs {
+  DevPred preds[kMaxPreds];
+  int32_t n_preds;
+  int32_t n_cols;
+  const uint32_t* src[kMaxCols];
+  uint32_t* dst[kMaxCols];
+  uint64_t n;
+};
+
+__device__ __forceinline__ bool eval_preds(const FilterArgs& A, uint64_t row) {
+  // SQL three-valued logic with 0 = NULL: a comparison involving NULL is not TRUE → row dropped.
+  for (int i = 0; i < A.n_preds; i++) {
+    const DevPred& p = A.preds[i];
+    uint32_t v = __ldg(p.a + row);
+    bool ok;
+    switch (p.op) {
+      case RFGPU_F_EQ_CONST: ok = v != 0 && v == p.value; break;
+      case RFGPU_F_NE_CONST: ok = v != 0 && p.value != 0 && v != p.value; break;
+      case RFGPU_F_EQ_COL: { uint32_t w = __ldg(p.b + row); ok = v != 0 && v == w; break; }
+      case RFGPU_F_NE_COL: { uint32_t w = __ldg(p.b + row); ok = v != 0 && w != 0 && v != w; break; }
+      case RFGPU_F_BETWEEN: ok = v != 0 && v >= p.value && v <= p.hi; break;
+      case RFGPU_F_IN: {
+        ok = false;
+        if (v != 0) {
+          if (p.ids == nullptr) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) ok |= (k < (int)p.n_ids) && (p.inl[k] == v);
+          } else {
+            uint32_t lo = 0, hi = p.n_ids;
+            while (lo < hi) {
+              uint32_t mid = (lo + hi) >> 1;
+              uint32_t x = __ldg(p.ids + mid);
+              if (x < v) lo = mid + 1; else hi = mid;
+            }
+            ok = lo < p.n_ids && __ldg(p.ids + lo) == v;
+          }
+        }
+        break;
+      }
+      case RFGPU_F_IS_NULL: ok = v == 0; break;
+      default: ok = v != 0; break;  // RFGPU_F_IS_NOT_NULL
+    }
+    if (!ok) return false;
+  }
+  return true;
+}
+
+__global__ void __launch_bounds__(kFThreads)
+k_filter_compact(const __grid_constant__ FilterArgs A, unsigned long long* __restrict__ status,
+                 unsigned long long* __restrict__ total) {
+  __shared__ uint32_t s_stage[kFTile];
+  __shared__ uint32_t s_warp[kFThreads / 32 + 1];
+  __shared__ unsigned long long s_base;
+
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t tile = blockIdx.x;
+  const uint64_t warp_row0 = (uint64_t)tile * kFTile + (uint64_t)warp * (32 * kFItems);
+
+  uint32_t ballots[kFItems];
+  uint32_t wcount = 0;
+#pragma unroll
+  for (int k = 0; k < kFItems; k++) {
+    uint64_t row = warp_row0 + k * 32 + lane;
+    bool sel = row < A.n && eval_preds(A, row);
+    ballots[k] = __ballot_sync(0xFFFFFFFFu, sel);
+    wcount += __popc(ballots[k]);
+  }
+  if (lane == 0) s_warp[warp] = wcount;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t v = lane < kFThreads / 32 ? s_warp[lane] : 0;
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if ((int)lane >= o) incl += t;
+    }
+    uint32_t btotal = __shfl_sync(0xFFFFFFFFu, incl, kFThreads / 32 - 1);
+    if (lane < kFThreads / 32) s_warp[lane] = incl - v;  // exclusive warp offsets
+    if (lane == 0) s_warp[kFThreads / 32] = btotal;
+    unsigned long long excl = dev::lookback_exclusive(status, tile, btotal);
+    if (lane == 0) {
+      s_base = excl;
+      if (tile == gridDim.x - 1) *total = excl + btotal;
+    }
+  }
+  __syncthreads();
+  const uint32_t woff = s_warp[warp];
+  const uint32_t btotal = s_warp[kFThreads / 32];
+  const unsigned long long base = s_base;
+  if (btotal == 0) return;
+  const uint32_t lt = (1u << lane) - 1u;
+
+  for (int c = 0; c < A.n_cols; c++) {
+    const uint32_t* __restrict__ src = A.src[c];
+    uint32_t o = woff;
+#pragma unroll
+    for (int k = 0; k < kFItems; k++) {
+      uint32_t b = ballots[k];
+      if ((b >> lane) & 1u) s_stage[o + __popc(b & lt)] = __ldg(src + warp_row0 + k * 32 + lane);
+      o += __popc(b);
+    }
+    __syncthreads();
+    uint32_t* __restrict__ dst = A.dst[c] + base;
+    for (uint32_t i = tid; i < btotal; i += kFThreads) dst[i] = s_stage[i];
+    __syncthreads();
+  }
+}
+
+uint64_t filter_compact(rfgpu_ctx* ctx, const std::vector<DevPred>& preds, const std::vector<const uint32_t*>& src,
+                        uint64_t n, std::vector<BufRef>* out, const char* kernel_name, uint64_t bytes_in) {
+  RF_REQUIRE(preds.size() <= (size_t)kMaxPreds, RFGPU_E_UNSUPPORTED, "more than 8 conjuncts in one filter");
+  RF_REQUIRE(src.size() <= (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 columns in one filter");
+  out->clear();
+  if (n == 0) {
+    for (size_t c = 0; c < src.size(); c++) out->push_back(alloc_col(ctx, 0));
+    return 0;
+  }
+  FilterArgs A{};
+  A.n_preds = (int32_t)preds.size();
+  for (size_t i = 0; i < preds.size(); i++) A.preds[i] = preds[i];
+  A.n_cols = (int32_t)src.size();
+  A.n = n;
+  for (size_t c = 0; c < src.size(); c++) {
+    out->push_back(alloc_col(ctx, n));  // worst case; stream-ordered pool keeps this cheap
+    A.src[c] = src[c];
+    A.dst[c] = (*out)[c]->as<uint32_t>();
+  }
+  uint32_t tiles = div_up(n, kFTile);
+  auto status = ctx->alloc((uint64_t)tiles * 8 + 8);
+  RF_CUDA(cudaMemsetAsync(status->ptr, 0, (uint64_t)tiles * 8 + 8, ctx->stream()));
+  unsigned long long* d_total = status->as<unsigned long long>() + tiles;
+  {
+    KernelScope ks(ctx, kernel_name, bytes_in);
+    k_filter_compact<<<tiles, kFThreads, 0, ctx->stream()>>>(A, status->as<unsigned long long>(), d_total);
+  }
+  RF_CUDA(cudaMemcpyAsync(ctx->h_scratch, d_total, 8, cudaMemcpyDeviceToHost, ctx->stream()));
+  ctx->sync();
+  uint64_t kept = ctx->h_scratch[0];
+  // account the written bytes too
+  ctx->kstats[ctx->kstat_index(kernel_name)].second.bytes += 4ull * src.size() * kept;
+  return kept;
+}
+
+// ---------------- device-wide exclusive scan (u32) ----------------
+constexpr int kSThreads = 256;
+constexpr int kSItems = 16;
+constexpr int kSTile = kSThreads * kSItems;
+
+__global__ void __launch_bounds__(kSThreads)
+k_exclusive_scan_u32(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, uint64_t n,
+                     unsigned long long* __restrict__ status, unsigned long long* __restrict__ total) {
+  __shared__ uint32_t s_warp[kSThreads / 32];
+  __shared__ unsigned long long s_base;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t tile = blockIdx.x;
+  const uint64_t t0 = (uint64_t)tile * kSTile + (uint64_t)tid * kSItems;  // blocked: 16 consecutive items per thread
+  uint32_t v[kSItems];
+  if (t0 + kSItems <= n) {
+    const uint4* p = reinterpret_cast<const uint4*>(in + t0);  // `in` is 256-B aligned (own allocation)
+#pragma unroll
+    for (int q = 0; q < kSItems / 4; q++) {
+      uint4 x = p[q];
+      v[4 * q] = x.x; v[4 * q + 1] = x.y; v[4 * q + 2] = x.z; v[4 * q + 3] = x.w;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < kSItems; k++) v[k] = t0 + k < n ? in[t0 + k] : 0;
+  }
+  uint32_t tsum = 0;
+#pragma unroll
+  for (int k = 0; k < kSItems; k++) tsum += v[k];
+  uint32_t incl = tsum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if ((int)lane >= o) incl += t;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = lane < kSThreads / 32 ? s_warp[lane] : 0;
+    uint32_t wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+      if ((int)lane >= o) wi += t;
+    }
+    uint32_t btotal = __shfl_sync(0xFFFFFFFFu, wi, kSThreads / 32 - 1);
+    if (lane < kSThreads / 32) s_warp[lane] = wi - w;
+    unsigned long long excl = dev::lookback_exclusive(status, tile, btotal);
+    if (lane == 0) {
+      s_base = excl;
+      if (tile == gridDim.x - 1) *total = excl + btotal;
+    }
+  }
+  __syncthreads();
+  uint32_t run = (uint32_t)s_base + s_warp[warp] + (incl - tsum);
+  uint32_t o[kSItems];
+#pragma unroll
+  for (int k = 0; k < kSItems; k++) {
+    o[k] = run;
+    run += v[k];
+  }
+  if (t0 + kSItems <= n) {
+    uint4* p = reinterpret_cast<uint4*>(out + t0);
+#pragma unroll
+    for (int q = 0; q < kSItems / 4; q++) p[q] = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < kSItems; k++)
+      if (t0 + k < n) out[t0 + k] = o[k];
+  }
+}
+
+// in / out must be 16-B aligned (own allocations are); out may alias in.  The total (u64) lands in *h_total_slot
+// (pinned) after the caller synchronises the stream.
+void exclusive_scan_u32(rfgpu_ctx* ctx, const uint32_t* in, uint32_t* out, uint64_t n, uint64_t* h_total_slot) {
+  if (n == 0) {
+    if (h_total_slot) *h_total_slot = 0;
+    return;
+  }
+  uint32_t tiles = div_up(n, kSTile);
+  auto status = ctx->alloc((uint64_t)tiles * 8 + 8);
+  RF_CUDA(cudaMemsetAsync(status->ptr, 0, (uint64_t)tiles * 8 + 8, ctx->stream()));
+  unsigned long long* d_total = status->as<unsigned long long>() + tiles;
+  {
+    KernelScope ks(ctx, "k_exclusive_scan_u32", 8 * n);
+    k_exclusive_scan_u32<<<tiles, kSThreads, 0, ctx->stream()>>>(in, out, n, status->as<unsigned long long>(), d_total);
+  }
+  if (h_total_slot) RF_CUDA(cudaMemcpyAsync(h_total_slot, d_total, 8, cudaMemcpyDeviceToHost, ctx->stream()));
+  // `status` is freed stream-ordered after the kernel (cudaFreeAsync in ~DevBuf)
+}
+
+}  // namespace rf
+
+extern "C" int32_t rfgpu_filter(rfgpu_ctx* ctx, const rfgpu_table* in, const rfgpu_filter_pred* preds, int32_t n,
+                                rfgpu_table** out) {
+  RF_API_BEGIN
+  using namespace rf;
+  RF_REQUIRE(ctx && in && out && n >= 0 && (preds || n == 0), RFGPU_E_INVALID, "NULL / negative argument");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  int nc = (int)in->cols.size();
+  std::vector<DevPred> dp;
+  std::vector<BufRef> keep;
+  uint64_t pred_cols_mask = 0;
+  for (int i = 0; i < n; i++) {
+    const rfgpu_filter_pred& p = preds[i];
+    RF_REQUIRE(p.op >= 0 && p.op <= RFGPU_F_IS_NOT_NULL, RFGPU_E_INVALID, "bad filter op");
+    RF_REQUIRE(p.col >= 0 && p.col < nc, RFGPU_E_INVALID, "filter column out of range");
+    DevPred d{};
+    d.op = p.op;
+    d.a = in->cols[p.col].data;
+    pred_cols_mask |= 1ull << p.col;
+    d.value = p.value;
+    d.hi = p.hi;
+    if (p.op == RFGPU_F_EQ_COL || p.op == RFGPU_F_NE_COL) {
+      RF_REQUIRE(p.col2 >= 0 && p.col2 < nc, RFGPU_E_INVALID, "second filter column out of range");
+      d.b = in->cols[p.col2].data;
+      pred_cols_mask |= 1ull << p.col2;
+    }
+    if (p.op == RFGPU_F_IN) {
+      RF_REQUIRE(p.ids || p.n_ids == 0, RFGPU_E_INVALID, "IN without ids");
+      std::vector<uint32_t> ids(p.ids, p.ids + p.n_ids);
+      std::sort(ids.begin(), ids.end());
+      ids.erase(std::unique(ids.begin(), ids.end()), ids.end());
+      d.n_ids = (uint32_t)ids.size();
+      if (ids.size() <= 8) {
+        for (size_t k = 0; k < ids.size(); k++) d.inl[k] = ids[k];
+      } else {
+        auto b = ctx->alloc(ids.size() * 4);
+        RF_CUDA(cudaMemcpyAsync(b->ptr, ids.data(), ids.size() * 4, cudaMemcpyHostToDevice, ctx->stream()));
+        ctx->sync();  // `ids` is a host temporary
+        d.ids = b->as<uint32_t>();
+        keep.push_back(b);
+      }
+    }
+    dp.push_back(d);
+  }
+  std::vector<const uint32_t*> src;
+  for (auto& c : in->cols) src.push_back(c.data);
+  // algorithmic bytes: predicate columns once + remaining output columns once (+ output, added later)
+  uint64_t bytes_in = 4ull * in->rows * (uint64_t)std::max<int>(nc, __builtin_popcountll(pred_cols_mask));
+  std::vector<BufRef> bufs;
+  uint64_t kept = filter_compact(ctx, dp, src, in->rows, &bufs, "k_filter_compact", bytes_in);
+  std::unique_ptr<rfgpu_table> t(new_table());
+  t->rows = kept;
+  for (int c = 0; c < nc; c++) {
+    Column col;
+    col.name = in->cols[c].name;
+    col.nullable = in->cols[c].nullable;
+    col.owner = bufs[c];
+    col.data = bufs[c]->as<uint32_t>();
+    t->cols.push_back(std::move(col));
+  }
+  ctx->m.filter_rows_in += in->rows;
+  ctx->m.filter_rows_out += kept;
+  ctx->m.algorithmic_bytes += bytes_in + 4ull * nc * kept;
+  *out = t.release();
+  RF_API_END(ctx)
+}

@@ -1,0 +1,407 @@
+// join.cu — SPARQL join on device-resident solution tables: lowering decision + orchestration of kernel 3.
+//
+// Mirrors SparqlJoinLoweringRule::rewrite_sparql_join (lib/logical/src/join/rewrite.rs:71-111):
+//   no shared variable            → CrossJoinExec / keyless Left join            (:76-96)
+//   no shared column nullable     → equi hash join, NullEqualsNothing            (:126-168)
+//   otherwise                     → compatible-mapping join + COALESCE           (:183-221, is_compatible.rs:170-182)
+// The compatible join is NOT run as the reference's O(Nl*Nr) nested loop: rows are split by the null mask of their key
+// columns; class pair (ml, mr) is an equi join on the keys bound on both sides (or a product when there are none),
+// which yields exactly the pairs with  ∀k: l.k IS NULL ∨ r.k IS NULL ∨ l.k = r.k.
+#include <algorithm>
+
+#include "join_kernels.cuh"
+
+namespace rf {
+
+namespace {
+
+__global__ void k_iota(uint32_t* __restrict__ out, uint64_t n) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) out[i] = (uint32_t)i + 1;  // +1: 0 would read as NULL
+}
+
+// flag[orig_row] = 1 for every probe row that produced an entry (orig = hidden[m_row[q]] - 1)
+__global__ void k_mark_entries(const uint32_t* __restrict__ m_row, uint64_t n_entries,
+                               const uint32_t* __restrict__ hidden, uint32_t* __restrict__ flag) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < n_entries; i += stride) flag[hidden[m_row ? m_row[i] : i] - 1] = 1;
+}
+
+uint32_t grid_for(rfgpu_ctx* ctx, uint64_t n, int threads = 256) {
+  return (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(n, threads), (uint64_t)ctx->core->num_sms * 16));
+}
+
+struct ProbeResult {
+  bool cross = false;
+  uint64_t n_left = 0, n_right = 0;  // cross
+  BufRef m_row, m_gs, m_off, rowids;
+  uint64_t n_entries = 0, n_out = 0;
+};
+
+// build a hash table over (bk0[,bk1]) and probe it with (pk0[,pk1]); no output rows are written yet
+ProbeResult hash_probe(rfgpu_ctx* ctx, int nk, const uint32_t* bk0, const uint32_t* bk1, uint64_t nb,
+                       const uint32_t* pk0, const uint32_t* pk1, uint64_t np, bool left) {
+  ProbeResult R;
+  if (np == 0) return R;
+  RF_REQUIRE(nk == 1 || nk == 2, RFGPU_E_UNSUPPORTED, "hash join supports 1 or 2 key columns");
+  // ---- build ----
+  uint64_t cap = 1024;
+  while (cap < 2 * nb) cap <<= 1;
+  RF_REQUIRE(cap <= (1ull << 31), RFGPU_E_UNSUPPORTED, "build side too large for one hash table");
+  const uint32_t mask = (uint32_t)(cap - 1);
+  const size_t ksz = nk == 1 ? 4 : 8;
+  BufRef keys = ctx->alloc(cap * ksz);
+  BufRef offs_raw = ctx->alloc((cap + 1 + 3) * 4);  // offs = raw + 3 so that offs + 1 is 16-B aligned for the scan
+  uint32_t* offs = offs_raw->as<uint32_t>() + 3;
+  BufRef row_slot = ctx->alloc(std::max<uint64_t>(nb, 1) * 4);
+  R.rowids = ctx->alloc(std::max<uint64_t>(nb, 1) * 4);
+  RF_CUDA(cudaMemsetAsync(keys->ptr, 0, cap * ksz, ctx->stream()));
+  RF_CUDA(cudaMemsetAsync(offs_raw->ptr, 0, (cap + 4) * 4, ctx->stream()));
+  if (nb) {
+    {
+      KernelScope ks(ctx, nk == 1 ? "k_join_build_insert<1>" : "k_join_build_insert<2>", 4ull * nk * nb);
+      if (nk == 1)
+        k_join_build_insert<1><<<grid_for(ctx, nb), 256, 0, ctx->stream()>>>(bk0, bk1, nb, keys->as<uint32_t>(), offs, mask,
+                                                                            row_slot->as<uint32_t>());
+      else
+        k_join_build_insert<2><<<grid_for(ctx, nb), 256, 0, ctx->stream()>>>(
+            bk0, bk1, nb, keys->as<unsigned long long>(), offs, mask, row_slot->as<uint32_t>());
+    }
+    exclusive_scan_u32(ctx, offs + 1, offs + 1, cap, nullptr);
+    {
+      KernelScope ks(ctx, "k_join_build_fill");
+      k_join_build_fill<<<grid_for(ctx, nb), 256, 0, ctx->stream()>>>(row_slot->as<uint32_t>(), nb, offs,
+                                                                     R.rowids->as<uint32_t>());
+    }
+  }
+  // ---- probe ----
+  const uint32_t n_tiles = div_up(np, kPTile);
+  R.m_row = ctx->alloc(np * 4);
+  R.m_gs = ctx->alloc(np * 4);
+  R.m_off = ctx->alloc(np * 4 + 4);
+  BufRef status = ctx->alloc(((uint64_t)n_tiles * 2 + 2) * 8);
+  RF_CUDA(cudaMemsetAsync(status->ptr, 0, ((uint64_t)n_tiles * 2 + 2) * 8, ctx->stream()));
+  ProbeArgs A{};
+  A.k0 = pk0;
+  A.k1 = pk1;
+  A.n = np;
+  A.keys = keys->ptr;
+  A.offs = offs;
+  A.mask = mask;
+  A.left = left ? 1 : 0;
+  A.m_row = R.m_row->as<uint32_t>();
+  A.m_gs = R.m_gs->as<uint32_t>();
+  A.m_off = R.m_off->as<uint32_t>();
+  A.st_cnt = status->as<unsigned long long>();
+  A.st_out = A.st_cnt + n_tiles;
+  A.totals = A.st_out + n_tiles;
+  A.n_tiles = n_tiles;
+  {
+    // persistent CTAs: every CTA must be co-resident (look-back waits on lower tiles owned by other CTAs)
+    int per_sm = 0;
+    if (nk == 1)
+      RF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_join_probe<1>, kPThreads, 0));
+    else
+      RF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_join_probe<2>, kPThreads, 0));
+    RF_REQUIRE(per_sm > 0, RFGPU_E_EXEC, "probe kernel cannot be resident");
+    uint32_t grid = std::min<uint32_t>(n_tiles, (uint32_t)(ctx->core->num_sms * per_sm));
+    KernelScope ks(ctx, nk == 1 ? "k_join_probe<1>" : "k_join_probe<2>", 4ull * nk * np);
+    if (nk == 1)
+      k_join_probe<1><<<grid, kPThreads, 0, ctx->stream()>>>(A);
+    else
+      k_join_probe<2><<<grid, kPThreads, 0, ctx->stream()>>>(A);
+  }
+  RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 8, A.totals, 16, cudaMemcpyDeviceToHost, ctx->stream()));
+  ctx->sync();
+  R.n_entries = ctx->h_scratch[8];
+  R.n_out = ctx->h_scratch[9];
+  RF_REQUIRE(R.n_out < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED,
+             "join output exceeds 2^32-2 rows on one GPU (" + std::to_string(R.n_out) + ")");
+  return R;
+}
+
+void expand(rfgpu_ctx* ctx, const ProbeResult& P, const std::vector<OutColSpec>& specs,
+            const std::vector<uint32_t*>& dst, uint64_t dst_off) {
+  if (P.n_out == 0 || specs.empty()) return;
+  RF_REQUIRE(specs.size() <= (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 output columns in one join");
+  uint64_t bytes = 4ull * specs.size() * P.n_out;
+  if (P.cross) {
+    CrossArgs C{};
+    C.n_left = P.n_left;
+    C.n_right = P.n_right;
+    C.n_out = P.n_out;
+    C.n_cols = (int32_t)specs.size();
+    for (size_t c = 0; c < specs.size(); c++) {
+      C.cols[c] = specs[c];
+      C.dst[c] = dst[c] + dst_off;
+    }
+    KernelScope ks(ctx, "k_cross_expand", bytes);
+    k_cross_expand<<<grid_for(ctx, P.n_out), 256, 0, ctx->stream()>>>(C);
+    return;
+  }
+  const uint32_t n_tiles = div_up(P.n_out, kETile);
+  BufRef tile_first = ctx->alloc((uint64_t)n_tiles * 4);
+  {
+    KernelScope ks(ctx, "k_join_tile_first");
+    k_join_tile_first<<<div_up(n_tiles, 256), 256, 0, ctx->stream()>>>(P.m_off->as<uint32_t>(), P.n_entries, n_tiles,
+                                                                      tile_first->as<uint32_t>());
+  }
+  ExpandArgs E{};
+  E.m_row = P.m_row->as<uint32_t>();
+  E.m_gs = P.m_gs->as<uint32_t>();
+  E.m_off = P.m_off->as<uint32_t>();
+  E.tile_first = tile_first->as<uint32_t>();
+  E.rowids = P.rowids->as<uint32_t>();
+  E.n_entries = P.n_entries;
+  E.n_out = P.n_out;
+  E.n_cols = (int32_t)specs.size();
+  for (size_t c = 0; c < specs.size(); c++) {
+    E.cols[c] = specs[c];
+    E.dst[c] = dst[c] + dst_off;
+  }
+  KernelScope ks(ctx, "k_join_expand", bytes);
+  k_join_expand<<<n_tiles, 256, 0, ctx->stream()>>>(E);
+}
+
+struct KeyPair { int l, r; };
+
+// rows of `t` whose key columns have null mask `m` (bit k set ⇔ key k bound); `extra` rides along as last column
+std::vector<BufRef> split_class(rfgpu_ctx* ctx, const rfgpu_table* t, const std::vector<int>& keycols, uint32_t m,
+                                const uint32_t* extra, uint64_t* rows) {
+  std::vector<DevPred> preds;
+  for (size_t k = 0; k < keycols.size(); k++) {
+    DevPred d{};
+    d.op = (m >> k) & 1 ? RFGPU_F_IS_NOT_NULL : RFGPU_F_IS_NULL;
+    d.a = t->cols[keycols[k]].data;
+    preds.push_back(d);
+  }
+  std::vector<const uint32_t*> src;
+  for (auto& c : t->cols) src.push_back(c.data);
+  if (extra) src.push_back(extra);
+  std::vector<BufRef> out;
+  *rows = filter_compact(ctx, preds, src, t->rows, &out, "k_join_class_split", 4ull * src.size() * t->rows);
+  return out;
+}
+
+}  // namespace
+
+rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table* R, int join_type) {
+  RF_REQUIRE(join_type == RFGPU_JOIN_INNER || join_type == RFGPU_JOIN_LEFT, RFGPU_E_INVALID, "bad join type");
+  const bool left = join_type == RFGPU_JOIN_LEFT;
+  // join keys: shared variable names, sorted (join/rewrite.rs:95-99)
+  std::vector<std::pair<std::string, KeyPair>> shared;
+  for (size_t i = 0; i < L->cols.size(); i++) {
+    int j = find_col(R, L->cols[i].name);
+    if (j >= 0) shared.push_back({L->cols[i].name, {(int)i, j}});
+  }
+  std::sort(shared.begin(), shared.end(), [](auto& a, auto& b) { return a.first < b.first; });
+  std::vector<KeyPair> keys;
+  for (auto& s : shared) keys.push_back(s.second);
+  bool any_nullable = false;
+  for (auto& k : keys) any_nullable |= L->cols[k.l].nullable || R->cols[k.r].nullable;
+  const int algo = keys.empty() ? RFGPU_JOIN_ALGO_CROSS : (any_nullable ? RFGPU_JOIN_ALGO_COMPATIBLE : RFGPU_JOIN_ALGO_EQUI);
+  ctx->last_join_algo = algo;
+
+  // output schema: lhs fields, then rhs-only fields (join/logical.rs:251-279)
+  std::vector<int> rhs_only;
+  for (size_t j = 0; j < R->cols.size(); j++) {
+    bool is_key = false;
+    for (auto& k : keys) is_key |= k.r == (int)j;
+    if (!is_key) rhs_only.push_back((int)j);
+  }
+  const size_t nl = L->cols.size(), nout = nl + rhs_only.size();
+  RF_REQUIRE(nout <= (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 output columns in one join");
+  std::unique_ptr<rfgpu_table> T(new_table());
+  for (size_t i = 0; i < nl; i++) {
+    Column c;
+    c.name = L->cols[i].name;
+    c.nullable = L->cols[i].nullable;
+    T->cols.push_back(c);
+  }
+  for (int j : rhs_only) {
+    Column c;
+    c.name = R->cols[j].name;
+    c.nullable = left ? true : R->cols[j].nullable;
+    T->cols.push_back(c);
+  }
+  auto finish = [&](std::vector<BufRef>& bufs, uint64_t rows) {
+    for (size_t c = 0; c < nout; c++) {
+      T->cols[c].owner = bufs[c];
+      T->cols[c].data = bufs[c]->as<uint32_t>();
+    }
+    T->rows = rows;
+    ctx->m.join_rows_out += rows;
+    ctx->m.algorithmic_bytes += 4ull * (nl * L->rows + R->cols.size() * R->rows + nout * rows);
+    return T.release();
+  };
+  auto alloc_out = [&](uint64_t rows) {
+    std::vector<BufRef> b;
+    for (size_t c = 0; c < nout; c++) b.push_back(alloc_col(ctx, rows));
+    return b;
+  };
+  auto raw = [&](std::vector<BufRef>& b) {
+    std::vector<uint32_t*> p;
+    for (auto& x : b) p.push_back(x->as<uint32_t>());
+    return p;
+  };
+
+  if (algo == RFGPU_JOIN_ALGO_CROSS) {
+    ctx->m.join_probe_rows += L->rows;
+    ctx->m.join_build_rows += R->rows;
+    ProbeResult P;
+    P.cross = true;
+    P.n_left = L->rows;
+    P.n_right = R->rows;
+    bool pad = left && R->rows == 0;  // keyless Left join with an empty rhs keeps lhs padded with NULLs
+    if (pad) P.n_right = 1;
+    unsigned __int128 prod = (unsigned __int128)P.n_left * P.n_right;
+    RF_REQUIRE(prod < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "cross join output exceeds 2^32-2 rows");
+    P.n_out = (uint64_t)prod;
+    std::vector<OutColSpec> specs;
+    for (size_t i = 0; i < nl; i++) specs.push_back({L->cols[i].data, nullptr});
+    for (int j : rhs_only) specs.push_back({nullptr, pad ? nullptr : R->cols[j].data});
+    auto bufs = alloc_out(P.n_out);
+    expand(ctx, P, specs, raw(bufs), 0);
+    return finish(bufs, P.n_out);
+  }
+
+  if (algo == RFGPU_JOIN_ALGO_EQUI) {
+    RF_REQUIRE(keys.size() <= 2, RFGPU_E_UNSUPPORTED, "equi join on more than 2 shared variables");
+    // Left: lhs must be the preserved (probe) side.  Inner: build on the smaller input (JoinSelection does the same
+    // from statistics; the multiset does not depend on it).
+    const bool probe_is_l = left || L->rows >= R->rows;
+    const rfgpu_table* Pt = probe_is_l ? L : R;
+    const rfgpu_table* Bt = probe_is_l ? R : L;
+    auto kc = [&](const rfgpu_table* t, size_t k) -> const uint32_t* {
+      if (k >= keys.size()) return nullptr;
+      return t->cols[t == L ? keys[k].l : keys[k].r].data;
+    };
+    ctx->m.join_probe_rows += Pt->rows;
+    ctx->m.join_build_rows += Bt->rows;
+    ProbeResult P = hash_probe(ctx, (int)keys.size(), kc(Bt, 0), kc(Bt, 1), Bt->rows, kc(Pt, 0), kc(Pt, 1), Pt->rows, left);
+    std::vector<OutColSpec> specs;
+    for (size_t i = 0; i < nl; i++)
+      specs.push_back(probe_is_l ? OutColSpec{L->cols[i].data, nullptr} : OutColSpec{nullptr, L->cols[i].data});
+    for (int j : rhs_only)
+      specs.push_back(probe_is_l ? OutColSpec{nullptr, R->cols[j].data} : OutColSpec{R->cols[j].data, nullptr});
+    auto bufs = alloc_out(P.n_out);
+    expand(ctx, P, specs, raw(bufs), 0);
+    return finish(bufs, P.n_out);
+  }
+
+  // ---- compatible-mapping join ----
+  const size_t nk = keys.size();
+  RF_REQUIRE(nk <= 4, RFGPU_E_UNSUPPORTED, "compatible join on more than 4 shared variables");
+  ctx->m.join_probe_rows += L->rows;
+  ctx->m.join_build_rows += R->rows;
+  std::vector<int> lk, rk;
+  for (auto& k : keys) {
+    lk.push_back(k.l);
+    rk.push_back(k.r);
+  }
+  BufRef hidden, flag;
+  if (left) {
+    hidden = alloc_col(ctx, L->rows);
+    flag = alloc_col(ctx, L->rows);
+    RF_CUDA(cudaMemsetAsync(flag->ptr, 0, L->rows * 4 + 4, ctx->stream()));
+    if (L->rows) {
+      KernelScope ks(ctx, "k_iota");
+      k_iota<<<grid_for(ctx, L->rows), 256, 0, ctx->stream()>>>(hidden->as<uint32_t>(), L->rows);
+    }
+  }
+  const uint32_t ncls = 1u << nk;
+  struct Cls { std::vector<BufRef> cols; uint64_t rows = 0; };
+  std::vector<Cls> lc(ncls), rc(ncls);
+  for (uint32_t m = 0; m < ncls; m++) {
+    lc[m].cols = split_class(ctx, L, lk, m, left ? hidden->as<uint32_t>() : nullptr, &lc[m].rows);
+    rc[m].cols = split_class(ctx, R, rk, m, nullptr, &rc[m].rows);
+  }
+  struct Sub { ProbeResult P; uint32_t ml, mr; };
+  std::vector<Sub> subs;
+  uint64_t total = 0;
+  for (uint32_t ml = 0; ml < ncls; ml++)
+    for (uint32_t mr = 0; mr < ncls; mr++) {
+      if (lc[ml].rows == 0 || rc[mr].rows == 0) continue;
+      std::vector<size_t> ks;  // keys bound on both sides
+      for (size_t k = 0; k < nk; k++)
+        if (((ml >> k) & 1) && ((mr >> k) & 1)) ks.push_back(k);
+      RF_REQUIRE(ks.size() <= 2, RFGPU_E_UNSUPPORTED, "compatible join with more than 2 simultaneously bound keys");
+      Sub s;
+      s.ml = ml;
+      s.mr = mr;
+      if (ks.empty()) {
+        s.P.cross = true;
+        s.P.n_left = lc[ml].rows;
+        s.P.n_right = rc[mr].rows;
+        unsigned __int128 prod = (unsigned __int128)s.P.n_left * s.P.n_right;
+        RF_REQUIRE(prod < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "compatible join output exceeds 2^32-2 rows");
+        s.P.n_out = (uint64_t)prod;
+        s.P.n_entries = lc[ml].rows;
+      } else {
+        auto lcol = [&](size_t i) { return i < ks.size() ? lc[ml].cols[lk[ks[i]]]->as<uint32_t>() : nullptr; };
+        auto rcol = [&](size_t i) { return i < ks.size() ? rc[mr].cols[rk[ks[i]]]->as<uint32_t>() : nullptr; };
+        s.P = hash_probe(ctx, (int)ks.size(), rcol(0), rcol(1), rc[mr].rows, lcol(0), lcol(1), lc[ml].rows, false);
+      }
+      if (left && s.P.n_entries) {
+        KernelScope ksx(ctx, "k_mark_entries");
+        k_mark_entries<<<grid_for(ctx, s.P.n_entries), 256, 0, ctx->stream()>>>(
+            s.P.cross ? nullptr : s.P.m_row->as<uint32_t>(), s.P.n_entries, lc[ml].cols[nl]->as<uint32_t>(),
+            flag->as<uint32_t>());
+      }
+      total += s.P.n_out;
+      subs.push_back(std::move(s));
+    }
+  // unmatched lhs rows (OPTIONAL): flag == 0
+  std::vector<BufRef> un;
+  uint64_t n_un = 0;
+  if (left) {
+    DevPred d{};
+    d.op = RFGPU_F_IS_NULL;
+    d.a = flag->as<uint32_t>();
+    std::vector<const uint32_t*> src;
+    for (auto& c : L->cols) src.push_back(c.data);
+    n_un = filter_compact(ctx, {d}, src, L->rows, &un, "k_join_unmatched", 4ull * (nl + 1) * L->rows);
+  }
+  RF_REQUIRE(total + n_un < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "compatible join output exceeds 2^32-2 rows");
+  auto bufs = alloc_out(total + n_un);
+  auto dst = raw(bufs);
+  uint64_t off = 0;
+  for (auto& s : subs) {
+    std::vector<OutColSpec> specs;
+    for (size_t i = 0; i < nl; i++) {
+      OutColSpec sp{lc[s.ml].cols[i]->as<uint32_t>(), nullptr};
+      for (auto& k : keys)  // value_from_joined(.., requires_coalesce = true): COALESCE(lhs.k, rhs.k)
+        if (k.l == (int)i) sp.build = rc[s.mr].cols[k.r]->as<uint32_t>();
+      specs.push_back(sp);
+    }
+    for (int j : rhs_only) specs.push_back({nullptr, rc[s.mr].cols[j]->as<uint32_t>()});
+    expand(ctx, s.P, specs, dst, off);
+    off += s.P.n_out;
+  }
+  if (n_un) {
+    for (size_t i = 0; i < nl; i++)
+      RF_CUDA(cudaMemcpyAsync(dst[i] + off, un[i]->ptr, n_un * 4, cudaMemcpyDeviceToDevice, ctx->stream()));
+    for (size_t c = nl; c < nout; c++) RF_CUDA(cudaMemsetAsync(dst[c] + off, 0, n_un * 4, ctx->stream()));
+  }
+  ctx->sync();  // class tables are freed stream-ordered, but keep the API synchronous for callers that time it
+  return finish(bufs, total + n_un);
+}
+
+}  // namespace rf
+
+extern "C" {
+
+int32_t rfgpu_sparql_join(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_table* rhs, int32_t join_type,
+                          rfgpu_table** out) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx && lhs && rhs && out, RFGPU_E_INVALID, "NULL argument");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  *out = rf::sparql_join(ctx, lhs, rhs, join_type);
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_last_join_algo(const rfgpu_ctx* ctx) { return ctx ? ctx->last_join_algo : -1; }
+
+}  // extern "C"

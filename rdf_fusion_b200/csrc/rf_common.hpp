@@ -1,0 +1,174 @@
+// rf_common.hpp — shared host-side plumbing of librfgpu: context, device buffers, tables, errors.
+// Product code: must never include anything under oracle/.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/rfgpu.h"
+
+namespace rf {
+
+struct Error : std::runtime_error {
+  int32_t code;
+  Error(int32_t c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+
+#define RF_CUDA(expr)                                                                                   \
+  do {                                                                                                  \
+    cudaError_t _e = (expr);                                                                            \
+    if (_e != cudaSuccess)                                                                              \
+      throw ::rf::Error(RFGPU_E_CUDA, std::string(#expr) + ": " + cudaGetErrorName(_e) + " (" +        \
+                                          cudaGetErrorString(_e) + ") at " + __FILE__ + ":" +          \
+                                          std::to_string(__LINE__));                                    \
+  } while (0)
+
+#define RF_REQUIRE(cond, code, msg)                  \
+  do {                                               \
+    if (!(cond)) throw ::rf::Error((code), (msg));   \
+  } while (0)
+
+constexpr int kNumSMsB200 = 148;
+constexpr size_t kPad = 256;  // every device allocation is padded so 16-B vector / bulk over-reads stay in bounds
+
+// Device + stream shared by a ctx and every buffer it allocated (buffers may outlive the ctx handle).
+struct Core {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  int num_sms = kNumSMsB200;
+  ~Core();
+};
+
+struct DevBuf {
+  std::shared_ptr<Core> core;
+  void* ptr = nullptr;
+  size_t bytes = 0;
+  DevBuf(std::shared_ptr<Core> c, size_t n);
+  ~DevBuf();
+  DevBuf(const DevBuf&) = delete;
+  template <class T>
+  T* as() const { return reinterpret_cast<T*>(ptr); }
+};
+using BufRef = std::shared_ptr<DevBuf>;
+
+struct Column {
+  std::string name;
+  bool nullable = false;
+  const uint32_t* data = nullptr;  // device, 4-B aligned (views into an index keep the index' alignment)
+  BufRef owner;                    // keeps `data` alive
+};
+
+struct KernelStat {
+  uint64_t launches = 0;
+  double ms = 0;
+  uint64_t bytes = 0;
+};
+
+struct Comm;  // NCCL communicator wrapper (shuffle.cu)
+
+}  // namespace rf
+
+struct rfgpu_table {
+  std::atomic<int> refs{1};
+  std::vector<rf::Column> cols;
+  uint64_t rows = 0;
+};
+
+struct rfgpu_index_t {
+  uint32_t perm = 0;
+  uint64_t rows = 0;
+  rf::BufRef col[4];  // level i column, uint32_t[rows]
+};
+
+struct rfgpu_store {
+  std::atomic<int> refs{1};
+  std::vector<rfgpu_index_t> indexes;
+};
+
+struct rfgpu_ctx {
+  std::shared_ptr<rf::Core> core;
+  std::string err;
+  rfgpu_metrics m{};
+  int last_join_algo = -1;
+  uint64_t last_from = 0, last_to = 0;
+  // pinned host scratch for small device→host results (ranges, counts)
+  uint64_t* h_scratch = nullptr;  // 64 x u64
+  // profiling
+  bool profiling = false;
+  std::vector<std::pair<std::string, rf::KernelStat>> kstats;
+  struct Pending { int idx; cudaEvent_t a, b; };
+  std::vector<Pending> pending;
+  cudaEvent_t t0 = nullptr, t1 = nullptr;
+  void* flush_buf = nullptr;
+  size_t flush_bytes = 0;
+  std::shared_ptr<rf::Comm> comm;
+
+  rf::BufRef alloc(size_t bytes) { return std::make_shared<rf::DevBuf>(core, bytes); }
+  cudaStream_t stream() const { return core->stream; }
+  void sync() { RF_CUDA(cudaStreamSynchronize(core->stream)); }
+  // kernel launch accounting: KernelScope ks(ctx, "name", bytes); kernel<<<..., ctx->stream()>>>(...); (dtor closes)
+  int kstat_index(const char* name);
+  void collect_profile();
+};
+
+namespace rf {
+
+struct KernelScope {
+  rfgpu_ctx* ctx;
+  int idx = -1;
+  cudaEvent_t a = nullptr, b = nullptr;
+  KernelScope(rfgpu_ctx* c, const char* name, uint64_t algorithmic_bytes = 0);
+  ~KernelScope() noexcept(false);
+};
+
+inline uint32_t div_up(uint64_t a, uint64_t b) { return (uint32_t)((a + b - 1) / b); }
+
+rfgpu_table* new_table();
+BufRef alloc_col(rfgpu_ctx* ctx, uint64_t rows);  // uint32_t[rows] (+pad)
+int find_col(const rfgpu_table* t, const std::string& name);
+
+// device-wide exclusive scan of u32 → u32 (total returned via pinned scratch slot); scan.cu
+void exclusive_scan_u32(rfgpu_ctx* ctx, const uint32_t* in, uint32_t* out, uint64_t n, uint64_t* h_total_slot);
+
+// filter.cu — generic predicate program over column pointers
+struct DevPred {
+  int32_t op;            // rfgpu_filter_op
+  const uint32_t* a;     // column
+  const uint32_t* b;     // second column (EQ_COL / NE_COL)
+  uint32_t value, hi;
+  const uint32_t* ids;   // IN with more than kInlineIds ids: sorted device array
+  uint32_t n_ids;
+  uint32_t inl[8];       // IN with <= 8 ids
+};
+constexpr int kMaxPreds = 8;
+constexpr int kMaxCols = 16;
+// Evaluates preds over rows [0,n) and compacts `n_cols` source columns into freshly allocated outputs.
+// Returns the number of rows kept.
+uint64_t filter_compact(rfgpu_ctx* ctx, const std::vector<DevPred>& preds, const std::vector<const uint32_t*>& src,
+                        uint64_t n, std::vector<BufRef>* out, const char* kernel_name, uint64_t algorithmic_bytes_in);
+
+}  // namespace rf
+
+// C-ABI guard: translate exceptions to codes
+#define RF_API_BEGIN try {
+#define RF_API_END(ctx)                                   \
+  return RFGPU_OK;                                        \
+  }                                                       \
+  catch (const ::rf::Error& e) {                          \
+    ::rf::set_error((ctx), e.what());                     \
+    return e.code;                                        \
+  }                                                       \
+  catch (const std::exception& e) {                       \
+    ::rf::set_error((ctx), e.what());                     \
+    return RFGPU_E_EXEC;                                  \
+  }
+
+namespace rf {
+void set_error(const rfgpu_ctx* ctx, const std::string& msg);
+}

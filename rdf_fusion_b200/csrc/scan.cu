@@ -1,0 +1,308 @@
+// scan.cu — kernel 1: range lookup over a sorted index permutation + column gather (and hand-off to kernel 2 for
+// residual predicates).
+//
+// Replaces MemIndexData::prune_relevant_row_groups + MemColumnChunk::find_range_between
+// (lib/storage/src/memory/storage/quad_index_data.rs:155-284,600-650: a linear walk over all row groups per level)
+// and the batch loop of MemQuadIndexScanIterator::next (scan.rs:101-213) with
+//   1a. ONE lexicographic 1024-ary search: the leading Eq levels and the first range level form a lower and an upper
+//       key tuple; lower_bound/upper_bound over the 4 sorted columns are found in ceil(log_1024 N) dependent steps
+//       (3 at N = 1e8..1e9) by two CTAs of 1024 threads, instead of ~log2(N)*8 dependent loads;
+//   1b. a 128-bit coalesced copy of the bound columns of [from,to) (or a zero-copy view, like the reference's Arc slices);
+//   2.  the fused predicate + compaction kernel (filter.cu) when predicates remain that pruning cannot absorb.
+#include <algorithm>
+
+#include "rf_common.hpp"
+#include "rf_device.cuh"
+#include "scan_plan.hpp"
+
+namespace rf {
+
+struct SearchArgs {
+  const uint32_t* col[4];
+  uint64_t n;
+  uint32_t key[2][4];  // [0] lower tuple, [1] upper tuple
+  int32_t depth;       // number of leading columns compared
+};
+
+// true ⇔ row tuple >= key (which = 0, lower_bound) / row tuple > key (which = 1, upper_bound)
+__device__ __forceinline__ bool tuple_cmp(const SearchArgs& A, int which, uint64_t row) {
+  for (int j = 0; j < A.depth; j++) {
+    uint32_t v = __ldg(A.col[j] + row);
+    uint32_t k = A.key[which][j];
+    if (v != k) return v > k;
+  }
+  return which == 0;
+}
+
+constexpr int kSearchThreads = 1024;
+
+// grid = 2 CTAs: blockIdx.x = 0 → lower bound of key[0]; 1 → upper bound of key[1].  result[] is pinned host memory.
+__global__ void __launch_bounds__(kSearchThreads)
+k_range_search(const __grid_constant__ SearchArgs A, unsigned long long* __restrict__ result) {
+  const int which = blockIdx.x;
+  uint64_t lo = 0, hi = A.n;  // answer in [lo, hi]
+  while (hi > lo) {
+    uint64_t width = hi - lo;
+    if (width <= kSearchThreads) {
+      uint64_t row = lo + threadIdx.x;
+      bool below = row < hi && !tuple_cmp(A, which, row);
+      lo += __syncthreads_count(below);
+      break;
+    }
+    uint64_t step = (width + kSearchThreads - 1) / kSearchThreads;
+    uint64_t pivot = lo + (uint64_t)(threadIdx.x + 1) * step - 1;  // last row of chunk threadIdx.x
+    bool below = pivot < hi && !tuple_cmp(A, which, pivot);
+    uint64_t c = __syncthreads_count(below);  // monotone: the first c pivots are below the key
+    uint64_t nlo = lo + c * step;
+    uint64_t nhi = min(hi, nlo + step - 1);  // pivot c is >= key (or past hi)
+    lo = min(nlo, hi);
+    hi = max(nhi, lo);
+  }
+  if (threadIdx.x == 0) result[which] = lo;
+}
+
+// ---- 1b: column gather ----
+struct GatherArgs {
+  const uint32_t* src[4];  // already offset to row `from`
+  uint32_t* dst[4];        // congruent to src modulo 16 bytes
+  uint64_t n;
+  int32_t n_cols;
+};
+
+constexpr int kGatherThreads = 256;
+constexpr int kGatherUnroll = 4;
+
+__global__ void __launch_bounds__(kGatherThreads)
+k_gather_range(const __grid_constant__ GatherArgs A) {
+  const int c = blockIdx.y;
+  const uint32_t* __restrict__ src = A.src[c];
+  uint32_t* __restrict__ dst = A.dst[c];
+  const uint64_t n = A.n;
+  // head: elements until src is 16-B aligned (dst is congruent, so it becomes aligned at the same element)
+  uint64_t head = ((16 - ((uintptr_t)src & 15)) & 15) >> 2;
+  if (head > n) head = n;
+  const uint64_t nvec = (n - head) >> 2;
+  const uint64_t tail0 = head + (nvec << 2);
+  const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
+  if (tid < head) dst[tid] = src[tid];
+  if (tid < n - tail0) dst[tail0 + tid] = src[tail0 + tid];
+  const uint4* __restrict__ s4 = reinterpret_cast<const uint4*>(src + head);
+  uint4* __restrict__ d4 = reinterpret_cast<uint4*>(dst + head);
+  uint64_t i = tid;
+  for (; i + (kGatherUnroll - 1) * nthreads < nvec; i += kGatherUnroll * nthreads) {
+    uint4 v[kGatherUnroll];
+#pragma unroll
+    for (int u = 0; u < kGatherUnroll; u++) v[u] = __ldcs(s4 + i + u * nthreads);  // streaming: read once
+#pragma unroll
+    for (int u = 0; u < kGatherUnroll; u++) d4[i + u * nthreads] = v[u];
+  }
+  for (; i < nvec; i += nthreads) d4[i] = __ldcs(s4 + i);
+}
+
+static const rfgpu_index_t* find_index(const rfgpu_store* s, uint32_t perm) {
+  for (auto& ix : s->indexes)
+    if (ix.perm == perm) return &ix;
+  return nullptr;
+}
+
+}  // namespace rf
+
+extern "C" {
+
+int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t flags, rfgpu_table** out) {
+  RF_API_BEGIN
+  using namespace rf;
+  RF_REQUIRE(ctx && p && out, RFGPU_E_INVALID, "NULL argument");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  const rfgpu_index_t* ix = find_index(p->store, p->perm);
+  RF_REQUIRE(ix, RFGPU_E_EXEC, "Index must exist");
+  const ScanInstrs ins = p->gspo.reorder(p->perm);
+
+  // output schema: scanned variables in G,S,P,O first-occurrence order; graph nullable
+  // (lib/logical/src/patterns/mod.rs:68-107, lib/encoding/src/quad_storage_encoding.rs:79-93)
+  struct OutCol { std::string name; int level; bool nullable; };
+  std::vector<OutCol> oc;
+  for (int comp = 0; comp < 4; comp++) {
+    if (!p->gspo.at[comp].scan) continue;
+    int level = -1;
+    for (int l = 0; l < 4; l++)
+      if (perm_level(p->perm, l) == comp) level = l;
+    oc.push_back({p->gspo.at[comp].var, level, comp == RFGPU_G});
+  }
+  auto make_empty = [&]() {
+    std::unique_ptr<rfgpu_table> t(new_table());
+    for (auto& o : oc) {
+      Column c;
+      c.name = o.name;
+      c.nullable = o.nullable;
+      c.owner = alloc_col(ctx, 0);
+      c.data = c.owner->as<uint32_t>();
+      t->cols.push_back(std::move(c));
+    }
+    return t.release();
+  };
+
+  bool any_false = false;
+  for (int l = 0; l < 4; l++) any_false |= ins.at[l].pred.kind == RFGPU_PRED_FALSE;
+  ctx->last_from = ctx->last_to = 0;
+  if (ix->rows == 0 || any_false) {
+    *out = make_empty();
+    return RFGPU_OK;
+  }
+
+  // ---- 1a: pruning → one contiguous range.  Walk levels while they carry a pruning predicate; continue past a
+  // level only if it pins a single id (quad_index_data.rs:162-243).
+  SearchArgs S{};
+  S.n = ix->rows;
+  int depth = 0;
+  for (int l = 0; l < 4; l++) {
+    uint32_t a, b;
+    if (!ins.at[l].pred.pruning(&a, &b)) break;
+    S.key[0][l] = a;
+    S.key[1][l] = b;
+    depth = l + 1;
+    if (a != b) break;
+  }
+  S.depth = depth;
+  for (int l = 0; l < 4; l++) S.col[l] = ix->col[l]->as<uint32_t>();
+  uint64_t from = 0, to = ix->rows;
+  if (depth > 0) {
+    {
+      KernelScope ks(ctx, "k_range_search");
+      k_range_search<<<2, kSearchThreads, 0, ctx->stream()>>>(S, (unsigned long long*)ctx->h_scratch);
+    }
+    ctx->sync();
+    from = ctx->h_scratch[0];
+    to = ctx->h_scratch[1];
+    if (to < from) to = from;
+  }
+  ctx->last_from = from;
+  ctx->last_to = to;
+  const uint64_t R = to - from;
+  ctx->m.scan_rows_in += R;
+  if (R == 0) {
+    *out = make_empty();
+    return RFGPU_OK;
+  }
+
+  // ---- residual predicates: drop what pruning guarantees (quad_index_data.rs:245-278), keep the rest
+  std::vector<DevPred> residual;
+  std::vector<BufRef> keep;
+  bool dropping = true;
+  uint64_t pred_levels = 0;
+  for (int l = 0; l < 4; l++) {
+    const ScanPred& sp = ins.at[l].pred;
+    if (dropping) {
+      if (sp.kind == RFGPU_PRED_IN && sp.ids.size() == 1) continue;  // implied
+      if (sp.kind == RFGPU_PRED_BETWEEN) {
+        dropping = sp.lo == sp.hi;  // a true range is applied, but nothing after it
+        continue;
+      }
+      dropping = false;
+    }
+    if (sp.kind == RFGPU_PRED_NONE) continue;
+    DevPred d{};
+    d.a = S.col[l] + from;
+    if (sp.kind == RFGPU_PRED_IN) {
+      d.op = RFGPU_F_IN;
+      d.n_ids = (uint32_t)sp.ids.size();
+      if (sp.ids.size() <= 8) {
+        for (size_t k = 0; k < sp.ids.size(); k++) d.inl[k] = sp.ids[k];
+      } else {
+        auto b = ctx->alloc(sp.ids.size() * 4);
+        RF_CUDA(cudaMemcpyAsync(b->ptr, sp.ids.data(), sp.ids.size() * 4, cudaMemcpyHostToDevice, ctx->stream()));
+        d.ids = b->as<uint32_t>();
+        keep.push_back(b);
+      }
+    } else if (sp.kind == RFGPU_PRED_BETWEEN) {
+      d.op = RFGPU_F_BETWEEN;
+      d.value = sp.lo;
+      d.hi = sp.hi;
+    } else {  // EQUAL_TO: compare with the level that scans the variable (scan.rs:309-318)
+      int other = -1;
+      for (int j = 0; j < 4 && other < 0; j++)
+        if (ins.at[j].scan && ins.at[j].var == sp.var) other = j;
+      if (other < 0) continue;  // `position(..)?` → no predicate
+      d.op = RFGPU_F_EQ_COL;
+      d.b = S.col[other] + from;
+      pred_levels |= 1ull << other;
+    }
+    pred_levels |= 1ull << l;
+    residual.push_back(d);
+  }
+
+  std::unique_ptr<rfgpu_table> t(new_table());
+  if (residual.empty()) {
+    t->rows = R;
+    if (flags & RFGPU_SCAN_ALLOW_VIEW) {
+      for (auto& o : oc) {
+        Column c;
+        c.name = o.name;
+        c.nullable = o.nullable;
+        c.owner = ix->col[o.level];
+        c.data = S.col[o.level] + from;
+        t->cols.push_back(std::move(c));
+      }
+    } else if (!oc.empty()) {
+      GatherArgs G{};
+      G.n = R;
+      G.n_cols = (int32_t)oc.size();
+      for (size_t k = 0; k < oc.size(); k++) {
+        Column c;
+        c.name = oc[k].name;
+        c.nullable = oc[k].nullable;
+        c.owner = ctx->alloc(R * 4 + 16);
+        const uint32_t* src = S.col[oc[k].level] + from;
+        uint32_t* dst = c.owner->as<uint32_t>() + (((uintptr_t)src & 15) >> 2);
+        c.data = dst;
+        G.src[k] = src;
+        G.dst[k] = dst;
+        t->cols.push_back(std::move(c));
+      }
+      uint64_t bytes = 8ull * oc.size() * R;
+      uint64_t nvec = R / 4;
+      uint32_t bx = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(nvec, (uint64_t)kGatherThreads * kGatherUnroll),
+                                                                      (uint64_t)ctx->core->num_sms * 8));
+      KernelScope ks(ctx, "k_gather_range", bytes);
+      k_gather_range<<<dim3(bx, (uint32_t)oc.size()), kGatherThreads, 0, ctx->stream()>>>(G);
+      ctx->m.algorithmic_bytes += bytes;
+    }
+    ctx->m.scan_rows_out += R;
+  } else {
+    RF_REQUIRE(!oc.empty() || true, RFGPU_E_EXEC, "");
+    std::vector<const uint32_t*> src;
+    for (auto& o : oc) src.push_back(S.col[o.level] + from);
+    uint64_t nread = 0;
+    for (int l = 0; l < 4; l++) {
+      bool is_out = false;
+      for (auto& o : oc) is_out |= o.level == l;
+      if (is_out || ((pred_levels >> l) & 1)) nread++;
+    }
+    uint64_t bytes_in = 4ull * nread * R;
+    std::vector<BufRef> bufs;
+    uint64_t kept = filter_compact(ctx, residual, src, R, &bufs, "k_scan_filter_compact", bytes_in);
+    t->rows = kept;
+    for (size_t k = 0; k < oc.size(); k++) {
+      Column c;
+      c.name = oc[k].name;
+      c.nullable = oc[k].nullable;
+      c.owner = bufs[k];
+      c.data = bufs[k]->as<uint32_t>();
+      t->cols.push_back(std::move(c));
+    }
+    ctx->m.scan_rows_out += kept;
+    ctx->m.algorithmic_bytes += bytes_in + 4ull * oc.size() * kept;
+  }
+  *out = t.release();
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_scan_last_range(const rfgpu_ctx* ctx, uint64_t* from, uint64_t* to) {
+  if (!ctx || !from || !to) return RFGPU_E_INVALID;
+  *from = ctx->last_from;
+  *to = ctx->last_to;
+  return RFGPU_OK;
+}
+
+}  // extern "C"
