@@ -190,7 +190,7 @@ int32_t rfgpu_ctx_synchronize(rfgpu_ctx* ctx) {
 // ---- store ----
 int32_t rfgpu_store_create(rfgpu_ctx* ctx, rfgpu_store** out) {
   RF_API_BEGIN
-  RF_REQUIRE(ctx && out, RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(out, RFGPU_E_INVALID, "NULL argument");  // ctx may be NULL: a host-only store for planning
   *out = new rfgpu_store();
   RF_API_END(ctx)
 }
@@ -207,7 +207,8 @@ void rfgpu_store_release(rfgpu_store* s) {
 int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm, const uint32_t* const cols[4],
                               uint64_t n_rows, int32_t on_device) {
   RF_API_BEGIN
-  RF_REQUIRE(ctx && s && cols, RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(s && (cols || n_rows == 0), RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(ctx || n_rows == 0, RFGPU_E_INVALID, "a ctx is required to upload rows");
   RF_REQUIRE(perm < 256, RFGPU_E_INVALID, "bad permutation code");
   int seen = 0;
   for (int i = 0; i < 4; i++) seen |= 1 << ((perm >> (2 * i)) & 3);
@@ -216,10 +217,14 @@ int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm, con
   for (auto& ix : s->indexes) RF_REQUIRE(ix.perm != perm, RFGPU_E_INVALID, "permutation already present");
   if (!s->indexes.empty())
     RF_REQUIRE(s->indexes[0].rows == n_rows, RFGPU_E_INVALID, "all permutations must hold the same quads");
-  RF_CUDA(cudaSetDevice(ctx->core->device));
   rfgpu_index_t ix;
   ix.perm = perm;
   ix.rows = n_rows;
+  if (!ctx) {  // planning-only store (no device): choose_index / apply_filter / describe work without a GPU
+    s->indexes.push_back(std::move(ix));
+    return RFGPU_OK;
+  }
+  RF_CUDA(cudaSetDevice(ctx->core->device));
   for (int i = 0; i < 4; i++) {
     RF_REQUIRE(cols[i] || n_rows == 0, RFGPU_E_INVALID, "NULL column");
     ix.col[i] = rf::alloc_col(ctx, n_rows);

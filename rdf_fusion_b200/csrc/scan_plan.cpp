@@ -213,7 +213,7 @@ extern "C" {
 int32_t rfgpu_scan_plan_create(rfgpu_ctx* ctx, rfgpu_store* s, const rfgpu_scan_instruction gspo[4],
                                rfgpu_scan_plan** out) {
   RF_API_BEGIN
-  RF_REQUIRE(ctx && s && gspo && out, RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(s && gspo && out, RFGPU_E_INVALID, "NULL argument");
   RF_REQUIRE(!s->indexes.empty(), RFGPU_E_INVALID, "At least one index must be available");
   std::unique_ptr<rfgpu_scan_plan> p(new rfgpu_scan_plan);
   p->gspo = rf::ScanInstrs::from_c(gspo);
@@ -232,7 +232,7 @@ void rfgpu_scan_plan_destroy(rfgpu_scan_plan* p) {
 int32_t rfgpu_scan_plan_apply_filter(rfgpu_ctx* ctx, rfgpu_scan_plan* p, const char* column, int32_t op,
                                      uint32_t value) {
   RF_API_BEGIN
-  RF_REQUIRE(ctx && p && column, RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(p && column, RFGPU_E_INVALID, "NULL argument");
   rf::ScanInstrs copy = p->gspo;
   copy.apply(column, rf::pushdown_binary(op, value));
   p->gspo = copy;
@@ -243,7 +243,7 @@ int32_t rfgpu_scan_plan_apply_filter(rfgpu_ctx* ctx, rfgpu_scan_plan* p, const c
 int32_t rfgpu_scan_plan_apply_between(rfgpu_ctx* ctx, rfgpu_scan_plan* p, const char* column, uint32_t lo,
                                       uint32_t hi) {
   RF_API_BEGIN
-  RF_REQUIRE(ctx && p && column, RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(p && column, RFGPU_E_INVALID, "NULL argument");
   rf::ScanInstrs copy = p->gspo;
   copy.apply(column, rf::ScanPred::between(lo, hi));
   p->gspo = copy;
@@ -253,7 +253,7 @@ int32_t rfgpu_scan_plan_apply_between(rfgpu_ctx* ctx, rfgpu_scan_plan* p, const 
 
 int32_t rfgpu_scan_plan_set_index(rfgpu_ctx* ctx, rfgpu_scan_plan* p, uint32_t perm) {
   RF_API_BEGIN
-  RF_REQUIRE(ctx && p, RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(p, RFGPU_E_INVALID, "NULL argument");
   bool found = false;
   for (auto& ix : p->store->indexes) found |= ix.perm == perm;
   RF_REQUIRE(found, RFGPU_E_INVALID, "the store does not hold permutation " + rf::perm_name(perm));

@@ -1,0 +1,154 @@
+"""CPU: the C-ABI library loads, exports every symbol include/rfgpu.h declares, refuses to run without a GPU, and
+its host-side planning logic (choose_index / apply_filter / describe) agrees with the oracle and the golden vectors.
+No compute entry point is called here."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import rdf_fusion_b200 as rf
+from rdf_fusion_b200 import _ffi as F
+
+from helpers import OPS, PERMS, decode_instr, random_pattern, random_quads
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "rfgpu.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(rfgpu_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = F.load()
+    names = _declared_symbols()
+    assert len(names) >= 50
+    for n in names:
+        assert hasattr(lib, n), f"librfgpu.so does not export {n}"
+        assert n in F.SIGNATURES, f"_ffi.py does not bind {n}"
+    assert lib.rfgpu_version().decode().startswith("rfgpu")
+
+
+def test_no_gpu_means_loud_failure():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(rf.RfgpuError) as e:
+        rf.Context(0)
+    assert e.value.code == F.E_NOGPU
+    assert "no CPU fallback" in e.value.message
+
+
+class HostStore:
+    """planning-only store (ctx = NULL): permutations declared with zero rows"""
+
+    def __init__(self, perms):
+        self.lib = F.load()
+        self.h = C.c_void_p()
+        assert self.lib.rfgpu_store_create(None, C.byref(self.h)) == 0
+        for p in perms:
+            assert self.lib.rfgpu_store_add_index(None, self.h, p, None, 0, 0) == 0
+
+    def plan(self, instr):
+        arr, keep = rf.make_instructions(instr)
+        h = C.c_void_p()
+        rc = self.lib.rfgpu_scan_plan_create(None, self.h, arr, C.byref(h))
+        if rc != 0:
+            raise rf.RfgpuError(rc, self.lib.rfgpu_last_error(None).decode())
+        return HostPlan(self.lib, h)
+
+
+class HostPlan:
+    def __init__(self, lib, h):
+        self.lib, self.h = lib, h
+
+    def apply_filter(self, col, op, v):
+        rc = self.lib.rfgpu_scan_plan_apply_filter(None, self.h, col.encode(), op, v)
+        if rc != 0:
+            raise rf.RfgpuError(rc, self.lib.rfgpu_last_error(None).decode())
+        return self
+
+    def apply_between(self, col, lo, hi):
+        rc = self.lib.rfgpu_scan_plan_apply_between(None, self.h, col.encode(), lo, hi)
+        if rc != 0:
+            raise rf.RfgpuError(rc, self.lib.rfgpu_last_error(None).decode())
+        return self
+
+    @property
+    def index(self):
+        return self.lib.rfgpu_scan_plan_index(self.h)
+
+    def describe(self):
+        n = self.lib.rfgpu_scan_plan_describe(self.h, None, 0)
+        buf = C.create_string_buffer(n)
+        self.lib.rfgpu_scan_plan_describe(self.h, buf, n)
+        return buf.value.decode()
+
+
+def test_choose_index_golden(scan_golden):
+    st = HostStore([F.GSPO, F.GPOS, F.GOSP])
+    for case in scan_golden["choose_index_cases"]:
+        assert F.PERM_NAMES[st.plan([decode_instr(e) for e in case["instr"]]).index] == case["expect"], case["name"]
+    for case in scan_golden["scan_cases"]:
+        if "index" not in case["expect"]:
+            continue
+        plan = HostStore([PERMS[p] for p in case["perms"]]).plan([decode_instr(e) for e in case["instr"]])
+        for col, lo, hi in case.get("dynamic_between", []):
+            plan.apply_between(col, lo, hi)
+        assert F.PERM_NAMES[plan.index] == case["expect"]["index"], case["name"]
+
+
+def test_pushdown_display_golden(scan_golden):
+    for case in scan_golden["pushdown_cases"]:
+        plan = HostStore([F.GSPO, F.GPOS, F.GOSP]).plan(
+            [rf.traverse(0), rf.scan("subject"), rf.traverse(7), rf.scan("object")])
+        if case["op"] == "gt_and_lt":
+            plan.apply_filter("object", F.OP_GT, case["value"]).apply_filter("object", F.OP_LT, case["value2"])
+        else:
+            plan.apply_filter("object", OPS[case["op"]], case["value"])
+        d = plan.describe()
+        assert d.startswith("[" + case["expect_index"] + "] ") and d.endswith(case["expect_filters"]), (case, d)
+
+
+def test_planning_matches_oracle_on_random_programs(oracle):
+    rng = np.random.default_rng(7)
+    quads = random_quads(rng, 200)
+    perms = [F.GSPO, F.GPOS, F.GOSP]
+    host = HostStore(perms)
+    ost = oracle.OracleStore(16, perms)
+    for _ in range(400):
+        instr = random_pattern(rng, quads)
+        hp, op = host.plan(instr), ost.plan(instr)
+        assert hp.index == op.index
+        assert hp.describe() == op.describe()
+        names = [i.var for i in instr if i.action == F.SCAN]
+        if names and rng.random() < 0.7:
+            col = names[rng.integers(0, len(names))]
+            opn = int(rng.integers(0, 5))
+            v = int(rng.integers(0, 70))
+            herr = oerr = None
+            try:
+                hp.apply_filter(col, opn, v)
+            except rf.RfgpuError as e:
+                herr = e.message
+            try:
+                op.apply_filter(col, opn, v)
+            except oracle.OracleError as e:
+                oerr = str(e)
+            assert herr == oerr
+            assert hp.index == op.index and hp.describe() == op.describe()
+
+
+def test_invalid_arguments_are_errors_not_crashes():
+    st = HostStore([F.GSPO])
+    with pytest.raises(rf.RfgpuError, match="In predicate needs at least one id"):
+        st.plan([rf.traverse(rf.In()), rf.traverse(), rf.traverse(), rf.traverse()])
+    with pytest.raises(rf.RfgpuError, match="Could not find scan instruction"):
+        st.plan([rf.traverse(), rf.scan("s"), rf.traverse(), rf.traverse()]).apply_filter("x", F.OP_EQ, 1)
+    lib = F.load()
+    h = C.c_void_p()
+    assert lib.rfgpu_store_add_index(None, st.h, 0, None, 0, 0) == F.E_INVALID  # perm 0 = GGGG
+    assert F.load().rfgpu_shuffle_dest(123, 8) < 8

@@ -1,0 +1,276 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs and
+against the reference's golden vectors.  Bit-exact (integer ids): same multiset of rows after canonical sort; scans
+must also keep the index order."""
+import numpy as np
+import pytest
+
+import rdf_fusion_b200 as rf
+from rdf_fusion_b200 import _ffi as F
+
+from helpers import (PERMS, assert_same_table, canonical, case_quads, decode_instr, random_pattern, random_quads)
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu_store(ctx, quads, perms=(F.GSPO, F.GPOS, F.GOSP)):
+    return ctx.store().load_quads(np.asarray(quads, dtype=np.uint32).reshape(-1, 4), perms)
+
+
+def test_golden_scan_cases(ctx, scan_golden):
+    for case in scan_golden["scan_cases"]:
+        quads = [q for q in case_quads(case) if q not in case.get("remove", [])]
+        st = _gpu_store(ctx, quads, [PERMS[p] for p in case["perms"]])
+        plan = st.plan([decode_instr(e) for e in case["instr"]])
+        for col, lo, hi in case.get("dynamic_between", []):
+            plan.apply_between(col, lo, hi)
+        exp = case["expect"]
+        if "index" in exp:
+            assert F.PERM_NAMES[plan.index] == exp["index"], case["name"]
+        for view in (False, True):
+            t = plan.execute(allow_view=view)
+            assert t.num_rows == exp["rows"], case["name"]
+            assert len(t.names) == exp["cols"], case["name"]
+            cols = t.to_numpy()
+            if "columns" in exp:
+                for name, vals in exp["columns"].items():
+                    assert list(cols[t.names.index(name)]) == vals, case["name"]
+            if "names" in exp:
+                assert t.names == exp["names"], case["name"]
+            if "nullable" in exp:
+                assert t.nullable == exp["nullable"], case["name"]
+
+
+def test_golden_prune_ranges(ctx, scan_golden):
+    for case in scan_golden["prune_cases"]:
+        st = _gpu_store(ctx, case["index_order"], [F.GSPO])
+        plan = st.plan([decode_instr(e) for e in case["instr"]])
+        plan.execute()
+        a, b = plan.last_range()
+        assert b - a == case["expect_rows"], case["name"]
+
+
+@pytest.mark.parametrize("seed,n", [(1, 50), (2, 3000), (3, 40000)])
+def test_random_scans_match_oracle(ctx, oracle, seed, n):
+    rng = np.random.default_rng(seed)
+    quads = random_quads(rng, n, n_s=max(8, n // 20), n_o=max(8, n // 10))
+    perms = [F.GSPO, F.GPOS, F.GOSP]
+    st = _gpu_store(ctx, quads, perms)
+    ost = oracle.OracleStore(64, perms).load_quads(quads)
+    assert len(st) == len(ost)
+    for k in range(150):
+        instr = random_pattern(rng, quads)
+        gp, op = st.plan(instr), ost.plan(instr)
+        if rng.random() < 0.3:  # also scan through a non-preferred permutation
+            p = perms[rng.integers(0, 3)]
+            gp.set_index(p)
+            op.set_index(p)
+        assert gp.index == op.index
+        exp = op.execute()
+        got = gp.execute(allow_view=bool(k & 1))
+        assert got.names == exp.names and got.nullable == exp.nullable
+        cols = got.to_numpy()
+        assert got.num_rows == exp._rows, (k, gp.describe())
+        for a, b in zip(cols, exp.cols):
+            assert np.array_equal(a, b), (k, gp.describe())  # same ORDER too: rows come out in index order
+
+
+def test_scan_large_in_set_and_dynamic_between(ctx, oracle):
+    rng = np.random.default_rng(11)
+    quads = random_quads(rng, 20000, n_s=3000, n_o=5000, n_p=9)
+    st = _gpu_store(ctx, quads)
+    ost = oracle.OracleStore(128).load_quads(quads)
+    ids = [int(x) for x in rng.integers(1, 5000, 300)]
+    instr = [rf.traverse(0), rf.scan("s"), rf.scan("p"), rf.scan("o", rf.In(*ids))]
+    gp, op = st.plan(instr), ost.plan(instr)
+    gp.apply_between("s", 100, 2000)
+    op.apply_between("s", 100, 2000)
+    got, exp = gp.execute(), op.execute()
+    assert got.num_rows == exp._rows > 0
+    for a, b in zip(got.to_numpy(), exp.cols):
+        assert np.array_equal(a, b)
+
+
+def _rand_table(rng, n, names, nullable, null_frac, key_space):
+    cols = {}
+    for nm, nl in zip(names, nullable):
+        v = rng.integers(1, key_space + 1, n).astype(np.uint32)
+        if nl and null_frac > 0:
+            v[rng.random(n) < null_frac] = 0
+        cols[nm] = v
+    return cols
+
+
+def _check_join(ctx, oracle, lc, ln, rc, rn, jt, impl="nested"):
+    L = ctx.import_table(lc, dict(zip(lc, ln)))
+    R = ctx.import_table(rc, dict(zip(rc, rn)))
+    got = L.join(R, jt)
+    ol = oracle.OTable(list(lc), ln, list(lc.values()))
+    orr = oracle.OTable(list(rc), rn, list(rc.values()))
+    exp, algo, _ = oracle.sparql_join(ol, orr, jt, impl)
+    assert got.last_join_algo == algo
+    assert got.nullable == exp.nullable, (got.nullable, exp.nullable)
+    assert_same_table(got.names, got.to_numpy() if got.num_rows else [np.zeros(0, np.uint32)] * len(got.names),
+                      exp.names, exp.cols)
+    return got, algo
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_equi_join_one_key(ctx, oracle, jt, seed):
+    rng = np.random.default_rng(seed)
+    for nl, nr, ks in [(0, 5, 3), (7, 0, 3), (1, 1, 1), (300, 200, 40), (2500, 1800, 300), (900, 4000, 5)]:
+        lc = _rand_table(rng, nl, ["s", "o1"], [False, False], 0, ks)
+        rc = _rand_table(rng, nr, ["s", "o2"], [False, False], 0, ks)
+        _, algo = _check_join(ctx, oracle, lc, [False, False], rc, [False, False], jt)
+        assert algo == F.ALGO_EQUI
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_equi_join_two_keys_and_wide_payload(ctx, oracle, jt):
+    rng = np.random.default_rng(5)
+    lc = _rand_table(rng, 1200, ["offer", "vendor", "x", "y"], [False] * 4, 0, 25)
+    rc = _rand_table(rng, 1500, ["vendor", "z", "offer"], [False] * 3, 0, 25)
+    _, algo = _check_join(ctx, oracle, lc, [False] * 4, rc, [False] * 3, jt)
+    assert algo == F.ALGO_EQUI
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_skewed_keys_heavy_hitter(ctx, oracle, jt):
+    rng = np.random.default_rng(9)
+    n = 6000
+    ls = np.where(rng.random(n) < 0.5, 7, rng.integers(1, 500, n)).astype(np.uint32)
+    rs = np.where(rng.random(300) < 0.3, 7, rng.integers(1, 500, 300)).astype(np.uint32)
+    lc = {"s": ls, "a": np.arange(1, n + 1, dtype=np.uint32)}
+    rc = {"s": rs, "b": np.arange(1, 301, dtype=np.uint32)}
+    got, _ = _check_join(ctx, oracle, lc, [False, False], rc, [False, False], jt, impl="hash")
+    assert got.num_rows > 200000  # the heavy key alone yields ~3000 x ~90 rows
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+@pytest.mark.parametrize("seed", [0, 1])
+def test_compatible_join_nullable_keys(ctx, oracle, jt, seed):
+    rng = np.random.default_rng(100 + seed)
+    for nl, nr, nf in [(40, 30, 0.3), (300, 200, 0.2), (150, 150, 0.0), (60, 0, 0.5), (0, 60, 0.5), (80, 80, 1.0)]:
+        lc = _rand_table(rng, nl, ["v", "a"], [True, False], nf, 12)
+        rc = _rand_table(rng, nr, ["v", "w"], [True, True], nf, 12)
+        _, algo = _check_join(ctx, oracle, lc, [True, False], rc, [True, True], jt)
+        assert algo == F.ALGO_COMPATIBLE
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_compatible_join_two_keys_mixed_nulls(ctx, oracle, jt):
+    rng = np.random.default_rng(21)
+    lc = _rand_table(rng, 120, ["k1", "k2", "a"], [True, False, False], 0.3, 6)
+    rc = _rand_table(rng, 90, ["k2", "b", "k1"], [True, True, True], 0.3, 6)
+    _, algo = _check_join(ctx, oracle, lc, [True, False, False], rc, [True, True, True], jt)
+    assert algo == F.ALGO_COMPATIBLE
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_cross_and_keyless_left(ctx, oracle, jt):
+    rng = np.random.default_rng(3)
+    for nl, nr in [(5, 7), (0, 4), (6, 0), (1, 1), (70, 50)]:
+        lc = _rand_table(rng, nl, ["a", "b"], [False, True], 0.3, 9)
+        rc = _rand_table(rng, nr, ["c"], [False], 0, 9)
+        _, algo = _check_join(ctx, oracle, lc, [False, True], rc, [False], jt)
+        assert algo == F.ALGO_CROSS
+
+
+def test_filter_matches_oracle(ctx, oracle):
+    rng = np.random.default_rng(4)
+    for n in [0, 1, 31, 4096, 4097, 50000]:
+        cols = _rand_table(rng, n, ["a", "b", "c"], [True, True, False], 0.2, 30)
+        T = ctx.import_table(cols, {"a": True, "b": True})
+        ot = oracle.OTable(list(cols), [True, True, False], list(cols.values()))
+        ids = [int(x) for x in rng.integers(1, 31, 12)]
+        programs = [
+            [rf.FPred(F.F_EQ_CONST, 0, value=5)],
+            [rf.FPred(F.F_NE_CONST, 0, value=5)],
+            [rf.FPred(F.F_EQ_COL, 0, col2=1)],
+            [rf.FPred(F.F_NE_COL, 0, col2=2)],
+            [rf.FPred(F.F_BETWEEN, 2, value=4, hi=17)],
+            [rf.FPred(F.F_IN, 2, ids=ids[:3])],
+            [rf.FPred(F.F_IN, 2, ids=ids)],
+            [rf.FPred(F.F_IS_NULL, 1)],
+            [rf.FPred(F.F_IS_NOT_NULL, 1), rf.FPred(F.F_NE_CONST, 2, value=9), rf.FPred(F.F_BETWEEN, 0, value=2, hi=25)],
+            [],
+        ]
+        for prog in programs:
+            got = T.filter(prog)
+            exp = oracle.filter_table(ot, prog)
+            assert got.num_rows == exp._rows, (n, prog)
+            for a, b in zip(got.to_numpy(), exp.cols):
+                assert np.array_equal(a, b), (n, prog)  # order-preserving
+
+
+def test_import_export_validity_and_arrow_roundtrip(ctx):
+    import pyarrow as pa
+    rng = np.random.default_rng(8)
+    n = 1000
+    a = rng.integers(1, 100, n).astype(np.uint32)
+    b = rng.integers(1, 100, n).astype(np.uint32)
+    mask = rng.random(n) < 0.25
+    batch = pa.record_batch([pa.array(a, type=pa.uint32()), pa.array(b, type=pa.uint32(), mask=mask)],
+                            schema=pa.schema([pa.field("x", pa.uint32(), nullable=False), pa.field("y", pa.uint32())]))
+    T = ctx.import_arrow(batch)
+    assert T.names == ["x", "y"] and T.nullable == [False, True] and T.num_rows == n
+    cols, bits, nulls = T.to_numpy(with_validity=True)
+    assert np.array_equal(cols[0], a)
+    assert np.array_equal(cols[1], np.where(mask, 0, b))
+    assert nulls == [0, int(mask.sum())]
+    assert np.array_equal(np.unpackbits(bits[1], bitorder="little")[:n].astype(bool), ~mask)
+    back = T.to_arrow()
+    assert back.schema.equals(batch.schema)
+    assert back.equals(batch)
+    sl = T.to_arrow(row_off=100, n_rows=333)
+    assert sl.equals(batch.slice(100, 333))
+    # a sliced (offset) input batch
+    T2 = ctx.import_arrow(batch.slice(13, 500))
+    assert T2.to_arrow().equals(batch.slice(13, 500))
+
+
+def test_partition_groups_rows_by_destination(ctx):
+    rng = np.random.default_rng(12)
+    n = 30000
+    cols = {"k": rng.integers(1, 5000, n).astype(np.uint32), "v": np.arange(1, n + 1, dtype=np.uint32)}
+    T = ctx.import_table(cols)
+    for parts in (1, 2, 8):
+        P, counts = T.partition("k", parts)
+        assert sum(counts) == n
+        k, v = P.to_numpy()
+        assert np.array_equal(canonical([k, v]), canonical([cols["k"], cols["v"]]))
+        dest = np.array([F.load().rfgpu_shuffle_dest(int(x), parts) for x in k[:2000]])
+        off = np.concatenate([[0], np.cumsum(counts)])
+        for p in range(parts):
+            seg = k[off[p]:off[p + 1]]
+            assert all(F.load().rfgpu_shuffle_dest(int(x), parts) == p for x in seg[:200])
+        assert np.all(np.diff(dest) >= 0)
+
+
+def test_pattern_plan_end_to_end(ctx, oracle):
+    """?s p1 ?o1 . ?s p2 ?o2 OPTIONAL { ?o2 p3 ?x } FILTER(!BOUND(?x)) on a synthetic graph, device-resident."""
+    g = rf.generate_graph(60000, n_predicates=16, s=1.0, seed=2)
+    quads = g.quads()
+    st = _gpu_store(ctx, quads)
+    ost = oracle.OracleStore(8192).load_quads(quads)
+    p1, p2, p3 = g.pred_id(1), g.pred_id(2), g.pred_id(3)
+
+    def plans(store):
+        a = store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(p1), rf.scan("o1")])
+        b = store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(p2), rf.scan("o2")])
+        c = store.plan([rf.traverse(0), rf.scan("o2"), rf.traverse(p3), rf.scan("x")])
+        return a, b, c
+    ga, gb, gc = (p.execute(allow_view=True) for p in plans(st))
+    oa, ob, oc = (p.execute() for p in plans(ost))
+    gj = ga.join(gb).join(gc, F.JOIN_LEFT)
+    oj, _, _ = oracle.sparql_join(oracle.sparql_join(oa, ob, F.JOIN_INNER, "hash")[0], oc, F.JOIN_LEFT, "hash")
+    assert gj.names == oj.names == ["s", "o1", "o2", "x"]
+    assert gj.num_rows == oj._rows > 0
+    assert_same_table(gj.names, gj.to_numpy(), oj.names, oj.cols)
+    xi = gj.names.index("x")
+    gf = gj.filter([rf.FPred(F.F_IS_NULL, xi)])
+    of = oracle.filter_table(oj, [rf.FPred(F.F_IS_NULL, xi)])
+    assert gf.num_rows == of._rows
+    assert_same_table(gf.names, gf.to_numpy(), of.names, of.cols)
+    m = ctx.metrics()
+    assert m["kernel_launches"] > 0 and m["join_rows_out"] > 0

@@ -1,0 +1,131 @@
+"""CPU: the oracle restatement against the reference's own known-answer tests (tests/golden/scan_golden.json)."""
+import numpy as np
+import pytest
+
+import rdf_fusion_b200 as rf
+from rdf_fusion_b200 import _ffi as F
+
+from helpers import OPS, PERMS, case_quads, decode_instr, decode_pred
+
+
+def _store(oracle, case):
+    st = oracle.OracleStore(case["batch_size"], [PERMS[p] for p in case.get("perms", ["GSPO", "GPOS", "GOSP"])])
+    q = case_quads(case)
+    if q:
+        st.insert(q)
+    return st
+
+
+def test_scan_cases(oracle, scan_golden):
+    for case in scan_golden["scan_cases"]:
+        st = _store(oracle, case)
+        if "remove" in case:
+            assert st.remove(case["remove"]) == case["expect_removed"], case["name"]
+        plan = st.plan([decode_instr(e) for e in case["instr"]])
+        for col, lo, hi in case.get("dynamic_between", []):
+            plan.apply_between(col, lo, hi)
+        exp = case["expect"]
+        if "index" in exp:
+            assert F.PERM_NAMES[plan.index] == exp["index"], case["name"]
+        t = plan.execute()
+        assert t._rows == exp["rows"], case["name"]
+        assert len(t.names) == exp["cols"], case["name"]
+        if "columns" in exp:
+            for name, vals in exp["columns"].items():
+                assert list(t.cols[t.names.index(name)]) == vals, case["name"]
+        if "names" in exp:
+            assert t.names == exp["names"], case["name"]
+        if "batches" in exp:
+            assert t.batch_rows == exp["batches"], case["name"]
+        if "nullable" in exp:
+            assert t.nullable == exp["nullable"], case["name"]
+
+
+def test_choose_index(oracle, scan_golden):
+    st = oracle.OracleStore(100)
+    for case in scan_golden["choose_index_cases"]:
+        plan = st.plan([decode_instr(e) for e in case["instr"]])
+        assert F.PERM_NAMES[plan.index] == case["expect"], case["name"]
+
+
+def test_try_and_with(oracle, scan_golden):
+    kinds = {"false": F.PRED_FALSE, "in": F.PRED_IN, "between": F.PRED_BETWEEN}
+    for case in scan_golden["try_and_with_cases"]:
+        r = oracle.try_and_with(decode_pred(case["a"]), decode_pred(case["b"]))
+        e = case["expect"]
+        if e is None:
+            assert r is None, case
+            continue
+        kind, lo, hi, ids = r
+        (k, v), = e.items()
+        assert kind == kinds[k], case
+        if k == "in":
+            assert ids == v, case
+        if k == "between":
+            assert [lo, hi] == v, case
+
+
+def test_find_range(oracle, scan_golden):
+    for case in scan_golden["find_range_cases"]:
+        kind, a, b = oracle.find_range(case["values"], case["find"], case["find"])
+        exp = case["expect"]
+        assert kind == exp[0], case
+        if kind == "Contained":
+            assert [a, b] == exp[1:], case
+        if kind == "NotContained":
+            assert a == exp[1], case
+
+
+def test_row_groups(oracle, scan_golden):
+    for case in scan_golden["row_group_cases"]:
+        st = oracle.OracleStore(case["batch_size"], [F.GSPO])
+        st.insert([[v] * 4 for v in case["diag"]])
+        if "diag2" in case:
+            st.insert([[v] * 4 for v in case["diag2"]])
+        if "expect_lens" in case:
+            assert st.group_lens() == case["expect_lens"], case
+        if "expect_len" in case:
+            assert len(st) == case["expect_len"], case
+
+
+def test_prune(oracle, scan_golden):
+    for case in scan_golden["prune_cases"]:
+        st = oracle.OracleStore(case["batch_size"], [F.GSPO])
+        st.insert(case["index_order"])
+        plan = st.plan([decode_instr(e) for e in case["instr"]])
+        rows, slices = plan.pruned_rows()
+        assert (slices, rows) == (case["expect_slices"], case["expect_rows"]), case["name"]
+
+
+def test_pushdown_display(oracle, scan_golden):
+    for case in scan_golden["pushdown_cases"]:
+        st = oracle.OracleStore(100)
+        plan = st.plan([rf.traverse(0), rf.scan("subject"), rf.traverse(7), rf.scan("object")])
+        if case["op"] == "gt_and_lt":
+            plan.apply_filter("object", F.OP_GT, case["value"]).apply_filter("object", F.OP_LT, case["value2"])
+        else:
+            plan.apply_filter("object", OPS[case["op"]], case["value"])
+        d = plan.describe()
+        assert d.startswith("[" + case["expect_index"] + "] "), (case, d)
+        assert d.endswith(case["expect_filters"]), (case, d)
+
+
+def test_apply_filter_errors(oracle):
+    st = oracle.OracleStore(100)
+    plan = st.plan([rf.traverse(0), rf.scan("s"), rf.scan("s"), rf.scan("o")])
+    with pytest.raises(oracle.OracleError, match="Could not find scan instruction"):
+        plan.apply_filter("nope", F.OP_EQ, 1)
+
+
+def test_named_graph_patterns(oracle):
+    """AnyNamedGraph = Between(1, MAX) on the graph level; default graph rows (id 0 = NULL) are excluded and a bound
+    graph variable reports 0 only for the default graph (scan_instructions.rs:323-355)."""
+    st = oracle.OracleStore(4)
+    st.insert([[0, 1, 2, 3], [5, 1, 2, 3], [6, 1, 2, 4], [0, 9, 2, 3]])
+    t = st.plan([rf.scan("g", rf.Between(1, 0xFFFFFFFF)), rf.scan("s"), rf.traverse(2), rf.scan("o")]).execute()
+    assert sorted(t.cols[0]) == [5, 6]
+    t = st.plan([rf.scan("g"), rf.scan("s"), rf.traverse(2), rf.scan("o")]).execute()
+    assert sorted(t.cols[0]) == [0, 0, 5, 6]
+    # a multi-id In containing the default graph id cannot match NULL rows in the selection vector (arrow eq on NULL)
+    t = st.plan([rf.scan("g", rf.In(0, 5)), rf.scan("s"), rf.traverse(2), rf.scan("o")]).execute()
+    assert sorted(t.cols[0]) == [5]
