@@ -1,0 +1,326 @@
+#!/usr/bin/env python
+"""bench.py — pattern-scan + join rows/s on B200 (BASELINE.json configs[1]):
+single quad-pattern scans + a 2-pattern star join on a synthetic 100M-triple graph with Zipf-distributed predicates.
+
+One step = one pass of the hot path over the resident index:
+  Q2a  ?s <p_r> ?o  for r in {1, 10, 100}      range lookup + 128-bit column gather (materialised, 2 columns)
+  Q2b  ?s <p_1> ?o1 . ?s <p_2> ?o2             two scans (zero-copy views) + equi hash join on ?s (3 output columns)
+rows per step = rows matched by the three Q2a scans + build and probe rows of the Q2b join (inputs, not outputs).
+
+`value`  : device-resident — index in HBM, results stay in HBM.
+`e2e`    : the same step through the C ABI with HOST buffers: every scan result is exported to pinned host memory, the
+           join imports both inputs from pinned host memory and exports its result (what a GPU ExecutionPlan node with
+           CPU children/parents would do per query).
+`--impl reference`: the reference's CPU algorithm (the oracle port; the Rust crate cannot be built here) on the host
+           cores, on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+RANKS = (1, 10, 100)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--triples", type=int, default=100_000_000, help="triples per GPU (weak scaling)")
+    ap.add_argument("--predicates", type=int, default=1024)
+    ap.add_argument("--zipf", type=float, default=1.0)
+    ap.add_argument("--seed", type=int, default=2)
+    ap.add_argument("--cpu-triples", type=int, default=4_000_000, help="bounded sample for the CPU baseline")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a, n):
+    return (f"configs[1]: Q2a ?s <p_r> ?o (r=1,10,100) + Q2b star join ?s <p1> ?o1 . ?s <p2> ?o2 on "
+            f"G(N={n}, P={a.predicates}, zipf={a.zipf}, seed={a.seed})")
+
+
+# ------------------------------------------------------------------ CPU baseline / reference arm (oracle port)
+def cpu_reference(a, steps, warmup):
+    """The reference's algorithm restated on the CPU (oracle/): row groups of 8192, linear row-group pruning, arrow-style
+    predicate passes, build-left/probe-right hash join partitioned over all host threads."""
+    import rdf_fusion_b200 as rf
+    from oracle import oracle_py as orc
+    from rdf_fusion_b200 import _ffi as F
+    cores = os.cpu_count() or 1
+    n = a.cpu_triples
+    g = rf.generate_graph(n, a.predicates, a.zipf, a.seed)
+    ost = orc.OracleStore(8192).load_quads(g.quads())
+
+    def step():
+        rows = 0
+        for r in RANKS:
+            t = ost.plan([rf.traverse(0), rf.scan("s"), rf.traverse(g.pred_id(r)), rf.scan("o")]).execute()
+            rows += t._rows
+        ta = ost.plan([rf.traverse(0), rf.scan("s"), rf.traverse(g.pred_id(1)), rf.scan("o1")]).execute()
+        tb = ost.plan([rf.traverse(0), rf.scan("s"), rf.traverse(g.pred_id(2)), rf.scan("o2")]).execute()
+        tj, _, _ = orc.sparql_join(ta, tb, F.JOIN_INNER, "hash", cores)
+        rows += ta._rows + tb._rows
+        return rows, tj._rows
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    rows = out = 0
+    for _ in range(steps):
+        r, o = step()
+        rows += r
+        out += o
+    dt = time.perf_counter() - t0
+    return {"value": rows / dt, "unit": "rows/s", "cores": cores, "kind": "port",
+            "sample": f"same queries on G(N={n}) ({len(ost)} distinct triples), {steps} steps, {rows // max(steps,1)} rows/step, "
+                      f"oracle port of the reference algorithm (Rust toolchain absent: reference itself unbuildable here)",
+            "ms_per_step": 1e3 * dt / max(steps, 1), "rows_out_per_step": out // max(steps, 1)}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, min(a.steps, 5))
+    warm = max(1, min(a.warmup, 2))
+    cb = cpu_reference(a, steps, warm)
+    line = {"impl": "reference", "metric": "pattern-scan+join rows/s", "value": cb["value"], "unit": "rows/s",
+            "n_gpus": a.gpus, "steps": steps, "warmup": warm, "ms_per_step": cb["ms_per_step"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": workload_name(a, a.cpu_triples), "note": "bounded sample of the GPU arm's workload"},
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                       "-i", str(self.gpu)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        sm, mx, reasons = [], [], set()
+        for ln in open(self.f.name):
+            parts = [x.strip() for x in ln.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                mx.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ GPU arm
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+
+    import rdf_fusion_b200 as rf
+    from rdf_fusion_b200 import _ffi as F
+    from rdf_fusion_b200.loader import load_store_device, partition_by_subject
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = rf.Context(local)
+
+    # ---- set-up (untimed): the global graph has world * triples rows; this rank owns the quads whose subject hashes
+    # to it, so every scan is local and the star join on ?s needs no exchange (weak scaling, no data-path collective)
+    n_global = a.triples * world
+    t0 = time.perf_counter()
+    g = rf.generate_graph(n_global, a.predicates, a.zipf, a.seed)
+    cols = partition_by_subject((g.g, g.s, g.p, g.o), rank, world)
+    store = load_store_device(ctx, *cols)
+    del cols
+    setup_s = time.perf_counter() - t0
+    pid = g.pred_id
+    n_local = len(store)
+
+    plans_a = [store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(pid(r)), rf.scan("o")]) for r in RANKS]
+    plan_j1 = store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(pid(1)), rf.scan("o1")])
+    plan_j2 = store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(pid(2)), rf.scan("o2")])
+
+    def step_device():
+        rows = 0
+        for p in plans_a:
+            t = p.execute(allow_view=False)
+            rows += t.num_rows
+        ta = plan_j1.execute(allow_view=True)
+        tb = plan_j2.execute(allow_view=True)
+        tj = ta.join(tb, F.JOIN_INNER)
+        rows += ta.num_rows + tb.num_rows
+        return rows, tj.num_rows
+
+    # ---- e2e: host buffers in and out, through the C ABI
+    def pinned(n):
+        return torch.empty(max(n, 1), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
+    probe = [p.execute(allow_view=True) for p in plans_a]
+    ja, jb = plan_j1.execute(allow_view=True), plan_j2.execute(allow_view=True)
+    jout = ja.join(jb, F.JOIN_INNER)
+    scan_bufs = [[pinned(t.num_rows) for _ in range(2)] for t in probe]
+    in_a = [pinned(ja.num_rows) for _ in range(2)]
+    in_b = [pinned(jb.num_rows) for _ in range(2)]
+    ja.to_numpy(out=in_a)
+    jb.to_numpy(out=in_b)
+    na, nb, nj = ja.num_rows, jb.num_rows, jout.num_rows
+    out_bufs = [pinned(nj) for _ in range(3)]
+    h2d = 4 * 2 * (na + nb)
+    d2h = 4 * (2 * sum(t.num_rows for t in probe) + 3 * nj)
+    del probe, ja, jb, jout
+
+    def step_e2e():
+        rows = 0
+        for p, bufs in zip(plans_a, scan_bufs):
+            t = p.execute(allow_view=True)
+            t.to_numpy(out=bufs)
+            rows += t.num_rows
+        ta = ctx.import_table({"s": in_a[0][:na], "o1": in_a[1][:na]})
+        tb = ctx.import_table({"s": in_b[0][:nb], "o2": in_b[1][:nb]})
+        tj = ta.join(tb, F.JOIN_INNER)
+        tj.to_numpy(out=out_bufs)
+        rows += na + nb
+        return rows, tj.num_rows
+
+    def barrier():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def timed(fn, steps, warmup, profile=False):
+        for _ in range(warmup):
+            fn()
+        ctx.metrics_reset()
+        ctx.profile_enable(profile)
+        barrier()
+        rows = out = 0
+        ms = 0.0
+        for _ in range(steps):
+            ctx.flush_l2()  # write 256 MB (> 126 MB L2) between timed iterations, outside the timed region
+            ctx.synchronize()
+            ctx.timer_start()
+            r, o = fn()
+            ms += ctx.timer_stop()
+            rows += r
+            out += o
+        barrier()
+        prof = ctx.profile() if profile else {}
+        ctx.profile_enable(False)
+        m = ctx.metrics()
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+            c = torch.tensor([rows, out], dtype=torch.int64, device="cuda")
+            dist.all_reduce(c, op=dist.ReduceOp.SUM)
+            rows, out = int(c[0].item()), int(c[1].item())
+        return rows, out, ms, prof, m
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    rows, out, ms, prof, met = timed(step_device, a.steps, max(a.warmup, 3), profile=True)
+    clocks = sampler.stop()
+    e2e = None
+    if not a.no_e2e:
+        erows, eout, ems, _, emet = timed(step_e2e, a.steps, max(a.warmup, 3))
+        e2e = {"value": erows / (ems / 1e3), "unit": "rows/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ms_per_step": ems / a.steps}
+
+    # ---- roofline of the dominant kernel (per-launch CUDA-event time on the ctx stream, inside the timed region)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    kern = {k: v for k, v in prof.items() if v["ms"] > 0}
+    roof = None
+    breakdown = {}
+    if kern:
+        tot = sum(v["ms"] for v in kern.values())
+        for k, v in sorted(kern.items(), key=lambda kv: -kv[1]["ms"]):
+            gbs = v["bytes"] / (v["ms"] / 1e3) / 1e9 if v["bytes"] else None
+            breakdown[k] = {"launches": v["launches"], "ms_per_launch": v["ms"] / v["launches"],
+                            "share": v["ms"] / tot, "alg_GBps": gbs}
+        top = max(kern, key=lambda k: kern[k]["ms"])
+        v = kern[top]
+        ach = v["bytes"] / (v["ms"] / 1e3) / 1e9
+        roof = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": peak_src,
+                "alg_bytes_per_launch": v["bytes"] / v["launches"], "ms_per_launch": v["ms"] / v["launches"]}
+
+    if rank == 0:
+        cb = None
+        if world == 1 and not a.no_cpu_baseline:
+            c = cpu_reference(a, 2, 1)
+            cb = {k: c[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        line = {"metric": "pattern-scan+join rows/s", "value": rows / (ms / 1e3), "unit": "rows/s", "n_gpus": world,
+                "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms / a.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+                "config": {"workload": workload_name(a, n_global), "triples_per_gpu": a.triples,
+                           "distinct_triples_rank0": n_local, "rows_in_per_step": rows // a.steps,
+                           "rows_out_per_step": out // a.steps, "l2": "flushed between iterations (256 MB memset)",
+                           "partitioning": "quads hash-partitioned on subject; star join on ?s needs no exchange",
+                           "setup_s": round(setup_s, 1), "kernels": breakdown},
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(met["kernel_launches"]),
+                "roofline": roof, "cpu_baseline": cb}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

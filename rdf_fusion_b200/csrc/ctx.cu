@@ -40,8 +40,16 @@ KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes) : ctx(c
   ctx->kstats[idx].second.launches++;
   ctx->kstats[idx].second.bytes += bytes;
   if (ctx->profiling) {
-    RF_CUDA(cudaEventCreate(&a));
-    RF_CUDA(cudaEventCreate(&b));
+    auto take = [&](cudaEvent_t* e) {
+      if (!ctx->event_pool.empty()) {
+        *e = ctx->event_pool.back();
+        ctx->event_pool.pop_back();
+      } else {
+        RF_CUDA(cudaEventCreate(e));
+      }
+    };
+    take(&a);
+    take(&b);
     RF_CUDA(cudaEventRecord(a, ctx->stream()));
   }
 }
@@ -83,8 +91,8 @@ void rfgpu_ctx::collect_profile() {
     float ms = 0;
     cudaEventElapsedTime(&ms, p.a, p.b);
     kstats[p.idx].second.ms += ms;
-    cudaEventDestroy(p.a);
-    cudaEventDestroy(p.b);
+    event_pool.push_back(p.a);
+    event_pool.push_back(p.b);
   }
   pending.clear();
 }
@@ -170,6 +178,7 @@ void rfgpu_ctx_destroy(rfgpu_ctx* ctx) {
     cudaEventDestroy(p.a);
     cudaEventDestroy(p.b);
   }
+  for (auto e : ctx->event_pool) cudaEventDestroy(e);
   if (ctx->t0) cudaEventDestroy(ctx->t0);
   if (ctx->t1) cudaEventDestroy(ctx->t1);
   if (ctx->h_scratch) cudaFreeHost(ctx->h_scratch);

@@ -104,6 +104,7 @@ struct rfgpu_ctx {
   std::vector<std::pair<std::string, rf::KernelStat>> kstats;
   struct Pending { int idx; cudaEvent_t a, b; };
   std::vector<Pending> pending;
+  std::vector<cudaEvent_t> event_pool;
   cudaEvent_t t0 = nullptr, t1 = nullptr;
   void* flush_buf = nullptr;
   size_t flush_bytes = 0;
