@@ -136,6 +136,11 @@ size_t rfgpu_scan_plan_describe(const rfgpu_scan_plan* p, char* buf, size_t cap)
 int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t flags, rfgpu_table** out);
 /* the contiguous index range pruning narrowed to, and rows kept by the residual predicates */
 int32_t rfgpu_scan_last_range(const rfgpu_ctx* ctx, uint64_t* from, uint64_t* to);
+/* Interesting orders: among the permutations that tie for the best choose_index score, prefer the one whose scan
+ * output comes out sorted by `column` (rows of a scan are in index order, scan.rs:135-205), so that a following
+ * join on that variable can run as a streaming merge join instead of a hash join.  *achieved = 1 if such a
+ * permutation exists (plan switched to it), 0 otherwise (plan unchanged).  Results are permutation-independent. */
+int32_t rfgpu_scan_plan_order_by(rfgpu_ctx* ctx, rfgpu_scan_plan* p, const char* column, int32_t* achieved);
 
 /* ---- tables (solution mappings on the device) ---- */
 rfgpu_table* rfgpu_table_retain(rfgpu_table* t);
@@ -161,6 +166,11 @@ int32_t rfgpu_table_project(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t n_cols
                             const int32_t* cols, const char* const* new_names, rfgpu_table** out);
 /* override schema nullability (a field's is_nullable is a schema property: join/rewrite.rs:131-139) */
 int32_t rfgpu_table_set_nullable(rfgpu_table* t, int32_t col, int32_t nullable);
+/* column the rows are known to be sorted by (ascending, NULL first), or -1.  Set by scans, kept by filters and joins. */
+int32_t rfgpu_table_sorted_col(const rfgpu_table* t);
+/* Declare an imported table sorted by `col` (the child plan's output_ordering); verified on the device
+ * (RFGPU_E_INVALID if the column is not ascending).  col = -1 clears the property. */
+int32_t rfgpu_table_set_sorted_col(rfgpu_ctx* ctx, rfgpu_table* t, int32_t col);
 
 /* ---- Arrow C Data Interface (what arrow-rs `arrow::ffi` speaks) ---- */
 struct ArrowSchema;
@@ -218,6 +228,16 @@ int32_t rfgpu_sparql_join(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_ta
                           int32_t join_type, rfgpu_table** out);
 /* which lowering the last rfgpu_sparql_join on this ctx took (rfgpu_join_algo) */
 int32_t rfgpu_last_join_algo(const rfgpu_ctx* ctx);
+/* physical operator the last equi (sub-)join used */
+typedef enum { RFGPU_JOIN_PHYS_NONE = 0, RFGPU_JOIN_PHYS_HASH = 1, RFGPU_JOIN_PHYS_MERGE = 2 } rfgpu_join_phys;
+int32_t rfgpu_last_join_phys(const rfgpu_ctx* ctx);
+
+/* ---- options ---- */
+typedef enum {
+  RFGPU_OPT_MERGE_JOIN = 1 /* 1 (default): one-key equi joins whose inputs are both sorted on the key run as a
+                              streaming merge join; 0: always build/probe the hash table */
+} rfgpu_option;
+int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value);
 
 /* ---- multi-GPU: one process (ctx) per GPU, NCCL over NVLink ---- */
 #define RFGPU_UNIQUE_ID_BYTES 128

@@ -32,6 +32,8 @@ F_EQ_CONST, F_NE_CONST, F_EQ_COL, F_NE_COL, F_BETWEEN, F_IN, F_IS_NULL, F_IS_NOT
 JOIN_INNER, JOIN_LEFT = 0, 1
 ALGO_CROSS, ALGO_EQUI, ALGO_COMPATIBLE = 0, 1, 2
 SCAN_ALLOW_VIEW = 1
+PHYS_NONE, PHYS_HASH, PHYS_MERGE = 0, 1, 2
+OPT_MERGE_JOIN = 1
 UNIQUE_ID_BYTES = 128
 
 u32p = C.POINTER(C.c_uint32)
@@ -102,6 +104,11 @@ SIGNATURES = {
     "rfgpu_filter": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(FilterPred), C.c_int32, C.POINTER(C.c_void_p)]),
     "rfgpu_sparql_join": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]),
     "rfgpu_last_join_algo": (C.c_int32, [C.c_void_p]),
+    "rfgpu_last_join_phys": (C.c_int32, [C.c_void_p]),
+    "rfgpu_ctx_set_option": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int64]),
+    "rfgpu_table_sorted_col": (C.c_int32, [C.c_void_p]),
+    "rfgpu_table_set_sorted_col": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32]),
+    "rfgpu_scan_plan_order_by": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_char_p, C.POINTER(C.c_int32)]),
     "rfgpu_comm_unique_id": (C.c_int32, [u8p]),
     "rfgpu_comm_init": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, u8p]),
     "rfgpu_comm_rank": (C.c_int32, [C.c_void_p]),

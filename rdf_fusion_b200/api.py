@@ -147,6 +147,9 @@ class Context:
     def synchronize(self):
         self.check(self.lib.rfgpu_ctx_synchronize(self.h))
 
+    def set_option(self, option: int, value: int):
+        self.check(self.lib.rfgpu_ctx_set_option(self.h, option, value))
+
     # ---- store ----
     def store(self) -> "Store":
         return Store(self)
@@ -312,6 +315,12 @@ class ScanPlan:
         self.ctx.check(self.ctx.lib.rfgpu_scan_plan_set_index(self.ctx.h, self.h, perm))
         return self
 
+    def order_by(self, column: str) -> bool:
+        """prefer, among equally scored permutations, one that returns `column` sorted (enables merge joins)"""
+        got = C.c_int32()
+        self.ctx.check(self.ctx.lib.rfgpu_scan_plan_order_by(self.ctx.h, self.h, column.encode(), C.byref(got)))
+        return bool(got.value)
+
     @property
     def index(self) -> int:
         return int(self.ctx.lib.rfgpu_scan_plan_index(self.h))
@@ -435,3 +444,16 @@ class Table:
     @property
     def last_join_algo(self) -> int:
         return int(self.ctx.lib.rfgpu_last_join_algo(self.ctx.h))
+
+    @property
+    def last_join_phys(self) -> int:
+        return int(self.ctx.lib.rfgpu_last_join_phys(self.ctx.h))
+
+    @property
+    def sorted_col(self) -> int:
+        return int(self.ctx.lib.rfgpu_table_sorted_col(self.h))
+
+    def set_sorted(self, col) -> "Table":
+        i = self.names.index(col) if isinstance(col, str) else int(col)
+        self.ctx.check(self.ctx.lib.rfgpu_table_set_sorted_col(self.ctx.h, self.h, i))
+        return self

@@ -307,6 +307,7 @@ extern "C" int32_t rfgpu_filter(rfgpu_ctx* ctx, const rfgpu_table* in, const rfg
   uint64_t kept = filter_compact(ctx, dp, src, in->rows, &bufs, "k_filter_compact", bytes_in);
   std::unique_ptr<rfgpu_table> t(new_table());
   t->rows = kept;
+  t->sorted_col = in->sorted_col;  // order-preserving compaction
   for (int c = 0; c < nc; c++) {
     Column col;
     col.name = in->cols[c].name;

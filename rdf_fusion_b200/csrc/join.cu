@@ -9,11 +9,62 @@
 // which yields exactly the pairs with  ∀k: l.k IS NULL ∨ r.k IS NULL ∨ l.k = r.k.
 #include <algorithm>
 
-#include "join_kernels.cuh"
+#include "merge_join.cuh"
 
 namespace rf {
 
 namespace {
+
+// streaming merge join of two inputs sorted on their single key column; returns the output row count and fills `bufs`
+uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint32_t* bk, uint64_t nb, bool left,
+                    const std::vector<OutColSpec>& specs, std::vector<BufRef>* bufs) {
+  bufs->clear();
+  if (np == 0) {
+    for (size_t c = 0; c < specs.size(); c++) bufs->push_back(alloc_col(ctx, 0));
+    return 0;
+  }
+  RF_REQUIRE(specs.size() <= (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 output columns in one join");
+  const uint32_t n_tiles = div_up(np, kMTile);
+  BufRef scratch = ctx->alloc((uint64_t)n_tiles * (8 + 8 + 8) + 16);
+  RF_CUDA(cudaMemsetAsync(scratch->ptr, 0, (uint64_t)n_tiles * 8, ctx->stream()));  // look-back words
+  MergeArgs A{};
+  A.pk = pk;
+  A.np = np;
+  A.bk = bk;
+  A.nb = nb;
+  A.left = left ? 1 : 0;
+  A.n_tiles = n_tiles;
+  A.status = scratch->as<unsigned long long>();
+  A.tile_base = A.status + n_tiles;
+  A.tile_win = reinterpret_cast<uint2*>(A.tile_base + n_tiles);
+  A.total = reinterpret_cast<unsigned long long*>(A.tile_win + n_tiles);
+  {
+    KernelScope ks(ctx, "k_merge_windows");
+    k_merge_windows<<<div_up((uint64_t)n_tiles * 32, 256), 256, 0, ctx->stream()>>>(A);
+  }
+  {
+    KernelScope ks(ctx, "k_merge_count", 4ull * (np + nb));
+    k_merge_count<<<n_tiles, kMThreads, 0, ctx->stream()>>>(A);
+  }
+  RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 10, A.total, 8, cudaMemcpyDeviceToHost, ctx->stream()));
+  ctx->sync();
+  const uint64_t n_out = ctx->h_scratch[10];
+  RF_REQUIRE(n_out < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED,
+             "join output exceeds 2^32-2 rows on one GPU (" + std::to_string(n_out) + ")");
+  for (size_t c = 0; c < specs.size(); c++) bufs->push_back(alloc_col(ctx, n_out));
+  if (n_out == 0) return 0;
+  A.n_cols = (int32_t)specs.size();
+  uint64_t in_cols_p = 0, in_cols_b = 0;
+  for (size_t c = 0; c < specs.size(); c++) {
+    A.cols[c] = specs[c];
+    A.dst[c] = (*bufs)[c]->as<uint32_t>();
+    in_cols_p += specs[c].probe != nullptr;
+    in_cols_b += specs[c].build != nullptr;
+  }
+  KernelScope ks(ctx, "k_merge_emit", 4ull * (in_cols_p * np + in_cols_b * nb + specs.size() * n_out));
+  k_merge_emit<<<n_tiles, kMThreads, 0, ctx->stream()>>>(A);
+  return n_out;
+}
 
 __global__ void k_iota(uint32_t* __restrict__ out, uint64_t n) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -203,6 +254,7 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
   for (auto& k : keys) any_nullable |= L->cols[k.l].nullable || R->cols[k.r].nullable;
   const int algo = keys.empty() ? RFGPU_JOIN_ALGO_CROSS : (any_nullable ? RFGPU_JOIN_ALGO_COMPATIBLE : RFGPU_JOIN_ALGO_EQUI);
   ctx->last_join_algo = algo;
+  ctx->last_join_phys = RFGPU_JOIN_PHYS_NONE;
 
   // output schema: lhs fields, then rhs-only fields (join/logical.rs:251-279)
   std::vector<int> rhs_only;
@@ -280,14 +332,37 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
     };
     ctx->m.join_probe_rows += Pt->rows;
     ctx->m.join_build_rows += Bt->rows;
-    ProbeResult P = hash_probe(ctx, (int)keys.size(), kc(Bt, 0), kc(Bt, 1), Bt->rows, kc(Pt, 0), kc(Pt, 1), Pt->rows, left);
     std::vector<OutColSpec> specs;
     for (size_t i = 0; i < nl; i++)
       specs.push_back(probe_is_l ? OutColSpec{L->cols[i].data, nullptr} : OutColSpec{nullptr, L->cols[i].data});
     for (int j : rhs_only)
       specs.push_back(probe_is_l ? OutColSpec{nullptr, R->cols[j].data} : OutColSpec{R->cols[j].data, nullptr});
+    // output rows come out in probe order: a sorted probe side keeps the result sorted on the same variable
+    int out_sorted = -1;
+    if (Pt->sorted_col >= 0) {
+      if (probe_is_l) {
+        out_sorted = Pt->sorted_col;
+      } else {
+        for (auto& k : keys)
+          if (k.r == Pt->sorted_col) out_sorted = k.l;
+        for (size_t x = 0; x < rhs_only.size(); x++)
+          if (rhs_only[x] == Pt->sorted_col) out_sorted = (int)(nl + x);
+      }
+    }
+    // both inputs sorted on the single join key (scans in index order): streaming merge join, no hash table
+    if (ctx->opt_merge_join && keys.size() == 1 && L->sorted_col == keys[0].l && R->sorted_col == keys[0].r &&
+        Pt->rows > 0) {
+      std::vector<BufRef> bufs;
+      uint64_t n_out = merge_join(ctx, kc(Pt, 0), Pt->rows, kc(Bt, 0), Bt->rows, left, specs, &bufs);
+      ctx->last_join_phys = RFGPU_JOIN_PHYS_MERGE;
+      T->sorted_col = keys[0].l;
+      return finish(bufs, n_out);
+    }
+    ProbeResult P = hash_probe(ctx, (int)keys.size(), kc(Bt, 0), kc(Bt, 1), Bt->rows, kc(Pt, 0), kc(Pt, 1), Pt->rows, left);
+    ctx->last_join_phys = RFGPU_JOIN_PHYS_HASH;
     auto bufs = alloc_out(P.n_out);
     expand(ctx, P, specs, raw(bufs), 0);
+    T->sorted_col = out_sorted;
     return finish(bufs, P.n_out);
   }
 
@@ -403,5 +478,16 @@ int32_t rfgpu_sparql_join(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_ta
 }
 
 int32_t rfgpu_last_join_algo(const rfgpu_ctx* ctx) { return ctx ? ctx->last_join_algo : -1; }
+int32_t rfgpu_last_join_phys(const rfgpu_ctx* ctx) { return ctx ? ctx->last_join_phys : 0; }
+
+int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
+  switch (option) {
+    case RFGPU_OPT_MERGE_JOIN: ctx->opt_merge_join = value != 0; break;
+    default: throw rf::Error(RFGPU_E_INVALID, "unknown option");
+  }
+  RF_API_END(ctx)
+}
 
 }  // extern "C"

@@ -78,6 +78,7 @@ struct rfgpu_table {
   std::atomic<int> refs{1};
   std::vector<rf::Column> cols;
   uint64_t rows = 0;
+  int sorted_col = -1;  // rows ascend by this column (NULL = 0 first); -1 unknown
 };
 
 struct rfgpu_index_t {
@@ -96,6 +97,8 @@ struct rfgpu_ctx {
   std::string err;
   rfgpu_metrics m{};
   int last_join_algo = -1;
+  int last_join_phys = 0;
+  bool opt_merge_join = true;
   uint64_t last_from = 0, last_to = 0;
   // pinned host scratch for small device→host results (ranges, counts)
   uint64_t* h_scratch = nullptr;  // 64 x u64

@@ -100,6 +100,72 @@ k_gather_range(const __grid_constant__ GatherArgs A) {
   for (; i < nvec; i += nthreads) d4[i] = __ldcs(s4 + i);
 }
 
+// ---- 1b (large ranges): the same copy driven by the TMA engine.  One warp per CTA; one elected lane streams 16 KB
+// chunks global → shared (cp.async.bulk + mbarrier complete_tx) → global (cp.async.bulk.global.shared) through a
+// 4-stage ring, so no data passes through registers and ~48 KB per CTA is always in flight.
+constexpr int kTmaChunk = 16384;  // bytes
+constexpr int kTmaStages = 4;
+
+__global__ void __launch_bounds__(32)
+k_gather_range_tma(const __grid_constant__ GatherArgs A) {
+  extern __shared__ __align__(128) unsigned char s_ring[];
+  __shared__ __align__(8) uint64_t s_full[kTmaStages];
+  const uint32_t lane = threadIdx.x;
+  // per column: head (scalar, until 16-B aligned), body (bulk chunks), tail (scalar)
+  const uint64_t n = A.n;
+  uint64_t head = ((16 - ((uintptr_t)A.src[0] & 15)) & 15) >> 2;  // all columns share the range's alignment
+  if (head > n) head = n;
+  const uint64_t body_bytes = ((n - head) * 4) & ~15ull;
+  const uint64_t tail0 = head + body_bytes / 4;
+  const uint64_t chunks_per_col = (body_bytes + kTmaChunk - 1) / kTmaChunk;
+  const uint64_t total_chunks = chunks_per_col * A.n_cols;
+  if (blockIdx.x == 0) {
+    for (int c = 0; c < A.n_cols; c++) {
+      if (lane < head) A.dst[c][lane] = A.src[c][lane];
+      if (lane < n - tail0) A.dst[c][tail0 + lane] = A.src[c][tail0 + lane];
+    }
+  }
+  if (lane != 0) return;
+  for (int s = 0; s < kTmaStages; s++) dev::mbar_init(&s_full[s], 1);
+  dev::mbar_fence_init();
+  auto chunk_ptrs = [&](uint64_t q, const unsigned char** src, unsigned char** dst, uint32_t* bytes) {
+    uint64_t c = q / chunks_per_col, k = q - c * chunks_per_col;
+    uint64_t off = k * kTmaChunk;
+    *bytes = (uint32_t)min((uint64_t)kTmaChunk, body_bytes - off);
+    *src = (const unsigned char*)(A.src[c] + head) + off;
+    *dst = (unsigned char*)(A.dst[c] + head) + off;
+  };
+  auto load = [&](uint64_t i, uint64_t q) {
+    int st = (int)(i % kTmaStages);
+    const unsigned char* src;
+    unsigned char* dst;
+    uint32_t bytes;
+    chunk_ptrs(q, &src, &dst, &bytes);
+    dev::mbar_expect_tx(&s_full[st], bytes);
+    dev::bulk_g2s(s_ring + (size_t)st * kTmaChunk, src, bytes, &s_full[st]);
+  };
+  // my chunks: q = blockIdx.x + i * gridDim.x
+  uint64_t n_mine = blockIdx.x < total_chunks ? (total_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  for (uint64_t i = 0; i < n_mine && i < (uint64_t)kTmaStages - 1; i++) load(i, blockIdx.x + i * gridDim.x);
+  for (uint64_t i = 0; i < n_mine; i++) {
+    int st = (int)(i % kTmaStages);
+    dev::mbar_wait(&s_full[st], (uint32_t)((i / kTmaStages) & 1));
+    const unsigned char* src;
+    unsigned char* dst;
+    uint32_t bytes;
+    chunk_ptrs(blockIdx.x + i * gridDim.x, &src, &dst, &bytes);
+    dev::bulk_s2g(dst, s_ring + (size_t)st * kTmaChunk, bytes);
+    dev::bulk_commit();
+    // refill the stage used by store i-1 (its smem has been read once at most one store group is still pending)
+    uint64_t nxt = i + kTmaStages - 1;
+    if (nxt < n_mine) {
+      dev::bulk_wait_read<1>();
+      load(nxt, blockIdx.x + nxt * gridDim.x);
+    }
+  }
+  dev::bulk_wait<0>();
+}
+
 static const rfgpu_index_t* find_index(const rfgpu_store* s, uint32_t perm) {
   for (auto& ix : s->indexes)
     if (ix.perm == perm) return &ix;
@@ -130,8 +196,16 @@ int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t fl
       if (perm_level(p->perm, l) == comp) level = l;
     oc.push_back({p->gspo.at[comp].var, level, comp == RFGPU_G});
   }
+  // rows come out in index order (compaction preserves it): remember which output column that order sorts
+  int sorted_out = -1;
+  {
+    std::string sv = ins.sorted_var();
+    for (size_t k = 0; k < oc.size(); k++)
+      if (!sv.empty() && oc[k].name == sv) sorted_out = (int)k;
+  }
   auto make_empty = [&]() {
     std::unique_ptr<rfgpu_table> t(new_table());
+    t->sorted_col = sorted_out;
     for (auto& o : oc) {
       Column c;
       c.name = o.name;
@@ -233,6 +307,7 @@ int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t fl
   }
 
   std::unique_ptr<rfgpu_table> t(new_table());
+  t->sorted_col = sorted_out;
   if (residual.empty()) {
     t->rows = R;
     if (flags & RFGPU_SCAN_ALLOW_VIEW) {
@@ -264,8 +339,21 @@ int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t fl
       uint64_t nvec = R / 4;
       uint32_t bx = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(nvec, (uint64_t)kGatherThreads * kGatherUnroll),
                                                                       (uint64_t)ctx->core->num_sms * 8));
-      KernelScope ks(ctx, "k_gather_range", bytes);
-      k_gather_range<<<dim3(bx, (uint32_t)oc.size()), kGatherThreads, 0, ctx->stream()>>>(G);
+      if (R * 4 >= (1u << 20)) {
+        static bool attr_set = false;
+        const int smem = kTmaChunk * kTmaStages;
+        if (!attr_set) {
+          RF_CUDA(cudaFuncSetAttribute(k_gather_range_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+          attr_set = true;
+        }
+        uint64_t chunks = ((R * 4 + kTmaChunk - 1) / kTmaChunk) * oc.size();
+        uint32_t grid = (uint32_t)std::min<uint64_t>(chunks, (uint64_t)ctx->core->num_sms * 3);
+        KernelScope ks(ctx, "k_gather_range_tma", bytes);
+        k_gather_range_tma<<<grid, 32, smem, ctx->stream()>>>(G);
+      } else {
+        KernelScope ks(ctx, "k_gather_range", bytes);
+        k_gather_range<<<dim3(bx, (uint32_t)oc.size()), kGatherThreads, 0, ctx->stream()>>>(G);
+      }
       ctx->m.algorithmic_bytes += bytes;
     }
     ctx->m.scan_rows_out += R;

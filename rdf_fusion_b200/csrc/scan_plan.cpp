@@ -161,6 +161,17 @@ size_t ScanInstrs::score() const {
   return s;
 }
 
+std::string ScanInstrs::sorted_var() const {
+  for (int i = 0; i < 4; i++) {
+    uint32_t a, b;
+    bool point = at[i].pred.pruning(&a, &b) && a == b &&
+                 (at[i].pred.kind != RFGPU_PRED_IN || at[i].pred.ids.size() == 1);
+    if (point) continue;  // constant along the range: does not affect the order
+    return at[i].scan ? at[i].var : std::string();
+  }
+  return std::string();
+}
+
 void ScanInstrs::apply(const std::string& column, const ScanPred& p) {
   int idx = -1;
   for (int i = 0; i < 4 && idx < 0; i++)
@@ -262,6 +273,23 @@ int32_t rfgpu_scan_plan_set_index(rfgpu_ctx* ctx, rfgpu_scan_plan* p, uint32_t p
 }
 
 uint32_t rfgpu_scan_plan_index(const rfgpu_scan_plan* p) { return p ? p->perm : 0xFFFFFFFFu; }
+
+int32_t rfgpu_scan_plan_order_by(rfgpu_ctx* ctx, rfgpu_scan_plan* p, const char* column, int32_t* achieved) {
+  RF_API_BEGIN
+  RF_REQUIRE(p && column, RFGPU_E_INVALID, "NULL argument");
+  if (achieved) *achieved = 0;
+  size_t best = 0;
+  for (auto& ix : p->store->indexes) best = std::max(best, p->gspo.reorder(ix.perm).score());
+  for (auto& ix : p->store->indexes) {
+    rf::ScanInstrs r = p->gspo.reorder(ix.perm);
+    if (r.score() == best && r.sorted_var() == column) {
+      p->perm = ix.perm;
+      if (achieved) *achieved = 1;
+      break;
+    }
+  }
+  RF_API_END(ctx)
+}
 
 size_t rfgpu_scan_plan_describe(const rfgpu_scan_plan* p, char* buf, size_t cap) {
   if (!p) return 0;

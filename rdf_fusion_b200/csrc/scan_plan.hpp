@@ -37,6 +37,9 @@ struct ScanInstrs {
   static ScanInstrs from_c(const rfgpu_scan_instruction gspo[4]);  // MemIndexScanInstructions::new_gspo :19-51
   ScanInstrs reorder(uint32_t to_perm) const;                      // :136-153
   size_t score() const;                                            // MemQuadIndex::compute_scan_score quad_index.rs:100-130
+  // Variable whose output column the scan returns sorted ("" if none): rows come out in index order, so after the
+  // leading levels pinned to one id the first remaining level orders the rows — if that level is scanned.
+  std::string sorted_var() const;
   // MemIndexScanInstructions::apply_filter :101-133 (throws rf::Error)
   void apply(const std::string& column, const ScanPred& p);
 };

