@@ -24,9 +24,9 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
     return 0;
   }
   RF_REQUIRE(specs.size() <= (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 output columns in one join");
+  RF_REQUIRE(nb < 0xFFFFFFFFull && np < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "merge join input exceeds 2^32-2 rows");
   const uint32_t n_tiles = div_up(np, kMTile);
-  BufRef scratch = ctx->alloc((uint64_t)n_tiles * (8 + 8 + 8) + 16);
-  RF_CUDA(cudaMemsetAsync(scratch->ptr, 0, (uint64_t)n_tiles * 8, ctx->stream()));  // look-back words
+  BufRef scratch = ctx->alloc((uint64_t)n_tiles * (8 + 8) + 16);
   MergeArgs A{};
   A.pk = pk;
   A.np = np;
@@ -35,34 +35,49 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
   A.left = left ? 1 : 0;
   A.n_tiles = n_tiles;
   A.status = scratch->as<unsigned long long>();
-  A.tile_base = A.status + n_tiles;
-  A.tile_win = reinterpret_cast<uint2*>(A.tile_base + n_tiles);
+  A.tile_win = reinterpret_cast<uint2*>(A.status + n_tiles);
   A.total = reinterpret_cast<unsigned long long*>(A.tile_win + n_tiles);
-  {
-    KernelScope ks(ctx, "k_merge_windows");
-    k_merge_windows<<<div_up((uint64_t)n_tiles * 32, 256), 256, 0, ctx->stream()>>>(A);
-  }
-  {
-    KernelScope ks(ctx, "k_merge_count", 4ull * (np + nb));
-    k_merge_count<<<n_tiles, kMThreads, 0, ctx->stream()>>>(A);
-  }
-  RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 10, A.total, 8, cudaMemcpyDeviceToHost, ctx->stream()));
-  ctx->sync();
-  const uint64_t n_out = ctx->h_scratch[10];
-  RF_REQUIRE(n_out < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED,
-             "join output exceeds 2^32-2 rows on one GPU (" + std::to_string(n_out) + ")");
-  for (size_t c = 0; c < specs.size(); c++) bufs->push_back(alloc_col(ctx, n_out));
-  if (n_out == 0) return 0;
   A.n_cols = (int32_t)specs.size();
   uint64_t in_cols_p = 0, in_cols_b = 0;
   for (size_t c = 0; c < specs.size(); c++) {
     A.cols[c] = specs[c];
-    A.dst[c] = (*bufs)[c]->as<uint32_t>();
-    in_cols_p += specs[c].probe != nullptr;
-    in_cols_b += specs[c].build != nullptr;
+    in_cols_p += specs[c].probe != nullptr && specs[c].probe != pk;  // payload columns besides the staged keys
+    in_cols_b += specs[c].build != nullptr && specs[c].build != bk;
   }
-  KernelScope ks(ctx, "k_merge_emit", 4ull * (in_cols_p * np + in_cols_b * nb + specs.size() * n_out));
-  k_merge_emit<<<n_tiles, kMThreads, 0, ctx->stream()>>>(A);
+  {
+    KernelScope ks(ctx, "k_merge_windows");
+    k_merge_windows<<<div_up((uint64_t)n_tiles * 32, 256), 256, 0, ctx->stream()>>>(A);
+  }
+  // Optimistic sizing: the output of the one-pass kernel is allocated before its size is known.  Twice the larger input
+  // covers joins whose average fan-out is <= 2 (every BSBM star/chain join); the kernel always reports the exact total
+  // and a second, exactly sized pass runs only when the guess was too small.
+  const uint64_t kLimit = 0xFFFFFFFEull;
+  uint64_t cap = std::min<uint64_t>(kLimit, 2 * std::max(np, nb) + 1024);
+  uint64_t n_out = 0;
+  for (int attempt = 0;; attempt++) {
+    bufs->clear();
+    for (size_t c = 0; c < specs.size(); c++) {
+      bufs->push_back(alloc_col(ctx, cap));
+      A.dst[c] = (*bufs)[c]->as<uint32_t>();
+    }
+    A.cap = cap;
+    RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_tiles * 8, ctx->stream()));  // look-back words
+    {
+      KernelScope ks(ctx, "k_merge_join", 4ull * (np + nb));  // keys; payload + output bytes are added below
+      k_merge_join<<<n_tiles, kMThreads, 0, ctx->stream()>>>(A);
+    }
+    RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 10, A.total, 8, cudaMemcpyDeviceToHost, ctx->stream()));
+    ctx->sync();
+    n_out = ctx->h_scratch[10];
+    RF_REQUIRE(n_out <= kLimit, RFGPU_E_UNSUPPORTED,
+               "join output exceeds 2^32-2 rows on one GPU (" + std::to_string(n_out) + ")");
+    if (n_out <= cap) break;
+    RF_REQUIRE(attempt == 0, RFGPU_E_EXEC, "merge join total changed between passes");
+    cap = n_out;
+  }
+  // payload columns other than the staged keys are gathered once per output row; count them per §8(d) as inputs read once
+  ctx->kstats[ctx->kstat_index("k_merge_join")].second.bytes +=
+      4ull * (in_cols_p * np + in_cols_b * nb + specs.size() * n_out);
   return n_out;
 }
 

@@ -339,3 +339,49 @@ def test_pattern_plan_end_to_end(ctx, oracle):
     assert_same_table(gf.names, gf.to_numpy(), of.names, of.cols)
     m = ctx.metrics()
     assert m["kernel_launches"] > 0 and m["join_rows_out"] > 0
+
+
+def _sorted_table(rng, n, key_space, payload, dup_heavy=None):
+    k = np.sort(rng.integers(1, key_space + 1, n).astype(np.uint32))
+    if dup_heavy is not None and n:
+        key, count = dup_heavy
+        k[:min(count, n)] = key
+        k = np.sort(k)
+    return {"k": k, payload: rng.integers(1, 1 << 30, n).astype(np.uint32)}
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_merge_join_adversarial_shapes(ctx, oracle, jt):
+    """The one-pass merge join on imported, declared-sorted tables: partial tiles, runs that straddle thread and tile
+    boundaries, a build side locally far denser than the probe side (window not staged), fan-out above the optimistic
+    output capacity (second, exactly sized pass), empty sides."""
+    rng = np.random.default_rng(11)
+    shapes = [
+        # (n_left, n_right, key_space, heavy_left, heavy_right)
+        (1, 1, 1, None, None),
+        (5, 0, 3, None, None),
+        (2047, 2049, 900, None, None),
+        (2048, 2048, 5000, None, None),
+        (6000, 5000, 3, None, None),             # 3 keys: every run spans many threads; fan-out ~1700 (> capacity guess)
+        (5000, 40000, 100000, None, None),       # sparse probe / dense build
+        (300, 200000, 50, None, None),           # build windows far larger than the staged window
+        (20000, 20000, 1 << 30, None, None),     # nearly no matches
+        (9000, 7000, 4000, (77, 3000), (77, 2500)),  # one heavy hitter on both sides (7.5M output rows)
+        (4100, 3000, 2000, (1, 2100), (2000, 900)),  # heavy run at the very start / very end
+    ]
+    for nl, nr, ks, hl, hr in shapes:
+        lc = _sorted_table(rng, nl, ks, "a", hl)
+        rc = _sorted_table(rng, nr, ks, "b", hr)
+        L = ctx.import_table(lc).set_sorted("k")
+        R = ctx.import_table(rc).set_sorted("k")
+        got = L.join(R, jt)
+        if nl and nr:
+            assert got.last_join_phys == F.PHYS_MERGE, (nl, nr)
+        ol = oracle.OTable(list(lc), [False, False], list(lc.values()))
+        orr = oracle.OTable(list(rc), [False, False], list(rc.values()))
+        exp, _, _ = oracle.sparql_join(ol, orr, jt, "hash")
+        assert got.num_rows == exp._rows, (nl, nr, ks, got.num_rows, exp._rows)
+        if exp._rows:
+            assert_same_table(got.names, got.to_numpy(), exp.names, exp.cols)
+            kk = got.to_numpy()[0]
+            assert np.all(np.diff(kk.astype(np.int64)) >= 0)  # output stays sorted on the key
