@@ -234,8 +234,9 @@ int32_t rfgpu_last_join_phys(const rfgpu_ctx* ctx);
 
 /* ---- options ---- */
 typedef enum {
-  RFGPU_OPT_MERGE_JOIN = 1 /* 1 (default): one-key equi joins whose inputs are both sorted on the key run as a
+  RFGPU_OPT_MERGE_JOIN = 1, /* 1 (default): one-key equi joins whose inputs are both sorted on the key run as a
                               streaming merge join; 0: always build/probe the hash table */
+  RFGPU_OPT_MERGE_THREADS = 2 /* CTA size of the merge-join kernel: 64, 128 (default) or 256 threads, 8 probe rows each */
 } rfgpu_option;
 int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value);
 

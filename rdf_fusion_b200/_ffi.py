@@ -34,6 +34,7 @@ ALGO_CROSS, ALGO_EQUI, ALGO_COMPATIBLE = 0, 1, 2
 SCAN_ALLOW_VIEW = 1
 PHYS_NONE, PHYS_HASH, PHYS_MERGE = 0, 1, 2
 OPT_MERGE_JOIN = 1
+OPT_MERGE_THREADS = 2
 UNIQUE_ID_BYTES = 128
 
 u32p = C.POINTER(C.c_uint32)

@@ -8,6 +8,7 @@
 // columns; class pair (ml, mr) is an equi join on the keys bound on both sides (or a product when there are none),
 // which yields exactly the pairs with  ∀k: l.k IS NULL ∨ r.k IS NULL ∨ l.k = r.k.
 #include <algorithm>
+#include <cstdlib>
 
 #include "merge_join.cuh"
 
@@ -25,8 +26,9 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
   }
   RF_REQUIRE(specs.size() <= (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 output columns in one join");
   RF_REQUIRE(nb < 0xFFFFFFFFull && np < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "merge join input exceeds 2^32-2 rows");
-  const uint32_t n_tiles = div_up(np, kMTile);
-  BufRef scratch = ctx->alloc((uint64_t)n_tiles * (8 + 8) + 16);
+  const int threads = ctx->opt_merge_threads;
+  const uint32_t n_tiles = div_up(np, (uint64_t)threads * kMItems);
+  BufRef scratch = ctx->alloc((uint64_t)n_tiles * 8 + 16);
   MergeArgs A{};
   A.pk = pk;
   A.np = np;
@@ -35,18 +37,14 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
   A.left = left ? 1 : 0;
   A.n_tiles = n_tiles;
   A.status = scratch->as<unsigned long long>();
-  A.tile_win = reinterpret_cast<uint2*>(A.status + n_tiles);
-  A.total = reinterpret_cast<unsigned long long*>(A.tile_win + n_tiles);
+  A.total = A.status + n_tiles;
   A.n_cols = (int32_t)specs.size();
+  if (const char* d = getenv("RFGPU_DEBUG_MERGE")) A.dbg = atoi(d);
   uint64_t in_cols_p = 0, in_cols_b = 0;
   for (size_t c = 0; c < specs.size(); c++) {
     A.cols[c] = specs[c];
     in_cols_p += specs[c].probe != nullptr && specs[c].probe != pk;  // payload columns besides the staged keys
     in_cols_b += specs[c].build != nullptr && specs[c].build != bk;
-  }
-  {
-    KernelScope ks(ctx, "k_merge_windows");
-    k_merge_windows<<<div_up((uint64_t)n_tiles * 32, 256), 256, 0, ctx->stream()>>>(A);
   }
   // Optimistic sizing: the output of the one-pass kernel is allocated before its size is known.  Twice the larger input
   // covers joins whose average fan-out is <= 2 (every BSBM star/chain join); the kernel always reports the exact total
@@ -64,11 +62,16 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
     RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_tiles * 8, ctx->stream()));  // look-back words
     {
       KernelScope ks(ctx, "k_merge_join", 4ull * (np + nb));  // keys; payload + output bytes are added below
-      k_merge_join<<<n_tiles, kMThreads, 0, ctx->stream()>>>(A);
+      switch (threads) {
+        case 64: k_merge_join<64><<<n_tiles, 64, 0, ctx->stream()>>>(A); break;
+        case 128: k_merge_join<128><<<n_tiles, 128, 0, ctx->stream()>>>(A); break;
+        default: k_merge_join<256><<<n_tiles, 256, 0, ctx->stream()>>>(A); break;
+      }
     }
     RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 10, A.total, 8, cudaMemcpyDeviceToHost, ctx->stream()));
     ctx->sync();
     n_out = ctx->h_scratch[10];
+    if (A.dbg) n_out = std::min(n_out, cap);
     RF_REQUIRE(n_out <= kLimit, RFGPU_E_UNSUPPORTED,
                "join output exceeds 2^32-2 rows on one GPU (" + std::to_string(n_out) + ")");
     if (n_out <= cap) break;
@@ -500,6 +503,10 @@ int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value) {
   RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
   switch (option) {
     case RFGPU_OPT_MERGE_JOIN: ctx->opt_merge_join = value != 0; break;
+    case RFGPU_OPT_MERGE_THREADS:
+      RF_REQUIRE(value == 64 || value == 128 || value == 256, RFGPU_E_INVALID, "merge-join CTA size must be 64, 128 or 256");
+      ctx->opt_merge_threads = (int)value;
+      break;
     default: throw rf::Error(RFGPU_E_INVALID, "unknown option");
   }
   RF_API_END(ctx)

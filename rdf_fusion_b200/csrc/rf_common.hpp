@@ -99,6 +99,7 @@ struct rfgpu_ctx {
   int last_join_algo = -1;
   int last_join_phys = 0;
   bool opt_merge_join = true;
+  int opt_merge_threads = 128;  // CTA size of k_merge_join (tile = 8 rows per thread)
   uint64_t last_from = 0, last_to = 0;
   // pinned host scratch for small device→host results (ranges, counts)
   uint64_t* h_scratch = nullptr;  // 64 x u64

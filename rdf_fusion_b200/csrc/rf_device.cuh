@@ -32,11 +32,14 @@ __device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v)
 }
 
 // Called by all 32 lanes of ONE warp of the tile's CTA.  Publishes `agg` for `tile` and returns the sum of the
-// aggregates of tiles [0, tile).
-__device__ __forceinline__ unsigned long long lookback_exclusive(unsigned long long* status, uint32_t tile,
-                                                                 unsigned long long agg) {
+// aggregates of tiles [0, tile).  The two halves can be called apart (publish early, resolve late) so that work which
+// does not need the prefix overlaps the time the predecessors' words take to become visible.
+__device__ __forceinline__ void lookback_publish(unsigned long long* status, uint32_t tile, unsigned long long agg) {
+  if ((threadIdx.x & 31) == 0) st_status(status + tile, (tile == 0 ? kFlagP : kFlagA) | agg);
+}
+__device__ __forceinline__ unsigned long long lookback_resolve(unsigned long long* status, uint32_t tile,
+                                                               unsigned long long agg) {
   const uint32_t lane = threadIdx.x & 31;
-  if (lane == 0) st_status(status + tile, (tile == 0 ? kFlagP : kFlagA) | agg);
   if (tile == 0) return 0;
   unsigned long long excl = 0;
   int64_t look = (int64_t)tile - 1;
@@ -56,6 +59,11 @@ __device__ __forceinline__ unsigned long long lookback_exclusive(unsigned long l
   }
   if (lane == 0) st_status(status + tile, kFlagP | (excl + agg));
   return excl;
+}
+__device__ __forceinline__ unsigned long long lookback_exclusive(unsigned long long* status, uint32_t tile,
+                                                                 unsigned long long agg) {
+  lookback_publish(status, tile, agg);
+  return lookback_resolve(status, tile, agg);
 }
 
 // Two prefixes at once (status arrays sa / sb advance together).
@@ -152,6 +160,10 @@ __device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint3
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)),
                "r"(bytes)
                : "memory");
+}
+// L2 prefetch of a byte range (src 16-B aligned, bytes a multiple of 16); no completion to wait for
+__device__ __forceinline__ void bulk_prefetch_l2(const void* gsrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>

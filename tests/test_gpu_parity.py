@@ -350,8 +350,16 @@ def _sorted_table(rng, n, key_space, payload, dup_heavy=None):
     return {"k": k, payload: rng.integers(1, 1 << 30, n).astype(np.uint32)}
 
 
+@pytest.fixture
+def merge_threads(ctx, request):
+    ctx.set_option(F.OPT_MERGE_THREADS, request.param)
+    yield request.param
+    ctx.set_option(F.OPT_MERGE_THREADS, 128)
+
+
+@pytest.mark.parametrize("merge_threads", [64, 128, 256], indirect=True)
 @pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
-def test_merge_join_adversarial_shapes(ctx, oracle, jt):
+def test_merge_join_adversarial_shapes(ctx, oracle, jt, merge_threads):
     """The one-pass merge join on imported, declared-sorted tables: partial tiles, runs that straddle thread and tile
     boundaries, a build side locally far denser than the probe side (window not staged), fan-out above the optimistic
     output capacity (second, exactly sized pass), empty sides."""
