@@ -110,3 +110,129 @@ def random_pattern(rng, quads, var_names=("a", "b", "c", "d")):
         else:
             instr.append(rf.traverse(rf.FALSE))
     return instr
+
+
+# ---------------------------------------------------------------- ID-level plans of tests/golden/join_golden.json
+MAX_ID = 0xFFFFFFFF
+
+
+class OracleBackend:
+    """Drives oracle/ (CPU restatement of the reference)."""
+
+    def __init__(self, oracle, quads):
+        self.o = oracle
+        self.store = oracle.OracleStore(8192).load_quads(np.asarray(quads, dtype=np.uint32).reshape(-1, 4))
+
+    def scan(self, instr):
+        t = self.store.plan(instr).execute()
+        return t.names, t.nullable, t.cols
+
+    def make(self, names, nullable, cols):
+        return self.o.OTable(names, nullable, cols)
+
+    def join(self, l, r, jt):
+        t = self.o.sparql_join(self.make(*l), self.make(*r), jt, "nested")[0]
+        return t.names, t.nullable, t.cols
+
+    def filter(self, t, preds):
+        r = self.o.filter_table(self.make(*t), preds)
+        return r.names, r.nullable, r.cols
+
+
+class GpuBackend:
+    """Drives the CUDA path through the C ABI; intermediates cross the host only for UNION (a host operator)."""
+
+    def __init__(self, ctx, quads):
+        self.ctx = ctx
+        self.store = ctx.store().load_quads(np.asarray(quads, dtype=np.uint32).reshape(-1, 4))
+
+    def _out(self, t):
+        n = len(t.names)
+        cols = t.to_numpy() if t.num_rows else [np.zeros(0, np.uint32)] * n
+        return t.names, t.nullable, cols
+
+    def scan(self, instr):
+        return self._out(self.store.plan(instr).execute())
+
+    def make(self, names, nullable, cols):
+        return self.ctx.import_table(dict(zip(names, cols)), dict(zip(names, nullable)))
+
+    def join(self, l, r, jt):
+        return self._out(self.make(*l).join(self.make(*r), jt))
+
+    def filter(self, t, preds):
+        return self._out(self.make(*t).filter(preds))
+
+
+def _empty(names, nullable):
+    return list(names), list(nullable), [np.zeros(0, np.uint32) for _ in names]
+
+
+def eval_plan(be, node):
+    """-> (names, nullable, cols).  Mirrors the reference's lowering: scan → QuadPatternNode, join / leftjoin →
+    SparqlJoinNode, union → schema-aligned UNION ALL, filter → FilterExec on id columns."""
+    op = node["op"]
+    if op == "scan":
+        comps = [node["g"], node["s"], node["p"], node["o"]]
+        instr, names = [], []
+        unknown = False
+        for k, c in enumerate(comps):
+            if c == "default":
+                instr.append(rf.traverse(rf.In(0)))
+            elif "var" in c:
+                pred = rf.Between(1, MAX_ID) if k == 0 else None  # GRAPH ?g: any named graph (scan_instructions.rs:323-355)
+                instr.append(rf.scan(c["var"], pred))
+                if c["var"] not in names:
+                    names.append(c["var"])
+            elif c["id"] is None:
+                unknown = True
+                instr.append(rf.traverse(rf.FALSE))
+            else:
+                instr.append(rf.traverse(rf.In(int(c["id"]))))
+        if unknown:  # constant not in the dictionary ⇒ EmptyExec (snapshot.rs:101-110)
+            return _empty(names, [isinstance(comps[0], dict) and comps[0].get("var") == n for n in names])
+        return be.scan(instr)
+    if op in ("join", "leftjoin"):
+        l, r = eval_plan(be, node["l"]), eval_plan(be, node["r"])
+        return be.join(l, r, F.JOIN_LEFT if op == "leftjoin" else F.JOIN_INNER)
+    if op == "union":
+        (ln, lnl, lc), (rn, rnl, rc) = eval_plan(be, node["l"]), eval_plan(be, node["r"])
+        names = list(ln) + [n for n in rn if n not in ln]
+        nl_rows = len(lc[0]) if lc else 0
+        nr_rows = len(rc[0]) if rc else 0
+        cols, nullable = [], []
+        for n in names:
+            a = lc[ln.index(n)] if n in ln else np.zeros(nl_rows, np.uint32)
+            b = rc[rn.index(n)] if n in rn else np.zeros(nr_rows, np.uint32)
+            cols.append(np.concatenate([a, b]).astype(np.uint32))
+            nullable.append((n not in ln) or (n not in rn) or lnl[ln.index(n)] or rnl[rn.index(n)])
+        return names, nullable, cols
+    if op == "filter":
+        t = eval_plan(be, node["in"])
+        preds = []
+        for p in node["preds"]:
+            code = {"is_null": F.F_IS_NULL, "is_not_null": F.F_IS_NOT_NULL}[p["op"]]
+            preds.append(rf.FPred(code, t[0].index(p["var"])))
+        return be.filter(t, preds)
+    if op == "filter_any_bound":  # FILTER(bound(a) || bound(b) ..): a disjunction stays a host FilterExec
+        names, nullable, cols = eval_plan(be, node["in"])
+        keep = np.zeros(len(cols[0]) if cols else 0, dtype=bool)
+        for v in node["vars"]:
+            if v in names:
+                keep |= cols[names.index(v)] != 0
+        return names, nullable, [c[keep] for c in cols]
+    raise ValueError(op)
+
+
+def check_w3c_case(be, case):
+    names, _, cols = eval_plan(be, case["plan"])
+    n = len(cols[0]) if cols else 0
+    bn = np.asarray(case["bnode_ids"], dtype=np.int64)
+    sel = []
+    for v in case["select"]:
+        c = cols[names.index(v)].astype(np.int64) if v in names else np.zeros(n, np.int64)
+        c = np.where(np.isin(c, bn), -1, c)
+        sel.append(c)
+    got = sorted(map(tuple, np.stack(sel, axis=1).tolist())) if n else []
+    exp = sorted(map(tuple, case["expected"]))
+    assert got == exp, (case["name"], got, exp)

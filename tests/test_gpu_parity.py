@@ -393,3 +393,11 @@ def test_merge_join_adversarial_shapes(ctx, oracle, jt, merge_threads):
             assert_same_table(got.names, got.to_numpy(), exp.names, exp.cols)
             kk = got.to_numpy()[0]
             assert np.all(np.diff(kk.astype(np.int64)) >= 0)  # output stays sorted on the key
+
+
+def test_w3c_join_cases(ctx, join_golden):
+    """CUDA path against the expected results of the W3C evaluation tests (OPTIONAL nesting, compatible-mapping joins after
+    UNION / OPTIONAL, GRAPH ?g, FILTER(!bound)) — tests/golden/join_golden.json."""
+    from helpers import GpuBackend, check_w3c_case
+    for case in join_golden["cases"]:
+        check_w3c_case(GpuBackend(ctx, case["quads"]), case)
