@@ -1,0 +1,130 @@
+"""One rank of the multi-rank pattern-plan test.  Launched by tests/test_dist_cpu.py (gloo, CPU: the oracle is the per-rank
+engine and the exchange is emulated with the same layout arithmetic) and tests/test_gpu_dist.py (one GPU per rank: the
+CUDA path + rfgpu_shuffle over NCCL).
+
+Plan (BASELINE configs[3] in miniature): chain  ?a p1 ?b . ?b p2 ?c . ?c p3 ?d   and   ?a p1 ?b OPTIONAL { ?b p2 ?c },
+plus the star  ?s p1 ?x . ?s p2 ?y  that needs no exchange.  Quads live on rank mix32(subject) mod g; a solution table is
+shuffled on the next join variable, the other side is a local scan that is already partitioned on it.
+Rank 0 gathers every rank's rows and compares the multiset with the single-store oracle.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import torch.distributed as dist  # noqa: E402
+
+import rdf_fusion_b200 as rf  # noqa: E402
+from oracle import oracle_py as orc  # noqa: E402
+from rdf_fusion_b200 import _ffi as F  # noqa: E402
+from rdf_fusion_b200.dist import exchange_layout, init_comm, owner_of_subject, partition_np  # noqa: E402
+
+
+def main():
+    mode = sys.argv[1]  # "cpu" | "gpu"
+    n_triples = int(sys.argv[2]) if len(sys.argv) > 2 else 40000
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if mode == "gpu":
+        import torch
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        dist.init_process_group("gloo")
+
+    g = rf.generate_graph(n_triples, n_predicates=8, s=1.1, seed=4, s_o=1.05)
+    quads = g.quads()
+    mine = quads[owner_of_subject(quads[:, 1], world) == rank]
+    p1, p2, p3 = g.pred_id(1), g.pred_id(2), g.pred_id(3)
+
+    if mode == "gpu":
+        ctx = rf.Context(local)
+        init_comm(ctx)
+        store = ctx.store().load_quads(mine)
+
+        def scan(s, p, o):
+            return store.plan([rf.traverse(0), rf.scan(s), rf.traverse(p), rf.scan(o)]).execute(allow_view=True)
+
+        def shuffle(t, key):
+            out = t.shuffle(key)
+            k = out.to_numpy()[out.names.index(key)] if out.num_rows else np.zeros(0, np.uint32)
+            assert np.all(owner_of_subject(k, world) == rank), "shuffled row landed on the wrong rank"
+            return out
+
+        def join(l, r, jt):
+            return l.join(r, jt)
+
+        def rows(t):
+            return t.names, (t.to_numpy() if t.num_rows else [np.zeros(0, np.uint32)] * len(t.names))
+    else:
+        store = orc.OracleStore(8192).load_quads(mine)
+
+        def scan(s, p, o):
+            return store.plan([rf.traverse(0), rf.scan(s), rf.traverse(p), rf.scan(o)]).execute()
+
+        def shuffle(t, key):
+            # the exchange of rfgpu_shuffle, with gloo carrying the blocks: partition, all-gather the count matrix,
+            # place every peer's block at exchange_layout's offsets
+            cols, counts = partition_np(t.cols, t.names.index(key), world)
+            matrix = [None] * world
+            dist.all_gather_object(matrix, counts)
+            send_off, recv_off, total = exchange_layout(np.asarray(matrix), rank)
+            blocks = [[c[send_off[d]:send_off[d] + counts[d]] for c in cols] for d in range(world)]
+            inbox = [None] * world
+            dist.all_gather_object(inbox, blocks)  # inbox[r][d] = what r sends to d
+            out = [np.zeros(total, np.uint32) for _ in cols]
+            for r in range(world):
+                blk = inbox[r][rank]
+                n = len(blk[0]) if blk else 0
+                assert n == matrix[r][rank]
+                for ci in range(len(cols)):
+                    out[ci][recv_off[r]:recv_off[r] + n] = blk[ci]
+            return orc.OTable(t.names, t.nullable, out)
+
+        def join(l, r, jt):
+            return orc.sparql_join(l, r, jt, "hash")[0]
+
+        def rows(t):
+            return t.names, t.cols
+
+    results = {}
+    # chain: shuffle the running solution on the next join variable; the scan side is already partitioned on it
+    ab = scan("a", p1, "b")
+    abc = join(shuffle(ab, "b"), scan("b", p2, "c"), F.JOIN_INNER)
+    abcd = join(shuffle(abc, "c"), scan("c", p3, "d"), F.JOIN_INNER)
+    results["chain"] = rows(abcd)
+    results["optional"] = rows(join(shuffle(scan("a", p1, "b"), "b"), scan("b", p2, "c"), F.JOIN_LEFT))
+    results["star"] = rows(join(scan("s", p1, "x"), scan("s", p2, "y"), F.JOIN_INNER))
+
+    gathered = [None] * world
+    dist.all_gather_object(gathered, {k: (v[0], [np.asarray(c) for c in v[1]]) for k, v in results.items()})
+    if rank == 0:
+        ost = orc.OracleStore(8192).load_quads(quads)
+
+        def oscan(s, p, o):
+            return ost.plan([rf.traverse(0), rf.scan(s), rf.traverse(p), rf.scan(o)]).execute()
+        exp = {
+            "chain": orc.sparql_join(orc.sparql_join(oscan("a", p1, "b"), oscan("b", p2, "c"), F.JOIN_INNER, "hash")[0],
+                                     oscan("c", p3, "d"), F.JOIN_INNER, "hash")[0],
+            "optional": orc.sparql_join(oscan("a", p1, "b"), oscan("b", p2, "c"), F.JOIN_LEFT, "hash")[0],
+            "star": orc.sparql_join(oscan("s", p1, "x"), oscan("s", p2, "y"), F.JOIN_INNER, "hash")[0],
+        }
+        for name, e in exp.items():
+            names = gathered[0][name][0]
+            assert names == e.names, (name, names, e.names)
+            cols = [np.concatenate([gathered[r][name][1][c] for r in range(world)]) for c in range(len(names))]
+            got = orc.canonical_rows(cols)
+            want = orc.canonical_rows(e.cols)
+            assert got.shape == want.shape and np.array_equal(got, want), (name, got.shape, want.shape)
+            assert len(want) > 0, name
+            print(f"dist {mode} world={world} {name}: {len(want)} rows identical to the single-store oracle", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

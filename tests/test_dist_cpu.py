@@ -1,0 +1,52 @@
+"""CPU, world_size 2 (gloo): the multi-rank plan's host logic — subject partitioning, shuffle destinations, count-matrix
+layout — with the oracle as the per-rank engine; and the host mirrors against the library's own hash."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+from rdf_fusion_b200 import _ffi as F
+from rdf_fusion_b200.dist import exchange_layout, partition_np, shuffle_dest_np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_shuffle_dest_mirror_matches_library():
+    lib = F.load()
+    rng = np.random.default_rng(1)
+    ids = np.concatenate([rng.integers(0, 2**32, 500, dtype=np.uint64).astype(np.uint32), np.arange(64, dtype=np.uint32)])
+    for g in (1, 2, 3, 8, 64):
+        want = np.array([lib.rfgpu_shuffle_dest(int(i), g) for i in ids], dtype=np.uint32)
+        assert np.array_equal(shuffle_dest_np(ids, g), want)
+
+
+def test_exchange_layout_and_partition():
+    rng = np.random.default_rng(2)
+    g = 4
+    tables = [[rng.integers(1, 1000, n).astype(np.uint32), rng.integers(1, 99, n).astype(np.uint32)] for n in (0, 17, 400, 33)]
+    parts = [partition_np(t, 0, g) for t in tables]
+    m = np.array([p[1] for p in parts])
+    assert m.sum() == sum(len(t[0]) for t in tables)
+    recv = []
+    for me in range(g):
+        send_off, recv_off, total = exchange_layout(m, me)
+        assert total == m[:, me].sum()
+        buf = np.zeros(total, np.uint32)
+        for r in range(g):
+            so, _, _ = exchange_layout(m, r)
+            blk = parts[r][0][0][so[me]:so[me] + m[r, me]]
+            buf[recv_off[r]:recv_off[r] + len(blk)] = blk
+        assert np.all(shuffle_dest_np(buf, g) == me)
+        recv.append(buf)
+    assert sorted(np.concatenate(recv).tolist()) == sorted(np.concatenate([t[0] for t in tables]).tolist())
+
+
+def test_two_rank_chain_join_gloo():
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29541", os.path.join(ROOT, "tests", "dist_worker.py"), "cpu", "30000"]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    for name in ("chain", "optional", "star"):
+        assert f"world=2 {name}:" in r.stdout, r.stdout
