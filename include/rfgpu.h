@@ -232,6 +232,16 @@ int32_t rfgpu_last_join_algo(const rfgpu_ctx* ctx);
 typedef enum { RFGPU_JOIN_PHYS_NONE = 0, RFGPU_JOIN_PHYS_HASH = 1, RFGPU_JOIN_PHYS_MERGE = 2 } rfgpu_join_phys;
 int32_t rfgpu_last_join_phys(const rfgpu_ctx* ctx);
 
+/* ---- aggregation on id columns: DataFusion AggregateExec(mode=Single, gby=[..], aggr=[COUNT]) ---- */
+/* GROUP BY key_cols with one COUNT: counted_col = -1 → COUNT(*), else COUNT(col) (non-NULL values).  NULL keys form a
+ * group of their own (SQL GROUP BY).  Output: the key columns, then a non-nullable column `count_name` holding the count
+ * as a uint32 NUMBER (not an object id; INT64_AS_TERM turns it into a term on the host:
+ * lib/logical/src/logical_plan_builder.rs:235-264).  Row order unspecified. */
+int32_t rfgpu_group_count(rfgpu_ctx* ctx, const rfgpu_table* in, const int32_t* key_cols, int32_t n_keys,
+                          int32_t counted_col, const char* count_name, rfgpu_table** out);
+/* SELECT DISTINCT over all columns (ReplaceDistinctWithAggregate: a GROUP BY on every column). */
+int32_t rfgpu_distinct(rfgpu_ctx* ctx, const rfgpu_table* in, rfgpu_table** out);
+
 /* ---- options ---- */
 typedef enum {
   RFGPU_OPT_MERGE_JOIN = 1, /* 1 (default): one-key equi joins whose inputs are both sorted on the key run as a

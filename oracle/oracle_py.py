@@ -276,3 +276,30 @@ def canonical_rows(cols: Sequence[np.ndarray]) -> np.ndarray:
         return m
     order = np.lexsort(tuple(m[:, i] for i in reversed(range(m.shape[1]))))
     return m[order]
+
+
+def group_count(t: OTable, keys: Sequence, counted=None, count_name="count") -> OTable:
+    """DataFusion AggregateExec(mode=Single, gby=keys, aggr=[COUNT(*) | COUNT(col)]) on id columns: SQL GROUP BY (NULLs
+    form one group), COUNT(col) counts non-NULL values.  (lib/logical/src/logical_plan_builder.rs:235-264)"""
+    idx = [t.names.index(k) if isinstance(k, str) else int(k) for k in keys]
+    n = t.num_rows
+    if n == 0:
+        return OTable([t.names[i] for i in idx] + [count_name], [t.nullable[i] for i in idx] + [False],
+                      [np.zeros(0, np.uint32) for _ in range(len(idx) + 1)])
+    m = np.stack([t.cols[i] for i in idx], axis=1)
+    w = np.ones(n, np.int64)
+    if counted is not None:
+        cc = t.names.index(counted) if isinstance(counted, str) else int(counted)
+        w = (t.cols[cc] != 0).astype(np.int64)
+    uniq, inv = np.unique(m, axis=0, return_inverse=True)
+    cnt = np.bincount(inv.reshape(-1), weights=w, minlength=len(uniq)).astype(np.uint32)
+    return OTable([t.names[i] for i in idx] + [count_name], [t.nullable[i] for i in idx] + [False],
+                  [uniq[:, k].astype(np.uint32) for k in range(len(idx))] + [cnt])
+
+
+def distinct(t: OTable) -> OTable:
+    """SELECT DISTINCT = GROUP BY on every column (ReplaceDistinctWithAggregate)."""
+    if t.num_rows == 0:
+        return OTable(t.names, t.nullable, t.cols)
+    uniq = np.unique(np.stack(t.cols, axis=1), axis=0)
+    return OTable(t.names, t.nullable, [uniq[:, k].astype(np.uint32) for k in range(len(t.names))])

@@ -104,6 +104,9 @@ SIGNATURES = {
     "rfgpu_table_export_arrow": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]),
     "rfgpu_filter": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(FilterPred), C.c_int32, C.POINTER(C.c_void_p)]),
     "rfgpu_sparql_join": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]),
+    "rfgpu_group_count": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_char_p,
+                                      C.POINTER(C.c_void_p)]),
+    "rfgpu_distinct": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]),
     "rfgpu_last_join_algo": (C.c_int32, [C.c_void_p]),
     "rfgpu_last_join_phys": (C.c_int32, [C.c_void_p]),
     "rfgpu_ctx_set_option": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int64]),

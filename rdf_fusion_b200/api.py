@@ -417,6 +417,20 @@ class Table:
         self.ctx.check(self.ctx.lib.rfgpu_sparql_join(self.ctx.h, self.h, rhs.h, join_type, C.byref(out)))
         return Table(self.ctx, out)
 
+    def group_count(self, keys: Sequence, counted=None, count_name: str = "count") -> "Table":
+        """GROUP BY keys with COUNT(*) (counted=None) or COUNT(counted): AggregateExec on id columns."""
+        idx = [self.names.index(k) if isinstance(k, str) else int(k) for k in keys]
+        ci = (C.c_int32 * max(1, len(idx)))(*idx)
+        cc = -1 if counted is None else (self.names.index(counted) if isinstance(counted, str) else int(counted))
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_group_count(self.ctx.h, self.h, ci, len(idx), cc, count_name.encode(), C.byref(out)))
+        return Table(self.ctx, out)
+
+    def distinct(self) -> "Table":
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_distinct(self.ctx.h, self.h, C.byref(out)))
+        return Table(self.ctx, out)
+
     def project(self, cols: Sequence, new_names: Optional[Sequence[str]] = None) -> "Table":
         names = self.names
         idx = [names.index(c) if isinstance(c, str) else int(c) for c in cols]

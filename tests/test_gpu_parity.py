@@ -401,3 +401,38 @@ def test_w3c_join_cases(ctx, join_golden):
     from helpers import GpuBackend, check_w3c_case
     for case in join_golden["cases"]:
         check_w3c_case(GpuBackend(ctx, case["quads"]), case)
+
+
+def test_group_count_and_distinct(ctx, oracle):
+    """GROUP BY / COUNT / DISTINCT on id columns against the oracle: 1–3 group columns, NULL groups,
+    COUNT(*) vs COUNT(col), heavy groups, all-distinct inputs, empty input."""
+    rng = np.random.default_rng(21)
+    for n, ks in [(0, 5), (1, 1), (5000, 7), (200000, 50), (300000, 1 << 20)]:
+        cols = _rand_table(rng, n, ["a", "b", "c"], [True, True, True], 0.1, ks)
+        T = ctx.import_table(cols, {"a": True, "b": True, "c": True})
+        O = oracle.OTable(list(cols), [True] * 3, list(cols.values()))
+        for keys, counted in [(["a"], None), (["a"], "c"), (["b", "a"], None), (["a", "b", "c"], "b")]:
+            got = T.group_count(keys, counted, "n")
+            exp = oracle.group_count(O, keys, counted, "n")
+            assert got.names == exp.names and got.nullable == exp.nullable
+            assert got.num_rows == exp.num_rows, (n, ks, keys)
+            if exp.num_rows:
+                assert_same_table(got.names, got.to_numpy(), exp.names, exp.cols)
+        d, e = T.distinct(), oracle.distinct(O)
+        assert d.num_rows == e.num_rows and d.names == e.names
+        if e.num_rows:
+            assert_same_table(d.names, d.to_numpy(), e.names, e.cols)
+    # on top of a join chain, as in the BSBM business-intelligence plans
+    g = rf.generate_graph(80000, n_predicates=10, s=1.0, seed=3)
+    st = _gpu_store(ctx, g.quads())
+    ost = oracle.OracleStore(8192).load_quads(g.quads())
+
+    def q(store):
+        a = store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(g.pred_id(1)), rf.scan("x")]).execute()
+        b = store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(g.pred_id(2)), rf.scan("y")]).execute()
+        return a, b
+    ga, gb = q(st)
+    oa, ob = q(ost)
+    got = ga.join(gb).group_count(["y"], None, "n")
+    exp = oracle.group_count(oracle.sparql_join(oa, ob, F.JOIN_INNER, "hash")[0], ["y"], None, "n")
+    assert_same_table(got.names, got.to_numpy(), exp.names, exp.cols)
