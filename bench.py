@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--merge-threads", type=int, default=0, help="CTA size of the merge-join kernel (64/128/256)")
+    ap.add_argument("--radix-join", action="store_true", help="with --hash-join: the radix-partitioned variant")
     ap.add_argument("--hash-join", action="store_true", help="scan the join inputs through GPOS and force the hash join")
     return ap.parse_args()
 
@@ -172,6 +173,8 @@ def run_ours(a):
     ctx = rf.Context(local)
     if a.merge_threads:
         ctx.set_option(F.OPT_MERGE_THREADS, a.merge_threads)
+    if a.radix_join:
+        ctx.set_option(F.OPT_RADIX_JOIN, 1)
 
     # ---- set-up (untimed): the global graph has world * triples rows; this rank owns the quads whose subject hashes
     # to it, so every scan is local and the star join on ?s needs no exchange (weak scaling, no data-path collective)
@@ -309,7 +312,7 @@ def run_ours(a):
 
     # operator view: the whole join (every kernel it launches) against its SURVEY §8d bytes 4(cb*Nb + cp*Np + co*No)
     roof_op = None
-    jk = {k: v for k, v in kern.items() if k.startswith(("k_merge_", "k_join_", "k_exclusive_scan"))}
+    jk = {k: v for k, v in kern.items() if k.startswith(("k_merge_", "k_join_", "k_exclusive_scan", "k_rp_"))}
     if jk:
         jms = sum(v["ms"] for v in jk.values()) / a.steps
         jbytes = 4 * (2 * na + 2 * nb + 3 * nj)

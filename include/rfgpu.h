@@ -229,7 +229,12 @@ int32_t rfgpu_sparql_join(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_ta
 /* which lowering the last rfgpu_sparql_join on this ctx took (rfgpu_join_algo) */
 int32_t rfgpu_last_join_algo(const rfgpu_ctx* ctx);
 /* physical operator the last equi (sub-)join used */
-typedef enum { RFGPU_JOIN_PHYS_NONE = 0, RFGPU_JOIN_PHYS_HASH = 1, RFGPU_JOIN_PHYS_MERGE = 2 } rfgpu_join_phys;
+typedef enum {
+  RFGPU_JOIN_PHYS_NONE = 0,
+  RFGPU_JOIN_PHYS_HASH = 1,  /* one open-addressing table in HBM */
+  RFGPU_JOIN_PHYS_MERGE = 2, /* both inputs sorted on the key */
+  RFGPU_JOIN_PHYS_RADIX = 3  /* radix-partitioned, per-partition tables in shared memory */
+} rfgpu_join_phys;
 int32_t rfgpu_last_join_phys(const rfgpu_ctx* ctx);
 
 /* ---- aggregation on id columns: DataFusion AggregateExec(mode=Single, gby=[..], aggr=[COUNT]) ---- */
@@ -246,6 +251,9 @@ int32_t rfgpu_distinct(rfgpu_ctx* ctx, const rfgpu_table* in, rfgpu_table** out)
 typedef enum {
   RFGPU_OPT_MERGE_JOIN = 1, /* 1 (default): one-key equi joins whose inputs are both sorted on the key run as a
                               streaming merge join; 0: always build/probe the hash table */
+  RFGPU_OPT_RADIX_JOIN = 3,     /* 1: equi joins with at least RADIX_MIN_ROWS build rows are radix-partitioned (default 0:
+                                   experimental) */
+  RFGPU_OPT_RADIX_MIN_ROWS = 4, /* default 65536 */
   RFGPU_OPT_MERGE_THREADS = 2 /* CTA size of the merge-join kernel: 64, 128 (default) or 256 threads, 8 probe rows each */
 } rfgpu_option;
 int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value);

@@ -32,9 +32,11 @@ F_EQ_CONST, F_NE_CONST, F_EQ_COL, F_NE_COL, F_BETWEEN, F_IN, F_IS_NULL, F_IS_NOT
 JOIN_INNER, JOIN_LEFT = 0, 1
 ALGO_CROSS, ALGO_EQUI, ALGO_COMPATIBLE = 0, 1, 2
 SCAN_ALLOW_VIEW = 1
-PHYS_NONE, PHYS_HASH, PHYS_MERGE = 0, 1, 2
+PHYS_NONE, PHYS_HASH, PHYS_MERGE, PHYS_RADIX = 0, 1, 2, 3
 OPT_MERGE_JOIN = 1
 OPT_MERGE_THREADS = 2
+OPT_RADIX_JOIN = 3
+OPT_RADIX_MIN_ROWS = 4
 UNIQUE_ID_BYTES = 128
 
 u32p = C.POINTER(C.c_uint32)

@@ -11,6 +11,7 @@
 #include <cstdlib>
 
 #include "merge_join.cuh"
+#include "radix_join.cuh"
 
 namespace rf {
 
@@ -189,6 +190,150 @@ ProbeResult hash_probe(rfgpu_ctx* ctx, int nk, const uint32_t* bk0, const uint32
   RF_REQUIRE(R.n_out < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED,
              "join output exceeds 2^32-2 rows on one GPU (" + std::to_string(R.n_out) + ")");
   return R;
+}
+
+// ---- radix-partitioned hash join (radix_join.cuh).  Returns false when the shape is not handled (caller falls back to
+// the one-table join): no rows, too many partitions for one pass, more carried columns than kRpMaxJoinCols, or a build
+// partition that does not fit the shared-memory table (heavy duplicate keys).
+struct RpSide {
+  std::vector<const uint32_t*> src;   // distinct original columns carried (keys first)
+  std::vector<BufRef> part;           // their partitioned copies
+  BufRef off;                         // partition offsets [2^bits + 2]
+  const uint32_t* mapped(const uint32_t* orig) const {
+    for (size_t i = 0; i < src.size(); i++)
+      if (src[i] == orig) return part[i]->as<uint32_t>();
+    return nullptr;
+  }
+};
+
+template <int NK>
+bool rp_partition_side(rfgpu_ctx* ctx, RpSide& S, uint64_t n, int bits, bool null_bin, uint32_t* h_max /*pinned*/) {
+  const uint32_t bins = (1u << bits) + 1;
+  const uint32_t n_chunks = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(n, 8192), (uint64_t)ctx->core->num_sms * 4));
+  const uint64_t chunk = (n + n_chunks - 1) / n_chunks;
+  BufRef matrix = ctx->alloc((uint64_t)bins * n_chunks * 4 + 16);
+  S.off = ctx->alloc(((uint64_t)bins + 2) * 4);
+  BufRef d_max = ctx->alloc(16);
+  RF_CUDA(cudaMemsetAsync(d_max->ptr, 0, 16, ctx->stream()));
+  RpSideArgs A{};
+  A.k0 = S.src[0];
+  A.k1 = NK == 2 ? S.src[1] : nullptr;
+  A.n = n;
+  A.chunk = chunk;
+  A.n_chunks = n_chunks;
+  A.bits = bits;
+  A.null_bin = null_bin ? 1 : 0;
+  A.matrix = matrix->as<uint32_t>();
+  A.n_cols = (int32_t)S.src.size();
+  S.part.clear();
+  for (size_t c = 0; c < S.src.size(); c++) {
+    S.part.push_back(alloc_col(ctx, n));
+    A.src[c] = S.src[c];
+    A.dst[c] = S.part[c]->as<uint32_t>();
+  }
+  const size_t smem = (size_t)bins * 4;
+  {
+    KernelScope ks(ctx, "k_rp_hist", 4ull * NK * n);
+    k_rp_hist<NK><<<n_chunks, kRpThreads, smem, ctx->stream()>>>(A);
+  }
+  exclusive_scan_u32(ctx, A.matrix, A.matrix, (uint64_t)bins * n_chunks, nullptr);
+  {
+    KernelScope ks(ctx, "k_rp_bounds");
+    k_rp_bounds<<<div_up(bins + 1, 256), 256, 0, ctx->stream()>>>(A.matrix, n_chunks, bits, n, S.off->as<uint32_t>(),
+                                                                  d_max->as<uint32_t>());
+  }
+  {
+    KernelScope ks(ctx, "k_rp_scatter", 8ull * S.src.size() * n);
+    k_rp_scatter<NK><<<n_chunks, kRpThreads, smem, ctx->stream()>>>(A);
+  }
+  if (h_max) RF_CUDA(cudaMemcpyAsync(h_max, d_max->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream()));
+  return true;
+}
+
+template <int NK>
+bool radix_join_nk(rfgpu_ctx* ctx, const uint32_t* bk0, const uint32_t* bk1, uint64_t nb, const uint32_t* pk0,
+                   const uint32_t* pk1, uint64_t np, bool left, const std::vector<OutColSpec>& specs,
+                   std::vector<BufRef>* bufs, uint64_t* n_out) {
+  constexpr uint64_t kAvg = RpShape<NK>::kCap * 2 / 5;  // target rows per build partition (40 % of the table capacity)
+  if (nb == 0 || np == 0 || nb >= 0xFFFFFFFFull || np >= 0xFFFFFFFFull) return false;
+  int bits = 0;
+  while (bits < kRpMaxBits && (nb >> bits) > kAvg) bits++;
+  if ((nb >> bits) > kAvg) return false;  // would need a second partitioning pass
+  RpSide B, P;
+  auto add = [](RpSide& s, const uint32_t* p) {
+    if (!p) return;
+    for (auto q : s.src)
+      if (q == p) return;
+    s.src.push_back(p);
+  };
+  add(B, bk0);
+  add(P, pk0);
+  if (NK == 2) {
+    if (bk1 == bk0 || pk1 == pk0) return false;  // keys[] must stay at slots 0 and 1
+    add(B, bk1);
+    add(P, pk1);
+  }
+  for (auto& sp : specs) {
+    add(B, sp.build);
+    add(P, sp.probe);
+  }
+  if (B.src.size() > (size_t)kRpMaxJoinCols || P.src.size() > (size_t)kRpMaxJoinCols) return false;
+  uint32_t* h_max = reinterpret_cast<uint32_t*>(ctx->h_scratch + 12);
+  rp_partition_side<NK>(ctx, B, nb, bits, /*null_bin=*/true, h_max);
+  rp_partition_side<NK>(ctx, P, np, bits, /*null_bin=*/false, nullptr);
+  ctx->sync();
+  if (*h_max > (uint32_t)RpShape<NK>::kCap) return false;  // a partition overflows the shared-memory table
+
+  RpJoinArgs A{};
+  A.bk0 = B.part[0]->as<uint32_t>();
+  A.pk0 = P.part[0]->as<uint32_t>();
+  if (NK == 2) {
+    A.bk1 = B.part[1]->as<uint32_t>();
+    A.pk1 = P.part[1]->as<uint32_t>();
+  }
+  A.b_off = B.off->as<uint32_t>();
+  A.p_off = P.off->as<uint32_t>();
+  A.bits = bits;
+  A.left = left ? 1 : 0;
+  A.n_cols = (int32_t)specs.size();
+  for (size_t c = 0; c < specs.size(); c++) A.cols[c] = OutColSpec{P.mapped(specs[c].probe), B.mapped(specs[c].build)};
+  BufRef cursor = ctx->alloc(16);
+  A.cursor = cursor->as<unsigned long long>();
+  const size_t smem = sizeof(RpSmem<NK>) + 16;
+  static bool attr_set = false;
+  if (!attr_set) {
+    RF_CUDA(cudaFuncSetAttribute(k_rp_join<NK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  int per_sm = 0;
+  RF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_rp_join<NK>, kRpThreads, smem));
+  RF_REQUIRE(per_sm > 0, RFGPU_E_EXEC, "radix join kernel cannot be resident");
+  const uint32_t grid = std::min<uint32_t>(1u << bits, (uint32_t)(ctx->core->num_sms * per_sm));
+  const uint64_t kLimit = 0xFFFFFFFEull;
+  uint64_t cap = std::min<uint64_t>(kLimit, 2 * std::max(np, nb) + 1024);  // optimistic, as in merge_join()
+  for (int attempt = 0;; attempt++) {
+    bufs->clear();
+    for (size_t c = 0; c < specs.size(); c++) {
+      bufs->push_back(alloc_col(ctx, cap));
+      A.dst[c] = (*bufs)[c]->as<uint32_t>();
+    }
+    A.cap = cap;
+    RF_CUDA(cudaMemsetAsync(A.cursor, 0, 8, ctx->stream()));
+    {
+      KernelScope ks(ctx, NK == 1 ? "k_rp_join<1>" : "k_rp_join<2>", 4ull * (B.src.size() * nb + P.src.size() * np));
+      k_rp_join<NK><<<grid, kRpThreads, smem, ctx->stream()>>>(A);
+    }
+    RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 10, A.cursor, 8, cudaMemcpyDeviceToHost, ctx->stream()));
+    ctx->sync();
+    *n_out = ctx->h_scratch[10];
+    RF_REQUIRE(*n_out <= kLimit, RFGPU_E_UNSUPPORTED,
+               "join output exceeds 2^32-2 rows on one GPU (" + std::to_string(*n_out) + ")");
+    if (*n_out <= cap) break;
+    RF_REQUIRE(attempt == 0, RFGPU_E_EXEC, "radix join total changed between passes");
+    cap = *n_out;
+  }
+  ctx->kstats[ctx->kstat_index(NK == 1 ? "k_rp_join<1>" : "k_rp_join<2>")].second.bytes += 4ull * specs.size() * *n_out;
+  return true;
 }
 
 void expand(rfgpu_ctx* ctx, const ProbeResult& P, const std::vector<OutColSpec>& specs,
@@ -376,6 +521,18 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
       T->sorted_col = keys[0].l;
       return finish(bufs, n_out);
     }
+    if (ctx->opt_radix_join && Bt->rows >= (uint64_t)ctx->opt_radix_min_rows) {
+      std::vector<BufRef> bufs;
+      uint64_t n_out = 0;
+      bool done = keys.size() == 1
+                      ? radix_join_nk<1>(ctx, kc(Bt, 0), nullptr, Bt->rows, kc(Pt, 0), nullptr, Pt->rows, left, specs, &bufs, &n_out)
+                      : radix_join_nk<2>(ctx, kc(Bt, 0), kc(Bt, 1), Bt->rows, kc(Pt, 0), kc(Pt, 1), Pt->rows, left, specs,
+                                         &bufs, &n_out);
+      if (done) {
+        ctx->last_join_phys = RFGPU_JOIN_PHYS_RADIX;
+        return finish(bufs, n_out);  // rows come out in partition order: no sorted column
+      }
+    }
     ProbeResult P = hash_probe(ctx, (int)keys.size(), kc(Bt, 0), kc(Bt, 1), Bt->rows, kc(Pt, 0), kc(Pt, 1), Pt->rows, left);
     ctx->last_join_phys = RFGPU_JOIN_PHYS_HASH;
     auto bufs = alloc_out(P.n_out);
@@ -503,6 +660,11 @@ int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value) {
   RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
   switch (option) {
     case RFGPU_OPT_MERGE_JOIN: ctx->opt_merge_join = value != 0; break;
+    case RFGPU_OPT_RADIX_JOIN: ctx->opt_radix_join = value != 0; break;
+    case RFGPU_OPT_RADIX_MIN_ROWS:
+      RF_REQUIRE(value >= 1, RFGPU_E_INVALID, "radix-join threshold must be >= 1 build row");
+      ctx->opt_radix_min_rows = value;
+      break;
     case RFGPU_OPT_MERGE_THREADS:
       RF_REQUIRE(value == 64 || value == 128 || value == 256, RFGPU_E_INVALID, "merge-join CTA size must be 64, 128 or 256");
       ctx->opt_merge_threads = (int)value;

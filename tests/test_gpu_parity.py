@@ -436,3 +436,43 @@ def test_group_count_and_distinct(ctx, oracle):
     got = ga.join(gb).group_count(["y"], None, "n")
     exp = oracle.group_count(oracle.sparql_join(oa, ob, F.JOIN_INNER, "hash")[0], ["y"], None, "n")
     assert_same_table(got.names, got.to_numpy(), exp.names, exp.cols)
+
+
+@pytest.fixture
+def radix_everywhere(ctx):
+    ctx.set_option(F.OPT_RADIX_JOIN, 1)
+    ctx.set_option(F.OPT_RADIX_MIN_ROWS, 1)
+    yield
+    ctx.set_option(F.OPT_RADIX_MIN_ROWS, 65536)
+    ctx.set_option(F.OPT_RADIX_JOIN, 0)
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_radix_hash_join_shapes(ctx, oracle, jt, radix_everywhere):
+    """The radix-partitioned hash join (unsorted inputs): one partition up to thousands, 1 and 2 keys, wide payload,
+    fan-out above the optimistic output capacity, and the fall-back to the one-table join when a key's duplicates
+    overflow a shared-memory partition."""
+    rng = np.random.default_rng(31)
+    seen = set()
+    shapes = [
+        # n_left, n_right, key_space, n_keys
+        (1, 1, 1, 1), (40, 30, 10, 1), (3000, 2500, 700, 1), (3000, 2500, 40, 2),
+        (200000, 150000, 60000, 1), (150000, 260000, 300000, 1), (120000, 90000, 300, 2),
+        (50000, 40000, 30, 1),      # ~1300 duplicates per key on the build side, fan-out ~1600: exact-size second pass
+        (2000, 15000, 3, 1),        # Left: build side = rhs, 5000 duplicates per key overflow a partition → one-table join
+        (400000, 500000, 1 << 30, 1),  # nearly no matches
+    ]
+    for nl, nr, ks, nk in shapes:
+        lc = _rand_table(rng, nl, ["k", "a", "a2"], [False] * 3, 0, ks)
+        rc = _rand_table(rng, nr, ["k", "b"], [False] * 2, 0, ks)
+        if nk == 2:
+            lc["k2"] = rng.integers(1, 5, nl).astype(np.uint32)
+            rc["k2"] = rng.integers(1, 5, nr).astype(np.uint32)
+        if nl * nr // max(ks, 1) > 60_000_000:
+            continue
+        got, algo = _check_join(ctx, oracle, lc, [False] * len(lc), rc, [False] * len(rc), jt, impl="hash")
+        assert algo == F.ALGO_EQUI
+        seen.add(got.last_join_phys)
+    assert F.PHYS_RADIX in seen, seen
+    if jt == F.JOIN_LEFT:
+        assert F.PHYS_HASH in seen, seen
