@@ -306,8 +306,12 @@ def run_ours(a):
         top = max((k for k in kern if kern[k]["bytes"]), key=lambda k: kern[k]["ms"], default=max(kern, key=lambda k: kern[k]["ms"]))
         v = kern[top]
         ach = v["bytes"] / (v["ms"] / 1e3) / 1e9
+        try:  # per-launch DRAM traffic of this kernel from the committed ncu --set full capture of the same workload
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(top)
+        except Exception:
+            traffic = None
         roof = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src,
+                "traffic": traffic, "peak_source": peak_src,
                 "alg_bytes_per_launch": v["bytes"] / v["launches"], "ms_per_launch": v["ms"] / v["launches"]}
 
     # operator view: the whole join (every kernel it launches) against its SURVEY §8d bytes 4(cb*Nb + cp*Np + co*No)

@@ -26,10 +26,15 @@ struct SearchArgs {
 
 // true ⇔ row tuple >= key (which = 0, lower_bound) / row tuple > key (which = 1, upper_bound)
 __device__ __forceinline__ bool tuple_cmp(const SearchArgs& A, int which, uint64_t row) {
-  for (int j = 0; j < A.depth; j++) {
-    uint32_t v = __ldg(A.col[j] + row);
-    uint32_t k = A.key[which][j];
-    if (v != k) return v > k;
+  // all compared columns are loaded up front: one memory round trip per search level instead of one per column
+  uint32_t v[4];
+#pragma unroll
+  for (int j = 0; j < 4; j++) v[j] = j < A.depth ? __ldg(A.col[j] + row) : 0u;
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    if (j >= A.depth) break;
+    const uint32_t k = A.key[which][j];
+    if (v[j] != k) return v[j] > k;
   }
   return which == 0;
 }
