@@ -134,6 +134,11 @@ size_t rfgpu_scan_plan_describe(const rfgpu_scan_plan* p, char* buf, size_t cap)
  * one pass.  Output columns: scanned variables in first-occurrence G,S,P,O order
  * (lib/logical/src/patterns/mod.rs:68-107); graph column nullable, others not. */
 int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t flags, rfgpu_table** out);
+/* Batched form: the range look-ups of all `n` plans run in ONE launch (2 CTAs per plan) and one host hand-off, then every
+ * plan's gather / filter is issued back to back.  Same results as n calls of rfgpu_scan_execute; out[i] is plan i's table.
+ * For callers that hold several patterns at once (the scans of a BGP: logical_plan_builder_context.rs:233-251). */
+int32_t rfgpu_scan_execute_many(rfgpu_ctx* ctx, const rfgpu_scan_plan* const* plans, int32_t n, uint32_t flags,
+                                rfgpu_table** out);
 /* the contiguous index range pruning narrowed to, and rows kept by the residual predicates */
 int32_t rfgpu_scan_last_range(const rfgpu_ctx* ctx, uint64_t* from, uint64_t* to);
 /* Interesting orders: among the permutations that tie for the best choose_index score, prefer the one whose scan

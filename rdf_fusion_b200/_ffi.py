@@ -87,6 +87,7 @@ SIGNATURES = {
     "rfgpu_scan_plan_index": (C.c_uint32, [C.c_void_p]),
     "rfgpu_scan_plan_describe": (C.c_size_t, [C.c_void_p, C.c_char_p, C.c_size_t]),
     "rfgpu_scan_execute": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "rfgpu_scan_execute_many": (C.c_int32, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int32, C.c_uint32, C.POINTER(C.c_void_p)]),
     "rfgpu_scan_last_range": (C.c_int32, [C.c_void_p, u64p, u64p]),
     "rfgpu_table_retain": (C.c_void_p, [C.c_void_p]),
     "rfgpu_table_release": (None, [C.c_void_p]),

@@ -343,6 +343,18 @@ class ScanPlan:
         return a.value, b.value
 
 
+def execute_many(plans: Sequence["ScanPlan"], allow_view: bool = False) -> List["Table"]:
+    """All plans' range look-ups in one launch (rfgpu_scan_execute_many); same results as [p.execute() for p in plans]."""
+    if not plans:
+        return []
+    ctx = plans[0].store.ctx
+    n = len(plans)
+    arr = (C.c_void_p * n)(*[p.h for p in plans])
+    out = (C.c_void_p * n)()
+    ctx.check(ctx.lib.rfgpu_scan_execute_many(ctx.h, arr, n, F.SCAN_ALLOW_VIEW if allow_view else 0, out))
+    return [Table(ctx, C.c_void_p(out[i])) for i in range(n)]
+
+
 class Table:
     """Device-resident solution mappings (rfgpu_table): UInt32 columns, 0 = NULL."""
 

@@ -104,7 +104,7 @@ struct rfgpu_ctx {
   int opt_merge_threads = 128;  // CTA size of k_merge_join (tile = 8 rows per thread)
   uint64_t last_from = 0, last_to = 0;
   // pinned host scratch for small device→host results (ranges, counts)
-  uint64_t* h_scratch = nullptr;  // 64 x u64
+  uint64_t* h_scratch = nullptr;  // 256 x u64: [0,16) scalars, [16,80) partition counts, [128,160) batched ranges
   // profiling
   bool profiling = false;
   std::vector<std::pair<std::string, rf::KernelStat>> kstats;

@@ -66,6 +66,37 @@ k_range_search(const __grid_constant__ SearchArgs A, unsigned long long* __restr
   if (threadIdx.x == 0) result[which] = lo;
 }
 
+// Batched form: Q look-ups per launch (grid = 2Q CTAs) — the "vectorised" range lookup for callers that hold several
+// patterns at once (a BGP's scans, index-nested-loop probes, dynamic-filter re-planning).  result[2q], result[2q+1].
+constexpr int kMaxBatch = 16;
+struct SearchBatch {
+  SearchArgs q[kMaxBatch];
+};
+__global__ void __launch_bounds__(kSearchThreads)
+k_range_search_many(const __grid_constant__ SearchBatch B, unsigned long long* __restrict__ result) {
+  const SearchArgs& A = B.q[blockIdx.x >> 1];
+  const int which = blockIdx.x & 1;
+  uint64_t lo = 0, hi = A.n;
+  while (hi > lo) {
+    uint64_t width = hi - lo;
+    if (width <= kSearchThreads) {
+      uint64_t row = lo + threadIdx.x;
+      bool below = row < hi && !tuple_cmp(A, which, row);
+      lo += __syncthreads_count(below);
+      break;
+    }
+    uint64_t step = (width + kSearchThreads - 1) / kSearchThreads;
+    uint64_t pivot = lo + (uint64_t)(threadIdx.x + 1) * step - 1;
+    bool below = pivot < hi && !tuple_cmp(A, which, pivot);
+    uint64_t c = __syncthreads_count(below);
+    uint64_t nlo = lo + c * step;
+    uint64_t nhi = min(hi, nlo + step - 1);
+    lo = min(nlo, hi);
+    hi = max(nhi, lo);
+  }
+  if (threadIdx.x == 0) result[blockIdx.x] = lo;
+}
+
 // ---- 1b: column gather ----
 struct GatherArgs {
   const uint32_t* src[4];  // already offset to row `from`
@@ -177,15 +208,28 @@ static const rfgpu_index_t* find_index(const rfgpu_store* s, uint32_t perm) {
   return nullptr;
 }
 
-}  // namespace rf
+// pruning → the key tuples of one lexicographic lower/upper bound.  Walk levels while they carry a pruning predicate;
+// continue past a level only if it pins a single id (quad_index_data.rs:162-243).  Returns the depth (0: whole index).
+static int search_args_for(const rfgpu_index_t* ix, const ScanInstrs& ins, SearchArgs* S) {
+  *S = SearchArgs{};
+  S->n = ix->rows;
+  int depth = 0;
+  for (int l = 0; l < 4; l++) {
+    uint32_t a, b;
+    if (!ins.at[l].pred.pruning(&a, &b)) break;
+    S->key[0][l] = a;
+    S->key[1][l] = b;
+    depth = l + 1;
+    if (a != b) break;
+  }
+  S->depth = depth;
+  for (int l = 0; l < 4; l++) S->col[l] = ix->col[l]->as<uint32_t>();
+  return depth;
+}
 
-extern "C" {
-
-int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t flags, rfgpu_table** out) {
-  RF_API_BEGIN
-  using namespace rf;
-  RF_REQUIRE(ctx && p && out, RFGPU_E_INVALID, "NULL argument");
-  RF_CUDA(cudaSetDevice(ctx->core->device));
+// `range` != nullptr: [from, to) already known (batched look-up)
+static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t flags, rfgpu_table** out,
+                              const uint64_t* range) {
   const rfgpu_index_t* ix = find_index(p->store, p->perm);
   RF_REQUIRE(ix, RFGPU_E_EXEC, "Index must exist");
   const ScanInstrs ins = p->gspo.reorder(p->perm);
@@ -227,26 +271,17 @@ int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t fl
   ctx->last_from = ctx->last_to = 0;
   if (ix->rows == 0 || any_false) {
     *out = make_empty();
-    return RFGPU_OK;
+    return;
   }
 
-  // ---- 1a: pruning → one contiguous range.  Walk levels while they carry a pruning predicate; continue past a
-  // level only if it pins a single id (quad_index_data.rs:162-243).
-  SearchArgs S{};
-  S.n = ix->rows;
-  int depth = 0;
-  for (int l = 0; l < 4; l++) {
-    uint32_t a, b;
-    if (!ins.at[l].pred.pruning(&a, &b)) break;
-    S.key[0][l] = a;
-    S.key[1][l] = b;
-    depth = l + 1;
-    if (a != b) break;
-  }
-  S.depth = depth;
-  for (int l = 0; l < 4; l++) S.col[l] = ix->col[l]->as<uint32_t>();
+  // ---- 1a: pruning → one contiguous range
+  SearchArgs S;
+  const int depth = search_args_for(ix, ins, &S);
   uint64_t from = 0, to = ix->rows;
-  if (depth > 0) {
+  if (range) {
+    from = range[0];
+    to = std::max(range[0], range[1]);
+  } else if (depth > 0) {
     {
       KernelScope ks(ctx, "k_range_search");
       k_range_search<<<2, kSearchThreads, 0, ctx->stream()>>>(S, (unsigned long long*)ctx->h_scratch);
@@ -262,7 +297,7 @@ int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t fl
   ctx->m.scan_rows_in += R;
   if (R == 0) {
     *out = make_empty();
-    return RFGPU_OK;
+    return;
   }
 
   // ---- residual predicates: drop what pruning guarantees (quad_index_data.rs:245-278), keep the rest
@@ -388,6 +423,55 @@ int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t fl
     ctx->m.algorithmic_bytes += bytes_in + 4ull * oc.size() * kept;
   }
   *out = t.release();
+}
+
+}  // namespace rf
+
+extern "C" {
+
+int32_t rfgpu_scan_execute(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t flags, rfgpu_table** out) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx && p && out, RFGPU_E_INVALID, "NULL argument");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  rf::scan_execute_impl(ctx, p, flags, out, nullptr);
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_scan_execute_many(rfgpu_ctx* ctx, const rfgpu_scan_plan* const* plans, int32_t n, uint32_t flags,
+                                rfgpu_table** out) {
+  RF_API_BEGIN
+  using namespace rf;
+  RF_REQUIRE(ctx && plans && out && n >= 0, RFGPU_E_INVALID, "NULL / negative argument");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  for (int i = 0; i < n; i++) out[i] = nullptr;
+  try {
+    for (int base = 0; base < n; base += kMaxBatch) {
+      const int q = std::min(kMaxBatch, n - base);
+      SearchBatch B{};
+      for (int i = 0; i < q; i++) {
+        const rfgpu_scan_plan* p = plans[base + i];
+        RF_REQUIRE(p, RFGPU_E_INVALID, "NULL plan");
+        const rfgpu_index_t* ix = find_index(p->store, p->perm);
+        RF_REQUIRE(ix, RFGPU_E_EXEC, "Index must exist");
+        search_args_for(ix, p->gspo.reorder(p->perm), &B.q[i]);  // depth 0 → [0, n) falls out of the search itself
+      }
+      uint64_t* res = ctx->h_scratch + 128;
+      {
+        KernelScope ks(ctx, "k_range_search_many");
+        k_range_search_many<<<2 * q, kSearchThreads, 0, ctx->stream()>>>(B, (unsigned long long*)res);
+      }
+      ctx->sync();
+      uint64_t ranges[2 * kMaxBatch];
+      for (int i = 0; i < 2 * q; i++) ranges[i] = res[i];
+      for (int i = 0; i < q; i++) scan_execute_impl(ctx, plans[base + i], flags, &out[base + i], &ranges[2 * i]);
+    }
+  } catch (...) {
+    for (int i = 0; i < n; i++) {
+      if (out[i]) rfgpu_table_release(out[i]);
+      out[i] = nullptr;
+    }
+    throw;
+  }
   RF_API_END(ctx)
 }
 

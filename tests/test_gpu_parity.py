@@ -476,3 +476,27 @@ def test_radix_hash_join_shapes(ctx, oracle, jt, radix_everywhere):
     assert F.PHYS_RADIX in seen, seen
     if jt == F.JOIN_LEFT:
         assert F.PHYS_HASH in seen, seen
+
+
+def test_execute_many_equals_single_scans(ctx, oracle):
+    """The batched range look-up (rfgpu_scan_execute_many) returns exactly what one rfgpu_scan_execute per plan returns:
+    bound / unbound / empty / residual-predicate / named-graph patterns, more plans than one launch holds."""
+    rng = np.random.default_rng(9)
+    quads = random_quads(rng, 4000)
+    st = _gpu_store(ctx, quads)
+    ost = oracle.OracleStore(8192).load_quads(quads)
+    pats = [random_pattern(rng, quads) for _ in range(37)]
+    pats.append([rf.traverse(0), rf.scan("s"), rf.traverse(rf.In(999999)), rf.scan("o")])   # no match
+    pats.append([rf.scan("g"), rf.scan("s"), rf.scan("p"), rf.scan("o")])                    # whole index
+    pats.append([rf.scan("g", rf.Between(1, 0xFFFFFFFF)), rf.scan("x"), rf.scan("p"), rf.scan("x")])  # repeated variable
+    plans = [st.plan(p) for p in pats]
+    for view in (False, True):
+        many = rf.execute_many(plans, allow_view=view)
+        assert len(many) == len(plans)
+        for p, pat, t in zip(plans, pats, many):
+            exp = ost.plan(pat).execute()
+            assert t.names == exp.names and t.num_rows == exp._rows
+            if exp._rows:
+                for a, b in zip(t.to_numpy(), exp.cols):
+                    assert np.array_equal(a, b)
+    assert rf.execute_many([]) == []
