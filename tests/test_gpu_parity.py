@@ -500,3 +500,61 @@ def test_execute_many_equals_single_scans(ctx, oracle):
                 for a, b in zip(t.to_numpy(), exp.cols):
                     assert np.array_equal(a, b)
     assert rf.execute_many([]) == []
+
+
+def test_full_size_properties_config1(ctx):
+    """BASELINE configs[1] at FULL size (100 M triples, the bench's graph): size-independent properties instead of an oracle
+    run — scan cardinalities against numpy counts, sortedness, join cardinality = sum_k |A_k|·|B_k|, column checksums
+    (a checksum of checksums over the join), merge join == hash join as multisets."""
+    from rdf_fusion_b200.loader import load_store_device
+    n = 100_000_000
+    g = rf.generate_graph(n, 1024, 1.0, 2)
+    store = load_store_device(ctx, g.g, g.s, g.p, g.o, perms=(F.GSPO, F.GPOS, F.GOSP, F.GPSO))
+    # independent host view: de-duplicated (s, p, o) of the two join predicates
+    p1, p2, p100 = g.pred_id(1), g.pred_id(2), g.pred_id(100)
+
+    def host_rows(pid):
+        m = g.p == pid
+        so = np.unique(np.stack([g.s[m], g.o[m]], axis=1), axis=0)  # the store is a set
+        return so[:, 0], so[:, 1]
+    for pid in (p100, p2):
+        hs, ho = host_rows(pid)
+        t = store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(pid), rf.scan("o")]).execute()
+        assert t.num_rows == len(hs)
+        s_col, o_col = t.to_numpy()
+        assert int(s_col.astype(np.uint64).sum()) == int(hs.astype(np.uint64).sum())
+        assert int(o_col.astype(np.uint64).sum()) == int(ho.astype(np.uint64).sum())
+        assert np.all(np.diff(o_col.astype(np.int64)) >= 0)  # GPOS: rows in (o, s) order
+    a_s, a_o = host_rows(p1)
+    b_s, b_o = host_rows(p2)
+    ka, ca = np.unique(a_s, return_counts=True)
+    kb, cb = np.unique(b_s, return_counts=True)
+    common, ia, ib = np.intersect1d(ka, kb, assume_unique=True, return_indices=True)
+    want_rows = int((ca[ia].astype(np.int64) * cb[ib].astype(np.int64)).sum())
+    # checksum of checksums: sum over join rows of o1 = sum_k (sum of o1 in A_k) * |B_k|, likewise o2 and s
+    sum_a = np.bincount(np.searchsorted(ka, a_s), weights=a_o.astype(np.float64), minlength=len(ka))
+    sum_b = np.bincount(np.searchsorted(kb, b_s), weights=b_o.astype(np.float64), minlength=len(kb))
+    want_o1 = int(np.rint((sum_a[ia] * cb[ib]).sum()))
+    want_o2 = int(np.rint((sum_b[ib] * ca[ia]).sum()))
+    want_s = int((common.astype(np.int64) * ca[ia] * cb[ib]).sum())
+    pa = store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(p1), rf.scan("o1")])
+    pb = store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(p2), rf.scan("o2")])
+    assert pa.order_by("s") and pb.order_by("s")
+    ta, tb = rf.execute_many([pa, pb], allow_view=True)
+    tj = ta.join(tb)
+    assert tj.last_join_phys == F.PHYS_MERGE and tj.num_rows == want_rows
+    s_col, o1, o2 = tj.to_numpy()
+    assert int(s_col.astype(np.uint64).sum()) == want_s
+    assert int(o1.astype(np.uint64).sum()) == want_o1
+    assert int(o2.astype(np.uint64).sum()) == want_o2
+    assert np.all(np.diff(s_col.astype(np.int64)) >= 0)
+    ctx.set_option(F.OPT_MERGE_JOIN, 0)
+    try:
+        th = ta.join(tb)
+        assert th.last_join_phys == F.PHYS_HASH and th.num_rows == want_rows
+        h = th.to_numpy()
+    finally:
+        ctx.set_option(F.OPT_MERGE_JOIN, 1)
+    for got, want in zip(h, (s_col, o1, o2)):
+        assert int(got.astype(np.uint64).sum()) == int(want.astype(np.uint64).sum())
+    assert np.array_equal(np.sort(h[0]), s_col)  # same keys with the same multiplicities
