@@ -259,6 +259,8 @@ typedef enum {
   RFGPU_OPT_RADIX_JOIN = 3,     /* 1: equi joins with at least RADIX_MIN_ROWS build rows are radix-partitioned (default 0:
                                    experimental) */
   RFGPU_OPT_RADIX_MIN_ROWS = 4, /* default 65536 */
+  RFGPU_OPT_HASH_L2_BYTES = 5,  /* hash join: table bytes per pass (default: unlimited = one pass); larger build sides are
+                                   joined in up to 8 passes over disjoint hash ranges so each pass's table stays in L2 */
   RFGPU_OPT_MERGE_THREADS = 2 /* CTA size of the merge-join kernel: 64, 128 (default) or 256 threads, 8 probe rows each */
 } rfgpu_option;
 int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value);

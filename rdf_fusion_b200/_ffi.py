@@ -37,6 +37,7 @@ OPT_MERGE_JOIN = 1
 OPT_MERGE_THREADS = 2
 OPT_RADIX_JOIN = 3
 OPT_RADIX_MIN_ROWS = 4
+OPT_HASH_L2_BYTES = 5
 UNIQUE_ID_BYTES = 128
 
 u32p = C.POINTER(C.c_uint32)

@@ -112,13 +112,14 @@ struct ProbeResult {
 
 // build a hash table over (bk0[,bk1]) and probe it with (pk0[,pk1]); no output rows are written yet
 ProbeResult hash_probe(rfgpu_ctx* ctx, int nk, const uint32_t* bk0, const uint32_t* bk1, uint64_t nb,
-                       const uint32_t* pk0, const uint32_t* pk1, uint64_t np, bool left) {
+                       const uint32_t* pk0, const uint32_t* pk1, uint64_t np, bool left, uint32_t n_chunks = 1,
+                       uint32_t chunk = 0, uint64_t chunk_rows = 0) {
   ProbeResult R;
   if (np == 0) return R;
   RF_REQUIRE(nk == 1 || nk == 2, RFGPU_E_UNSUPPORTED, "hash join supports 1 or 2 key columns");
   // ---- build ----
   uint64_t cap = 1024;
-  while (cap < 2 * nb) cap <<= 1;
+  while (cap < 2 * (n_chunks > 1 ? chunk_rows : nb)) cap <<= 1;  // the table holds distinct keys: <= the rows it is given
   RF_REQUIRE(cap <= (1ull << 31), RFGPU_E_UNSUPPORTED, "build side too large for one hash table");
   const uint32_t mask = (uint32_t)(cap - 1);
   const size_t ksz = nk == 1 ? 4 : 8;
@@ -134,10 +135,10 @@ ProbeResult hash_probe(rfgpu_ctx* ctx, int nk, const uint32_t* bk0, const uint32
       KernelScope ks(ctx, nk == 1 ? "k_join_build_insert<1>" : "k_join_build_insert<2>", 4ull * nk * nb);
       if (nk == 1)
         k_join_build_insert<1><<<grid_for(ctx, nb), 256, 0, ctx->stream()>>>(bk0, bk1, nb, keys->as<uint32_t>(), offs, mask,
-                                                                            row_slot->as<uint32_t>());
+                                                                            row_slot->as<uint32_t>(), n_chunks, chunk);
       else
         k_join_build_insert<2><<<grid_for(ctx, nb), 256, 0, ctx->stream()>>>(
-            bk0, bk1, nb, keys->as<unsigned long long>(), offs, mask, row_slot->as<uint32_t>());
+            bk0, bk1, nb, keys->as<unsigned long long>(), offs, mask, row_slot->as<uint32_t>(), n_chunks, chunk);
     }
     exclusive_scan_u32(ctx, offs + 1, offs + 1, cap, nullptr);
     {
@@ -161,6 +162,8 @@ ProbeResult hash_probe(rfgpu_ctx* ctx, int nk, const uint32_t* bk0, const uint32
   A.offs = offs;
   A.mask = mask;
   A.left = left ? 1 : 0;
+  A.n_chunks = n_chunks;
+  A.chunk = chunk;
   A.m_row = R.m_row->as<uint32_t>();
   A.m_gs = R.m_gs->as<uint32_t>();
   A.m_off = R.m_off->as<uint32_t>();
@@ -334,6 +337,23 @@ bool radix_join_nk(rfgpu_ctx* ctx, const uint32_t* bk0, const uint32_t* bk1, uin
   }
   ctx->kstats[ctx->kstat_index(NK == 1 ? "k_rp_join<1>" : "k_rp_join<2>")].second.bytes += 4ull * specs.size() * *n_out;
   return true;
+}
+
+// build rows whose key hashes into each of the n_chunks ranges
+std::vector<uint64_t> build_chunk_rows(rfgpu_ctx* ctx, int nk, const uint32_t* bk0, const uint32_t* bk1, uint64_t nb,
+                                       uint32_t n_chunks) {
+  BufRef d = ctx->alloc(32 * 8);
+  RF_CUDA(cudaMemsetAsync(d->ptr, 0, 32 * 8, ctx->stream()));
+  if (nb) {
+    KernelScope ks(ctx, "k_join_chunk_hist", 4ull * nk * nb);
+    if (nk == 1)
+      k_join_chunk_hist<1><<<grid_for(ctx, nb), 256, 0, ctx->stream()>>>(bk0, bk1, nb, n_chunks, d->as<unsigned long long>());
+    else
+      k_join_chunk_hist<2><<<grid_for(ctx, nb), 256, 0, ctx->stream()>>>(bk0, bk1, nb, n_chunks, d->as<unsigned long long>());
+  }
+  RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 96, d->ptr, n_chunks * 8, cudaMemcpyDeviceToHost, ctx->stream()));
+  ctx->sync();
+  return std::vector<uint64_t>(ctx->h_scratch + 96, ctx->h_scratch + 96 + n_chunks);
 }
 
 void expand(rfgpu_ctx* ctx, const ProbeResult& P, const std::vector<OutColSpec>& specs,
@@ -533,8 +553,35 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
         return finish(bufs, n_out);  // rows come out in partition order: no sorted column
       }
     }
-    ProbeResult P = hash_probe(ctx, (int)keys.size(), kc(Bt, 0), kc(Bt, 1), Bt->rows, kc(Pt, 0), kc(Pt, 1), Pt->rows, left);
+    // L2 blocking: as many passes over the hash space as it takes for one pass's table (distinct keys + CSR offsets, at
+    // most half full) to stay L2-resident; every pass streams both key columns once more (sequential, cheap) and its
+    // random sector accesses hit L2 instead of HBM
     ctx->last_join_phys = RFGPU_JOIN_PHYS_HASH;
+    {
+      const uint64_t table_bytes = 2 * Bt->rows * ((keys.size() == 1 ? 4 : 8) + 4);
+      uint32_t n_chunks = 1;
+      while (n_chunks < 8 && table_bytes / n_chunks > (uint64_t)ctx->opt_hash_l2_bytes) n_chunks++;
+      if (n_chunks > 1 && Pt->rows > 0) {
+        auto rows_c = build_chunk_rows(ctx, (int)keys.size(), kc(Bt, 0), kc(Bt, 1), Bt->rows, n_chunks);
+        std::vector<ProbeResult> Ps;
+        uint64_t total = 0;
+        for (uint32_t c = 0; c < n_chunks; c++) {
+          Ps.push_back(hash_probe(ctx, (int)keys.size(), kc(Bt, 0), kc(Bt, 1), Bt->rows, kc(Pt, 0), kc(Pt, 1), Pt->rows,
+                                  left, n_chunks, c, rows_c[c]));
+          total += Ps.back().n_out;
+        }
+        RF_REQUIRE(total < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED,
+                   "join output exceeds 2^32-2 rows on one GPU (" + std::to_string(total) + ")");
+        auto bufs = alloc_out(total);
+        uint64_t off = 0;
+        for (auto& P : Ps) {
+          expand(ctx, P, specs, raw(bufs), off);
+          off += P.n_out;
+        }
+        return finish(bufs, total);  // chunk after chunk: no sorted column
+      }
+    }
+    ProbeResult P = hash_probe(ctx, (int)keys.size(), kc(Bt, 0), kc(Bt, 1), Bt->rows, kc(Pt, 0), kc(Pt, 1), Pt->rows, left);
     auto bufs = alloc_out(P.n_out);
     expand(ctx, P, specs, raw(bufs), 0);
     T->sorted_col = out_sorted;
@@ -664,6 +711,10 @@ int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value) {
     case RFGPU_OPT_RADIX_MIN_ROWS:
       RF_REQUIRE(value >= 1, RFGPU_E_INVALID, "radix-join threshold must be >= 1 build row");
       ctx->opt_radix_min_rows = value;
+      break;
+    case RFGPU_OPT_HASH_L2_BYTES:
+      RF_REQUIRE(value >= 1024, RFGPU_E_INVALID, "L2 budget of one hash-join pass must be >= 1 KiB");
+      ctx->opt_hash_l2_bytes = value;
       break;
     case RFGPU_OPT_MERGE_THREADS:
       RF_REQUIRE(value == 64 || value == 128 || value == 256, RFGPU_E_INVALID, "merge-join CTA size must be 64, 128 or 256");

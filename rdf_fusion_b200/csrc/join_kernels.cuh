@@ -34,12 +34,42 @@ __device__ __forceinline__ uint32_t key_hash(typename KeyT<NK>::type k) {
   else return dev::mix64to32((uint64_t)k);
 }
 
+// L2 blocking: the hash space is cut into `n_chunks` ranges (top bits of the hash; the table slot uses the low bits) and
+// the join runs once per range with a table small enough to stay L2-resident, so the random sector accesses of build and
+// probe are served by L2 instead of HBM.  Every key belongs to exactly one chunk; NULL probe keys to chunk 0.
+__device__ __forceinline__ uint32_t chunk_of(uint32_t h, uint32_t n_chunks) {
+  return (uint32_t)(((unsigned long long)h * n_chunks) >> 32);
+}
+
+// build rows per chunk (sizes each pass's table by what it will actually hold)
+template <int NK>
+__global__ void __launch_bounds__(256)
+k_join_chunk_hist(const uint32_t* __restrict__ k0, const uint32_t* __restrict__ k1, uint64_t n, uint32_t n_chunks,
+                  unsigned long long* __restrict__ counts) {
+  using K = typename KeyT<NK>::type;
+  __shared__ uint32_t s_h[32];
+  if (threadIdx.x < 32) s_h[threadIdx.x] = 0;
+  __syncthreads();
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const uint32_t a = __ldg(k0 + i);
+    const uint32_t b = NK == 2 ? __ldg(k1 + i) : 1u;
+    if (a == 0 || b == 0) continue;
+    K key;
+    if constexpr (NK == 1) key = a; else key = (K)a | ((K)b << 32);
+    atomicAdd(&s_h[chunk_of(key_hash<NK>(key), n_chunks)], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < n_chunks && s_h[threadIdx.x]) atomicAdd(counts + threadIdx.x, (unsigned long long)s_h[threadIdx.x]);
+}
+
 // ---------------- build ----------------
 template <int NK>
 __global__ void __launch_bounds__(256)
 k_join_build_insert(const uint32_t* __restrict__ k0, const uint32_t* __restrict__ k1, uint64_t n,
                     typename KeyT<NK>::type* __restrict__ keys, uint32_t* __restrict__ offs, uint32_t mask,
-                    uint32_t* __restrict__ row_slot) {
+                    uint32_t* __restrict__ row_slot, uint32_t n_chunks, uint32_t chunk) {
   using K = typename KeyT<NK>::type;
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -52,7 +82,12 @@ k_join_build_insert(const uint32_t* __restrict__ k0, const uint32_t* __restrict_
     }
     K key;
     if constexpr (NK == 1) key = a; else key = (K)a | ((K)b << 32);
-    uint32_t h = key_hash<NK>(key) & mask;
+    const uint32_t hh = key_hash<NK>(key);
+    if (n_chunks > 1 && chunk_of(hh, n_chunks) != chunk) {  // another pass owns this key
+      row_slot[i] = kNone;
+      continue;
+    }
+    uint32_t h = hh & mask;
     while (true) {
       K prev = keys[h];
       if (prev == key) break;
@@ -95,6 +130,7 @@ struct ProbeArgs {
   const uint32_t* offs;
   uint32_t mask;
   int32_t left;           // emit unmatched probe rows (Left join, probe side preserved)
+  uint32_t n_chunks, chunk;  // L2 blocking: only probe rows whose key hashes into `chunk` take part in this pass
   // outputs
   uint32_t* m_row;        // probe row of entry q
   uint32_t* m_gs;         // group start in rowids (kNone: unmatched → NULL build side)
@@ -169,6 +205,7 @@ k_join_probe(const __grid_constant__ ProbeArgs A) {
     K key[kPItems];
     uint32_t h[kPItems];
     K cur[kPItems];
+    bool mine[kPItems];
 #pragma unroll
     for (int r = 0; r < kPItems; r++) {
       uint32_t lr = tid * kPItems + r;
@@ -182,7 +219,11 @@ k_join_probe(const __grid_constant__ ProbeArgs A) {
       } else {
         if constexpr (NK == 1) key[r] = a; else key[r] = (K)a | ((K)b << 32);
       }
-      h[r] = key_hash<NK>(key[r]) & A.mask;
+      const uint32_t hh = key_hash<NK>(key[r]);
+      h[r] = hh & A.mask;
+      const uint32_t ch = key[r] ? chunk_of(hh, A.n_chunks) : 0u;
+      mine[r] = lr < rows && (A.n_chunks <= 1 || ch == A.chunk);
+      if (!mine[r]) key[r] = 0;
     }
     // first probe of all 8 rows in flight together (memory-level parallelism), then resolve collisions
 #pragma unroll
@@ -217,7 +258,7 @@ k_join_probe(const __grid_constant__ ProbeArgs A) {
     for (int r = 0; r < kPItems; r++) {
       uint32_t lr = tid * kPItems + r;
       e[r] = cnt[r];
-      if (A.left && cnt[r] == 0 && lr < rows) e[r] = 1;
+      if (A.left && cnt[r] == 0 && lr < rows && mine[r]) e[r] = 1;
       tcnt += e[r] != 0;
       tout += e[r];
     }

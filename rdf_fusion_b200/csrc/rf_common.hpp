@@ -101,6 +101,8 @@ struct rfgpu_ctx {
   bool opt_merge_join = true;
   bool opt_radix_join = false;       // opt-in: radix-partitioned shared-memory hash join (correct, not yet faster: DESIGN.md §5)
   int64_t opt_radix_min_rows = 65536;  // build rows below which the one-table hash join is used
+  int64_t opt_hash_l2_bytes = 1ll << 40;   // table bytes one pass of the hash join may hold; > this ⇒ multi-pass L2 blocking
+                                           // (opt-in: measured no faster yet)
   int opt_merge_threads = 128;  // CTA size of k_merge_join (tile = 8 rows per thread)
   uint64_t last_from = 0, last_to = 0;
   // pinned host scratch for small device→host results (ranges, counts)

@@ -558,3 +558,24 @@ def test_full_size_properties_config1(ctx):
     for got, want in zip(h, (s_col, o1, o2)):
         assert int(got.astype(np.uint64).sum()) == int(want.astype(np.uint64).sum())
     assert np.array_equal(np.sort(h[0]), s_col)  # same keys with the same multiplicities
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+@pytest.mark.parametrize("budget", [1024, 20000])
+def test_hash_join_l2_blocked_passes(ctx, oracle, jt, budget):
+    """The one-table hash join run in several passes over disjoint hash ranges (L2 blocking): every probe row is answered
+    by exactly one pass — unmatched rows of a Left join exactly once — whatever the number of passes."""
+    rng = np.random.default_rng(41)
+    ctx.set_option(F.OPT_HASH_L2_BYTES, budget)
+    try:
+        for nl, nr, ks, nk in [(1, 1, 1, 1), (300, 200, 40, 1), (2500, 1800, 300, 1), (900, 4000, 5, 1), (3000, 2500, 40, 2),
+                               (60000, 50000, 20000, 1), (20000, 30000, 1 << 30, 1)]:
+            lc = _rand_table(rng, nl, ["k", "a"], [False, False], 0, ks)
+            rc = _rand_table(rng, nr, ["k", "b"], [False, False], 0, ks)
+            if nk == 2:
+                lc["k2"] = rng.integers(1, 5, nl).astype(np.uint32)
+                rc["k2"] = rng.integers(1, 5, nr).astype(np.uint32)
+            got, algo = _check_join(ctx, oracle, lc, [False] * len(lc), rc, [False] * len(rc), jt, impl="hash")
+            assert algo == F.ALGO_EQUI and got.last_join_phys == F.PHYS_HASH
+    finally:
+        ctx.set_option(F.OPT_HASH_L2_BYTES, 1 << 40)
