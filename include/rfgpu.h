@@ -166,6 +166,11 @@ int32_t rfgpu_table_import(rfgpu_ctx* ctx, int32_t n_cols, const char* const* na
  * null count per column in null_counts when non-NULL. */
 int32_t rfgpu_table_export(rfgpu_ctx* ctx, const rfgpu_table* t, uint64_t row_off, uint64_t n_rows,
                            uint32_t* const* values, uint8_t* const* validity, uint64_t* null_counts);
+/* Asynchronous export of the value buffers (no validity: NULL = 0 in the values): the device→host copies run on the ctx's
+ * copy stream once the work queued so far has produced `t`, and overlap later kernels and host→device imports.  The caller's
+ * buffers (page-locked for a real overlap) are valid after the next rfgpu_ctx_synchronize; `t` is retained until then. */
+int32_t rfgpu_table_export_async(rfgpu_ctx* ctx, rfgpu_table* t, uint64_t row_off, uint64_t n_rows,
+                                 uint32_t* const* values);
 /* zero-copy projection / rename (DataFusion ProjectionExec over plain columns) */
 int32_t rfgpu_table_project(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t n_cols,
                             const int32_t* cols, const char* const* new_names, rfgpu_table** out);

@@ -101,6 +101,7 @@ SIGNATURES = {
                                        C.POINTER(C.c_void_p), C.c_uint64, C.POINTER(C.c_void_p)]),
     "rfgpu_table_export": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_void_p),
                                        C.POINTER(C.c_void_p), u64p]),
+    "rfgpu_table_export_async": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_void_p)]),
     "rfgpu_table_project": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_char_p),
                                         C.POINTER(C.c_void_p)]),
     "rfgpu_table_set_nullable": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32]),

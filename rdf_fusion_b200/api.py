@@ -405,6 +405,15 @@ class Table:
         self.ctx.check(self.ctx.lib.rfgpu_table_export(self.ctx.h, self.h, row_off, n, vals, None, None))
         return arrs
 
+    def to_numpy_async(self, out: List[np.ndarray], row_off=0, n_rows=None) -> List[np.ndarray]:
+        """Queue the device→host copies of the value buffers on the ctx's copy stream (rfgpu_table_export_async); `out`
+        (pinned for a real overlap) is valid after ctx.synchronize()."""
+        nc = len(self.names)
+        n = self.num_rows - row_off if n_rows is None else n_rows
+        vals = (C.c_void_p * max(1, nc))(*[a.ctypes.data for a in out])
+        self.ctx.check(self.ctx.lib.rfgpu_table_export_async(self.ctx.h, self.h, row_off, n, vals))
+        return out
+
     def to_arrow(self, row_off=0, n_rows=None):
         """-> pyarrow.RecordBatch through the Arrow C Data Interface (what arrow-rs `ffi` would import)."""
         import pyarrow as pa

@@ -174,6 +174,12 @@ void rfgpu_ctx_destroy(rfgpu_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->core->device);
   cudaStreamSynchronize(ctx->core->stream);
+  if (ctx->copy_stream) {
+    cudaStreamSynchronize(ctx->copy_stream);
+    for (auto* t : ctx->pending_exports) rfgpu_table_release(t);
+    cudaStreamDestroy(ctx->copy_stream);
+    cudaEventDestroy(ctx->copy_event);
+  }
   for (auto& p : ctx->pending) {
     cudaEventDestroy(p.a);
     cudaEventDestroy(p.b);
@@ -193,6 +199,11 @@ int32_t rfgpu_ctx_synchronize(rfgpu_ctx* ctx) {
   RF_API_BEGIN
   RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
   ctx->sync();
+  if (ctx->copy_stream) {
+    RF_CUDA(cudaStreamSynchronize(ctx->copy_stream));
+    for (auto* t : ctx->pending_exports) rfgpu_table_release(t);
+    ctx->pending_exports.clear();
+  }
   RF_API_END(ctx)
 }
 

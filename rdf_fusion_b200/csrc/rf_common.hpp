@@ -117,6 +117,11 @@ struct rfgpu_ctx {
   void* flush_buf = nullptr;
   size_t flush_bytes = 0;
   std::shared_ptr<rf::Comm> comm;
+  // asynchronous exports: device→host copies on their own stream so they overlap host→device imports (PCIe is full
+  // duplex) and kernels; the exported tables stay retained until rfgpu_ctx_synchronize
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t copy_event = nullptr;
+  std::vector<rfgpu_table*> pending_exports;
 
   rf::BufRef alloc(size_t bytes) { return std::make_shared<rf::DevBuf>(core, bytes); }
   cudaStream_t stream() const { return core->stream; }

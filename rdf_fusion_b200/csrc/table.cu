@@ -191,6 +191,30 @@ int32_t rfgpu_table_export(rfgpu_ctx* ctx, const rfgpu_table* t, uint64_t row_of
   RF_API_END(ctx)
 }
 
+int32_t rfgpu_table_export_async(rfgpu_ctx* ctx, rfgpu_table* t, uint64_t row_off, uint64_t n_rows,
+                                 uint32_t* const* values) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx && t, RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(row_off <= t->rows && n_rows <= t->rows - row_off, RFGPU_E_INVALID, "row range out of bounds");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  const size_t nc = t->cols.size();
+  RF_REQUIRE(nc == 0 || values, RFGPU_E_INVALID, "values missing");
+  if (!ctx->copy_stream) {
+    RF_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    RF_CUDA(cudaEventCreateWithFlags(&ctx->copy_event, cudaEventDisableTiming));
+  }
+  // the copies start once everything queued on the ctx stream so far (the kernels that produce `t`) has finished
+  RF_CUDA(cudaEventRecord(ctx->copy_event, ctx->stream()));
+  RF_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->copy_event, 0));
+  for (size_t c = 0; c < nc; c++)
+    if (n_rows && values[c]) {
+      RF_CUDA(cudaMemcpyAsync(values[c], t->cols[c].data + row_off, n_rows * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
+      ctx->m.d2h_bytes += n_rows * 4;
+    }
+  ctx->pending_exports.push_back(rfgpu_table_retain(t));
+  RF_API_END(ctx)
+}
+
 int32_t rfgpu_table_project(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t n_cols, const int32_t* cols,
                             const char* const* new_names, rfgpu_table** out) {
   RF_API_BEGIN

@@ -579,3 +579,20 @@ def test_hash_join_l2_blocked_passes(ctx, oracle, jt, budget):
             assert algo == F.ALGO_EQUI and got.last_join_phys == F.PHYS_HASH
     finally:
         ctx.set_option(F.OPT_HASH_L2_BYTES, 1 << 40)
+
+
+def test_async_export_matches_sync_export(ctx):
+    rng = np.random.default_rng(3)
+    cols = _rand_table(rng, 300000, ["a", "b", "c"], [True, False, True], 0.2, 1 << 28)
+    t = ctx.import_table(cols, {"a": True, "b": False, "c": True})
+    f = t.filter([rf.FPred(F.F_IS_NOT_NULL, 0)])
+    outs = [np.zeros(f.num_rows, np.uint32) for _ in range(3)]
+    f.to_numpy_async(outs)
+    part = [np.zeros(1000, np.uint32) for _ in range(3)]
+    f.to_numpy_async(part, row_off=5, n_rows=1000)
+    del f  # the ctx keeps the table alive until the copies have landed
+    ctx.synchronize()
+    keep = cols["a"] != 0
+    for o, p, name in zip(outs, part, ["a", "b", "c"]):
+        assert np.array_equal(o, cols[name][keep])
+        assert np.array_equal(p, cols[name][keep][5:1005])
