@@ -596,3 +596,51 @@ def test_async_export_matches_sync_export(ctx):
     for o, p, name in zip(outs, part, ["a", "b", "c"]):
         assert np.array_equal(o, cols[name][keep])
         assert np.array_equal(p, cols[name][keep][5:1005])
+
+
+def test_config5_filter_optional_skewed_keys(ctx, oracle):
+    """BASELINE configs[4] in miniature (3 M triples, Zipf 1.2 on predicates and objects): OPTIONAL on a skewed key, FILTER
+    on ids, a compatible-mapping join on a variable left unbound by an OPTIONAL, FILTER(!BOUND), then GROUP BY/COUNT."""
+    g = rf.generate_graph(3_000_000, n_predicates=64, s=1.2, seed=5, s_o=1.2)
+    quads = g.quads()
+    st = _gpu_store(ctx, quads)
+    ost = oracle.OracleStore(8192).load_quads(quads)
+    p1, p2, p3, p9 = g.pred_id(3), g.pred_id(4), g.pred_id(6), g.pred_id(60)
+
+    def scans(store):
+        def sc(s, p, o):
+            return store.plan([rf.traverse(0), rf.scan(s), rf.traverse(p), rf.scan(o)]).execute()
+        return sc("s", p1, "o"), sc("s", p2, "v"), sc("o", p3, "w"), sc("v", p9, "z")
+    ga, gb, gc, gd = scans(st)
+    oa, ob, oc, od = scans(ost)
+    J = lambda l, r, jt: oracle.sparql_join(l, r, jt, "hash")[0]
+
+    def same(gt, ot):
+        assert gt.names == ot.names and gt.nullable == ot.nullable
+        assert gt.num_rows == ot.num_rows
+        assert_same_table(gt.names, gt.to_numpy(), ot.names, ot.cols)
+    # Q5a: ?s p1 ?o OPTIONAL { ?s p2 ?v } FILTER(?o != c)      (equi Left + NE filter)
+    c = int(g.subject_base)  # the heaviest object
+    g5a = ga.join(gb, F.JOIN_LEFT)
+    o5a = J(oa, ob, F.JOIN_LEFT)
+    same(g5a, o5a)
+    pred = [rf.FPred(F.F_NE_CONST, 1, value=c)]
+    same(g5a.filter(pred), oracle.filter_table(o5a, pred))
+    # skewed probe keys: OPTIONAL keyed on the Zipf-distributed object
+    same(ga.join(gc, F.JOIN_LEFT), J(oa, oc, F.JOIN_LEFT))
+    # Q5b: { ?s p1 ?o OPTIONAL { ?s p2 ?v } FILTER(..) } . { ?v p9 ?z }   (?v nullable by schema ⇒ compatible-mapping join;
+    # rows with ?v unbound pair with EVERY rhs row, so the lhs is narrowed first to keep the broadcast ~4 M rows)
+    narrow = [rf.FPred(F.F_EQ_CONST, 1, value=c),
+              rf.FPred(F.F_BETWEEN, 0, value=g.subject_base, hi=g.subject_base + g.n_subjects // 20)]
+    g5n, o5n = g5a.filter(narrow), oracle.filter_table(o5a, narrow)
+    same(g5n, o5n)
+    assert 100 < o5n.num_rows < 5000
+    g5b = g5n.join(gd, F.JOIN_INNER)
+    assert g5b.last_join_algo == F.ALGO_COMPATIBLE
+    same(g5b, J(o5n, od, F.JOIN_INNER))
+    same(g5n.join(gd, F.JOIN_LEFT), J(o5n, od, F.JOIN_LEFT))
+    # Q5c: FILTER(!BOUND(?v)), then GROUP BY ?o COUNT(*)
+    nb = [rf.FPred(F.F_IS_NULL, g5a.names.index("v"))]
+    g5c, o5c = g5a.filter(nb), oracle.filter_table(o5a, nb)
+    same(g5c, o5c)
+    same(g5c.group_count(["o"], None, "n"), oracle.group_count(o5c, ["o"], None, "n"))

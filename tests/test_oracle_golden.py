@@ -162,3 +162,26 @@ def test_equi_join_matches_arrow_acero(oracle, jt, how):
             ref = pa.table(lc).join(pa.table(rc), keys=keys, join_type=how)
             ref_cols = [np.asarray(ref[n].fill_null(0).to_numpy(), dtype=np.uint32) for n in got.names]
             assert np.array_equal(oracle.canonical_rows(got.cols), oracle.canonical_rows(ref_cols)), (nl, nr, impl)
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_oracle_hash_join_equals_definition(oracle, jt):
+    """The oracle's fast (hash, class-split) join must be the same relation as its nested-loop restatement of the
+    definition — it is the checker for the large GPU cases, where the nested loop cannot finish."""
+    rng = np.random.default_rng(17)
+    for nl, nr, ks, nullable_l, nullable_r in [(60, 50, 6, True, True), (200, 150, 12, True, False), (150, 200, 9, False, True),
+                                               (120, 90, 5, False, False)]:
+        def tab(n, names, nullable):
+            cols = []
+            for nm, nu in zip(names, nullable):
+                v = rng.integers(1, ks + 1, n).astype(np.uint32)
+                if nu:
+                    v[rng.random(n) < 0.3] = 0
+                cols.append(v)
+            return oracle.OTable(names, nullable, cols)
+        l = tab(nl, ["k", "k2", "a"], [nullable_l, nullable_l, False])
+        r = tab(nr, ["k", "k2", "b"], [nullable_r, False, True])
+        a, algo_a, _ = oracle.sparql_join(l, r, jt, "nested")
+        b, algo_b, _ = oracle.sparql_join(l, r, jt, "hash")
+        assert algo_a == algo_b and a.names == b.names and a.nullable == b.nullable
+        assert np.array_equal(oracle.canonical_rows(a.cols), oracle.canonical_rows(b.cols))
