@@ -45,6 +45,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--merge-threads", type=int, default=0, help="CTA size of the merge-join kernel (64/128/256)")
+    ap.add_argument("--workload", default="star", choices=["star", "chain"],
+                    help="star: BASELINE configs[1] (default, the driver's line); chain: ?a p1 ?b . ?b p2 ?c with an NVLink "
+                         "shuffle on ?b between the ranks (configs[3] in miniature; evidence run, needs --gpus >= 2 to shuffle)")
     ap.add_argument("--unbatched", action="store_true", help="one range look-up launch per scan instead of the batched form")
     ap.add_argument("--radix-join", action="store_true", help="with --hash-join: the radix-partitioned variant")
     ap.add_argument("--hash-join", action="store_true", help="scan the join inputs through GPOS and force the hash join")
@@ -365,6 +368,103 @@ def run_ours(a):
         dist.destroy_process_group()
 
 
+def run_chain(a):
+    """?a p1 ?b . ?b p2 ?c over subject-partitioned stores: the lhs solutions are hash-shuffled on ?b (partition kernel + NCCL
+    all-to-all over NVLink), the rhs is a local scan already partitioned (and sorted) on ?b; hash join on ?b."""
+    import torch
+    import torch.distributed as dist
+
+    import rdf_fusion_b200 as rf
+    from rdf_fusion_b200 import _ffi as F
+    from rdf_fusion_b200.dist import init_comm
+    from rdf_fusion_b200.loader import load_store_device, partition_by_subject
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.pop("NCCL_DEBUG", None)
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = rf.Context(local)
+    if world > 1:
+        init_comm(ctx)
+    g = rf.generate_graph(a.triples * world, a.predicates, a.zipf, a.seed)
+    cols = partition_by_subject((g.g, g.s, g.p, g.o), rank, world)
+    store = load_store_device(ctx, *cols, perms=(F.GSPO, F.GPOS, F.GPSO))
+    del cols
+    p_ab = store.plan([rf.traverse(0), rf.scan("a"), rf.traverse(g.pred_id(1)), rf.scan("b")])
+    p_bc = store.plan([rf.traverse(0), rf.scan("b"), rf.traverse(g.pred_id(2)), rf.scan("c")])
+    p_bc.order_by("b")
+    stats = {"shuffle_ms": 0.0, "join_ms": 0.0, "scan_ms": 0.0, "sent_rows": 0}
+
+    def step():
+        ctx.timer_start()
+        ab, bc = rf.execute_many([p_ab, p_bc], allow_view=True)
+        stats["scan_ms"] += ctx.timer_stop()
+        ctx.timer_start()
+        sh = ab.shuffle("b")
+        stats["shuffle_ms"] += ctx.timer_stop()
+        stats["sent_rows"] += ab.num_rows
+        ctx.timer_start()
+        j = sh.join(bc, F.JOIN_INNER)
+        stats["join_ms"] += ctx.timer_stop()
+        return ab.num_rows + bc.num_rows, j.num_rows
+
+    def barrier():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+    for _ in range(max(a.warmup, 3)):
+        step()
+    for k in stats:
+        stats[k] = 0
+    barrier()
+    rows = out = 0
+    ms = 0.0
+    for _ in range(a.steps):
+        ctx.flush_l2()
+        barrier()  # the shuffle is a collective: ranks enter the timed step together
+        t0 = time.perf_counter()
+        r, o = step()
+        ctx.synchronize()
+        ms += 1e3 * (time.perf_counter() - t0)
+        rows += r
+        out += o
+    barrier()
+    if world > 1:
+        t = torch.tensor([ms, stats["shuffle_ms"], stats["join_ms"], stats["scan_ms"]], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, stats["shuffle_ms"], stats["join_ms"], stats["scan_ms"] = [float(x) for x in t.tolist()]
+        c = torch.tensor([rows, out, stats["sent_rows"]], dtype=torch.int64, device="cuda")
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        rows, out, sent = [int(x) for x in c.tolist()]
+    else:
+        sent = stats["sent_rows"]
+    if rank == 0:
+        # bytes that cross NVLink per rank and direction: 2 columns x 4 B x rows x (g-1)/g
+        link_bytes = 8.0 * (sent / world) * (world - 1) / world / a.steps
+        sh_ms = stats["shuffle_ms"] / a.steps
+        link = {"bytes_per_rank_per_step": link_bytes, "ms": sh_ms,
+                "achieved": (link_bytes / (sh_ms / 1e3) / 1e9) if sh_ms > 0 and world > 1 else None, "unit": "GB/s",
+                "peak": 770.0, "peak_source": "measured peer copy per direction (B200_PROFILING.md); nominal 900",
+                "note": "shuffle = partition kernels + count all-gather + grouped ncclSend/ncclRecv + host syncs"}
+        if link["achieved"]:
+            link["frac"] = link["achieved"] / link["peak"]
+        emit({"metric": "chain-join rows/s (scan + NVLink shuffle + hash join)", "value": rows / (ms / 1e3), "unit": "rows/s",
+              "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms / a.steps,
+              "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+              "config": {"workload": f"chain ?a p1 ?b . ?b p2 ?c on G(N={a.triples * world}, P={a.predicates}, zipf={a.zipf}, "
+                                     f"seed={a.seed}); lhs shuffled on ?b", "triples_per_gpu": a.triples,
+                         "rows_in_per_step": rows // a.steps, "rows_out_per_step": out // a.steps,
+                         "timing": "host wall clock between barriers (the step contains a collective), max over ranks",
+                         "phases_ms": {k: stats[k] / a.steps for k in ("scan_ms", "shuffle_ms", "join_ms")}},
+              "nvlink": link})
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     a = parse_args()
     # stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner) are sent to stderr while
@@ -375,6 +475,8 @@ def main():
     os.dup2(2, 1)
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload == "chain":
+        run_chain(a)
     else:
         run_ours(a)
 

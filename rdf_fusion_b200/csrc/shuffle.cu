@@ -270,26 +270,31 @@ int32_t rfgpu_shuffle(rfgpu_ctx* ctx, const rfgpu_table* in, int32_t key_col, rf
   RF_REQUIRE(recv_total < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "shuffle result exceeds 2^32-2 rows on one GPU");
   t->rows = recv_total;
   uint64_t link_bytes = 0;
+  std::vector<uint32_t*> dsts;
   for (size_t c = 0; c < in->cols.size(); c++) {
     Column col = in->cols[c];
     col.owner = alloc_col(ctx, recv_total);
     col.data = col.owner->as<uint32_t>();
-    uint32_t* dst = col.owner->as<uint32_t>();
+    dsts.push_back(col.owner->as<uint32_t>());
+    t->cols.push_back(std::move(col));
+  }
+  // one NCCL group for every (column, peer) pair: a single fused all-to-all launch
+  RF_NCCL(nccl().GroupStart());
+  for (size_t c = 0; c < in->cols.size(); c++) {
     const uint32_t* src = parts[c]->as<uint32_t>();
-    RF_NCCL(nccl().GroupStart());
     for (int r = 0; r < g; r++) {
       uint64_t ns = send_counts[r], nr = all[(size_t)r * g + me];
       if (r == me) continue;
       if (ns) RF_NCCL(nccl().Send(src + send_off[r], ns, ncclUint32, r, ctx->comm->comm, ctx->stream()));
-      if (nr) RF_NCCL(nccl().Recv(dst + recv_off[r], nr, ncclUint32, r, ctx->comm->comm, ctx->stream()));
+      if (nr) RF_NCCL(nccl().Recv(dsts[c] + recv_off[r], nr, ncclUint32, r, ctx->comm->comm, ctx->stream()));
       link_bytes += ns * 4;
     }
-    RF_NCCL(nccl().GroupEnd());
-    if (send_counts[me])  // my own partition never crosses NVLink
-      RF_CUDA(cudaMemcpyAsync(dst + recv_off[me], src + send_off[me], send_counts[me] * 4, cudaMemcpyDeviceToDevice,
-                              ctx->stream()));
-    t->cols.push_back(std::move(col));
   }
+  RF_NCCL(nccl().GroupEnd());
+  for (size_t c = 0; c < in->cols.size(); c++)
+    if (send_counts[me])  // my own partition never crosses NVLink
+      RF_CUDA(cudaMemcpyAsync(dsts[c] + recv_off[me], parts[c]->as<uint32_t>() + send_off[me], send_counts[me] * 4,
+                              cudaMemcpyDeviceToDevice, ctx->stream()));
   ctx->sync();
   ctx->m.algorithmic_bytes += link_bytes;
   *out = t.release();
