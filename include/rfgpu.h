@@ -171,6 +171,11 @@ int32_t rfgpu_table_export(rfgpu_ctx* ctx, const rfgpu_table* t, uint64_t row_of
  * buffers (page-locked for a real overlap) are valid after the next rfgpu_ctx_synchronize; `t` is retained until then. */
 int32_t rfgpu_table_export_async(rfgpu_ctx* ctx, rfgpu_table* t, uint64_t row_off, uint64_t n_rows,
                                  uint32_t* const* values);
+/* Bounds of the non-NULL values of a column: what HashJoinExec publishes as its dynamic filter (build-side min/max →
+ * Between on the probe-side scan: pattern_data_source.rs:107-151, predicate_pushdown.rs:253-268).  The host feeds the result
+ * to rfgpu_scan_plan_apply_between before the probe-side scan runs.  No non-NULL value: min = UINT32_MAX, max = 0. */
+int32_t rfgpu_table_col_min_max(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t col, uint32_t* min_out, uint32_t* max_out,
+                                uint64_t* non_null);
 /* zero-copy projection / rename (DataFusion ProjectionExec over plain columns) */
 int32_t rfgpu_table_project(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t n_cols,
                             const int32_t* cols, const char* const* new_names, rfgpu_table** out);

@@ -101,6 +101,7 @@ SIGNATURES = {
                                        C.POINTER(C.c_void_p), C.c_uint64, C.POINTER(C.c_void_p)]),
     "rfgpu_table_export": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_void_p),
                                        C.POINTER(C.c_void_p), u64p]),
+    "rfgpu_table_col_min_max": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), u64p]),
     "rfgpu_table_export_async": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_void_p)]),
     "rfgpu_table_project": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_char_p),
                                         C.POINTER(C.c_void_p)]),
@@ -143,6 +144,8 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
+    global LIB_PATH
+    LIB_PATH = os.environ.get("RFGPU_LIB", LIB_PATH)  # kernel-variant experiments load another build of the same library
     if not os.path.exists(LIB_PATH):
         raise ImportError(
             f"{LIB_PATH} is missing: build the CUDA library first (make -C rdf_fusion_b200/csrc). "

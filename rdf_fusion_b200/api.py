@@ -405,6 +405,13 @@ class Table:
         self.ctx.check(self.ctx.lib.rfgpu_table_export(self.ctx.h, self.h, row_off, n, vals, None, None))
         return arrs
 
+    def min_max(self, col):
+        """(min, max, non-null count) of a column's bound values: the dynamic-filter bounds a hash join publishes."""
+        i = self.names.index(col) if isinstance(col, str) else int(col)
+        mn, mx, nn = C.c_uint32(), C.c_uint32(), C.c_uint64()
+        self.ctx.check(self.ctx.lib.rfgpu_table_col_min_max(self.ctx.h, self.h, i, C.byref(mn), C.byref(mx), C.byref(nn)))
+        return int(mn.value), int(mx.value), int(nn.value)
+
     def to_numpy_async(self, out: List[np.ndarray], row_off=0, n_rows=None) -> List[np.ndarray]:
         """Queue the device→host copies of the value buffers on the ctx's copy stream (rfgpu_table_export_async); `out`
         (pinned for a real overlap) is valid after ctx.synchronize()."""

@@ -63,10 +63,11 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
     RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_tiles * 8, ctx->stream()));  // look-back words
     {
       KernelScope ks(ctx, "k_merge_join", 4ull * (np + nb));  // keys; payload + output bytes are added below
+      static const size_t dbg_smem = getenv("RFGPU_DEBUG_SMEM") ? (size_t)atoi(getenv("RFGPU_DEBUG_SMEM")) : 0;  // occupancy experiments
       switch (threads) {
-        case 64: k_merge_join<64><<<n_tiles, 64, 0, ctx->stream()>>>(A); break;
-        case 128: k_merge_join<128><<<n_tiles, 128, 0, ctx->stream()>>>(A); break;
-        default: k_merge_join<256><<<n_tiles, 256, 0, ctx->stream()>>>(A); break;
+        case 64: k_merge_join<64><<<n_tiles, 64, dbg_smem, ctx->stream()>>>(A); break;
+        case 128: k_merge_join<128><<<n_tiles, 128, dbg_smem, ctx->stream()>>>(A); break;
+        default: k_merge_join<256><<<n_tiles, 256, dbg_smem, ctx->stream()>>>(A); break;
       }
     }
     RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 10, A.total, 8, cudaMemcpyDeviceToHost, ctx->stream()));

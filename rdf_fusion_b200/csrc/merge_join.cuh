@@ -25,6 +25,9 @@
 
 namespace rf {
 
+#ifndef RF_MERGE_MIN_CTAS
+#define RF_MERGE_MIN_CTAS 12  // 40 registers/thread, 18.7 KB of shared memory per CTA: 12 CTAs (48 warps) per SM
+#endif
 constexpr int kMGran = 256;    // granularity of the coarse window search
 constexpr int kMItems = 8;     // probe rows (and output slots per round) per thread
 // CTA shape: kMThreads threads own a tile of 8*kMThreads probe rows.  Smaller CTAs = more resident CTAs per SM in
@@ -32,7 +35,7 @@ constexpr int kMItems = 8;     // probe rows (and output slots per round) per th
 template <int kMThreads>
 struct MergeShape {
   static constexpr int kTile = kMThreads * kMItems;   // probe rows per CTA
-  static constexpr int kWin = kMThreads * 14;         // build keys staged per tile; larger windows: global memory
+  static constexpr int kWin = kMThreads * 12;         // build keys staged per tile; larger windows: global memory
   static constexpr int kChunk = kTile;                // output rows expanded per round
 };
 
@@ -163,10 +166,19 @@ __device__ __forceinline__ unsigned long long block_excl_u64(unsigned long long 
   return wpre + inc - v;
 }
 
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+
 __device__ __forceinline__ uint32_t hpad(uint32_t x) { return x + (x >> 3); }  // 8 items per thread, conflict-free
 
 template <int kMThreads>
-__global__ void __launch_bounds__(kMThreads)
+__global__ void __launch_bounds__(kMThreads, kMThreads == 128 ? RF_MERGE_MIN_CTAS : 1)
 k_merge_join(const __grid_constant__ MergeArgs A) {
   constexpr int kMTile = MergeShape<kMThreads>::kTile, kMWin = MergeShape<kMThreads>::kWin,
                 kMChunk = MergeShape<kMThreads>::kChunk, kMChunkItems = kMItems;
@@ -264,25 +276,33 @@ k_merge_join(const __grid_constant__ MergeArgs A) {
       }
       runstart = r;
     }
-    uint32_t pk = i < rows ? sp[i] : 0xFFFFFFFFu;
-    uint32_t bk = sb[j];  // stale when j == wn: guarded below
+    // The walk below runs on shared-memory BYTE addresses (one add per consumed item, no index→address arithmetic):
+    //   pa / ba   next unread probe / build key,  run_a  first build key of the run that `lastb` belongs to.
+    const uint32_t sp_a = dev::smem_u32(sp), sb_a = dev::smem_u32(sb);
+    uint32_t pa = sp_a + 4 * i, ba = sb_a + 4 * j, run_a = sb_a + 4 * runstart;
+    const uint32_t pa_end = sp_a + 4 * rows, ba_end = sb_a + 4 * wn;
+    const uint32_t gs_delta = dev::smem_u32(S.gs) - sp_a, off_delta = dev::smem_u32(S.off) - sp_a;
+    const uint32_t cs4 = 4 * cs - sb_a;  // (run_a + cs4) / 4 = absolute build row of the run start
+    uint32_t pk = pa < pa_end ? lds32(pa) : 0xFFFFFFFFu;
+    uint32_t bk = lds32(ba);  // stale when ba == ba_end: guarded below
     // branch-free step: exactly one of (build key, probe row) is consumed
 #pragma unroll 2
     for (uint32_t s = d0; s < d1; s++) {
-      const bool take_b = (j < wn) & (bk <= pk);
+      const bool take_b = (ba < ba_end) & (bk <= pk);
+      const bool match = (lastb == pk) & (pk != 0);
+      const uint32_t gsv = match ? (run_a + cs4) >> 2 : kNone;
+      const uint32_t ev = match ? (ba - run_a) >> 2 : leftpad;
       if (!take_b) {
-        const uint32_t cnt = (lastb == pk && pk != 0) ? j - runstart : 0;
-        S.gs[i] = cnt ? cs + runstart : kNone;
-        S.off[i] = cnt ? cnt : leftpad;
+        sts32(pa + gs_delta, gsv);
+        sts32(pa + off_delta, ev);
       }
-      runstart = (take_b && bk != lastb) ? j : runstart;
+      run_a = (take_b & (bk != lastb)) ? ba : run_a;
       lastb = take_b ? bk : lastb;
-      j += take_b ? 1u : 0u;
-      i += take_b ? 0u : 1u;
-      const uint32_t* q = take_b ? sb + j : sp + i;
-      const uint32_t nxt = *q;
+      ba += take_b ? 4u : 0u;
+      pa += take_b ? 0u : 4u;
+      const uint32_t nxt = lds32(take_b ? ba : pa);
       bk = take_b ? nxt : bk;
-      pk = take_b ? pk : (i < rows ? nxt : 0xFFFFFFFFu);
+      pk = take_b ? pk : (pa < pa_end ? nxt : 0xFFFFFFFFu);
     }
   } else {
     // ---- window too large to stage (build side locally much denser): per-row binary searches in global memory ----

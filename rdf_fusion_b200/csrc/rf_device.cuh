@@ -51,7 +51,10 @@ __device__ __forceinline__ unsigned long long lookback_resolve(unsigned long lon
     uint32_t invalid = __ballot_sync(0xFFFFFFFFu, flag == 0);
     int firstP = pmask ? (__ffs(pmask) - 1) : 32;
     uint32_t need = firstP == 32 ? 0xFFFFFFFFu : ((2u << firstP) - 1u);
-    if (invalid & need) continue;  // a needed predecessor has not published yet
+    if (invalid & need) {  // a needed predecessor has not published yet: back off instead of burning issue slots
+      __nanosleep(64);
+      continue;
+    }
     unsigned long long val = ((int)lane <= firstP) ? (s & kValMask) : 0ull;
     excl += warp_sum_u64(val);
     if (pmask) break;

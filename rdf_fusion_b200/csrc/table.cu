@@ -50,6 +50,35 @@ __global__ void k_check_ascending(const uint32_t* __restrict__ v, uint64_t n, un
     if (v[i - 1] > v[i]) atomicMin(first_bad, (unsigned long long)i);
 }
 
+// min / max over the non-NULL values of a column (NULL = 0): block reduce + atomics on a {min, max, count} triple
+__global__ void __launch_bounds__(256)
+k_col_min_max(const uint32_t* __restrict__ v, uint64_t n, unsigned int* __restrict__ out /*min, max*/,
+              unsigned long long* __restrict__ non_null) {
+  uint32_t mn = 0xFFFFFFFFu, mx = 0;
+  unsigned long long cnt = 0;
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const uint32_t x = __ldg(v + i);
+    if (x != 0) {
+      mn = min(mn, x);
+      mx = max(mx, x);
+      cnt++;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mn = min(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, o));
+    mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+    cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
+  }
+  if ((threadIdx.x & 31) == 0 && cnt) {
+    atomicMin(out, mn);
+    atomicMax(out + 1, mx);
+    atomicAdd(non_null, cnt);
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -212,6 +241,35 @@ int32_t rfgpu_table_export_async(rfgpu_ctx* ctx, rfgpu_table* t, uint64_t row_of
       ctx->m.d2h_bytes += n_rows * 4;
     }
   ctx->pending_exports.push_back(rfgpu_table_retain(t));
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_table_col_min_max(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t col, uint32_t* min_out, uint32_t* max_out,
+                                uint64_t* non_null) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx && t && min_out && max_out, RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(col >= 0 && col < (int32_t)t->cols.size(), RFGPU_E_INVALID, "column index out of range");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  *min_out = 0xFFFFFFFFu;
+  *max_out = 0;
+  if (non_null) *non_null = 0;
+  if (t->rows) {
+    auto d = ctx->alloc(16);
+    const unsigned int init[4] = {0xFFFFFFFFu, 0u, 0u, 0u};
+    RF_CUDA(cudaMemcpyAsync(d->ptr, init, 16, cudaMemcpyHostToDevice, ctx->stream()));
+    {
+      rf::KernelScope ks(ctx, "k_col_min_max", 4ull * t->rows);
+      uint32_t blocks = (uint32_t)std::min<uint64_t>(rf::div_up(t->rows, 256 * 8), (uint64_t)ctx->core->num_sms * 8);
+      k_col_min_max<<<std::max(blocks, 1u), 256, 0, ctx->stream()>>>(t->cols[col].data, t->rows, d->as<unsigned int>(),
+                                                                    d->as<unsigned long long>() + 1);
+    }
+    RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 14, d->ptr, 16, cudaMemcpyDeviceToHost, ctx->stream()));
+    ctx->sync();
+    const uint32_t* r = reinterpret_cast<const uint32_t*>(ctx->h_scratch + 14);
+    *min_out = r[0];
+    *max_out = r[1];
+    if (non_null) *non_null = ctx->h_scratch[15];
+  }
   RF_API_END(ctx)
 }
 

@@ -644,3 +644,31 @@ def test_config5_filter_optional_skewed_keys(ctx, oracle):
     g5c, o5c = g5a.filter(nb), oracle.filter_table(o5a, nb)
     same(g5c, o5c)
     same(g5c.group_count(["o"], None, "n"), oracle.group_count(o5c, ["o"], None, "n"))
+
+
+def test_dynamic_filter_bounds_from_build_side(ctx, oracle):
+    """HashJoinExec's dynamic filter: the build side's key bounds become a Between on the probe-side scan
+    (scan.rs:217-261).  It changes the scan's work, never the join's result."""
+    g = rf.generate_graph(400000, n_predicates=12, s=1.0, seed=8)
+    quads = g.quads()
+    st = _gpu_store(ctx, quads)
+    ost = oracle.OracleStore(8192).load_quads(quads)
+    build = st.plan([rf.traverse(0), rf.scan("s", rf.Between(g.subject_base + 100, g.subject_base + 900)),
+                     rf.traverse(g.pred_id(2)), rf.scan("x")]).execute()
+    mn, mx, nn = build.min_max("s")
+    sc = build.to_numpy()[0]
+    assert (mn, mx, nn) == (int(sc.min()), int(sc.max()), len(sc))
+    probe_plan = st.plan([rf.traverse(0), rf.scan("s"), rf.traverse(g.pred_id(1)), rf.scan("y")])
+    full = probe_plan.execute()
+    probe_plan.apply_between("s", mn, mx)
+    pruned = probe_plan.execute()
+    assert 0 < pruned.num_rows < full.num_rows
+    ob = ost.plan([rf.traverse(0), rf.scan("s", rf.Between(g.subject_base + 100, g.subject_base + 900)),
+                   rf.traverse(g.pred_id(2)), rf.scan("x")]).execute()
+    op = ost.plan([rf.traverse(0), rf.scan("s"), rf.traverse(g.pred_id(1)), rf.scan("y")]).execute()
+    exp = oracle.sparql_join(ob, op, F.JOIN_INNER, "hash")[0]
+    for probe in (full, pruned):
+        got = build.join(probe)
+        assert_same_table(got.names, got.to_numpy(), exp.names, exp.cols)
+    empty = ctx.import_table({"a": np.zeros(5, np.uint32)}, {"a": True})
+    assert empty.min_max("a") == (0xFFFFFFFF, 0, 0)
