@@ -48,6 +48,8 @@ def parse_args():
     ap.add_argument("--workload", default="star", choices=["star", "chain"],
                     help="star: BASELINE configs[1] (default, the driver's line); chain: ?a p1 ?b . ?b p2 ?c with an NVLink "
                          "shuffle on ?b between the ranks (configs[3] in miniature; evidence run, needs --gpus >= 2 to shuffle)")
+    ap.add_argument("--nccl-shuffle", action="store_true",
+                    help="chain workload: partition kernels + ncclSend/ncclRecv instead of the fused peer-memory scatter")
     ap.add_argument("--unbatched", action="store_true", help="one range look-up launch per scan instead of the batched form")
     ap.add_argument("--radix-join", action="store_true", help="with --hash-join: the radix-partitioned variant")
     ap.add_argument("--hash-join", action="store_true", help="scan the join inputs through GPOS and force the hash join")
@@ -387,6 +389,8 @@ def run_chain(a):
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = rf.Context(local)
+    if a.nccl_shuffle:
+        ctx.set_option(F.OPT_SHUFFLE_P2P, 0)
     if world > 1:
         init_comm(ctx)
     g = rf.generate_graph(a.triples * world, a.predicates, a.zipf, a.seed)
@@ -421,6 +425,8 @@ def run_chain(a):
     for k in stats:
         stats[k] = 0
     barrier()
+    ctx.metrics_reset()
+    ctx.profile_enable(True)
     rows = out = 0
     ms = 0.0
     for _ in range(a.steps):
@@ -433,6 +439,8 @@ def run_chain(a):
         rows += r
         out += o
     barrier()
+    prof = ctx.profile()
+    ctx.profile_enable(False)
     if world > 1:
         t = torch.tensor([ms, stats["shuffle_ms"], stats["join_ms"], stats["scan_ms"]], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -449,7 +457,12 @@ def run_chain(a):
         link = {"bytes_per_rank_per_step": link_bytes, "ms": sh_ms,
                 "achieved": (link_bytes / (sh_ms / 1e3) / 1e9) if sh_ms > 0 and world > 1 else None, "unit": "GB/s",
                 "peak": 770.0, "peak_source": "measured peer copy per direction (B200_PROFILING.md); nominal 900",
-                "note": "shuffle = partition kernels + count all-gather + grouped ncclSend/ncclRecv + host syncs"}
+                "path": {F.SHUFFLE_LOCAL: "local", F.SHUFFLE_NCCL: "nccl", F.SHUFFLE_P2P: "p2p"}[ctx.last_shuffle_path],
+                "note": "p2p = one fused partition + peer-memory scatter kernel, one count all-gather (barrier), one host "
+                        "hand-off, local copy-out; nccl = partition kernels + count all-gather + grouped "
+                        "ncclSend/ncclRecv + host hand-offs",
+                "kernels_us_per_step": {k: round(1e3 * v["ms"] / a.steps, 1) for k, v in prof.items()
+                                        if "shuffle" in k or "part" in k}}
         if link["achieved"]:
             link["frac"] = link["achieved"] / link["peak"]
         emit({"metric": "chain-join rows/s (scan + NVLink shuffle + hash join)", "value": rows / (ms / 1e3), "unit": "rows/s",

@@ -271,7 +271,12 @@ typedef enum {
   RFGPU_OPT_RADIX_MIN_ROWS = 4, /* default 65536 */
   RFGPU_OPT_HASH_L2_BYTES = 5,  /* hash join: table bytes per pass (default: unlimited = one pass); larger build sides are
                                    joined in up to 8 passes over disjoint hash ranges so each pass's table stays in L2 */
-  RFGPU_OPT_MERGE_THREADS = 2 /* CTA size of the merge-join kernel: 64, 128 (default) or 256 threads, 8 probe rows each */
+  RFGPU_OPT_MERGE_THREADS = 2, /* CTA size of the merge-join kernel: 64, 128 (default) or 256 threads, 8 probe rows each */
+  RFGPU_OPT_SHUFFLE_P2P = 6,   /* 1 (default): rfgpu_shuffle partitions straight into the destination ranks' receive arenas
+                                  over NVLink peer memory (one fused kernel); 0: partition locally, then ncclSend/ncclRecv */
+  RFGPU_OPT_SHUFFLE_ARENA_BYTES = 7 /* size of this rank's receive arena (two halves, used alternately); read by
+                                       rfgpu_comm_init, default 1 GiB.  A shuffle whose rows do not fit one half on some
+                                       rank falls back to the NCCL exchange on every rank */
 } rfgpu_option;
 int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value);
 
@@ -282,10 +287,19 @@ int32_t rfgpu_comm_init(rfgpu_ctx* ctx, int32_t rank, int32_t n_ranks,
                         const uint8_t id[RFGPU_UNIQUE_ID_BYTES]);
 int32_t rfgpu_comm_rank(const rfgpu_ctx* ctx);
 int32_t rfgpu_comm_size(const rfgpu_ctx* ctx);
-/* Hash-partition `in` on column `key_col` (dest = mix32(id) mod n_ranks; NULL keys stay
- * local... see DESIGN.md) and exchange with a grouped ncclSend/ncclRecv all-to-all: the
- * exchange DataFusion's RepartitionExec(Hash) does between tokio tasks. */
+/* Hash-partition `in` on column `key_col` (dest = mix32(id) mod n_ranks; NULL is an ordinary key value) and
+ * exchange the rows between the ranks: the exchange DataFusion's RepartitionExec(Hash) does between tokio tasks.
+ * Collective: every rank of the communicator calls it, in the same order.  Default path: ONE kernel that computes the
+ * destinations, reserves space in each destination's receive arena with an atomic over NVLink and writes the rows there
+ * through peer memory (cudaIpc mappings set up by rfgpu_comm_init), followed by one 8-byte-per-rank all-gather that is
+ * both the completion barrier and the row-count exchange.  Fallback (option off, IPC unavailable, arena too small):
+ * partition kernels + count-matrix all-gather + grouped ncclSend/ncclRecv.  Row order of the result is unspecified. */
 int32_t rfgpu_shuffle(rfgpu_ctx* ctx, const rfgpu_table* in, int32_t key_col, rfgpu_table** out);
+/* which exchange the last rfgpu_shuffle of this ctx used */
+#define RFGPU_SHUFFLE_LOCAL 0 /* one rank: partition only */
+#define RFGPU_SHUFFLE_NCCL 1  /* partition kernels + grouped ncclSend/ncclRecv */
+#define RFGPU_SHUFFLE_P2P 2   /* fused partition + peer-memory scatter kernel */
+int32_t rfgpu_last_shuffle_path(const rfgpu_ctx* ctx);
 /* the destination rank of an id under the shuffle's hash (host mirror, for tests) */
 uint32_t rfgpu_shuffle_dest(uint32_t id, uint32_t n_ranks);
 /* partition only (no communication): rows grouped by destination, counts[n_parts] filled */

@@ -38,6 +38,9 @@ OPT_MERGE_THREADS = 2
 OPT_RADIX_JOIN = 3
 OPT_RADIX_MIN_ROWS = 4
 OPT_HASH_L2_BYTES = 5
+OPT_SHUFFLE_P2P = 6
+OPT_SHUFFLE_ARENA_BYTES = 7
+SHUFFLE_LOCAL, SHUFFLE_NCCL, SHUFFLE_P2P = 0, 1, 2
 UNIQUE_ID_BYTES = 128
 
 u32p = C.POINTER(C.c_uint32)
@@ -125,6 +128,7 @@ SIGNATURES = {
     "rfgpu_comm_size": (C.c_int32, [C.c_void_p]),
     "rfgpu_shuffle": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]),
     "rfgpu_shuffle_dest": (C.c_uint32, [C.c_uint32, C.c_uint32]),
+    "rfgpu_last_shuffle_path": (C.c_int32, [C.c_void_p]),
     "rfgpu_partition": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_uint32, C.POINTER(C.c_void_p), u64p]),
     "rfgpu_metrics_get": (C.c_int32, [C.c_void_p, C.POINTER(Metrics)]),
     "rfgpu_metrics_reset": (C.c_int32, [C.c_void_p]),

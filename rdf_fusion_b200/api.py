@@ -231,6 +231,11 @@ class Context:
         buf = (C.c_uint8 * F.UNIQUE_ID_BYTES)(*uid)
         self.check(self.lib.rfgpu_comm_init(self.h, rank, n_ranks, buf))
 
+    @property
+    def last_shuffle_path(self) -> int:
+        """F.SHUFFLE_LOCAL / SHUFFLE_NCCL / SHUFFLE_P2P of the last Table.shuffle on this context"""
+        return int(self.lib.rfgpu_last_shuffle_path(self.h))
+
 
 class Store:
     """IndexPermutations on the device (rfgpu_store)."""

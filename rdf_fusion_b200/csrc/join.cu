@@ -721,6 +721,11 @@ int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value) {
       RF_REQUIRE(value == 64 || value == 128 || value == 256, RFGPU_E_INVALID, "merge-join CTA size must be 64, 128 or 256");
       ctx->opt_merge_threads = (int)value;
       break;
+    case RFGPU_OPT_SHUFFLE_P2P: ctx->opt_shuffle_p2p = value != 0; break;
+    case RFGPU_OPT_SHUFFLE_ARENA_BYTES:
+      RF_REQUIRE(value >= (1 << 20), RFGPU_E_INVALID, "shuffle arena must be >= 1 MiB");
+      ctx->opt_shuffle_arena_bytes = value;
+      break;
     default: throw rf::Error(RFGPU_E_INVALID, "unknown option");
   }
   RF_API_END(ctx)

@@ -104,6 +104,9 @@ struct rfgpu_ctx {
   int64_t opt_hash_l2_bytes = 1ll << 40;   // table bytes one pass of the hash join may hold; > this ⇒ multi-pass L2 blocking
                                            // (opt-in: measured no faster yet)
   int opt_merge_threads = 128;  // CTA size of k_merge_join (tile = 8 rows per thread)
+  bool opt_shuffle_p2p = true;  // rfgpu_shuffle: fused partition + peer-memory scatter when the IPC arenas are mapped
+  int64_t opt_shuffle_arena_bytes = 1ll << 30;  // receive arena of this rank (read by rfgpu_comm_init)
+  int last_shuffle_path = 0;
   uint64_t last_from = 0, last_to = 0;
   // pinned host scratch for small device→host results (ranges, counts)
   uint64_t* h_scratch = nullptr;  // 256 x u64: [0,16) scalars, [16,80) partition counts, [128,160) batched ranges

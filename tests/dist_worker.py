@@ -27,6 +27,9 @@ from rdf_fusion_b200.dist import exchange_layout, init_comm, owner_of_subject, p
 def main():
     mode = sys.argv[1]  # "cpu" | "gpu"
     n_triples = int(sys.argv[2]) if len(sys.argv) > 2 else 40000
+    # gpu only: "p2p" (default: fused partition + peer-memory scatter), "nccl" (option off), "tiny" (1 MiB arena: rows do
+    # not fit, every rank must fall back to the NCCL exchange together)
+    exchange = sys.argv[3] if len(sys.argv) > 3 else "p2p"
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if mode == "gpu":
@@ -43,14 +46,20 @@ def main():
 
     if mode == "gpu":
         ctx = rf.Context(local)
+        if exchange == "tiny":
+            ctx.set_option(F.OPT_SHUFFLE_ARENA_BYTES, 1 << 20)
+        if exchange == "nccl":
+            ctx.set_option(F.OPT_SHUFFLE_P2P, 0)
         init_comm(ctx)
         store = ctx.store().load_quads(mine)
+        paths = set()
 
         def scan(s, p, o):
             return store.plan([rf.traverse(0), rf.scan(s), rf.traverse(p), rf.scan(o)]).execute(allow_view=True)
 
         def shuffle(t, key):
             out = t.shuffle(key)
+            paths.add(ctx.last_shuffle_path)
             k = out.to_numpy()[out.names.index(key)] if out.num_rows else np.zeros(0, np.uint32)
             assert np.all(owner_of_subject(k, world) == rank), "shuffled row landed on the wrong rank"
             return out
@@ -100,6 +109,12 @@ def main():
     results["optional"] = rows(join(shuffle(scan("a", p1, "b"), "b"), scan("b", p2, "c"), F.JOIN_LEFT))
     results["star"] = rows(join(scan("s", p1, "x"), scan("s", p2, "y"), F.JOIN_INNER))
 
+    if mode == "gpu" and world > 1:
+        want_paths = {"p2p": {F.SHUFFLE_P2P}, "nccl": {F.SHUFFLE_NCCL}}.get(exchange)
+        if want_paths is not None:
+            assert paths == want_paths, (exchange, paths)
+        else:  # tiny arena: the big tables overflow it (NCCL), small ones may still fit
+            assert F.SHUFFLE_NCCL in paths, paths
     gathered = [None] * world
     dist.all_gather_object(gathered, {k: (v[0], [np.asarray(c) for c in v[1]]) for k, v in results.items()})
     if rank == 0:
@@ -121,7 +136,7 @@ def main():
             want = orc.canonical_rows(e.cols)
             assert got.shape == want.shape and np.array_equal(got, want), (name, got.shape, want.shape)
             assert len(want) > 0, name
-            print(f"dist {mode} world={world} {name}: {len(want)} rows identical to the single-store oracle", flush=True)
+            print(f"dist {mode}{'/' + exchange if mode == 'gpu' else ''} world={world} {name}: {len(want)} rows identical to the single-store oracle", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 

@@ -252,7 +252,7 @@ def test_partition_groups_rows_by_destination(ctx):
     n = 30000
     cols = {"k": rng.integers(1, 5000, n).astype(np.uint32), "v": np.arange(1, n + 1, dtype=np.uint32)}
     T = ctx.import_table(cols)
-    for parts in (1, 2, 8):
+    for parts in (1, 2, 3, 8):
         P, counts = T.partition("k", parts)
         assert sum(counts) == n
         k, v = P.to_numpy()
