@@ -43,18 +43,30 @@ __global__ void __launch_bounds__(256)
 k_group_insert(const __grid_constant__ GroupArgs A) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  for (; i < A.n; i += stride) {
-    uint32_t h = hash_row(A, i) & A.mask;
-    while (true) {
-      uint32_t cur = A.rep[h];
-      if (cur == 0) {
-        cur = atomicCAS(A.rep + h, 0u, (uint32_t)i + 1);
-        if (cur == 0) break;  // this row is the group's representative
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t n_round = (A.n + 31) & ~31ull;  // whole warps stay together for the aggregation below
+  for (; i < n_round; i += stride) {
+    uint32_t h = 0xFFFFFFFFu;
+    bool counts = false;
+    if (i < A.n) {
+      h = hash_row(A, i) & A.mask;
+      while (true) {
+        uint32_t cur = A.rep[h];
+        if (cur == 0) {
+          cur = atomicCAS(A.rep + h, 0u, (uint32_t)i + 1);
+          if (cur == 0) break;  // this row is the group's representative
+        }
+        if (same_keys(A, i, cur - 1)) break;
+        h = (h + 1) & A.mask;
       }
-      if (same_keys(A, i, cur - 1)) break;
-      h = (h + 1) & A.mask;
+      counts = !A.counted || __ldg(A.counted + i) != 0;
     }
-    if (!A.counted || __ldg(A.counted + i) != 0) atomicAdd(A.cnt + h, 1u);
+    // rows of one warp that landed in the same group add their counts with ONE atomic: with skewed keys (a Zipf head
+    // holds a quarter of the rows) per-row atomicAdds on the same counter serialise in L2
+    __syncwarp();
+    const uint32_t same = __match_any_sync(0xFFFFFFFFu, h);
+    const uint32_t add = __popc(__ballot_sync(0xFFFFFFFFu, counts) & same);
+    if (h != 0xFFFFFFFFu && lane == (uint32_t)__ffs(same) - 1 && add) atomicAdd(A.cnt + h, add);
   }
 }
 

@@ -29,45 +29,24 @@ struct FilterArgs {
   uint64_t n;
 };
 
-__device__ __forceinline__ bool eval_preds(const FilterArgs& A, uint64_t row) {
-  // SQL three-valued logic with 0 = NULL: a comparison involving NULL is not TRUE → row dropped.
-  for (int i = 0; i < A.n_preds; i++) {
-    const DevPred& p = A.preds[i];
-    uint32_t v = __ldg(p.a + row);
-    bool ok;
-    switch (p.op) {
-      case RFGPU_F_EQ_CONST: ok = v != 0 && v == p.value; break;
-      case RFGPU_F_NE_CONST: ok = v != 0 && p.value != 0 && v != p.value; break;
-      case RFGPU_F_EQ_COL: { uint32_t w = __ldg(p.b + row); ok = v != 0 && v == w; break; }
-      case RFGPU_F_NE_COL: { uint32_t w = __ldg(p.b + row); ok = v != 0 && w != 0 && v != w; break; }
-      case RFGPU_F_BETWEEN: ok = v != 0 && v >= p.value && v <= p.hi; break;
-      case RFGPU_F_IN: {
-        ok = false;
-        if (v != 0) {
-          if (p.ids == nullptr) {
+// membership of v (non-NULL) in the conjunct's IN list: up to 8 ids inline, longer lists sorted in global memory
+__device__ __forceinline__ bool in_list(const DevPred& p, uint32_t v) {
+  if (p.ids == nullptr) {
+    bool ok = false;
 #pragma unroll
-            for (int k = 0; k < 8; k++) ok |= (k < (int)p.n_ids) && (p.inl[k] == v);
-          } else {
-            uint32_t lo = 0, hi = p.n_ids;
-            while (lo < hi) {
-              uint32_t mid = (lo + hi) >> 1;
-              uint32_t x = __ldg(p.ids + mid);
-              if (x < v) lo = mid + 1; else hi = mid;
-            }
-            ok = lo < p.n_ids && __ldg(p.ids + lo) == v;
-          }
-        }
-        break;
-      }
-      case RFGPU_F_IS_NULL: ok = v == 0; break;
-      default: ok = v != 0; break;  // RFGPU_F_IS_NOT_NULL
-    }
-    if (!ok) return false;
+    for (int k = 0; k < 8; k++) ok |= (k < (int)p.n_ids) && (p.inl[k] == v);
+    return ok;
   }
-  return true;
+  uint32_t lo = 0, hi = p.n_ids;
+  while (lo < hi) {
+    uint32_t mid = (lo + hi) >> 1;
+    uint32_t x = __ldg(p.ids + mid);
+    if (x < v) lo = mid + 1; else hi = mid;
+  }
+  return lo < p.n_ids && __ldg(p.ids + lo) == v;
 }
 
-__global__ void __launch_bounds__(kFThreads)
+__global__ void __launch_bounds__(kFThreads, 5)
 k_filter_compact(const __grid_constant__ FilterArgs A, unsigned long long* __restrict__ status,
                  unsigned long long* __restrict__ total) {
   __shared__ uint32_t s_stage[kFTile];
@@ -78,13 +57,53 @@ k_filter_compact(const __grid_constant__ FilterArgs A, unsigned long long* __res
   const uint32_t tile = blockIdx.x;
   const uint64_t warp_row0 = (uint64_t)tile * kFTile + (uint64_t)warp * (32 * kFItems);
 
+  // Conjunct by conjunct, the thread's 16 values of the conjunct's column(s) are loaded together (16 independent loads
+  // in flight; evaluating row by row would chain 16 memory round trips behind the ballots).  sel bit k = row k still
+  // passes; a row that failed an earlier conjunct is not loaded again.
+  uint32_t sel = 0;
+#pragma unroll
+  for (int k = 0; k < kFItems; k++)
+    if (warp_row0 + k * 32 + lane < A.n) sel |= 1u << k;
+  // SQL three-valued logic with 0 = NULL: a comparison involving NULL is not TRUE → row dropped.
+#define RF_KEEP_IF(cond)                                   \
+  _Pragma("unroll") for (int k = 0; k < kFItems; k++) {    \
+    const uint32_t x = v[k];                               \
+    if (!(cond)) sel &= ~(1u << k);                        \
+  }
+#define RF_KEEP_IF2(cond)                                                                        \
+  _Pragma("unroll") for (int k = 0; k < kFItems; k++) {                                          \
+    const uint32_t x = v[k];                                                                     \
+    const uint32_t w = (sel >> k) & 1u ? __ldg(p.b + warp_row0 + k * 32 + lane) : 0u;            \
+    if (!(cond)) sel &= ~(1u << k);                                                              \
+  }
+  for (int i = 0; i < A.n_preds; i++) {
+    const DevPred& p = A.preds[i];
+    uint32_t v[kFItems];
+#pragma unroll
+    for (int k = 0; k < kFItems; k++) v[k] = (sel >> k) & 1u ? __ldg(p.a + warp_row0 + k * 32 + lane) : 0u;
+    switch (p.op) {  // uniform across the grid
+      case RFGPU_F_EQ_CONST: RF_KEEP_IF(x != 0 && x == p.value) break;
+      case RFGPU_F_NE_CONST: RF_KEEP_IF(x != 0 && p.value != 0 && x != p.value) break;
+      case RFGPU_F_EQ_COL: RF_KEEP_IF2(x != 0 && x == w) break;
+      case RFGPU_F_NE_COL: RF_KEEP_IF2(x != 0 && w != 0 && x != w) break;
+      case RFGPU_F_BETWEEN: RF_KEEP_IF(x != 0 && x >= p.value && x <= p.hi) break;
+      case RFGPU_F_IN:
+#pragma unroll 1
+        for (int k = 0; k < kFItems; k++)
+          if ((sel >> k) & 1u)  // v[k] indexed dynamically would go to local memory: reload (L1 hit)
+            if (const uint32_t x = __ldg(p.a + warp_row0 + k * 32 + lane); x == 0 || !in_list(p, x)) sel &= ~(1u << k);
+        break;
+      case RFGPU_F_IS_NULL: RF_KEEP_IF(x == 0) break;
+      default: RF_KEEP_IF(x != 0) break;  // RFGPU_F_IS_NOT_NULL
+    }
+  }
+#undef RF_KEEP_IF
+#undef RF_KEEP_IF2
   uint32_t ballots[kFItems];
   uint32_t wcount = 0;
 #pragma unroll
   for (int k = 0; k < kFItems; k++) {
-    uint64_t row = warp_row0 + k * 32 + lane;
-    bool sel = row < A.n && eval_preds(A, row);
-    ballots[k] = __ballot_sync(0xFFFFFFFFu, sel);
+    ballots[k] = __ballot_sync(0xFFFFFFFFu, (sel >> k) & 1u);
     wcount += __popc(ballots[k]);
   }
   if (lane == 0) s_warp[warp] = wcount;
