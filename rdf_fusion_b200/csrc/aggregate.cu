@@ -114,7 +114,7 @@ static rfgpu_table* group_by(rfgpu_ctx* ctx, const rfgpu_table* in, const std::v
   std::vector<BufRef> compact;  // [rep, cnt]
   if (n) {
     uint64_t cap = 1024;
-    while (cap < 2 * n) cap <<= 1;
+    while (3 * cap < 4 * n) cap <<= 1;  // load factor <= 0.75 even if every row is its own group (memset + compaction scale with cap)
     BufRef tab = ctx->alloc(cap * 8);
     RF_CUDA(cudaMemsetAsync(tab->ptr, 0, cap * 8, ctx->stream()));
     GroupArgs A{};
