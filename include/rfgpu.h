@@ -241,7 +241,13 @@ typedef enum {
  * what DataFusion's HashJoinExec / NestedLoopJoinExec / CrossJoinExec would produce. */
 int32_t rfgpu_sparql_join(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_table* rhs,
                           int32_t join_type, rfgpu_table** out);
-/* which lowering the last rfgpu_sparql_join on this ctx took (rfgpu_join_algo) */
+/* SPARQL MINUS: MinusNode + MinusLoweringRule (lib/logical/src/minus/rewrite.rs:58-141) — a LeftAnti
+ * join that removes an lhs row iff some rhs row is compatible with it on every shared variable (equal, or NULL on either
+ * side) AND at least one shared variable is bound on both sides.  No shared variable → the lhs unchanged (:61-64).
+ * Output: the lhs schema, surviving rows in lhs order.  rfgpu_last_join_algo reports EQUI (no shared column nullable),
+ * COMPATIBLE, or CROSS (no shared variable).  Up to 4 shared variables, at most 2 bound on both sides of a class pair. */
+int32_t rfgpu_sparql_minus(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_table* rhs, rfgpu_table** out);
+/* which lowering the last rfgpu_sparql_join / rfgpu_sparql_minus on this ctx took (rfgpu_join_algo) */
 int32_t rfgpu_last_join_algo(const rfgpu_ctx* ctx);
 /* physical operator the last equi (sub-)join used */
 typedef enum {

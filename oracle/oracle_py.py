@@ -303,3 +303,30 @@ def distinct(t: OTable) -> OTable:
         return OTable(t.names, t.nullable, t.cols)
     uniq = np.unique(np.stack(t.cols, axis=1), axis=0)
     return OTable(t.names, t.nullable, [uniq[:, k].astype(np.uint32) for k in range(len(t.names))])
+
+
+def sparql_minus(l: OTable, r: OTable, block: int = 512) -> OTable:
+    """SPARQL MINUS as the reference lowers it (lib/logical/src/minus/rewrite.rs:58-93): a LeftAnti join with no equi keys
+    and the filter  AND_k IS_COMPATIBLE(lhs.k, rhs.k)  AND  OR_k (lhs.k IS NOT NULL AND rhs.k IS NOT NULL)  over the shared
+    variables k (:103-141; IS_COMPATIBLE = either side NULL or equal, lib/functions/src/builtin/query/is_compatible.rs:
+    170-182).  No shared variable -> the lhs unchanged (:61-64).  The output keeps the lhs schema and row order.
+    Evaluated as the definition (nested loop, blocked over lhs rows so numpy does the inner loop)."""
+    shared = [n for n in l.names if n in r.names]
+    n = l.num_rows
+    if not shared or n == 0 or r.num_rows == 0:
+        return OTable(list(l.names), list(l.nullable), [np.asarray(c, np.uint32).copy() for c in l.cols])
+    lk = [np.asarray(l.cols[l.names.index(k)], np.uint32) for k in shared]
+    rk = [np.asarray(r.cols[r.names.index(k)], np.uint32) for k in shared]
+    removed = np.zeros(n, dtype=bool)
+    for lo in range(0, n, block):
+        hi = min(n, lo + block)
+        compat = np.ones((hi - lo, r.num_rows), dtype=bool)
+        both = np.zeros((hi - lo, r.num_rows), dtype=bool)
+        for a, b in zip(lk, rk):
+            x = a[lo:hi, None]
+            y = b[None, :]
+            compat &= (x == 0) | (y == 0) | (x == y)
+            both |= (x != 0) & (y != 0)
+        removed[lo:hi] = (compat & both).any(axis=1)
+    keep = ~removed
+    return OTable(list(l.names), list(l.nullable), [np.asarray(c, np.uint32)[keep] for c in l.cols])

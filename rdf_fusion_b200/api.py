@@ -450,6 +450,13 @@ class Table:
         self.ctx.check(self.ctx.lib.rfgpu_sparql_join(self.ctx.h, self.h, rhs.h, join_type, C.byref(out)))
         return Table(self.ctx, out)
 
+    def minus(self, rhs: "Table") -> "Table":
+        """SPARQL MINUS (MinusNode → LeftAnti join, lib/logical/src/minus/rewrite.rs): lhs rows with no compatible rhs row
+        that shares a bound variable; lhs schema and order."""
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_sparql_minus(self.ctx.h, self.h, rhs.h, C.byref(out)))
+        return Table(self.ctx, out)
+
     def group_count(self, keys: Sequence, counted=None, count_name: str = "count") -> "Table":
         """GROUP BY keys with COUNT(*) (counted=None) or COUNT(counted): AggregateExec on id columns."""
         idx = [self.names.index(k) if isinstance(k, str) else int(k) for k in keys]

@@ -27,6 +27,12 @@ def join_golden():
 
 
 @pytest.fixture(scope="session")
+def minus_golden():
+    with open(os.path.join(GOLDEN, "minus_golden.json")) as f:
+        return json.load(f)
+
+
+@pytest.fixture(scope="session")
 def oracle():
     from oracle import oracle_py
     oracle_py.build()

@@ -138,6 +138,10 @@ class OracleBackend:
         r = self.o.filter_table(self.make(*t), preds)
         return r.names, r.nullable, r.cols
 
+    def minus(self, l, r):
+        t = self.o.sparql_minus(self.make(*l), self.make(*r))
+        return t.names, t.nullable, t.cols
+
 
 class GpuBackend:
     """Drives the CUDA path through the C ABI; intermediates cross the host only for UNION (a host operator)."""
@@ -162,6 +166,9 @@ class GpuBackend:
 
     def filter(self, t, preds):
         return self._out(self.make(*t).filter(preds))
+
+    def minus(self, l, r):
+        return self._out(self.make(*l).minus(self.make(*r)))
 
 
 def _empty(names, nullable):
@@ -195,6 +202,8 @@ def eval_plan(be, node):
     if op in ("join", "leftjoin"):
         l, r = eval_plan(be, node["l"]), eval_plan(be, node["r"])
         return be.join(l, r, F.JOIN_LEFT if op == "leftjoin" else F.JOIN_INNER)
+    if op == "minus":  # MinusNode -> LeftAnti join (minus/rewrite.rs:58-93)
+        return be.minus(eval_plan(be, node["l"]), eval_plan(be, node["r"]))
     if op == "union":
         (ln, lnl, lc), (rn, rnl, rc) = eval_plan(be, node["l"]), eval_plan(be, node["r"])
         names = list(ln) + [n for n in rn if n not in ln]
@@ -211,6 +220,9 @@ def eval_plan(be, node):
         t = eval_plan(be, node["in"])
         preds = []
         for p in node["preds"]:
+            if p["op"] == "in":  # ?v = c1 || ?v = c2 on IRIs: id equality (patterns/rewrite.rs:68-148)
+                preds.append(rf.FPred(F.F_IN, t[0].index(p["var"]), ids=[int(i) for i in p["ids"]]))
+                continue
             code = {"is_null": F.F_IS_NULL, "is_not_null": F.F_IS_NOT_NULL}[p["op"]]
             preds.append(rf.FPred(code, t[0].index(p["var"])))
         return be.filter(t, preds)
