@@ -1,10 +1,4 @@
-"""GPU: SPARQL MINUS (rfgpu_sparql_minus) against the oracle and the W3C negation tests.
-
-This file sorts last on purpose and its tests are non-strict xfail: rfgpu_sparql_minus was written after this round's GPU
-budget was spent.  It only composes kernels the compatible LEFT join already runs (class split, hash probe, entry marking,
-order-preserving compaction), but it has not been executed on a device yet — the round-end test run is its first; an XPASS
-there is the confirmation, after which the marker goes away.
-"""
+"""GPU: SPARQL MINUS (rfgpu_sparql_minus) against the oracle and the W3C SPARQL 1.1 negation tests."""
 import numpy as np
 import pytest
 
@@ -13,7 +7,7 @@ from rdf_fusion_b200 import _ffi as F
 
 from helpers import GpuBackend, check_w3c_case
 
-pytestmark = [pytest.mark.gpu, pytest.mark.xfail(strict=False, reason="first device run of rfgpu_sparql_minus (see module docstring)")]
+pytestmark = pytest.mark.gpu
 
 
 def test_w3c_minus_cases_gpu(ctx, minus_golden):
