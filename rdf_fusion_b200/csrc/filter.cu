@@ -108,28 +108,25 @@ k_filter_compact(const __grid_constant__ FilterArgs A, unsigned long long* __res
   }
   if (lane == 0) s_warp[warp] = wcount;
   __syncthreads();
-  if (warp == 0) {
-    uint32_t v = lane < kFThreads / 32 ? s_warp[lane] : 0;
-    uint32_t incl = v;
+  // every warp scans the 8 warp totals itself, so that only warp 0 waits for the look-back: the others already stage
+  // column 0 meanwhile (with the look-back under a CTA-wide barrier, barrier stalls were the kernel's top stall reason)
+  const uint32_t v = lane < kFThreads / 32 ? s_warp[lane] : 0;
+  uint32_t incl = v;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-      if ((int)lane >= o) incl += t;
-    }
-    uint32_t btotal = __shfl_sync(0xFFFFFFFFu, incl, kFThreads / 32 - 1);
-    if (lane < kFThreads / 32) s_warp[lane] = incl - v;  // exclusive warp offsets
-    if (lane == 0) s_warp[kFThreads / 32] = btotal;
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if ((int)lane >= o) incl += t;
+  }
+  const uint32_t btotal = __shfl_sync(0xFFFFFFFFu, incl, kFThreads / 32 - 1);
+  const uint32_t woff = __shfl_sync(0xFFFFFFFFu, incl - v, warp);  // exclusive offset of this warp in the tile
+  if (warp == 0) {
     unsigned long long excl = dev::lookback_exclusive(status, tile, btotal);
     if (lane == 0) {
       s_base = excl;
       if (tile == gridDim.x - 1) *total = excl + btotal;
     }
   }
-  __syncthreads();
-  const uint32_t woff = s_warp[warp];
-  const uint32_t btotal = s_warp[kFThreads / 32];
-  const unsigned long long base = s_base;
-  if (btotal == 0) return;
+  if (btotal == 0) return;  // uniform over the CTA; warp 0 has published its aggregate above
   const uint32_t lt = (1u << lane) - 1u;
 
   for (int c = 0; c < A.n_cols; c++) {
@@ -141,8 +138,8 @@ k_filter_compact(const __grid_constant__ FilterArgs A, unsigned long long* __res
       if ((b >> lane) & 1u) s_stage[o + __popc(b & lt)] = __ldg(src + warp_row0 + k * 32 + lane);
       o += __popc(b);
     }
-    __syncthreads();
-    uint32_t* __restrict__ dst = A.dst[c] + base;
+    __syncthreads();  // for column 0 this also publishes s_base
+    uint32_t* __restrict__ dst = A.dst[c] + s_base;
     for (uint32_t i = tid; i < btotal; i += kFThreads) dst[i] = s_stage[i];
     __syncthreads();
   }
