@@ -247,6 +247,13 @@ int32_t rfgpu_sparql_join(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_ta
  * Output: the lhs schema, surviving rows in lhs order.  rfgpu_last_join_algo reports EQUI (no shared column nullable),
  * COMPATIBLE, or CROSS (no shared variable).  Up to 4 shared variables, at most 2 bound on both sides of a class pair. */
 int32_t rfgpu_sparql_minus(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_table* rhs, rfgpu_table** out);
+/* FILTER EXISTS { rhs } (negated = 0) / FILTER NOT EXISTS { rhs } (negated = 1) over the solutions `lhs`: the correlated
+ * sub-query of RdfFusionExprBuilderContext::exists / not_exists (lib/logical/src/expr_builder_context.rs:203-338), i.e. the
+ * LeftSemi / LeftAnti join DataFusion decorrelates it into: an lhs row has a partner iff some rhs row is compatible with it
+ * on every shared variable (equal, or NULL on either side) — no "bound on both sides" requirement, unlike MINUS.
+ * Disjoint schemas: every lhs row has a partner iff rhs has a row (:246-262).  Output: lhs schema, lhs order. */
+int32_t rfgpu_sparql_exists(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_table* rhs, int32_t negated,
+                            rfgpu_table** out);
 /* which lowering the last rfgpu_sparql_join / rfgpu_sparql_minus on this ctx took (rfgpu_join_algo) */
 int32_t rfgpu_last_join_algo(const rfgpu_ctx* ctx);
 /* physical operator the last equi (sub-)join used */

@@ -330,3 +330,32 @@ def sparql_minus(l: OTable, r: OTable, block: int = 512) -> OTable:
         removed[lo:hi] = (compat & both).any(axis=1)
     keep = ~removed
     return OTable(list(l.names), list(l.nullable), [np.asarray(c, np.uint32)[keep] for c in l.cols])
+
+
+def sparql_exists(l: OTable, r: OTable, negated: bool = False, block: int = 512) -> OTable:
+    """FILTER EXISTS { r } / FILTER NOT EXISTS { r } over the solutions l, as the reference lowers it
+    (lib/logical/src/expr_builder_context.rs:223-293): a correlated EXISTS sub-query whose filter is, for every variable k
+    the two patterns share, `outer.k = inner.k` when neither side is nullable and IS_COMPATIBLE(outer.k, inner.k) otherwise
+    (:295-338) — i.e. a LeftSemi / LeftAnti join on compatibility, WITHOUT the "some shared variable bound on both sides"
+    condition MINUS has.  Disjoint schemas (:246-262): EXISTS is `count(inner) > 0` for every outer row.
+    The output keeps the lhs schema and row order."""
+    shared = [n for n in l.names if n in r.names]
+    n = l.num_rows
+    if n == 0:
+        return OTable(list(l.names), list(l.nullable), [np.asarray(c, np.uint32).copy() for c in l.cols])
+    if not shared or r.num_rows == 0:
+        found = np.full(n, r.num_rows > 0, dtype=bool)
+    else:
+        lk = [np.asarray(l.cols[l.names.index(k)], np.uint32) for k in shared]
+        rk = [np.asarray(r.cols[r.names.index(k)], np.uint32) for k in shared]
+        found = np.zeros(n, dtype=bool)
+        for lo in range(0, n, block):
+            hi = min(n, lo + block)
+            compat = np.ones((hi - lo, r.num_rows), dtype=bool)
+            for a, b in zip(lk, rk):
+                x = a[lo:hi, None]
+                y = b[None, :]
+                compat &= (x == 0) | (y == 0) | (x == y)
+            found[lo:hi] = compat.any(axis=1)
+    keep = ~found if negated else found
+    return OTable(list(l.names), list(l.nullable), [np.asarray(c, np.uint32)[keep] for c in l.cols])

@@ -118,6 +118,7 @@ SIGNATURES = {
     "rfgpu_distinct": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]),
     "rfgpu_last_join_algo": (C.c_int32, [C.c_void_p]),
     "rfgpu_sparql_minus": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]),
+    "rfgpu_sparql_exists": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]),
     "rfgpu_last_join_phys": (C.c_int32, [C.c_void_p]),
     "rfgpu_ctx_set_option": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int64]),
     "rfgpu_table_sorted_col": (C.c_int32, [C.c_void_p]),

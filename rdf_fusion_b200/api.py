@@ -457,6 +457,13 @@ class Table:
         self.ctx.check(self.ctx.lib.rfgpu_sparql_minus(self.ctx.h, self.h, rhs.h, C.byref(out)))
         return Table(self.ctx, out)
 
+    def exists(self, rhs: "Table", negated: bool = False) -> "Table":
+        """FILTER EXISTS { rhs } / FILTER NOT EXISTS { rhs } (expr_builder_context.rs:203-338): lhs rows with (without) a
+        compatible rhs row; lhs schema and order."""
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_sparql_exists(self.ctx.h, self.h, rhs.h, 1 if negated else 0, C.byref(out)))
+        return Table(self.ctx, out)
+
     def group_count(self, keys: Sequence, counted=None, count_name: str = "count") -> "Table":
         """GROUP BY keys with COUNT(*) (counted=None) or COUNT(counted): AggregateExec on id columns."""
         idx = [self.names.index(k) if isinstance(k, str) else int(k) for k in keys]

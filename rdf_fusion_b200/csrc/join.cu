@@ -687,15 +687,25 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
   return finish(bufs, total + n_un);
 }
 
-// SPARQL MINUS.  The reference lowers MinusNode to a LeftAnti NestedLoopJoin with the filter
+// SPARQL MINUS and FILTER [NOT] EXISTS: semi / anti joins on compatibility.
+//
+// MINUS: the reference lowers MinusNode to a LeftAnti NestedLoopJoin with the filter
 //   AND_k IS_COMPATIBLE(lhs.k, rhs.k)  AND  OR_k (lhs.k IS NOT NULL AND rhs.k IS NOT NULL)      over the shared variables k
-// (lib/logical/src/minus/rewrite.rs:58-141); no shared variable → the lhs unchanged (:61-64).  Here, with the machinery of
-// the compatible LEFT join above: rows are split by the null mask of their shared columns; for every class pair that has
-// at least one variable bound on both sides, the lhs class probes a hash table over the rhs class on exactly those
-// variables (compatibility on the others holds because one side is NULL) and the lhs rows that find a partner are
-// flagged; class pairs with no variable bound on both sides cannot remove anything.  The result is the order-preserving
-// compaction (kernel 2) of the unflagged lhs rows.
-rfgpu_table* sparql_minus(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table* R) {
+// (lib/logical/src/minus/rewrite.rs:58-141); no shared variable → the lhs unchanged (:61-64).
+// EXISTS / NOT EXISTS: a correlated sub-query filtered by `outer.k = inner.k` (neither side nullable) or
+// IS_COMPATIBLE(outer.k, inner.k) per shared variable (lib/logical/src/expr_builder_context.rs:223-338), which DataFusion
+// decorrelates into a LeftSemi / LeftAnti join — the same condition WITHOUT the "bound on both sides" conjunct; disjoint
+// schemas: `count(inner) > 0` for every outer row (:246-262).
+//
+// Here, with the machinery of the compatible LEFT join above: rows are split by the null mask of their shared columns;
+// for every class pair with at least one variable bound on both sides, the lhs class probes a hash table over the rhs
+// class on exactly those variables (compatibility on the others holds because one side is NULL) and the lhs rows that
+// find a partner are flagged.  A class pair with NO variable bound on both sides is compatible row for row: it flags the
+// whole lhs class for EXISTS and nothing for MINUS.  The result is the order-preserving compaction (kernel 2) of the
+// flagged (EXISTS) or unflagged (MINUS, NOT EXISTS) lhs rows.
+enum class SemiMode { kMinus, kExists, kNotExists };
+
+rfgpu_table* semi_anti_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table* R, SemiMode mode) {
   std::vector<std::pair<std::string, KeyPair>> shared;
   for (size_t i = 0; i < L->cols.size(); i++) {
     int j = find_col(R, L->cols[i].name);
@@ -710,16 +720,35 @@ rfgpu_table* sparql_minus(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_tabl
     any_nullable |= L->cols[s.second.l].nullable || R->cols[s.second.r].nullable;
   }
   const size_t nk = lk.size(), nl = L->cols.size();
+  const bool minus = mode == SemiMode::kMinus;
   ctx->last_join_algo = nk == 0 ? RFGPU_JOIN_ALGO_CROSS : (any_nullable ? RFGPU_JOIN_ALGO_COMPATIBLE : RFGPU_JOIN_ALGO_EQUI);
   ctx->last_join_phys = RFGPU_JOIN_PHYS_NONE;
   std::unique_ptr<rfgpu_table> T(new_table());
-  if (nk == 0 || L->rows == 0 || R->rows == 0) {  // nothing can be removed: the lhs columns are shared, not copied
+  auto whole_lhs = [&]() {  // the lhs columns are shared, not copied
     T->cols = L->cols;
     T->rows = L->rows;
     T->sorted_col = L->sorted_col;
     return T.release();
+  };
+  auto no_rows = [&]() {
+    for (size_t i = 0; i < nl; i++) {
+      Column c;
+      c.name = L->cols[i].name;
+      c.nullable = L->cols[i].nullable;
+      c.owner = alloc_col(ctx, 0);
+      c.data = c.owner->as<uint32_t>();
+      T->cols.push_back(std::move(c));
+    }
+    T->sorted_col = L->sorted_col;
+    return T.release();
+  };
+  if (L->rows == 0) return whole_lhs();
+  if (nk == 0 || R->rows == 0) {
+    // MINUS: nothing can be removed.  EXISTS: every lhs row sees the same answer, "the rhs has a row".
+    const bool keep_all = minus || (mode == SemiMode::kExists ? R->rows > 0 : R->rows == 0);
+    return keep_all ? whole_lhs() : no_rows();
   }
-  RF_REQUIRE(nk <= 4, RFGPU_E_UNSUPPORTED, "MINUS on more than 4 shared variables");
+  RF_REQUIRE(nk <= 4, RFGPU_E_UNSUPPORTED, "MINUS / EXISTS on more than 4 shared variables");
   ctx->m.join_probe_rows += L->rows;
   ctx->m.join_build_rows += R->rows;
   ctx->last_join_phys = RFGPU_JOIN_PHYS_HASH;
@@ -729,46 +758,51 @@ rfgpu_table* sparql_minus(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_tabl
     KernelScope ks(ctx, "k_iota");
     k_iota<<<grid_for(ctx, L->rows), 256, 0, ctx->stream()>>>(hidden->as<uint32_t>(), L->rows);
   }
-  auto mark = [&](const ProbeResult& P, const uint32_t* hid) {
-    if (!P.n_entries) return;
+  // flag the lhs rows hid[m_row[q]] (m_row == nullptr: hid[q]) for q < n
+  auto mark = [&](const uint32_t* m_row, uint64_t n, const uint32_t* hid) {
+    if (!n) return;
     KernelScope ks(ctx, "k_mark_entries");
-    k_mark_entries<<<grid_for(ctx, P.n_entries), 256, 0, ctx->stream()>>>(P.m_row->as<uint32_t>(), P.n_entries, hid,
-                                                                          flag->as<uint32_t>());
+    k_mark_entries<<<grid_for(ctx, n), 256, 0, ctx->stream()>>>(m_row, n, hid, flag->as<uint32_t>());
   };
-  if (!any_nullable) {  // one class on each side: a plain anti join on all shared variables
-    RF_REQUIRE(nk <= 2, RFGPU_E_UNSUPPORTED, "MINUS on more than 2 shared non-nullable variables");
+  if (!any_nullable) {  // one class on each side: a plain semi / anti join on all shared variables
+    RF_REQUIRE(nk <= 2, RFGPU_E_UNSUPPORTED, "MINUS / EXISTS on more than 2 shared non-nullable variables");
     ProbeResult P = hash_probe(ctx, (int)nk, R->cols[rk[0]].data, nk > 1 ? R->cols[rk[1]].data : nullptr, R->rows,
                                L->cols[lk[0]].data, nk > 1 ? L->cols[lk[1]].data : nullptr, L->rows, false);
-    mark(P, hidden->as<uint32_t>());
+    if (P.n_entries) mark(P.m_row->as<uint32_t>(), P.n_entries, hidden->as<uint32_t>());
   } else {
     const uint32_t ncls = 1u << nk;
     struct Cls { std::vector<BufRef> cols; uint64_t rows = 0; };
     std::vector<Cls> lc(ncls), rc(ncls);
-    for (uint32_t m = 1; m < ncls; m++) {  // class 0 (no shared variable bound) neither removes nor is removed
+    // class 0 (no shared variable bound) neither removes nor is removed under MINUS; under EXISTS it matches everything
+    for (uint32_t m = minus ? 1 : 0; m < ncls; m++) {
       lc[m].cols = split_class(ctx, L, lk, m, hidden->as<uint32_t>(), &lc[m].rows);
       rc[m].cols = split_class(ctx, R, rk, m, nullptr, &rc[m].rows);
     }
-    for (uint32_t ml = 1; ml < ncls; ml++)
-      for (uint32_t mr = 1; mr < ncls; mr++) {
+    for (uint32_t ml = minus ? 1 : 0; ml < ncls; ml++)
+      for (uint32_t mr = minus ? 1 : 0; mr < ncls; mr++) {
         if (lc[ml].rows == 0 || rc[mr].rows == 0) continue;
         std::vector<size_t> ks;  // variables bound on both sides
         for (size_t k = 0; k < nk; k++)
           if (((ml >> k) & 1) && ((mr >> k) & 1)) ks.push_back(k);
-        if (ks.empty()) continue;
-        RF_REQUIRE(ks.size() <= 2, RFGPU_E_UNSUPPORTED, "MINUS with more than 2 simultaneously bound shared variables");
+        const uint32_t* hid = lc[ml].cols[nl]->as<uint32_t>();
+        if (ks.empty()) {
+          if (!minus) mark(nullptr, lc[ml].rows, hid);  // every row of the lhs class is compatible with the rhs class
+          continue;
+        }
+        RF_REQUIRE(ks.size() <= 2, RFGPU_E_UNSUPPORTED, "MINUS / EXISTS with more than 2 simultaneously bound shared variables");
         auto lcol = [&](size_t i) { return i < ks.size() ? lc[ml].cols[lk[ks[i]]]->as<uint32_t>() : nullptr; };
         auto rcol = [&](size_t i) { return i < ks.size() ? rc[mr].cols[rk[ks[i]]]->as<uint32_t>() : nullptr; };
         ProbeResult P = hash_probe(ctx, (int)ks.size(), rcol(0), rcol(1), rc[mr].rows, lcol(0), lcol(1), lc[ml].rows, false);
-        mark(P, lc[ml].cols[nl]->as<uint32_t>());
+        if (P.n_entries) mark(P.m_row->as<uint32_t>(), P.n_entries, hid);
       }
   }
   DevPred d{};
-  d.op = RFGPU_F_IS_NULL;
+  d.op = mode == SemiMode::kExists ? RFGPU_F_IS_NOT_NULL : RFGPU_F_IS_NULL;
   d.a = flag->as<uint32_t>();
   std::vector<const uint32_t*> src;
   for (auto& c : L->cols) src.push_back(c.data);
   std::vector<BufRef> kept;
-  const uint64_t n = filter_compact(ctx, {d}, src, L->rows, &kept, "k_minus_compact", 4ull * (nl + 1) * L->rows);
+  const uint64_t n = filter_compact(ctx, {d}, src, L->rows, &kept, "k_semi_anti_compact", 4ull * (nl + 1) * L->rows);
   for (size_t i = 0; i < nl; i++) {
     Column c;
     c.name = L->cols[i].name;
@@ -802,7 +836,16 @@ int32_t rfgpu_sparql_minus(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_t
   RF_API_BEGIN
   RF_REQUIRE(ctx && lhs && rhs && out, RFGPU_E_INVALID, "NULL argument");
   RF_CUDA(cudaSetDevice(ctx->core->device));
-  *out = rf::sparql_minus(ctx, lhs, rhs);
+  *out = rf::semi_anti_join(ctx, lhs, rhs, rf::SemiMode::kMinus);
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_sparql_exists(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_table* rhs, int32_t negated,
+                            rfgpu_table** out) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx && lhs && rhs && out, RFGPU_E_INVALID, "NULL argument");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  *out = rf::semi_anti_join(ctx, lhs, rhs, negated ? rf::SemiMode::kNotExists : rf::SemiMode::kExists);
   RF_API_END(ctx)
 }
 

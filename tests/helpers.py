@@ -142,6 +142,10 @@ class OracleBackend:
         t = self.o.sparql_minus(self.make(*l), self.make(*r))
         return t.names, t.nullable, t.cols
 
+    def exists(self, l, r, negated):
+        t = self.o.sparql_exists(self.make(*l), self.make(*r), negated)
+        return t.names, t.nullable, t.cols
+
 
 class GpuBackend:
     """Drives the CUDA path through the C ABI; intermediates cross the host only for UNION (a host operator)."""
@@ -169,6 +173,9 @@ class GpuBackend:
 
     def minus(self, l, r):
         return self._out(self.make(*l).minus(self.make(*r)))
+
+    def exists(self, l, r, negated):
+        return self._out(self.make(*l).exists(self.make(*r), negated))
 
 
 def _empty(names, nullable):
@@ -204,6 +211,8 @@ def eval_plan(be, node):
         return be.join(l, r, F.JOIN_LEFT if op == "leftjoin" else F.JOIN_INNER)
     if op == "minus":  # MinusNode -> LeftAnti join (minus/rewrite.rs:58-93)
         return be.minus(eval_plan(be, node["l"]), eval_plan(be, node["r"]))
+    if op == "exists":  # FILTER [NOT] EXISTS -> semi / anti join on compatibility (expr_builder_context.rs:223-338)
+        return be.exists(eval_plan(be, node["l"]), eval_plan(be, node["r"]), bool(node.get("negated")))
     if op == "union":
         (ln, lnl, lc), (rn, rnl, rc) = eval_plan(be, node["l"]), eval_plan(be, node["r"])
         names = list(ln) + [n for n in rn if n not in ln]

@@ -1,4 +1,5 @@
-"""GPU: SPARQL MINUS (rfgpu_sparql_minus) against the oracle and the W3C SPARQL 1.1 negation tests."""
+"""GPU: SPARQL MINUS and FILTER [NOT] EXISTS (rfgpu_sparql_minus / rfgpu_sparql_exists) against the oracle
+and the W3C SPARQL 1.1 negation tests."""
 import numpy as np
 import pytest
 
@@ -75,3 +76,28 @@ def test_minus_on_scans_keeps_order(ctx, oracle):
     assert np.all(np.diff(gs.astype(np.int64)) >= 0)
     from helpers import canonical
     assert np.array_equal(canonical([gs, go]), canonical(want.cols))
+
+
+@pytest.mark.parametrize("negated", [False, True])
+@pytest.mark.parametrize("shape", [
+    (("a", "k"), (False, False), ("k", "z"), (False, False)),
+    (("k1", "a", "k2"), (False, False, False), ("k2", "z", "k1"), (False, False, False)),
+    (("a", "k"), (False, True), ("k", "z"), (True, False)),
+    (("k1", "a", "k2"), (True, False, True), ("k2", "k1"), (True, True)),
+    (("a", "b"), (False, True), ("c", "d"), (False, False)),
+])
+def test_exists_matches_oracle(ctx, oracle, shape, negated):
+    ln, lnl, rn, rnl = shape
+    rng = np.random.default_rng(34)
+    for nl_, nr_, hi, nf in [(0, 50, 9, 0.3), (70, 0, 9, 0.3), (300, 200, 25, 0.3), (6000, 3000, 400, 0.05),
+                             (20000, 9000, 30000, 0.001)]:
+        lc, lnull = _table(rng, ln, lnl, nl_, hi, nf)
+        rc, rnull = _table(rng, rn, rnl, nr_, hi, nf)
+        got = ctx.import_table(lc, lnull).exists(ctx.import_table(rc, rnull), negated)
+        want = oracle.sparql_exists(oracle.OTable(list(ln), list(lnl), [lc[n] for n in ln]),
+                                    oracle.OTable(list(rn), list(rnl), [rc[n] for n in rn]), negated)
+        assert got.names == list(ln) and got.nullable == list(lnl)
+        assert got.num_rows == want.num_rows, (shape, negated, nl_, nr_)
+        if got.num_rows:
+            for g, w in zip(got.to_numpy(), want.cols):
+                assert np.array_equal(g, w)

@@ -193,7 +193,7 @@ def test_w3c_minus_cases(oracle, minus_golden):
     OPTIONAL-produced unbound variables on both sides of the MINUS: they pin the compatibility + "some shared variable
     bound on both sides" condition of minus/rewrite.rs:103-141."""
     from helpers import OracleBackend, check_w3c_case
-    assert len(minus_golden["cases"]) == 3
+    assert len(minus_golden["cases"]) == 6  # 3 MINUS + 3 FILTER [NOT] EXISTS
     for case in minus_golden["cases"]:
         check_w3c_case(OracleBackend(oracle, case["quads"]), case)
 
@@ -251,3 +251,56 @@ def test_minus_definition_and_edge_cases(oracle):
     r = oracle.OTable(["k"], [True], [np.array([0, 5], np.uint32)])
     out = oracle.sparql_minus(l, r)
     assert list(out.cols[0]) == [1] and list(out.cols[1]) == [0]
+
+
+def test_exists_definition_and_edge_cases(oracle):
+    """FILTER [NOT] EXISTS as a semi / anti join on compatibility (expr_builder_context.rs:223-338) against a
+    row-at-a-time restatement; EXISTS and NOT EXISTS partition the lhs; differs from MINUS exactly on the rows whose only
+    compatible partners share no bound variable with them."""
+    rng = np.random.default_rng(22)
+
+    def table(names, nullable, n, hi, null_frac):
+        cols = []
+        for nl in nullable:
+            c = rng.integers(1, hi + 1, n).astype(np.uint32)
+            if nl:
+                c[rng.random(n) < null_frac] = 0
+            cols.append(c)
+        return oracle.OTable(list(names), list(nullable), cols)
+
+    def by_definition(l, r):
+        shared = [n for n in l.names if n in r.names]
+        found = []
+        for i in range(l.num_rows):
+            hit = False
+            for j in range(r.num_rows):
+                ok = True
+                for k in shared:
+                    a, b = int(l.cols[l.names.index(k)][i]), int(r.cols[r.names.index(k)][j])
+                    ok &= a == 0 or b == 0 or a == b
+                if ok:
+                    hit = True
+                    break
+            found.append(hit)
+        return np.array(found, dtype=bool)
+    shapes = [
+        (("a", "k"), (False, False), ("k", "z"), (False, False)),
+        (("a", "k"), (False, True), ("k", "z"), (True, False)),
+        (("k1", "a", "k2"), (True, False, True), ("k2", "k1"), (True, True)),
+        (("a", "b"), (False, True), ("c", "d"), (False, False)),  # disjoint: EXISTS <=> the rhs has a row
+    ]
+    for ln, lnl, rn, rnl in shapes:
+        for nl_, nr_ in [(0, 5), (7, 0), (60, 40), (200, 150)]:
+            l, r = table(ln, lnl, nl_, 12, 0.3), table(rn, rnl, nr_, 12, 0.3)
+            found = by_definition(l, r) if nl_ else np.zeros(0, bool)
+            ex, nex = oracle.sparql_exists(l, r, False, block=64), oracle.sparql_exists(l, r, True, block=64)
+            for c, e, n in zip(l.cols, ex.cols, nex.cols):
+                assert np.array_equal(e, c[found]) and np.array_equal(n, c[~found])
+            # MINUS removes a subset of what NOT EXISTS removes
+            assert oracle.sparql_minus(l, r).num_rows >= nex.num_rows
+    # an lhs row with every shared variable unbound: EXISTS holds as soon as the rhs has any row, MINUS never removes it
+    l = oracle.OTable(["a", "k"], [False, True], [np.array([1, 2], np.uint32), np.array([0, 5], np.uint32)])
+    r = oracle.OTable(["k"], [True], [np.array([7], np.uint32)])
+    assert list(oracle.sparql_exists(l, r).cols[0]) == [1]
+    assert list(oracle.sparql_exists(l, r, True).cols[0]) == [2]
+    assert oracle.sparql_minus(l, r).num_rows == 2
