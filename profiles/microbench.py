@@ -59,11 +59,26 @@ def main():
     a = sc("s", p1, "o", order="s")
     b = sc("s", p2, "v", order="s")
     na, nb = a.num_rows, b.num_rows
+    res = [None]
+    if os.environ.get("MB_ONLY") == "semi":  # MINUS / EXISTS only
+        def minus():
+            res[0] = a.minus(b)
+            return res[0].num_rows
+        nm = minus()
+        out.append(measure(ctx, "?s p1 ?o MINUS { ?s p2 ?v } (anti join on ?s)", minus, 4 * (2 * na + 2 * nb + 2 * nm)))
+
+        def exists():
+            res[0] = a.exists(b)
+            return res[0].num_rows
+        ne = exists()
+        out.append(measure(ctx, "?s p1 ?o FILTER EXISTS { ?s p2 ?v } (semi join on ?s)", exists, 4 * (2 * na + 2 * nb + 2 * ne)))
+        print(json.dumps({"graph": f"G(N={n}, P=256, zipf 1.2 / 1.2, seed 5)", "hbm_peak_GBps": PEAK,
+                          "sizes": {"a": na, "b": nb, "minus": nm, "exists": ne}, "operators": out}, indent=1))
+        return
 
     # kernel 2 as FilterExec: ?o != c  (1 predicate column, 2 output columns)
     c = int(g.subject_base)
     am = sc("s", p1, "o", view=False)
-    res = [None]
 
     def f_ne():
         res[0] = am.filter([rf.FPred(F.F_NE_CONST, 1, value=c)])
