@@ -292,9 +292,12 @@ __device__ __forceinline__ void p2p_reserve(const P2pArgs& A, P2pSmem& S, int b,
 // in shared memory and written to the arenas column by column (coalesced 128-B peer stores), tile t+1 has already been
 // hashed and ticketed (warp-aggregated) and its runs reserved — ONE system-scope atomicAdd per destination, whose NVLink
 // round trip thus overlaps the writes — and the loads run one step ahead of their use (keys of t+2, next column / first
-// column of t+1).  Without the pipeline the kernel is bound by latency x tiles per CTA (two HBM round trips and one
-// NVLink round trip per tile), not by bandwidth or instruction count (measured, 2 GPUs, 13.3 M rows x 2 columns: 158 us
-// unpipelined; 141 us after removing 40 % of its instructions; 178 us with one reservation per 8192-row chunk).
+// column of t+1).
+// Measured (2 GPUs, 13.3 M rows x 2 columns, 53 MB over the link per rank): 158 us unpipelined at 5 CTAs/SM; 141 us after
+// removing 40 % of the instructions; 178 us with one reservation per 8192-row chunk; 153 us with this pipeline — and 224 us
+// at 4 GPUs for 80 MB.  The time follows the bytes that cross NVLink (~355 GB/s per direction in every variant), not the
+// latency chain, the instruction count or the number of remote atomics: what bounds it is the rate at which 128-B
+// SM-issued peer stores drain into the link (next step there: 16-B aligned runs + bulk stores).
 template <bool kPow2>
 __global__ void __launch_bounds__(kP2pThreads, 3)
 k_shuffle_p2p(const __grid_constant__ P2pArgs A) {
