@@ -33,6 +33,12 @@ def minus_golden():
 
 
 @pytest.fixture(scope="session")
+def agg_golden():
+    with open(os.path.join(GOLDEN, "agg_golden.json")) as f:
+        return json.load(f)
+
+
+@pytest.fixture(scope="session")
 def oracle():
     from oracle import oracle_py
     oracle_py.build()

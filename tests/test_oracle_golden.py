@@ -304,3 +304,13 @@ def test_exists_definition_and_edge_cases(oracle):
     assert list(oracle.sparql_exists(l, r).cols[0]) == [1]
     assert list(oracle.sparql_exists(l, r, True).cols[0]) == [2]
     assert oracle.sparql_minus(l, r).num_rows == 2
+
+
+def test_w3c_distinct_and_count_cases(oracle, agg_golden):
+    """DISTINCT and GROUP BY / COUNT pinned at SPARQL level: W3C sparql10/distinct (DISTINCT is by term:
+    "1", "01", "1.0" stay apart, "abc" = "abc"^^xsd:string; unbound values form a row of their own) and sparql11/aggregates
+    agg02 (COUNT(?O) GROUP BY ?P) / agg05 (COUNT(*) GROUP BY ?P), hand-lowered by tests/golden/make_agg_golden.py."""
+    from helpers import OracleBackend, check_w3c_case
+    assert len(agg_golden["cases"]) == 13
+    for case in agg_golden["cases"]:
+        check_w3c_case(OracleBackend(oracle, case["quads"]), case)
