@@ -39,6 +39,12 @@ def agg_golden():
 
 
 @pytest.fixture(scope="session")
+def pattern_golden():
+    with open(os.path.join(GOLDEN, "pattern_golden.json")) as f:
+        return json.load(f)
+
+
+@pytest.fixture(scope="session")
 def oracle():
     from oracle import oracle_py
     oracle_py.build()

@@ -314,3 +314,12 @@ def test_w3c_distinct_and_count_cases(oracle, agg_golden):
     assert len(agg_golden["cases"]) == 13
     for case in agg_golden["cases"]:
         check_w3c_case(OracleBackend(oracle, case["quads"]), case)
+
+
+def test_w3c_pattern_cases(oracle, pattern_golden):
+    """The scan pinned at SPARQL level: W3C sparql10/triple-match (constants, variables, ?a ?a ?b) and sparql10/graph
+    (default graph vs GRAPH ?g over named graphs, unions and joins of the two), tests/golden/make_pattern_golden.py."""
+    from helpers import OracleBackend, check_w3c_case
+    assert len(pattern_golden["cases"]) == 15
+    for case in pattern_golden["cases"]:
+        check_w3c_case(OracleBackend(oracle, case["quads"]), case)
