@@ -39,6 +39,7 @@ def _opt(q): return G.leftjoin(q.scan(":x1", "?p", "?o"), q.scan("?o", ":q", "?v
 def opt_v(q): return project(_opt(q), ["v"])
 def distinct_opt_v(q): return distinct(_opt(q), ["v"])
 def distinct_star(q): return distinct(G.union(q.scan("?s", ":p", "?o"), q.scan("?s", ":q", "?o")), ["s", "o"])
+def group01(q): return distinct(q.scan("?s", ":p", "?v"), ["s"])  # GROUP BY ?s without an aggregate = DISTINCT ?s
 def agg02(q): return group_count(q.scan("?S", "?P", "?O"), ["P"], "O", "C")
 def agg05(q): return group_count(q.scan("?S", "?P", "?O"), ["P"], None, "C")
 
@@ -56,6 +57,8 @@ CASES = [
     ("distinct/no-distinct-all", [DIS + "data-all.ttl"], EX, all_v, DIS + "no-distinct-all.srx", DIS + "no-distinct-1.rq", []),
     ("distinct/distinct-all", [DIS + "data-all.ttl"], EX, distinct_v, DIS + "distinct-all.srx", DIS + "distinct-1.rq", []),
     ("distinct/distinct-star-1", [DIS + "data-star.ttl"], EX, distinct_star, DIS + "distinct-star-1.srx", DIS + "distinct-star-1.rq", []),
+    ("grouping/group01", ["../sparql11/grouping/group-data-1.ttl"], EX, group01, "../sparql11/grouping/group01.srx",
+     "../sparql11/grouping/group01.rq", []),
     ("aggregates/agg02", [AGG + "agg01.ttl"], EXO, agg02, AGG + "agg02.srx", AGG + "agg02.rq", ["C"]),
     ("aggregates/agg05", [AGG + "agg01.ttl"], EXO, agg05, AGG + "agg05.srx", AGG + "agg05.rq", ["C"]),
 ]

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Generates tests/golden/minus_golden.json from the W3C SPARQL 1.1 negation tests the reference runs
-(testsuite/tests/sparql.rs:36-43, manifest-sparql11-query.ttl -> sparql11/negation): the MINUS and FILTER [NOT] EXISTS cases that need no
+(testsuite/tests/sparql.rs:36-43, manifest-sparql11-query.ttl -> sparql11/negation, sparql11/exists): the MINUS and FILTER [NOT] EXISTS cases that need no
 value-level FILTER.  Same conventions as make_join_golden.py (whose Turtle / result parsers and plan DSL are reused): data dictionary-
 encoded to object ids, the query HAND-LOWERED to the ID-level plan of the reference (MinusNode -> LeftAnti join,
 lib/logical/src/minus/rewrite.rs:58-93; EXISTS -> correlated sub-query -> semi / anti join, expr_builder_context.rs:223-338), expected solutions encoded with the same dictionary (unbound = 0).
@@ -16,6 +16,8 @@ import make_join_golden as G  # noqa: E402
 
 OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "minus_golden.json")
 NEG = "../sparql11/negation/"
+EXI = "../sparql11/exists/"
+EXW = {"ex": "http://www.example.org/", "rdf": G.RDF}
 EX = {"": "http://example/", "rdf": G.RDF}
 EXN = {"ex": "http://www.w3.org/2009/sparql/docs/tests/data-sparql11/negation#", "rdf": G.RDF}
 
@@ -56,6 +58,23 @@ def subset_by_excl_01(q):
     return exists(q.scan("?animal", "a", "ex:Animal"), q.scan("?animal", "a", "ex:Insect"), negated=True)
 
 
+def exists01(q):
+    return exists(q.scan("?s", "?p", "?o"), q.scan("?s", "?p", "ex:o"))
+
+
+def exists03(q):  # both patterns inside GRAPH <exists02.ttl>
+    g = "<exists02.ttl>"
+    return exists(q.scan("?s", "?p", "ex:o1", graph=g), q.scan("?s", "?p", "ex:o2", graph=g))
+
+
+def exists04(q):
+    return exists(q.scan("?s", "?p", "ex:o"), exists(q.scan("?s", "?p", "ex:o1"), q.scan("?s", "?p", "ex:o2")))
+
+
+def exists05(q):
+    return exists(q.scan("?s", "?p", "ex:o"), exists(q.scan("?s", "?p", "ex:o1"), q.scan("?s", "?p", "ex:o2"), negated=True))
+
+
 CASES = [
     ("negation/full-minuend", [NEG + "full-minuend.ttl"], EX, full_minuend, NEG + "full-minuend.srx", NEG + "full-minuend.rq"),
     ("negation/part-minuend", [NEG + "part-minuend.ttl"], EX, part_minuend, NEG + "part-minuend.srx", NEG + "part-minuend.rq"),
@@ -65,17 +84,27 @@ CASES = [
      NEG + "subsetByExcl01.rq"),
     ("negation/exists-01", [NEG + "set-data.ttl"], EX, exists_01, NEG + "exists-01.srx", NEG + "exists-01.rq"),
     ("negation/exists-02", [NEG + "set-data.ttl"], EX, exists_02, NEG + "exists-02.srx", NEG + "exists-02.rq"),
+    # sparql11/exists (exists02 has a variable-free inner pattern: a zero-column table, not expressible here)
+    ("exists/exists01", [EXI + "exists01.ttl"], EXW, exists01, EXI + "exists01.srx", EXI + "exists01.rq"),
+    ("exists/exists03", [EXI + "exists01.ttl"], EXW, exists03, EXI + "exists03.srx", EXI + "exists03.rq", [EXI + "exists02.ttl"]),
+    ("exists/exists04", [EXI + "exists01.ttl"], EXW, exists04, EXI + "exists04.srx", EXI + "exists04.rq"),
+    ("exists/exists05", [EXI + "exists01.ttl"], EXW, exists05, EXI + "exists05.srx", EXI + "exists05.rq"),
 ]
 
 
 def main():
     out = []
-    for name, data, px, plan_fn, result, rq in CASES:
+    for name, data, px, plan_fn, result, rq, *rest in CASES:
+        named = rest[0] if rest else []
         d = G.Dict()
         quads = []
         for k, rel in enumerate(data):
             for s, p, o in G.Turtle(G.read(rel), "d%d_" % k).parse():
                 quads.append([0, d.id(s), d.id(p), d.id(o)])
+        for k, rel in enumerate(named):  # a named graph is called by the relative IRI the queries use
+            gid = d.id("<%s>" % os.path.basename(rel))
+            for s, p, o in G.Turtle(G.read(rel), "g%d_" % k).parse():
+                quads.append([gid, d.id(s), d.id(p), d.id(o)])
         plan = plan_fn(G.Q(d, px))
         vars_, sols = G.srx_solutions(result)
         rows = []
@@ -87,7 +116,7 @@ def main():
                 assert i is not None, (name, v, t)
                 row.append(i)
             rows.append(row)
-        out.append({"name": name, "reference_files": {"query": rq, "data": data, "graph_data": [], "result": result},
+        out.append({"name": name, "reference_files": {"query": rq, "data": data, "graph_data": named, "result": result},
                     "n_terms": len(d.ids), "bnode_ids": [], "quads": quads, "plan": plan, "select": vars_, "expected": rows})
     doc = {"_comment": "Generated by tests/golden/make_minus_golden.py from the W3C SPARQL 1.1 negation tests under "
                        "testsuite/rdf-tests/sparql/sparql11/negation of the reference (run by testsuite/tests/sparql.rs:36-43). "
