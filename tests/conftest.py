@@ -45,6 +45,12 @@ def pattern_golden():
 
 
 @pytest.fixture(scope="session")
+def values_golden():
+    with open(os.path.join(GOLDEN, "values_golden.json")) as f:
+        return json.load(f)
+
+
+@pytest.fixture(scope="session")
 def oracle():
     from oracle import oracle_py
     oracle_py.build()

@@ -227,6 +227,9 @@ def eval_plan(be, node):
         return be.minus(eval_plan(be, node["l"]), eval_plan(be, node["r"]))
     if op == "exists":  # FILTER [NOT] EXISTS -> semi / anti join on compatibility (expr_builder_context.rs:223-338)
         return be.exists(eval_plan(be, node["l"]), eval_plan(be, node["r"]), bool(node.get("negated")))
+    if op == "values":  # VALUES: an inline table, every column nullable by schema (create_values), 0 = UNDEF
+        rows = np.asarray(node["rows"], dtype=np.uint32).reshape(-1, len(node["vars"]))
+        return list(node["vars"]), [True] * len(node["vars"]), [rows[:, i].copy() for i in range(rows.shape[1])]
     if op == "project":
         names, nullable, cols = eval_plan(be, node["in"])
         idx = [names.index(v) for v in node["vars"]]

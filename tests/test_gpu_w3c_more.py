@@ -1,6 +1,7 @@
 """GPU: further W3C evaluation tests through the CUDA path — the same hand-lowered plans the oracle is pinned on in
 test_oracle_golden.py: DISTINCT and GROUP BY / COUNT (tests/golden/agg_golden.json: sparql10/distinct, sparql11/aggregates
-agg02 / agg05) and the quad-pattern scan itself (tests/golden/pattern_golden.json: sparql10/triple-match, sparql10/graph)."""
+agg02 / agg05), the quad-pattern scan itself (tests/golden/pattern_golden.json: sparql10/triple-match, sparql10/graph) and
+the compatible-mapping join on VALUES with UNDEF (tests/golden/values_golden.json: sparql11/bindings)."""
 import pytest
 
 from helpers import GpuBackend, check_w3c_case
@@ -15,4 +16,11 @@ def test_w3c_distinct_and_count_cases_gpu(ctx, agg_golden):
 @pytest.mark.gpu
 def test_w3c_pattern_cases_gpu(ctx, pattern_golden):
     for case in pattern_golden["cases"]:
+        check_w3c_case(GpuBackend(ctx, case["quads"]), case)
+
+
+@pytest.mark.gpu
+def test_w3c_values_cases_gpu(ctx, values_golden):
+    """VALUES with UNDEF: the compatible-mapping join against an all-nullable inline table (tests/golden/values_golden.json)."""
+    for case in values_golden["cases"]:
         check_w3c_case(GpuBackend(ctx, case["quads"]), case)

@@ -323,3 +323,12 @@ def test_w3c_pattern_cases(oracle, pattern_golden):
     assert len(pattern_golden["cases"]) == 15
     for case in pattern_golden["cases"]:
         check_w3c_case(OracleBackend(oracle, case["quads"]), case)
+
+
+def test_w3c_values_cases(oracle, values_golden):
+    """The compatible-mapping join pinned on the W3C VALUES tests (sparql11/bindings): an inline table is all-nullable by
+    schema, UNDEF is an unbound value (tests/golden/make_values_golden.py)."""
+    from helpers import OracleBackend, check_w3c_case
+    assert len(values_golden["cases"]) == 10
+    for case in values_golden["cases"]:
+        check_w3c_case(OracleBackend(oracle, case["quads"]), case)
