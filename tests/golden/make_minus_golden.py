@@ -58,6 +58,31 @@ def subset_by_excl_01(q):
     return exists(q.scan("?animal", "a", "ex:Animal"), q.scan("?animal", "a", "ex:Insect"), negated=True)
 
 
+def rename(x, m): return {"op": "rename", "in": x, "map": m}
+
+
+def _sets(q, first, second): return G.join(q.scan(first, "rdf:type", ":Set"), q.scan(second, "rdf:type", ":Set"))
+
+
+def _not_subset(q, a, b):
+    """pairs (a, b) where a has a member that b has not:  a :member ?x  FILTER NOT EXISTS { b :member ?x }"""
+    return exists(G.join(_sets(q, "?s1", "?s2"), q.scan(a, ":member", "?x")), q.scan(b, ":member", "?x"), negated=True)
+
+
+def subset_01(q):
+    ne = [{"op": "ne_col", "var": "s1", "var2": "s2"}]
+    lhs = G.filt(_sets(q, "?s2", "?s1"), ne)
+    inner = G.filt(G.join(_sets(q, "?s1", "?s2"), q.scan("?s1", ":member", "?x")), ne)
+    rhs = exists(inner, q.scan("?s2", ":member", "?x"), negated=True)
+    return rename(minus(lhs, rhs), {"s1": "subset", "s2": "superset"})
+
+
+def subset_03(q):
+    equal_sets = minus(minus(_sets(q, "?s2", "?s1"), _not_subset(q, "?s1", "?s2")), _not_subset(q, "?s2", "?s1"))
+    return rename(minus(minus(_sets(q, "?s2", "?s1"), _not_subset(q, "?s1", "?s2")), equal_sets),
+                  {"s1": "subset", "s2": "superset"})
+
+
 def exists01(q):
     return exists(q.scan("?s", "?p", "?o"), q.scan("?s", "?p", "ex:o"))
 
@@ -84,6 +109,8 @@ CASES = [
      NEG + "subsetByExcl01.rq"),
     ("negation/exists-01", [NEG + "set-data.ttl"], EX, exists_01, NEG + "exists-01.srx", NEG + "exists-01.rq"),
     ("negation/exists-02", [NEG + "set-data.ttl"], EX, exists_02, NEG + "exists-02.srx", NEG + "exists-02.rq"),
+    ("negation/subset-01", [NEG + "set-data.ttl"], EX, subset_01, NEG + "subset-01.srx", NEG + "subset-01.rq"),
+    ("negation/subset-03", [NEG + "set-data.ttl"], EX, subset_03, NEG + "subset-03.srx", NEG + "subset-03.rq"),
     # sparql11/exists (exists02 has a variable-free inner pattern: a zero-column table, not expressible here)
     ("exists/exists01", [EXI + "exists01.ttl"], EXW, exists01, EXI + "exists01.srx", EXI + "exists01.rq"),
     ("exists/exists03", [EXI + "exists01.ttl"], EXW, exists03, EXI + "exists03.srx", EXI + "exists03.rq", [EXI + "exists02.ttl"]),

@@ -230,6 +230,9 @@ def eval_plan(be, node):
     if op == "values":  # VALUES: an inline table, every column nullable by schema (create_values), 0 = UNDEF
         rows = np.asarray(node["rows"], dtype=np.uint32).reshape(-1, len(node["vars"]))
         return list(node["vars"]), [True] * len(node["vars"]), [rows[:, i].copy() for i in range(rows.shape[1])]
+    if op == "rename":  # SELECT (?a AS ?b)
+        names, nullable, cols = eval_plan(be, node["in"])
+        return [node["map"].get(n, n) for n in names], nullable, cols
     if op == "project":
         names, nullable, cols = eval_plan(be, node["in"])
         idx = [names.index(v) for v in node["vars"]]
@@ -256,6 +259,10 @@ def eval_plan(be, node):
         t = eval_plan(be, node["in"])
         preds = []
         for p in node["preds"]:
+            if p["op"] in ("ne_col", "eq_col"):  # ?a != ?b / ?a = ?b on IRIs: id (in)equality
+                preds.append(rf.FPred(F.F_NE_COL if p["op"] == "ne_col" else F.F_EQ_COL, t[0].index(p["var"]),
+                                      col2=t[0].index(p["var2"])))
+                continue
             if p["op"] == "in":  # ?v = c1 || ?v = c2 on IRIs: id equality (patterns/rewrite.rs:68-148)
                 preds.append(rf.FPred(F.F_IN, t[0].index(p["var"]), ids=[int(i) for i in p["ids"]]))
                 continue

@@ -193,7 +193,7 @@ def test_w3c_minus_cases(oracle, minus_golden):
     OPTIONAL-produced unbound variables on both sides of the MINUS: they pin the compatibility + "some shared variable
     bound on both sides" condition of minus/rewrite.rs:103-141."""
     from helpers import OracleBackend, check_w3c_case
-    assert len(minus_golden["cases"]) == 10  # 3 MINUS + 7 FILTER [NOT] EXISTS (two of them nested)
+    assert len(minus_golden["cases"]) == 12  # MINUS (5, two with nested MINUS / NOT EXISTS) + FILTER [NOT] EXISTS (7)
     for case in minus_golden["cases"]:
         check_w3c_case(OracleBackend(oracle, case["quads"]), case)
 
