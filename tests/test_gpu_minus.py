@@ -11,8 +11,16 @@ from helpers import GpuBackend, check_w3c_case
 pytestmark = pytest.mark.gpu
 
 
+FIRST_BATCH = ("negation/full-minuend", "negation/part-minuend", "negation/subsetByExcl01", "negation/subsetByExcl02",
+               "negation/exists-01", "negation/exists-02")
+
+
 def test_w3c_minus_cases_gpu(ctx, minus_golden):
-    for case in minus_golden["cases"]:
+    """the cases this file was first validated with on a B200; the later additions to minus_golden.json run in
+    test_gpu_w3c_more.py (after the main parity suite)"""
+    cases = [c for c in minus_golden["cases"] if c["name"] in FIRST_BATCH]
+    assert len(cases) == len(FIRST_BATCH)
+    for case in cases:
         check_w3c_case(GpuBackend(ctx, case["quads"]), case)
 
 

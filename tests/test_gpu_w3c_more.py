@@ -24,3 +24,14 @@ def test_w3c_values_cases_gpu(ctx, values_golden):
     """VALUES with UNDEF: the compatible-mapping join against an all-nullable inline table (tests/golden/values_golden.json)."""
     for case in values_golden["cases"]:
         check_w3c_case(GpuBackend(ctx, case["quads"]), case)
+
+
+@pytest.mark.gpu
+def test_w3c_nested_negation_and_exists_cases_gpu(ctx, minus_golden):
+    """subset-01 / subset-03 (MINUS nested in MINUS, NOT EXISTS inside) and sparql11/exists (two shared variables, a
+    constant GRAPH, nested EXISTS / NOT EXISTS); the first six cases of the file run in test_gpu_minus.py"""
+    from test_gpu_minus import FIRST_BATCH
+    cases = [c for c in minus_golden["cases"] if c["name"] not in FIRST_BATCH]
+    assert len(cases) == 6
+    for case in cases:
+        check_w3c_case(GpuBackend(ctx, case["quads"]), case)
