@@ -261,7 +261,9 @@ typedef enum {
   RFGPU_JOIN_PHYS_NONE = 0,
   RFGPU_JOIN_PHYS_HASH = 1,  /* one open-addressing table in HBM */
   RFGPU_JOIN_PHYS_MERGE = 2, /* both inputs sorted on the key */
-  RFGPU_JOIN_PHYS_RADIX = 3  /* radix-partitioned, per-partition tables in shared memory */
+  RFGPU_JOIN_PHYS_RADIX = 3, /* radix-partitioned, per-partition tables in shared memory */
+  RFGPU_JOIN_PHYS_SORT_MERGE = 4 /* unsorted side(s) radix-sorted on the key, then the merge join (RFGPU_OPT_SORT_MERGE_JOIN);
+                                    for MINUS / EXISTS: sorted rhs key list + binary search (RFGPU_OPT_SORT_SEMI) */
 } rfgpu_join_phys;
 int32_t rfgpu_last_join_phys(const rfgpu_ctx* ctx);
 
@@ -275,6 +277,27 @@ int32_t rfgpu_group_count(rfgpu_ctx* ctx, const rfgpu_table* in, const int32_t* 
 /* SELECT DISTINCT over all columns (ReplaceDistinctWithAggregate: a GROUP BY on every column). */
 int32_t rfgpu_distinct(rfgpu_ctx* ctx, const rfgpu_table* in, rfgpu_table** out);
 
+/* physical operator of the last rfgpu_group_count / rfgpu_distinct */
+typedef enum {
+  RFGPU_AGG_PHYS_NONE = 0,
+  RFGPU_AGG_PHYS_HASH = 1, /* representative-row table in HBM */
+  RFGPU_AGG_PHYS_SORT = 2  /* radix sort by the keys + run-length encoding (RFGPU_OPT_SORT_AGG) */
+} rfgpu_agg_phys;
+int32_t rfgpu_last_agg_phys(const rfgpu_ctx* ctx);
+
+/* ---- sorting on ids (sort.cu): the primitive under the index build and the sort-based operators ---- */
+/* Rows of `t` ordered ascending by key_cols (major first; NULL = 0 first), ties in input order (stable LSD radix sort).
+ * The result has sorted_col = key_cols[0], so a following single-key rfgpu_sparql_join on that column streams through
+ * the merge join.  Ordering is by object id, not by term value: this is an execution primitive, not SPARQL ORDER BY. */
+int32_t rfgpu_table_sort(rfgpu_ctx* ctx, const rfgpu_table* t, const int32_t* key_cols, int32_t n_keys, rfgpu_table** out);
+/* Bulk load: builds the permutations `perms` of the quads (quads[0..3] = graph, subject, predicate, object
+ * id columns, any order, duplicates allowed; host pointers, or device pointers when on_device != 0) on the device: per
+ * permutation a stable radix sort from the least significant level up, then de-duplication (the store is a set).
+ * Replaces MemQuadIndex::insert / MemIndexData::insert for every permutation (lib/storage/src/memory/storage/
+ * quad_index.rs:132-156, quad_index_data.rs:287-376, lib/storage/src/index/permutations.rs:102-128). */
+int32_t rfgpu_store_build(rfgpu_ctx* ctx, rfgpu_store* s, const uint32_t* const quads[4], uint64_t n_rows,
+                          int32_t on_device, const uint32_t* perms, int32_t n_perms);
+
 /* ---- options ---- */
 typedef enum {
   RFGPU_OPT_MERGE_JOIN = 1, /* 1 (default): one-key equi joins whose inputs are both sorted on the key run as a
@@ -287,6 +310,12 @@ typedef enum {
   RFGPU_OPT_MERGE_THREADS = 2, /* CTA size of the merge-join kernel: 64, 128 (default) or 256 threads, 8 probe rows each */
   RFGPU_OPT_SHUFFLE_P2P = 6,   /* 1 (default): rfgpu_shuffle partitions straight into the destination ranks' receive arenas
                                   over NVLink peer memory (one fused kernel); 0: partition locally, then ncclSend/ncclRecv */
+  RFGPU_OPT_SORT_MERGE_JOIN = 8, /* 1: a single-key equi join whose inputs are not both sorted on the key sorts the
+                                    unsorted side(s) and runs the merge join instead of the hash join (default 0) */
+  RFGPU_OPT_SORT_SEMI = 9,       /* 1: single-key MINUS / [NOT] EXISTS without nullable shared columns searches a sorted
+                                    list of the rhs keys instead of probing a hash table (default 0) */
+  RFGPU_OPT_SORT_AGG = 10,       /* 1: GROUP BY / COUNT / DISTINCT over at most 4 columns by sort + run-length encoding
+                                    (default 0) */
   RFGPU_OPT_SHUFFLE_ARENA_BYTES = 7 /* size of this rank's receive arena (two halves, used alternately); read by
                                        rfgpu_comm_init, default 1 GiB.  A shuffle whose rows do not fit one half on some
                                        rank falls back to the NCCL exchange on every rank */

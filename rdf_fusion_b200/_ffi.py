@@ -32,7 +32,8 @@ F_EQ_CONST, F_NE_CONST, F_EQ_COL, F_NE_COL, F_BETWEEN, F_IN, F_IS_NULL, F_IS_NOT
 JOIN_INNER, JOIN_LEFT = 0, 1
 ALGO_CROSS, ALGO_EQUI, ALGO_COMPATIBLE = 0, 1, 2
 SCAN_ALLOW_VIEW = 1
-PHYS_NONE, PHYS_HASH, PHYS_MERGE, PHYS_RADIX = 0, 1, 2, 3
+PHYS_NONE, PHYS_HASH, PHYS_MERGE, PHYS_RADIX, PHYS_SORT_MERGE = 0, 1, 2, 3, 4
+AGG_PHYS_NONE, AGG_PHYS_HASH, AGG_PHYS_SORT = 0, 1, 2
 OPT_MERGE_JOIN = 1
 OPT_MERGE_THREADS = 2
 OPT_RADIX_JOIN = 3
@@ -40,6 +41,9 @@ OPT_RADIX_MIN_ROWS = 4
 OPT_HASH_L2_BYTES = 5
 OPT_SHUFFLE_P2P = 6
 OPT_SHUFFLE_ARENA_BYTES = 7
+OPT_SORT_MERGE_JOIN = 8
+OPT_SORT_SEMI = 9
+OPT_SORT_AGG = 10
 SHUFFLE_LOCAL, SHUFFLE_NCCL, SHUFFLE_P2P = 0, 1, 2
 UNIQUE_ID_BYTES = 128
 
@@ -140,6 +144,10 @@ SIGNATURES = {
     "rfgpu_timer_start": (C.c_int32, [C.c_void_p]),
     "rfgpu_timer_stop": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
     "rfgpu_flush_l2": (C.c_int32, [C.c_void_p]),
+    "rfgpu_last_agg_phys": (C.c_int32, [C.c_void_p]),
+    "rfgpu_table_sort": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_void_p)]),
+    "rfgpu_store_build": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.c_uint64, C.c_int32, u32p,
+                                      C.c_int32]),
 }
 
 _lib = None

@@ -280,6 +280,23 @@ class Store:
             self.add_index(p, [c[order] for c in cols])
         return self
 
+    def build(self, quads, perms=(F.GSPO, F.GPOS, F.GOSP), on_device: bool = False):
+        """Bulk load on the device (rfgpu_store_build): `quads` is an (n,4) array of g,s,p,o ids in any order,
+        duplicates allowed — or, with on_device, ((g_ptr, s_ptr, p_ptr, o_ptr), n) device pointers.  Every permutation is
+        radix-sorted and de-duplicated by the library; nothing is sorted on the host."""
+        if on_device:
+            ptrs, n = quads
+            arr = (C.c_void_p * 4)(*ptrs)
+            keep = None
+        else:
+            q = np.ascontiguousarray(quads, dtype=np.uint32).reshape(-1, 4)
+            keep = [np.ascontiguousarray(q[:, c]) for c in range(4)]
+            n = len(q)
+            arr = (C.c_void_p * 4)(*[x.ctypes.data for x in keep])
+        pa_ = (C.c_uint32 * len(perms))(*perms)
+        self.ctx.check(self.ctx.lib.rfgpu_store_build(self.ctx.h, self.h, arr, n, 1 if on_device else 0, pa_, len(perms)))
+        return self
+
     @property
     def perms(self) -> List[int]:
         return [int(self.ctx.lib.rfgpu_store_index_perm(self.h, i))
@@ -509,6 +526,18 @@ class Table:
     @property
     def last_join_phys(self) -> int:
         return int(self.ctx.lib.rfgpu_last_join_phys(self.ctx.h))
+
+    @property
+    def last_agg_phys(self) -> int:
+        return int(self.ctx.lib.rfgpu_last_agg_phys(self.ctx.h))
+
+    def sort(self, keys: Sequence) -> "Table":
+        """Rows ascending by the id columns `keys` (major first), ties in input order (rfgpu_table_sort)."""
+        idx = [self.names.index(k) if isinstance(k, str) else int(k) for k in keys]
+        ci = (C.c_int32 * max(1, len(idx)))(*idx)
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_table_sort(self.ctx.h, self.h, ci, len(idx), C.byref(out)))
+        return Table(self.ctx, out)
 
     @property
     def sorted_col(self) -> int:

@@ -514,6 +514,17 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
       if (k >= keys.size()) return nullptr;
       return t->cols[t == L ? keys[k].l : keys[k].r].data;
     };
+    // opt-in: a side that is not sorted on the single key is radix-sorted on it (all its columns ride along), then the
+    // streaming merge join runs; no hash table, no random HBM sectors
+    if (ctx->opt_sort_merge_join && ctx->opt_merge_join && keys.size() == 1 && L->rows > 0 && R->rows > 0 &&
+        !(L->sorted_col == keys[0].l && R->sorted_col == keys[0].r)) {
+      std::unique_ptr<rfgpu_table> Ls, Rs;
+      if (L->sorted_col != keys[0].l) Ls.reset(sort_table(ctx, L, {keys[0].l}));
+      if (R->sorted_col != keys[0].r) Rs.reset(sort_table(ctx, R, {keys[0].r}));
+      rfgpu_table* out = sparql_join(ctx, Ls ? Ls.get() : L, Rs ? Rs.get() : R, join_type);
+      ctx->last_join_phys = RFGPU_JOIN_PHYS_SORT_MERGE;
+      return out;
+    }
     ctx->m.join_probe_rows += Pt->rows;
     ctx->m.join_build_rows += Bt->rows;
     std::vector<OutColSpec> specs;
@@ -764,7 +775,18 @@ rfgpu_table* semi_anti_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_ta
     KernelScope ks(ctx, "k_mark_entries");
     k_mark_entries<<<grid_for(ctx, n), 256, 0, ctx->stream()>>>(m_row, n, hid, flag->as<uint32_t>());
   };
-  if (!any_nullable) {  // one class on each side: a plain semi / anti join on all shared variables
+  if (!any_nullable && nk == 1 && ctx->opt_sort_semi) {
+    // existence only: the rhs keys as one ascending list (the column itself when the rhs is sorted on it), and a
+    // lower-bound search per lhs row; no table, no row lists
+    ctx->last_join_phys = RFGPU_JOIN_PHYS_SORT_MERGE;
+    const uint32_t* list = R->cols[rk[0]].data;
+    std::vector<BufRef> sorted;
+    if (R->sorted_col != rk[0]) {
+      sorted = sort_rows_lex(ctx, {list}, {0}, R->rows);
+      list = sorted[0]->as<uint32_t>();
+    }
+    sorted_contains(ctx, list, R->rows, L->cols[lk[0]].data, L->rows, flag->as<uint32_t>());
+  } else if (!any_nullable) {  // one class on each side: a plain semi / anti join on all shared variables
     RF_REQUIRE(nk <= 2, RFGPU_E_UNSUPPORTED, "MINUS / EXISTS on more than 2 shared non-nullable variables");
     ProbeResult P = hash_probe(ctx, (int)nk, R->cols[rk[0]].data, nk > 1 ? R->cols[rk[1]].data : nullptr, R->rows,
                                L->cols[lk[0]].data, nk > 1 ? L->cols[lk[1]].data : nullptr, L->rows, false);
@@ -857,6 +879,9 @@ int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value) {
   RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
   switch (option) {
     case RFGPU_OPT_MERGE_JOIN: ctx->opt_merge_join = value != 0; break;
+    case RFGPU_OPT_SORT_MERGE_JOIN: ctx->opt_sort_merge_join = value != 0; break;
+    case RFGPU_OPT_SORT_SEMI: ctx->opt_sort_semi = value != 0; break;
+    case RFGPU_OPT_SORT_AGG: ctx->opt_sort_agg = value != 0; break;
     case RFGPU_OPT_RADIX_JOIN: ctx->opt_radix_join = value != 0; break;
     case RFGPU_OPT_RADIX_MIN_ROWS:
       RF_REQUIRE(value >= 1, RFGPU_E_INVALID, "radix-join threshold must be >= 1 build row");

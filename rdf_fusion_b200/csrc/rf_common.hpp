@@ -106,6 +106,11 @@ struct rfgpu_ctx {
   int opt_merge_threads = 128;  // CTA size of k_merge_join (tile = 8 rows per thread)
   bool opt_shuffle_p2p = true;  // rfgpu_shuffle: fused partition + peer-memory scatter when the IPC arenas are mapped
   int64_t opt_shuffle_arena_bytes = 1ll << 30;  // receive arena of this rank (read by rfgpu_comm_init)
+  // sort-based operators (sort.cu); opt-in until measured on a device
+  bool opt_sort_merge_join = false;  // unsorted single-key equi joins: radix-sort the unsorted side(s), then k_merge_join
+  bool opt_sort_semi = false;        // single-key MINUS / EXISTS: sorted rhs key list + one binary search per lhs row
+  bool opt_sort_agg = false;         // GROUP BY / COUNT / DISTINCT over at most 4 columns: sort + run-length encoding
+  int last_agg_phys = 0;             // rfgpu_agg_phys of the last rfgpu_group_count / rfgpu_distinct
   int last_shuffle_path = 0;
   uint64_t last_from = 0, last_to = 0;
   // pinned host scratch for small device→host results (ranges, counts)
@@ -152,6 +157,15 @@ int find_col(const rfgpu_table* t, const std::string& name);
 
 // device-wide exclusive scan of u32 → u32 (total returned via pinned scratch slot); scan.cu
 void exclusive_scan_u32(rfgpu_ctx* ctx, const uint32_t* in, uint32_t* out, uint64_t n, uint64_t* h_total_slot);
+
+// sort.cu — stable LSD radix sort of id columns and the run-length encoding of sorted rows
+std::vector<BufRef> sort_rows_lex(rfgpu_ctx* ctx, const std::vector<const uint32_t*>& cols, const std::vector<int>& key_order,
+                                  uint64_t n);
+rfgpu_table* sort_table(rfgpu_ctx* ctx, const rfgpu_table* t, const std::vector<int>& key_cols);
+uint64_t encode_runs(rfgpu_ctx* ctx, const std::vector<const uint32_t*>& cols, int n_keys, uint64_t n,
+                     std::vector<BufRef>* out, BufRef* cnt, const uint32_t* counted);
+// flag[i] = 1 where probe[i] occurs in the ascending list sorted[0..ns) (flag is left alone elsewhere)
+void sorted_contains(rfgpu_ctx* ctx, const uint32_t* sorted, uint64_t ns, const uint32_t* probe, uint64_t np, uint32_t* flag);
 
 // filter.cu — generic predicate program over column pointers
 struct DevPred {

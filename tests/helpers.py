@@ -158,9 +158,11 @@ class OracleBackend:
 class GpuBackend:
     """Drives the CUDA path through the C ABI; intermediates cross the host only for UNION (a host operator)."""
 
-    def __init__(self, ctx, quads):
+    def __init__(self, ctx, quads, device_build=False):
         self.ctx = ctx
-        self.store = ctx.store().load_quads(np.asarray(quads, dtype=np.uint32).reshape(-1, 4))
+        q = np.asarray(quads, dtype=np.uint32).reshape(-1, 4)
+        # device_build: the permutations are sorted and de-duplicated by rfgpu_store_build, not on the host
+        self.store = ctx.store().build(q) if device_build else ctx.store().load_quads(q)
 
     def _out(self, t):
         n = len(t.names)
