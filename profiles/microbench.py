@@ -76,6 +76,70 @@ def main():
                           "sizes": {"a": na, "b": nb, "minus": nm, "exists": ne}, "operators": out}, indent=1))
         return
 
+    if os.environ.get("MB_ONLY") == "sort":  # the sort-based paths of sort.cu against what they replace
+        import numpy as np
+        import time
+        # index build on the device: 3 permutations from the unsorted host columns, H2D included
+        t0 = time.time()
+        built = ctx.store().build(np.stack([g.g, g.s, g.p, g.o], axis=1), (F.GSPO, F.GPOS, F.GOSP))
+        ctx.synchronize()
+        build_s = time.time() - t0
+        ctx.metrics_reset()
+        ctx.profile_enable(True)
+        ctx.store().build(np.stack([g.g, g.s, g.p, g.o], axis=1), (F.GSPO, F.GPOS, F.GOSP))
+        prof = ctx.profile()
+        ctx.profile_enable(False)
+        out.append({"operator": "rfgpu_store_build, 3 permutations", "rows_in": n, "rows_out": len(built),
+                    "wall_s_incl_h2d": round(build_s, 3),
+                    "kernels": {k: {"launches": v["launches"], "us": round(1e3 * v["ms"], 1)} for k, v in prof.items() if v["ms"] > 0}})
+        # unsorted inputs: the same two scans in ?o order (GPOS), joined on ?s
+        au, bu = sc("s", p1, "o", view=False), sc("s", p2, "v", view=False)
+        assert au.sorted_col != 0 and bu.sorted_col != 0
+
+        def j_hash():
+            res[0] = au.join(bu, F.JOIN_LEFT)
+            return res[0].num_rows
+        no = j_hash()
+        out.append(measure(ctx, "OPTIONAL left join, unsorted inputs, one-table hash", j_hash, 4 * (2 * na + 2 * nb + 3 * no)))
+        ctx.set_option(F.OPT_SORT_MERGE_JOIN, 1)
+        assert j_hash() == no and res[0].last_join_phys == F.PHYS_SORT_MERGE
+        out.append(measure(ctx, "OPTIONAL left join, unsorted inputs, radix sort + merge", j_hash, 4 * (2 * na + 2 * nb + 3 * no)))
+        ctx.set_option(F.OPT_SORT_MERGE_JOIN, 0)
+
+        def srt():
+            res[0] = au.sort(["s"])
+            return res[0].num_rows
+        out.append(measure(ctx, "rfgpu_table_sort (2 columns by ?s)", srt, 4 * 4 * na))
+        for flag, tag in ((0, "hash"), (1, "sorted list")):
+            ctx.set_option(F.OPT_SORT_SEMI, flag)
+
+            def minus():
+                res[0] = au.minus(bu)
+                return res[0].num_rows
+            nm = minus()
+            out.append(measure(ctx, f"MINUS on ?s, unsorted inputs, {tag}", minus, 4 * (2 * na + 2 * nb + 2 * nm)))
+        ctx.set_option(F.OPT_SORT_SEMI, 0)
+        opt = a.join(b, F.JOIN_LEFT)
+        ov = opt.project(["o", "v"])
+        for flag, tag in ((0, "hash"), (1, "sort + run lengths")):
+            ctx.set_option(F.OPT_SORT_AGG, flag)
+
+            def grp():
+                res[0] = opt.group_count(["o"], None, "n")
+                return res[0].num_rows
+            ng = grp()
+            out.append(measure(ctx, f"GROUP BY ?o COUNT(*), {tag}", grp, 4 * (opt.num_rows + 2 * ng)))
+
+            def dist():
+                res[0] = ov.distinct()
+                return res[0].num_rows
+            nd = dist()
+            out.append(measure(ctx, f"DISTINCT ?o ?v, {tag}", dist, 4 * (2 * opt.num_rows + 2 * nd)))
+        ctx.set_option(F.OPT_SORT_AGG, 0)
+        print(json.dumps({"graph": f"G(N={n}, P=256, zipf 1.2 / 1.2, seed 5)", "hbm_peak_GBps": PEAK,
+                          "sizes": {"a": na, "b": nb, "optional": opt.num_rows}, "operators": out}, indent=1))
+        return
+
     # kernel 2 as FilterExec: ?o != c  (1 predicate column, 2 output columns)
     c = int(g.subject_base)
     am = sc("s", p1, "o", view=False)
