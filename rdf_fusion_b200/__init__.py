@@ -9,4 +9,4 @@ from ._ffi import (ALGO_COMPATIBLE, ALGO_CROSS, ALGO_EQUI, F_BETWEEN, F_EQ_COL, 
                    JOIN_LEFT, OP_EQ, OP_GT, OP_GTEQ, OP_LT, OP_LTEQ, PERM_NAMES)
 from .api import (FALSE, Between, Context, EqualTo, FPred, In, Instr, Pred, RfgpuError, ScanPlan, Store,  # noqa: F401
                   Table, execute_many, make_filter_preds, make_instructions, scan, traverse)
-from .synth import SynthGraph, generate_graph  # noqa: F401
+from .synth import BsbmLikeGraph, SynthGraph, generate_bsbm_like, generate_graph  # noqa: F401

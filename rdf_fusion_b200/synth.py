@@ -99,3 +99,63 @@ def generate_graph(n: int, n_predicates: int = 1024, s: float = 1.0, seed: int =
                 named = _unit(gu) < named_graph_frac
                 g[lo:hi] = np.where(named, 1 + (gu % np.uint64(16)).astype(np.int64), 0).astype(np.uint32)
     return SynthGraph(n, P, S, L, g, sub, pred, obj)
+
+
+# ---------------------------------------------------------------- BSBM-shaped graph in id space
+@dataclass
+class BsbmLikeGraph:
+    """Quads with the vocabulary and fan-outs of the BSBM e-commerce graph, generated directly as object ids (BASELINE
+    configs[0] / [2] need the Java bsbm-tools generator, which this box does not have; SURVEY §8d substitutes an id-space
+    graph that reproduces the join trees of the reference's plan snapshots, bench/tests/plans/snapshots/)."""
+    quads: np.ndarray
+    vocab: dict
+
+    def __getattr__(self, k):
+        try:
+            return self.vocab[k]
+        except KeyError:
+            raise AttributeError(k)
+
+
+def generate_bsbm_like(n_products: int = 300, seed: int = 7) -> BsbmLikeGraph:
+    """Per product: 1–2 types, a producer, a label, 3–6 features, two numeric properties, ~10 reviews; producers and
+    reviewers live in one of 10 countries.  Numeric literal ids ascend with their value, so `?p1 > c` on ENC_TV is an id
+    range here (the reference decodes; §8f-2)."""
+    v = dict(rdf_type=1, producer=2, country=3, review_for=4, reviewer=5, label=6, feature=7, num1=8, num3=9,
+             product_type_class=20, country_base=30, n_countries=10, type_base=100, feature_base=300,
+             producer_base=1000, product_base=10000, reviewer_base=100000, review_base=200000,
+             label_base=2000000, numeric_base=3000000)
+    n_types = max(4, n_products // 75)
+    n_features = max(10, n_products // 30)
+    n_producers = max(3, n_products // 20)
+    n_reviews = 10 * n_products
+    n_reviewers = max(5, n_reviews // 8)
+    v.update(n_types=n_types, n_features=n_features, n_producers=n_producers, n_reviews=n_reviews,
+             n_reviewers=n_reviewers, n_products=n_products)
+
+    def u(stream, rows, mod):
+        return (_draw(seed, stream, np.arange(rows, dtype=np.uint64)) % np.uint64(mod)).astype(np.int64)
+    q = []
+
+    def add(s, p, o):
+        s, o = np.asarray(s, np.int64), np.asarray(o, np.int64)
+        s, o = np.broadcast_arrays(s, o)
+        q.append(np.stack([np.zeros(len(s), np.int64), s, np.full(len(s), p, np.int64), o], axis=1))
+    products = v["product_base"] + np.arange(n_products)
+    add(v["type_base"] + np.arange(n_types), v["rdf_type"], v["product_type_class"])
+    add(products, v["rdf_type"], v["type_base"] + u(1, n_products, n_types))
+    second = u(2, n_products, 2) == 0
+    add(products[second], v["rdf_type"], v["type_base"] + u(3, n_products, n_types)[second])
+    add(products, v["producer"], v["producer_base"] + u(4, n_products, n_producers))
+    add(v["producer_base"] + np.arange(n_producers), v["country"], v["country_base"] + u(5, n_producers, v["n_countries"]))
+    add(products, v["label"], v["label_base"] + np.arange(n_products))
+    for k in range(6):
+        keep = (u(10 + k, n_products, 6) >= k - 2)  # 3 always, then thinning
+        add(products[keep], v["feature"], v["feature_base"] + u(20 + k, n_products, n_features)[keep])
+    add(products, v["num1"], v["numeric_base"] + u(30, n_products, 2000))
+    add(products, v["num3"], v["numeric_base"] + u(31, n_products, 2000))
+    reviews = v["review_base"] + np.arange(n_reviews)
+    add(reviews, v["review_for"], v["product_base"] + u(40, n_reviews, n_products))
+    add(reviews, v["reviewer"], v["reviewer_base"] + u(41, n_reviews, n_reviewers))
+    add(v["reviewer_base"] + np.arange(n_reviewers), v["country"], v["country_base"] + u(42, n_reviewers, v["n_countries"]))
+    return BsbmLikeGraph(np.concatenate(q).astype(np.uint32), v)

@@ -265,6 +265,9 @@ def eval_plan(be, node):
                 preds.append(rf.FPred(F.F_NE_COL if p["op"] == "ne_col" else F.F_EQ_COL, t[0].index(p["var"]),
                                       col2=t[0].index(p["var2"])))
                 continue
+            if p["op"] == "between":  # id range (a value range when the ids ascend with the value, as in generate_bsbm_like)
+                preds.append(rf.FPred(F.F_BETWEEN, t[0].index(p["var"]), value=int(p["lo"]), hi=int(p["hi"])))
+                continue
             if p["op"] == "in":  # ?v = c1 || ?v = c2 on IRIs: id equality (patterns/rewrite.rs:68-148)
                 preds.append(rf.FPred(F.F_IN, t[0].index(p["var"]), ids=[int(i) for i in p["ids"]]))
                 continue
@@ -294,3 +297,126 @@ def check_w3c_case(be, case):
     got = sorted(map(tuple, np.stack(sel, axis=1).tolist())) if n else []
     exp = sorted(map(tuple, case["expected"]))
     assert got == exp, (case["name"], got, exp)
+
+
+# ---------------------------------------------------------------- plan shapes of BASELINE configs[0] / [2] / [3]
+def _tp(s, p, o):
+    """triple pattern in the default graph; str = variable, int = constant id"""
+    def c(x):
+        return {"var": x} if isinstance(x, str) else {"id": int(x)}
+    return {"op": "scan", "g": "default", "s": c(s), "p": c(p), "o": c(o)}
+
+
+def _join_all(parts, op="join"):
+    node = parts[0]
+    for nxt in parts[1:]:
+        node = {"op": op, "l": node, "r": nxt}
+    return node
+
+
+def bsbm_bi_q1_plan(v, country_a, country_b):
+    """BSBM Business Intelligence Q1 as the reference executes it (bench/tests/plans/snapshots/
+    "…Business Intelligence - Q1 (Execution Plan).snap"): 7 quad patterns, a left-deep tree of 6 single-key inner joins
+    (productType, product, producer, product, review, reviewer), then GROUP BY ?productType COUNT(?review)."""
+    parts = [_tp("productType", v["rdf_type"], v["product_type_class"]),
+             _tp("product", v["rdf_type"], "productType"),
+             _tp("product", v["producer"], "producer"),
+             _tp("producer", v["country"], country_a),
+             _tp("review", v["review_for"], "product"),
+             _tp("review", v["reviewer"], "reviewer"),
+             _tp("reviewer", v["country"], country_b)]
+    return {"op": "group_count", "in": _join_all(parts), "keys": ["productType"], "counted": "review", "name": "reviewCount"}
+
+
+def bsbm_explore_q3_plan(v, ptype, feature1, feature2, lo1, hi3):
+    """BSBM Explore Q3 ("…Explore - Q3 (Execution Plan).snap"): 5 inner joins on ?product (two of the inputs filtered on a
+    numeric property: an id range here, see generate_bsbm_like), a Left join with the OPTIONAL block (feature2 ⋈ label AS
+    ?testVar), FILTER(!BOUND(?testVar)), projection to (?product, ?label)."""
+    num = v["numeric_base"]
+    p1 = {"op": "project", "vars": ["product"], "in": {"op": "filter", "in": _tp("product", v["num1"], "p1"),
+          "preds": [{"op": "between", "var": "p1", "lo": num + lo1 + 1, "hi": 0xFFFFFFFF}]}}
+    p3 = {"op": "project", "vars": ["product"], "in": {"op": "filter", "in": _tp("product", v["num3"], "p3"),
+          "preds": [{"op": "between", "var": "p3", "lo": 0, "hi": num + hi3 - 1}]}}
+    lhs = _join_all([_tp("product", v["label"], "label"), _tp("product", v["rdf_type"], ptype),
+                     _tp("product", v["feature"], feature1), p1, p3])
+    rhs = _join_all([_tp("product", v["feature"], feature2), _tp("product", v["label"], "testVar")])
+    return {"op": "project", "vars": ["product", "label"],
+            "in": {"op": "filter", "preds": [{"op": "is_null", "var": "testVar"}],
+                   "in": {"op": "leftjoin", "l": lhs, "r": rhs}}}
+
+
+def chain5_plan(p):
+    """BASELINE configs[3]: ?a p1 ?b . ?b p2 ?c . ?c p3 ?d . ?d p4 ?e . ?e p5 ?f (SURVEY §8d cfg 4)"""
+    names = "abcdef"
+    return _join_all([_tp(names[i], p[i], names[i + 1]) for i in range(5)])
+
+
+def snowflake5_plan(p):
+    """BASELINE configs[3]: ?x p1 ?a . ?x p2 ?b . ?a p3 ?c . ?b p4 ?d . ?c p5 ?e (SURVEY §8d cfg 4)"""
+    return _join_all([_tp("x", p[0], "a"), _tp("x", p[1], "b"), _tp("a", p[2], "c"), _tp("b", p[3], "d"), _tp("c", p[4], "e")])
+
+
+class PandasBackend:
+    """A third, independent evaluator for plans without unbound join keys: numpy masks for the scans, pandas.merge for the
+    joins.  Used on the CPU to cross-check the oracle on multi-way plans (it shares no code with oracle/)."""
+
+    def __init__(self, quads):
+        self.q = np.unique(np.asarray(quads, dtype=np.uint32).reshape(-1, 4), axis=0)
+
+    def scan(self, instr):
+        keep = np.ones(len(self.q), dtype=bool)
+        names, cols = [], []
+        for k, ins in enumerate(instr):
+            c = self.q[:, k]
+            p = ins.pred
+            if p is not None and p.kind == F.PRED_IN:
+                keep &= np.isin(c, np.asarray(p.ids, dtype=np.uint32))
+            elif p is not None and p.kind == F.PRED_BETWEEN:
+                keep &= (c >= p.lo) & (c <= p.hi)
+            elif p is not None and p.kind != F.PRED_NONE:
+                raise ValueError(p)
+            if ins.action == F.SCAN:
+                if ins.var in names:
+                    keep &= c == cols[names.index(ins.var)]
+                else:
+                    names.append(ins.var)
+                    cols.append(c)
+        return names, [False] * len(names), [c[keep] for c in cols]
+
+    def _df(self, t):
+        import pandas as pd
+        return pd.DataFrame({n: c.astype(np.int64) for n, c in zip(t[0], t[2])})
+
+    def _out(self, df, nullable):
+        return list(df.columns), nullable, [df[c].to_numpy().astype(np.uint32) for c in df.columns]
+
+    def join(self, l, r, jt):
+        shared = [n for n in l[0] if n in r[0]]
+        assert shared and not any(l[1][l[0].index(n)] or r[1][r[0].index(n)] for n in shared), "equi joins only"
+        a, b = self._df(l), self._df(r)
+        m = a.merge(b, on=shared, how="left" if jt == F.JOIN_LEFT else "inner").fillna(0)
+        nullable = list(l[1]) + [jt == F.JOIN_LEFT or r[1][r[0].index(n)] for n in r[0] if n not in shared]
+        return self._out(m, nullable)
+
+    def filter(self, t, preds):
+        keep = np.ones(len(t[2][0]) if t[2] else 0, dtype=bool)
+        for p in preds:
+            c = t[2][p.col]
+            if p.op == F.F_BETWEEN:
+                keep &= (c >= p.value) & (c <= p.hi)
+            elif p.op == F.F_IS_NULL:
+                keep &= c == 0
+            elif p.op == F.F_IS_NOT_NULL:
+                keep &= c != 0
+            else:
+                raise ValueError(p.op)
+        return t[0], t[1], [c[keep] for c in t[2]]
+
+    def group_count(self, t, keys, counted, name):
+        df = self._df(t)
+        if counted is None:
+            g = df.groupby(keys, sort=False).size()
+        else:
+            g = (df[counted] != 0).groupby([df[k] for k in keys], sort=False).sum()
+        out = g.reset_index(name=name)
+        return self._out(out, [t[1][t[0].index(k)] for k in keys] + [False])
