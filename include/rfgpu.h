@@ -277,6 +277,40 @@ int32_t rfgpu_group_count(rfgpu_ctx* ctx, const rfgpu_table* in, const int32_t* 
 /* SELECT DISTINCT over all columns (ReplaceDistinctWithAggregate: a GROUP BY on every column). */
 int32_t rfgpu_distinct(rfgpu_ctx* ctx, const rfgpu_table* in, rfgpu_table** out);
 
+/* ---- object id -> plain term decode: a device dictionary gather ---- */
+/* Replaces MemObjectIdMapping::decode_array (lib/storage/src/memory/object_id_mapping.rs:331-378) behind ENC_PT
+ * (lib/functions/src/builtin/encoding/with_plain_term_encoding.rs:60-100).  The dictionary holds, for the ids 1..n_ids
+ * (arrays are indexed by id, entry 0 is unused; id 0 = NULL decodes to a null struct):
+ *   term_type[id]   PlainTermType: 0 named node, 1 blank node, 2 literal (lib/encoding/src/plain_term/encoding.rs:108-116)
+ *   value_off       n_ids + 2 ascending byte offsets: the lexical value of id is value_bytes[value_off[id], value_off[id+1])
+ *   datatype[id]    literals: index (1..n_aux) of the data type IRI in the string table (rdf:langString for language-tagged
+ *                   literals, as LiteralRef::datatype() reports); 0 for named / blank nodes
+ *   language[id]    language-tagged literals: index of the tag in the string table; 0 otherwise
+ *   aux_off         n_aux + 2 ascending offsets into aux_bytes (entry 0 unused)
+ * All pointers are host memory; the dictionary is copied to the device once.  The encode direction stays on the host. */
+typedef struct rfgpu_dict rfgpu_dict;
+typedef struct rfgpu_plain_terms rfgpu_plain_terms;
+int32_t rfgpu_dict_create(rfgpu_ctx* ctx, uint32_t n_ids, const uint8_t* term_type, const uint64_t* value_off,
+                          const uint8_t* value_bytes, const uint32_t* datatype, const uint32_t* language, uint32_t n_aux,
+                          const uint32_t* aux_off, const uint8_t* aux_bytes, rfgpu_dict** out);
+rfgpu_dict* rfgpu_dict_retain(rfgpu_dict* d);
+void rfgpu_dict_release(rfgpu_dict* d);
+uint32_t rfgpu_dict_len(const rfgpu_dict* d);
+/* Decodes rows [row_off, row_off + n_rows) of column `col` into the four children of the PlainTerm struct array
+ * (lib/encoding/src/plain_term/element_builder.rs:29-134), device-resident.  An id that is neither 0 nor in 1..n_ids is
+ * RFGPU_E_INVALID (the reference panics: "Missing EncodedObjectId").  More than 2^31-2 bytes in one child: RFGPU_E_UNSUPPORTED
+ * (Utf8 offsets are i32) — decode a smaller row range. */
+int32_t rfgpu_dict_decode(rfgpu_ctx* ctx, const rfgpu_dict* d, const rfgpu_table* t, int32_t col, uint64_t row_off,
+                          uint64_t n_rows, rfgpu_plain_terms** out);
+void rfgpu_plain_terms_release(rfgpu_plain_terms* p);
+/* rows; byte sizes of the value / data_type / language_tag children; null counts of the struct (= term_type = value
+ * children), the data_type and the language_tag children */
+int32_t rfgpu_plain_terms_sizes(const rfgpu_plain_terms* p, uint64_t* rows, uint64_t bytes[3], uint64_t nulls[3]);
+/* Copies the Arrow buffers to host memory: term_type[rows]; per child k (value, data_type, language_tag) the validity
+ * bitmap ((rows + 7) / 8 bytes; validity[0] is also the struct's and term_type's), rows + 1 i32 offsets and the bytes. */
+int32_t rfgpu_plain_terms_export(rfgpu_ctx* ctx, const rfgpu_plain_terms* p, uint8_t* term_type, uint8_t* const validity[3],
+                                 int32_t* const offsets[3], uint8_t* const data[3]);
+
 /* physical operator of the last rfgpu_group_count / rfgpu_distinct */
 typedef enum {
   RFGPU_AGG_PHYS_NONE = 0,

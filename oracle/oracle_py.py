@@ -359,3 +359,42 @@ def sparql_exists(l: OTable, r: OTable, negated: bool = False, block: int = 512)
             found[lo:hi] = compat.any(axis=1)
     keep = ~found if negated else found
     return OTable(list(l.names), list(l.nullable), [np.asarray(c, np.uint32)[keep] for c in l.cols])
+
+
+# ---------------------------------------------------------------- object id -> plain term decode
+RDF_LANG_STRING = "http://www.w3.org/1999/02/22-rdf-syntax-ns#langString"
+
+
+def decode_plain_terms(terms, ids):
+    """CPU restatement of MemObjectIdMapping::decode_array (lib/storage/src/memory/object_id_mapping.rs:331-378) feeding
+    PlainTermArrayElementBuilder (lib/encoding/src/plain_term/element_builder.rs:29-134), row at a time.
+    terms[i] is the EncodedTerm of object id i + 1: ("nn", iri) | ("bn", label) | ("lit", value, datatype) |
+    ("lang", value, tag); id 0 / None = NULL.  -> pyarrow StructArray in the PlainTermEncoding layout
+    (lib/encoding/src/plain_term/encoding.rs:34-72): NULL appends a null to all four children and a null struct slot
+    (:29-47); a language-tagged literal reports rdf:langString as its data type (LiteralRef::datatype)."""
+    import pyarrow as pa
+    tt, val, dt, lang, mask = [], [], [], [], []
+    for oid in ids:
+        oid = int(oid) if oid is not None else 0
+        if oid == 0:
+            tt.append(None); val.append(None); dt.append(None); lang.append(None); mask.append(True)  # noqa: E702
+            continue
+        if not 1 <= oid <= len(terms):
+            raise OracleError(f"Missing EncodedObjectId {oid}")  # .expect("Missing EncodedObjectId") :340
+        t = terms[oid - 1]
+        mask.append(False)
+        val.append(t[1])
+        if t[0] == "nn":
+            tt.append(0); dt.append(None); lang.append(None)  # noqa: E702
+        elif t[0] == "bn":
+            tt.append(1); dt.append(None); lang.append(None)  # noqa: E702
+        elif t[0] == "lit":
+            tt.append(2); dt.append(t[2]); lang.append(None)  # noqa: E702
+        elif t[0] == "lang":
+            tt.append(2); dt.append(RDF_LANG_STRING); lang.append(t[2])  # noqa: E702
+        else:
+            raise ValueError(t)
+    fields = [pa.field("term_type", pa.uint8(), False), pa.field("value", pa.utf8(), False),
+              pa.field("data_type", pa.utf8(), True), pa.field("language_tag", pa.utf8(), True)]
+    kids = [pa.array(tt, pa.uint8()), pa.array(val, pa.utf8()), pa.array(dt, pa.utf8()), pa.array(lang, pa.utf8())]
+    return pa.StructArray.from_arrays(kids, fields=fields, mask=pa.array(mask, pa.bool_()) if len(mask) else None)

@@ -145,6 +145,17 @@ SIGNATURES = {
     "rfgpu_timer_stop": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
     "rfgpu_flush_l2": (C.c_int32, [C.c_void_p]),
     "rfgpu_last_agg_phys": (C.c_int32, [C.c_void_p]),
+    "rfgpu_dict_create": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]),
+    "rfgpu_dict_retain": (C.c_void_p, [C.c_void_p]),
+    "rfgpu_dict_release": (None, [C.c_void_p]),
+    "rfgpu_dict_len": (C.c_uint32, [C.c_void_p]),
+    "rfgpu_dict_decode": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_uint64, C.c_uint64,
+                                      C.POINTER(C.c_void_p)]),
+    "rfgpu_plain_terms_release": (None, [C.c_void_p]),
+    "rfgpu_plain_terms_sizes": (C.c_int32, [C.c_void_p, u64p, u64p, u64p]),
+    "rfgpu_plain_terms_export": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                             C.POINTER(C.c_void_p)]),
     "rfgpu_table_sort": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_void_p)]),
     "rfgpu_store_build": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.c_uint64, C.c_int32, u32p,
                                       C.c_int32]),

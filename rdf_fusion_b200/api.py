@@ -547,3 +547,106 @@ class Table:
         i = self.names.index(col) if isinstance(col, str) else int(col)
         self.ctx.check(self.ctx.lib.rfgpu_table_set_sorted_col(self.ctx.h, self.h, i))
         return self
+
+
+# ---- object id -> plain term decode ----
+RDF_LANG_STRING = "http://www.w3.org/1999/02/22-rdf-syntax-ns#langString"
+TERM_NAMED_NODE, TERM_BLANK_NODE, TERM_LITERAL = 0, 1, 2
+
+
+def pack_terms(terms: Sequence[tuple]):
+    """terms[i] is the term of object id i + 1: ("nn", iri) | ("bn", label) | ("lit", value, datatype_iri) |
+    ("lang", value, tag).  -> the arrays rfgpu_dict_create takes (EncodedTerm, lib/storage/src/memory/encoding)."""
+    n = len(terms)
+    term_type = np.zeros(n + 1, np.uint8)
+    datatype = np.zeros(n + 1, np.uint32)
+    language = np.zeros(n + 1, np.uint32)
+    value_off = np.zeros(n + 2, np.uint64)
+    values, aux, aux_list = [], {}, []
+
+    def aux_id(s):
+        if s not in aux:
+            aux_list.append(s.encode("utf-8"))
+            aux[s] = len(aux_list)
+        return aux[s]
+    for i, t in enumerate(terms, start=1):
+        kind, val = t[0], t[1].encode("utf-8")
+        if kind == "nn":
+            term_type[i] = TERM_NAMED_NODE
+        elif kind == "bn":
+            term_type[i] = TERM_BLANK_NODE
+        elif kind == "lit":
+            term_type[i], datatype[i] = TERM_LITERAL, aux_id(t[2])
+        elif kind == "lang":
+            term_type[i], datatype[i], language[i] = TERM_LITERAL, aux_id(RDF_LANG_STRING), aux_id(t[2])
+        else:
+            raise ValueError(t)
+        values.append(val)
+        value_off[i + 1] = value_off[i] + len(val)
+    aux_off = np.zeros(len(aux_list) + 2, np.uint32)
+    for a, b in enumerate(aux_list, start=1):
+        aux_off[a + 1] = aux_off[a] + len(b)
+    return (term_type, value_off, np.frombuffer(b"".join(values), np.uint8), datatype, language,
+            aux_off, np.frombuffer(b"".join(aux_list), np.uint8))
+
+
+class Dictionary:
+    """Device-resident id -> term dictionary (rfgpu_dict); decode() is ENC_PT on a column of object ids."""
+
+    def __init__(self, ctx: Context, terms: Sequence[tuple]):
+        self.ctx = ctx
+        tt, vo, vb, dt, lg, ao, ab = pack_terms(terms)
+        h = C.c_void_p()
+        p = lambda a: a.ctypes.data if a.size else None  # noqa: E731
+        ctx.check(ctx.lib.rfgpu_dict_create(ctx.h, len(terms), p(tt), p(vo), p(vb), p(dt), p(lg), len(ao) - 2, p(ao), p(ab),
+                                            C.byref(h)))
+        self.h = h
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.ctx.lib.rfgpu_dict_release(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def __len__(self):
+        return int(self.ctx.lib.rfgpu_dict_len(self.h))
+
+    def decode(self, table: "Table", col, row_off: int = 0, n_rows: Optional[int] = None):
+        """-> pyarrow StructArray {term_type: uint8, value: utf8, data_type: utf8, language_tag: utf8} (PlainTermEncoding)"""
+        i = table.names.index(col) if isinstance(col, str) else int(col)
+        n = table.num_rows - row_off if n_rows is None else n_rows
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_dict_decode(self.ctx.h, self.h, table.h, i, row_off, n, C.byref(out)))
+        try:
+            rows = C.c_uint64()
+            sizes, nulls = (C.c_uint64 * 3)(), (C.c_uint64 * 3)()
+            self.ctx.check(self.ctx.lib.rfgpu_plain_terms_sizes(out, C.byref(rows), sizes, nulls))
+            n = int(rows.value)
+            term_type = np.zeros(max(n, 1), np.uint8)
+            valid = [np.zeros((n + 7) // 8 + 1, np.uint8) for _ in range(3)]
+            offs = [np.zeros(n + 1, np.int32) for _ in range(3)]
+            data = [np.zeros(max(int(sizes[k]), 1), np.uint8) for k in range(3)]
+            arr = lambda xs: (C.c_void_p * 3)(*[x.ctypes.data for x in xs])  # noqa: E731
+            self.ctx.check(self.ctx.lib.rfgpu_plain_terms_export(self.ctx.h, out, term_type.ctypes.data, arr(valid), arr(offs),
+                                                                 arr(data)))
+        finally:
+            self.ctx.lib.rfgpu_plain_terms_release(out)
+        return plain_terms_to_arrow(n, term_type, valid, offs, data, [int(x) for x in sizes], [int(x) for x in nulls])
+
+
+def plain_terms_to_arrow(n, term_type, valid, offs, data, sizes, nulls):
+    """The buffers rfgpu_plain_terms_export fills -> pyarrow StructArray in the PlainTermEncoding layout, zero decoding
+    work on the host (the buffers ARE the Arrow buffers)."""
+    import pyarrow as pa
+    vb = [pa.py_buffer(v[:(n + 7) // 8].tobytes()) for v in valid]
+    tt = pa.Array.from_buffers(pa.uint8(), n, [vb[0], pa.py_buffer(term_type[:n].tobytes())], null_count=nulls[0])
+    kids = [tt]
+    for k in range(3):
+        kids.append(pa.Array.from_buffers(pa.utf8(), n, [vb[k], pa.py_buffer(offs[k].tobytes()),
+                                                         pa.py_buffer(data[k][:sizes[k]].tobytes())], null_count=nulls[k]))
+    fields = [pa.field("term_type", pa.uint8(), False), pa.field("value", pa.utf8(), False),
+              pa.field("data_type", pa.utf8(), True), pa.field("language_tag", pa.utf8(), True)]
+    null_struct = ~np.unpackbits(np.frombuffer(vb[0], np.uint8), bitorder="little")[:n].astype(bool) if n else None
+    return pa.StructArray.from_arrays(kids, fields=fields, mask=pa.array(null_struct, pa.bool_()) if n else None)
