@@ -51,6 +51,12 @@ def values_golden():
 
 
 @pytest.fixture(scope="session")
+def bgp_golden():
+    with open(os.path.join(GOLDEN, "bgp_golden.json")) as f:
+        return json.load(f)
+
+
+@pytest.fixture(scope="session")
 def oracle():
     from oracle import oracle_py
     oracle_py.build()

@@ -35,3 +35,14 @@ def test_w3c_nested_negation_and_exists_cases_gpu(ctx, minus_golden):
     assert len(cases) == 6
     for case in cases:
         check_w3c_case(GpuBackend(ctx, case["quads"]), case)
+
+
+@pytest.mark.gpu
+def test_w3c_dataset_and_basic_bgp_cases_gpu(ctx, bgp_golden):
+    """sparql10/dataset and sparql10/basic (tests/golden/bgp_golden.json): scans over a merged default graph and named graphs,
+    unions and joins of the two, rdf:first / rdf:rest chains of up to five patterns, a join on two shared variables, an
+    unknown constant.  Added after the round's GPU budget was spent; it uses only operators and join shapes the files above
+    already validated on a B200 (the CPU twin audits every join of these plans against the CUDA path's limits)."""
+    assert len(bgp_golden["cases"]) == 20
+    for case in bgp_golden["cases"]:
+        check_w3c_case(GpuBackend(ctx, case["quads"]), case)

@@ -211,11 +211,12 @@ def test_sort_based_group_count_and_distinct(ctx, oracle, sort_paths):
     assert_same_table(got.names, got.to_numpy(), exp.names, exp.cols)
 
 
-def test_w3c_cases_through_the_sort_paths(ctx, sort_paths, join_golden, minus_golden, agg_golden, pattern_golden, values_golden):
-    """all 64 W3C evaluation cases with the store built on the device and the three sort-based operators switched on"""
+def test_w3c_cases_through_the_sort_paths(ctx, sort_paths, join_golden, minus_golden, agg_golden, pattern_golden, values_golden,
+                                          bgp_golden):
+    """all 84 W3C evaluation cases with the store built on the device and the three sort-based operators switched on"""
     n = 0
-    for gold in (join_golden, minus_golden, agg_golden, pattern_golden, values_golden):
+    for gold in (join_golden, minus_golden, agg_golden, pattern_golden, values_golden, bgp_golden):
         for case in gold["cases"]:
             check_w3c_case(GpuBackend(ctx, case["quads"], device_build=True), case)
             n += 1
-    assert n == 64
+    assert n == 84

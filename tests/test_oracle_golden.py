@@ -332,3 +332,26 @@ def test_w3c_values_cases(oracle, values_golden):
     assert len(values_golden["cases"]) == 10
     for case in values_golden["cases"]:
         check_w3c_case(OracleBackend(oracle, case["quads"]), case)
+
+
+def test_w3c_dataset_and_basic_bgp_cases(oracle, bgp_golden):
+    """sparql10/dataset (FROM / FROM NAMED: merged default graph, named graphs, GRAPH ?g) and sparql10/basic (collections as
+    rdf:first / rdf:rest chains over fresh variables, a two-variable join, a constant that is not in the data),
+    tests/golden/make_bgp_golden.py.  Also audits every join of these plans against the limits of the CUDA path (at most two
+    shared non-nullable variables, four nullable ones, 16 columns), so the GPU twin cannot meet an unsupported shape."""
+    from helpers import OracleBackend, check_w3c_case
+    assert len(bgp_golden["cases"]) == 20
+    for case in bgp_golden["cases"]:
+        be = OracleBackend(oracle, case["quads"])
+        joins = []
+        inner_join = be.join
+
+        def audited(l, r, jt, _j=inner_join, _log=joins):
+            shared = [n for n in l[0] if n in r[0]]
+            nullable = any(l[1][l[0].index(n)] or r[1][r[0].index(n)] for n in shared)
+            _log.append((len(shared), nullable, len(l[0]) + len(r[0]) - len(shared)))
+            return _j(l, r, jt)
+        be.join = audited
+        check_w3c_case(be, case)
+        for n_shared, nullable, n_out in joins:
+            assert n_shared <= (4 if nullable else 2) and n_out <= 16, (case["name"], joins)
