@@ -152,3 +152,33 @@ def test_invalid_arguments_are_errors_not_crashes():
     h = C.c_void_p()
     assert lib.rfgpu_store_add_index(None, st.h, 0, None, 0, 0) == F.E_INVALID  # perm 0 = GGGG
     assert F.load().rfgpu_shuffle_dest(123, 8) < 8
+
+
+def test_new_entry_points_reject_bad_arguments_without_a_gpu():
+    """rfgpu_store_build / rfgpu_table_sort / rfgpu_dict_* validate their arguments before they touch the device: NULL
+    handles are RFGPU_E_INVALID, never a crash (no panics across the FFI)."""
+    lib = F.load()
+    out = C.c_void_p()
+    assert lib.rfgpu_table_sort(None, None, None, 0, C.byref(out)) == F.E_INVALID
+    assert lib.rfgpu_store_build(None, None, None, 0, 0, None, 0) == F.E_INVALID
+    assert lib.rfgpu_dict_create(None, 0, None, None, None, None, None, 0, None, None, C.byref(out)) == F.E_INVALID
+    assert lib.rfgpu_dict_decode(None, None, None, 0, 0, 0, C.byref(out)) == F.E_INVALID
+    assert lib.rfgpu_plain_terms_sizes(None, None, None, None) == F.E_INVALID
+    assert lib.rfgpu_plain_terms_export(None, None, None, None, None, None) == F.E_INVALID
+    assert lib.rfgpu_dict_len(None) == 0 and lib.rfgpu_last_agg_phys(None) == 0
+    lib.rfgpu_dict_release(None)
+    lib.rfgpu_plain_terms_release(None)
+    assert b"NULL" in lib.rfgpu_last_error(None)
+
+
+def test_pack_terms_layout():
+    """the dictionary arrays rfgpu_dict_create takes: indexed by id, entry 0 unused, rdf:langString as the data type of a
+    language-tagged literal, string-table entries shared"""
+    xs = "http://www.w3.org/2001/XMLSchema#string"
+    tt, vo, vb, dt, lg, ao, ab = rf.pack_terms([("nn", "http://e/a"), ("lit", "x", xs), ("lang", "été", "fr"), ("lit", "", xs),
+                                               ("bn", "b0")])
+    assert tt.tolist() == [0, 0, 2, 2, 2, 1]
+    assert vo.tolist() == [0, 0, 10, 11, 16, 16, 18] and bytes(vb) == "http://e/axétéb0".encode()
+    assert dt.tolist() == [0, 0, 1, 2, 1, 0] and lg.tolist() == [0, 0, 0, 3, 0, 0]
+    strings = [bytes(ab[ao[i]:ao[i + 1]]).decode() for i in range(1, len(ao) - 1)]
+    assert strings == [xs, "http://www.w3.org/1999/02/22-rdf-syntax-ns#langString", "fr"]
