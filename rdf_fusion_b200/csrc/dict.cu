@@ -10,7 +10,6 @@
 //   k_dict_copy     one warp per row copies the value bytes and the two short strings, coalesced along the bytes
 // The encode direction (term → id: string hashing into the DashMap, :309-329) stays on the host.
 #include "rf_common.hpp"
-#include "rf_device.cuh"
 
 struct rfgpu_dict {
   std::atomic<int> refs{1};

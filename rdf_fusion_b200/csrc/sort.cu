@@ -14,7 +14,6 @@
 #include <algorithm>
 
 #include "rf_common.hpp"
-#include "rf_device.cuh"
 
 namespace rf {
 

@@ -1,0 +1,84 @@
+"""Builds tests/emu/_build/librfemu.so: rdf_fusion_b200/csrc/{sort,dict}.cu compiled by g++ for the host against the
+stand-in CUDA runtime of this directory (TEST INFRASTRUCTURE ONLY — see cuda_runtime.h).  The only change made to the
+sources is syntactic: `kernel<<<grid, block, smem, stream>>>(args);` becomes `EMU_LAUNCH(kernel, grid, block, args);`."""
+import os
+import re
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+CSRC = os.path.join(ROOT, "rdf_fusion_b200", "csrc")
+BUILD = os.path.join(HERE, "_build")
+SOURCES = ["sort.cu", "dict.cu"]
+
+
+def _balanced(s, i, open_, close):
+    """s[i] == open_ -> index just past the matching close"""
+    depth = 0
+    while True:
+        if s[i] == open_:
+            depth += 1
+        elif s[i] == close:
+            depth -= 1
+            if depth == 0:
+                return i + 1
+        i += 1
+
+
+def _split_top(s):
+    parts, depth, cur = [], 0, ""
+    for ch in s:
+        if ch == "(":
+            depth += 1
+        elif ch == ")":
+            depth -= 1
+        if ch == "," and depth == 0:
+            parts.append(cur.strip())
+            cur = ""
+        else:
+            cur += ch
+    parts.append(cur.strip())
+    return parts
+
+
+def rewrite_launches(src):
+    out, pos, n = "", 0, 0
+    for m in re.finditer(r"(\w+)<<<", src):
+        if m.start() < pos:
+            continue
+        end_cfg = src.index(">>>", m.end())
+        cfg = _split_top(src[m.end():end_cfg])
+        assert 2 <= len(cfg) <= 4, cfg
+        a0 = end_cfg + 3
+        assert src[a0] == "(", src[a0:a0 + 20]
+        a1 = _balanced(src, a0, "(", ")")
+        out += src[pos:m.start()] + "EMU_LAUNCH(%s, %s, %s, %s)" % (m.group(1), cfg[0], cfg[1], src[a0 + 1:a1 - 1])
+        pos = a1
+        n += 1
+    return out + src[pos:], n
+
+
+def build():
+    os.makedirs(BUILD, exist_ok=True)
+    cpps = [os.path.join(HERE, "emu_runtime.cpp")]
+    newest = max(os.path.getmtime(os.path.join(HERE, f)) for f in ("cuda_runtime.h", "emu_runtime.cpp", "build_emu.py"))
+    for f in SOURCES:
+        text, n = rewrite_launches(open(os.path.join(CSRC, f)).read())
+        assert n >= 2 and "<<<" not in text, (f, n)
+        dst = os.path.join(BUILD, f.replace(".cu", "_emu.cpp"))
+        if not os.path.exists(dst) or open(dst).read() != text:
+            open(dst, "w").write(text)
+        cpps.append(dst)
+        newest = max(newest, os.path.getmtime(dst))
+    for h in ("rf_common.hpp",):
+        newest = max(newest, os.path.getmtime(os.path.join(CSRC, h)))
+    so = os.path.join(BUILD, "librfemu.so")
+    if not os.path.exists(so) or os.path.getmtime(so) < newest:
+        cmd = ["g++", "-std=c++20", "-O1", "-g", "-fPIC", "-shared", "-pthread", "-Wall", "-Wno-unused-function",
+               "-Wno-unknown-pragmas", "-I", HERE, "-I", CSRC, "-o", so] + cpps
+        subprocess.run(cmd, check=True)
+    return so
+
+
+if __name__ == "__main__":
+    print(build())

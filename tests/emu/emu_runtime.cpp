@@ -1,0 +1,160 @@
+// tests/emu/emu_runtime.cpp — TEST INFRASTRUCTURE ONLY (see cuda_runtime.h in this directory).  Host-side stand-ins for
+// what ctx.cu / filter.cu / table.cu provide to sort.cu and dict.cu, so that those two files — kernels AND their host
+// orchestration, unmodified apart from the <<<>>> launch syntax — run on host threads; plus a few entry points the
+// Python test needs to put columns in and take them out ("device" memory is host memory here).
+#include <cstdio>
+#include <numeric>
+
+#include "rf_common.hpp"
+
+namespace rf {
+Core::~Core() {}
+DevBuf::DevBuf(std::shared_ptr<Core> c, size_t n) : core(std::move(c)), bytes(n) {
+  ptr = std::calloc(((n + kPad - 1) / kPad) * kPad + kPad, 1);
+  std::memset(ptr, 0xA5, n);  // uninitialised device memory is not zero
+}
+DevBuf::~DevBuf() { std::free(ptr); }
+KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes) : ctx(c) {
+  ctx->m.kernel_launches++;
+  idx = ctx->kstat_index(name);
+  ctx->kstats[idx].second.launches++;
+  ctx->kstats[idx].second.bytes += bytes;
+}
+KernelScope::~KernelScope() noexcept(false) {}
+rfgpu_table* new_table() { return new rfgpu_table(); }
+BufRef alloc_col(rfgpu_ctx* ctx, uint64_t rows) { return ctx->alloc(rows * sizeof(uint32_t)); }
+int find_col(const rfgpu_table* t, const std::string& name) {
+  for (size_t i = 0; i < t->cols.size(); i++)
+    if (t->cols[i].name == name) return (int)i;
+  return -1;
+}
+static thread_local std::string g_err;
+void set_error(const rfgpu_ctx* ctx, const std::string& msg) {
+  g_err = msg;
+  if (ctx) const_cast<rfgpu_ctx*>(ctx)->err = msg;
+}
+// the device-wide scan of filter.cu (validated on a B200 this round) is not what is under test here
+void exclusive_scan_u32(rfgpu_ctx*, const uint32_t* in, uint32_t* out, uint64_t n, uint64_t* h_total_slot) {
+  uint64_t run = 0;
+  for (uint64_t i = 0; i < n; i++) {
+    uint32_t v = in[i];
+    out[i] = (uint32_t)run;
+    run += v;
+  }
+  if (h_total_slot) *h_total_slot = run;
+}
+}  // namespace rf
+
+int rfgpu_ctx::kstat_index(const char* name) {
+  for (size_t i = 0; i < kstats.size(); i++)
+    if (kstats[i].first == name) return (int)i;
+  kstats.push_back({name, rf::KernelStat{}});
+  return (int)kstats.size() - 1;
+}
+void rfgpu_ctx::collect_profile() {}
+
+extern "C" {
+
+const char* rfgpu_last_error(const rfgpu_ctx* ctx) { return ctx ? ctx->err.c_str() : rf::g_err.c_str(); }
+
+int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm, const uint32_t* const cols[4], uint64_t n_rows,
+                              int32_t) {
+  RF_API_BEGIN
+  rfgpu_index_t ix;
+  ix.perm = perm;
+  ix.rows = n_rows;
+  for (int i = 0; i < 4; i++) {
+    ix.col[i] = rf::alloc_col(ctx, n_rows);
+    if (n_rows) std::memcpy(ix.col[i]->ptr, cols[i], n_rows * 4);
+  }
+  for (uint64_t r = 1; r < n_rows; r++) {  // k_check_sorted: strictly ascending in permutation order
+    int c = 0;
+    while (c < 4 && cols[c][r] == cols[c][r - 1]) c++;
+    RF_REQUIRE(c < 4 && cols[c][r] > cols[c][r - 1], RFGPU_E_INVALID,
+               "index columns are not strictly sorted in permutation order at row " + std::to_string(r));
+  }
+  if (!s->indexes.empty()) RF_REQUIRE(s->indexes[0].rows == n_rows, RFGPU_E_INVALID, "all permutations must hold the same quads");
+  s->indexes.push_back(std::move(ix));
+  RF_API_END(ctx)
+}
+
+rfgpu_ctx* emu_ctx_create() {
+  auto* c = new rfgpu_ctx();
+  c->core = std::make_shared<rf::Core>();
+  c->h_scratch = (uint64_t*)std::calloc(256, 8);
+  return c;
+}
+void emu_ctx_destroy(rfgpu_ctx* c) {
+  std::free(c->h_scratch);
+  delete c;
+}
+uint64_t emu_kernel_launches(rfgpu_ctx* c, const char* name) {
+  for (auto& k : c->kstats)
+    if (k.first == name) return k.second.launches;
+  return 0;
+}
+rfgpu_table* emu_table_create(rfgpu_ctx* ctx, int32_t n_cols, const uint32_t* const* cols, uint64_t rows, int32_t sorted_col) {
+  auto* t = rf::new_table();
+  t->rows = rows;
+  t->sorted_col = sorted_col;
+  for (int c = 0; c < n_cols; c++) {
+    rf::Column col;
+    col.name = "c" + std::to_string(c);
+    col.owner = rf::alloc_col(ctx, rows);
+    col.data = col.owner->as<uint32_t>();
+    if (rows) std::memcpy(col.owner->ptr, cols[c], rows * 4);
+    t->cols.push_back(col);
+  }
+  return t;
+}
+uint64_t emu_table_rows(const rfgpu_table* t) { return t->rows; }
+int32_t emu_table_cols(const rfgpu_table* t) { return (int32_t)t->cols.size(); }
+int32_t emu_table_sorted_col(const rfgpu_table* t) { return t->sorted_col; }
+const uint32_t* emu_table_col(const rfgpu_table* t, int32_t c) { return t->cols[c].data; }
+void emu_table_release(rfgpu_table* t) { delete t; }
+rfgpu_store* emu_store_create() { return new rfgpu_store(); }
+void emu_store_release(rfgpu_store* s) { delete s; }
+int32_t emu_store_indexes(const rfgpu_store* s) { return (int32_t)s->indexes.size(); }
+uint64_t emu_store_rows(const rfgpu_store* s, int32_t i) { return s->indexes[i].rows; }
+const uint32_t* emu_store_col(const rfgpu_store* s, int32_t i, int32_t level) { return s->indexes[i].col[level]->as<uint32_t>(); }
+
+// the call sequences of aggregate.cu's sort path and join.cu's sorted-list semi join, on raw columns
+int32_t emu_group_count(rfgpu_ctx* ctx, int32_t n_keys, const uint32_t* const* keys, const uint32_t* counted, uint64_t n,
+                        int32_t want_counts, rfgpu_table** out) {
+  RF_API_BEGIN
+  using namespace rf;
+  std::vector<const uint32_t*> cols(keys, keys + n_keys);
+  std::vector<int> order(n_keys);
+  std::iota(order.begin(), order.end(), 0);
+  if (counted) cols.push_back(counted);
+  std::vector<BufRef> sorted = sort_rows_lex(ctx, cols, order, n);
+  for (size_t c = 0; c < cols.size(); c++) cols[c] = sorted[c]->as<uint32_t>();
+  std::vector<BufRef> outk;
+  BufRef cnt;
+  uint64_t groups = encode_runs(ctx, cols, n_keys, n, &outk, want_counts ? &cnt : nullptr, counted ? cols.back() : nullptr);
+  auto* t = new_table();
+  t->rows = groups;
+  for (int k = 0; k < n_keys; k++) {
+    Column c;
+    c.owner = outk[k];
+    c.data = outk[k]->as<uint32_t>();
+    t->cols.push_back(c);
+  }
+  if (want_counts) {
+    Column c;
+    c.owner = cnt;
+    c.data = cnt->as<uint32_t>();
+    t->cols.push_back(c);
+  }
+  *out = t;
+  RF_API_END(ctx)
+}
+int32_t emu_sorted_contains(rfgpu_ctx* ctx, const uint32_t* rhs_keys, uint64_t nr, const uint32_t* probe, uint64_t np,
+                            uint32_t* flag) {
+  RF_API_BEGIN
+  auto sorted = rf::sort_rows_lex(ctx, {rhs_keys}, {0}, nr);
+  rf::sorted_contains(ctx, sorted[0]->as<uint32_t>(), nr, probe, np, flag);
+  RF_API_END(ctx)
+}
+
+}  // extern "C"

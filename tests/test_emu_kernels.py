@@ -1,0 +1,211 @@
+"""CPU: the kernels of rdf_fusion_b200/csrc/sort.cu and dict.cu — and their host orchestration, unmodified — executed on
+host threads through the stand-in CUDA runtime of tests/emu/ (every CTA thread an OS thread, real barriers, warp collectives
+through an exchange buffer), against numpy and the oracle.  This is a CHECK OF THE KERNELS' LOGIC in a container that has no
+GPU (index arithmetic, barrier placement, ballot / match.any use, tail tiles); it is not a CPU path of the product — nothing
+under rdf_fusion_b200/ can reach it — and the same files are compared with the oracle on a real B200 by
+tests/test_gpu_zz_sort.py and tests/test_gpu_zz_dict.py."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "emu"))
+import build_emu  # noqa: E402
+
+from rdf_fusion_b200 import _ffi as F  # noqa: E402
+from rdf_fusion_b200.api import pack_terms, plain_terms_to_arrow  # noqa: E402
+from test_dict_decode_cpu import REF_TERMS, random_terms  # noqa: E402
+
+vp, u32p, u64p = C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)
+
+
+@pytest.fixture(scope="module")
+def emu():
+    lib = C.CDLL(build_emu.build())
+    sig = {
+        "emu_ctx_create": (vp, []), "emu_ctx_destroy": (None, [vp]), "emu_kernel_launches": (C.c_uint64, [vp, C.c_char_p]),
+        "emu_table_create": (vp, [vp, C.c_int32, C.POINTER(vp), C.c_uint64, C.c_int32]), "emu_table_rows": (C.c_uint64, [vp]),
+        "emu_table_cols": (C.c_int32, [vp]), "emu_table_sorted_col": (C.c_int32, [vp]), "emu_table_col": (u32p, [vp, C.c_int32]),
+        "emu_table_release": (None, [vp]), "emu_store_create": (vp, []), "emu_store_release": (None, [vp]),
+        "emu_store_indexes": (C.c_int32, [vp]), "emu_store_rows": (C.c_uint64, [vp, C.c_int32]),
+        "emu_store_col": (u32p, [vp, C.c_int32, C.c_int32]),
+        "emu_group_count": (C.c_int32, [vp, C.c_int32, C.POINTER(vp), vp, C.c_uint64, C.c_int32, C.POINTER(vp)]),
+        "emu_sorted_contains": (C.c_int32, [vp, vp, C.c_uint64, vp, C.c_uint64, vp]),
+        "rfgpu_last_error": (C.c_char_p, [vp]),
+    }
+    for name in ("rfgpu_table_sort", "rfgpu_store_build", "rfgpu_dict_create", "rfgpu_dict_release", "rfgpu_dict_decode",
+                 "rfgpu_plain_terms_release", "rfgpu_plain_terms_sizes", "rfgpu_plain_terms_export"):
+        sig[name] = F.SIGNATURES[name]  # the product's own bindings
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+    lib.ctx = lib.emu_ctx_create()
+    yield lib
+    lib.emu_ctx_destroy(lib.ctx)
+
+
+def _ok(lib, rc):
+    assert rc == 0, (rc, lib.rfgpu_last_error(lib.ctx))
+
+
+def _table(lib, cols, sorted_col=-1):
+    cols = [np.ascontiguousarray(c, np.uint32) for c in cols]
+    arr = (vp * len(cols))(*[c.ctypes.data for c in cols])
+    return lib.emu_table_create(lib.ctx, len(cols), arr, len(cols[0]), sorted_col)
+
+
+def _cols(lib, t):
+    n = lib.emu_table_rows(t)
+    return [np.ctypeslib.as_array(lib.emu_table_col(t, c), shape=(n,)).copy() if n else np.zeros(0, np.uint32)
+            for c in range(lib.emu_table_cols(t))]
+
+
+def _sort(lib, cols, keys):
+    t = _table(lib, cols)
+    out = vp()
+    _ok(lib, lib.rfgpu_table_sort(lib.ctx, t, (C.c_int32 * len(keys))(*keys), len(keys), C.byref(out)))
+    got = _cols(lib, out)
+    assert lib.emu_table_sorted_col(out) == keys[0]
+    lib.emu_table_release(out)
+    lib.emu_table_release(t)
+    return got
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 31, 33, 4095, 4096, 4097, 9001])
+def test_radix_sort_is_a_stable_lexicographic_sort(emu, n):
+    """empty, one row, partial warp, exactly one tile, one row over, three tiles × 0–4 digit passes × 1–3 sort columns ×
+    1–6 carried columns (more than 4: the row-number path with k_iota0 / k_gather_rows)"""
+    rng = np.random.default_rng(n + 7)
+    shapes = [(1, [0]), (2, [1]), (3, [2, 0]), (4, [1, 3, 0]), (6, [4]), (5, [0, 3])]
+    his = (0, 1, 200, 50000, 1 << 22, 0xFFFFFFFF)
+    if n <= 33:      # the emulation pays ~0.1 s per launch whatever the size: keep the small shapes to a cross-section
+        combos = [(his[k], shapes[(k + j) % 6]) for k in (0, 2, 5) for j in (0, 2, 4)]
+    elif n == 4097:  # every key range, every shape once or twice
+        combos = [(his[k], shapes[(k + j) % 6]) for k in range(6) for j in (0, 3)]
+    else:
+        combos = [(his[k], shapes[(k + j) % 6]) for k in (2, 4) for j in (1, 3)]
+    for hi, (ncols, keys) in combos:
+        cols = [rng.integers(0, hi, n, dtype=np.uint64, endpoint=True).astype(np.uint32) for _ in range(ncols)]
+        got = _sort(emu, cols, keys)
+        order = np.lexsort(tuple(cols[c] for c in reversed(keys))) if n else np.zeros(0, np.int64)
+        for g, c in zip(got, cols):
+            assert np.array_equal(g, c[order]), (n, hi, ncols, keys)
+
+
+def test_radix_sort_skewed_digit(emu):
+    rng = np.random.default_rng(5)
+    n = 10000
+    k = np.where(rng.random(n) < 0.97, 77, rng.integers(0, 1 << 30, n)).astype(np.uint32)
+    v = np.arange(n, dtype=np.uint32)
+    got = _sort(emu, [k, v], [0])
+    order = np.argsort(k, kind="stable")
+    assert np.array_equal(got[0], k[order]) and np.array_equal(got[1], v[order])
+
+
+@pytest.mark.parametrize("seed,n", [(1, 0), (2, 1), (3, 500), (4, 5000)])
+def test_store_build_sorts_and_deduplicates_every_permutation(emu, seed, n):
+    rng = np.random.default_rng(seed)
+    g = np.where(rng.random(n) < 0.6, 0, rng.integers(1, 4, n)).astype(np.uint32)
+    q = np.stack([g, rng.integers(1, max(4, n // 8) + 1, n).astype(np.uint32), rng.integers(1, 7, n).astype(np.uint32),
+                  rng.integers(1, max(4, n // 5) + 1, n).astype(np.uint32)], axis=1)
+    if n:
+        q = np.concatenate([q, q[rng.integers(0, n, n // 3)]])
+        q = q[rng.permutation(len(q))]
+    cols = [np.ascontiguousarray(q[:, c]) for c in range(4)]
+    perms = [F.GSPO, F.GPOS, F.GOSP, F.GPSO] if n <= 500 else [F.GPOS, F.GOSP]
+    st = emu.emu_store_create()
+    arr = (vp * 4)(*[c.ctypes.data for c in cols])
+    _ok(emu, emu.rfgpu_store_build(emu.ctx, st, arr, len(q), 1, (C.c_uint32 * len(perms))(*perms), len(perms)))
+    uq = np.unique(q, axis=0) if len(q) else q
+    assert emu.emu_store_indexes(st) == len(perms)
+    for i, p in enumerate(perms):
+        comps = [(p >> (2 * lv)) & 3 for lv in range(4)]
+        lv = [uq[:, c] for c in comps]
+        order = np.lexsort(tuple(reversed(lv))) if len(uq) else np.zeros(0, np.int64)
+        assert emu.emu_store_rows(st, i) == len(uq)
+        for level in range(4):
+            got = np.ctypeslib.as_array(emu.emu_store_col(st, i, level), shape=(len(uq),)) if len(uq) else np.zeros(0, np.uint32)
+            assert np.array_equal(got, lv[level][order]), (p, level)
+    emu.emu_store_release(st)
+
+
+def test_run_length_group_count_and_distinct(emu):
+    rng = np.random.default_rng(21)
+    import pandas as pd
+    for n, ks in [(0, 5), (1, 1), (33, 2), (5000, 7), (4200, 1 << 20)]:
+        a, b, c = [np.where(rng.random(n) < 0.1, 0, rng.integers(1, ks + 1, n)).astype(np.uint32) for _ in range(3)]
+        for keys, counted, want_counts in [([a], None, 1), ([a], c, 1), ([b, a], None, 1), ([a, b, c], b, 1), ([a, b], None, 0)]:
+            out = vp()
+            ka = (vp * len(keys))(*[k.ctypes.data for k in keys])
+            _ok(emu, emu.emu_group_count(emu.ctx, len(keys), ka, counted.ctypes.data if counted is not None else None, n,
+                                         want_counts, C.byref(out)))
+            got = _cols(emu, out)
+            emu.emu_table_release(out)
+            df = pd.DataFrame({f"k{i}": k.astype(np.int64) for i, k in enumerate(keys)})
+            names = list(df.columns)
+            if n == 0:
+                assert all(len(g) == 0 for g in got)
+                continue
+            if counted is None:
+                exp = df.groupby(names, sort=True).size().reset_index(name="n")
+            else:
+                exp = (pd.Series(counted != 0)).groupby([df[k] for k in names], sort=True).sum().reset_index(name="n")
+            for i, k in enumerate(names):  # runs come out in key order
+                assert np.array_equal(got[i], exp[k].to_numpy().astype(np.uint32)), (n, ks, len(keys))
+            if want_counts:
+                assert np.array_equal(got[-1], exp["n"].to_numpy().astype(np.uint32))
+
+
+def test_sorted_list_semi_join_flags(emu):
+    rng = np.random.default_rng(43)
+    for nl, nr, hi in [(50, 1, 9), (300, 200, 25), (6000, 3000, 400), (9000, 5000, 90000)]:
+        l = rng.integers(0, hi + 1, nl).astype(np.uint32)  # 0 = NULL never has a partner
+        r = rng.integers(1, hi + 1, nr).astype(np.uint32)
+        flag = np.zeros(nl, np.uint32)
+        _ok(emu, emu.emu_sorted_contains(emu.ctx, r.ctypes.data, nr, l.ctypes.data, nl, flag.ctypes.data))
+        assert np.array_equal(flag != 0, np.isin(l, r) & (l != 0))
+
+
+def _decode(lib, terms, ids):
+    tt, vo, vb, dt, lg, ao, ab = pack_terms(terms)
+    p = lambda a: a.ctypes.data if a.size else None  # noqa: E731
+    d = vp()
+    _ok(lib, lib.rfgpu_dict_create(lib.ctx, len(terms), p(tt), p(vo), p(vb), p(dt), p(lg), len(ao) - 2, p(ao), p(ab), C.byref(d)))
+    t = _table(lib, [np.asarray(ids, np.uint32)])
+    out = vp()
+    rc = lib.rfgpu_dict_decode(lib.ctx, d, t, 0, 0, len(ids), C.byref(out))
+    if rc != 0:
+        msg = lib.rfgpu_last_error(lib.ctx).decode()
+        lib.rfgpu_dict_release(d)
+        lib.emu_table_release(t)
+        return rc, msg
+    rows = C.c_uint64()
+    sizes, nulls = (C.c_uint64 * 3)(), (C.c_uint64 * 3)()
+    _ok(lib, lib.rfgpu_plain_terms_sizes(out, C.byref(rows), sizes, nulls))
+    n = int(rows.value)
+    term_type = np.zeros(max(n, 1), np.uint8)
+    valid = [np.zeros((n + 7) // 8 + 1, np.uint8) for _ in range(3)]
+    offs = [np.zeros(n + 1, np.int32) for _ in range(3)]
+    data = [np.zeros(max(int(sizes[k]), 1), np.uint8) for k in range(3)]
+    arr = lambda xs: (vp * 3)(*[x.ctypes.data for x in xs])  # noqa: E731
+    _ok(lib, lib.rfgpu_plain_terms_export(lib.ctx, out, term_type.ctypes.data, arr(valid), arr(offs), arr(data)))
+    lib.rfgpu_plain_terms_release(out)
+    lib.rfgpu_dict_release(d)
+    lib.emu_table_release(t)
+    return 0, plain_terms_to_arrow(n, term_type, valid, offs, data, [int(x) for x in sizes], [int(x) for x in nulls])
+
+
+@pytest.mark.parametrize("n_terms,n_rows", [(4, 5), (1, 0), (1, 1), (50, 31), (50, 32), (50, 33), (400, 3000)])
+def test_dictionary_decode_matches_the_oracle(emu, oracle, n_terms, n_rows):
+    rng = np.random.default_rng(n_terms + n_rows)
+    terms = REF_TERMS if n_terms == 4 else random_terms(rng, n_terms)
+    ids = rng.integers(0, len(terms) + 1, n_rows).astype(np.uint32) if n_rows != 5 else np.array([1, 2, 3, 4, 0], np.uint32)
+    rc, got = _decode(emu, terms, ids)
+    assert rc == 0
+    exp = oracle.decode_plain_terms(terms, ids)
+    got.validate(full=True)
+    assert got.type == exp.type and got.null_count == exp.null_count and got.equals(exp)
+    rc, msg = _decode(emu, terms, np.array([1, len(terms) + 3], np.uint32))
+    assert rc == F.E_INVALID and str(len(terms) + 3) in msg
