@@ -241,6 +241,15 @@ typedef enum {
  * what DataFusion's HashJoinExec / NestedLoopJoinExec / CrossJoinExec would produce. */
 int32_t rfgpu_sparql_join(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_table* rhs,
                           int32_t join_type, rfgpu_table** out);
+/* The same join with SparqlJoinNode's optional filter (lib/logical/src/join/logical.rs:50; join/rewrite.rs:149-161 hands it to
+ * DataFusion as the join filter, :206-218 ANDs it to the IS_COMPATIBLE conjunction): a conjunction of ID-level predicates
+ * over the RESULT row — preds[i].col / col2 index the output schema (lhs columns, then rhs-only columns), a shared variable of
+ * a compatible join is its COALESCE (value_from_joined, :321-352).  Inner: the join followed by the filter.  Left
+ * (OPTIONAL { P FILTER(e) }): an lhs row is padded with NULLs iff no compatible rhs row passes the filter (SPARQL 1.1 §18.5
+ * LeftJoin).  Disjoint schemas with a filter are a filtered product (rewrite.rs:76 takes the cross-join shortcut only
+ * without a filter).  n_preds = 0 is rfgpu_sparql_join.  Row order unspecified. */
+int32_t rfgpu_sparql_join_filter(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_table* rhs, int32_t join_type,
+                                 const rfgpu_filter_pred* preds, int32_t n_preds, rfgpu_table** out);
 /* SPARQL MINUS: MinusNode + MinusLoweringRule (lib/logical/src/minus/rewrite.rs:58-141) — a LeftAnti
  * join that removes an lhs row iff some rhs row is compatible with it on every shared variable (equal, or NULL on either
  * side) AND at least one shared variable is bound on both sides.  No shared variable → the lhs unchanged (:61-64).

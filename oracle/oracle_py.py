@@ -398,3 +398,92 @@ def decode_plain_terms(terms, ids):
               pa.field("data_type", pa.utf8(), True), pa.field("language_tag", pa.utf8(), True)]
     kids = [pa.array(tt, pa.uint8()), pa.array(val, pa.utf8()), pa.array(dt, pa.utf8()), pa.array(lang, pa.utf8())]
     return pa.StructArray.from_arrays(kids, fields=fields, mask=pa.array(mask, pa.bool_()) if len(mask) else None)
+
+
+# ---------------------------------------------------------------- SparqlJoinNode with a join filter
+def _eval_pred(p, col):
+    """one ID-level predicate on value matrices; SQL three-valued logic: a comparison with NULL (0) is not true"""
+    v = col(p.col)
+    if p.op == F.F_EQ_CONST:
+        return (v == p.value) & (v != 0)
+    if p.op == F.F_NE_CONST:
+        return (v != p.value) & (v != 0)
+    if p.op in (F.F_EQ_COL, F.F_NE_COL):
+        w = col(p.col2)
+        return ((v == w) if p.op == F.F_EQ_COL else (v != w)) & (v != 0) & (w != 0)
+    if p.op == F.F_BETWEEN:
+        return (v >= p.value) & (v <= p.hi) & (v != 0)
+    if p.op == F.F_IN:
+        return np.isin(v, np.asarray(p.ids, dtype=np.uint32)) & (v != 0)
+    if p.op == F.F_IS_NULL:
+        return v == 0
+    if p.op == F.F_IS_NOT_NULL:
+        return v != 0
+    raise ValueError(p.op)
+
+
+def sparql_join_filtered(l: OTable, r: OTable, join_type, preds: Sequence[FPred], block: int = 256) -> OTable:
+    """SparqlJoinNode with its optional filter (lib/logical/src/join/logical.rs:50), evaluated as the definition — SPARQL 1.1
+    §18.5: Join / LeftJoin(Ω1, Ω2, expr) = { merge(μ1, μ2) | μ1, μ2 compatible and expr(merge(μ1, μ2)) is true } and, for
+    LeftJoin, ∪ { μ1 | no such μ2 } — i.e. what the reference's lowering computes (join/rewrite.rs:149-161: the filter is
+    DataFusion's join filter; :206-218: ANDed to the IS_COMPATIBLE conjunction; filter columns are the joined row's,
+    COALESCE(lhs.k, rhs.k) for shared variables: value_from_joined :321-352).  `preds` index the result schema (lhs columns,
+    then rhs-only columns).  Nested loop over row pairs, blocked over lhs rows."""
+    schema = sparql_join(OTable(l.names, l.nullable, [c[:0] for c in l.cols]),
+                         OTable(r.names, r.nullable, [c[:0] for c in r.cols]), join_type, "hash")[0]
+    shared = [n for n in l.names if n in r.names]
+    r_only = [n for n in r.names if n not in shared]
+    assert schema.names == list(l.names) + r_only
+    nl_, nr_ = l.num_rows, r.num_rows
+    out = [[] for _ in schema.names]
+    rcol = {n: np.asarray(r.cols[r.names.index(n)], np.uint32) for n in r.names}
+    for lo in range(0, nl_, block):
+        hi = min(nl_, lo + block)
+        lblk = {n: np.asarray(l.cols[l.names.index(n)], np.uint32)[lo:hi] for n in l.names}
+        ok = np.ones((hi - lo, nr_), dtype=bool)
+        for k in shared:
+            x, y = lblk[k][:, None], rcol[k][None, :]
+            ok &= (x == 0) | (y == 0) | (x == y)
+
+        def col(i, lblk=lblk):
+            n = schema.names[i]
+            if n in shared:
+                x, y = lblk[n][:, None], rcol[n][None, :]
+                return np.where(x != 0, x, y) + np.zeros((1, nr_), np.uint32)
+            if n in lblk:
+                return lblk[n][:, None] + np.zeros((1, nr_), np.uint32)
+            return rcol[n][None, :] + np.zeros((len(lblk[l.names[0]]), 1), np.uint32)
+        for p in preds:
+            ok &= _eval_pred(p, col)
+        li, rj = np.nonzero(ok)
+        for i, n in enumerate(schema.names):
+            out[i].append(col(i)[li, rj] if len(li) else np.zeros(0, np.uint32))
+        if join_type == F.JOIN_LEFT:
+            lonely = ~ok.any(axis=1)
+            for i, n in enumerate(schema.names):
+                out[i].append(lblk[n][lonely] if n in lblk else np.zeros(int(lonely.sum()), np.uint32))
+    cols = [np.concatenate(c).astype(np.uint32) if c else np.zeros(0, np.uint32) for c in out]
+    return OTable(schema.names, schema.nullable, cols)
+
+
+def sparql_join_filtered_composed(l: OTable, r: OTable, join_type, preds: Sequence[FPred]) -> OTable:
+    """The way rdf_fusion_b200/csrc/join.cu composes the filtered Left join from existing operators (lhs + row number ->
+    inner join -> filter -> anti join on the row number -> concatenation), restated with the oracle's own operators so the
+    composition can be checked against the definition above on the CPU."""
+    if join_type == F.JOIN_INNER:
+        return filter_table(sparql_join(l, r, F.JOIN_INNER, "hash")[0], preds)
+    nl_ = len(l.names)
+    lr = OTable(list(l.names) + ["\x01rid"], list(l.nullable) + [False], list(l.cols) + [np.arange(1, l.num_rows + 1, dtype=np.uint32)])
+    j = sparql_join(lr, r, F.JOIN_INNER, "hash")[0]
+    shifted = [FPred(p.op, p.col + (p.col >= nl_), p.col2 + (p.col2 >= nl_), p.value, p.hi, p.ids) for p in preds]
+    jf = filter_table(j, shifted)
+    u = sparql_exists(lr, OTable(["\x01rid"], [False], [jf.cols[nl_]]), negated=True)
+    names = [n for i, n in enumerate(j.names) if i != nl_]
+    nullable = list(l.nullable) + [True] * (len(names) - nl_)
+    cols = []
+    for i, n in enumerate(j.names):
+        if i == nl_:
+            continue
+        tail = u.cols[i] if i < nl_ else np.zeros(u.num_rows, np.uint32)
+        cols.append(np.concatenate([jf.cols[i], tail]).astype(np.uint32))
+    return OTable(names, nullable, cols)

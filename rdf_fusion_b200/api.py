@@ -462,9 +462,16 @@ class Table:
         self.ctx.check(self.ctx.lib.rfgpu_filter(self.ctx.h, self.h, arr, len(preds), C.byref(out)))
         return Table(self.ctx, out)
 
-    def join(self, rhs: "Table", join_type: int = F.JOIN_INNER) -> "Table":
+    def join(self, rhs: "Table", join_type: int = F.JOIN_INNER, filter: Optional[Sequence[FPred]] = None) -> "Table":
+        """SparqlJoinNode; `filter`: its optional join filter, ID-level predicates whose column indexes are those of the
+        result schema (lhs columns, then rhs-only columns) — OPTIONAL { P FILTER(e) } for a Left join."""
         out = C.c_void_p()
-        self.ctx.check(self.ctx.lib.rfgpu_sparql_join(self.ctx.h, self.h, rhs.h, join_type, C.byref(out)))
+        if filter:
+            arr, keep = make_filter_preds(filter)
+            self.ctx.check(self.ctx.lib.rfgpu_sparql_join_filter(self.ctx.h, self.h, rhs.h, join_type, arr, len(filter),
+                                                                 C.byref(out)))
+        else:
+            self.ctx.check(self.ctx.lib.rfgpu_sparql_join(self.ctx.h, self.h, rhs.h, join_type, C.byref(out)))
         return Table(self.ctx, out)
 
     def minus(self, rhs: "Table") -> "Table":

@@ -841,6 +841,92 @@ rfgpu_table* semi_anti_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_ta
   return T.release();
 }
 
+// SparqlJoinNode with a join filter (lib/logical/src/join/logical.rs:50, join/rewrite.rs:149-161,206-218): the filter is
+// part of the join condition, its columns are the joined row's (value_from_joined: COALESCE for shared variables of a
+// compatible join, :321-352).  Inner: the join followed by the filter.  Left (OPTIONAL { P FILTER(e) }): an lhs row whose
+// every partner fails the filter is kept, padded with NULLs (SPARQL 1.1 §18.5 LeftJoin).  Composed from operators that
+// exist already — no new kernel: lhs + hidden row number → inner join → filter → the lhs rows whose number did not
+// survive (anti join on the row number) → concatenation.
+rfgpu_table* sparql_join_filter(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table* R, int join_type,
+                                const rfgpu_filter_pred* preds, int n_preds) {
+  RF_REQUIRE(join_type == RFGPU_JOIN_INNER || join_type == RFGPU_JOIN_LEFT, RFGPU_E_INVALID, "bad join type");
+  if (n_preds == 0) return sparql_join(ctx, L, R, join_type);
+  const bool left = join_type == RFGPU_JOIN_LEFT;
+  const size_t nl = L->cols.size();
+  static const char* kRid = "\x01rid";  // not a SPARQL variable name
+  RF_REQUIRE(find_col(L, kRid) < 0 && find_col(R, kRid) < 0, RFGPU_E_INVALID, "reserved column name");
+  auto run_filter = [&](const rfgpu_table* t, const std::vector<rfgpu_filter_pred>& ps) {
+    rfgpu_table* out = nullptr;
+    int32_t rc = rfgpu_filter(ctx, t, ps.data(), (int32_t)ps.size(), &out);
+    if (rc != RFGPU_OK) throw Error(rc, ctx->err);
+    return std::unique_ptr<rfgpu_table>(out);
+  };
+  if (!left) {
+    std::unique_ptr<rfgpu_table> J(sparql_join(ctx, L, R, RFGPU_JOIN_INNER));
+    const int algo = ctx->last_join_algo, phys = ctx->last_join_phys;
+    auto out = run_filter(J.get(), std::vector<rfgpu_filter_pred>(preds, preds + n_preds));
+    ctx->last_join_algo = algo;
+    ctx->last_join_phys = phys;
+    return out.release();
+  }
+  RF_REQUIRE(nl + 1 <= (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 15 lhs columns in a filtered left join");
+  // lhs with its row number as one more (non-nullable) column
+  std::unique_ptr<rfgpu_table> Lr(new_table());
+  Lr->cols = L->cols;
+  Lr->rows = L->rows;
+  Lr->sorted_col = L->sorted_col;
+  {
+    Column c;
+    c.name = kRid;
+    c.owner = alloc_col(ctx, L->rows);
+    c.data = c.owner->as<uint32_t>();
+    KernelScope ks(ctx, "k_iota");
+    k_iota<<<grid_for(ctx, L->rows), 256, 0, ctx->stream()>>>(c.owner->as<uint32_t>(), L->rows);
+    Lr->cols.push_back(std::move(c));
+  }
+  std::unique_ptr<rfgpu_table> J(sparql_join(ctx, Lr.get(), R, RFGPU_JOIN_INNER));  // (lhs…, rid, rhs-only…)
+  const int algo = ctx->last_join_algo, phys = ctx->last_join_phys;
+  const size_t n_out = J->cols.size() - 1;
+  std::vector<rfgpu_filter_pred> ps(preds, preds + n_preds);
+  for (auto& p : ps) {  // the caller's indexes are those of the result schema, which has no row-number column
+    RF_REQUIRE(p.col >= 0 && (size_t)p.col < n_out && p.col2 >= 0 && (size_t)p.col2 < std::max<size_t>(n_out, 1), RFGPU_E_INVALID,
+               "join filter column out of range");
+    if ((size_t)p.col >= nl) p.col++;
+    if ((size_t)p.col2 >= nl) p.col2++;
+  }
+  auto Jf = run_filter(J.get(), ps);
+  // lhs rows none of whose partners passed
+  std::unique_ptr<rfgpu_table> K(new_table());
+  K->cols.push_back(Jf->cols[nl]);
+  K->rows = Jf->rows;
+  std::unique_ptr<rfgpu_table> U(semi_anti_join(ctx, Lr.get(), K.get(), SemiMode::kNotExists));
+  const uint64_t total = Jf->rows + U->rows;
+  RF_REQUIRE(total < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "join output exceeds 2^32-2 rows on one GPU");
+  std::unique_ptr<rfgpu_table> T(new_table());
+  for (size_t c = 0; c < J->cols.size(); c++) {
+    if (c == nl) continue;
+    Column o;
+    o.name = J->cols[c].name;
+    o.nullable = c < nl ? L->cols[c].nullable : true;  // rhs-only columns of a Left join are nullable (join/logical.rs:251-279)
+    o.owner = alloc_col(ctx, total);
+    o.data = o.owner->as<uint32_t>();
+    uint32_t* dst = o.owner->as<uint32_t>();
+    if (Jf->rows) RF_CUDA(cudaMemcpyAsync(dst, Jf->cols[c].data, Jf->rows * 4, cudaMemcpyDeviceToDevice, ctx->stream()));
+    if (U->rows) {
+      if (c < nl)
+        RF_CUDA(cudaMemcpyAsync(dst + Jf->rows, U->cols[c].data, U->rows * 4, cudaMemcpyDeviceToDevice, ctx->stream()));
+      else
+        RF_CUDA(cudaMemsetAsync(dst + Jf->rows, 0, U->rows * 4, ctx->stream()));
+    }
+    T->cols.push_back(std::move(o));
+  }
+  T->rows = total;
+  ctx->sync();
+  ctx->last_join_algo = algo;
+  ctx->last_join_phys = phys;
+  return T.release();
+}
+
 }  // namespace rf
 
 extern "C" {
@@ -851,6 +937,15 @@ int32_t rfgpu_sparql_join(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_ta
   RF_REQUIRE(ctx && lhs && rhs && out, RFGPU_E_INVALID, "NULL argument");
   RF_CUDA(cudaSetDevice(ctx->core->device));
   *out = rf::sparql_join(ctx, lhs, rhs, join_type);
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_sparql_join_filter(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_table* rhs, int32_t join_type,
+                                 const rfgpu_filter_pred* preds, int32_t n_preds, rfgpu_table** out) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx && lhs && rhs && out && n_preds >= 0 && (preds || n_preds == 0), RFGPU_E_INVALID, "NULL / negative argument");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  *out = rf::sparql_join_filter(ctx, lhs, rhs, join_type, preds, n_preds);
   RF_API_END(ctx)
 }
 

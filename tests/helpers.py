@@ -138,6 +138,10 @@ class OracleBackend:
         r = self.o.filter_table(self.make(*t), preds)
         return r.names, r.nullable, r.cols
 
+    def join_filtered(self, l, r, jt, preds):
+        t = self.o.sparql_join_filtered(self.make(*l), self.make(*r), jt, preds)
+        return t.names, t.nullable, t.cols
+
     def minus(self, l, r):
         t = self.o.sparql_minus(self.make(*l), self.make(*r))
         return t.names, t.nullable, t.cols
@@ -181,6 +185,9 @@ class GpuBackend:
     def filter(self, t, preds):
         return self._out(self.make(*t).filter(preds))
 
+    def join_filtered(self, l, r, jt, preds):
+        return self._out(self.make(*l).join(self.make(*r), jt, filter=preds))
+
     def minus(self, l, r):
         return self._out(self.make(*l).minus(self.make(*r)))
 
@@ -192,6 +199,24 @@ class GpuBackend:
 
     def group_count(self, t, keys, counted, name):
         return self._out(self.make(*t).group_count(keys, counted, name))
+
+
+def _resolve_preds(preds, names):
+    """plan-level predicates (by variable name) -> FPreds on the columns of a table with these names"""
+    out = []
+    for p in preds:
+        i = names.index(p["var"])
+        if p["op"] in ("ne_col", "eq_col"):  # ?a != ?b / ?a = ?b on IRIs: id (in)equality
+            out.append(rf.FPred(F.F_NE_COL if p["op"] == "ne_col" else F.F_EQ_COL, i, col2=names.index(p["var2"])))
+        elif p["op"] == "between":  # id range (a value range when the ids ascend with the value, as in generate_bsbm_like)
+            out.append(rf.FPred(F.F_BETWEEN, i, value=int(p["lo"]), hi=int(p["hi"])))
+        elif p["op"] == "in":  # ?v = c1 || ?v = c2 on IRIs: id equality (patterns/rewrite.rs:68-148)
+            out.append(rf.FPred(F.F_IN, i, ids=[int(x) for x in p["ids"]]))
+        elif p["op"] == "eq_const":  # ?v = c where the term of c has one lexical form in the data: id equality
+            out.append(rf.FPred(F.F_EQ_CONST, i, value=int(p["id"])) if p["id"] is not None else rf.FPred(F.F_IN, i, ids=[]))
+        else:
+            out.append(rf.FPred({"is_null": F.F_IS_NULL, "is_not_null": F.F_IS_NOT_NULL}[p["op"]], i))
+    return out
 
 
 def _empty(names, nullable):
@@ -224,7 +249,11 @@ def eval_plan(be, node):
         return be.scan(instr)
     if op in ("join", "leftjoin"):
         l, r = eval_plan(be, node["l"]), eval_plan(be, node["r"])
-        return be.join(l, r, F.JOIN_LEFT if op == "leftjoin" else F.JOIN_INNER)
+        jt = F.JOIN_LEFT if op == "leftjoin" else F.JOIN_INNER
+        if node.get("filter"):  # SparqlJoinNode.filter: predicates over the joined row (lhs columns, then rhs-only columns)
+            out_names = list(l[0]) + [n for n in r[0] if n not in l[0]]
+            return be.join_filtered(l, r, jt, _resolve_preds(node["filter"], out_names))
+        return be.join(l, r, jt)
     if op == "minus":  # MinusNode -> LeftAnti join (minus/rewrite.rs:58-93)
         return be.minus(eval_plan(be, node["l"]), eval_plan(be, node["r"]))
     if op == "exists":  # FILTER [NOT] EXISTS -> semi / anti join on compatibility (expr_builder_context.rs:223-338)
@@ -259,21 +288,7 @@ def eval_plan(be, node):
         return names, nullable, cols
     if op == "filter":
         t = eval_plan(be, node["in"])
-        preds = []
-        for p in node["preds"]:
-            if p["op"] in ("ne_col", "eq_col"):  # ?a != ?b / ?a = ?b on IRIs: id (in)equality
-                preds.append(rf.FPred(F.F_NE_COL if p["op"] == "ne_col" else F.F_EQ_COL, t[0].index(p["var"]),
-                                      col2=t[0].index(p["var2"])))
-                continue
-            if p["op"] == "between":  # id range (a value range when the ids ascend with the value, as in generate_bsbm_like)
-                preds.append(rf.FPred(F.F_BETWEEN, t[0].index(p["var"]), value=int(p["lo"]), hi=int(p["hi"])))
-                continue
-            if p["op"] == "in":  # ?v = c1 || ?v = c2 on IRIs: id equality (patterns/rewrite.rs:68-148)
-                preds.append(rf.FPred(F.F_IN, t[0].index(p["var"]), ids=[int(i) for i in p["ids"]]))
-                continue
-            code = {"is_null": F.F_IS_NULL, "is_not_null": F.F_IS_NOT_NULL}[p["op"]]
-            preds.append(rf.FPred(code, t[0].index(p["var"])))
-        return be.filter(t, preds)
+        return be.filter(t, _resolve_preds(node["preds"], t[0]))
     if op == "filter_any_bound":  # FILTER(bound(a) || bound(b) ..): a disjunction stays a host FilterExec
         names, nullable, cols = eval_plan(be, node["in"])
         keep = np.zeros(len(cols[0]) if cols else 0, dtype=bool)
