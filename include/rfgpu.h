@@ -320,6 +320,16 @@ int32_t rfgpu_plain_terms_sizes(const rfgpu_plain_terms* p, uint64_t* rows, uint
 int32_t rfgpu_plain_terms_export(rfgpu_ctx* ctx, const rfgpu_plain_terms* p, uint8_t* term_type, uint8_t* const validity[3],
                                  int32_t* const offsets[3], uint8_t* const data[3]);
 
+/* Value-level filters without decoding (the other half of §8f-2: every value FILTER of the reference starts with ENC_TV(col),
+ * lib/functions/src/builtin/encoding/with_typed_value_encoding.rs): appends the column `name` = table[t.col[i]] to `t` (ids
+ * outside [0, n_table), NULL ids and zero entries read as NULL).  With a table that maps an object id to the 1-based RANK of
+ * its numeric value among the dictionary's numeric literals (0 for every other term; built by the host next to the
+ * dictionary), `?x > c` is RFGPU_F_BETWEEN(rank(c) + 1, MAX) on the new column — an ID-level predicate for rfgpu_filter or
+ * rfgpu_sparql_join_filter — and a non-numeric ?x fails the comparison like SPARQL's type error does.  `table` is host
+ * memory, or device memory when on_device != 0. */
+int32_t rfgpu_table_lookup(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t col, const uint32_t* table, uint32_t n_table,
+                           int32_t on_device, const char* name, rfgpu_table** out);
+
 /* physical operator of the last rfgpu_group_count / rfgpu_distinct */
 typedef enum {
   RFGPU_AGG_PHYS_NONE = 0,

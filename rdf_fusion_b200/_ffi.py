@@ -145,6 +145,8 @@ SIGNATURES = {
     "rfgpu_timer_stop": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
     "rfgpu_flush_l2": (C.c_int32, [C.c_void_p]),
     "rfgpu_last_agg_phys": (C.c_int32, [C.c_void_p]),
+    "rfgpu_table_lookup": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_uint32, C.c_int32, C.c_char_p,
+                                       C.POINTER(C.c_void_p)]),
     "rfgpu_sparql_join_filter": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(FilterPred), C.c_int32,
                                              C.POINTER(C.c_void_p)]),
     "rfgpu_dict_create": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

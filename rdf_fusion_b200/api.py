@@ -534,6 +534,16 @@ class Table:
     def last_join_phys(self) -> int:
         return int(self.ctx.lib.rfgpu_last_join_phys(self.ctx.h))
 
+    def lookup(self, col, table: np.ndarray, name: str) -> "Table":
+        """This table plus the column `name` = table[col] (rfgpu_table_lookup): e.g. the numeric rank of every object id, so
+        that a value comparison becomes an id-level BETWEEN on the new column."""
+        i = self.names.index(col) if isinstance(col, str) else int(col)
+        tb = _u32(table)
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_table_lookup(self.ctx.h, self.h, i, tb.ctypes.data if tb.size else None, len(tb), 0,
+                                                       name.encode(), C.byref(out)))
+        return Table(self.ctx, out)
+
     @property
     def last_agg_phys(self) -> int:
         return int(self.ctx.lib.rfgpu_last_agg_phys(self.ctx.h))
@@ -595,6 +605,42 @@ def pack_terms(terms: Sequence[tuple]):
         aux_off[a + 1] = aux_off[a] + len(b)
     return (term_type, value_off, np.frombuffer(b"".join(values), np.uint8), datatype, language,
             aux_off, np.frombuffer(b"".join(aux_list), np.uint8))
+
+
+XSD = "http://www.w3.org/2001/XMLSchema#"
+NUMERIC_TYPES = tuple(XSD + t for t in ("integer", "decimal", "float", "double", "long", "int", "short", "byte",
+                                        "nonNegativeInteger", "positiveInteger", "nonPositiveInteger", "negativeInteger",
+                                        "unsignedLong", "unsignedInt", "unsignedShort", "unsignedByte"))
+
+
+def numeric_rank_table(terms: Sequence[tuple]) -> np.ndarray:
+    """table[id] = 1-based dense rank of the numeric value of term id among the numeric literals of the dictionary (equal
+    values share a rank whatever their datatype or lexical form: "2"^^xsd:integer = "2.0"^^xsd:decimal), 0 for every other
+    term and for ill-formed numerics.  Host-side dictionary preparation, done once per load; exact (Fraction) for integers
+    and decimals, float for xsd:float / xsd:double."""
+    from fractions import Fraction
+    vals = {}
+    for i, t in enumerate(terms, start=1):
+        if t[0] != "lit" or t[2] not in NUMERIC_TYPES:
+            continue
+        try:
+            if t[2] in (XSD + "float", XSD + "double"):
+                f = float(t[1])
+                if f != f or f in (float("inf"), float("-inf")):
+                    continue
+                vals[i] = Fraction(f)
+            else:
+                vals[i] = Fraction(t[1])
+        except (ValueError, ZeroDivisionError):
+            continue
+    table = np.zeros(len(terms) + 1, np.uint32)
+    rank, prev = 0, None
+    for i in sorted(vals, key=lambda k: vals[k]):
+        if vals[i] != prev:
+            rank += 1
+            prev = vals[i]
+        table[i] = rank
+    return table
 
 
 class Dictionary:

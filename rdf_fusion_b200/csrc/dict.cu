@@ -9,6 +9,8 @@
 //   exclusive scan  lengths → Arrow offsets (filter.cu)
 //   k_dict_copy     one warp per row copies the value bytes and the two short strings, coalesced along the bytes
 // The encode direction (term → id: string hashing into the DashMap, :309-329) stays on the host.
+#include <algorithm>
+
 #include "rf_common.hpp"
 
 struct rfgpu_dict {
@@ -125,6 +127,17 @@ __global__ void __launch_bounds__(256) k_dict_copy(const __grid_constant__ Decod
       const uint32_t o = A.off[2][row], len = A.off[2][row + 1] - o;
       warp_copy_bytes(A.data[2] + o, A.D.aux_bytes + __ldg(A.D.aux_off + lg), len, lane);
     }
+  }
+}
+
+// out[i] = table[ids[i]] for ids inside the table, else 0 (NULL)
+__global__ void __launch_bounds__(256) k_lookup(const uint32_t* __restrict__ ids, uint64_t n, const uint32_t* __restrict__ table,
+                                                uint32_t n_table, uint32_t* __restrict__ out) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const uint32_t id = __ldg(ids + i);
+    out[i] = id < n_table ? __ldg(table + id) : 0u;
   }
 }
 
@@ -250,6 +263,41 @@ int32_t rfgpu_dict_decode(rfgpu_ctx* ctx, const rfgpu_dict* d, const rfgpu_table
   ctx->m.algorithmic_bytes += 4ull * n + 2 * (P->bytes[0] + P->bytes[1] + P->bytes[2]) + 13ull * n;
   ctx->sync();
   *out = P.release();
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_table_lookup(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t col, const uint32_t* table, uint32_t n_table,
+                           int32_t on_device, const char* name, rfgpu_table** out) {
+  RF_API_BEGIN
+  using namespace rf;
+  RF_REQUIRE(ctx && t && out && name && (table || n_table == 0), RFGPU_E_INVALID, "NULL argument");
+  RF_REQUIRE(col >= 0 && col < (int32_t)t->cols.size(), RFGPU_E_INVALID, "column index out of range");
+  RF_REQUIRE(find_col(t, name) < 0, RFGPU_E_INVALID, std::string("duplicate column name ") + name);
+  RF_REQUIRE(t->cols.size() < (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 columns");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  BufRef staged;
+  const uint32_t* d_table = table;
+  if (!on_device) {
+    staged = upload(ctx, table, (size_t)n_table * 4);
+    d_table = staged->as<uint32_t>();
+  }
+  std::unique_ptr<rfgpu_table> r(new_table());
+  r->cols = t->cols;
+  r->rows = t->rows;
+  r->sorted_col = t->sorted_col;
+  Column c;
+  c.name = name;
+  c.nullable = true;  // ids outside the table, NULL ids and entries that are 0 all read as NULL
+  c.owner = alloc_col(ctx, t->rows);
+  c.data = c.owner->as<uint32_t>();
+  if (t->rows) {
+    KernelScope ks(ctx, "k_lookup", 8ull * t->rows);
+    uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(t->rows, 256), (uint64_t)ctx->core->num_sms * 16));
+    k_lookup<<<grid, 256, 0, ctx->stream()>>>(t->cols[col].data, t->rows, d_table, n_table, c.owner->as<uint32_t>());
+  }
+  r->cols.push_back(std::move(c));
+  ctx->sync();
+  *out = r.release();
   RF_API_END(ctx)
 }
 

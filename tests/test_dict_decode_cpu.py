@@ -85,3 +85,14 @@ def test_host_half_of_the_product_path_matches_the_oracle(oracle, n_terms, n_row
     assert got.to_pylist() == exp.to_pylist() and got.equals(exp)
     for k in range(4):
         assert got.field(k).null_count == exp.field(k).null_count
+
+
+def test_numeric_rank_table():
+    """value order across datatypes and lexical forms; non-numeric and ill-formed terms have no rank"""
+    from rdf_fusion_b200 import numeric_rank_table
+    X = "http://www.w3.org/2001/XMLSchema#"
+    terms = [("lit", "2", X + "integer"), ("nn", "http://e/a"), ("lit", "2.0", X + "decimal"), ("lit", "-1", X + "integer"),
+             ("lit", "1e1", X + "double"), ("lit", "x", X + "integer"), ("lit", "3", X + "string"), ("lang", "4", "en"),
+             ("lit", "0.1", X + "decimal"), ("lit", "NaN", X + "double"), ("lit", "02", X + "int")]
+    t = numeric_rank_table(terms)
+    assert t.tolist() == [0, 3, 0, 3, 1, 4, 0, 0, 0, 2, 0, 3]

@@ -36,7 +36,7 @@ def emu():
         "rfgpu_last_error": (C.c_char_p, [vp]),
     }
     for name in ("rfgpu_table_sort", "rfgpu_store_build", "rfgpu_dict_create", "rfgpu_dict_release", "rfgpu_dict_decode",
-                 "rfgpu_plain_terms_release", "rfgpu_plain_terms_sizes", "rfgpu_plain_terms_export"):
+                 "rfgpu_plain_terms_release", "rfgpu_plain_terms_sizes", "rfgpu_plain_terms_export", "rfgpu_table_lookup"):
         sig[name] = F.SIGNATURES[name]  # the product's own bindings
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -209,3 +209,20 @@ def test_dictionary_decode_matches_the_oracle(emu, oracle, n_terms, n_rows):
     assert got.type == exp.type and got.null_count == exp.null_count and got.equals(exp)
     rc, msg = _decode(emu, terms, np.array([1, len(terms) + 3], np.uint32))
     assert rc == F.E_INVALID and str(len(terms) + 3) in msg
+
+
+def test_lookup_column(emu):
+    """rfgpu_table_lookup: table[id] for ids inside the table, NULL (0) for NULL ids and ids beyond it"""
+    rng = np.random.default_rng(8)
+    for n, nt in [(0, 5), (1, 1), (33, 0), (5000, 700)]:
+        ids = rng.integers(0, nt + 40, n).astype(np.uint32)
+        table = rng.integers(0, 1000, nt).astype(np.uint32)
+        t = _table(emu, [ids, ids[::-1].copy()])
+        out = vp()
+        _ok(emu, emu.rfgpu_table_lookup(emu.ctx, t, 1, table.ctypes.data if nt else None, nt, 0, b"rank", C.byref(out)))
+        got = _cols(emu, out)
+        assert len(got) == 3 and np.array_equal(got[0], ids)
+        want = np.where(ids[::-1] < nt, table[np.minimum(ids[::-1], max(nt - 1, 0))] if nt else 0, 0).astype(np.uint32)
+        assert np.array_equal(got[2], want)
+        emu.emu_table_release(out)
+        emu.emu_table_release(t)

@@ -67,3 +67,37 @@ def test_decode_after_a_join(ctx, oracle):
     cols = j.to_numpy()
     for name, col in zip(j.names, cols):
         assert d.decode(j, name).equals(oracle.decode_plain_terms(terms, col))
+
+
+def test_value_filter_through_a_rank_lookup(ctx):
+    """FILTER(?p1 > c) / FILTER(?p3 < c) of BSBM Explore Q3 without decoding: object ids assigned in arbitrary order, the
+    numeric rank of every id looked up on the device (rfgpu_table_lookup), the comparison an id-level BETWEEN on the rank
+    column — against numpy on the values themselves; a non-numeric object fails the comparison (SPARQL type error)."""
+    from rdf_fusion_b200 import _ffi as F
+    rng = np.random.default_rng(17)
+    X = "http://www.w3.org/2001/XMLSchema#"
+    n_terms = 4000
+    values = rng.integers(-500, 500, n_terms)
+    kinds = rng.integers(0, 4, n_terms)  # integer, decimal with a fraction digit, double, IRI
+    terms = []
+    for v, k in zip(values, kinds):
+        terms.append([("lit", str(v), X + "integer"), ("lit", f"{v}.0", X + "decimal"), ("lit", f"{v}e0", X + "double"),
+                      ("nn", f"http://example.com/{v}")][k])
+    rank = rf.numeric_rank_table(terms)
+    n = 60000
+    obj = rng.integers(0, n_terms + 1, n).astype(np.uint32)
+    T = ctx.import_table({"product": np.arange(1, n + 1, dtype=np.uint32), "p1": obj}, {"p1": True})
+    withrank = T.lookup("p1", rank, "p1_rank")
+    assert withrank.names == ["product", "p1", "p1_rank"] and withrank.nullable[2]
+    val = np.concatenate([[0], values]).astype(np.int64)
+    numeric = np.concatenate([[False], kinds != 3])
+    for c in (-600, -37, 0, 123, 499, 700):
+        rank_c = int(np.unique(values[(kinds != 3) & (values <= c)]).size)  # rank of the largest value <= c (0: none)
+        gt = withrank.filter([rf.FPred(F.F_BETWEEN, 2, value=rank_c + 1, hi=0xFFFFFFFF)])
+        want = numeric[obj] & (val[obj] > c)
+        assert gt.num_rows == int(want.sum()), c
+        if gt.num_rows:
+            assert np.array_equal(gt.to_numpy()[0], np.arange(1, n + 1, dtype=np.uint32)[want])
+        if rank_c:
+            le = withrank.filter([rf.FPred(F.F_BETWEEN, 2, value=1, hi=rank_c)])
+            assert le.num_rows == int((numeric[obj] & (val[obj] <= c)).sum())
