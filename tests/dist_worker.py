@@ -21,7 +21,8 @@ import torch.distributed as dist  # noqa: E402
 import rdf_fusion_b200 as rf  # noqa: E402
 from oracle import oracle_py as orc  # noqa: E402
 from rdf_fusion_b200 import _ffi as F  # noqa: E402
-from rdf_fusion_b200.dist import exchange_layout, init_comm, owner_of_subject, partition_np  # noqa: E402
+from rdf_fusion_b200.dist import (exchange_layout, init_comm, owner_of_subject, partition_np,  # noqa: E402
+                                  skew_aware_join)
 
 
 def main():
@@ -109,6 +110,63 @@ def main():
     results["optional"] = rows(join(shuffle(scan("a", p1, "b"), "b"), scan("b", p2, "c"), F.JOIN_LEFT))
     results["star"] = rows(join(scan("s", p1, "x"), scan("s", p2, "y"), F.JOIN_INNER))
 
+    # skewed join variable (BASELINE configs[4]): ?a p1 ?b [OPTIONAL] { ?b p2 ?c } with Zipf objects — the heavy ?b values are
+    # not shuffled: their rhs rows are replicated (dist.skew_aware_join).  GPU mode runs it only on request until it has been
+    # validated on a multi-GPU box.
+    if mode == "cpu" or os.environ.get("RFGPU_TEST_SKEW") == "1":
+        def gather(obj):
+            box = [None] * world
+            dist.all_gather_object(box, obj)
+            return box
+
+        _shuffle, _join = shuffle, join
+
+        class Ops:
+            if mode == "gpu":
+                @staticmethod
+                def num_rows(t): return t.num_rows
+
+                @staticmethod
+                def histogram(t, key):
+                    h = t.group_count([key], None, "n")
+                    k, c = h.to_numpy() if h.num_rows else (np.zeros(0, np.uint32), np.zeros(0, np.uint32))
+                    return k, c
+
+                @staticmethod
+                def semi(t, key, ids, negated):
+                    return t.exists(ctx.import_table({key: np.asarray(ids, np.uint32)}), negated)
+
+                @staticmethod
+                def to_host(t): return t.names, t.nullable, (t.to_numpy() if t.num_rows else [np.zeros(0, np.uint32)] * len(t.names))
+
+                @staticmethod
+                def from_host(names, nullable, cols): return ctx.import_table(dict(zip(names, cols)), dict(zip(names, nullable)))
+            else:
+                @staticmethod
+                def num_rows(t): return t.num_rows
+
+                @staticmethod
+                def histogram(t, key):
+                    h = orc.group_count(t, [key], None, "n")
+                    return h.cols[0], h.cols[1]
+
+                @staticmethod
+                def semi(t, key, ids, negated):
+                    return orc.sparql_exists(t, orc.OTable([key], [False], [np.asarray(ids, np.uint32)]), negated, block=4096)
+
+                @staticmethod
+                def to_host(t): return t.names, t.nullable, t.cols
+
+                @staticmethod
+                def from_host(names, nullable, cols): return orc.OTable(names, nullable, cols)
+            shuffle = staticmethod(_shuffle)
+            join = staticmethod(_join)
+        for name, jt in (("skew_inner", F.JOIN_INNER), ("skew_optional", F.JOIN_LEFT)):
+            parts, heavy = skew_aware_join(scan("a", p1, "b"), scan("b", p2, "c"), "b", jt, Ops, world, gather, heavy_factor=0.02)
+            assert world == 1 or len(heavy) > 0, "the test graph must have heavy join keys"
+            got = [rows(t) for t in parts]
+            results[name] = (got[0][0], [np.concatenate([np.asarray(g[1][c]) for g in got]) for c in range(len(got[0][0]))])
+
     if mode == "gpu" and world > 1:
         want_paths = {"p2p": {F.SHUFFLE_P2P}, "nccl": {F.SHUFFLE_NCCL}}.get(exchange)
         if want_paths is not None:
@@ -128,6 +186,9 @@ def main():
             "optional": orc.sparql_join(oscan("a", p1, "b"), oscan("b", p2, "c"), F.JOIN_LEFT, "hash")[0],
             "star": orc.sparql_join(oscan("s", p1, "x"), oscan("s", p2, "y"), F.JOIN_INNER, "hash")[0],
         }
+        if "skew_inner" in results:
+            exp["skew_inner"] = orc.sparql_join(oscan("a", p1, "b"), oscan("b", p2, "c"), F.JOIN_INNER, "hash")[0]
+            exp["skew_optional"] = exp["optional"]
         for name, e in exp.items():
             names = gathered[0][name][0]
             assert names == e.names, (name, names, e.names)

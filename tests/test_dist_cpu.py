@@ -48,5 +48,44 @@ def test_two_rank_chain_join_gloo():
            "--master-port", "29541", os.path.join(ROOT, "tests", "dist_worker.py"), "cpu", "30000"]
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
-    for name in ("chain", "optional", "star"):
+    for name in ("chain", "optional", "star", "skew_inner", "skew_optional"):
         assert f"world=2 {name}:" in r.stdout, r.stdout
+
+
+def test_find_heavy_keys_is_exact():
+    """two-exchange heavy-hitter detection against a global histogram, for several rank counts and thresholds"""
+    from rdf_fusion_b200.dist import find_heavy_keys
+    rng = np.random.default_rng(5)
+    for g in (1, 2, 5, 8):
+        keys = np.concatenate([rng.zipf(1.3, 20000) % 5000 + 1, np.zeros(50, np.int64)]).astype(np.uint32)
+        parts = np.array_split(rng.permutation(keys), g)
+        hists = [np.unique(p, return_counts=True) for p in parts]
+        for factor in (0.01, 0.1, 0.5, 5.0):
+            # emulate the collective: every rank calls with the same sequence of all_gathers
+            calls = [[] for _ in range(2)]
+
+            def run(rank, stage_inputs):
+                step = [0]
+
+                def all_gather(obj):
+                    i = step[0]
+                    step[0] += 1
+                    return stage_inputs[i]
+                return find_heavy_keys(hists[rank][0], hists[rank][1], len(keys), g, all_gather, factor)
+            thr = factor * len(keys) / g
+            cands = [h[0][h[1] * g > thr].astype(np.uint32) for h in hists]
+            union = np.unique(np.concatenate(cands))
+            union = union[union != 0]
+            mine = []
+            for h in hists:
+                m = np.zeros(len(union), np.int64)
+                for k, c in zip(*h):
+                    j = np.searchsorted(union, k)
+                    if j < len(union) and union[j] == k:
+                        m[j] += c
+                mine.append(m)
+            got = [run(r, [cands, mine]) for r in range(g)]
+            uk, uc = np.unique(keys, return_counts=True)
+            want = uk[(uc > thr) & (uk != 0)]
+            for x in got:
+                assert np.array_equal(x, want), (g, factor)
