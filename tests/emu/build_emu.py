@@ -58,7 +58,11 @@ def rewrite_launches(src):
     return out + src[pos:], n
 
 
-def build():
+def build(asan=False, tsan=False):
+    """asan=True: librfemu_asan.so with AddressSanitizer and unpadded "device" allocations (load it in a process started with
+    LD_PRELOAD=$(gcc -print-file-name=libasan.so) ASAN_OPTIONS=detect_leaks=0).
+    tsan=True: librfemu_tsan.so with ThreadSanitizer (LD_PRELOAD=$(gcc -print-file-name=libtsan.so)): the CTA threads are
+    real threads and the barriers real barriers, so a missing __syncthreads / __syncwarp shows up as a data race."""
     os.makedirs(BUILD, exist_ok=True)
     cpps = [os.path.join(HERE, "emu_runtime.cpp")]
     newest = max(os.path.getmtime(os.path.join(HERE, f)) for f in ("cuda_runtime.h", "emu_runtime.cpp", "build_emu.py"))
@@ -72,13 +76,16 @@ def build():
         newest = max(newest, os.path.getmtime(dst))
     for h in ("rf_common.hpp",):
         newest = max(newest, os.path.getmtime(os.path.join(CSRC, h)))
-    so = os.path.join(BUILD, "librfemu.so")
+    so = os.path.join(BUILD, "librfemu_asan.so" if asan else "librfemu_tsan.so" if tsan else "librfemu.so")
     if not os.path.exists(so) or os.path.getmtime(so) < newest:
+        extra = ["-fsanitize=address", "-fno-omit-frame-pointer", "-DEMU_STRICT_ALLOC"] if asan else []
+        extra += ["-fsanitize=thread", "-fno-omit-frame-pointer"] if tsan else []
         cmd = ["g++", "-std=c++20", "-O1", "-g", "-fPIC", "-shared", "-pthread", "-Wall", "-Wno-unused-function",
-               "-Wno-unknown-pragmas", "-I", HERE, "-I", CSRC, "-o", so] + cpps
+               "-Wno-unknown-pragmas", "-I", HERE, "-I", CSRC, "-o", so] + extra + cpps
         subprocess.run(cmd, check=True)
     return so
 
 
 if __name__ == "__main__":
-    print(build())
+    import sys
+    print(build(asan="--asan" in sys.argv, tsan="--tsan" in sys.argv))

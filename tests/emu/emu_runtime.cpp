@@ -10,7 +10,11 @@
 namespace rf {
 Core::~Core() {}
 DevBuf::DevBuf(std::shared_ptr<Core> c, size_t n) : core(std::move(c)), bytes(n) {
+#ifdef EMU_STRICT_ALLOC  // AddressSanitizer runs: no padding, so that a read or write one element past a buffer is reported
+  ptr = std::malloc(n ? n : 1);
+#else
   ptr = std::calloc(((n + kPad - 1) / kPad) * kPad + kPad, 1);
+#endif
   std::memset(ptr, 0xA5, n);  // uninitialised device memory is not zero
 }
 DevBuf::~DevBuf() { std::free(ptr); }

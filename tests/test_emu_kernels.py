@@ -23,7 +23,9 @@ vp, u32p, u64p = C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)
 
 @pytest.fixture(scope="module")
 def emu():
-    lib = C.CDLL(build_emu.build())
+    # EMU_ASAN=1 / EMU_TSAN=1 (with libasan / libtsan preloaded): the AddressSanitizer build with unpadded allocations, the
+    # ThreadSanitizer build in which a missing barrier is a reported data race
+    lib = C.CDLL(build_emu.build(asan=os.environ.get("EMU_ASAN") == "1", tsan=os.environ.get("EMU_TSAN") == "1"))
     sig = {
         "emu_ctx_create": (vp, []), "emu_ctx_destroy": (None, [vp]), "emu_kernel_launches": (C.c_uint64, [vp, C.c_char_p]),
         "emu_table_create": (vp, [vp, C.c_int32, C.POINTER(vp), C.c_uint64, C.c_int32]), "emu_table_rows": (C.c_uint64, [vp]),
@@ -207,8 +209,9 @@ def test_dictionary_decode_matches_the_oracle(emu, oracle, n_terms, n_rows):
     exp = oracle.decode_plain_terms(terms, ids)
     got.validate(full=True)
     assert got.type == exp.type and got.null_count == exp.null_count and got.equals(exp)
-    rc, msg = _decode(emu, terms, np.array([1, len(terms) + 3], np.uint32))
-    assert rc == F.E_INVALID and str(len(terms) + 3) in msg
+    if os.environ.get("EMU_ASAN") != "1" and os.environ.get("EMU_TSAN") != "1":  # a C++ throw inside a dlopen-ed ASAN library trips the sanitizer's own interceptor
+        rc, msg = _decode(emu, terms, np.array([1, len(terms) + 3], np.uint32))
+        assert rc == F.E_INVALID and str(len(terms) + 3) in msg
 
 
 def test_lookup_column(emu):
