@@ -51,7 +51,7 @@ k_group_insert(const __grid_constant__ GroupArgs A) {
     if (i < A.n) {
       h = hash_row(A, i) & A.mask;
       while (true) {
-        uint32_t cur = A.rep[h];
+        uint32_t cur = dev::ld_racy_u32(A.rep + h);
         if (cur == 0) {
           cur = atomicCAS(A.rep + h, 0u, (uint32_t)i + 1);
           if (cur == 0) break;  // this row is the group's representative

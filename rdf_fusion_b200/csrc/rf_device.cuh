@@ -16,6 +16,7 @@ constexpr unsigned long long kFlagA = 1ull << 62;
 constexpr unsigned long long kFlagP = 2ull << 62;
 constexpr unsigned long long kValMask = (1ull << 62) - 1;
 
+#ifdef __CUDACC__
 __device__ __forceinline__ unsigned long long ld_status(const unsigned long long* p) {
   unsigned long long v;
   asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -24,6 +25,21 @@ __device__ __forceinline__ unsigned long long ld_status(const unsigned long long
 __device__ __forceinline__ void st_status(unsigned long long* p, unsigned long long v) {
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+#else  // host build of tests/emu (kernel logic checked on OS threads): the same relaxed accesses as C++ atomics
+inline unsigned long long ld_status(const unsigned long long* p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }
+inline void st_status(unsigned long long* p, unsigned long long v) { __atomic_store_n(p, v, __ATOMIC_RELAXED); }
+#endif
+
+// A plain load of a word that another thread may be publishing with an atomic at the same time, in code that handles
+// either outcome (e.g. an open-addressing slot that goes 0 -> value once: a stale 0 is re-read by the CAS that follows, a
+// value never changes again).  On the device it is deliberately an ordinary load (it may be served by L1, which is what
+// makes hot groups cheap); the host build of tests/emu spells it as a relaxed atomic so that ThreadSanitizer reports only
+// races that are not of this kind.
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t ld_racy_u32(const uint32_t* p) { return *p; }
+#else
+inline uint32_t ld_racy_u32(const uint32_t* p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }
+#endif
 
 __device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v) {
 #pragma unroll
@@ -125,6 +141,7 @@ __device__ __host__ __forceinline__ uint32_t mix64to32(uint64_t x) {
   return (uint32_t)x;
 }
 
+#ifdef __CUDACC__  // the TMA / mbarrier wrappers exist on the device only
 // ---------------- mbarrier + 1-D bulk async copy (TMA engine, SASS: UBLKCP) ----------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -178,6 +195,7 @@ __device__ __forceinline__ void bulk_wait() {
   asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+#endif  // __CUDACC__
 
 }  // namespace dev
 }  // namespace rf

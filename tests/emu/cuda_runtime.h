@@ -116,6 +116,13 @@ inline unsigned atomicMin(unsigned* p, unsigned v) {
   while (old > v && !__atomic_compare_exchange_n(p, &old, v, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) {}
   return old;
 }
+inline unsigned atomicCAS(unsigned* p, unsigned expected, unsigned desired) {
+  __atomic_compare_exchange_n(p, &expected, desired, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED);
+  return expected;  // the value found, like the device intrinsic
+}
+inline void __nanosleep(unsigned) { std::this_thread::yield(); }
+struct alignas(16) uint4 { unsigned x, y, z, w; };
+inline uint4 make_uint4(unsigned x, unsigned y, unsigned z, unsigned w) { return uint4{x, y, z, w}; }
 using std::max;
 using std::min;
 

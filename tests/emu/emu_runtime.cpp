@@ -37,16 +37,6 @@ void set_error(const rfgpu_ctx* ctx, const std::string& msg) {
   g_err = msg;
   if (ctx) const_cast<rfgpu_ctx*>(ctx)->err = msg;
 }
-// the device-wide scan of filter.cu (validated on a B200 this round) is not what is under test here
-void exclusive_scan_u32(rfgpu_ctx*, const uint32_t* in, uint32_t* out, uint64_t n, uint64_t* h_total_slot) {
-  uint64_t run = 0;
-  for (uint64_t i = 0; i < n; i++) {
-    uint32_t v = in[i];
-    out[i] = (uint32_t)run;
-    run += v;
-  }
-  if (h_total_slot) *h_total_slot = run;
-}
 }  // namespace rf
 
 int rfgpu_ctx::kstat_index(const char* name) {
@@ -92,6 +82,8 @@ void emu_ctx_destroy(rfgpu_ctx* c) {
   std::free(c->h_scratch);
   delete c;
 }
+void emu_set_sort_agg(rfgpu_ctx* c, int32_t on) { c->opt_sort_agg = on != 0; }
+void emu_table_set_nullable(rfgpu_table* t, int32_t col, int32_t nullable) { t->cols[col].nullable = nullable != 0; }
 uint64_t emu_kernel_launches(rfgpu_ctx* c, const char* name) {
   for (auto& k : c->kstats)
     if (k.first == name) return k.second.launches;

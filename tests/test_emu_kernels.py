@@ -36,9 +36,11 @@ def emu():
         "emu_group_count": (C.c_int32, [vp, C.c_int32, C.POINTER(vp), vp, C.c_uint64, C.c_int32, C.POINTER(vp)]),
         "emu_sorted_contains": (C.c_int32, [vp, vp, C.c_uint64, vp, C.c_uint64, vp]),
         "rfgpu_last_error": (C.c_char_p, [vp]),
+        "emu_set_sort_agg": (None, [vp, C.c_int32]), "emu_table_set_nullable": (None, [vp, C.c_int32, C.c_int32]),
     }
     for name in ("rfgpu_table_sort", "rfgpu_store_build", "rfgpu_dict_create", "rfgpu_dict_release", "rfgpu_dict_decode",
-                 "rfgpu_plain_terms_release", "rfgpu_plain_terms_sizes", "rfgpu_plain_terms_export", "rfgpu_table_lookup"):
+                 "rfgpu_plain_terms_release", "rfgpu_plain_terms_sizes", "rfgpu_plain_terms_export", "rfgpu_table_lookup",
+                 "rfgpu_group_count", "rfgpu_distinct", "rfgpu_last_agg_phys", "rfgpu_filter"):
         sig[name] = F.SIGNATURES[name]  # the product's own bindings
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -228,4 +230,61 @@ def test_lookup_column(emu):
         want = np.where(ids[::-1] < nt, table[np.minimum(ids[::-1], max(nt - 1, 0))] if nt else 0, 0).astype(np.uint32)
         assert np.array_equal(got[2], want)
         emu.emu_table_release(out)
+        emu.emu_table_release(t)
+
+
+@pytest.mark.parametrize("sort_agg", [0, 1])
+def test_group_count_and_distinct_entry_points(emu, oracle, sort_agg):
+    """rfgpu_group_count / rfgpu_distinct themselves (aggregate.cu on host threads): the hash-table path that ran on a B200
+    this round, and the RFGPU_OPT_SORT_AGG hook in front of it, against the oracle"""
+    rng = np.random.default_rng(31 + sort_agg)
+    emu.emu_set_sort_agg(emu.ctx, sort_agg)
+    try:
+        for n, ks in [(0, 5), (1, 1), (33, 2), (3000, 7), (4200, 1 << 20)]:
+            cols = [np.where(rng.random(n) < 0.1, 0, rng.integers(1, ks + 1, n)).astype(np.uint32) for _ in range(3)]
+            t = _table(emu, cols)
+            for c in range(3):
+                emu.emu_table_set_nullable(t, c, 1)
+            O = oracle.OTable(["c0", "c1", "c2"], [True] * 3, cols)
+            for keys, counted in [([0], -1), ([0], 2), ([1, 0], -1), ([0, 1, 2], 1)]:
+                out = vp()
+                _ok(emu, emu.rfgpu_group_count(emu.ctx, t, (C.c_int32 * len(keys))(*keys), len(keys), counted, b"n", C.byref(out)))
+                got = _cols(emu, out)
+                emu.emu_table_release(out)
+                if n:
+                    assert emu.rfgpu_last_agg_phys(emu.ctx) == (F.AGG_PHYS_SORT if sort_agg else F.AGG_PHYS_HASH)
+                exp = oracle.group_count(O, [f"c{k}" for k in keys], None if counted < 0 else f"c{counted}", "n")
+                a, b = oracle.canonical_rows(got), oracle.canonical_rows(exp.cols)
+                assert a.shape == b.shape and np.array_equal(a, b), (n, ks, keys, counted)
+            out = vp()
+            _ok(emu, emu.rfgpu_distinct(emu.ctx, t, C.byref(out)))
+            got = _cols(emu, out)
+            emu.emu_table_release(out)
+            exp = oracle.distinct(O)
+            a, b = oracle.canonical_rows(got), oracle.canonical_rows(exp.cols)
+            assert a.shape == b.shape and np.array_equal(a, b)
+            emu.emu_table_release(t)
+    finally:
+        emu.emu_set_sort_agg(emu.ctx, 0)
+
+
+def test_filter_entry_point(emu, oracle):
+    """rfgpu_filter (k_filter_compact + the look-back scan, validated on a B200) on host threads: the same kernels now also
+    run under the sanitizers of this harness"""
+    import rdf_fusion_b200 as rf
+    rng = np.random.default_rng(77)
+    for n in (0, 1, 33, 4096, 4097, 9000):
+        cols = [np.where(rng.random(n) < 0.2, 0, rng.integers(1, 9, n)).astype(np.uint32) for _ in range(3)]
+        t = _table(emu, cols)
+        O = oracle.OTable(["c0", "c1", "c2"], [True] * 3, cols)
+        for preds in ([rf.FPred(F.F_NE_CONST, 0, value=3)], [rf.FPred(F.F_EQ_COL, 0, col2=1), rf.FPred(F.F_IS_NOT_NULL, 2)],
+                      [rf.FPred(F.F_IN, 1, ids=[1, 2, 5, 7, 8, 3, 4, 6, 9, 10, 11])], [rf.FPred(F.F_IS_NULL, 2)]):
+            arr, keep = rf.make_filter_preds(preds)
+            out = vp()
+            _ok(emu, emu.rfgpu_filter(emu.ctx, t, arr, len(preds), C.byref(out)))
+            got = _cols(emu, out)
+            emu.emu_table_release(out)
+            exp = oracle.filter_table(O, preds)
+            for g, e in zip(got, exp.cols):
+                assert np.array_equal(g, e), (n, [p.op for p in preds])  # order-preserving
         emu.emu_table_release(t)
