@@ -1,5 +1,5 @@
 // tests/emu/cuda_runtime.h — TEST INFRASTRUCTURE ONLY.  A stand-in for the CUDA runtime and the device intrinsics that lets
-// g++ compile the kernels of rdf_fusion_b200/csrc/{sort,dict}.cu for the HOST, so that their index arithmetic, barriers
+// g++ compile the kernels of rdf_fusion_b200/csrc/{sort,dict,filter,aggregate}.cu for the HOST, so that their index arithmetic, barriers
 // and warp-collective logic can be exercised in the build container, which has no GPU (tests/test_emu_kernels.py).
 // One CTA runs at a time: its threads are OS threads; __syncthreads / __syncwarp are real barriers; ballot / match / shfl
 // exchange through a per-warp buffer between two barrier phases; "device memory" is host memory.  Nothing under

@@ -1,4 +1,4 @@
-"""CPU: the kernels of rdf_fusion_b200/csrc/sort.cu and dict.cu — and their host orchestration, unmodified — executed on
+"""CPU: the kernels of rdf_fusion_b200/csrc/sort.cu, dict.cu, filter.cu and aggregate.cu — and their host orchestration, unmodified — executed on
 host threads through the stand-in CUDA runtime of tests/emu/ (every CTA thread an OS thread, real barriers, warp collectives
 through an exchange buffer), against numpy and the oracle.  This is a CHECK OF THE KERNELS' LOGIC in a container that has no
 GPU (index arithmetic, barrier placement, ballot / match.any use, tail tiles); it is not a CPU path of the product — nothing
