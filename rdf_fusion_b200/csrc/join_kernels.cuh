@@ -89,7 +89,7 @@ k_join_build_insert(const uint32_t* __restrict__ k0, const uint32_t* __restrict_
     }
     uint32_t h = hh & mask;
     while (true) {
-      K prev = keys[h];
+      K prev = dev::ld_racy(keys + h);  // may race with another row's CAS on this slot: either value is handled
       if (prev == key) break;
       if (prev == 0) {
         prev = atomicCAS(keys + h, (K)0, key);

@@ -166,6 +166,7 @@ __device__ __forceinline__ unsigned long long block_excl_u64(unsigned long long 
   return wpre + inc - v;
 }
 
+#ifdef __CUDACC__
 __device__ __forceinline__ uint32_t lds32(uint32_t a) {
   uint32_t v;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
@@ -174,6 +175,10 @@ __device__ __forceinline__ uint32_t lds32(uint32_t a) {
 __device__ __forceinline__ void sts32(uint32_t a, uint32_t v) {
   asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
 }
+#else  // host build of tests/emu
+inline uint32_t lds32(uint32_t a) { return dev::smem_ld32(a); }
+inline void sts32(uint32_t a, uint32_t v) { dev::smem_st32(a, v); }
+#endif
 
 __device__ __forceinline__ uint32_t hpad(uint32_t x) { return x + (x >> 3); }  // 8 items per thread, conflict-free
 

@@ -36,8 +36,12 @@ inline void st_status(unsigned long long* p, unsigned long long v) { __atomic_st
 // makes hot groups cheap); the host build of tests/emu spells it as a relaxed atomic so that ThreadSanitizer reports only
 // races that are not of this kind.
 #ifdef __CUDACC__
+template <class T>
+__device__ __forceinline__ T ld_racy(const T* p) { return *p; }
 __device__ __forceinline__ uint32_t ld_racy_u32(const uint32_t* p) { return *p; }
 #else
+template <class T>
+inline T ld_racy(const T* p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }
 inline uint32_t ld_racy_u32(const uint32_t* p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }
 #endif
 
@@ -195,6 +199,9 @@ __device__ __forceinline__ void bulk_wait() {
   asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+#elif defined(RF_HOST_DEVICE_SHIM)
+// host build of the kernel-logic tests (tests/emu): the harness supplies stand-ins for the wrappers above
+#include RF_HOST_DEVICE_SHIM
 #endif  // __CUDACC__
 
 }  // namespace dev

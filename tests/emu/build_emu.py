@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "rdf_fusion_b200", "csrc")
 BUILD = os.path.join(HERE, "_build")
-SOURCES = ["sort.cu", "dict.cu", "filter.cu", "aggregate.cu"]
+SOURCES = ["sort.cu", "dict.cu", "filter.cu", "aggregate.cu", "join.cu"]
 
 
 def _balanced(s, i, open_, close):
@@ -43,7 +43,7 @@ def _split_top(s):
 
 def rewrite_launches(src):
     out, pos, n = "", 0, 0
-    for m in re.finditer(r"(\w+)<<<", src):
+    for m in re.finditer(r"(\w+(?:<[^<>;(){}]*>)?)<<<", src):
         if m.start() < pos:
             continue
         end_cfg = src.index(">>>", m.end())
@@ -52,10 +52,19 @@ def rewrite_launches(src):
         a0 = end_cfg + 3
         assert src[a0] == "(", src[a0:a0 + 20]
         a1 = _balanced(src, a0, "(", ")")
-        out += src[pos:m.start()] + "EMU_LAUNCH(%s, %s, %s, %s)" % (m.group(1), cfg[0], cfg[1], src[a0 + 1:a1 - 1])
+        smem = cfg[2] if len(cfg) > 2 else "0"
+        # a template kernel name carries commas: parenthesise it for the macro, EMU_UNPAREN strips the parentheses again
+        out += src[pos:m.start()] + "EMU_LAUNCH(EMU_UNPAREN(%s), %s, %s, %s, %s)" % (m.group(1), cfg[0], cfg[1], smem,
+                                                                                     src[a0 + 1:a1 - 1])
         pos = a1
         n += 1
     return out + src[pos:], n
+
+
+def rewrite_dynamic_smem(src):
+    """extern __shared__ [__align__(n)] T name[];  ->  T* name = (T*)emu::g_dyn_smem;"""
+    return re.sub(r"extern\s+__shared__\s+(?:__align__\(\d+\)\s+)?([\w ]+?)\s+(\w+)\[\];",
+                  lambda m: "%s* %s = reinterpret_cast<%s*>(emu::g_dyn_smem);" % (m.group(1), m.group(2), m.group(1)), src)
 
 
 def build(asan=False, tsan=False):
@@ -67,21 +76,31 @@ def build(asan=False, tsan=False):
     cpps = [os.path.join(HERE, "emu_runtime.cpp")]
     newest = max(os.path.getmtime(os.path.join(HERE, f)) for f in ("cuda_runtime.h", "emu_runtime.cpp", "build_emu.py"))
     for f in SOURCES:
-        text, n = rewrite_launches(open(os.path.join(CSRC, f)).read())
+        text, n = rewrite_launches(rewrite_dynamic_smem(open(os.path.join(CSRC, f)).read()))
         assert n >= 1 and "<<<" not in text, (f, n)
         dst = os.path.join(BUILD, f.replace(".cu", "_emu.cpp"))
         if not os.path.exists(dst) or open(dst).read() != text:
             open(dst, "w").write(text)
         cpps.append(dst)
         newest = max(newest, os.path.getmtime(dst))
+    for h in ("merge_join.cuh", "join_kernels.cuh", "radix_join.cuh"):  # kernel headers get the same rewrite, next to the sources
+        text, _ = rewrite_launches(rewrite_dynamic_smem(open(os.path.join(CSRC, h)).read()))
+        dst = os.path.join(BUILD, h)
+        if not os.path.exists(dst) or open(dst).read() != text:
+            open(dst, "w").write(text)
+        newest = max(newest, os.path.getmtime(dst))
     for h in ("rf_common.hpp", "rf_device.cuh"):
         newest = max(newest, os.path.getmtime(os.path.join(CSRC, h)))
+    newest = max(newest, os.path.getmtime(os.path.join(HERE, "emu_device.inl")))
     so = os.path.join(BUILD, "librfemu_asan.so" if asan else "librfemu_tsan.so" if tsan else "librfemu.so")
     if not os.path.exists(so) or os.path.getmtime(so) < newest:
-        extra = ["-fsanitize=address", "-fno-omit-frame-pointer", "-DEMU_STRICT_ALLOC"] if asan else []
+        # unpadded "device" allocations unless EMU_ASAN_PAD=1: the TMA staging of the join kernels reads whole 16-B granules
+        # and relies on the 256-B padding every real allocation has (rf_common.hpp kPad)
+        strict = [] if os.environ.get("EMU_ASAN_PAD") == "1" else ["-DEMU_STRICT_ALLOC"]
+        extra = ["-fsanitize=address", "-fno-omit-frame-pointer"] + strict if asan else []
         extra += ["-fsanitize=thread", "-fno-omit-frame-pointer"] if tsan else []
         cmd = ["g++", "-std=c++20", "-O1", "-g", "-fPIC", "-shared", "-pthread", "-Wall", "-Wno-unused-function",
-               "-Wno-unknown-pragmas", "-I", HERE, "-I", CSRC, "-o", so] + extra + cpps
+               "-Wno-unknown-pragmas", '-DRF_HOST_DEVICE_SHIM="emu_device.inl"', "-I", HERE, "-I", CSRC, "-o", so] + extra + cpps
         subprocess.run(cmd, check=True)
     return so
 

@@ -1,5 +1,5 @@
 // tests/emu/cuda_runtime.h — TEST INFRASTRUCTURE ONLY.  A stand-in for the CUDA runtime and the device intrinsics that lets
-// g++ compile the kernels of rdf_fusion_b200/csrc/{sort,dict,filter,aggregate}.cu for the HOST, so that their index arithmetic, barriers
+// g++ compile the kernels of rdf_fusion_b200/csrc/{sort,dict,filter,aggregate,join}.cu for the HOST, so that their index arithmetic, barriers
 // and warp-collective logic can be exercised in the build container, which has no GPU (tests/test_emu_kernels.py).
 // One CTA runs at a time: its threads are OS threads; __syncthreads / __syncwarp are real barriers; ballot / match / shfl
 // exchange through a per-warp buffer between two barrier phases; "device memory" is host memory.  Nothing under
@@ -13,6 +13,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <functional>
+#include <map>
+#include <mutex>
 #include <memory>
 #include <thread>
 #include <vector>
@@ -36,6 +38,15 @@ inline cudaError_t cudaMemsetAsync(void* d, int v, size_t n, cudaStream_t) {
   return cudaSuccess;
 }
 
+enum cudaFuncAttribute { cudaFuncAttributeMaxDynamicSharedMemorySize };
+template <class K>
+inline cudaError_t cudaFuncSetAttribute(K, cudaFuncAttribute, int) { return cudaSuccess; }
+template <class K>
+inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int* n, K, int, size_t) {
+  *n = 2;
+  return cudaSuccess;
+}
+
 // ---- device side ----
 namespace emu {
 struct Dim { unsigned x = 1, y = 1, z = 1; };
@@ -46,6 +57,7 @@ struct Cta {
   uint64_t xchg[kMaxThreads];
 };
 inline Cta* g_cta = nullptr;
+inline unsigned char* g_dyn_smem = nullptr;  // `extern __shared__` of the running kernel (size = the launch's third argument)
 }  // namespace emu
 inline thread_local emu::Dim threadIdx, blockIdx;
 inline emu::Dim blockDim, gridDim;
@@ -58,6 +70,7 @@ inline emu::Dim blockDim, gridDim;
 #define __launch_bounds__(...)
 #define __grid_constant__
 #define __shared__ static
+#define __align__(n) __attribute__((aligned(n)))
 
 inline void __syncthreads() { emu::g_cta->all->arrive_and_wait(); }
 inline void __syncwarp(unsigned = 0xFFFFFFFFu) { emu::g_cta->warp[threadIdx.x >> 5]->arrive_and_wait(); }
@@ -116,20 +129,26 @@ inline unsigned atomicMin(unsigned* p, unsigned v) {
   while (old > v && !__atomic_compare_exchange_n(p, &old, v, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) {}
   return old;
 }
-inline unsigned atomicCAS(unsigned* p, unsigned expected, unsigned desired) {
+template <class T>
+inline T atomicCAS(T* p, T expected, T desired) {
   __atomic_compare_exchange_n(p, &expected, desired, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED);
   return expected;  // the value found, like the device intrinsic
 }
 inline void __nanosleep(unsigned) { std::this_thread::yield(); }
+struct alignas(8) uint2 { unsigned x, y; };
+inline uint2 make_uint2(unsigned x, unsigned y) { return uint2{x, y}; }
 struct alignas(16) uint4 { unsigned x, y, z, w; };
 inline uint4 make_uint4(unsigned x, unsigned y, unsigned z, unsigned w) { return uint4{x, y, z, w}; }
 using std::max;
 using std::min;
 
 namespace emu {
-// kernel<<<grid, block>>>(args): CTAs one after the other, `block` OS threads each
-inline void launch(unsigned grid, unsigned block, const std::function<void()>& body) {
+// kernel<<<grid, block, smem>>>(args): CTAs one after the other, `block` OS threads each.  (A persistent worker pool was
+// tried and was slower: 256 sleepers woken through one condition variable cost more than 256 thread creations.)
+inline void launch(unsigned grid, unsigned block, size_t dyn_smem, const std::function<void()>& body) {
   Cta cta;
+  std::vector<unsigned char> dyn(dyn_smem + 256);
+  g_dyn_smem = dyn.data() + (128 - reinterpret_cast<uintptr_t>(dyn.data()) % 128) % 128;
   cta.all = std::make_unique<std::barrier<>>(block);
   for (unsigned w = 0; w < (block + 31) / 32; w++)
     cta.warp.push_back(std::make_unique<std::barrier<>>(std::min(32u, block - 32 * w)));
@@ -149,6 +168,8 @@ inline void launch(unsigned grid, unsigned block, const std::function<void()>& b
     });
   for (auto& x : th) x.join();
   g_cta = nullptr;
+  g_dyn_smem = nullptr;
 }
 }  // namespace emu
-#define EMU_LAUNCH(kernel, grid, block, ...) emu::launch((grid), (block), [&] { kernel(__VA_ARGS__); })
+#define EMU_LAUNCH(kernel, grid, block, smem, ...) emu::launch((grid), (block), (smem), [&] { kernel(__VA_ARGS__); })
+#define EMU_UNPAREN(...) __VA_ARGS__

@@ -1,4 +1,5 @@
-"""CPU: the kernels of rdf_fusion_b200/csrc/sort.cu, dict.cu, filter.cu and aggregate.cu — and their host orchestration, unmodified — executed on
+"""CPU: the kernels of rdf_fusion_b200/csrc/sort.cu, dict.cu, filter.cu, aggregate.cu and join.cu (with the merge / hash / radix
+join headers) — and their host orchestration, unmodified — executed on
 host threads through the stand-in CUDA runtime of tests/emu/ (every CTA thread an OS thread, real barriers, warp collectives
 through an exchange buffer), against numpy and the oracle.  This is a CHECK OF THE KERNELS' LOGIC in a container that has no
 GPU (index arithmetic, barrier placement, ballot / match.any use, tail tiles); it is not a CPU path of the product — nothing
@@ -19,6 +20,13 @@ from rdf_fusion_b200.api import pack_terms, plain_terms_to_arrow  # noqa: E402
 from test_dict_decode_cpu import REF_TERMS, random_terms  # noqa: E402
 
 vp, u32p, u64p = C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)
+# Every emulated launch costs ~0.1 s (256 OS threads, real barriers), so the default run keeps a cross-section of each
+# test's shapes — still every tile shape, lowering and option — and EMU_FULL=1 runs the whole matrix (about 10 minutes).
+FULL = os.environ.get("EMU_FULL") == "1"
+
+
+def some(full, default):
+    return full if FULL else default
 
 
 @pytest.fixture(scope="module")
@@ -37,10 +45,14 @@ def emu():
         "emu_sorted_contains": (C.c_int32, [vp, vp, C.c_uint64, vp, C.c_uint64, vp]),
         "rfgpu_last_error": (C.c_char_p, [vp]),
         "emu_set_sort_agg": (None, [vp, C.c_int32]), "emu_table_set_nullable": (None, [vp, C.c_int32, C.c_int32]),
+        "emu_table_set_name": (None, [vp, C.c_int32, C.c_char_p]), "emu_table_name": (C.c_char_p, [vp, C.c_int32]),
+        "emu_table_nullable": (C.c_int32, [vp, C.c_int32]),
     }
     for name in ("rfgpu_table_sort", "rfgpu_store_build", "rfgpu_dict_create", "rfgpu_dict_release", "rfgpu_dict_decode",
                  "rfgpu_plain_terms_release", "rfgpu_plain_terms_sizes", "rfgpu_plain_terms_export", "rfgpu_table_lookup",
-                 "rfgpu_group_count", "rfgpu_distinct", "rfgpu_last_agg_phys", "rfgpu_filter"):
+                 "rfgpu_group_count", "rfgpu_distinct", "rfgpu_last_agg_phys", "rfgpu_filter", "rfgpu_sparql_join",
+                 "rfgpu_sparql_join_filter", "rfgpu_sparql_minus", "rfgpu_sparql_exists", "rfgpu_last_join_algo",
+                 "rfgpu_last_join_phys", "rfgpu_ctx_set_option"):
         sig[name] = F.SIGNATURES[name]  # the product's own bindings
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -77,7 +89,7 @@ def _sort(lib, cols, keys):
     return got
 
 
-@pytest.mark.parametrize("n", [0, 1, 2, 31, 33, 4095, 4096, 4097, 9001])
+@pytest.mark.parametrize("n", some([0, 1, 2, 31, 33, 4095, 4096, 4097, 9001], [0, 33, 4096, 4097]))
 def test_radix_sort_is_a_stable_lexicographic_sort(emu, n):
     """empty, one row, partial warp, exactly one tile, one row over, three tiles × 0–4 digit passes × 1–3 sort columns ×
     1–6 carried columns (more than 4: the row-number path with k_iota0 / k_gather_rows)"""
@@ -87,7 +99,7 @@ def test_radix_sort_is_a_stable_lexicographic_sort(emu, n):
     if n <= 33:      # the emulation pays ~0.1 s per launch whatever the size: keep the small shapes to a cross-section
         combos = [(his[k], shapes[(k + j) % 6]) for k in (0, 2, 5) for j in (0, 2, 4)]
     elif n == 4097:  # every key range, every shape once or twice
-        combos = [(his[k], shapes[(k + j) % 6]) for k in range(6) for j in (0, 3)]
+        combos = [(his[k], shapes[(k + j) % 6]) for k in range(6) for j in some((0, 3), (k % 2 * 3,))]
     else:
         combos = [(his[k], shapes[(k + j) % 6]) for k in (2, 4) for j in (1, 3)]
     for hi, (ncols, keys) in combos:
@@ -108,7 +120,7 @@ def test_radix_sort_skewed_digit(emu):
     assert np.array_equal(got[0], k[order]) and np.array_equal(got[1], v[order])
 
 
-@pytest.mark.parametrize("seed,n", [(1, 0), (2, 1), (3, 500), (4, 5000)])
+@pytest.mark.parametrize("seed,n", some([(1, 0), (2, 1), (3, 500), (4, 5000)], [(1, 0), (3, 500)]))
 def test_store_build_sorts_and_deduplicates_every_permutation(emu, seed, n):
     rng = np.random.default_rng(seed)
     g = np.where(rng.random(n) < 0.6, 0, rng.integers(1, 4, n)).astype(np.uint32)
@@ -138,7 +150,7 @@ def test_store_build_sorts_and_deduplicates_every_permutation(emu, seed, n):
 def test_run_length_group_count_and_distinct(emu):
     rng = np.random.default_rng(21)
     import pandas as pd
-    for n, ks in [(0, 5), (1, 1), (33, 2), (5000, 7), (4200, 1 << 20)]:
+    for n, ks in some([(0, 5), (1, 1), (33, 2), (5000, 7), (4200, 1 << 20)], [(0, 5), (33, 2), (4200, 1 << 20)]):
         a, b, c = [np.where(rng.random(n) < 0.1, 0, rng.integers(1, ks + 1, n)).astype(np.uint32) for _ in range(3)]
         for keys, counted, want_counts in [([a], None, 1), ([a], c, 1), ([b, a], None, 1), ([a, b, c], b, 1), ([a, b], None, 0)]:
             out = vp()
@@ -201,7 +213,8 @@ def _decode(lib, terms, ids):
     return 0, plain_terms_to_arrow(n, term_type, valid, offs, data, [int(x) for x in sizes], [int(x) for x in nulls])
 
 
-@pytest.mark.parametrize("n_terms,n_rows", [(4, 5), (1, 0), (1, 1), (50, 31), (50, 32), (50, 33), (400, 3000)])
+@pytest.mark.parametrize("n_terms,n_rows", some([(4, 5), (1, 0), (1, 1), (50, 31), (50, 32), (50, 33), (400, 3000)],
+                                                 [(4, 5), (1, 0), (50, 33), (300, 900)]))
 def test_dictionary_decode_matches_the_oracle(emu, oracle, n_terms, n_rows):
     rng = np.random.default_rng(n_terms + n_rows)
     terms = REF_TERMS if n_terms == 4 else random_terms(rng, n_terms)
@@ -240,7 +253,7 @@ def test_group_count_and_distinct_entry_points(emu, oracle, sort_agg):
     rng = np.random.default_rng(31 + sort_agg)
     emu.emu_set_sort_agg(emu.ctx, sort_agg)
     try:
-        for n, ks in [(0, 5), (1, 1), (33, 2), (3000, 7), (4200, 1 << 20)]:
+        for n, ks in some([(0, 5), (1, 1), (33, 2), (3000, 7), (4200, 1 << 20)], [(0, 5), (33, 2), (4200, 300)]):
             cols = [np.where(rng.random(n) < 0.1, 0, rng.integers(1, ks + 1, n)).astype(np.uint32) for _ in range(3)]
             t = _table(emu, cols)
             for c in range(3):
@@ -273,7 +286,7 @@ def test_filter_entry_point(emu, oracle):
     run under the sanitizers of this harness"""
     import rdf_fusion_b200 as rf
     rng = np.random.default_rng(77)
-    for n in (0, 1, 33, 4096, 4097, 9000):
+    for n in some((0, 1, 33, 4096, 4097, 9000), (0, 33, 4097)):
         cols = [np.where(rng.random(n) < 0.2, 0, rng.integers(1, 9, n)).astype(np.uint32) for _ in range(3)]
         t = _table(emu, cols)
         O = oracle.OTable(["c0", "c1", "c2"], [True] * 3, cols)
@@ -288,3 +301,151 @@ def test_filter_entry_point(emu, oracle):
             for g, e in zip(got, exp.cols):
                 assert np.array_equal(g, e), (n, [p.op for p in preds])  # order-preserving
         emu.emu_table_release(t)
+
+
+# ---------------------------------------------------------------- join.cu: the SPARQL join family on host threads
+def _named(lib, names, nullable, cols, sorted_col=-1):
+    t = _table(lib, cols, sorted_col)
+    for i, (n, nl) in enumerate(zip(names, nullable)):
+        lib.emu_table_set_name(t, i, n.encode())
+        lib.emu_table_set_nullable(t, i, int(nl))
+    return t
+
+
+def _take(lib, t):
+    names = [lib.emu_table_name(t, c).decode() for c in range(lib.emu_table_cols(t))]
+    nullable = [bool(lib.emu_table_nullable(t, c)) for c in range(lib.emu_table_cols(t))]
+    cols = _cols(lib, t)
+    lib.emu_table_release(t)
+    return names, nullable, cols
+
+
+def _rand_cols(rng, names, nullable, n, hi, null_frac=0.3):
+    out = []
+    for nl in nullable:
+        c = rng.integers(1, hi + 1, n).astype(np.uint32)
+        if nl:
+            c[rng.random(n) < null_frac] = 0
+        out.append(c)
+    return out
+
+
+JOIN_SHAPES = [
+    (("a", "k"), (False, False), ("k", "z"), (False, False)),
+    (("k1", "a", "k2"), (False, False, False), ("k2", "z", "k1"), (False,) * 3),
+    (("a", "k"), (False, True), ("k", "z"), (True, False)),
+    (("k1", "a", "k2"), (True, False, True), ("k2", "k1", "z"), (True, True, True)),
+    (("a", "b"), (False, True), ("c", "d"), (False, False)),
+]
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+@pytest.mark.parametrize("shape", JOIN_SHAPES, ids=lambda s: "+".join(s[0]) + "|" + "+".join(s[2]))
+def test_sparql_join_and_join_filter(emu, oracle, shape, jt):
+    """rfgpu_sparql_join (hash, compatible, cross lowerings — validated on a B200) and rfgpu_sparql_join_filter (the new
+    composition) against the oracle; the filtered join against the SPARQL 1.1 §18.5 definition"""
+    import rdf_fusion_b200 as rf
+    ln, lnl, rn, rnl = shape
+    rng = np.random.default_rng(len(ln) * 11 + jt)
+    for nl_, nr_, hi in some([(0, 9, 4), (8, 0, 4), (1, 1, 1), (40, 30, 5), (700, 300, 25)], [(0, 9, 4), (8, 0, 4), (90, 60, 7)]):
+        lc, rc = _rand_cols(rng, ln, lnl, nl_, hi), _rand_cols(rng, rn, rnl, nr_, hi)
+        L, R = _named(emu, ln, lnl, lc), _named(emu, rn, rnl, rc)
+        OL, OR = oracle.OTable(list(ln), list(lnl), lc), oracle.OTable(list(rn), list(rnl), rc)
+        out = vp()
+        _ok(emu, emu.rfgpu_sparql_join(emu.ctx, L, R, jt, C.byref(out)))
+        names, nullable, cols = _take(emu, out)
+        exp, algo, _ = oracle.sparql_join(OL, OR, jt, "hash")
+        assert names == exp.names and nullable == exp.nullable and emu.rfgpu_last_join_algo(emu.ctx) == algo
+        a, b = oracle.canonical_rows(cols), oracle.canonical_rows(exp.cols)
+        assert a.shape == b.shape and np.array_equal(a, b), (shape, nl_, nr_)
+        last = len(names) - 1
+        for preds in ([rf.FPred(F.F_NE_COL, 0, col2=last)], [rf.FPred(F.F_EQ_CONST, last, value=2)],
+                      [rf.FPred(F.F_IS_NOT_NULL, 1), rf.FPred(F.F_IN, last, ids=[1, 3, 4])], [rf.FPred(F.F_IS_NULL, 1)])[::some(1, 2)]:
+            arr, keep = rf.make_filter_preds(preds)
+            out = vp()
+            _ok(emu, emu.rfgpu_sparql_join_filter(emu.ctx, L, R, jt, arr, len(preds), C.byref(out)))
+            names, nullable, cols = _take(emu, out)
+            want = oracle.sparql_join_filtered(OL, OR, jt, preds)
+            assert names == want.names and nullable == want.nullable
+            a, b = oracle.canonical_rows(cols), oracle.canonical_rows(want.cols)
+            assert a.shape == b.shape and np.array_equal(a, b), (shape, nl_, nr_, [(p.op, p.col) for p in preds])
+        emu.emu_table_release(L)
+        emu.emu_table_release(R)
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_merge_join_and_sort_merge_join(emu, oracle, jt):
+    """both inputs sorted on the key: k_merge_join (TMA staging and mbarriers through the host stand-ins); unsorted inputs
+    with RFGPU_OPT_SORT_MERGE_JOIN: radix sort of the unsorted side(s), then the same kernel"""
+    rng = np.random.default_rng(5 + jt)
+    for nl_, nr_, hi, wide in some([(1, 1, 1, False), (300, 500, 40, False), (3000, 1400, 300, True), (2500, 2500, 12, False)],
+                                   [(300, 500, 40, False), (1300, 700, 60, True)]):
+        ln = ["k", "a"] + (["c", "d", "e"] if wide else [])
+        rn = ["b", "k"]
+        lc = [rng.integers(1, hi + 1, nl_).astype(np.uint32) for _ in ln]
+        rc = [rng.integers(1, hi + 1, nr_).astype(np.uint32) for _ in rn]
+        OL, OR = oracle.OTable(ln, [False] * len(ln), lc), oracle.OTable(rn, [False] * 2, rc)
+        exp = oracle.sparql_join(OL, OR, jt, "hash")[0]
+        b = oracle.canonical_rows(exp.cols)
+        # (1) sorted inputs
+        lo, ro = np.argsort(lc[0], kind="stable"), np.argsort(rc[1], kind="stable")
+        L = _named(emu, ln, [False] * len(ln), [c[lo] for c in lc], sorted_col=0)
+        R = _named(emu, rn, [False] * 2, [c[ro] for c in rc], sorted_col=1)
+        out = vp()
+        _ok(emu, emu.rfgpu_sparql_join(emu.ctx, L, R, jt, C.byref(out)))
+        assert emu.rfgpu_last_join_phys(emu.ctx) == F.PHYS_MERGE
+        names, _, cols = _take(emu, out)
+        a = oracle.canonical_rows(cols)
+        assert names == exp.names and a.shape == b.shape and np.array_equal(a, b), ("merge", nl_, nr_)
+        emu.emu_table_release(L)
+        emu.emu_table_release(R)
+        # (2) unsorted inputs through the sort-merge option, and one side sorted
+        _ok(emu, emu.rfgpu_ctx_set_option(emu.ctx, F.OPT_SORT_MERGE_JOIN, 1))
+        try:
+            for l_sorted in (False, True):
+                L = (_named(emu, ln, [False] * len(ln), [c[lo] for c in lc], sorted_col=0) if l_sorted
+                     else _named(emu, ln, [False] * len(ln), lc))
+                R = _named(emu, rn, [False] * 2, rc)
+                out = vp()
+                _ok(emu, emu.rfgpu_sparql_join(emu.ctx, L, R, jt, C.byref(out)))
+                assert emu.rfgpu_last_join_phys(emu.ctx) == F.PHYS_SORT_MERGE
+                assert emu.emu_table_sorted_col(out) == 0
+                names, _, cols = _take(emu, out)
+                a = oracle.canonical_rows(cols)
+                assert names == exp.names and a.shape == b.shape and np.array_equal(a, b), ("sort-merge", nl_, nr_, l_sorted)
+                emu.emu_table_release(L)
+                emu.emu_table_release(R)
+        finally:
+            _ok(emu, emu.rfgpu_ctx_set_option(emu.ctx, F.OPT_SORT_MERGE_JOIN, 0))
+
+
+@pytest.mark.parametrize("sort_semi", [0, 1])
+def test_minus_and_exists(emu, oracle, sort_semi):
+    """rfgpu_sparql_minus / rfgpu_sparql_exists: the hash semi / anti join (validated on a B200) and the sorted-list path of
+    RFGPU_OPT_SORT_SEMI, same rows in the same (lhs) order"""
+    rng = np.random.default_rng(43 + sort_semi)
+    _ok(emu, emu.rfgpu_ctx_set_option(emu.ctx, F.OPT_SORT_SEMI, sort_semi))
+    try:
+        for ln, lnl, rn, rnl in [(("a", "k"), (False, False), ("k", "z"), (False, False)),
+                                 (("a", "k"), (False, True), ("k", "z"), (True, False))]:
+            for nl_, nr_, hi in some([(50, 1, 9), (300, 200, 25), (2000, 900, 400)], [(50, 1, 9), (600, 200, 25)]):
+                lc, rc = _rand_cols(rng, ln, lnl, nl_, hi), _rand_cols(rng, rn, rnl, nr_, hi)
+                L, R = _named(emu, ln, lnl, lc), _named(emu, rn, rnl, rc)
+                OL, OR = oracle.OTable(list(ln), list(lnl), lc), oracle.OTable(list(rn), list(rnl), rc)
+                for mode in ("minus", "exists", "not_exists"):
+                    out = vp()
+                    if mode == "minus":
+                        _ok(emu, emu.rfgpu_sparql_minus(emu.ctx, L, R, C.byref(out)))
+                        want = oracle.sparql_minus(OL, OR)
+                    else:
+                        _ok(emu, emu.rfgpu_sparql_exists(emu.ctx, L, R, int(mode == "not_exists"), C.byref(out)))
+                        want = oracle.sparql_exists(OL, OR, mode == "not_exists")
+                    if sort_semi and not any(lnl) and not any(rnl):
+                        assert emu.rfgpu_last_join_phys(emu.ctx) == F.PHYS_SORT_MERGE
+                    _, _, cols = _take(emu, out)
+                    for g, w in zip(cols, want.cols):
+                        assert np.array_equal(g, w), (mode, ln, lnl, nl_, nr_)
+                emu.emu_table_release(L)
+                emu.emu_table_release(R)
+    finally:
+        _ok(emu, emu.rfgpu_ctx_set_option(emu.ctx, F.OPT_SORT_SEMI, 0))
