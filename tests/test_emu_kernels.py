@@ -346,6 +346,8 @@ def test_sparql_join_and_join_filter(emu, oracle, shape, jt):
     composition) against the oracle; the filtered join against the SPARQL 1.1 §18.5 definition"""
     import rdf_fusion_b200 as rf
     ln, lnl, rn, rnl = shape
+    if not FULL and len(ln) == 3 and jt == F.JOIN_INNER:
+        pytest.skip("two-key shapes run as Left joins in the default cross-section (EMU_FULL=1 runs both)")
     rng = np.random.default_rng(len(ln) * 11 + jt)
     for nl_, nr_, hi in some([(0, 9, 4), (8, 0, 4), (1, 1, 1), (40, 30, 5), (700, 300, 25)], [(0, 9, 4), (8, 0, 4), (90, 60, 7)]):
         lc, rc = _rand_cols(rng, ln, lnl, nl_, hi), _rand_cols(rng, rn, rnl, nr_, hi)
