@@ -52,6 +52,10 @@ def parse_args():
                     help="chain workload: partition kernels + ncclSend/ncclRecv instead of the fused peer-memory scatter")
     ap.add_argument("--unbatched", action="store_true", help="one range look-up launch per scan instead of the batched form")
     ap.add_argument("--radix-join", action="store_true", help="with --hash-join: the radix-partitioned variant")
+    ap.add_argument("--device-build", action="store_true",
+                    help="set-up: build the permutations with rfgpu_store_build (radix sort on the device) instead of torch.sort")
+    ap.add_argument("--sort-merge-join", action="store_true",
+                    help="with --hash-join: unsorted inputs are radix-sorted and merge-joined (RFGPU_OPT_SORT_MERGE_JOIN)")
     ap.add_argument("--hash-join", action="store_true", help="scan the join inputs through GPOS and force the hash join")
     return ap.parse_args()
 
@@ -193,6 +197,8 @@ def run_ours(a):
         ctx.set_option(F.OPT_MERGE_THREADS, a.merge_threads)
     if a.radix_join:
         ctx.set_option(F.OPT_RADIX_JOIN, 1)
+    if a.sort_merge_join:
+        ctx.set_option(F.OPT_SORT_MERGE_JOIN, 1)
 
     # ---- set-up (untimed): the global graph has world * triples rows; this rank owns the quads whose subject hashes
     # to it, so every scan is local and the star join on ?s needs no exchange (weak scaling, no data-path collective)
@@ -200,7 +206,10 @@ def run_ours(a):
     t0 = time.perf_counter()
     g = rf.generate_graph(n_global, a.predicates, a.zipf, a.seed)
     cols = partition_by_subject((g.g, g.s, g.p, g.o), rank, world)
-    store = load_store_device(ctx, *cols, perms=(F.GSPO, F.GPOS, F.GOSP, F.GPSO))
+    if a.device_build:  # unsorted columns go over once, every permutation is sorted and de-duplicated there
+        store = ctx.store().build(np.stack(cols, axis=1), (F.GSPO, F.GPOS, F.GOSP, F.GPSO))
+    else:
+        store = load_store_device(ctx, *cols, perms=(F.GSPO, F.GPOS, F.GOSP, F.GPSO))
     del cols
     setup_s = time.perf_counter() - t0
     pid = g.pred_id
