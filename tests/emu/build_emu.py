@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "rdf_fusion_b200", "csrc")
 BUILD = os.path.join(HERE, "_build")
-SOURCES = ["sort.cu", "dict.cu", "filter.cu", "aggregate.cu", "join.cu"]
+SOURCES = ["sort.cu", "dict.cu", "filter.cu", "aggregate.cu", "join.cu", "scan.cu", "scan_plan.cpp"]
 
 
 def _balanced(s, i, open_, close):
@@ -77,8 +77,8 @@ def build(asan=False, tsan=False):
     newest = max(os.path.getmtime(os.path.join(HERE, f)) for f in ("cuda_runtime.h", "emu_runtime.cpp", "build_emu.py"))
     for f in SOURCES:
         text, n = rewrite_launches(rewrite_dynamic_smem(open(os.path.join(CSRC, f)).read()))
-        assert n >= 1 and "<<<" not in text, (f, n)
-        dst = os.path.join(BUILD, f.replace(".cu", "_emu.cpp"))
+        assert "<<<" not in text, (f, n)
+        dst = os.path.join(BUILD, f.replace(".cu", "_emu.cpp").replace("scan_plan.cpp", "scan_plan_emu.cpp"))
         if not os.path.exists(dst) or open(dst).read() != text:
             open(dst, "w").write(text)
         cpps.append(dst)

@@ -1,5 +1,5 @@
 // tests/emu/cuda_runtime.h — TEST INFRASTRUCTURE ONLY.  A stand-in for the CUDA runtime and the device intrinsics that lets
-// g++ compile the kernels of rdf_fusion_b200/csrc/{sort,dict,filter,aggregate,join}.cu for the HOST, so that their index arithmetic, barriers
+// g++ compile the kernels of rdf_fusion_b200/csrc/{sort,dict,filter,aggregate,join,scan}.cu for the HOST, so that their index arithmetic, barriers
 // and warp-collective logic can be exercised in the build container, which has no GPU (tests/test_emu_kernels.py).
 // One CTA runs at a time: its threads are OS threads; __syncthreads / __syncwarp are real barriers; ballot / match / shfl
 // exchange through a per-warp buffer between two barrier phases; "device memory" is host memory.  Nothing under
@@ -55,6 +55,7 @@ struct Cta {
   std::unique_ptr<std::barrier<>> all;
   std::vector<std::unique_ptr<std::barrier<>>> warp;
   uint64_t xchg[kMaxThreads];
+  std::atomic<int> count{0};
 };
 inline Cta* g_cta = nullptr;
 inline unsigned char* g_dyn_smem = nullptr;  // `extern __shared__` of the running kernel (size = the launch's third argument)
@@ -73,6 +74,15 @@ inline emu::Dim blockDim, gridDim;
 #define __align__(n) __attribute__((aligned(n)))
 
 inline void __syncthreads() { emu::g_cta->all->arrive_and_wait(); }
+inline int __syncthreads_count(int pred) {
+  if (pred) emu::g_cta->count.fetch_add(1, std::memory_order_relaxed);
+  __syncthreads();
+  const int r = emu::g_cta->count.load(std::memory_order_relaxed);
+  __syncthreads();
+  if (threadIdx.x == 0) emu::g_cta->count.store(0, std::memory_order_relaxed);
+  __syncthreads();
+  return r;
+}
 inline void __syncwarp(unsigned = 0xFFFFFFFFu) { emu::g_cta->warp[threadIdx.x >> 5]->arrive_and_wait(); }
 namespace emu {
 // every lane deposits v, all lanes see all 32 values; the second barrier lets the buffer be reused
@@ -117,6 +127,10 @@ inline int __popc(unsigned v) { return __builtin_popcount(v); }
 inline int __ffs(unsigned v) { return __builtin_ffs((int)v); }
 template <class T>
 inline T __ldg(const T* p) { return *p; }
+template <class T>
+inline T __ldcs(const T* p) { return *p; }
+template <class T>
+inline void __stcs(T* p, T v) { *p = v; }
 template <class T, class U>
 inline T atomicAdd(T* p, U v) { return __atomic_fetch_add(p, (T)v, __ATOMIC_RELAXED); }
 inline unsigned atomicMax(unsigned* p, unsigned v) {
@@ -145,7 +159,13 @@ using std::min;
 namespace emu {
 // kernel<<<grid, block, smem>>>(args): CTAs one after the other, `block` OS threads each.  (A persistent worker pool was
 // tried and was slower: 256 sleepers woken through one condition variable cost more than 256 thread creations.)
-inline void launch(unsigned grid, unsigned block, size_t dyn_smem, const std::function<void()>& body) {
+}  // namespace emu
+struct dim3 {
+  unsigned x, y, z;
+  dim3(unsigned x_ = 1, unsigned y_ = 1, unsigned z_ = 1) : x(x_), y(y_), z(z_) {}
+};
+namespace emu {
+inline void launch(dim3 grid, unsigned block, size_t dyn_smem, const std::function<void()>& body) {
   Cta cta;
   std::vector<unsigned char> dyn(dyn_smem + 256);
   g_dyn_smem = dyn.data() + (128 - reinterpret_cast<uintptr_t>(dyn.data()) % 128) % 128;
@@ -154,17 +174,20 @@ inline void launch(unsigned grid, unsigned block, size_t dyn_smem, const std::fu
     cta.warp.push_back(std::make_unique<std::barrier<>>(std::min(32u, block - 32 * w)));
   g_cta = &cta;
   blockDim.x = block;
-  gridDim.x = grid;
+  gridDim.x = grid.x;
+  gridDim.y = grid.y;
   std::barrier<> between(block);
   std::vector<std::thread> th;
   for (unsigned t = 0; t < block; t++)
     th.emplace_back([&, t] {
       threadIdx.x = t;
-      for (unsigned b = 0; b < grid; b++) {
-        blockIdx.x = b;
-        body();
-        between.arrive_and_wait();  // a CTA's static "shared memory" is reused by the next one
-      }
+      for (unsigned by = 0; by < grid.y; by++)
+        for (unsigned b = 0; b < grid.x; b++) {
+          blockIdx.x = b;
+          blockIdx.y = by;
+          body();
+          between.arrive_and_wait();  // a CTA's static "shared memory" is reused by the next one
+        }
     });
   for (auto& x : th) x.join();
   g_cta = nullptr;

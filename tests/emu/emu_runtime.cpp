@@ -72,6 +72,18 @@ int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm, con
   RF_API_END(ctx)
 }
 
+// table.cu / ctx.cu one-liners the scan needs
+void rfgpu_table_release(rfgpu_table* t) {
+  if (t && --t->refs == 0) delete t;
+}
+rfgpu_store* rfgpu_store_retain(rfgpu_store* s) {
+  if (s) s->refs++;
+  return s;
+}
+void rfgpu_store_release(rfgpu_store* s) {
+  if (s && --s->refs == 0) delete s;
+}
+
 rfgpu_ctx* emu_ctx_create() {
   auto* c = new rfgpu_ctx();
   c->core = std::make_shared<rf::Core>();
@@ -110,9 +122,9 @@ uint64_t emu_table_rows(const rfgpu_table* t) { return t->rows; }
 int32_t emu_table_cols(const rfgpu_table* t) { return (int32_t)t->cols.size(); }
 int32_t emu_table_sorted_col(const rfgpu_table* t) { return t->sorted_col; }
 const uint32_t* emu_table_col(const rfgpu_table* t, int32_t c) { return t->cols[c].data; }
-void emu_table_release(rfgpu_table* t) { delete t; }
+void emu_table_release(rfgpu_table* t) { rfgpu_table_release(t); }
 rfgpu_store* emu_store_create() { return new rfgpu_store(); }
-void emu_store_release(rfgpu_store* s) { delete s; }
+void emu_store_release(rfgpu_store* s) { rfgpu_store_release(s); }
 int32_t emu_store_indexes(const rfgpu_store* s) { return (int32_t)s->indexes.size(); }
 uint64_t emu_store_rows(const rfgpu_store* s, int32_t i) { return s->indexes[i].rows; }
 const uint32_t* emu_store_col(const rfgpu_store* s, int32_t i, int32_t level) { return s->indexes[i].col[level]->as<uint32_t>(); }
