@@ -57,6 +57,9 @@ def parse_args():
     ap.add_argument("--sort-merge-join", action="store_true",
                     help="with --hash-join: unsorted inputs are radix-sorted and merge-joined (RFGPU_OPT_SORT_MERGE_JOIN)")
     ap.add_argument("--hash-join", action="store_true", help="scan the join inputs through GPOS and force the hash join")
+    ap.add_argument("--sorted-build", action="store_true",
+                    help="with --hash-join: the build side (p2) is scanned in ?s order (GPSO), the probe side (p1) stays unsorted")
+    ap.add_argument("--no-lookup-join", action="store_true", help="dense keys: open-addressing hash table instead of the direct-address table")
     return ap.parse_args()
 
 
@@ -199,6 +202,8 @@ def run_ours(a):
         ctx.set_option(F.OPT_RADIX_JOIN, 1)
     if a.sort_merge_join:
         ctx.set_option(F.OPT_SORT_MERGE_JOIN, 1)
+    if a.no_lookup_join:
+        ctx.set_option(F.OPT_LOOKUP_JOIN, 0)
 
     # ---- set-up (untimed): the global graph has world * triples rows; this rank owns the quads whose subject hashes
     # to it, so every scan is local and the star join on ?s needs no exchange (weak scaling, no data-path collective)
@@ -221,6 +226,8 @@ def run_ours(a):
     # interesting order: both join inputs sorted on ?s (GPSO) → streaming merge join; --hash-join keeps GPOS + hash join
     if not a.hash_join:
         plan_j1.order_by("s")
+        plan_j2.order_by("s")
+    elif a.sorted_build:
         plan_j2.order_by("s")
 
     def step_device():
@@ -351,7 +358,8 @@ def run_ours(a):
 
     # operator view: the whole join (every kernel it launches) against its SURVEY §8d bytes 4(cb*Nb + cp*Np + co*No)
     roof_op = None
-    jk = {k: v for k, v in kern.items() if k.startswith(("k_merge_", "k_join_", "k_exclusive_scan", "k_rp_"))}
+    jk = {k: v for k, v in kern.items() if k.startswith(("k_merge_", "k_join_", "k_exclusive_scan", "k_rp_", "k_lookup_", "k_dense_",
+                                                         "k_suffix_", "k_key_min"))}
     if jk:
         jms = sum(v["ms"] for v in jk.values()) / a.steps
         jbytes = 4 * (2 * na + 2 * nb + 3 * nj)

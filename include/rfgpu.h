@@ -271,8 +271,9 @@ typedef enum {
   RFGPU_JOIN_PHYS_HASH = 1,  /* one open-addressing table in HBM */
   RFGPU_JOIN_PHYS_MERGE = 2, /* both inputs sorted on the key */
   RFGPU_JOIN_PHYS_RADIX = 3, /* radix-partitioned, per-partition tables in shared memory */
-  RFGPU_JOIN_PHYS_SORT_MERGE = 4 /* unsorted side(s) radix-sorted on the key, then the merge join (RFGPU_OPT_SORT_MERGE_JOIN);
+  RFGPU_JOIN_PHYS_SORT_MERGE = 4, /* unsorted side(s) radix-sorted on the key, then the merge join (RFGPU_OPT_SORT_MERGE_JOIN);
                                     for MINUS / EXISTS: sorted rhs key list + binary search (RFGPU_OPT_SORT_SEMI) */
+  RFGPU_JOIN_PHYS_LOOKUP = 5      /* dense build keys: direct-address (identity hash) table, one u32 per possible key */
 } rfgpu_join_phys;
 int32_t rfgpu_last_join_phys(const rfgpu_ctx* ctx);
 
@@ -369,6 +370,9 @@ typedef enum {
                                     list of the rhs keys instead of probing a hash table (default 0) */
   RFGPU_OPT_SORT_AGG = 10,       /* 1: GROUP BY / COUNT / DISTINCT over at most 4 columns by sort + run-length encoding
                                     (default 0) */
+  RFGPU_OPT_LOOKUP_JOIN = 11,    /* 1 (default): single-key equi joins, MINUS / EXISTS and GROUP BY whose (build) keys span a
+                                    range of at most 8 slots per input row use a direct-address table (slot = id - min id)
+                                    instead of the open-addressing hash table; 0: always hash */
   RFGPU_OPT_SHUFFLE_ARENA_BYTES = 7 /* size of this rank's receive arena (two halves, used alternately); read by
                                        rfgpu_comm_init, default 1 GiB.  A shuffle whose rows do not fit one half on some
                                        rank falls back to the NCCL exchange on every rank */

@@ -32,7 +32,7 @@ F_EQ_CONST, F_NE_CONST, F_EQ_COL, F_NE_COL, F_BETWEEN, F_IN, F_IS_NULL, F_IS_NOT
 JOIN_INNER, JOIN_LEFT = 0, 1
 ALGO_CROSS, ALGO_EQUI, ALGO_COMPATIBLE = 0, 1, 2
 SCAN_ALLOW_VIEW = 1
-PHYS_NONE, PHYS_HASH, PHYS_MERGE, PHYS_RADIX, PHYS_SORT_MERGE = 0, 1, 2, 3, 4
+PHYS_NONE, PHYS_HASH, PHYS_MERGE, PHYS_RADIX, PHYS_SORT_MERGE, PHYS_LOOKUP = 0, 1, 2, 3, 4, 5
 AGG_PHYS_NONE, AGG_PHYS_HASH, AGG_PHYS_SORT = 0, 1, 2
 OPT_MERGE_JOIN = 1
 OPT_MERGE_THREADS = 2
@@ -44,6 +44,7 @@ OPT_SHUFFLE_ARENA_BYTES = 7
 OPT_SORT_MERGE_JOIN = 8
 OPT_SORT_SEMI = 9
 OPT_SORT_AGG = 10
+OPT_LOOKUP_JOIN = 11
 SHUFFLE_LOCAL, SHUFFLE_NCCL, SHUFFLE_P2P = 0, 1, 2
 UNIQUE_ID_BYTES = 128
 

@@ -10,7 +10,7 @@
 #include <algorithm>
 #include <cstdlib>
 
-#include "merge_join.cuh"
+#include "lookup_join.cuh"
 #include "radix_join.cuh"
 
 namespace rf {
@@ -40,7 +40,6 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
   A.status = scratch->as<unsigned long long>();
   A.total = A.status + n_tiles;
   A.n_cols = (int32_t)specs.size();
-  if (const char* d = getenv("RFGPU_DEBUG_MERGE")) A.dbg = atoi(d);
   uint64_t in_cols_p = 0, in_cols_b = 0;
   for (size_t c = 0; c < specs.size(); c++) {
     A.cols[c] = specs[c];
@@ -63,17 +62,15 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
     RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_tiles * 8, ctx->stream()));  // look-back words
     {
       KernelScope ks(ctx, "k_merge_join", 4ull * (np + nb));  // keys; payload + output bytes are added below
-      static const size_t dbg_smem = getenv("RFGPU_DEBUG_SMEM") ? (size_t)atoi(getenv("RFGPU_DEBUG_SMEM")) : 0;  // occupancy experiments
       switch (threads) {
-        case 64: k_merge_join<64><<<n_tiles, 64, dbg_smem, ctx->stream()>>>(A); break;
-        case 128: k_merge_join<128><<<n_tiles, 128, dbg_smem, ctx->stream()>>>(A); break;
-        default: k_merge_join<256><<<n_tiles, 256, dbg_smem, ctx->stream()>>>(A); break;
+        case 64: k_merge_join<64><<<n_tiles, 64, 0, ctx->stream()>>>(A); break;
+        case 128: k_merge_join<128><<<n_tiles, 128, 0, ctx->stream()>>>(A); break;
+        default: k_merge_join<256><<<n_tiles, 256, 0, ctx->stream()>>>(A); break;
       }
     }
     RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 10, A.total, 8, cudaMemcpyDeviceToHost, ctx->stream()));
     ctx->sync();
     n_out = ctx->h_scratch[10];
-    if (A.dbg) n_out = std::min(n_out, cap);
     RF_REQUIRE(n_out <= kLimit, RFGPU_E_UNSUPPORTED,
                "join output exceeds 2^32-2 rows on one GPU (" + std::to_string(n_out) + ")");
     if (n_out <= cap) break;
@@ -83,6 +80,189 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
   // payload columns other than the staged keys are gathered once per output row; count them per §8(d) as inputs read once
   ctx->kstats[ctx->kstat_index("k_merge_join")].second.bytes +=
       4ull * (in_cols_p * np + in_cols_b * nb + specs.size() * n_out);
+  return n_out;
+}
+
+uint32_t grid_for(rfgpu_ctx* ctx, uint64_t n, int threads);
+
+// ---- direct-address (dense key) table: lookup_join.cuh ----
+struct DenseRange {
+  bool ok = false;      // the identity-hash table applies
+  uint32_t kmin = 1, range = 0;
+};
+
+// Bounds of the non-NULL build keys and whether a table of one u32 per possible key is worth it: at most 8 slots per
+// input row (memset + scan of the table stay below the cost of streaming the inputs) and at most 2^28 slots.
+DenseRange dense_range(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, bool sorted, uint64_t np) {
+  DenseRange D;
+  if (!ctx->opt_lookup_join || nb == 0 || nb >= 0xFFFFFFFFull) return D;
+  uint32_t* h = reinterpret_cast<uint32_t*>(ctx->h_scratch + 12);
+  bool have = false;
+  if (sorted) {  // ascending, NULL (0) first: the ends are the bounds unless NULLs lead
+    RF_CUDA(cudaMemcpyAsync(h, bk, 4, cudaMemcpyDeviceToHost, ctx->stream()));
+    RF_CUDA(cudaMemcpyAsync(h + 1, bk + nb - 1, 4, cudaMemcpyDeviceToHost, ctx->stream()));
+    ctx->sync();
+    have = h[0] != 0;
+  }
+  if (!have) {
+    BufRef d = ctx->alloc(16);
+    const unsigned int init[2] = {0xFFFFFFFFu, 0u};
+    RF_CUDA(cudaMemcpyAsync(d->ptr, init, 8, cudaMemcpyHostToDevice, ctx->stream()));
+    {
+      KernelScope ks(ctx, "k_key_min_max", 4ull * nb);
+      k_key_min_max<<<grid_for(ctx, div_up(nb, 4), 256), 256, 0, ctx->stream()>>>(bk, nb, d->as<unsigned int>());
+    }
+    RF_CUDA(cudaMemcpyAsync(h, d->ptr, 8, cudaMemcpyDeviceToHost, ctx->stream()));
+    ctx->sync();
+    if (h[1] == 0) {  // no non-NULL build key: an empty table, nothing matches
+      D.ok = true;
+      return D;
+    }
+    h[0] += 1;  // the kernel keeps min - 1
+  }
+  const uint64_t range = (uint64_t)h[1] - h[0] + 1;
+  if (range > (1ull << 28) || range > 8 * (nb + np) + 65536) return D;
+  D.ok = true;
+  D.kmin = h[0];
+  D.range = (uint32_t)range;
+  return D;
+}
+
+// offs[0 .. range] of lookup_join.cuh for a build side SORTED on the key; positions are build row numbers
+BufRef dense_table_sorted(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, const DenseRange& D, const uint32_t** offs) {
+  const uint64_t n = (uint64_t)D.range + 1;
+  BufRef tab = ctx->alloc(n * 4);
+  RF_CUDA(cudaMemsetAsync(tab->ptr, 0xFF, n * 4, ctx->stream()));
+  {
+    KernelScope ks(ctx, "k_dense_heads", 4ull * nb);
+    k_dense_heads<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(bk, nb, D.kmin, D.range, tab->as<uint32_t>());
+  }
+  const uint32_t tiles = div_up(n, kSmTile);
+  BufRef status = ctx->alloc((uint64_t)tiles * 8);
+  RF_CUDA(cudaMemsetAsync(status->ptr, 0, (uint64_t)tiles * 8, ctx->stream()));
+  {
+    KernelScope ks(ctx, "k_suffix_min_u32", 8ull * n);
+    k_suffix_min_u32<<<tiles, kSmThreads, 0, ctx->stream()>>>(tab->as<uint32_t>(), n, status->as<unsigned long long>());
+  }
+  *offs = tab->as<uint32_t>();
+  return tab;
+}
+
+// Counting sort of an UNSORTED build side by key: the table, and the columns `cols` (distinct build columns) rewritten in
+// key order into `sorted` (same order as cols).
+BufRef dense_table_unsorted(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, const DenseRange& D,
+                            const std::vector<const uint32_t*>& cols, std::vector<BufRef>* sorted, const uint32_t** offs) {
+  // raw[3] = 0 = offs[0]; cnt = raw + 4 is 16-byte aligned for the scan; offs = raw + 3 (see k_dense_fill)
+  BufRef raw = ctx->alloc(((uint64_t)D.range + 8) * 4);
+  RF_CUDA(cudaMemsetAsync(raw->ptr, 0, ((uint64_t)D.range + 8) * 4, ctx->stream()));
+  uint32_t* cnt = raw->as<uint32_t>() + 4;
+  sorted->clear();
+  for (size_t c = 0; c < cols.size(); c++) sorted->push_back(alloc_col(ctx, nb));
+  if (D.range) {
+    {
+      KernelScope ks(ctx, "k_dense_count", 4ull * nb);
+      k_dense_count<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(bk, nb, D.kmin, cnt);
+    }
+    exclusive_scan_u32(ctx, cnt, cnt, D.range, nullptr);
+    DenseFillArgs F{};
+    F.bk = bk;
+    F.nb = nb;
+    F.kmin = D.kmin;
+    F.cnt = cnt;
+    F.n_cols = (int32_t)cols.size();
+    for (size_t c = 0; c < cols.size(); c++) {
+      F.src[c] = cols[c];
+      F.dst[c] = (*sorted)[c]->as<uint32_t>();
+    }
+    KernelScope ks(ctx, "k_dense_fill", 4ull * (1 + 2 * cols.size()) * nb);
+    k_dense_fill<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(F);
+  }
+  *offs = raw->as<uint32_t>() + 3;
+  return raw;
+}
+
+// Equi join through the direct-address table; `specs` as for merge_join (probe columns by probe row, build columns by
+// build row).  Returns the output row count and fills `bufs`.
+uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint32_t* bk, uint64_t nb, bool build_sorted,
+                     bool left, const DenseRange& D, std::vector<OutColSpec> specs, std::vector<BufRef>* bufs) {
+  bufs->clear();
+  if (np == 0) {
+    for (size_t c = 0; c < specs.size(); c++) bufs->push_back(alloc_col(ctx, 0));
+    return 0;
+  }
+  RF_REQUIRE(specs.size() <= (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 output columns in one join");
+  RF_REQUIRE(np < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "join input exceeds 2^32-2 rows");
+  // a build-side key column in the output equals the probe key on every matched row (and Left joins preserve the probe side)
+  for (auto& sp : specs)
+    if (sp.build == bk && !sp.probe && !left) sp = OutColSpec{pk, nullptr};
+  const uint32_t* offs = nullptr;
+  BufRef tab;
+  std::vector<BufRef> sorted_cols;
+  uint64_t in_cols_b = 0;
+  if (build_sorted) {
+    tab = dense_table_sorted(ctx, bk, nb, D, &offs);
+    for (auto& sp : specs) in_cols_b += sp.build != nullptr && sp.build != bk;
+  } else {
+    std::vector<const uint32_t*> cols;
+    for (auto& sp : specs) {
+      if (!sp.build) continue;
+      bool seen = false;
+      for (auto q : cols) seen |= q == sp.build;
+      if (!seen) cols.push_back(sp.build);
+    }
+    tab = dense_table_unsorted(ctx, bk, nb, D, cols, &sorted_cols, &offs);
+    for (auto& sp : specs)
+      for (size_t c = 0; c < cols.size(); c++)
+        if (sp.build == cols[c]) {
+          sp.build = sorted_cols[c]->as<uint32_t>();
+          break;
+        }
+  }
+  const int threads = 128;
+  const uint32_t n_tiles = div_up(np, (uint64_t)threads * 8);
+  BufRef scratch = ctx->alloc((uint64_t)n_tiles * 8 + 16);
+  LookupArgs A{};
+  A.pk = pk;
+  A.np = np;
+  A.offs = offs;
+  A.kmin = D.kmin;
+  A.range = D.range;
+  A.left = left ? 1 : 0;
+  A.n_tiles = n_tiles;
+  A.status = scratch->as<unsigned long long>();
+  A.total = A.status + n_tiles;
+  A.n_cols = (int32_t)specs.size();
+  uint64_t in_cols_p = 0;
+  for (size_t c = 0; c < specs.size(); c++) {
+    A.cols[c] = specs[c];
+    in_cols_p += specs[c].probe != nullptr && specs[c].probe != pk;
+  }
+  const uint64_t kLimit = 0xFFFFFFFEull;
+  uint64_t cap = std::min<uint64_t>(kLimit, 2 * std::max(np, nb) + 1024);  // optimistic, as in merge_join()
+  uint64_t n_out = 0;
+  for (int attempt = 0;; attempt++) {
+    bufs->clear();
+    for (size_t c = 0; c < specs.size(); c++) {
+      bufs->push_back(alloc_col(ctx, cap));
+      A.dst[c] = (*bufs)[c]->as<uint32_t>();
+    }
+    A.cap = cap;
+    RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_tiles * 8, ctx->stream()));
+    {
+      KernelScope ks(ctx, "k_lookup_join", 4ull * np);
+      k_lookup_join<128><<<n_tiles, 128, 0, ctx->stream()>>>(A);
+    }
+    RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 10, A.total, 8, cudaMemcpyDeviceToHost, ctx->stream()));
+    ctx->sync();
+    n_out = ctx->h_scratch[10];
+    RF_REQUIRE(n_out <= kLimit, RFGPU_E_UNSUPPORTED,
+               "join output exceeds 2^32-2 rows on one GPU (" + std::to_string(n_out) + ")");
+    if (n_out <= cap) break;
+    RF_REQUIRE(attempt == 0, RFGPU_E_EXEC, "lookup join total changed between passes");
+    cap = n_out;
+  }
+  ctx->kstats[ctx->kstat_index("k_lookup_join")].second.bytes +=
+      4ull * (in_cols_p * np + (build_sorted ? (1 + in_cols_b) * nb : 0) + specs.size() * n_out);
   return n_out;
 }
 
@@ -507,7 +687,17 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
     RF_REQUIRE(keys.size() <= 2, RFGPU_E_UNSUPPORTED, "equi join on more than 2 shared variables");
     // Left: lhs must be the preserved (probe) side.  Inner: build on the smaller input (JoinSelection does the same
     // from statistics; the multiset does not depend on it).
-    const bool probe_is_l = left || L->rows >= R->rows;
+    bool probe_is_l = left || L->rows >= R->rows;
+    if (!left && keys.size() == 1 && ctx->opt_lookup_join) {
+      // exactly one input sorted on the key: build on it (its direct-address table needs no counting sort) unless it is
+      // much the larger side
+      const bool ls = L->sorted_col == keys[0].l, rs = R->sorted_col == keys[0].r;
+      if (ls != rs) {
+        const rfgpu_table* sorted_side = ls ? L : R;
+        const rfgpu_table* other = ls ? R : L;
+        if (sorted_side->rows <= 4 * other->rows + 1024) probe_is_l = !ls;
+      }
+    }
     const rfgpu_table* Pt = probe_is_l ? L : R;
     const rfgpu_table* Bt = probe_is_l ? R : L;
     auto kc = [&](const rfgpu_table* t, size_t k) -> const uint32_t* {
@@ -552,6 +742,20 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
       ctx->last_join_phys = RFGPU_JOIN_PHYS_MERGE;
       T->sorted_col = keys[0].l;
       return finish(bufs, n_out);
+    }
+    // dense build keys (object ids are dictionary ids): identity-hash table, one u32 per possible key, probe = one 16-byte
+    // load from an L2-resident table; a build side sorted on the key needs no counting sort
+    if (keys.size() == 1 && Pt->rows > 0 && Bt->rows > 0) {
+      const int bkey = Bt == L ? keys[0].l : keys[0].r;
+      const bool bsorted = Bt->sorted_col == bkey;
+      const DenseRange D = dense_range(ctx, kc(Bt, 0), Bt->rows, bsorted, Pt->rows);
+      if (D.ok) {
+        std::vector<BufRef> bufs;
+        const uint64_t n_out = lookup_join(ctx, kc(Pt, 0), Pt->rows, kc(Bt, 0), Bt->rows, bsorted, left, D, specs, &bufs);
+        ctx->last_join_phys = RFGPU_JOIN_PHYS_LOOKUP;
+        T->sorted_col = out_sorted;
+        return finish(bufs, n_out);
+      }
     }
     if (ctx->opt_radix_join && Bt->rows >= (uint64_t)ctx->opt_radix_min_rows) {
       std::vector<BufRef> bufs;
@@ -974,6 +1178,7 @@ int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value) {
   RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
   switch (option) {
     case RFGPU_OPT_MERGE_JOIN: ctx->opt_merge_join = value != 0; break;
+    case RFGPU_OPT_LOOKUP_JOIN: ctx->opt_lookup_join = value != 0; break;
     case RFGPU_OPT_SORT_MERGE_JOIN: ctx->opt_sort_merge_join = value != 0; break;
     case RFGPU_OPT_SORT_SEMI: ctx->opt_sort_semi = value != 0; break;
     case RFGPU_OPT_SORT_AGG: ctx->opt_sort_agg = value != 0; break;

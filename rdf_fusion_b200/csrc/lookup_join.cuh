@@ -1,0 +1,453 @@
+// lookup_join.cuh — kernel 3, direct-address form: the build/probe hash join on object ids when the build keys are DENSE.
+//
+// What it replaces: DataFusion 52 HashJoinExec(mode=CollectLeft) as configured by try_build_regular_join
+// (lib/logical/src/join/rewrite.rs:126-168): equi join on one UInt32 key column, NullEqualsNothing, Inner / Left.
+//
+// Why: object ids are dictionary ids (lib/storage/src/memory/object_id_mapping.rs), i.e. dense integers, and the keys of a
+// join (the subjects of a predicate, the objects that are entities) span a range not much larger than their number.  The
+// open-addressing table of join_kernels.cuh pays ~3 random HBM sectors per key (hash slot, CSR offsets, row id) into a
+// table that does not fit L2: 44 G random loads/s from DRAM against 289 G/s from L2 (profiles/r2a_hwbench.json).  With the
+// identity hash  slot = key - kmin  the table needs no keys, no CAS and no collision handling; it is ONE u32 per possible
+// key (40 MB for the 10^7 subjects of BASELINE configs[1]: L2-resident) and a probe is one aligned 16-byte load:
+//
+//   offs[i] = number of build rows with key < kmin + i      (i = 0 .. range; build rows in KEY order)
+//   build rows of key k = positions [offs[k - kmin], offs[k - kmin + 1])
+//
+// Build, sorted build side (a scan in index order — every rhs of a left-deep BGP fold can be one):
+//   k_dense_heads     offs[key - kmin] = row, written once per distinct key at the head of its run
+//   k_suffix_min_u32  absent keys take the next present key's start (in-place suffix-min scan, decoupled look-back)
+// Build, unsorted build side: counting sort of the build rows by key
+//   k_dense_count (RED.ADD per row) -> exclusive scan -> k_dense_fill (cursor per key, payload columns written in key order)
+// Probe + expand (k_lookup_join): one pass, same output stage as the merge join — per tile of probe rows: coalesced key
+// loads, table look-ups (4 rows x 16 B in flight per thread), block scan of the match counts, decoupled look-back for the
+// tile's output offset, max-scan expansion with coalesced stores.  Output rows come out in probe order.
+#pragma once
+#include "merge_join.cuh"
+
+namespace rf {
+
+// ---------------- min / max of the non-NULL keys ----------------
+__global__ void __launch_bounds__(256)
+k_key_min_max(const uint32_t* __restrict__ k, uint64_t n, unsigned int* __restrict__ out /*min, max*/) {
+  uint32_t mn = 0xFFFFFFFFu, mx = 0;
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i + 3 * stride < n; i += 4 * stride) {
+    uint32_t x[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) x[u] = __ldg(k + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      mx = max(mx, x[u]);
+      mn = min(mn, x[u] - 1u);  // 0 (NULL) wraps to UINT32_MAX and never wins
+    }
+  }
+  for (; i < n; i += stride) {
+    const uint32_t x = __ldg(k + i);
+    mx = max(mx, x);
+    mn = min(mn, x - 1u);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mn = min(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, o));
+    mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+  }
+  // one atomic pair per CTA: thousands of same-address atomics would serialise in L2 for longer than the reads take
+  __shared__ uint32_t s_mn[8], s_mx[8];
+  if ((threadIdx.x & 31) == 0) {
+    s_mn[threadIdx.x >> 5] = mn;
+    s_mx[threadIdx.x >> 5] = mx;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int w = 1; w < 8; w++) {
+      mn = min(mn, s_mn[w]);
+      mx = max(mx, s_mx[w]);
+    }
+    if (mx != 0) {
+      atomicMin(out, mn);  // holds min - 1
+      atomicMax(out + 1, mx);
+    }
+  }
+}
+
+// ---------------- sorted build side: run heads + suffix-min ----------------
+__global__ void __launch_bounds__(256)
+k_dense_heads(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t range, uint32_t* __restrict__ offs) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) offs[range] = (uint32_t)nb;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < nb; i += stride) {
+    const uint32_t k = __ldg(bk + i);
+    if (k != 0 && (i == 0 || __ldg(bk + i - 1) != k)) offs[k - kmin] = (uint32_t)i;
+  }
+}
+
+constexpr int kSmThreads = 256;
+constexpr int kSmItems = 16;
+constexpr int kSmTile = kSmThreads * kSmItems;
+
+// a[i] = min(a[i], a[i+1], ..., a[n-1]) in place.  Tile b covers the b-th tile counted from the END of the array, so that
+// a tile only waits on lower-numbered blocks (status word: [63:62] flag, [31:0] value; identity = UINT32_MAX).
+__global__ void __launch_bounds__(kSmThreads)
+k_suffix_min_u32(uint32_t* __restrict__ a, uint64_t n, unsigned long long* __restrict__ status) {
+  __shared__ uint32_t s_warp[kSmThreads / 32];
+  __shared__ uint32_t s_excl;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t tile = blockIdx.x;
+  // item j of this thread (j = 0 is the RIGHTMOST): index n - 1 - (tile * kSmTile + tid * kSmItems + j)
+  const uint64_t r0 = (uint64_t)tile * kSmTile + (uint64_t)tid * kSmItems;
+  uint32_t v[kSmItems];
+  // the thread's items are the 16 consecutive words ending at index n - 1 - r0: four 16-byte accesses when they are all
+  // inside the array and the run is 16-byte aligned (a is 256-byte aligned, so that is n % 4 == 0)
+  const bool vec = r0 + kSmItems <= n && (n & 3) == 0;
+  if (vec) {
+    const uint4* p = reinterpret_cast<const uint4*>(a + (n - r0 - kSmItems));
+#pragma unroll
+    for (int q = 0; q < kSmItems / 4; q++) {
+      const uint4 x = p[q];  // words n-r0-16+4q .. +3  =  items j = 15-4q, 14-4q, 13-4q, 12-4q
+      v[kSmItems - 1 - 4 * q] = x.x;
+      v[kSmItems - 2 - 4 * q] = x.y;
+      v[kSmItems - 3 - 4 * q] = x.z;
+      v[kSmItems - 4 - 4 * q] = x.w;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < kSmItems; j++) v[j] = r0 + j < n ? a[n - 1 - (r0 + j)] : 0xFFFFFFFFu;
+  }
+#pragma unroll
+  for (int j = 1; j < kSmItems; j++) v[j] = min(v[j], v[j - 1]);  // inclusive, right to left
+  const uint32_t tmin = v[kSmItems - 1];
+  uint32_t incl = tmin;  // inclusive over the threads to the right (lower tid)
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if ((int)lane >= o) incl = min(incl, t);
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  uint32_t texcl = __shfl_up_sync(0xFFFFFFFFu, incl, 1);
+  if (lane == 0) texcl = 0xFFFFFFFFu;
+  __syncthreads();
+  uint32_t wexcl = 0xFFFFFFFFu, bmin = 0xFFFFFFFFu;
+#pragma unroll
+  for (int w = 0; w < kSmThreads / 32; w++) {
+    const uint32_t x = s_warp[w];
+    if (w < (int)warp) wexcl = min(wexcl, x);
+    bmin = min(bmin, x);
+  }
+  if (warp == 0) {
+    if (lane == 0) dev::st_status(status + tile, (tile == 0 ? dev::kFlagP : dev::kFlagA) | bmin);
+    uint32_t excl = 0xFFFFFFFFu;
+    if (tile != 0) {
+      int64_t look = (int64_t)tile - 1;
+      while (true) {
+        const int64_t idx = look - lane;
+        const unsigned long long s = idx >= 0 ? dev::ld_status(status + idx) : (dev::kFlagP | 0xFFFFFFFFull);
+        const uint32_t flag = (uint32_t)(s >> 62);
+        const uint32_t pmask = __ballot_sync(0xFFFFFFFFu, flag == 2);
+        const uint32_t invalid = __ballot_sync(0xFFFFFFFFu, flag == 0);
+        const int firstP = pmask ? (__ffs(pmask) - 1) : 32;
+        const uint32_t need = firstP == 32 ? 0xFFFFFFFFu : ((2u << firstP) - 1u);
+        if (invalid & need) {
+          __nanosleep(64);
+          continue;
+        }
+        uint32_t val = ((int)lane <= firstP) ? (uint32_t)(s & 0xFFFFFFFFull) : 0xFFFFFFFFu;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) val = min(val, __shfl_xor_sync(0xFFFFFFFFu, val, o));
+        excl = min(excl, val);
+        if (pmask) break;
+        look -= 32;
+      }
+      if (lane == 0) dev::st_status(status + tile, dev::kFlagP | min(excl, bmin));
+    }
+    if (lane == 0) s_excl = excl;
+  }
+  __syncthreads();
+  const uint32_t base = min(s_excl, min(wexcl, texcl));
+  if (vec) {
+    uint4* p = reinterpret_cast<uint4*>(a + (n - r0 - kSmItems));
+#pragma unroll
+    for (int q = 0; q < kSmItems / 4; q++)
+      p[q] = make_uint4(min(v[kSmItems - 1 - 4 * q], base), min(v[kSmItems - 2 - 4 * q], base),
+                        min(v[kSmItems - 3 - 4 * q], base), min(v[kSmItems - 4 - 4 * q], base));
+  } else {
+#pragma unroll
+    for (int j = 0; j < kSmItems; j++)
+      if (r0 + j < n) a[n - 1 - (r0 + j)] = min(v[j], base);
+  }
+}
+
+// ---------------- unsorted build side: counting sort by key ----------------
+__global__ void __launch_bounds__(256)
+k_dense_count(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t* __restrict__ cnt) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < nb; i += stride) {
+    const uint32_t k = __ldg(bk + i);
+    if (k != 0) atomicAdd(cnt + (k - kmin), 1u);  // no return value: RED.ADD
+  }
+}
+
+struct DenseFillArgs {
+  const uint32_t* bk;
+  uint64_t nb;
+  uint32_t kmin;
+  uint32_t* cnt;  // after the exclusive scan cnt[s] = start(s); the fill walks it to end(s) = start(s + 1)
+  const uint32_t* src[kMaxCols];
+  uint32_t* dst[kMaxCols];
+  int32_t n_cols;
+};
+
+__global__ void __launch_bounds__(256)
+k_dense_fill(const __grid_constant__ DenseFillArgs A) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < A.nb; i += stride) {
+    const uint32_t k = __ldg(A.bk + i);
+    if (k == 0) continue;
+    const uint32_t pos = atomicAdd(A.cnt + (k - A.kmin), 1u);
+    for (int c = 0; c < A.n_cols; c++) A.dst[c][pos] = __ldg(A.src[c] + i);
+  }
+}
+
+// ---------------- probe + expand ----------------
+struct LookupArgs {
+  const uint32_t* pk;  // probe keys (any order, 0 = NULL never matches)
+  uint64_t np;
+  const uint32_t* offs;  // [range + 1], any 4-byte alignment; the 16-byte look-up reads the enclosing aligned granule, so the
+                         // allocation has >= 3 readable words on either side
+  uint32_t kmin, range;
+  int32_t left;  // probe side preserved (OPTIONAL): unmatched probe rows emit one padded row
+  uint32_t n_tiles;
+  unsigned long long* status;  // look-back words [n_tiles]
+  unsigned long long* total;   // out: exact number of output rows
+  uint64_t cap;                // rows the dst columns can hold
+  OutColSpec cols[kMaxCols];   // probe: indexed by probe row; build: indexed by build POSITION (key order)
+  uint32_t* dst[kMaxCols];
+  int32_t n_cols;
+};
+
+template <int kLThreads>
+struct LookupSmem {
+  static constexpr int kTile = kLThreads * 8;
+  __align__(16) uint32_t gs[kTile];       // first build position of the row's key group; kNone = no match
+  __align__(16) uint32_t off[kTile + 4];  // emitted rows per probe row, then their exclusive prefix
+  uint32_t H[kTile + kTile / 8 + 8];      // expansion buffer
+  unsigned long long sc[kLThreads / 32];
+  unsigned long long base;
+  uint32_t wmax[kLThreads / 32];
+};
+
+template <int kLThreads>
+__global__ void __launch_bounds__(kLThreads, kLThreads == 128 ? 12 : 1)
+k_lookup_join(const __grid_constant__ LookupArgs A) {
+  constexpr int kTile = kLThreads * 8, kChunk = kTile;
+  __shared__ LookupSmem<kLThreads> S;
+  const uint32_t tile = blockIdx.x, tid = threadIdx.x;
+  const uint32_t lane = tid & 31, warp = tid >> 5;
+  const uint64_t row0 = (uint64_t)tile * kTile;
+  const uint32_t rows = (uint32_t)min((uint64_t)kTile, A.np - row0);
+  const uint32_t leftpad = A.left ? 1u : 0u;
+  // the table is probed at random by every tile and should stay in L2; keys, probe payload and output only stream through
+  const uint64_t keep = dev::l2_policy_evict_last(), strm = dev::l2_policy_evict_first();
+
+  // ---- keys (coalesced, striped) and table look-ups, 4 rows at a time: 4 x 16 B in flight per thread ----
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    uint32_t key[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const uint32_t i = tid + (h * 4 + k) * kLThreads;
+      key[k] = i < rows ? dev::ld_hint_u32(A.pk + row0 + i, strm) : 0u;
+    }
+    uint4 v[4];
+    uint32_t slot[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      slot[k] = key[k] - A.kmin;  // NULL (0) and keys below kmin wrap to >= range
+      v[k] = make_uint4(0u, 0u, 0u, 0u);
+      if (slot[k] < A.range)
+        v[k] = dev::ld_hint_v4(reinterpret_cast<const uint4*>((uintptr_t)(A.offs + slot[k]) & ~(uintptr_t)15), keep);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const uint32_t i = tid + (h * 4 + k) * kLThreads;
+      uint32_t o0 = 0, o1 = 0;
+      if (slot[k] < A.range) {
+        const uint32_t q = (uint32_t)((uintptr_t)(A.offs + slot[k]) >> 2) & 3u;
+        o0 = q == 0 ? v[k].x : q == 1 ? v[k].y : q == 2 ? v[k].z : v[k].w;
+        o1 = q == 0 ? v[k].y : q == 1 ? v[k].z : q == 2 ? v[k].w : dev::ld_hint_u32(A.offs + slot[k] + 1, keep);
+      }
+      const uint32_t cnt = o1 - o0;
+      S.gs[i] = cnt ? o0 : kNone;
+      S.off[i] = i < rows ? (cnt ? cnt : leftpad) : 0u;
+    }
+  }
+  if (tid < 4) S.off[kTile + tid] = 0;
+  if (tid == kLThreads - 1) {
+    // pull this tile's probe payload into L2 now: the expansion gathers it later
+    for (int c = 0; c < A.n_cols; c++) {
+      const uint32_t* pp = A.cols[c].probe;
+      if (pp && pp != A.pk) {
+        const uintptr_t a0 = (uintptr_t)(pp + row0) & ~(uintptr_t)15;
+        const uintptr_t a1 = ((uintptr_t)(pp + row0 + rows) + 15) & ~(uintptr_t)15;
+        dev::bulk_prefetch_l2((const void*)a0, (uint32_t)(a1 - a0));
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- exclusive scan of the emitted-row counts (8 consecutive rows per thread) ----
+  uint32_t e[8];
+  {
+    const uint4* p4 = reinterpret_cast<const uint4*>(&S.off[tid * 8]);
+    const uint4 x = p4[0], y = p4[1];
+    e[0] = x.x; e[1] = x.y; e[2] = x.z; e[3] = x.w; e[4] = y.x; e[5] = y.y; e[6] = y.z; e[7] = y.w;
+  }
+  unsigned long long t = 0;
+#pragma unroll
+  for (int r = 0; r < 8; r++) t += e[r];
+  unsigned long long tot;
+  const unsigned long long pre = block_excl_u64<kLThreads>(t, S.sc, &tot);
+  // publish the tile aggregate now, resolve the look-back only when the first stores need it
+  if (warp == 0) dev::lookback_publish(A.status, tile, tot);
+  {  // each thread overwrites only the 8 counts it has read itself
+    uint32_t run = (uint32_t)pre;
+    uint4 x, y;
+    x.x = run; run += e[0]; x.y = run; run += e[1]; x.z = run; run += e[2]; x.w = run; run += e[3];
+    y.x = run; run += e[4]; y.y = run; run += e[5]; y.z = run; run += e[6]; y.w = run; run += e[7];
+    uint4* p4 = reinterpret_cast<uint4*>(&S.off[tid * 8]);
+    p4[0] = x;
+    p4[1] = y;
+    if (tid == kLThreads - 1) S.off[kTile] = run;
+  }
+  auto resolve = [&]() {
+    if (warp == 0) {
+      const unsigned long long excl = dev::lookback_resolve(A.status, tile, tot);
+      if (lane == 0) {
+        S.base = excl;
+        if (tile == A.n_tiles - 1) *A.total = excl + tot;
+      }
+    }
+  };
+  if (tot == 0 || tot > 0xFFFFFFFEull) {  // nothing this tile could write
+    resolve();
+    return;
+  }
+  __syncthreads();
+
+  // ---- expansion, kChunk output rows per round (as in merge_join.cuh) ----
+  uint32_t* H = S.H;
+  const uint32_t tot32 = (uint32_t)tot;
+  unsigned long long base = 0;
+  uint32_t carry = 0;  // (row + 1) covering the last slot of the previous round
+  for (uint32_t c0 = 0; c0 < tot32; c0 += kChunk) {
+    const uint32_t n = min((uint32_t)kChunk, tot32 - c0);
+#pragma unroll
+    for (int k = 0; k < 8; k++) H[tid * 9 + k] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const uint32_t i = tid + k * kLThreads;
+      const uint32_t o = S.off[i];
+      const uint32_t rel = o - c0;  // o < c0 wraps around: not in this round
+      if (S.off[i + 1] != o && rel < (uint32_t)kChunk) H[hpad(rel)] = i + 1;
+    }
+    __syncthreads();
+    uint32_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = H[tid * 9 + k];
+#pragma unroll
+    for (int k = 1; k < 8; k++) v[k] = max(v[k], v[k - 1]);
+    uint32_t inc = v[7];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+      if ((int)lane >= o) inc = max(inc, u);
+    }
+    if (lane == 31) S.wmax[warp] = inc;
+    uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, inc, 1);
+    if (lane == 0) prev = 0;
+    __syncthreads();
+    uint32_t m = max(carry, prev);
+#pragma unroll
+    for (int w = 0; w < kLThreads / 32; w++)
+      if (w < (int)warp) m = max(m, S.wmax[w]);
+#pragma unroll
+    for (int k = 0; k < 8; k++) H[tid * 9 + k] = max(v[k], m);
+    __syncthreads();
+    carry = H[hpad(kChunk - 1)];
+    // slot -> (probe row, build position); slots of one thread are kLThreads apart so every store is coalesced
+    uint32_t prow[8], brow[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const uint32_t jj = tid + k * kLThreads;
+      uint32_t row = 0, b = kNone;
+      if (jj < n) {
+        row = H[hpad(jj)] - 1;
+        const uint32_t g = S.gs[row];
+        if (g != kNone) b = g + (c0 + jj - S.off[row]);
+      }
+      prow[k] = row;
+      brow[k] = b;
+    }
+    if (c0 == 0) {
+      resolve();
+      __syncthreads();
+      base = S.base;
+      if (base + tot > A.cap) return;  // over the optimistic capacity: the host re-runs with the exact size
+    }
+    for (int c = 0; c < A.n_cols; c++) {
+      const uint32_t* __restrict__ pp = A.cols[c].probe;
+      const uint32_t* __restrict__ bp = A.cols[c].build;
+      uint32_t* __restrict__ d = A.dst[c] + base + c0 + tid;
+      if (pp) pp += row0;
+      if (pp && !bp) {
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+          if (tid + k * kLThreads < n) dev::st_hint_u32(d + k * kLThreads, dev::ld_hint_u32(pp + prow[k], strm), strm);
+      } else if (!pp) {
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+          if (tid + k * kLThreads < n)
+            dev::st_hint_u32(d + k * kLThreads, (bp && brow[k] != kNone) ? dev::ld_hint_u32(bp + brow[k], keep) : 0u, strm);
+      } else {  // COALESCE(probe, build)
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+          if (tid + k * kLThreads < n) {
+            uint32_t val = dev::ld_hint_u32(pp + prow[k], strm);
+            if (val == 0 && brow[k] != kNone) val = dev::ld_hint_u32(bp + brow[k], keep);
+            dev::st_hint_u32(d + k * kLThreads, val, strm);
+          }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------- existence / counts over the same table (MINUS, [NOT] EXISTS, GROUP BY key COUNT) ----------------
+// flag[i] = 1 where probe key i has at least one build row (flag is left alone elsewhere)
+__global__ void __launch_bounds__(256)
+k_dense_contains(const uint32_t* __restrict__ pk, uint64_t np, const uint32_t* __restrict__ cnt, uint32_t kmin,
+                 uint32_t range, uint32_t* __restrict__ flag) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i + 3 * stride < np; i += 4 * stride) {
+    uint32_t s[4], c[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) s[u] = __ldg(pk + i + u * stride) - kmin;
+#pragma unroll
+    for (int u = 0; u < 4; u++) c[u] = s[u] < range ? __ldg(cnt + s[u]) : 0u;
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (c[u]) flag[i + u * stride] = 1u;
+  }
+  for (; i < np; i += stride) {
+    const uint32_t s = __ldg(pk + i) - kmin;
+    if (s < range && __ldg(cnt + s)) flag[i] = 1u;
+  }
+}
+
+}  // namespace rf

@@ -52,7 +52,6 @@ struct MergeArgs {
   OutColSpec cols[kMaxCols];
   uint32_t* dst[kMaxCols];
   int32_t n_cols;
-  int32_t dbg;  // experiments only: 1 = stop before the expansion, 2 = no look-back, 4 = stop after staging
 };
 
 // One 32-ary narrowing step of a warp-cooperative bound search: the answer stays in [lo, hi].
@@ -254,7 +253,6 @@ k_merge_join(const __grid_constant__ MergeArgs A) {
   const uint32_t* sp = &S.pk[psh];
   const uint32_t* sb = &S.bk[bsh];
   const uint32_t leftpad = A.left ? 1u : 0u;
-  if (A.dbg & 4) return;
 
   if (staged) {
     // ---- merge-path split: thread t walks merged items [d0, d1); build keys <= probe key come first ----
@@ -342,7 +340,7 @@ k_merge_join(const __grid_constant__ MergeArgs A) {
   const unsigned long long pre = block_excl_u64<kMThreads>(t, S.sc, &tot);
   // publish the tile aggregate now, resolve the look-back only when the first stores need it: the expansion's local
   // work and the flight time of the predecessors' words overlap
-  if (warp == 0 && !(A.dbg & 2)) dev::lookback_publish(A.status, tile, tot);
+  if (warp == 0) dev::lookback_publish(A.status, tile, tot);
   {
     // local offsets fit 32 bits whenever this tile is written at all (cap < 2^32)
     uint32_t run = (uint32_t)pre;
@@ -356,14 +354,14 @@ k_merge_join(const __grid_constant__ MergeArgs A) {
   }
   auto resolve = [&]() {
     if (warp == 0) {
-      const unsigned long long excl = (A.dbg & 2) ? 0ull : dev::lookback_resolve(A.status, tile, tot);
+      const unsigned long long excl = dev::lookback_resolve(A.status, tile, tot);
       if (lane == 0) {
         S.base = excl;
         if (tile == A.n_tiles - 1) *A.total = excl + tot;
       }
     }
   };
-  if (tot == 0 || tot > 0xFFFFFFFEull || (A.dbg & 1)) {  // nothing this tile could write
+  if (tot == 0 || tot > 0xFFFFFFFEull) {  // nothing this tile could write
     resolve();
     return;
   }

@@ -99,6 +99,7 @@ struct rfgpu_ctx {
   int last_join_algo = -1;
   int last_join_phys = 0;
   bool opt_merge_join = true;
+  bool opt_lookup_join = true;       // dense build keys: direct-address table instead of the open-addressing hash table
   bool opt_radix_join = false;       // opt-in: radix-partitioned shared-memory hash join (correct, not yet faster: DESIGN.md §5)
   int64_t opt_radix_min_rows = 65536;  // build rows below which the one-table hash join is used
   int64_t opt_hash_l2_bytes = 1ll << 40;   // table bytes one pass of the hash join may hold; > this ⇒ multi-pass L2 blocking

@@ -145,6 +145,43 @@ __device__ __host__ __forceinline__ uint32_t mix64to32(uint64_t x) {
   return (uint32_t)x;
 }
 
+// ---------------- L2 residency hints ----------------
+// A look-up table that every tile probes at random competes for L2 with the columns that only stream through the kernel.
+// evict_last keeps the table's lines, evict_first lets the streamed lines go first (PTX createpolicy + L2::cache_hint).
+#ifdef __CUDACC__
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint4 ld_hint_v4(const uint4* p, uint64_t pol) {
+  uint4 v;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_hint_u32(const uint32_t* p, uint64_t pol) {
+  uint32_t v;
+  asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ void st_hint_u32(uint32_t* p, uint32_t v, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(p), "r"(v), "l"(pol) : "memory");
+}
+#else  // host build of tests/emu: the hints have no meaning there
+inline uint64_t l2_policy_evict_last() { return 0; }
+inline uint64_t l2_policy_evict_first() { return 0; }
+inline uint4 ld_hint_v4(const uint4* p, uint64_t) { return *p; }
+inline uint32_t ld_hint_u32(const uint32_t* p, uint64_t) { return *p; }
+inline void st_hint_u32(uint32_t* p, uint32_t v, uint64_t) { *p = v; }
+#endif
+
 #ifdef __CUDACC__  // the TMA / mbarrier wrappers exist on the device only
 // ---------------- mbarrier + 1-D bulk async copy (TMA engine, SASS: UBLKCP) ----------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }

@@ -83,7 +83,7 @@ def build(asan=False, tsan=False):
             open(dst, "w").write(text)
         cpps.append(dst)
         newest = max(newest, os.path.getmtime(dst))
-    for h in ("merge_join.cuh", "join_kernels.cuh", "radix_join.cuh"):  # kernel headers get the same rewrite, next to the sources
+    for h in ("merge_join.cuh", "join_kernels.cuh", "radix_join.cuh", "lookup_join.cuh"):  # kernel headers get the same rewrite, next to the sources
         text, _ = rewrite_launches(rewrite_dynamic_smem(open(os.path.join(CSRC, h)).read()))
         dst = os.path.join(BUILD, h)
         if not os.path.exists(dst) or open(dst).read() != text:

@@ -422,6 +422,43 @@ def test_merge_join_and_sort_merge_join(emu, oracle, jt):
             _ok(emu, emu.rfgpu_ctx_set_option(emu.ctx, F.OPT_SORT_MERGE_JOIN, 0))
 
 
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_lookup_join_dense_keys(emu, oracle, jt):
+    """lookup_join.cuh: the direct-address table for a sorted build side (run heads + suffix-min scan) and an unsorted one
+    (counting sort), the fused probe + expansion kernel over several tiles, heavy keys, keys outside the build range, and the
+    same joins with the option off (open-addressing hash table)"""
+    rng = np.random.default_rng(77 + jt)
+    shapes = some([(1, 1, 1, 0), (5000, 3000, 900, 100), (2600, 9000, 40, 7), (1500, 1200, 50000, 3), (9000, 20, 6, 0)],
+                  [(2300, 1400, 500, 60), (1100, 2600, 30, 5)])
+    for nl_, nr_, hi, base in shapes:
+        ln, rn = ["a", "k", "c"], ["k", "z"]
+        lc = [rng.integers(1, 1000, nl_).astype(np.uint32), rng.integers(1, hi + 40, nl_).astype(np.uint32) + base,
+              rng.integers(1, 1000, nl_).astype(np.uint32)]
+        rc = [rng.integers(20, hi + 21, nr_).astype(np.uint32) + base, rng.integers(1, 1000, nr_).astype(np.uint32)]
+        OL, OR = oracle.OTable(ln, [False] * 3, lc), oracle.OTable(rn, [False] * 2, rc)
+        exp = oracle.sparql_join(OL, OR, jt, "hash")[0]
+        b = oracle.canonical_rows(exp.cols)
+        ro = np.argsort(rc[0], kind="stable")
+        for r_sorted, lookup in ((False, 1), (True, 1), (False, 0)):
+            _ok(emu, emu.rfgpu_ctx_set_option(emu.ctx, F.OPT_LOOKUP_JOIN, lookup))
+            try:
+                L = _named(emu, ln, [False] * 3, lc)
+                R = (_named(emu, rn, [False] * 2, [c[ro] for c in rc], sorted_col=0) if r_sorted
+                     else _named(emu, rn, [False] * 2, rc))
+                out = vp()
+                _ok(emu, emu.rfgpu_sparql_join(emu.ctx, L, R, jt, C.byref(out)))
+                phys = emu.rfgpu_last_join_phys(emu.ctx)
+                dense = hi + 40 <= 8 * (nl_ + nr_) + 65536
+                assert phys == (F.PHYS_LOOKUP if lookup and dense else F.PHYS_HASH), (phys, nl_, nr_, hi)
+                names, _, cols = _take(emu, out)
+                a = oracle.canonical_rows(cols)
+                assert names == exp.names and a.shape == b.shape and np.array_equal(a, b), (nl_, nr_, hi, r_sorted, lookup)
+                emu.emu_table_release(L)
+                emu.emu_table_release(R)
+            finally:
+                _ok(emu, emu.rfgpu_ctx_set_option(emu.ctx, F.OPT_LOOKUP_JOIN, 1))
+
+
 @pytest.mark.parametrize("sort_semi", [0, 1])
 def test_minus_and_exists(emu, oracle, sort_semi):
     """rfgpu_sparql_minus / rfgpu_sparql_exists: the hash semi / anti join (validated on a B200) and the sorted-list path of

@@ -295,10 +295,15 @@ def test_merge_join_on_sorted_scans(ctx, oracle, jt):
         ctx.set_option(F.OPT_MERGE_JOIN, 0)
         try:
             hj = ta.join(tb, jt)
-            assert hj.last_join_phys == F.PHYS_HASH
+            assert hj.last_join_phys == F.PHYS_LOOKUP  # subject ids are dense: direct-address table, sorted build side
+            ctx.set_option(F.OPT_LOOKUP_JOIN, 0)
+            hh = ta.join(tb, jt)
+            assert hh.last_join_phys == F.PHYS_HASH
         finally:
             ctx.set_option(F.OPT_MERGE_JOIN, 1)
+            ctx.set_option(F.OPT_LOOKUP_JOIN, 1)
         assert_same_table(hj.names, hj.to_numpy(), exp.names, exp.cols)
+        assert_same_table(hh.names, hh.to_numpy(), exp.names, exp.cols)
     # chained: the merge output stays sorted on ?s and feeds another merge join
     def mk2(store, r, name):
         return store.plan([rf.traverse(0), rf.scan("s"), rf.traverse(g.pred_id(r)), rf.scan(name)])
@@ -442,7 +447,9 @@ def test_group_count_and_distinct(ctx, oracle):
 def radix_everywhere(ctx):
     ctx.set_option(F.OPT_RADIX_JOIN, 1)
     ctx.set_option(F.OPT_RADIX_MIN_ROWS, 1)
+    ctx.set_option(F.OPT_LOOKUP_JOIN, 0)  # dense keys would take the direct-address table first
     yield
+    ctx.set_option(F.OPT_LOOKUP_JOIN, 1)
     ctx.set_option(F.OPT_RADIX_MIN_ROWS, 65536)
     ctx.set_option(F.OPT_RADIX_JOIN, 0)
 
@@ -551,7 +558,7 @@ def test_full_size_properties_config1(ctx):
     ctx.set_option(F.OPT_MERGE_JOIN, 0)
     try:
         th = ta.join(tb)
-        assert th.last_join_phys == F.PHYS_HASH and th.num_rows == want_rows
+        assert th.last_join_phys == F.PHYS_LOOKUP and th.num_rows == want_rows
         h = th.to_numpy()
     finally:
         ctx.set_option(F.OPT_MERGE_JOIN, 1)
@@ -567,6 +574,7 @@ def test_hash_join_l2_blocked_passes(ctx, oracle, jt, budget):
     by exactly one pass — unmatched rows of a Left join exactly once — whatever the number of passes."""
     rng = np.random.default_rng(41)
     ctx.set_option(F.OPT_HASH_L2_BYTES, budget)
+    ctx.set_option(F.OPT_LOOKUP_JOIN, 0)
     try:
         for nl, nr, ks, nk in [(1, 1, 1, 1), (300, 200, 40, 1), (2500, 1800, 300, 1), (900, 4000, 5, 1), (3000, 2500, 40, 2),
                                (60000, 50000, 20000, 1), (20000, 30000, 1 << 30, 1)]:
@@ -579,6 +587,7 @@ def test_hash_join_l2_blocked_passes(ctx, oracle, jt, budget):
             assert algo == F.ALGO_EQUI and got.last_join_phys == F.PHYS_HASH
     finally:
         ctx.set_option(F.OPT_HASH_L2_BYTES, 1 << 40)
+        ctx.set_option(F.OPT_LOOKUP_JOIN, 1)
 
 
 def test_async_export_matches_sync_export(ctx):

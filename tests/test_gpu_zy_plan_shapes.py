@@ -4,9 +4,7 @@ Business Intelligence Q1 (7 patterns, 6 inner joins, GROUP BY / COUNT), BSBM Exp
 cross-checked against an independent pandas evaluation.  A second, larger instance of each runs device-resident (tables are
 not re-imported between operators) with the hash and the merge join.
 
-Only operators already validated on a B200 are used (scan, single-key inner / left join, id filters, GROUP BY / COUNT);
-the file itself was written after the round's GPU budget was spent, so it runs late in the suite and as a non-strict xfail
-until its first green run."""
+Green on a B200 since the round-1 driver run (GPUTEST_r01.json)."""
 import numpy as np
 import pytest
 
@@ -15,8 +13,7 @@ from rdf_fusion_b200 import _ffi as F
 from helpers import GpuBackend, OracleBackend, assert_same_table, eval_plan
 from test_plan_shapes_cpu import plan_cases
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.xfail(reason="new test file, not yet run on a device (round-1 GPU budget spent)", strict=False)]
+pytestmark = [pytest.mark.gpu]
 
 
 @pytest.mark.parametrize("case", plan_cases(), ids=lambda c: c[0])

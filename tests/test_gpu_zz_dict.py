@@ -2,15 +2,14 @@
 SURVEY §8f-2) against the oracle restatement of MemObjectIdMapping::decode_array, pinned in test_dict_decode_cpu.py on the
 reference's own roundtrip vector.
 
-Status: written after this round's GPU budget was spent — non-strict xfail until its first green run on a B200."""
+Green on a B200 since the round-1 driver run (GPUTEST_r01.json)."""
 import numpy as np
 import pytest
 
 import rdf_fusion_b200 as rf
 from test_dict_decode_cpu import REF_TERMS, random_terms
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.xfail(reason="dict.cu has not run on a device yet (round-1 GPU budget spent); green on host threads: test_emu_kernels.py", strict=False)]
+pytestmark = [pytest.mark.gpu]
 
 
 def test_reference_roundtrip_vector(ctx, oracle):

@@ -2,7 +2,7 @@
 of the SPARQL 1.1 §18.5 definition, on random tables of every lowering (equi, compatible, disjoint + filter) and on the W3C
 algebra tests (tests/golden/optfilter_golden.json).  The entry point is a composition of operators validated on a B200
 (inner join, ID filter, anti join, device copies; no new kernel) whose algorithm test_join_filter_cpu.py checks against the
-definition on the CPU; it was added after the round's GPU budget was spent: non-strict xfail until its first green run."""
+definition on the CPU.  Green on a B200 since the round-1 driver run (GPUTEST_r01.json)."""
 import json
 import os
 
@@ -14,8 +14,7 @@ from conftest import GOLDEN
 from helpers import GpuBackend, check_w3c_case
 from test_join_filter_cpu import SHAPES, _table, filter_cases
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.xfail(reason="new entry point, not yet run on a device (round-1 GPU budget spent); green on host threads: test_emu_kernels.py", strict=False)]
+pytestmark = [pytest.mark.gpu]
 
 
 @pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])

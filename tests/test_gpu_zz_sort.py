@@ -2,9 +2,7 @@
 top of the radix sort: sort-merge join for unsorted inputs (RFGPU_OPT_SORT_MERGE_JOIN), sorted-list MINUS / EXISTS
 (RFGPU_OPT_SORT_SEMI), sort + run-length GROUP BY / COUNT / DISTINCT (RFGPU_OPT_SORT_AGG).
 
-Status: written after this round's GPU budget was spent, so none of it has run on a device yet.  The file sorts last in
-the suite and every test is a non-strict xfail until a first green run on a B200 (then drop the marker, as was done for
-test_gpu_minus.py): a failure here cannot mask the validated parity tests, and a pass shows up as XPASS."""
+Green on a B200 since the round-1 driver run (GPUTEST_r01.json); first timings in profiles/r2a_sort_microbench.json."""
 import numpy as np
 import pytest
 
@@ -12,8 +10,7 @@ import rdf_fusion_b200 as rf
 from rdf_fusion_b200 import _ffi as F
 from helpers import GpuBackend, assert_same_table, check_w3c_case, random_quads
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.xfail(reason="sort.cu has not run on a device yet (round-1 GPU budget spent); green on host threads: test_emu_kernels.py", strict=False)]
+pytestmark = [pytest.mark.gpu]
 
 
 @pytest.fixture
