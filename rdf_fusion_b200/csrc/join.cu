@@ -227,6 +227,17 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
   A.offs = offs;
   A.kmin = D.kmin;
   A.range = D.range;
+  // compact copy of the table (2 bytes per key): what the probe reads unless a key has more than 255 build rows
+  const uint32_t groups = (D.range + 3) / 4;
+  BufRef tab2 = ctx->alloc((uint64_t)groups * 8 + 16);
+  uint32_t* d_over = reinterpret_cast<uint32_t*>(tab2->as<uint8_t>() + (uint64_t)groups * 8);
+  RF_CUDA(cudaMemsetAsync(d_over, 0, 16, ctx->stream()));
+  A.tab2 = tab2->as<uint2>();
+  A.overflow = d_over;
+  if (groups) {
+    KernelScope ks(ctx, "k_dense_compress", 6ull * D.range);
+    k_dense_compress<<<grid_for(ctx, groups, 256), 256, 0, ctx->stream()>>>(offs, D.range, tab2->as<uint2>(), d_over);
+  }
   A.left = left ? 1 : 0;
   A.n_tiles = n_tiles;
   A.status = scratch->as<unsigned long long>();

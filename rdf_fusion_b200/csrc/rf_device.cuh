@@ -166,6 +166,11 @@ __device__ __forceinline__ uint4 ld_hint_v4(const uint4* p, uint64_t pol) {
                : "l"(p), "l"(pol));
   return v;
 }
+__device__ __forceinline__ uint2 ld_hint_v2(const uint2* p, uint64_t pol) {
+  uint2 v;
+  asm volatile("ld.global.nc.L2::cache_hint.v2.u32 {%0,%1}, [%2], %3;" : "=r"(v.x), "=r"(v.y) : "l"(p), "l"(pol));
+  return v;
+}
 __device__ __forceinline__ uint32_t ld_hint_u32(const uint32_t* p, uint64_t pol) {
   uint32_t v;
   asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
@@ -178,6 +183,7 @@ __device__ __forceinline__ void st_hint_u32(uint32_t* p, uint32_t v, uint64_t po
 inline uint64_t l2_policy_evict_last() { return 0; }
 inline uint64_t l2_policy_evict_first() { return 0; }
 inline uint4 ld_hint_v4(const uint4* p, uint64_t) { return *p; }
+inline uint2 ld_hint_v2(const uint2* p, uint64_t) { return *p; }
 inline uint32_t ld_hint_u32(const uint32_t* p, uint64_t) { return *p; }
 inline void st_hint_u32(uint32_t* p, uint32_t v, uint64_t) { *p = v; }
 #endif

@@ -149,6 +149,11 @@ inline T atomicCAS(T* p, T expected, T desired) {
   return expected;  // the value found, like the device intrinsic
 }
 inline void __nanosleep(unsigned) { std::this_thread::yield(); }
+inline unsigned atomicOr(unsigned* p, unsigned v) { return __atomic_fetch_or(p, v, __ATOMIC_RELAXED); }
+inline unsigned __dp4a(unsigned a, unsigned b, unsigned c) {
+  for (int i = 0; i < 4; i++) c += ((a >> (8 * i)) & 255u) * ((b >> (8 * i)) & 255u);
+  return c;
+}
 struct alignas(8) uint2 { unsigned x, y; };
 inline uint2 make_uint2(unsigned x, unsigned y) { return uint2{x, y}; }
 struct alignas(16) uint4 { unsigned x, y, z, w; };
