@@ -225,6 +225,20 @@ typedef struct {
 int32_t rfgpu_filter(rfgpu_ctx* ctx, const rfgpu_table* in, const rfgpu_filter_pred* preds,
                      int32_t n, rfgpu_table** out);
 
+/* The same filter for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  It calls no cudaMalloc /
+ * cudaFree / allocating routine: the caller passes device pointers for the n_cols input columns (uint32_t[n_rows]), for the
+ * n_cols output columns (capacity n_rows each; rows kept, in input order) and for the row count (one uint64_t in device
+ * memory, written by the kernel; read it after synchronising the ctx stream).  preds[i].col / col2 index `cols`.  The
+ * kernel's look-back scratch is a static device array of 128 KB that every GPU loading the library holds until exit:
+ * n_rows > RFGPU_FILTER_NOALLOC_MAX_ROWS -> RFGPU_E_UNSUPPORTED, as are IN lists of more than 8 ids (they would need a
+ * device copy).  All calls on one device share that array: calls that overlap on the GPU (two ctxs / streams of one device)
+ * race; calls on one ctx are stream-ordered and safe back to back.  Asynchronous: the work is queued on the ctx stream. */
+#define RFGPU_FILTER_NOALLOC_MAX_ROWS (1ull << 26)
+int32_t rfgpu_filter_noalloc(rfgpu_ctx* ctx, int32_t n_cols, const uint32_t* const* cols, uint64_t n_rows,
+                             const rfgpu_filter_pred* preds, int32_t n_preds, uint32_t* const* out_cols,
+                             uint64_t* out_rows_device);
+
 /* ---- SPARQL join: SparqlJoinNode + SparqlJoinLoweringRule ---- */
 typedef enum { RFGPU_JOIN_INNER = 0, RFGPU_JOIN_LEFT = 1 } rfgpu_join_type;
 typedef enum {

@@ -117,6 +117,8 @@ SIGNATURES = {
     "rfgpu_table_import_arrow": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]),
     "rfgpu_table_export_arrow": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]),
     "rfgpu_filter": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(FilterPred), C.c_int32, C.POINTER(C.c_void_p)]),
+    "rfgpu_filter_noalloc": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.c_uint64, C.POINTER(FilterPred),
+                                         C.c_int32, C.POINTER(C.c_void_p), C.c_void_p]),
     "rfgpu_sparql_join": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]),
     "rfgpu_group_count": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_char_p,
                                       C.POINTER(C.c_void_p)]),

@@ -270,7 +270,97 @@ void exclusive_scan_u32(rfgpu_ctx* ctx, const uint32_t* in, uint32_t* out, uint6
   // `status` is freed stream-ordered after the kernel (cudaFreeAsync in ~DevBuf)
 }
 
+// ---------------- the filter without any allocation (rfgpu_filter_noalloc) ----------------
+// Look-back words of k_filter_compact for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops): a
+// file-scope device array instead of a pool allocation.  Every GPU that loads the library holds these 128 KB until exit.
+// In host code `g_noalloc_status` is only a stand-in for the symbol, not a device address: the address a kernel can use
+// comes from cudaGetSymbolAddress, taken once per device at context creation with that device current.
+constexpr uint64_t kNoAllocMaxRows = 1ull << 26;                    // 67 108 864 rows = 16 384 tiles of 4096
+constexpr uint32_t kNoAllocMaxTiles = (uint32_t)(kNoAllocMaxRows / kFTile);
+static __device__ __align__(256) unsigned long long g_noalloc_status[kNoAllocMaxTiles + 8];  // [tiles] look-back words
+
+constexpr int kMaxDevices = 64;
+static unsigned long long* g_noalloc_ptr[kMaxDevices] = {};  // device address of g_noalloc_status on device d
+static cudaError_t g_noalloc_err[kMaxDevices] = {};
+
+// called by rfgpu_ctx_create with `device` current; never throws: a failure is reported by the entry point that needs it
+void filter_noalloc_setup(int device) {
+  if (device < 0 || device >= kMaxDevices || g_noalloc_ptr[device]) return;
+  unsigned long long* p = nullptr;
+  const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_status);
+  g_noalloc_err[device] = e;
+  if (e == cudaSuccess) g_noalloc_ptr[device] = p;
+  else cudaGetLastError();
+}
+
 }  // namespace rf
+
+extern "C" int32_t rfgpu_filter_noalloc(rfgpu_ctx* ctx, int32_t n_cols, const uint32_t* const* cols, uint64_t n_rows,
+                                        const rfgpu_filter_pred* preds, int32_t n_preds, uint32_t* const* out_cols,
+                                        uint64_t* out_rows_device) {
+  RF_API_BEGIN
+  using namespace rf;
+  RF_REQUIRE(ctx && cols && out_cols && out_rows_device && n_cols >= 1 && n_preds >= 0 && (preds || n_preds == 0),
+             RFGPU_E_INVALID, "NULL / negative argument");
+  RF_REQUIRE(n_cols <= kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 columns in one filter");
+  RF_REQUIRE(n_preds <= kMaxPreds, RFGPU_E_UNSUPPORTED, "more than 8 conjuncts in one filter");
+  RF_REQUIRE(n_rows <= kNoAllocMaxRows, RFGPU_E_UNSUPPORTED,
+             "rfgpu_filter_noalloc: " + std::to_string(n_rows) + " rows exceed the static scratch (at most " +
+                 std::to_string(kNoAllocMaxRows) + " rows per call); use rfgpu_filter");
+  const int dev = ctx->core->device;
+  RF_REQUIRE(dev >= 0 && dev < kMaxDevices, RFGPU_E_UNSUPPORTED, "device index beyond 63");
+  RF_REQUIRE(g_noalloc_ptr[dev] != nullptr, RFGPU_E_CUDA,
+             std::string("rfgpu_filter_noalloc: cudaGetSymbolAddress of the static scratch failed at context creation: ") +
+                 cudaGetErrorString(g_noalloc_err[dev]));
+  RF_CUDA(cudaSetDevice(dev));
+  FilterArgs A{};
+  A.n_preds = n_preds;
+  for (int i = 0; i < n_preds; i++) {
+    const rfgpu_filter_pred& p = preds[i];
+    RF_REQUIRE(p.op >= 0 && p.op <= RFGPU_F_IS_NOT_NULL, RFGPU_E_INVALID, "bad filter op");
+    RF_REQUIRE(p.col >= 0 && p.col < n_cols, RFGPU_E_INVALID, "filter column out of range");
+    DevPred& d = A.preds[i];
+    d.op = p.op;
+    d.a = cols[p.col];
+    d.value = p.value;
+    d.hi = p.hi;
+    if (p.op == RFGPU_F_EQ_COL || p.op == RFGPU_F_NE_COL) {
+      RF_REQUIRE(p.col2 >= 0 && p.col2 < n_cols, RFGPU_E_INVALID, "second filter column out of range");
+      d.b = cols[p.col2];
+    }
+    if (p.op == RFGPU_F_IN) {  // a longer list would need a device copy of the ids, i.e. an allocation
+      RF_REQUIRE(p.n_ids <= 8 && (p.ids || p.n_ids == 0), RFGPU_E_UNSUPPORTED,
+                 "rfgpu_filter_noalloc: IN lists are limited to 8 ids; use rfgpu_filter");
+      uint32_t n = 0;
+      for (uint32_t k = 0; k < p.n_ids; k++) {  // de-duplicated, on the stack
+        bool dup = false;
+        for (uint32_t j = 0; j < n; j++) dup |= d.inl[j] == p.ids[k];
+        if (!dup) d.inl[n++] = p.ids[k];
+      }
+      d.n_ids = n;
+    }
+  }
+  A.n_cols = n_cols;
+  A.n = n_rows;
+  for (int c = 0; c < n_cols; c++) {
+    RF_REQUIRE(n_rows == 0 || (cols[c] && out_cols[c]), RFGPU_E_INVALID, "NULL column pointer");
+    A.src[c] = cols[c];
+    A.dst[c] = out_cols[c];
+  }
+  unsigned long long* total = reinterpret_cast<unsigned long long*>(out_rows_device);
+  if (n_rows == 0) {
+    RF_CUDA(cudaMemsetAsync(total, 0, 8, ctx->stream()));
+  } else {
+    const uint32_t tiles = div_up(n_rows, kFTile);
+    // the array keeps the previous call's words: the look-back flags of this call's tiles must start at zero
+    RF_CUDA(cudaMemsetAsync(g_noalloc_ptr[dev], 0, (uint64_t)tiles * 8, ctx->stream()));
+    k_filter_compact<<<tiles, kFThreads, 0, ctx->stream()>>>(A, g_noalloc_ptr[dev], total);
+    RF_CUDA(cudaGetLastError());
+    ctx->m.kernel_launches++;
+  }
+  ctx->m.filter_rows_in += n_rows;
+  RF_API_END(ctx)
+}
 
 extern "C" int32_t rfgpu_filter(rfgpu_ctx* ctx, const rfgpu_table* in, const rfgpu_filter_pred* preds, int32_t n,
                                 rfgpu_table** out) {

@@ -168,6 +168,9 @@ uint64_t encode_runs(rfgpu_ctx* ctx, const std::vector<const uint32_t*>& cols, i
 // flag[i] = 1 where probe[i] occurs in the ascending list sorted[0..ns) (flag is left alone elsewhere)
 void sorted_contains(rfgpu_ctx* ctx, const uint32_t* sorted, uint64_t ns, const uint32_t* probe, uint64_t np, uint32_t* flag);
 
+// filter.cu — resolves the device address of the static scratch of rfgpu_filter_noalloc for `device` (which must be current)
+void filter_noalloc_setup(int device);
+
 // filter.cu — generic predicate program over column pointers
 struct DevPred {
   int32_t op;            // rfgpu_filter_op

@@ -27,6 +27,12 @@ typedef void* cudaEvent_t;
 enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice };
 inline const char* cudaGetErrorName(cudaError_t) { return "emu"; }
 inline const char* cudaGetErrorString(cudaError_t) { return "emu"; }
+inline cudaError_t cudaGetLastError() { return cudaSuccess; }
+template <class T>
+inline cudaError_t cudaGetSymbolAddress(void** p, T& symbol) {  // host build: the symbol IS the memory
+  *p = (void*)&symbol;
+  return cudaSuccess;
+}
 inline cudaError_t cudaSetDevice(int) { return cudaSuccess; }
 inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
 inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, cudaMemcpyKind, cudaStream_t) {
