@@ -103,7 +103,16 @@ void rfgpu_store_release(rfgpu_store* s);
  * + MemIndexData::insert (quad_index_data.rs:287-332) for bulk load. */
 int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm,
                               const uint32_t* const cols[4], uint64_t n_rows, int32_t on_device);
+/* Sharded store (multi-GPU; north_star / SURVEY 8e): every permutation of this store is ONE RANK'S SHARD of the global
+ * permutation, and the permutations are sharded independently — a contiguous row slice of the globally sorted permutation
+ * ("the index is range-partitioned by leading key"), or the quads whose subject (GSPO, GPSO, GSOP) / object (GPOS, GOSP,
+ * GOPS) hashes to the rank, so that a scan comes out already partitioned on the variable it is joined on.  The permutations
+ * therefore hold different quads and different row counts.  A scan is the same binary search over the local shard; the union
+ * of the ranks' results is the global scan.  Must be set before the second rfgpu_store_add_index / rfgpu_store_build. */
+int32_t rfgpu_store_set_sharded(rfgpu_store* s, int32_t on);
 uint64_t rfgpu_store_len(const rfgpu_store* s);
+/* rows of permutation i (they differ in a range-sharded store) */
+uint64_t rfgpu_store_index_rows(const rfgpu_store* s, int32_t i);
 int32_t rfgpu_store_num_indexes(const rfgpu_store* s);
 uint32_t rfgpu_store_index_perm(const rfgpu_store* s, int32_t i);
 
@@ -365,6 +374,38 @@ int32_t rfgpu_table_sort(rfgpu_ctx* ctx, const rfgpu_table* t, const int32_t* ke
  * quad_index.rs:132-156, quad_index_data.rs:287-376, lib/storage/src/index/permutations.rs:102-128). */
 int32_t rfgpu_store_build(rfgpu_ctx* ctx, rfgpu_store* s, const uint32_t* const quads[4], uint64_t n_rows,
                           int32_t on_device, const uint32_t* perms, int32_t n_perms);
+
+/* ---- synthetic graphs in id space (benchmark / test set-up) ---- */
+/* G(N, P, s, seed): the deterministic graph every benchmark and large parity test runs on, generated on the device so that
+ * each rank of a multi-GPU run produces exactly the rows it owns without communication.  The reference generates its own
+ * benchmark data on the host (bench/src/benchmarks/windfarm/generate/generate_time_series.rs:23; BSBM through the Java
+ * bsbm-tools); this is the counterpart for the synthetic configs of BASELINE.json.  Bit-identical with the numpy generator
+ * rdf_fusion_b200/synth.py::generate_graph (the specification, and what the oracle consumes): row i draws
+ * splitmix64(i ^ splitmix64(seed * 256 + stream)); subjects uniform over S = N / 10, predicates Zipf by rank through
+ * `pred_cdf`, objects half entities (uniform, or Zipf through `obj_cdf`) half literals (uniform over L = N / 4).
+ * Duplicates are NOT removed (rfgpu_store_build does that). */
+typedef enum {
+  RFGPU_SYNTH_KEEP_ALL = 0,
+  RFGPU_SYNTH_KEEP_HASH_SUBJECT = 1, /* rows with rfgpu_shuffle_dest(subject, n_ranks) == rank */
+  RFGPU_SYNTH_KEEP_RANGE = 2,        /* rows whose quad, in the level order of `perm`, is in [lo, hi): one rank's contiguous
+                                        slice of the globally sorted permutation (range partitioning by leading key) */
+  RFGPU_SYNTH_KEEP_HASH_OBJECT = 3   /* rows with rfgpu_shuffle_dest(object, n_ranks) == rank */
+} rfgpu_synth_keep_mode;
+typedef struct {
+  uint64_t n_rows;          /* N: rows of the GLOBAL graph */
+  uint32_t n_predicates;    /* P */
+  uint64_t seed;
+  const double* pred_cdf;   /* host, [P]: cumulative Zipf weights, last = 1 */
+  const double* obj_cdf;    /* host, [max(N / 10, 1)], or NULL for uniform entity objects */
+  double named_graph_frac;  /* > 0: that fraction of the quads is placed in the named graphs 1..16 */
+  int32_t keep;             /* rfgpu_synth_keep_mode */
+  uint32_t rank, n_ranks;   /* HASH_SUBJECT / HASH_OBJECT */
+  uint32_t perm;            /* RANGE: RFGPU_PERM(..) */
+  uint32_t lo[4], hi[4];    /* RANGE: bounds in level order */
+  int32_t has_lo, has_hi;   /* RANGE: 0 = unbounded on that side (first / last rank) */
+} rfgpu_synth_desc;
+/* -> a table (graph, subject, predicate, object) of the kept rows, device-resident, in no particular order */
+int32_t rfgpu_synth_quads(rfgpu_ctx* ctx, const rfgpu_synth_desc* desc, rfgpu_table** out);
 
 /* ---- options ---- */
 typedef enum {

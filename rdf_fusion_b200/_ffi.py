@@ -67,6 +67,16 @@ class FilterPred(C.Structure):
                 ("ids", u32p), ("n_ids", C.c_uint32)]
 
 
+class SynthDesc(C.Structure):
+    _fields_ = [("n_rows", C.c_uint64), ("n_predicates", C.c_uint32), ("seed", C.c_uint64), ("pred_cdf", C.POINTER(C.c_double)),
+                ("obj_cdf", C.POINTER(C.c_double)), ("named_graph_frac", C.c_double), ("keep", C.c_int32), ("rank", C.c_uint32),
+                ("n_ranks", C.c_uint32), ("perm", C.c_uint32), ("lo", C.c_uint32 * 4), ("hi", C.c_uint32 * 4),
+                ("has_lo", C.c_int32), ("has_hi", C.c_int32)]
+
+
+SYNTH_KEEP_ALL, SYNTH_KEEP_HASH_SUBJECT, SYNTH_KEEP_RANGE, SYNTH_KEEP_HASH_OBJECT = 0, 1, 2, 3
+
+
 class Metrics(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "kernel_launches", "h2d_bytes", "d2h_bytes", "scan_rows_in", "scan_rows_out", "filter_rows_in",
@@ -87,6 +97,9 @@ SIGNATURES = {
     "rfgpu_store_add_index": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p), C.c_uint64, C.c_int32]),
     "rfgpu_store_len": (C.c_uint64, [C.c_void_p]),
     "rfgpu_store_num_indexes": (C.c_int32, [C.c_void_p]),
+    "rfgpu_store_set_sharded": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "rfgpu_store_index_rows": (C.c_uint64, [C.c_void_p, C.c_int32]),
+    "rfgpu_synth_quads": (C.c_int32, [C.c_void_p, C.POINTER(SynthDesc), C.POINTER(C.c_void_p)]),
     "rfgpu_store_index_perm": (C.c_uint32, [C.c_void_p, C.c_int32]),
     "rfgpu_scan_plan_create": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(ScanInstruction), C.POINTER(C.c_void_p)]),
     "rfgpu_scan_plan_destroy": (None, [C.c_void_p]),

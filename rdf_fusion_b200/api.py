@@ -154,6 +154,38 @@ class Context:
     def store(self) -> "Store":
         return Store(self)
 
+    def synth_quads(self, n: int, n_predicates: int = 1024, s: float = 1.0, seed: int = 2, s_o: float = 0.0,
+                    named_graph_frac: float = 0.0, keep=None) -> "Table":
+        """The rows of synth.generate_graph(n, ...) this rank keeps, generated on the device (rfgpu_synth_quads).
+        keep: None = all | ("hash_subject" / "hash_object", rank, n_ranks) | ("range", perm, lo, hi) with lo / hi = 4 ids in the level order of
+        `perm`, or None for an open end."""
+        from .synth import _zipf_cdf
+        d = F.SynthDesc()
+        d.n_rows, d.n_predicates, d.seed, d.named_graph_frac = n, n_predicates, seed, named_graph_frac
+        pcdf = np.ascontiguousarray(_zipf_cdf(n_predicates, s), np.float64)
+        d.pred_cdf = pcdf.ctypes.data_as(C.POINTER(C.c_double))
+        ocdf = None
+        if s_o > 0:
+            ocdf = np.ascontiguousarray(_zipf_cdf(max(n // 10, 1), s_o), np.float64)
+            d.obj_cdf = ocdf.ctypes.data_as(C.POINTER(C.c_double))
+        if keep is None:
+            d.keep = F.SYNTH_KEEP_ALL
+        elif keep[0] in ("hash_subject", "hash_object"):
+            d.keep = F.SYNTH_KEEP_HASH_SUBJECT if keep[0] == "hash_subject" else F.SYNTH_KEEP_HASH_OBJECT
+            d.rank, d.n_ranks = keep[1], keep[2]
+        elif keep[0] == "range":
+            d.keep, d.perm = F.SYNTH_KEEP_RANGE, keep[1]
+            for name, bound in (("lo", keep[2]), ("hi", keep[3])):
+                setattr(d, "has_" + name, 0 if bound is None else 1)
+                if bound is not None:
+                    for l in range(4):
+                        getattr(d, name)[l] = int(bound[l])
+        else:
+            raise ValueError(keep)
+        out = C.c_void_p()
+        self.check(self.lib.rfgpu_synth_quads(self.h, C.byref(d), C.byref(out)))
+        return Table(self, out)
+
     # ---- tables ----
     def import_table(self, cols: Dict[str, np.ndarray], nullable: Optional[Dict[str, bool]] = None,
                      validity: Optional[Dict[str, np.ndarray]] = None) -> "Table":
@@ -296,6 +328,19 @@ class Store:
         pa_ = (C.c_uint32 * len(perms))(*perms)
         self.ctx.check(self.ctx.lib.rfgpu_store_build(self.ctx.h, self.h, arr, n, 1 if on_device else 0, pa_, len(perms)))
         return self
+
+    def build_from_table(self, quads: "Table", perms=(F.GSPO, F.GPOS, F.GOSP)):
+        """rfgpu_store_build over a device-resident (graph, subject, predicate, object) table, e.g. Context.synth_quads."""
+        ptrs = [int(self.ctx.lib.rfgpu_table_col_device_ptr(quads.h, c) or 0) for c in range(4)]
+        return self.build((ptrs, quads.num_rows), perms, on_device=True)
+
+    def set_sharded(self, on: bool = True):
+        """every permutation of this store is one rank's row slice of the global permutation (rfgpu_store_set_sharded)"""
+        self.ctx.check(self.ctx.lib.rfgpu_store_set_sharded(self.h, 1 if on else 0))
+        return self
+
+    def index_rows(self, perm: int) -> int:
+        return int(self.ctx.lib.rfgpu_store_index_rows(self.h, self.perms.index(perm)))
 
     @property
     def perms(self) -> List[int]:

@@ -236,7 +236,7 @@ int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm, con
   RF_REQUIRE(seen == 15, RFGPU_E_INVALID, "permutation must name each of G,S,P,O once");
   RF_REQUIRE(n_rows < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "an index holds at most 2^32-2 rows per GPU");
   for (auto& ix : s->indexes) RF_REQUIRE(ix.perm != perm, RFGPU_E_INVALID, "permutation already present");
-  if (!s->indexes.empty())
+  if (!s->indexes.empty() && !s->sharded)
     RF_REQUIRE(s->indexes[0].rows == n_rows, RFGPU_E_INVALID, "all permutations must hold the same quads");
   rfgpu_index_t ix;
   ix.perm = perm;
@@ -278,6 +278,14 @@ int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm, con
   RF_API_END(ctx)
 }
 
+int32_t rfgpu_store_set_sharded(rfgpu_store* s, int32_t on) {
+  if (!s) return RFGPU_E_INVALID;
+  s->sharded = on != 0;
+  return RFGPU_OK;
+}
+uint64_t rfgpu_store_index_rows(const rfgpu_store* s, int32_t i) {
+  return s && i >= 0 && i < (int32_t)s->indexes.size() ? s->indexes[i].rows : 0;
+}
 uint64_t rfgpu_store_len(const rfgpu_store* s) { return s && !s->indexes.empty() ? s->indexes[0].rows : 0; }
 int32_t rfgpu_store_num_indexes(const rfgpu_store* s) { return s ? (int32_t)s->indexes.size() : 0; }
 uint32_t rfgpu_store_index_perm(const rfgpu_store* s, int32_t i) {

@@ -89,6 +89,7 @@ struct rfgpu_index_t {
 
 struct rfgpu_store {
   std::atomic<int> refs{1};
+  bool sharded = false;  // permutations are row slices of the global permutations: different quads per index
   std::vector<rfgpu_index_t> indexes;
 };
 

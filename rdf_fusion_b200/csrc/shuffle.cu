@@ -490,6 +490,9 @@ static bool shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col, rfgp
     if (r == me) mine = tot;
   }
   uint8_t* local = cm.arena[me] + off;
+  // cursor back to 0 for shuffle k+2 — queued before anything below can throw: an error on this rank must not leave the
+  // arena half unusable for the peers (the copy-out below only reads rows, the cursor word is not part of them)
+  RF_CUDA(cudaMemsetAsync(local, 0, 8, ctx->stream()));
   if (fits) {
     RF_REQUIRE(mine < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "shuffle result exceeds 2^32-2 rows on one GPU");
     t->rows = mine;
@@ -507,7 +510,6 @@ static bool shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col, rfgp
       if (r != me) link_rows += all[(size_t)me * g + r];
     ctx->m.algorithmic_bytes += link_rows * 4 * C;
   }
-  RF_CUDA(cudaMemsetAsync(local, 0, 8, ctx->stream()));  // cursor back to 0 for shuffle k+2
   return fits;
 }
 

@@ -102,3 +102,132 @@ def skew_aware_join(lhs, rhs_local, key: str, join_type: int, ops, n_ranks: int,
     cols = [np.concatenate([np.asarray(p[2][c], dtype=np.uint32) for p in parts]) for c in range(len(names))]
     rhs_heavy_all = ops.from_host(names, nullable, cols)
     return [ops.join(ops.shuffle(lhs_light, key), rhs_light, join_type), ops.join(lhs_heavy, rhs_heavy_all, join_type)], heavy
+
+
+# ---------------------------------------------------------------- sharded stores: which rank holds which quad of a permutation
+# Layouts of a multi-GPU store (one shard per rank and PERMUTATION; rfgpu_store_set_sharded):
+#   "hash"    a quad of a permutation lives on rank shuffle_dest(component) where the component is the one the permutation
+#             is joined on: the subject for GSPO / GPSO / GSOP, the object for GPOS / GOSP / GOPS.  `?a p ?b` scanned
+#             through GPOS comes out partitioned (and sorted) on ?b, through GPSO on ?a: a join of a scan's object with the
+#             next scan's subject — every step of a chain — needs no exchange for its scan sides.
+#   "range"   north_star / SURVEY §8e: each permutation is cut into g contiguous row slices of the globally sorted
+#             permutation ("range-partitioned by leading key"); a scan's rows are wherever their slice is, so both sides of
+#             a join are shuffled on the join variable.
+#   "subject" (round 1) every permutation holds the quads whose subject hashes to the rank.
+_S_PLACED = None
+
+
+def placement_component(perm: int) -> int:
+    """component (F.G/S/P/O index: 0..3) whose hash places a quad of permutation `perm` under the "hash" layout"""
+    from . import _ffi as F
+    comps = [(perm >> (2 * i)) & 3 for i in range(4)]
+    non_g = [c for c in comps if c != 0]
+    first = non_g[0]
+    if first == 2:  # predicate-leading: the component after the predicate decides (GPOS -> object, GPSO -> subject)
+        first = non_g[1]
+    return first
+
+
+def range_cuts(sample_cols, perm: int, n_ranks: int, round_tolerance: float = 0.05):
+    """g-1 cut tuples (level order of `perm`) that split the lexicographically sorted sample into g nearly equal slices.
+    A cut is moved down to the start of its (graph, first non-graph key) run when that shifts it by less than
+    round_tolerance of a slice — "cut points moved to the next change of the first non-graph key" — and stays inside the run
+    when the run is heavy (a Zipf-rank-1 predicate spans several slices; a range scan only needs bounds per slice)."""
+    comps = [(perm >> (2 * i)) & 3 for i in range(4)]
+    lv = [np.asarray(sample_cols[c], dtype=np.uint32) for c in comps]
+    order = np.lexsort(tuple(reversed(lv)))
+    lv = [c[order] for c in lv]
+    m = len(order)
+    cuts = []
+    for r in range(1, n_ranks):
+        q = (m * r) // n_ranks
+        t = tuple(int(c[q]) for c in lv)
+        # start of the (level0, level1) run that contains q
+        key = (lv[0].astype(np.uint64) << np.uint64(32)) | lv[1].astype(np.uint64)
+        start = int(np.searchsorted(key, key[q], side="left"))
+        if (q - start) <= round_tolerance * m / n_ranks:
+            t = (t[0], t[1], 0, 0)
+        if cuts and t <= cuts[-1]:
+            t = cuts[-1]  # empty slice (more ranks than distinct tuples)
+        cuts.append(t)
+    return cuts
+
+
+def range_owner_np(cols, perm: int, cuts) -> np.ndarray:
+    """rank of every quad under the range layout of `perm`: slice r holds cuts[r-1] <= tuple < cuts[r] (host mirror of
+    RFGPU_SYNTH_KEEP_RANGE, used by the tests to shard numpy graphs)."""
+    comps = [(perm >> (2 * i)) & 3 for i in range(4)]
+    lv = [np.asarray(cols[c], dtype=np.uint64) for c in comps]
+    owner = np.zeros(len(lv[0]), dtype=np.int64)
+    for cut in cuts:
+        ge = np.zeros(len(owner), dtype=bool)
+        eq = np.ones(len(owner), dtype=bool)
+        for l in range(4):
+            ge |= eq & (lv[l] > cut[l])
+            eq &= lv[l] == cut[l]
+        owner += (ge | eq)
+    return owner
+
+
+def shard_quads_np(cols, perm: int, rank: int, n_ranks: int, layout: str, cuts=None):
+    """(g, s, p, o) numpy columns of the quads of permutation `perm` that `rank` holds under `layout`."""
+    if n_ranks == 1:
+        return tuple(cols)
+    if layout == "range":
+        keep = range_owner_np(cols, perm, cuts) == rank
+    elif layout == "hash":
+        keep = shuffle_dest_np(cols[placement_component(perm)], n_ranks) == rank
+    elif layout == "subject":
+        keep = shuffle_dest_np(cols[1], n_ranks) == rank
+    else:
+        raise ValueError(layout)
+    return tuple(np.asarray(c)[keep] for c in cols)
+
+
+def scan_partition_var(layout: str, perm: int, pattern):
+    """The variable a scan's output is hash-partitioned on (None: not partitioned on any variable) — pattern = (g, s, p, o)
+    with str = variable, int = constant."""
+    if layout == "range":
+        return None
+    comp = 1 if layout == "subject" else placement_component(perm)
+    v = pattern[comp]
+    return v if isinstance(v, str) else None
+
+
+def fold_bgp(ops, patterns, join_type: int = 0):
+    """Left-deep fold of a basic graph pattern over sharded stores (the reference folds its triple patterns the same way:
+    lib/logical/src/logical_plan_builder_context.rs:233-251), with an exchange only where a side is not yet hash-partitioned
+    on the join variable — the job DataFusion's RepartitionExec(Hash) does above the scans (pattern_data_source.rs:47-49).
+
+    patterns: [(s, p, o)] with str = variable, int = constant id.  `ops` adapts the engine:
+      scan(pattern, order_by) -> (table, partition variable or None)   rows in index order; order_by = the variable the scan
+                                                                        should come out sorted (and, layout permitting, partitioned) on
+      shuffle(table, var) -> table      rfgpu_shuffle: rows to rank shuffle_dest(var)
+      join(lhs, rhs, join_type) -> table
+      names(table) -> [str]; nullable(table) -> [bool]
+    -> (table, partition variable, number of exchanges)"""
+    def vars_of(p):
+        return [v for v in p if isinstance(v, str)]
+    cur, cur_pk, n_ex = None, None, 0
+    for i, pat in enumerate(patterns):
+        if cur is None:
+            nxt = vars_of(patterns[1]) if len(patterns) > 1 else []
+            shared = sorted(set(vars_of(pat)) & set(nxt))
+            cur, cur_pk = ops.scan(pat, shared[0] if shared else None)
+            continue
+        shared = sorted(set(ops.names(cur)) & set(vars_of(pat)))
+        if not shared:
+            raise NotImplementedError("cross joins are not distributed (tiny in the reference's plans: SURVEY appendix B)")
+        key = cur_pk if cur_pk in shared else shared[0]
+        t, pk = ops.scan(pat, key)
+        # an unbound (NULL) key is compatible with every row on every rank: hashing it to one rank would lose rows
+        if ops.nullable(cur)[ops.names(cur).index(key)] or ops.nullable(t)[ops.names(t).index(key)]:
+            raise NotImplementedError(f"distributed join on the nullable variable ?{key}: the NULL class must be broadcast")
+        if cur_pk != key:
+            cur = ops.shuffle(cur, key)
+            n_ex += 1
+        if pk != key:
+            t = ops.shuffle(t, key)
+            n_ex += 1
+        cur, cur_pk = ops.join(cur, t, join_type), key
+    return cur, cur_pk, n_ex

@@ -68,37 +68,56 @@ class SynthGraph:
         return np.stack([self.g, self.s, self.p, self.o], axis=1)
 
 
+def generate_rows(n: int, rows: np.ndarray, n_predicates: int = 1024, s: float = 1.0, seed: int = 2, s_o: float = 0.0,
+                  named_graph_frac: float = 0.0, _cdfs=None):
+    """(g, s, p, o) of the rows `rows` (uint64 row numbers < n) of G(n, P, s, seed): any subset, in any order — what makes
+    the graph independent of chunking, and what lets a rank (or a sampler) draw only the rows it needs."""
+    S = max(n // 10, 1)
+    L = max(n // 4, 1)
+    P = n_predicates
+    pcdf, ocdf = _cdfs if _cdfs is not None else (_zipf_cdf(P, s), _zipf_cdf(S, s_o) if s_o > 0 else None)
+    rows = np.asarray(rows, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        sub = (17 + P + (_draw(seed, 1, rows) % np.uint64(S))).astype(np.uint32)
+        pr = np.searchsorted(pcdf, _unit(_draw(seed, 2, rows)), side="right")
+        pred = (17 + np.minimum(pr, P - 1)).astype(np.uint32)
+        kind = _draw(seed, 3, rows) & np.uint64(1)
+        u = _draw(seed, 4, rows)
+        if ocdf is None:
+            ent = (u % np.uint64(S)).astype(np.int64)
+        else:
+            ent = np.minimum(np.searchsorted(ocdf, _unit(u), side="right"), S - 1)
+        lit = (u % np.uint64(L)).astype(np.int64)
+        obj = np.where(kind == 0, 17 + P + ent, 17 + P + S + lit).astype(np.uint32)
+        g = np.zeros(len(rows), dtype=np.uint32)
+        if named_graph_frac > 0:
+            gu = _draw(seed, 5, rows)
+            named = _unit(gu) < named_graph_frac
+            g = np.where(named, 1 + (gu % np.uint64(16)).astype(np.int64), 0).astype(np.uint32)
+    return g, sub, pred, obj
+
+
 def generate_graph(n: int, n_predicates: int = 1024, s: float = 1.0, seed: int = 2, s_o: float = 0.0,
                    named_graph_frac: float = 0.0, chunk: int = 1 << 24) -> SynthGraph:
     S = max(n // 10, 1)
     L = max(n // 4, 1)
     P = n_predicates
-    pcdf = _zipf_cdf(P, s)
-    ocdf = _zipf_cdf(S, s_o) if s_o > 0 else None
+    cdfs = (_zipf_cdf(P, s), _zipf_cdf(S, s_o) if s_o > 0 else None)
     g = np.zeros(n, dtype=np.uint32)
     sub = np.empty(n, dtype=np.uint32)
     pred = np.empty(n, dtype=np.uint32)
     obj = np.empty(n, dtype=np.uint32)
-    with np.errstate(over="ignore"):
-        for lo in range(0, n, chunk):
-            hi = min(n, lo + chunk)
-            rows = np.arange(lo, hi, dtype=np.uint64)
-            sub[lo:hi] = (17 + P + (_draw(seed, 1, rows) % np.uint64(S))).astype(np.uint32)
-            pr = np.searchsorted(pcdf, _unit(_draw(seed, 2, rows)), side="right")
-            pred[lo:hi] = (17 + np.minimum(pr, P - 1)).astype(np.uint32)
-            kind = _draw(seed, 3, rows) & np.uint64(1)
-            u = _draw(seed, 4, rows)
-            if ocdf is None:
-                ent = (u % np.uint64(S)).astype(np.int64)
-            else:
-                ent = np.minimum(np.searchsorted(ocdf, _unit(u), side="right"), S - 1)
-            lit = (u % np.uint64(L)).astype(np.int64)
-            obj[lo:hi] = np.where(kind == 0, 17 + P + ent, 17 + P + S + lit).astype(np.uint32)
-            if named_graph_frac > 0:
-                gu = _draw(seed, 5, rows)
-                named = _unit(gu) < named_graph_frac
-                g[lo:hi] = np.where(named, 1 + (gu % np.uint64(16)).astype(np.int64), 0).astype(np.uint32)
+    for lo in range(0, n, chunk):
+        hi = min(n, lo + chunk)
+        g[lo:hi], sub[lo:hi], pred[lo:hi], obj[lo:hi] = generate_rows(
+            n, np.arange(lo, hi, dtype=np.uint64), P, s, seed, s_o, named_graph_frac, cdfs)
     return SynthGraph(n, P, S, L, g, sub, pred, obj)
+
+
+def graph_shape(n: int, n_predicates: int = 1024) -> SynthGraph:
+    """The id-space layout of G(n, P, ..) without any rows (pred_id, subject_base, literal_base)."""
+    z = np.zeros(0, np.uint32)
+    return SynthGraph(n, n_predicates, max(n // 10, 1), max(n // 4, 1), z, z, z, z)
 
 
 # ---------------------------------------------------------------- BSBM-shaped graph in id space

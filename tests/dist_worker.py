@@ -21,8 +21,8 @@ import torch.distributed as dist  # noqa: E402
 import rdf_fusion_b200 as rf  # noqa: E402
 from oracle import oracle_py as orc  # noqa: E402
 from rdf_fusion_b200 import _ffi as F  # noqa: E402
-from rdf_fusion_b200.dist import (exchange_layout, init_comm, owner_of_subject, partition_np,  # noqa: E402
-                                  skew_aware_join)
+from rdf_fusion_b200.dist import (exchange_layout, fold_bgp, init_comm, owner_of_subject, partition_np,  # noqa: E402
+                                  range_cuts, scan_partition_var, shard_quads_np, skew_aware_join)
 
 
 def main():
@@ -31,6 +31,8 @@ def main():
     # gpu only: "p2p" (default: fused partition + peer-memory scatter), "nccl" (option off), "tiny" (1 MiB arena: rows do
     # not fit, every rank must fall back to the NCCL exchange together)
     exchange = sys.argv[3] if len(sys.argv) > 3 else "p2p"
+    # how the quads of each permutation are spread over the ranks (rdf_fusion_b200/dist.py): "subject" | "hash" | "range"
+    layout = sys.argv[4] if len(sys.argv) > 4 else "subject"
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if mode == "gpu":
@@ -42,8 +44,14 @@ def main():
 
     g = rf.generate_graph(n_triples, n_predicates=8, s=1.1, seed=4, s_o=1.05)
     quads = g.quads()
-    mine = quads[owner_of_subject(quads[:, 1], world) == rank]
+    gcols = (g.g, g.s, g.p, g.o)
     p1, p2, p3 = g.pred_id(1), g.pred_id(2), g.pred_id(3)
+    perms = (F.GSPO, F.GPOS, F.GOSP, F.GPSO)
+    cuts = {pm: range_cuts(gcols, pm, world) for pm in perms} if layout == "range" else {}
+
+    def shard(pm):
+        return np.stack(shard_quads_np(gcols, pm, rank, world, layout, cuts.get(pm)), axis=1)
+    mine = shard(F.GSPO)  # the "subject" layout's quads (every permutation holds them)
 
     if mode == "gpu":
         ctx = rf.Context(local)
@@ -52,11 +60,19 @@ def main():
         if exchange == "nccl":
             ctx.set_option(F.OPT_SHUFFLE_P2P, 0)
         init_comm(ctx)
-        store = ctx.store().load_quads(mine)
+        if layout == "subject":
+            store = ctx.store().load_quads(mine)
+        else:  # one shard per permutation, sorted and de-duplicated on the device
+            store = ctx.store().set_sharded()
+            for pm in perms:
+                store.build(shard(pm), (pm,))
         paths = set()
 
-        def scan(s, p, o):
-            return store.plan([rf.traverse(0), rf.scan(s), rf.traverse(p), rf.scan(o)]).execute(allow_view=True)
+        def scan(s, p, o, order_by=None):
+            plan = store.plan([rf.traverse(0), rf.scan(s), rf.traverse(p), rf.scan(o)])
+            if order_by:
+                plan.order_by(order_by)
+            return plan.execute(allow_view=True), scan_partition_var(layout, plan.index, (0, s, p, o))
 
         def shuffle(t, key):
             out = t.shuffle(key)
@@ -70,11 +86,24 @@ def main():
 
         def rows(t):
             return t.names, (t.to_numpy() if t.num_rows else [np.zeros(0, np.uint32)] * len(t.names))
-    else:
-        store = orc.OracleStore(8192).load_quads(mine)
 
-        def scan(s, p, o):
-            return store.plan([rf.traverse(0), rf.scan(s), rf.traverse(p), rf.scan(o)]).execute()
+        def names(t): return t.names
+
+        def nullable(t): return t.nullable
+    else:
+        # the oracle as per-rank engine.  Its store keeps every permutation over the same quads, so the sharded layouts are
+        # emulated with one oracle store per shard: results are permutation-independent, only WHICH quads a rank scans matters
+        stores = {}
+
+        def ostore(pm):
+            if pm not in stores:
+                stores[pm] = orc.OracleStore(8192).load_quads(mine if layout == "subject" else shard(pm))
+            return stores[pm]
+
+        def scan(s, p, o, order_by=None):
+            pm = F.GPSO if order_by == s else F.GPOS  # what rfgpu_scan_plan_order_by picks for `?s <p> ?o`
+            t = ostore(pm).plan([rf.traverse(0), rf.scan(s), rf.traverse(p), rf.scan(o)]).execute()
+            return t, scan_partition_var(layout, pm, (0, s, p, o))
 
         def shuffle(t, key):
             # the exchange of rfgpu_shuffle, with gloo carrying the blocks: partition, all-gather the count matrix,
@@ -101,19 +130,40 @@ def main():
         def rows(t):
             return t.names, t.cols
 
+        def names(t): return t.names
+
+        def nullable(t): return t.nullable
+
+    class Fold:  # the engine adapter of dist.fold_bgp
+        pass
+    Fold.scan = staticmethod(lambda pat, order_by: scan(pat[0], pat[1], pat[2], order_by))
+    Fold.shuffle, Fold.join, Fold.names, Fold.nullable = (staticmethod(f) for f in (shuffle, join, names, nullable))
+
     results = {}
-    # chain: shuffle the running solution on the next join variable; the scan side is already partitioned on it
-    ab = scan("a", p1, "b")
-    abc = join(shuffle(ab, "b"), scan("b", p2, "c"), F.JOIN_INNER)
-    abcd = join(shuffle(abc, "c"), scan("c", p3, "d"), F.JOIN_INNER)
-    results["chain"] = rows(abcd)
-    results["optional"] = rows(join(shuffle(scan("a", p1, "b"), "b"), scan("b", p2, "c"), F.JOIN_LEFT))
-    results["star"] = rows(join(scan("s", p1, "x"), scan("s", p2, "y"), F.JOIN_INNER))
+    # every join goes through dist.fold_bgp: an exchange only where a side is not yet partitioned on the join variable
+    chain, _, ex_chain = fold_bgp(Fold, [("a", p1, "b"), ("b", p2, "c"), ("c", p3, "d")], F.JOIN_INNER)
+    results["chain"] = rows(chain)
+    opt, opt_pk, ex_opt = fold_bgp(Fold, [("a", p1, "b"), ("b", p2, "c")], F.JOIN_LEFT)
+    results["optional"] = rows(opt)
+    star, _, ex_star = fold_bgp(Fold, [("s", p1, "x"), ("s", p2, "y")], F.JOIN_INNER)
+    results["star"] = rows(star)
+    if world > 1:  # what each layout costs in exchanges
+        want = {"subject": (2, 1, 0), "hash": (1, 0, 0), "range": (4, 2, 2)}[layout]
+        assert (ex_chain, ex_opt, ex_star) == want, (layout, ex_chain, ex_opt, ex_star)
+    # a join on a variable that an OPTIONAL left unbound must not be hashed to one rank (NULL is compatible with every row)
+    try:
+        fold_bgp(Fold, [("a", p1, "b"), ("b", p2, "c"), ("c", p3, "d")], F.JOIN_LEFT)  # ?c is unbound where the OPTIONAL failed
+        raise AssertionError("a distributed join on a nullable key must be refused")
+    except NotImplementedError:
+        pass
+
+    def scan1(s, p, o):  # subject-partitioned scans of the skew test below (layout "subject" only)
+        return scan(s, p, o)[0]
 
     # skewed join variable (BASELINE configs[4]): ?a p1 ?b [OPTIONAL] { ?b p2 ?c } with Zipf objects — the heavy ?b values are
     # not shuffled: their rhs rows are replicated (dist.skew_aware_join).  GPU mode runs it only on request until it has been
     # validated on a multi-GPU box.
-    if mode == "cpu" or os.environ.get("RFGPU_TEST_SKEW") == "1":
+    if layout == "subject" and (mode == "cpu" or os.environ.get("RFGPU_TEST_SKEW") == "1"):
         def gather(obj):
             box = [None] * world
             dist.all_gather_object(box, obj)
@@ -162,7 +212,7 @@ def main():
             shuffle = staticmethod(_shuffle)
             join = staticmethod(_join)
         for name, jt in (("skew_inner", F.JOIN_INNER), ("skew_optional", F.JOIN_LEFT)):
-            parts, heavy = skew_aware_join(scan("a", p1, "b"), scan("b", p2, "c"), "b", jt, Ops, world, gather, heavy_factor=0.02)
+            parts, heavy = skew_aware_join(scan1("a", p1, "b"), scan1("b", p2, "c"), "b", jt, Ops, world, gather, heavy_factor=0.02)
             assert world == 1 or len(heavy) > 0, "the test graph must have heavy join keys"
             got = [rows(t) for t in parts]
             results[name] = (got[0][0], [np.concatenate([np.asarray(g[1][c]) for g in got]) for c in range(len(got[0][0]))])
@@ -197,7 +247,7 @@ def main():
             want = orc.canonical_rows(e.cols)
             assert got.shape == want.shape and np.array_equal(got, want), (name, got.shape, want.shape)
             assert len(want) > 0, name
-            print(f"dist {mode}{'/' + exchange if mode == 'gpu' else ''} world={world} {name}: {len(want)} rows identical to the single-store oracle", flush=True)
+            print(f"dist {mode}{'/' + exchange if mode == 'gpu' else ''} layout={layout} world={world} {name}: {len(want)} rows identical to the single-store oracle", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 

@@ -42,14 +42,39 @@ def test_exchange_layout_and_partition():
     assert sorted(np.concatenate(recv).tolist()) == sorted(np.concatenate([t[0] for t in tables]).tolist())
 
 
-def test_two_rank_chain_join_gloo():
+import pytest  # noqa: E402
+
+
+@pytest.mark.parametrize("layout,world", [("subject", 2), ("hash", 2), ("range", 2), ("range", 3)])
+def test_chain_join_gloo(layout, world):
+    """dist.fold_bgp over `world` gloo ranks, oracle as per-rank engine: chain / OPTIONAL / star identical to the single-store
+    oracle under every layout, the number of exchanges each layout needs, and the refusal of a nullable join key"""
     env = dict(os.environ, MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="1")
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
-           "--master-port", "29541", os.path.join(ROOT, "tests", "dist_worker.py"), "cpu", "30000"]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
+           "127.0.0.1", "--master-port", "29541", os.path.join(ROOT, "tests", "dist_worker.py"), "cpu", "30000", "-", layout]
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
-    for name in ("chain", "optional", "star", "skew_inner", "skew_optional"):
-        assert f"world=2 {name}:" in r.stdout, r.stdout
+    for name in ("chain", "optional", "star") + (("skew_inner", "skew_optional") if layout == "subject" else ()):
+        assert f"layout={layout} world={world} {name}:" in r.stdout, r.stdout
+
+
+def test_range_cuts_and_owner():
+    """slices are contiguous in the sorted permutation, nearly equal, and cuts fall on key starts unless the key is heavy"""
+    import rdf_fusion_b200 as rf
+    from rdf_fusion_b200.dist import range_cuts, range_owner_np
+    g = rf.generate_graph(60000, 16, 1.1, 3)
+    cols = (g.g, g.s, g.p, g.o)
+    for perm in (F.GSPO, F.GPOS, F.GOSP, F.GPSO):
+        comps = [(perm >> (2 * i)) & 3 for i in range(4)]
+        order = np.lexsort(tuple(reversed([cols[c] for c in comps])))
+        for world in (2, 5, 8):
+            cuts = range_cuts(cols, perm, world)
+            owner = range_owner_np(cols, perm, cuts)[order]
+            assert np.all(np.diff(owner) >= 0) and owner.max() <= world - 1  # contiguous slices in sorted order
+            sizes = np.bincount(owner, minlength=world)
+            assert sizes.max() <= 1.2 * len(order) / world, (perm, world, sizes)
+            if perm == F.GSPO:  # subjects are light keys: every cut is the start of a subject
+                assert all(c[2] == 0 and c[3] == 0 for c in cuts)
 
 
 def test_find_heavy_keys_is_exact():
