@@ -26,6 +26,19 @@ def build(force=False):
     return LIB_PATH
 
 
+def use_native_build():
+    """bench.py's CPU arm: (re)build the oracle with -march=native ON THIS MACHINE and load that library instead
+    of the portable one.  Must be called before the first lib() of the process; falls back to the portable build."""
+    global LIB_PATH
+    assert _lib is None, "the oracle library is already loaded"
+    try:
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B", "native"])
+        LIB_PATH = os.path.join(_HERE, "_build", "librf_oracle_native.so")
+        return True
+    except Exception:
+        return False
+
+
 def lib():
     global _lib
     if _lib is None:

@@ -452,6 +452,18 @@ std::vector<Batch> Index::scan(const Instructions& in) const {
         b.names.push_back(eff.ins[c].var);
         b.cols.emplace_back();
       }
+    bool unfiltered = true;
+    for (int c = 0; c < 4; c++) unfiltered = unfiltered && eff.ins[c].pred.kind == Predicate::None;
+    if (unfiltered) {
+      // scan.rs:146-170: no predicate left after pruning -> the reference hands out Arc slices of the column chunks
+      // (zero-copy).  Here: one bulk copy per bound column, no per-row work.
+      size_t k = 0;
+      for (int c = 0; c < 4; c++)
+        if (eff.ins[c].scan) b.cols[k++].assign(data[c], data[c] + n);
+      b.rows = n;
+      if (b.rows) out.push_back(std::move(b));
+      continue;
+    }
     for (size_t r = 0; r < n; r++) {
       bool keep = true;
       for (int c = 0; c < 4 && keep; c++) {
