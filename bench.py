@@ -224,6 +224,8 @@ def build_store(ctx, a, n_global, rank, world):
     if world == 1:
         return store.build_from_table(ctx.synth_quads(n_global, **gen), s_placed + o_placed)
     store.set_sharded()
+    if a.layout in ("hash", "subject"):
+        store.set_placement(a.layout, world, rank)
     if a.layout == "subject":
         store.build_from_table(ctx.synth_quads(n_global, keep=("hash_subject", rank, world), **gen), s_placed + o_placed)
     elif a.layout == "hash":
@@ -291,6 +293,7 @@ def run_ours(a):
     cnt = {"rows": 0, "out": 0, "sent": 0, "sent_bytes": 0, "shuffles": 0, "shuffle_ms": 0.0, "time_shuffles": False}
     join_bytes = {}  # physical operator -> algorithmic bytes 4 (cb Nb + cp Np + co No) of the joins that used it
     plan_cache = {}
+    prefetched, chain_keys = {}, []
 
     class Ops:  # the engine adapter of dist.fold_bgp
         @staticmethod
@@ -299,7 +302,7 @@ def run_ours(a):
             if key not in plan_cache:
                 plan_cache[key] = mkplan(pat[0], pat[1], pat[2], order_by)
             pl = plan_cache[key]
-            t = pl.execute(allow_view=True)
+            t = prefetched.pop(key) if key in prefetched else pl.execute(allow_view=True)
             cnt["rows"] += t.num_rows
             return t, (scan_partition_var(layout, pl.index, (0,) + pat) if world > 1 else order_by)
 
@@ -350,7 +353,14 @@ def run_ours(a):
         return tj
 
     def part_chain():
+        # the range look-ups of all the chain's scans share one launch and one host hand-off (rfgpu_scan_execute_many); the
+        # (pattern, order) list is the one the first fold asked for
+        if chain_keys:
+            for key, t in zip(chain_keys, rf.execute_many([plan_cache[k] for k in chain_keys], allow_view=True)):
+                prefetched[key] = t
         t, _, _ = fold_bgp(Ops, chain, F.JOIN_INNER)
+        if not chain_keys:
+            chain_keys.extend(k for k in plan_cache if k[0] in chain)
         cnt["out"] += t.num_rows
         return t
 

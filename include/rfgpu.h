@@ -110,6 +110,17 @@ int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm,
  * therefore hold different quads and different row counts.  A scan is the same binary search over the local shard; the union
  * of the ranks' results is the global scan.  Must be set before the second rfgpu_store_add_index / rfgpu_store_build. */
 int32_t rfgpu_store_set_sharded(rfgpu_store* s, int32_t on);
+/* Declares how the quads of a sharded store were placed, so that scans can tag their output: under rfgpu_shuffle's
+ * destination (id mod n_ranks) the placement column of a permutation holds only ids = rank (mod n_ranks), and a join's
+ * direct-address table over such a column needs one slot per n_ranks ids.  Verified on the device by every later
+ * rfgpu_store_add_index / rfgpu_store_build (RFGPU_E_INVALID if a quad does not belong to this rank).  Call before adding
+ * permutations. */
+typedef enum {
+  RFGPU_PLACE_NONE = 0,
+  RFGPU_PLACE_JOINED_COMPONENT = 1, /* subject for GSPO / GPSO / GSOP, object for GPOS / GOSP / GOPS */
+  RFGPU_PLACE_SUBJECT = 2           /* every permutation holds the quads whose subject belongs to the rank */
+} rfgpu_placement_mode;
+int32_t rfgpu_store_set_placement(rfgpu_store* s, int32_t mode, uint32_t n_ranks, uint32_t rank);
 uint64_t rfgpu_store_len(const rfgpu_store* s);
 /* rows of permutation i (they differ in a range-sharded store) */
 uint64_t rfgpu_store_index_rows(const rfgpu_store* s, int32_t i);
@@ -441,7 +452,7 @@ int32_t rfgpu_comm_init(rfgpu_ctx* ctx, int32_t rank, int32_t n_ranks,
                         const uint8_t id[RFGPU_UNIQUE_ID_BYTES]);
 int32_t rfgpu_comm_rank(const rfgpu_ctx* ctx);
 int32_t rfgpu_comm_size(const rfgpu_ctx* ctx);
-/* Hash-partition `in` on column `key_col` (dest = mix32(id) mod n_ranks; NULL is an ordinary key value) and
+/* Hash-partition `in` on column `key_col` (dest = id mod n_ranks — ids are dense dictionary ids; NULL is an ordinary key value and goes to rank 0) and
  * exchange the rows between the ranks: the exchange DataFusion's RepartitionExec(Hash) does between tokio tasks.
  * Collective: every rank of the communicator calls it, in the same order.  Default path: ONE kernel that computes the
  * destinations, reserves space in each destination's receive arena with an atomic over NVLink and writes the rows there

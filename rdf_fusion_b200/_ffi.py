@@ -74,6 +74,7 @@ class SynthDesc(C.Structure):
                 ("has_lo", C.c_int32), ("has_hi", C.c_int32)]
 
 
+PLACE_NONE, PLACE_JOINED_COMPONENT, PLACE_SUBJECT = 0, 1, 2
 SYNTH_KEEP_ALL, SYNTH_KEEP_HASH_SUBJECT, SYNTH_KEEP_RANGE, SYNTH_KEEP_HASH_OBJECT = 0, 1, 2, 3
 
 
@@ -99,6 +100,7 @@ SIGNATURES = {
     "rfgpu_store_num_indexes": (C.c_int32, [C.c_void_p]),
     "rfgpu_store_set_sharded": (C.c_int32, [C.c_void_p, C.c_int32]),
     "rfgpu_store_index_rows": (C.c_uint64, [C.c_void_p, C.c_int32]),
+    "rfgpu_store_set_placement": (C.c_int32, [C.c_void_p, C.c_int32, C.c_uint32, C.c_uint32]),
     "rfgpu_synth_quads": (C.c_int32, [C.c_void_p, C.POINTER(SynthDesc), C.POINTER(C.c_void_p)]),
     "rfgpu_store_index_perm": (C.c_uint32, [C.c_void_p, C.c_int32]),
     "rfgpu_scan_plan_create": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(ScanInstruction), C.POINTER(C.c_void_p)]),

@@ -339,6 +339,14 @@ class Store:
         self.ctx.check(self.ctx.lib.rfgpu_store_set_sharded(self.h, 1 if on else 0))
         return self
 
+    def set_placement(self, layout: str, n_ranks: int, rank: int):
+        """declare (before adding permutations) that the quads were placed by rfgpu_shuffle's destination: layout "hash" = by
+        the component each permutation is joined on, "subject" = every permutation by subject.  Verified on upload; scans
+        then tag the placement column with its residue class (rfgpu_store_set_placement)."""
+        mode = {"hash": F.PLACE_JOINED_COMPONENT, "subject": F.PLACE_SUBJECT}[layout]
+        self.ctx.check(self.ctx.lib.rfgpu_store_set_placement(self.h, mode, n_ranks, rank))
+        return self
+
     def index_rows(self, perm: int) -> int:
         return int(self.ctx.lib.rfgpu_store_index_rows(self.h, self.perms.index(perm)))
 

@@ -97,6 +97,14 @@ void rfgpu_ctx::collect_profile() {
   pending.clear();
 }
 
+__global__ void k_check_residue(const uint32_t* __restrict__ v, uint64_t n, uint32_t g, uint32_t r,
+                                unsigned long long* __restrict__ first_bad) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride)
+    if (v[i] % g != r) atomicMin(first_bad, (unsigned long long)i);
+}
+
 // ---- sortedness / uniqueness check of an index permutation ----
 __global__ void k_check_sorted(const uint32_t* __restrict__ c0, const uint32_t* __restrict__ c1,
                                const uint32_t* __restrict__ c2, const uint32_t* __restrict__ c3, uint64_t n,
@@ -274,10 +282,36 @@ int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm, con
   } else {
     ctx->sync();
   }
+  if (const int pl = rf::placement_level(perm, s->place_mode); pl >= 0 && s->place_g > 1 && n_rows) {
+    // the declared placement is what scans tag their output with: every id of the placement column must be ours
+    unsigned long long* bad = (unsigned long long*)ctx->h_scratch;
+    auto d_bad = ctx->alloc(8);
+    RF_CUDA(cudaMemsetAsync(d_bad->ptr, 0xFF, 8, ctx->stream()));
+    {
+      rf::KernelScope ks(ctx, "k_check_residue");
+      uint32_t blocks = std::min<uint64_t>(rf::div_up(n_rows, 256), (uint64_t)ctx->core->num_sms * 8);
+      k_check_residue<<<blocks, 256, 0, ctx->stream()>>>(ix.col[pl]->as<uint32_t>(), n_rows, s->place_g, s->place_r,
+                                                         d_bad->as<unsigned long long>());
+    }
+    RF_CUDA(cudaMemcpyAsync(bad, d_bad->ptr, 8, cudaMemcpyDeviceToHost, ctx->stream()));
+    ctx->sync();
+    if (*bad != ~0ull)
+      throw rf::Error(RFGPU_E_INVALID, "row " + std::to_string(*bad) + " of the permutation does not belong to rank " +
+                                           std::to_string(s->place_r) + " of " + std::to_string(s->place_g) +
+                                           " under the declared placement");
+  }
   s->indexes.push_back(std::move(ix));
   RF_API_END(ctx)
 }
 
+int32_t rfgpu_store_set_placement(rfgpu_store* s, int32_t mode, uint32_t n_ranks, uint32_t rank) {
+  if (!s || mode < RFGPU_PLACE_NONE || mode > RFGPU_PLACE_SUBJECT || n_ranks == 0 || rank >= n_ranks || !s->indexes.empty())
+    return RFGPU_E_INVALID;
+  s->place_mode = mode;
+  s->place_g = mode == RFGPU_PLACE_NONE ? 1 : n_ranks;
+  s->place_r = mode == RFGPU_PLACE_NONE ? 0 : rank;
+  return RFGPU_OK;
+}
 int32_t rfgpu_store_set_sharded(rfgpu_store* s, int32_t on) {
   if (!s) return RFGPU_E_INVALID;
   s->sharded = on != 0;

@@ -418,6 +418,8 @@ extern "C" int32_t rfgpu_filter(rfgpu_ctx* ctx, const rfgpu_table* in, const rfg
     Column col;
     col.name = in->cols[c].name;
     col.nullable = in->cols[c].nullable;
+    col.mod_g = in->cols[c].mod_g;  // a filter only drops rows
+    col.mod_r = in->cols[c].mod_r;
     col.owner = bufs[c];
     col.data = bufs[c]->as<uint32_t>();
     t->cols.push_back(std::move(col));

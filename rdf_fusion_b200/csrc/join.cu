@@ -89,12 +89,14 @@ uint32_t grid_for(rfgpu_ctx* ctx, uint64_t n, int threads);
 struct DenseRange {
   bool ok = false;      // the identity-hash table applies
   uint32_t kmin = 1, range = 0;
+  uint32_t stride = 1;  // slot = (key - kmin) / stride (the build keys' residue class: Column::mod_g)
 };
 
 // Bounds of the non-NULL build keys and whether a table of one u32 per possible key is worth it: at most 8 slots per
 // input row (memset + scan of the table stay below the cost of streaming the inputs) and at most 2^28 slots.
-DenseRange dense_range(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, bool sorted, uint64_t np) {
+DenseRange dense_range(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, bool sorted, uint64_t np, uint32_t stride) {
   DenseRange D;
+  D.stride = std::max<uint32_t>(stride, 1);
   if (!ctx->opt_lookup_join || nb == 0 || nb >= 0xFFFFFFFFull) return D;
   uint32_t* h = reinterpret_cast<uint32_t*>(ctx->h_scratch + 12);
   bool have = false;
@@ -120,7 +122,7 @@ DenseRange dense_range(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, bool sor
     }
     h[0] += 1;  // the kernel keeps min - 1
   }
-  const uint64_t range = (uint64_t)h[1] - h[0] + 1;
+  const uint64_t range = ((uint64_t)h[1] - h[0]) / D.stride + 1;
   if (range > (1ull << 28) || range > 8 * (nb + np) + 65536) return D;
   D.ok = true;
   D.kmin = h[0];
@@ -135,7 +137,7 @@ BufRef dense_table_sorted(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, const
   RF_CUDA(cudaMemsetAsync(tab->ptr, 0xFF, n * 4, ctx->stream()));
   {
     KernelScope ks(ctx, "k_dense_heads", 4ull * nb);
-    k_dense_heads<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(bk, nb, D.kmin, D.range, tab->as<uint32_t>());
+    k_dense_heads<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(bk, nb, D.kmin, D.stride, D.range, tab->as<uint32_t>());
   }
   const uint32_t tiles = div_up(n, kSmTile);
   BufRef status = ctx->alloc((uint64_t)tiles * 8);
@@ -161,13 +163,14 @@ BufRef dense_table_unsorted(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, con
   if (D.range) {
     {
       KernelScope ks(ctx, "k_dense_count", 4ull * nb);
-      k_dense_count<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(bk, nb, D.kmin, cnt);
+      k_dense_count<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(bk, nb, D.kmin, D.stride, cnt);
     }
     exclusive_scan_u32(ctx, cnt, cnt, D.range, nullptr);
     DenseFillArgs F{};
     F.bk = bk;
     F.nb = nb;
     F.kmin = D.kmin;
+    F.stride = D.stride;
     F.cnt = cnt;
     F.n_cols = (int32_t)cols.size();
     for (size_t c = 0; c < cols.size(); c++) {
@@ -227,6 +230,7 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
   A.offs = offs;
   A.kmin = D.kmin;
   A.range = D.range;
+  A.stride = D.stride;
   // compact copy of the table (2 bytes per key): what the probe reads unless a key has more than 255 build rows
   const uint32_t groups = (D.range + 3) / 4;
   BufRef tab2 = ctx->alloc((uint64_t)groups * 8 + 16);
@@ -645,12 +649,21 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
     Column c;
     c.name = L->cols[i].name;
     c.nullable = L->cols[i].nullable;
+    // residue class of the values (rf_common.hpp): an lhs column keeps its own; a shared column of a compatible join is
+    // COALESCE(lhs, rhs) and keeps it only if the rhs column is in the same class
+    c.mod_g = L->cols[i].mod_g;
+    c.mod_r = L->cols[i].mod_r;
+    if (algo == RFGPU_JOIN_ALGO_COMPATIBLE)
+      for (auto& k : keys)
+        if (k.l == (int)i && (R->cols[k.r].mod_g != c.mod_g || R->cols[k.r].mod_r != c.mod_r)) c.mod_g = 1, c.mod_r = 0;
     T->cols.push_back(c);
   }
   for (int j : rhs_only) {
     Column c;
     c.name = R->cols[j].name;
     c.nullable = left ? true : R->cols[j].nullable;
+    c.mod_g = R->cols[j].mod_g;
+    c.mod_r = R->cols[j].mod_r;
     T->cols.push_back(c);
   }
   auto finish = [&](std::vector<BufRef>& bufs, uint64_t rows) {
@@ -759,7 +772,7 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
     if (keys.size() == 1 && Pt->rows > 0 && Bt->rows > 0) {
       const int bkey = Bt == L ? keys[0].l : keys[0].r;
       const bool bsorted = Bt->sorted_col == bkey;
-      const DenseRange D = dense_range(ctx, kc(Bt, 0), Bt->rows, bsorted, Pt->rows);
+      const DenseRange D = dense_range(ctx, kc(Bt, 0), Bt->rows, bsorted, Pt->rows, Bt->cols[bkey].mod_g);
       if (D.ok) {
         std::vector<BufRef> bufs;
         const uint64_t n_out = lookup_join(ctx, kc(Pt, 0), Pt->rows, kc(Bt, 0), Bt->rows, bsorted, left, D, specs, &bufs);
@@ -1044,6 +1057,8 @@ rfgpu_table* semi_anti_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_ta
     Column c;
     c.name = L->cols[i].name;
     c.nullable = L->cols[i].nullable;
+    c.mod_g = L->cols[i].mod_g;
+    c.mod_r = L->cols[i].mod_r;
     c.owner = kept[i];
     c.data = kept[i]->as<uint32_t>();
     T->cols.push_back(std::move(c));

@@ -10,8 +10,10 @@
 // identity hash  slot = key - kmin  the table needs no keys, no CAS and no collision handling; it is ONE u32 per possible
 // key (40 MB for the 10^7 subjects of BASELINE configs[1]: L2-resident) and a probe is one aligned 16-byte load:
 //
-//   offs[i] = number of build rows with key < kmin + i      (i = 0 .. range; build rows in KEY order)
-//   build rows of key k = positions [offs[k - kmin], offs[k - kmin + 1])
+//   offs[i] = number of build rows with key < kmin + i * stride      (i = 0 .. range; build rows in KEY order)
+//   build rows of key k = positions [offs[slot(k)], offs[slot(k) + 1]),   slot(k) = (k - kmin) / stride
+// stride = 1, or — when the build keys are known to lie in one residue class mod g (the key column of a shuffle result, the
+// placement column of a sharded scan: Column::mod_g) — stride = g, so that a rank's share of a dense id range is dense again.
 //
 // Build, sorted build side (a scan in index order — every rhs of a left-deep BGP fold can be one):
 //   k_dense_heads     offs[key - kmin] = row, written once per distinct key at the head of its run
@@ -74,13 +76,14 @@ k_key_min_max(const uint32_t* __restrict__ k, uint64_t n, unsigned int* __restri
 
 // ---------------- sorted build side: run heads + suffix-min ----------------
 __global__ void __launch_bounds__(256)
-k_dense_heads(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t range, uint32_t* __restrict__ offs) {
+k_dense_heads(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t kstride, uint32_t range,
+              uint32_t* __restrict__ offs) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i == 0) offs[range] = (uint32_t)nb;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (; i < nb; i += stride) {
     const uint32_t k = __ldg(bk + i);
-    if (k != 0 && (i == 0 || __ldg(bk + i - 1) != k)) offs[k - kmin] = (uint32_t)i;
+    if (k != 0 && (i == 0 || __ldg(bk + i - 1) != k)) offs[(k - kmin) / kstride] = (uint32_t)i;
   }
 }
 
@@ -181,19 +184,19 @@ k_suffix_min_u32(uint32_t* __restrict__ a, uint64_t n, unsigned long long* __res
 
 // ---------------- unsorted build side: counting sort by key ----------------
 __global__ void __launch_bounds__(256)
-k_dense_count(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t* __restrict__ cnt) {
+k_dense_count(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t kstride, uint32_t* __restrict__ cnt) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (; i < nb; i += stride) {
     const uint32_t k = __ldg(bk + i);
-    if (k != 0) atomicAdd(cnt + (k - kmin), 1u);  // no return value: RED.ADD
+    if (k != 0) atomicAdd(cnt + (k - kmin) / kstride, 1u);  // no return value: RED.ADD
   }
 }
 
 struct DenseFillArgs {
   const uint32_t* bk;
   uint64_t nb;
-  uint32_t kmin;
+  uint32_t kmin, stride;
   uint32_t* cnt;  // after the exclusive scan cnt[s] = start(s); the fill walks it to end(s) = start(s + 1)
   const uint32_t* src[kMaxCols];
   uint32_t* dst[kMaxCols];
@@ -207,7 +210,7 @@ k_dense_fill(const __grid_constant__ DenseFillArgs A) {
   for (; i < A.nb; i += stride) {
     const uint32_t k = __ldg(A.bk + i);
     if (k == 0) continue;
-    const uint32_t pos = atomicAdd(A.cnt + (k - A.kmin), 1u);
+    const uint32_t pos = atomicAdd(A.cnt + (k - A.kmin) / A.stride, 1u);
     for (int c = 0; c < A.n_cols; c++) A.dst[c][pos] = __ldg(A.src[c] + i);
   }
 }
@@ -234,6 +237,16 @@ k_dense_compress(const uint32_t* __restrict__ offs, uint32_t range, uint2* __res
   if (over) atomicOr(overflow, 1u);
 }
 
+// slot of a probe key, or 0xFFFFFFFF when it can have no partner: NULL (0), below kmin, beyond the table, or (stride > 1)
+// not in the residue class of the build keys
+__device__ __forceinline__ uint32_t key_slot(uint32_t key, uint32_t kmin, uint32_t stride, uint32_t range) {
+  if (key < kmin || key == 0) return 0xFFFFFFFFu;
+  const uint32_t d = key - kmin;
+  if (stride == 1) return d < range ? d : 0xFFFFFFFFu;
+  const uint32_t q = d / stride;
+  return (q * stride == d && q < range) ? q : 0xFFFFFFFFu;
+}
+
 // ---------------- probe + expand ----------------
 struct LookupArgs {
   const uint32_t* pk;  // probe keys (any order, 0 = NULL never matches)
@@ -241,6 +254,7 @@ struct LookupArgs {
   const uint32_t* offs;  // [range + 1], any 4-byte alignment; the 16-byte look-up reads the enclosing aligned granule, so the
                          // allocation has >= 3 readable words on either side
   uint32_t kmin, range;
+  uint32_t stride;  // slot = (key - kmin) / stride; keys with (key - kmin) % stride != 0 are in no build row's class
   // compact form of the same table, 8 bytes per 4 keys {start of the first key, 4 x u8 row counts}: 2 bytes per key, so the
   // 10^7-key table of BASELINE configs[1] is 20 MB instead of 40 and stays L2-resident next to the streamed columns.
   // *overflow != 0: some key has more than 255 build rows and the kernel reads offs[] instead.
@@ -290,16 +304,17 @@ k_lookup_join(const __grid_constant__ LookupArgs A) {
       key[k] = i < rows ? dev::ld_hint_u32(A.pk + row0 + i, strm) : 0u;
     }
     uint2 w[8];
+    uint32_t slot[8];
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-      const uint32_t slot = key[k] - A.kmin;  // NULL (0) and keys below kmin wrap to >= range
+      slot[k] = key_slot(key[k], A.kmin, A.stride, A.range);  // >= range: NULL, out of range or another residue class
       w[k] = make_uint2(0u, 0u);
-      if (slot < A.range) w[k] = dev::ld_hint_v2(A.tab2 + (slot >> 2), keep);
+      if (slot[k] < A.range) w[k] = dev::ld_hint_v2(A.tab2 + (slot[k] >> 2), keep);
     }
 #pragma unroll
     for (int k = 0; k < 8; k++) {
       const uint32_t i = tid + k * kLThreads;
-      const uint32_t sh = ((key[k] - A.kmin) & 3u) * 8u;
+      const uint32_t sh = (slot[k] & 3u) * 8u;
       const uint32_t cnt = (w[k].y >> sh) & 255u;
       const uint32_t o0 = w[k].x + __dp4a(w[k].y & ((1u << sh) - 1u), 0x01010101u, 0u);  // + counts of the keys before it
       S.gs[i] = cnt ? o0 : kNone;
@@ -318,7 +333,7 @@ k_lookup_join(const __grid_constant__ LookupArgs A) {
     uint32_t slot[4];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-      slot[k] = key[k] - A.kmin;  // NULL (0) and keys below kmin wrap to >= range
+      slot[k] = key_slot(key[k], A.kmin, A.stride, A.range);
       v[k] = make_uint4(0u, 0u, 0u, 0u);
       if (slot[k] < A.range)
         v[k] = dev::ld_hint_v4(reinterpret_cast<const uint4*>((uintptr_t)(A.offs + slot[k]) & ~(uintptr_t)15), keep);
@@ -476,29 +491,6 @@ k_lookup_join(const __grid_constant__ LookupArgs A) {
       }
     }
     __syncthreads();
-  }
-}
-
-// ---------------- existence / counts over the same table (MINUS, [NOT] EXISTS, GROUP BY key COUNT) ----------------
-// flag[i] = 1 where probe key i has at least one build row (flag is left alone elsewhere)
-__global__ void __launch_bounds__(256)
-k_dense_contains(const uint32_t* __restrict__ pk, uint64_t np, const uint32_t* __restrict__ cnt, uint32_t kmin,
-                 uint32_t range, uint32_t* __restrict__ flag) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  for (; i + 3 * stride < np; i += 4 * stride) {
-    uint32_t s[4], c[4];
-#pragma unroll
-    for (int u = 0; u < 4; u++) s[u] = __ldg(pk + i + u * stride) - kmin;
-#pragma unroll
-    for (int u = 0; u < 4; u++) c[u] = s[u] < range ? __ldg(cnt + s[u]) : 0u;
-#pragma unroll
-    for (int u = 0; u < 4; u++)
-      if (c[u]) flag[i + u * stride] = 1u;
-  }
-  for (; i < np; i += stride) {
-    const uint32_t s = __ldg(pk + i) - kmin;
-    if (s < range && __ldg(cnt + s)) flag[i] = 1u;
   }
 }
 

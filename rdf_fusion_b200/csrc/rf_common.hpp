@@ -62,6 +62,11 @@ struct Column {
   bool nullable = false;
   const uint32_t* data = nullptr;  // device, 4-B aligned (views into an index keep the index' alignment)
   BufRef owner;                    // keeps `data` alive
+  // Residue class of the column: every non-NULL value v has v % mod_g == mod_r (mod_g = 1: nothing known).  Set where it is
+  // certain — the key column of a shuffle result (dest = id mod g), the placement column of a scan over a sharded store
+  // whose placement was verified on upload — and carried along by operators that copy values.  A direct-address join table
+  // over such a column indexes (v - min) / mod_g: dense on every rank.  Losing the tag costs speed, never correctness.
+  uint32_t mod_g = 1, mod_r = 0;
 };
 
 struct KernelStat {
@@ -90,6 +95,9 @@ struct rfgpu_index_t {
 struct rfgpu_store {
   std::atomic<int> refs{1};
   bool sharded = false;  // permutations are row slices of the global permutations: different quads per index
+  // hash placement (rfgpu_store_set_placement): the placement column of every permutation holds ids ≡ place_r (mod place_g)
+  uint32_t place_g = 1, place_r = 0;
+  int place_mode = 0;  // rfgpu_placement_mode
   std::vector<rfgpu_index_t> indexes;
 };
 
@@ -154,6 +162,7 @@ struct KernelScope {
 inline uint32_t div_up(uint64_t a, uint64_t b) { return (uint32_t)((a + b - 1) / b); }
 
 rfgpu_table* new_table();
+int placement_level(uint32_t perm, int mode);  // ctx.cu: level whose ids decide a quad's rank (-1: none)
 BufRef alloc_col(rfgpu_ctx* ctx, uint64_t rows);  // uint32_t[rows] (+pad)
 int find_col(const rfgpu_table* t, const std::string& name);
 

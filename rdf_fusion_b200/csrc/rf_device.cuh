@@ -127,6 +127,12 @@ __device__ __forceinline__ void lookback_exclusive2(unsigned long long* sa, unsi
   *excl_b = eb;
 }
 
+// ---------------- the shuffle's destination ----------------
+// dest = id mod g.  Object ids are dense dictionary ids (lib/storage/src/memory/object_id_mapping.rs), so the residue classes
+// are balanced, and — unlike a mixing hash — the ids a rank holds after a shuffle stay DENSE in (id - min) / g: the
+// direct-address join tables (lookup_join.cuh) keep one slot per possible local key on every rank.  NULL (0) goes to rank 0.
+__device__ __host__ __forceinline__ uint32_t shuffle_dest(uint32_t id, uint32_t n_ranks) { return id % n_ranks; }
+
 // ---------------- hashing ----------------
 __device__ __host__ __forceinline__ uint32_t mix32(uint32_t x) {  // murmur3 finaliser
   x ^= x >> 16;

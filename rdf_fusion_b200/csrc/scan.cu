@@ -252,6 +252,14 @@ static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t
     for (size_t k = 0; k < oc.size(); k++)
       if (!sv.empty() && oc[k].name == sv) sorted_out = (int)k;
   }
+  // a sharded store with a declared (and verified) placement: the placement column holds only ids = rank (mod n_ranks)
+  const int place_level = placement_level(p->perm, p->store->place_mode);
+  auto tag = [&](Column& c, int level) {
+    if (level == place_level && p->store->place_g > 1) {
+      c.mod_g = p->store->place_g;
+      c.mod_r = p->store->place_r;
+    }
+  };
   auto make_empty = [&]() {
     std::unique_ptr<rfgpu_table> t(new_table());
     t->sorted_col = sorted_out;
@@ -259,6 +267,7 @@ static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t
       Column c;
       c.name = o.name;
       c.nullable = o.nullable;
+      tag(c, o.level);
       c.owner = alloc_col(ctx, 0);
       c.data = c.owner->as<uint32_t>();
       t->cols.push_back(std::move(c));
@@ -355,6 +364,7 @@ static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t
         Column c;
         c.name = o.name;
         c.nullable = o.nullable;
+        tag(c, o.level);
         c.owner = ix->col[o.level];
         c.data = S.col[o.level] + from;
         t->cols.push_back(std::move(c));
@@ -367,6 +377,7 @@ static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t
         Column c;
         c.name = oc[k].name;
         c.nullable = oc[k].nullable;
+        tag(c, oc[k].level);
         c.owner = ctx->alloc(R * 4 + 16);
         const uint32_t* src = S.col[oc[k].level] + from;
         uint32_t* dst = c.owner->as<uint32_t>() + (((uintptr_t)src & 15) >> 2);
@@ -415,6 +426,7 @@ static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t
       Column c;
       c.name = oc[k].name;
       c.nullable = oc[k].nullable;
+      tag(c, oc[k].level);
       c.owner = bufs[k];
       c.data = bufs[k]->as<uint32_t>();
       t->cols.push_back(std::move(c));

@@ -320,3 +320,25 @@ size_t rfgpu_scan_plan_describe(const rfgpu_scan_plan* p, char* buf, size_t cap)
 }
 
 }  // extern "C"
+
+namespace rf {
+// level of `perm` whose ids decide the rank of a quad under `mode` (-1: no placement)
+int placement_level(uint32_t perm, int mode) {
+  if (mode == RFGPU_PLACE_NONE) return -1;
+  int comp = RFGPU_S;
+  if (mode == RFGPU_PLACE_JOINED_COMPONENT) {
+    int seen = 0;
+    for (int l = 0; l < 4; l++) {
+      const int c = (perm >> (2 * l)) & 3;
+      if (c == RFGPU_G || c == RFGPU_P) continue;  // the first of subject / object in level order
+      comp = c;
+      seen = 1;
+      break;
+    }
+    if (!seen) return -1;
+  }
+  for (int l = 0; l < 4; l++)
+    if ((int)((perm >> (2 * l)) & 3) == comp) return l;
+  return -1;
+}
+}  // namespace rf

@@ -1,7 +1,7 @@
 // shuffle.cu — multi-GPU exchange of solution tables: hash partition on the join variable + all-to-all over NVLink.
 //
 // The reference has no distributed backend; its only exchange is DataFusion's RepartitionExec(Hash) between tokio
-// tasks when target_partitions > 1.  Here: one process (ctx) per GPU, dest = mix32(id) mod n_ranks.
+// tasks when target_partitions > 1.  Here: one process (ctx) per GPU, dest = id mod n_ranks (rf_device.cuh: shuffle_dest).
 //
 // Default path (k_shuffle_p2p): partition and transfer are ONE kernel.  rfgpu_comm_init gives every rank a receive arena
 // (cudaMalloc + cudaIpc handle, mapped by all peers).  Per 2048-row tile a CTA computes the destinations, orders the tile
@@ -102,8 +102,7 @@ struct Comm {
 // ---- partition kernels (fallback path and rfgpu_partition) ----
 
 __device__ __forceinline__ uint32_t dest_of(uint32_t id, uint32_t n_parts) {
-  const uint32_t h = dev::mix32(id);
-  return (n_parts & (n_parts - 1)) == 0 ? h & (n_parts - 1) : h % n_parts;  // uniform branch; 2/4/8 ranks skip the divide
+  return (n_parts & (n_parts - 1)) == 0 ? id & (n_parts - 1) : id % n_parts;  // uniform branch; 2/4/8 ranks skip the divide
 }
 
 // Warp-aggregated "take a ticket at counter[d]": lanes with the same d share one shared-memory atomic (with 2..8
@@ -256,8 +255,7 @@ __device__ __forceinline__ void p2p_ticket(const uint32_t (&key)[kP2pRows], uint
   for (int k = 0; k < kP2pRows; k++) {
     uint32_t d = kMaxParts;
     if (k * kP2pThreads + tid < rows) {
-      const uint32_t h = dev::mix32(key[k]);
-      d = kPow2 ? h & (n_parts - 1) : h % n_parts;  // dest_of
+      d = kPow2 ? key[k] & (n_parts - 1) : key[k] % n_parts;  // dest_of
     }
     out[k] = warp_ticket(counter, d, tid & 31) | (d << 16);
   }
@@ -498,6 +496,9 @@ static bool shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col, rfgp
     t->rows = mine;
     for (size_t c = 0; c < C; c++) {
       Column col = in->cols[c];
+      // rows arrive from every rank: only the key column has a known residue class now (dest = id mod g)
+      col.mod_g = (int)c == key_col ? (uint32_t)g : 1u;
+      col.mod_r = (int)c == key_col ? (uint32_t)me : 0u;
       col.owner = alloc_col(ctx, mine);
       col.data = col.owner->as<uint32_t>();
       if (mine)
@@ -517,7 +518,7 @@ static bool shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col, rfgp
 
 extern "C" {
 
-uint32_t rfgpu_shuffle_dest(uint32_t id, uint32_t n_ranks) { return n_ranks ? rf::dev::mix32(id) % n_ranks : 0; }
+uint32_t rfgpu_shuffle_dest(uint32_t id, uint32_t n_ranks) { return n_ranks ? rf::dev::shuffle_dest(id, n_ranks) : 0; }
 
 int32_t rfgpu_comm_unique_id(uint8_t id[RFGPU_UNIQUE_ID_BYTES]) {
   RF_API_BEGIN
@@ -621,6 +622,8 @@ int32_t rfgpu_shuffle(rfgpu_ctx* ctx, const rfgpu_table* in, int32_t key_col, rf
   std::vector<uint32_t*> dsts;
   for (size_t c = 0; c < in->cols.size(); c++) {
     Column col = in->cols[c];
+    col.mod_g = (int)c == key_col ? (uint32_t)g : 1u;  // see shuffle_p2p
+    col.mod_r = (int)c == key_col ? (uint32_t)me : 0u;
     col.owner = alloc_col(ctx, recv_total);
     col.data = col.owner->as<uint32_t>();
     dsts.push_back(col.owner->as<uint32_t>());

@@ -9,7 +9,7 @@
 //
 // Placement filter (which of the N global rows this rank keeps):
 //   ALL            every row
-//   HASH_SUBJECT   rows whose subject hashes to this rank (dest = mix32(s) mod g, the shuffle's hash)
+//   HASH_SUBJECT   rows whose subject hashes to this rank (dest = s mod g, the shuffle's destination)
 //   HASH_OBJECT    rows whose object hashes to this rank (for the permutations that are joined on their object)
 //   RANGE          rows whose quad, read in the level order of a permutation, lies in [lo, hi) lexicographically:
 //                  this rank's contiguous slice of the globally sorted permutation (north_star: "the index is
@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(kSynThreads) k_synth(const __grid_constant__ S
     uint32_t q[4] = {0, 0, 0, 0};  // g, s, p, o
     if (keep) {
       q[1] = (uint32_t)(17 + A.P + splitmix64(row ^ A.base[1]) % A.S);
-      if (A.keep == RFGPU_SYNTH_KEEP_HASH_SUBJECT) keep = dev::mix32(q[1]) % A.n_ranks == A.rank;
+      if (A.keep == RFGPU_SYNTH_KEEP_HASH_SUBJECT) keep = dev::shuffle_dest(q[1], A.n_ranks) == A.rank;
     }
     if (keep) {
       const uint64_t pr = upper_bound_f64(A.pcdf, A.P, unit(splitmix64(row ^ A.base[2])));
@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(kSynThreads) k_synth(const __grid_constant__ S
         const uint64_t gu = splitmix64(row ^ A.base[5]);
         q[0] = unit(gu) < A.named_frac ? (uint32_t)(1 + gu % 16) : 0u;
       }
-      if (A.keep == RFGPU_SYNTH_KEEP_HASH_OBJECT) keep = dev::mix32(q[3]) % A.n_ranks == A.rank;
+      if (A.keep == RFGPU_SYNTH_KEEP_HASH_OBJECT) keep = dev::shuffle_dest(q[3], A.n_ranks) == A.rank;
       if (A.keep == RFGPU_SYNTH_KEEP_RANGE) {
         if (A.has_lo && tuple_cmp4(q, A.perm, A.lo) < 0) keep = false;
         if (A.has_hi && tuple_cmp4(q, A.perm, A.hi) >= 0) keep = false;

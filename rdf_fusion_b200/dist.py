@@ -11,12 +11,12 @@ from typing import List, Sequence, Tuple
 
 import numpy as np
 
-from .loader import mix32_np
 
 
 def shuffle_dest_np(ids: np.ndarray, n_ranks: int) -> np.ndarray:
-    """dest = mix32(id) mod n_ranks (rfgpu_shuffle_dest)."""
-    return (mix32_np(np.asarray(ids, dtype=np.uint32)) % np.uint32(max(n_ranks, 1))).astype(np.uint32)
+    """dest = id mod n_ranks (rfgpu_shuffle_dest): ids are dense, so the residue classes are balanced and a rank's ids stay
+    dense in (id - min) / n_ranks (what the direct-address join tables index by)."""
+    return (np.asarray(ids, dtype=np.uint32) % np.uint32(max(n_ranks, 1))).astype(np.uint32)
 
 
 def partition_np(cols: Sequence[np.ndarray], key_col: int, n_parts: int) -> Tuple[List[np.ndarray], List[int]]:

@@ -26,12 +26,12 @@ def mix32_np(x: np.ndarray) -> np.ndarray:
 
 
 def partition_by_subject(quads_cols, rank: int, n_ranks: int):
-    """rows of (g,s,p,o) owned by `rank`: dest = mix32(s) mod n_ranks — the same hash rfgpu_shuffle uses, so a join
+    """rows of (g,s,p,o) owned by `rank`: dest = s mod n_ranks — the same destination rfgpu_shuffle uses, so a join
     on ?s over subject-partitioned scans needs no exchange."""
     g, s, p, o = quads_cols
     if n_ranks == 1:
         return g, s, p, o
-    keep = (mix32_np(s) % np.uint32(n_ranks)) == rank
+    keep = (np.asarray(s, dtype=np.uint32) % np.uint32(n_ranks)) == rank
     return g[keep], s[keep], p[keep], o[keep]
 
 

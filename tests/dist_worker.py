@@ -3,7 +3,7 @@ engine and the exchange is emulated with the same layout arithmetic) and tests/t
 CUDA path + rfgpu_shuffle over NCCL).
 
 Plan (BASELINE configs[3] in miniature): chain  ?a p1 ?b . ?b p2 ?c . ?c p3 ?d   and   ?a p1 ?b OPTIONAL { ?b p2 ?c },
-plus the star  ?s p1 ?x . ?s p2 ?y  that needs no exchange.  Quads live on rank mix32(subject) mod g; a solution table is
+plus the star  ?s p1 ?x . ?s p2 ?y  that needs no exchange.  Quads live on rank subject mod g (layout "subject"); a solution table is
 shuffled on the next join variable, the other side is a local scan that is already partitioned on it.
 Rank 0 gathers every rank's rows and compares the multiset with the single-store oracle.
 """
@@ -61,9 +61,11 @@ def main():
             ctx.set_option(F.OPT_SHUFFLE_P2P, 0)
         init_comm(ctx)
         if layout == "subject":
-            store = ctx.store().load_quads(mine)
+            store = ctx.store().set_placement("subject", world, rank).load_quads(mine)
         else:  # one shard per permutation, sorted and de-duplicated on the device
             store = ctx.store().set_sharded()
+            if layout == "hash":
+                store.set_placement("hash", world, rank)
             for pm in perms:
                 store.build(shard(pm), (pm,))
         paths = set()

@@ -97,6 +97,11 @@ void emu_ctx_destroy(rfgpu_ctx* c) {
 void emu_set_sort_agg(rfgpu_ctx* c, int32_t on) { c->opt_sort_agg = on != 0; }
 void emu_table_set_nullable(rfgpu_table* t, int32_t col, int32_t nullable) { t->cols[col].nullable = nullable != 0; }
 void emu_table_set_name(rfgpu_table* t, int32_t col, const char* name) { t->cols[col].name = name; }
+void emu_table_set_mod(rfgpu_table* t, int32_t col, uint32_t g, uint32_t r) {  // what a shuffle / sharded scan declares
+  t->cols[col].mod_g = g;
+  t->cols[col].mod_r = r;
+}
+uint32_t emu_table_mod_g(const rfgpu_table* t, int32_t col) { return t->cols[col].mod_g; }
 const char* emu_table_name(const rfgpu_table* t, int32_t col) { return t->cols[col].name.c_str(); }
 int32_t emu_table_nullable(const rfgpu_table* t, int32_t col) { return t->cols[col].nullable; }
 uint64_t emu_kernel_launches(rfgpu_ctx* c, const char* name) {

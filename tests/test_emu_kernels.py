@@ -47,6 +47,7 @@ def emu():
         "emu_set_sort_agg": (None, [vp, C.c_int32]), "emu_table_set_nullable": (None, [vp, C.c_int32, C.c_int32]),
         "emu_table_set_name": (None, [vp, C.c_int32, C.c_char_p]), "emu_table_name": (C.c_char_p, [vp, C.c_int32]),
         "emu_table_nullable": (C.c_int32, [vp, C.c_int32]),
+        "emu_table_set_mod": (None, [vp, C.c_int32, C.c_uint32, C.c_uint32]), "emu_table_mod_g": (C.c_uint32, [vp, C.c_int32]),
     }
     for name in ("rfgpu_table_sort", "rfgpu_store_build", "rfgpu_dict_create", "rfgpu_dict_release", "rfgpu_dict_decode",
                  "rfgpu_plain_terms_release", "rfgpu_plain_terms_sizes", "rfgpu_plain_terms_export", "rfgpu_table_lookup",
@@ -457,6 +458,37 @@ def test_lookup_join_dense_keys(emu, oracle, jt):
                 emu.emu_table_release(R)
             finally:
                 _ok(emu, emu.rfgpu_ctx_set_option(emu.ctx, F.OPT_LOOKUP_JOIN, 1))
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_lookup_join_strided_keys(emu, oracle, jt):
+    """the build keys lie in one residue class mod g (the key column of a shuffle result, the placement column of a sharded
+    scan): table slot = (key - min) / g.  Probe keys of other classes, below the minimum and beyond the maximum find nothing;
+    the output's key column keeps the class tag."""
+    rng = np.random.default_rng(5 + jt)
+    for g, r, nl_, nr_, hi in some([(2, 1, 900, 700, 300), (8, 3, 3000, 2500, 4000), (3, 0, 2500, 1200, 90), (8, 7, 40, 30, 5)],
+                                   [(8, 3, 2300, 1500, 1500), (3, 0, 1200, 900, 60)]):
+        ln, rn = ["a", "k"], ["k", "z"]
+        rk = (rng.integers(5, hi + 5, nr_) * g + r).astype(np.uint32)           # all in class r, none below 5 g
+        lk = np.where(rng.random(nl_) < 0.7, rng.integers(0, hi + 12, nl_) * g + r,  # same class, some out of range
+                      rng.integers(1, (hi + 12) * g, nl_)).astype(np.uint32)     # any class
+        lc, rc = [rng.integers(1, 1000, nl_).astype(np.uint32), lk], [rk, rng.integers(1, 1000, nr_).astype(np.uint32)]
+        exp = oracle.sparql_join(oracle.OTable(ln, [False] * 2, lc), oracle.OTable(rn, [False] * 2, rc), jt, "hash")[0]
+        b = oracle.canonical_rows(exp.cols)
+        ro = np.argsort(rc[0], kind="stable")
+        for r_sorted in (False, True):
+            L = _named(emu, ln, [False] * 2, lc)
+            R = (_named(emu, rn, [False] * 2, [c[ro] for c in rc], sorted_col=0) if r_sorted else _named(emu, rn, [False] * 2, rc))
+            emu.emu_table_set_mod(R, 0, g, r)
+            out = vp()
+            _ok(emu, emu.rfgpu_sparql_join(emu.ctx, L, R, jt, C.byref(out)))
+            assert emu.rfgpu_last_join_phys(emu.ctx) == F.PHYS_LOOKUP
+            assert emu.emu_table_mod_g(out, 1) == 1 and emu.emu_table_mod_g(out, 2) == 1  # lhs ?k is untagged, ?z too
+            names, _, cols = _take(emu, out)
+            a = oracle.canonical_rows(cols)
+            assert names == exp.names and a.shape == b.shape and np.array_equal(a, b), (g, r, nl_, nr_, hi, r_sorted)
+            emu.emu_table_release(L)
+            emu.emu_table_release(R)
 
 
 @pytest.mark.parametrize("sort_semi", [0, 1])

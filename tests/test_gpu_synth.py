@@ -56,3 +56,42 @@ def test_store_from_device_generator_equals_numpy_load(ctx, oracle):
         assert got.num_rows == exp._rows
         for a, b in zip(got.to_numpy(), exp.cols):
             assert np.array_equal(a, b)
+
+
+def test_declared_placement_is_verified_and_joins_use_the_residue_class(ctx, oracle):
+    """one rank's shard under the "hash" layout on a single GPU: the placement is verified on upload, a chain step joins
+    through the strided direct-address table, and the result equals the oracle's join of the same shard's scans"""
+    from rdf_fusion_b200.api import RfgpuError
+    n, P, world, rank = 400000, 8, 4, 1
+    g = rf.generate_graph(n, P, 1.1, 4)
+    cols = (g.g, g.s, g.p, g.o)
+    st = ctx.store().set_sharded().set_placement("hash", world, rank)
+    shards = {}
+    for pm in (F.GPOS, F.GPSO):
+        shards[pm] = np.stack(shard_quads_np(cols, pm, rank, world, "hash"), axis=1)
+        st.build(shards[pm], (pm,))
+    p1, p2 = g.pred_id(1), g.pred_id(2)
+    pa = st.plan([rf.traverse(0), rf.scan("a"), rf.traverse(p1), rf.scan("b")])
+    pb = st.plan([rf.traverse(0), rf.scan("b"), rf.traverse(p2), rf.scan("c")])
+    assert pb.order_by("b")
+    assert F.PERM_NAMES[pa.index] == "GPOS" and F.PERM_NAMES[pb.index] == "GPSO"
+    ta, tb = pa.execute(allow_view=True), pb.execute(allow_view=True)
+    kb = tb.to_numpy()[0]
+    assert np.all(kb % world == rank) and np.all(ta.to_numpy()[1] % world == rank)
+    ctx.set_option(F.OPT_MERGE_JOIN, 0)  # both sides are sorted on ?b: force the build / probe join
+    try:
+        tj = ta.join(tb)
+        assert tj.last_join_phys == F.PHYS_LOOKUP
+    finally:
+        ctx.set_option(F.OPT_MERGE_JOIN, 1)
+    oa = oracle.OracleStore(8192).load_quads(shards[F.GPOS]).plan(
+        [rf.traverse(0), rf.scan("a"), rf.traverse(p1), rf.scan("b")]).execute()
+    ob = oracle.OracleStore(8192).load_quads(shards[F.GPSO]).plan(
+        [rf.traverse(0), rf.scan("b"), rf.traverse(p2), rf.scan("c")]).execute()
+    exp = oracle.sparql_join(oa, ob, F.JOIN_INNER, "hash")[0]
+    assert tj.num_rows == exp._rows > 0
+    assert np.array_equal(oracle.canonical_rows(tj.to_numpy()), oracle.canonical_rows(exp.cols))
+    # quads of another rank are refused
+    bad = ctx.store().set_sharded().set_placement("hash", world, rank)
+    with pytest.raises(RfgpuError):
+        bad.build(np.stack(shard_quads_np(cols, F.GPOS, (rank + 1) % world, world, "hash"), axis=1), (F.GPOS,))
