@@ -133,6 +133,28 @@ uint32_t rfgpu_store_index_perm(const rfgpu_store* s, int32_t i);
  * The permutation is picked by IndexPermutations::choose_index (permutations.rs:81-96). */
 int32_t rfgpu_scan_plan_create(rfgpu_ctx* ctx, rfgpu_store* s,
                                const rfgpu_scan_instruction gspo[4], rfgpu_scan_plan** out);
+/* Pattern -> plan, the whole of MemQuadStorageSnapshot::plan_pattern_evaluation (snapshot.rs:84-131) after the dictionary
+ * look-ups, so that a binder does not re-derive it: level G from the active graph (MemIndexScanInstruction::from_active_graph,
+ * scan_instructions.rs:323-355: Default -> In{0}, AllGraphs -> no predicate, Union -> In{ids}, AnyNamed -> Between(1, MAX);
+ * Scan(graph_variable) when the graph name is bound to a variable, else Traverse), levels S, P, O from the encoded term
+ * patterns (From<EncodedTermPattern>, :358-369).  A constant the dictionary does not know (RFGPU_TERM_UNKNOWN), or a union in
+ * which no graph could be encoded (n_graphs = 0), makes the pattern provably empty: *is_empty = 1 — the reference returns
+ * PlanPatternScanResult::Empty -> EmptyExec (snapshot.rs:101-110) — and the returned plan yields no rows with the right schema. */
+typedef enum { RFGPU_GRAPH_DEFAULT = 0, RFGPU_GRAPH_ALL = 1, RFGPU_GRAPH_UNION = 2, RFGPU_GRAPH_ANY_NAMED = 3 } rfgpu_graph_kind;
+typedef struct {
+  int32_t kind;            /* rfgpu_graph_kind */
+  const uint32_t* graphs;  /* UNION: the encoded graph ids (0 = default graph) */
+  uint32_t n_graphs;
+} rfgpu_active_graph;
+typedef enum { RFGPU_TERM_VARIABLE = 0, RFGPU_TERM_ID = 1, RFGPU_TERM_UNKNOWN = 2 } rfgpu_term_kind;
+typedef struct {
+  int32_t kind;     /* rfgpu_term_kind */
+  const char* var;  /* VARIABLE (blank nodes of a query are variables: BlankNodeMatchingMode::Variable) */
+  uint32_t id;      /* ID */
+} rfgpu_term_pattern;
+int32_t rfgpu_scan_plan_create_pattern(rfgpu_ctx* ctx, rfgpu_store* s, const rfgpu_active_graph* graph,
+                                       const char* graph_variable, const rfgpu_term_pattern spo[3], rfgpu_scan_plan** out,
+                                       int32_t* is_empty);
 void rfgpu_scan_plan_destroy(rfgpu_scan_plan* p);
 /* PlannedPatternScan::apply_filter (scan.rs:469-480) for `column <op> value`; re-chooses the
  * index afterwards (try_find_better_index, scan.rs:483-486). */

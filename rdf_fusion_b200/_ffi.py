@@ -62,6 +62,18 @@ class ScanInstruction(C.Structure):
     _fields_ = [("action", C.c_int32), ("var", C.c_char_p), ("pred", ScanPred)]
 
 
+class ActiveGraph(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("graphs", u32p), ("n_graphs", C.c_uint32)]
+
+
+class TermPattern(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("var", C.c_char_p), ("id", C.c_uint32)]
+
+
+GRAPH_DEFAULT, GRAPH_ALL, GRAPH_UNION, GRAPH_ANY_NAMED = 0, 1, 2, 3
+TERM_VARIABLE, TERM_ID, TERM_UNKNOWN = 0, 1, 2
+
+
 class FilterPred(C.Structure):
     _fields_ = [("op", C.c_int32), ("col", C.c_int32), ("col2", C.c_int32), ("value", C.c_uint32), ("hi", C.c_uint32),
                 ("ids", u32p), ("n_ids", C.c_uint32)]
@@ -104,6 +116,8 @@ SIGNATURES = {
     "rfgpu_synth_quads": (C.c_int32, [C.c_void_p, C.POINTER(SynthDesc), C.POINTER(C.c_void_p)]),
     "rfgpu_store_index_perm": (C.c_uint32, [C.c_void_p, C.c_int32]),
     "rfgpu_scan_plan_create": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(ScanInstruction), C.POINTER(C.c_void_p)]),
+    "rfgpu_scan_plan_create_pattern": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(ActiveGraph), C.c_char_p,
+                                                   C.POINTER(TermPattern), C.POINTER(C.c_void_p), C.POINTER(C.c_int32)]),
     "rfgpu_scan_plan_destroy": (None, [C.c_void_p]),
     "rfgpu_scan_plan_apply_filter": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32, C.c_uint32]),
     "rfgpu_scan_plan_apply_between": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_char_p, C.c_uint32, C.c_uint32]),

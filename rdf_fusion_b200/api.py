@@ -355,6 +355,33 @@ class Store:
         return [int(self.ctx.lib.rfgpu_store_index_perm(self.h, i))
                 for i in range(self.ctx.lib.rfgpu_store_num_indexes(self.h))]
 
+    def plan_pattern(self, graph, graph_variable: Optional[str], s, p, o) -> "ScanPlan":
+        """MemQuadStorageSnapshot::plan_pattern_evaluation through rfgpu_scan_plan_create_pattern.  graph: "default" | "all" |
+        "named" | a list of encoded graph ids (a union; [] = no graph could be encoded).  s / p / o: str = variable, int = object
+        id, None = a constant the dictionary does not know.  -> ScanPlan with .is_empty (the reference plans EmptyExec then)."""
+        g = F.ActiveGraph()
+        keep = None
+        if isinstance(graph, str):
+            g.kind = {"default": F.GRAPH_DEFAULT, "all": F.GRAPH_ALL, "named": F.GRAPH_ANY_NAMED}[graph]
+        else:
+            g.kind = F.GRAPH_UNION
+            keep = (C.c_uint32 * max(1, len(graph)))(*graph)
+            g.graphs, g.n_graphs = C.cast(keep, F.u32p), len(graph)
+        spo = (F.TermPattern * 3)()
+        for k, t in enumerate((s, p, o)):
+            if isinstance(t, str):
+                spo[k].kind, spo[k].var = F.TERM_VARIABLE, t.encode()
+            elif t is None:
+                spo[k].kind = F.TERM_UNKNOWN
+            else:
+                spo[k].kind, spo[k].id = F.TERM_ID, int(t)
+        h, empty = C.c_void_p(), C.c_int32()
+        self.ctx.check(self.ctx.lib.rfgpu_scan_plan_create_pattern(
+            self.ctx.h, self.h, C.byref(g), graph_variable.encode() if graph_variable else None, spo, C.byref(h), C.byref(empty)))
+        plan = ScanPlan.__new__(ScanPlan)
+        plan.store, plan.ctx, plan.h, plan.is_empty = self, self.ctx, h, bool(empty.value)
+        return plan
+
     def plan(self, gspo: Sequence[Instr]) -> "ScanPlan":
         return ScanPlan(self, gspo)
 
@@ -369,6 +396,7 @@ class ScanPlan:
         h = C.c_void_p()
         self.ctx.check(self.ctx.lib.rfgpu_scan_plan_create(self.ctx.h, store.h, arr, C.byref(h)))
         self.h = h
+        self.is_empty = False
 
     def __del__(self):
         try:

@@ -234,6 +234,70 @@ int32_t rfgpu_scan_plan_create(rfgpu_ctx* ctx, rfgpu_store* s, const rfgpu_scan_
   RF_API_END(ctx)
 }
 
+// MemQuadStorageSnapshot::plan_pattern_evaluation (snapshot.rs:84-131): active graph + triple pattern -> instructions.
+int32_t rfgpu_scan_plan_create_pattern(rfgpu_ctx* ctx, rfgpu_store* s, const rfgpu_active_graph* graph,
+                                       const char* graph_variable, const rfgpu_term_pattern spo[3], rfgpu_scan_plan** out,
+                                       int32_t* is_empty) {
+  RF_API_BEGIN
+  RF_REQUIRE(s && graph && spo && out && is_empty, RFGPU_E_INVALID, "NULL argument");
+  rfgpu_scan_instruction ins[4] = {};
+  bool empty = false;
+  // level G: MemIndexScanInstruction::from_active_graph (scan_instructions.rs:323-355)
+  ins[0].action = graph_variable ? RFGPU_SCAN : RFGPU_TRAVERSE;
+  ins[0].var = graph_variable;
+  const uint32_t zero = 0;  // DEFAULT_GRAPH_ID
+  switch (graph->kind) {
+    case RFGPU_GRAPH_DEFAULT:
+      ins[0].pred.kind = RFGPU_PRED_IN;
+      ins[0].pred.ids = &zero;
+      ins[0].pred.n_ids = 1;
+      break;
+    case RFGPU_GRAPH_ALL: ins[0].pred.kind = RFGPU_PRED_NONE; break;
+    case RFGPU_GRAPH_UNION:
+      RF_REQUIRE(graph->graphs || graph->n_graphs == 0, RFGPU_E_INVALID, "union of graphs without ids");
+      // encode_active_graph fails only "if no graph can be decoded" (snapshot.rs:101-104): nothing can match
+      if (graph->n_graphs == 0) empty = true;
+      ins[0].pred.kind = RFGPU_PRED_IN;
+      ins[0].pred.ids = graph->graphs;
+      ins[0].pred.n_ids = graph->n_graphs;
+      break;
+    case RFGPU_GRAPH_ANY_NAMED:
+      ins[0].pred.kind = RFGPU_PRED_BETWEEN;
+      ins[0].pred.lo = 1;  // DEFAULT_GRAPH_ID.next()
+      ins[0].pred.hi = 0xFFFFFFFFu;
+      break;
+    default: throw rf::Error(RFGPU_E_INVALID, "bad active graph kind");
+  }
+  // levels S, P, O: From<EncodedTermPattern> (:358-369); an unknown constant makes the whole scan empty (snapshot.rs:106-110)
+  for (int k = 0; k < 3; k++) {
+    rfgpu_scan_instruction& in = ins[k + 1];
+    switch (spo[k].kind) {
+      case RFGPU_TERM_VARIABLE:
+        RF_REQUIRE(spo[k].var, RFGPU_E_INVALID, "variable without a name");
+        in.action = RFGPU_SCAN;
+        in.var = spo[k].var;
+        break;
+      case RFGPU_TERM_ID:
+        in.action = RFGPU_TRAVERSE;
+        in.pred.kind = RFGPU_PRED_IN;
+        in.pred.ids = &spo[k].id;
+        in.pred.n_ids = 1;
+        break;
+      case RFGPU_TERM_UNKNOWN:
+        in.action = RFGPU_TRAVERSE;
+        in.pred.kind = RFGPU_PRED_FALSE;
+        empty = true;
+        break;
+      default: throw rf::Error(RFGPU_E_INVALID, "bad term pattern kind");
+    }
+  }
+  if (empty && graph->kind == RFGPU_GRAPH_UNION && graph->n_graphs == 0) ins[0].pred.kind = RFGPU_PRED_FALSE;
+  *is_empty = empty ? 1 : 0;
+  int32_t rc = rfgpu_scan_plan_create(ctx, s, ins, out);
+  if (rc != RFGPU_OK) return rc;
+  RF_API_END(ctx)
+}
+
 void rfgpu_scan_plan_destroy(rfgpu_scan_plan* p) {
   if (!p) return;
   rfgpu_store_release(p->store);

@@ -176,6 +176,22 @@ class GpuBackend:
     def scan(self, instr):
         return self._out(self.store.plan(instr).execute())
 
+    def scan_pattern(self, comps):
+        """the product's own pattern -> instructions lowering (rfgpu_scan_plan_create_pattern): active graph mapping and the
+        unknown-constant => empty rule live behind the C ABI, not in this file"""
+        g = comps[0]
+        if g == "default":
+            graph, gvar = "default", None
+        elif "var" in g:
+            graph, gvar = "named", g["var"]          # GRAPH ?g ranges over the named graphs
+        else:
+            graph, gvar = ([] if g["id"] is None else [int(g["id"])]), None  # GRAPH <iri>
+        terms = [c["var"] if "var" in c else c["id"] for c in comps[1:]]
+        plan = self.store.plan_pattern(graph, gvar, *terms)
+        out = self._out(plan.execute())
+        assert not plan.is_empty or len(out[2][0] if out[2] else []) == 0
+        return out
+
     def make(self, names, nullable, cols):
         return self.ctx.import_table(dict(zip(names, cols)), dict(zip(names, nullable)))
 
@@ -229,6 +245,8 @@ def eval_plan(be, node):
     op = node["op"]
     if op == "scan":
         comps = [node["g"], node["s"], node["p"], node["o"]]
+        if hasattr(be, "scan_pattern"):  # the CUDA path lowers the pattern itself
+            return be.scan_pattern(comps)
         instr, names = [], []
         unknown = False
         for k, c in enumerate(comps):

@@ -182,3 +182,55 @@ def test_pack_terms_layout():
     assert dt.tolist() == [0, 0, 1, 2, 1, 0] and lg.tolist() == [0, 0, 0, 3, 0, 0]
     strings = [bytes(ab[ao[i]:ao[i + 1]]).decode() for i in range(1, len(ao) - 1)]
     assert strings == [xs, "http://www.w3.org/1999/02/22-rdf-syntax-ns#langString", "fr"]
+
+
+def _pattern_plan(st, graph, gvar, s, p, o):
+    g = F.ActiveGraph()
+    keep = None
+    if isinstance(graph, str):
+        g.kind = {"default": F.GRAPH_DEFAULT, "all": F.GRAPH_ALL, "named": F.GRAPH_ANY_NAMED}[graph]
+    else:
+        g.kind = F.GRAPH_UNION
+        keep = (C.c_uint32 * max(1, len(graph)))(*graph)
+        g.graphs, g.n_graphs = C.cast(keep, F.u32p), len(graph)
+    spo = (F.TermPattern * 3)()
+    for k, t in enumerate((s, p, o)):
+        if isinstance(t, str):
+            spo[k].kind, spo[k].var = F.TERM_VARIABLE, t.encode()
+        elif t is None:
+            spo[k].kind = F.TERM_UNKNOWN
+        else:
+            spo[k].kind, spo[k].id = F.TERM_ID, t
+    h, empty = C.c_void_p(), C.c_int32()
+    rc = st.lib.rfgpu_scan_plan_create_pattern(None, st.h, C.byref(g), gvar.encode() if gvar else None, spo, C.byref(h),
+                                               C.byref(empty))
+    assert rc == 0, st.lib.rfgpu_last_error(None)
+    return HostPlan(st.lib, h), bool(empty.value)
+
+
+def test_pattern_lowering_matches_from_active_graph_and_the_empty_rule():
+    """rfgpu_scan_plan_create_pattern = MemIndexScanInstruction::from_active_graph (scan_instructions.rs:323-355) + From<
+    EncodedTermPattern> (:358-369) + the unknown-constant rule of plan_pattern_evaluation (snapshot.rs:98-110): the plan
+    equals the one built from hand-written instructions, for every active graph kind."""
+    st = HostStore([F.GSPO, F.GPOS, F.GOSP])
+    MAX = 0xFFFFFFFF
+    cases = [
+        (("default", None, "s", 7, "o"), [rf.traverse(rf.In(0)), rf.scan("s"), rf.traverse(rf.In(7)), rf.scan("o")]),
+        (("all", None, "s", "p", 9), [rf.traverse(), rf.scan("s"), rf.scan("p"), rf.traverse(rf.In(9))]),
+        (("all", "g", 4, "p", "o"), [rf.scan("g"), rf.traverse(rf.In(4)), rf.scan("p"), rf.scan("o")]),
+        (("named", "g", "s", 7, "o"), [rf.scan("g", rf.Between(1, MAX)), rf.scan("s"), rf.traverse(rf.In(7)), rf.scan("o")]),
+        (("named", None, "s", 7, "o"), [rf.traverse(rf.Between(1, MAX)), rf.scan("s"), rf.traverse(rf.In(7)), rf.scan("o")]),
+        (([3, 5], None, "s", 7, "o"), [rf.traverse(rf.In(3, 5)), rf.scan("s"), rf.traverse(rf.In(7)), rf.scan("o")]),
+        (([0, 5], "g", "x", "p", "x"), [rf.scan("g", rf.In(0, 5)), rf.scan("x"), rf.scan("p"), rf.scan("x")]),  # repeated variable
+    ]
+    for args, instr in cases:
+        got, empty = _pattern_plan(st, *args)
+        want = st.plan(instr)
+        assert not empty
+        assert got.index == want.index and got.describe() == want.describe(), (args, got.describe(), want.describe())
+    # a constant that is not in the dictionary, or a union in which no graph could be encoded: provably empty
+    for args in (("default", None, "s", None, "o"), ("all", "g", None, "p", "o"), ([], None, "s", 7, "o")):
+        plan, empty = _pattern_plan(st, *args)
+        assert empty
+        if args[0] != []:  # the display string does not print the graph level of a plan without a graph variable
+            assert "false" in plan.describe().lower(), plan.describe()
