@@ -617,6 +617,26 @@ std::vector<BufRef> split_class(rfgpu_ctx* ctx, const rfgpu_table* t, const std:
 
 }  // namespace
 
+rfgpu_table* sparql_join_filter(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table* R, int join_type,
+                                const rfgpu_filter_pred* preds, int n_preds);
+enum class SemiMode { kMinus, kExists, kNotExists };
+rfgpu_table* semi_anti_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table* R, SemiMode mode);
+
+static const char* kHiddenKey = "\x02k";  // prefix of rhs key columns that ride along as payload (not a SPARQL variable name)
+
+// `t` without the columns whose name starts with kHiddenKey / equals `drop` (columns are shared, not copied)
+static rfgpu_table* drop_hidden(const rfgpu_table* t, const char* drop = nullptr) {
+  std::unique_ptr<rfgpu_table> o(new_table());
+  o->rows = t->rows;
+  for (size_t c = 0; c < t->cols.size(); c++) {
+    const std::string& n = t->cols[c].name;
+    if (n.rfind(kHiddenKey, 0) == 0 || (drop && n == drop)) continue;
+    if ((int)c == t->sorted_col) o->sorted_col = (int)o->cols.size();
+    o->cols.push_back(t->cols[c]);
+  }
+  return o.release();
+}
+
 rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table* R, int join_type) {
   RF_REQUIRE(join_type == RFGPU_JOIN_INNER || join_type == RFGPU_JOIN_LEFT, RFGPU_E_INVALID, "bad join type");
   const bool left = join_type == RFGPU_JOIN_LEFT;
@@ -708,7 +728,38 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
   }
 
   if (algo == RFGPU_JOIN_ALGO_EQUI) {
-    RF_REQUIRE(keys.size() <= 2, RFGPU_E_UNSUPPORTED, "equi join on more than 2 shared variables");
+    if (keys.size() > 2) {
+      // The reference joins on every shared column (join/rewrite.rs:126-168).  Here the table key is the first two; the other
+      // rhs key columns ride along under hidden names and are compared by the join filter — `l.k = r.k` is part of the join
+      // condition, so an OPTIONAL keeps an lhs row whose every two-key partner fails on the third (sparql_join_filter).
+      std::unique_ptr<rfgpu_table> Rh(new_table());
+      Rh->cols = R->cols;
+      Rh->rows = R->rows;
+      Rh->sorted_col = R->sorted_col;
+      std::vector<int> rest_l, rest_r;
+      for (size_t k = 2; k < keys.size(); k++) {
+        Rh->cols[keys[k].r].name = kHiddenKey + std::to_string(k);
+        rest_l.push_back(keys[k].l);
+        rest_r.push_back(keys[k].r);
+      }
+      // output schema of the two-key join: lhs columns, then the rhs columns that are not one of its two keys, in rhs order
+      std::vector<rfgpu_filter_pred> ps;
+      for (size_t x = 0; x < rest_r.size(); x++) {
+        int pos = (int)nl;
+        for (int j = 0; j < rest_r[x]; j++) pos += (j != keys[0].r && j != keys[1].r);
+        rfgpu_filter_pred p{};
+        p.op = RFGPU_F_EQ_COL;
+        p.col = rest_l[x];
+        p.col2 = pos;
+        ps.push_back(p);
+      }
+      std::unique_ptr<rfgpu_table> J(sparql_join_filter(ctx, L, Rh.get(), join_type, ps.data(), (int)ps.size()));
+      rfgpu_table* out = drop_hidden(J.get());
+      RF_REQUIRE(out->cols.size() == nout, RFGPU_E_EXEC, "multi-key join schema mismatch");
+      for (size_t c = 0; c < nout; c++) out->cols[c].nullable = T->cols[c].nullable;
+      ctx->last_join_algo = RFGPU_JOIN_ALGO_EQUI;
+      return out;
+    }
     // Left: lhs must be the preserved (probe) side.  Inner: build on the smaller input (JoinSelection does the same
     // from statistics; the multiset does not depend on it).
     bool probe_is_l = left || L->rows >= R->rows;
@@ -942,8 +993,6 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
 // find a partner are flagged.  A class pair with NO variable bound on both sides is compatible row for row: it flags the
 // whole lhs class for EXISTS and nothing for MINUS.  The result is the order-preserving compaction (kernel 2) of the
 // flagged (EXISTS) or unflagged (MINUS, NOT EXISTS) lhs rows.
-enum class SemiMode { kMinus, kExists, kNotExists };
-
 rfgpu_table* semi_anti_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table* R, SemiMode mode) {
   std::vector<std::pair<std::string, KeyPair>> shared;
   for (size_t i = 0; i < L->cols.size(); i++) {
@@ -1014,8 +1063,28 @@ rfgpu_table* semi_anti_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_ta
       list = sorted[0]->as<uint32_t>();
     }
     sorted_contains(ctx, list, R->rows, L->cols[lk[0]].data, L->rows, flag->as<uint32_t>());
+  } else if (!any_nullable && nk > 2) {
+    // more than two shared variables: the partners are found by the (multi-key) inner join of the numbered lhs rows with
+    // the rhs keys; an lhs row has a partner iff its number survives
+    static const char* kRid = "\x01rid";
+    std::unique_ptr<rfgpu_table> Lr(new_table()), Rk(new_table());
+    Lr->rows = L->rows;
+    Rk->rows = R->rows;
+    for (size_t k = 0; k < nk; k++) {
+      Lr->cols.push_back(L->cols[lk[k]]);
+      Rk->cols.push_back(R->cols[rk[k]]);
+    }
+    Column rid;
+    rid.name = kRid;
+    rid.owner = hidden;
+    rid.data = hidden->as<uint32_t>();
+    Lr->cols.push_back(rid);
+    std::unique_ptr<rfgpu_table> J(sparql_join(ctx, Lr.get(), Rk.get(), RFGPU_JOIN_INNER));
+    ctx->last_join_algo = RFGPU_JOIN_ALGO_EQUI;
+    ctx->last_join_phys = RFGPU_JOIN_PHYS_HASH;
+    const int rc_ = find_col(J.get(), kRid);
+    if (J->rows) mark(nullptr, J->rows, J->cols[rc_].data);
   } else if (!any_nullable) {  // one class on each side: a plain semi / anti join on all shared variables
-    RF_REQUIRE(nk <= 2, RFGPU_E_UNSUPPORTED, "MINUS / EXISTS on more than 2 shared non-nullable variables");
     ProbeResult P = hash_probe(ctx, (int)nk, R->cols[rk[0]].data, nk > 1 ? R->cols[rk[1]].data : nullptr, R->rows,
                                L->cols[lk[0]].data, nk > 1 ? L->cols[lk[1]].data : nullptr, L->rows, false);
     if (P.n_entries) mark(P.m_row->as<uint32_t>(), P.n_entries, hidden->as<uint32_t>());
@@ -1084,7 +1153,6 @@ rfgpu_table* sparql_join_filter(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgp
   const bool left = join_type == RFGPU_JOIN_LEFT;
   const size_t nl = L->cols.size();
   static const char* kRid = "\x01rid";  // not a SPARQL variable name
-  RF_REQUIRE(find_col(L, kRid) < 0 && find_col(R, kRid) < 0, RFGPU_E_INVALID, "reserved column name");
   auto run_filter = [&](const rfgpu_table* t, const std::vector<rfgpu_filter_pred>& ps) {
     rfgpu_table* out = nullptr;
     int32_t rc = rfgpu_filter(ctx, t, ps.data(), (int32_t)ps.size(), &out);
@@ -1100,6 +1168,7 @@ rfgpu_table* sparql_join_filter(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgp
     return out.release();
   }
   RF_REQUIRE(nl + 1 <= (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 15 lhs columns in a filtered left join");
+  RF_REQUIRE(find_col(L, kRid) < 0 && find_col(R, kRid) < 0, RFGPU_E_INVALID, "reserved column name");
   // lhs with its row number as one more (non-nullable) column
   std::unique_ptr<rfgpu_table> Lr(new_table());
   Lr->cols = L->cols;

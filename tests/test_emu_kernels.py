@@ -338,6 +338,8 @@ JOIN_SHAPES = [
     (("a", "k"), (False, True), ("k", "z"), (True, False)),
     (("k1", "a", "k2"), (True, False, True), ("k2", "k1", "z"), (True, True, True)),
     (("a", "b"), (False, True), ("c", "d"), (False, False)),
+    (("k1", "a", "k2", "k3"), (False,) * 4, ("k3", "k2", "z", "k1"), (False,) * 4),  # three keys: two in the table, one in the filter
+    (("k4", "k1", "k2", "k3"), (False,) * 4, ("k3", "k2", "k4", "k1", "z"), (False,) * 5),
 ]
 
 
@@ -348,7 +350,7 @@ def test_sparql_join_and_join_filter(emu, oracle, shape, jt):
     composition) against the oracle; the filtered join against the SPARQL 1.1 §18.5 definition"""
     import rdf_fusion_b200 as rf
     ln, lnl, rn, rnl = shape
-    if not FULL and len(ln) == 3 and jt == F.JOIN_INNER:
+    if not FULL and len(ln) >= 3 and jt == F.JOIN_INNER:
         pytest.skip("two-key shapes run as Left joins in the default cross-section (EMU_FULL=1 runs both)")
     rng = np.random.default_rng(len(ln) * 11 + jt)
     for nl_, nr_, hi in some([(0, 9, 4), (8, 0, 4), (1, 1, 1), (40, 30, 5), (700, 300, 25)], [(0, 9, 4), (8, 0, 4), (90, 60, 7)]):
@@ -499,8 +501,11 @@ def test_minus_and_exists(emu, oracle, sort_semi):
     _ok(emu, emu.rfgpu_ctx_set_option(emu.ctx, F.OPT_SORT_SEMI, sort_semi))
     try:
         for ln, lnl, rn, rnl in [(("a", "k"), (False, False), ("k", "z"), (False, False)),
-                                 (("a", "k"), (False, True), ("k", "z"), (True, False))]:
+                                 (("a", "k"), (False, True), ("k", "z"), (True, False)),
+                                 (("k1", "a", "k2", "k3"), (False,) * 4, ("k3", "k2", "z", "k1"), (False,) * 4)][::1 if not sort_semi else 3]:
             for nl_, nr_, hi in some([(50, 1, 9), (300, 200, 25), (2000, 900, 400)], [(50, 1, 9), (600, 200, 25)]):
+                if len(ln) == 4:
+                    hi = min(hi, 6)  # three shared variables: keep the key space small enough for partners to exist
                 lc, rc = _rand_cols(rng, ln, lnl, nl_, hi), _rand_cols(rng, rn, rnl, nr_, hi)
                 L, R = _named(emu, ln, lnl, lc), _named(emu, rn, rnl, rc)
                 OL, OR = oracle.OTable(list(ln), list(lnl), lc), oracle.OTable(list(rn), list(rnl), rc)

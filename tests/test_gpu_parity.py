@@ -144,6 +144,32 @@ def test_equi_join_one_key(ctx, oracle, jt, seed):
 
 
 @pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_equi_join_three_and_four_keys(ctx, oracle, jt):
+    """the reference joins on every shared column (join/rewrite.rs:126-168): two keys in the table, the others in the join
+    filter (so an OPTIONAL keeps an lhs row whose two-key partners all fail on the third key)"""
+    rng = np.random.default_rng(17)
+    for nl, nr, ks, names_l, names_r in [(4000, 3000, 6, ["k1", "a", "k2", "k3"], ["k3", "k2", "z", "k1"]),
+                                         (60000, 50000, 14, ["k4", "k1", "k2", "k3"], ["k3", "k2", "k4", "k1", "z"]),
+                                         (0, 10, 3, ["k1", "k2", "k3"], ["k1", "k2", "k3", "z"]),
+                                         (10, 0, 3, ["k1", "k2", "k3"], ["k1", "k2", "k3", "z"])]:
+        lc = _rand_table(rng, nl, names_l, [False] * len(names_l), 0, ks)
+        rc = _rand_table(rng, nr, names_r, [False] * len(names_r), 0, ks)
+        got, algo = _check_join(ctx, oracle, lc, [False] * len(lc), rc, [False] * len(rc), jt, impl="hash")
+        assert algo == F.ALGO_EQUI
+    # MINUS / EXISTS / NOT EXISTS on three shared variables
+    lc = _rand_table(rng, 5000, ["k1", "a", "k2", "k3"], [False] * 4, 0, 6)
+    rc = _rand_table(rng, 3000, ["k3", "k2", "z", "k1"], [False] * 4, 0, 6)
+    L, R = ctx.import_table(lc), ctx.import_table(rc)
+    OL = oracle.OTable(list(lc), [False] * 4, list(lc.values()))
+    OR = oracle.OTable(list(rc), [False] * 4, list(rc.values()))
+    for got, want in ((L.minus(R), oracle.sparql_minus(OL, OR)), (L.exists(R), oracle.sparql_exists(OL, OR, False)),
+                      (L.exists(R, True), oracle.sparql_exists(OL, OR, True))):
+        assert got.num_rows == want._rows and 0 < got.num_rows < 5000
+        for g, w in zip(got.to_numpy(), want.cols):
+            assert np.array_equal(g, w)
+
+
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
 def test_equi_join_two_keys_and_wide_payload(ctx, oracle, jt):
     rng = np.random.default_rng(5)
     lc = _rand_table(rng, 1200, ["offer", "vendor", "x", "y"], [False] * 4, 0, 25)
