@@ -234,3 +234,24 @@ def test_pattern_lowering_matches_from_active_graph_and_the_empty_rule():
         assert empty
         if args[0] != []:  # the display string does not print the graph level of a plan without a graph variable
             assert "false" in plan.describe().lower(), plan.describe()
+
+
+def test_rust_ffi_declarations_cover_the_header():
+    """integration/rdf-fusion-cuda/src/ffi.rs (generated from include/rfgpu.h; uncompiled: no Rust toolchain in this image)
+    declares every function the header does, and is up to date with the generator"""
+    import importlib.util
+    ffi_rs = os.path.join(ROOT, "integration", "rdf-fusion-cuda", "src", "ffi.rs")
+    text = open(ffi_rs).read()
+    import re
+    declared = set(re.findall(r"pub fn (rfgpu_\w+)\(", text))
+    assert declared == set(_declared_symbols()), set(_declared_symbols()) ^ declared
+    spec = importlib.util.spec_from_file_location("gen_ffi", os.path.join(ROOT, "integration", "gen_ffi.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    gen.OUT = os.path.join(ROOT, "integration", "rdf-fusion-cuda", "src", ".ffi_check.rs")
+    try:
+        gen.main()
+        assert open(gen.OUT).read() == text, "run python integration/gen_ffi.py"
+    finally:
+        if os.path.exists(gen.OUT):
+            os.unlink(gen.OUT)
