@@ -43,8 +43,13 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--triples", type=int, default=125_000_000,
-                    help="triples per GPU (weak scaling); 8 GPUs x 1.25e8 = the 1e9 triples of configs[3]")
+    ap.add_argument("--triples", type=int, default=None,
+                    help="triples per GPU (weak scaling); default 1.25e8 (8 GPUs x 1.25e8 = the 1e9 triples of configs[3]), "
+                         "5e8 for --workload optional")
+    ap.add_argument("--workload", default="main", choices=["main", "optional"],
+                    help="main: the driver's step (configs[1] + configs[3]); optional: BASELINE configs[4] — FILTER + OPTIONAL + "
+                         "compatible-mapping join on a 5e8-triple graph with Zipf-1.2 predicates and objects (one GPU, per-operator "
+                         "report with a full parity check against the oracle at 1/100 of the size)")
     ap.add_argument("--predicates", type=int, default=1024)
     ap.add_argument("--zipf", type=float, default=1.0)
     ap.add_argument("--seed", type=int, default=2)
@@ -108,27 +113,27 @@ def cpu_reference(a, steps, warmup, parts):
         rows = out = 0
         if "star" in parts or "filter" in parts:
             ts = [scan("s", pid(r), "o") for r in RANKS]
-            rows += sum(t._rows for t in ts)
+            rows += sum(t.num_rows for t in ts)
             if "filter" in parts:
                 tf = orc.filter_table(ts[0], [ne])
-                rows += ts[0]._rows
-                out += tf._rows
+                rows += ts[0].num_rows
+                out += tf.num_rows
         if "star" in parts:
             ta, tb = scan("s", pid(1), "o1"), scan("s", pid(2), "o2")
             tj, _, _ = orc.sparql_join(ta, tb, F.JOIN_INNER, "hash", cores)
-            rows += 2 * (ta._rows + tb._rows)  # the two scans, then the join's inputs
-            out += tj._rows
+            rows += 2 * (ta.num_rows + tb.num_rows)  # the two scans, then the join's inputs
+            out += tj.num_rows
         if "chain" in parts:
             cur = None
             for s, p, o in chain_patterns(pid):
                 t = scan(s, p, o)
-                rows += t._rows
+                rows += t.num_rows
                 if cur is None:
                     cur = t
                 else:
-                    rows += cur._rows + t._rows
+                    rows += cur.num_rows + t.num_rows
                     cur, _, _ = orc.sparql_join(cur, t, F.JOIN_INNER, "hash", cores)
-            out += cur._rows
+            out += cur.num_rows
         return rows, out
     for _ in range(warmup):
         step()
@@ -603,8 +608,140 @@ def run_ours(a):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------ BASELINE configs[4]: FILTER + OPTIONAL, skewed keys
+def run_optional(a):
+    """SURVEY §8d cfg 5 (BASELINE configs[4]) on G(N, P=256, Zipf 1.2 predicates, Zipf 1.2 entity objects, seed 5):
+      Q5a  ?s p1 ?o OPTIONAL { ?s p2 ?v } FILTER(?o != c)            left join on ?s (both scans sorted on ?s) + ID filter
+      Q5a' ?s p1 ?o OPTIONAL { ?o p3 ?w }                            left join keyed on the Zipf-skewed OBJECT (heavy hitters)
+      Q5b  { Q5a narrowed to ~1e3 rows } . { ?v p9 ?z }, inner and OPTIONAL: ?v is nullable by schema => compatible-mapping
+           join (IS_COMPATIBLE + COALESCE, join/rewrite.rs:183-221); rows with ?v unbound pair with every rhs row
+      Q5c  Q5a's join, FILTER(!BOUND(?v)), then GROUP BY ?o COUNT(*)
+    Every operator is first checked against the oracle, full multiset, on the same plan at N / 100; then timed at N (kernel
+    time = CUDA events per kernel from the library's profile, wall = CUDA events around the call on the ctx stream)."""
+    import rdf_fusion_b200 as rf
+    from oracle import oracle_py as orc
+    from rdf_fusion_b200 import _ffi as F
+    from rdf_fusion_b200.synth import graph_shape
+    ctx = rf.Context(int(os.environ.get("LOCAL_RANK", "0")))
+    P, s, seed, s_o = 256, 1.2, 5, 1.2
+    peak = 6650.0
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        pass
+
+    def plans(n, store, execute):
+        sh = graph_shape(n, P)
+        p1, p2, p3, p9 = sh.pred_id(3), sh.pred_id(4), sh.pred_id(6), sh.pred_id(200)
+        def sc(sv, p, ov, order=None):
+            pl = store.plan([rf.traverse(0), rf.scan(sv), rf.traverse(p), rf.scan(ov)])
+            if order and hasattr(pl, "order_by"):
+                pl.order_by(order)
+            return execute(pl)
+        return sh, (sc("s", p1, "o", "s"), sc("s", p2, "v", "s"), sc("o", p3, "w", "o"), sc("v", p9, "z", "v"))
+
+    def narrow_preds(sh, n_eq):
+        frac = min(1.0 / 20, 1500.0 / max(n_eq, 1))
+        return [rf.FPred(F.F_EQ_CONST, 1, value=int(sh.subject_base)),
+                rf.FPred(F.F_BETWEEN, 0, value=int(sh.subject_base), hi=int(sh.subject_base + max(1, int(sh.n_subjects * frac))))]
+
+    # ---- parity at N / 100, full multiset against the oracle
+    n_small = max(a.triples // 100, 100_000)
+    g = rf.generate_graph(n_small, P, s, seed, s_o=s_o)
+    st_small = ctx.store().build(g.quads(), (F.GPSO, F.GPOS))
+    ost = orc.OracleStore(8192).load_quads(g.quads())
+    sh, (ga, gb, gc, gd) = plans(n_small, st_small, lambda pl: pl.execute(allow_view=True))
+    _, (oa, ob, oc, od) = plans(n_small, ost, lambda pl: pl.execute())
+    J = lambda l, r, jt: orc.sparql_join(l, r, jt, "hash", os.cpu_count() or 1)[0]
+    checked = {}
+
+    def same(name, gt, ot):
+        assert gt.names == ot.names and gt.nullable == ot.nullable, name
+        got = orc.canonical_rows(gt.to_numpy() if gt.num_rows else [np.zeros(0, np.uint32)] * len(gt.names))
+        want = orc.canonical_rows(ot.cols)
+        assert got.shape == want.shape and np.array_equal(got, want), name
+        checked[name] = int(len(want))
+    c_heavy = int(sh.subject_base)
+    g5a, o5a = ga.join(gb, F.JOIN_LEFT), J(oa, ob, F.JOIN_LEFT)
+    same("Q5a join", g5a, o5a)
+    ne = [rf.FPred(F.F_NE_CONST, 1, value=c_heavy)]
+    same("Q5a filter", g5a.filter(ne), orc.filter_table(o5a, ne))
+    same("Q5a' skewed-key OPTIONAL", ga.join(gc, F.JOIN_LEFT), J(oa, oc, F.JOIN_LEFT))
+    n_eq = g5a.filter([rf.FPred(F.F_EQ_CONST, 1, value=c_heavy)]).num_rows
+    nar = narrow_preds(sh, n_eq * 4)
+    g5n, o5n = g5a.filter(nar), orc.filter_table(o5a, nar)
+    same("Q5b narrowing filter", g5n, o5n)
+    same("Q5b compatible join (inner)", g5n.join(gd, F.JOIN_INNER), J(o5n, od, F.JOIN_INNER))
+    same("Q5b compatible join (OPTIONAL)", g5n.join(gd, F.JOIN_LEFT), J(o5n, od, F.JOIN_LEFT))
+    nb_ = [rf.FPred(F.F_IS_NULL, g5a.names.index("v"))]
+    g5c, o5c = g5a.filter(nb_), orc.filter_table(o5a, nb_)
+    same("Q5c !BOUND filter", g5c, o5c)
+    same("Q5c GROUP BY ?o COUNT(*)", g5c.group_count(["o"], None, "n"), orc.group_count(o5c, ["o"], None, "n"))
+    del st_small, ost, ga, gb, gc, gd, g5a, g5n, g5c, oa, ob, oc, od, o5a, o5n, o5c, g
+
+    # ---- timing at N
+    t0 = time.perf_counter()
+    store = ctx.store().build_from_table(ctx.synth_quads(a.triples, P, s, seed, s_o=s_o), (F.GPSO, F.GPOS))
+    ctx.synchronize()
+    setup_s = time.perf_counter() - t0
+    sh, (ta, tb, tc, td) = plans(a.triples, store, lambda pl: pl.execute(allow_view=True))
+    ops = []
+
+    def measure(name, fn, alg_bytes_of, reps=3):
+        out = fn()
+        ctx.metrics_reset()
+        ctx.profile_enable(True)
+        wall = 0.0
+        for _ in range(reps):
+            ctx.flush_l2()
+            ctx.synchronize()
+            ctx.timer_start()
+            out = fn()
+            wall += ctx.timer_stop()
+        prof = ctx.profile()
+        ctx.profile_enable(False)
+        k_ms = sum(v["ms"] for v in prof.values()) / reps
+        b = alg_bytes_of(out)
+        ops.append({"operator": name, "rows_out": out.num_rows, "alg_bytes": b, "kernel_ms": k_ms, "wall_ms": wall / reps,
+                    "alg_GBps": b / (k_ms / 1e3) / 1e9 if k_ms else None, "frac": b / (k_ms / 1e3) / 1e9 / peak if k_ms else None,
+                    "join_phys": getattr(out, "last_join_phys", None),
+                    "kernels_us": {k: round(1e3 * v["ms"] / reps, 1) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"]) if v["ms"] > 0}})
+        return out
+
+    def jb(l, r):
+        return lambda o: 4 * (len(l.names) * l.num_rows + len(r.names) * r.num_rows + len(o.names) * o.num_rows)
+
+    def fb(t, n_pred_cols=1):
+        return lambda o: 4 * (len(t.names) * t.num_rows + len(o.names) * o.num_rows)
+    c_heavy = int(sh.subject_base)
+    t5a = measure("Q5a OPTIONAL left join on ?s (sorted scans)", lambda: ta.join(tb, F.JOIN_LEFT), jb(ta, tb))
+    ne = [rf.FPred(F.F_NE_CONST, 1, value=c_heavy)]
+    measure("Q5a FILTER(?o != c)", lambda: t5a.filter(ne), fb(t5a))
+    measure("Q5a' OPTIONAL keyed on the Zipf-skewed object", lambda: ta.join(tc, F.JOIN_LEFT), jb(ta, tc))
+    n_eq = t5a.filter([rf.FPred(F.F_EQ_CONST, 1, value=c_heavy)]).num_rows
+    nar = narrow_preds(sh, n_eq)
+    t5n = measure("Q5b narrowing FILTER (= c AND subject range)", lambda: t5a.filter(nar), fb(t5a))
+    measure("Q5b compatible-mapping join, inner (NULL ?v broadcast)", lambda: t5n.join(td, F.JOIN_INNER), jb(t5n, td))
+    measure("Q5b compatible-mapping join, OPTIONAL", lambda: t5n.join(td, F.JOIN_LEFT), jb(t5n, td))
+    nb_ = [rf.FPred(F.F_IS_NULL, t5a.names.index("v"))]
+    t5c = measure("Q5c FILTER(!BOUND(?v))", lambda: t5a.filter(nb_), fb(t5a))
+    measure("Q5c GROUP BY ?o COUNT(*)", lambda: t5c.group_count(["o"], None, "n"),
+            lambda o: 4 * (t5c.num_rows + 2 * o.num_rows))
+    tot_rows = ta.num_rows + tb.num_rows + tc.num_rows + td.num_rows
+    emit({"metric": "FILTER + OPTIONAL operators, rows/s per operator", "unit": "rows/s", "n_gpus": 1, "dtype": "u32",
+          "data": "synthetic", "value": None, "vs_baseline": None, "higher_is_better": True,
+          "config": {"workload": f"configs[4]: Q5a / Q5a' / Q5b / Q5c on G(N={a.triples}, P={P}, zipf={s}, zipf_o={s_o}, seed={seed})",
+                     "scan_rows": {"?s p1 ?o": ta.num_rows, "?s p2 ?v": tb.num_rows, "?o p3 ?w": tc.num_rows, "?v p9 ?z": td.num_rows},
+                     "setup_s": round(setup_s, 1), "hbm_peak_GBps": peak,
+                     "parity": {"graph": f"the same plans on G(N={n_small})", "rule": "bit-exact multiset after canonical sort",
+                                "rows_compared": checked}},
+          "operators": ops})
+
+
 def main():
     a = parse_args()
+    if a.triples is None:
+        a.triples = 500_000_000 if a.workload == "optional" else 125_000_000
     # stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner, NCCL_DEBUG output) are
     # sent to stderr while the benchmark runs, and the line is written to the saved descriptor at the end
     global _REAL_STDOUT
@@ -613,6 +750,8 @@ def main():
     os.dup2(2, 1)
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload == "optional":
+        run_optional(a)
     else:
         run_ours(a)
 

@@ -456,8 +456,8 @@ typedef enum {
                                     unsorted side(s) and runs the merge join instead of the hash join (default 0) */
   RFGPU_OPT_SORT_SEMI = 9,       /* 1: single-key MINUS / [NOT] EXISTS without nullable shared columns searches a sorted
                                     list of the rhs keys instead of probing a hash table (default 0) */
-  RFGPU_OPT_SORT_AGG = 10,       /* 1: GROUP BY / COUNT / DISTINCT over at most 4 columns by sort + run-length encoding
-                                    (default 0) */
+  RFGPU_OPT_SORT_AGG = 10,       /* 1 (default): GROUP BY / COUNT / DISTINCT over at most 4 columns by sort + run-length
+                                    encoding; 0: representative-row hash table */
   RFGPU_OPT_LOOKUP_JOIN = 11,    /* 1 (default): single-key equi joins, MINUS / EXISTS and GROUP BY whose (build) keys span a
                                     range of at most 8 slots per input row use a direct-address table (slot = id - min id)
                                     instead of the open-addressing hash table; 0: always hash */

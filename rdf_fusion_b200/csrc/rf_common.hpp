@@ -119,7 +119,8 @@ struct rfgpu_ctx {
   // sort-based operators (sort.cu); opt-in until measured on a device
   bool opt_sort_merge_join = false;  // unsorted single-key equi joins: radix-sort the unsorted side(s), then k_merge_join
   bool opt_sort_semi = false;        // single-key MINUS / EXISTS: sorted rhs key list + one binary search per lhs row
-  bool opt_sort_agg = false;         // GROUP BY / COUNT / DISTINCT over at most 4 columns: sort + run-length encoding
+  bool opt_sort_agg = true;          // GROUP BY / COUNT / DISTINCT over at most 4 columns: sort + run-length encoding (default
+                                     // since round 2: 0.97 ms against 2.25 ms for the hash table, profiles/r2e_sort_microbench.json)
   int last_agg_phys = 0;             // rfgpu_agg_phys of the last rfgpu_group_count / rfgpu_distinct
   int last_shuffle_path = 0;
   uint64_t last_from = 0, last_to = 0;

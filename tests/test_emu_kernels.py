@@ -280,7 +280,7 @@ def test_group_count_and_distinct_entry_points(emu, oracle, sort_agg):
             assert a.shape == b.shape and np.array_equal(a, b)
             emu.emu_table_release(t)
     finally:
-        emu.emu_set_sort_agg(emu.ctx, 0)
+        emu.emu_set_sort_agg(emu.ctx, 1)  # the default
 
 
 def test_filter_entry_point(emu, oracle):

@@ -18,8 +18,8 @@ def sort_paths(ctx):
     for o in (F.OPT_SORT_MERGE_JOIN, F.OPT_SORT_SEMI, F.OPT_SORT_AGG):
         ctx.set_option(o, 1)
     yield
-    for o in (F.OPT_SORT_MERGE_JOIN, F.OPT_SORT_SEMI, F.OPT_SORT_AGG):
-        ctx.set_option(o, 0)
+    for o in (F.OPT_SORT_MERGE_JOIN, F.OPT_SORT_SEMI):
+        ctx.set_option(o, 0)  # RFGPU_OPT_SORT_AGG stays on: it is the default
 
 
 def _stable_lexsort(cols, keys):
