@@ -9,6 +9,7 @@
 // which yields exactly the pairs with  ∀k: l.k IS NULL ∨ r.k IS NULL ∨ l.k = r.k.
 #include <algorithm>
 #include <cstdlib>
+#include <mutex>
 
 #include "lookup_join.cuh"
 #include "radix_join.cuh"
@@ -130,26 +131,6 @@ DenseRange dense_range(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, bool sor
   return D;
 }
 
-// offs[0 .. range] of lookup_join.cuh for a build side SORTED on the key; positions are build row numbers
-BufRef dense_table_sorted(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, const DenseRange& D, const uint32_t** offs) {
-  const uint64_t n = (uint64_t)D.range + 1;
-  BufRef tab = ctx->alloc(n * 4);
-  RF_CUDA(cudaMemsetAsync(tab->ptr, 0xFF, n * 4, ctx->stream()));
-  {
-    KernelScope ks(ctx, "k_dense_heads", 4ull * nb);
-    k_dense_heads<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(bk, nb, D.kmin, D.stride, D.range, tab->as<uint32_t>());
-  }
-  const uint32_t tiles = div_up(n, kSmTile);
-  BufRef status = ctx->alloc((uint64_t)tiles * 8);
-  RF_CUDA(cudaMemsetAsync(status->ptr, 0, (uint64_t)tiles * 8, ctx->stream()));
-  {
-    KernelScope ks(ctx, "k_suffix_min_u32", 8ull * n);
-    k_suffix_min_u32<<<tiles, kSmThreads, 0, ctx->stream()>>>(tab->as<uint32_t>(), n, status->as<unsigned long long>());
-  }
-  *offs = tab->as<uint32_t>();
-  return tab;
-}
-
 // Counting sort of an UNSORTED build side by key: the table, and the columns `cols` (distinct build columns) rewritten in
 // key order into `sorted` (same order as cols).
 BufRef dense_table_unsorted(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, const DenseRange& D,
@@ -202,8 +183,9 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
   BufRef tab;
   std::vector<BufRef> sorted_cols;
   uint64_t in_cols_b = 0;
-  if (build_sorted) {
-    tab = dense_table_sorted(ctx, bk, nb, D, &offs);
+  const bool search = D.range == 0xFFFFFFFFu;  // sentinel set by sparql_join: sorted build side, tiny probe side, no table
+  const int mode = search ? 1 : (build_sorted ? 2 : 0);
+  if (mode != 0) {
     for (auto& sp : specs) in_cols_b += sp.build != nullptr && sp.build != bk;
   } else {
     std::vector<const uint32_t*> cols;
@@ -231,16 +213,29 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
   A.kmin = D.kmin;
   A.range = D.range;
   A.stride = D.stride;
-  // compact copy of the table (2 bytes per key): what the probe reads unless a key has more than 255 build rows
-  const uint32_t groups = (D.range + 3) / 4;
+  A.mode = mode;
+  if (mode != 0) {
+    A.bk_sorted = bk;
+    A.nb_sorted = (uint32_t)nb;
+    while ((1ull << A.search_steps) < nb + 1) A.search_steps++;
+  }
+  // the compact table (2 bytes per key) is what the probe reads: built directly from a sorted build side, or compressed from
+  // the wide table of the counting sort (which stays the fallback when a key has more than 255 build rows)
+  const uint32_t groups = search ? 0 : (D.range + 3) / 4;
   BufRef tab2 = ctx->alloc((uint64_t)groups * 8 + 16);
   uint32_t* d_over = reinterpret_cast<uint32_t*>(tab2->as<uint8_t>() + (uint64_t)groups * 8);
-  RF_CUDA(cudaMemsetAsync(d_over, 0, 16, ctx->stream()));
   A.tab2 = tab2->as<uint2>();
   A.overflow = d_over;
-  if (groups) {
-    KernelScope ks(ctx, "k_dense_compress", 6ull * D.range);
-    k_dense_compress<<<grid_for(ctx, groups, 256), 256, 0, ctx->stream()>>>(offs, D.range, tab2->as<uint2>(), d_over);
+  if (mode == 2) {
+    RF_CUDA(cudaMemsetAsync(tab2->ptr, 0, (uint64_t)groups * 8 + 16, ctx->stream()));
+    KernelScope ks(ctx, "k_dense_heads_compact", 4ull * nb + 2ull * D.range);
+    k_dense_heads_compact<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(bk, nb, D.kmin, D.stride, tab2->as<uint2>());
+  } else {
+    RF_CUDA(cudaMemsetAsync(d_over, 0, 16, ctx->stream()));
+    if (groups) {
+      KernelScope ks(ctx, "k_dense_compress", 6ull * D.range);
+      k_dense_compress<<<grid_for(ctx, groups, 256), 256, 0, ctx->stream()>>>(offs, D.range, tab2->as<uint2>(), d_over);
+    }
   }
   A.left = left ? 1 : 0;
   A.n_tiles = n_tiles;
@@ -499,10 +494,16 @@ bool radix_join_nk(rfgpu_ctx* ctx, const uint32_t* bk0, const uint32_t* bk1, uin
   BufRef cursor = ctx->alloc(16);
   A.cursor = cursor->as<unsigned long long>();
   const size_t smem = sizeof(RpSmem<NK>) + 16;
-  static bool attr_set = false;
-  if (!attr_set) {
-    RF_CUDA(cudaFuncSetAttribute(k_rp_join<NK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
+  // the attribute is per DEVICE (and per template instance): one flag per device, set under a lock
+  static std::mutex attr_mu;
+  static bool attr_set[64] = {};
+  {
+    std::lock_guard<std::mutex> g(attr_mu);
+    const int dev = ctx->core->device & 63;
+    if (!attr_set[dev]) {
+      RF_CUDA(cudaFuncSetAttribute(k_rp_join<NK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_set[dev] = true;
+    }
   }
   int per_sm = 0;
   RF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_rp_join<NK>, kRpThreads, smem));
@@ -764,14 +765,10 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
     // from statistics; the multiset does not depend on it).
     bool probe_is_l = left || L->rows >= R->rows;
     if (!left && keys.size() == 1 && ctx->opt_lookup_join) {
-      // exactly one input sorted on the key: build on it (its direct-address table needs no counting sort) unless it is
-      // much the larger side
+      // exactly one input sorted on the key: build on it — its compact direct-address table is written in one pass over the
+      // keys, and when it is much the larger side the probe rows binary-search it instead of building anything
       const bool ls = L->sorted_col == keys[0].l, rs = R->sorted_col == keys[0].r;
-      if (ls != rs) {
-        const rfgpu_table* sorted_side = ls ? L : R;
-        const rfgpu_table* other = ls ? R : L;
-        if (sorted_side->rows <= 4 * other->rows + 1024) probe_is_l = !ls;
-      }
+      if (ls != rs) probe_is_l = !ls;
     }
     const rfgpu_table* Pt = probe_is_l ? L : R;
     const rfgpu_table* Bt = probe_is_l ? R : L;
@@ -823,7 +820,15 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
     if (keys.size() == 1 && Pt->rows > 0 && Bt->rows > 0) {
       const int bkey = Bt == L ? keys[0].l : keys[0].r;
       const bool bsorted = Bt->sorted_col == bkey;
-      const DenseRange D = dense_range(ctx, kc(Bt, 0), Bt->rows, bsorted, Pt->rows, Bt->cols[bkey].mod_g);
+      // a probe side that is tiny next to a SORTED build side: two binary searches per probe row over the key column beat
+      // building any table (and need neither the key bounds nor density)
+      DenseRange D;
+      if (ctx->opt_lookup_join && bsorted && Pt->rows * 16 <= Bt->rows && Bt->rows < 0xFFFFFFFFull) {
+        D.ok = true;
+        D.range = 0xFFFFFFFFu;
+      } else {
+        D = dense_range(ctx, kc(Bt, 0), Bt->rows, bsorted, Pt->rows, Bt->cols[bkey].mod_g);
+      }
       if (D.ok) {
         std::vector<BufRef> bufs;
         const uint64_t n_out = lookup_join(ctx, kc(Pt, 0), Pt->rows, kc(Bt, 0), Bt->rows, bsorted, left, D, specs, &bufs);

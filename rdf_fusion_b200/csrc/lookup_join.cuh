@@ -15,11 +15,15 @@
 // stride = 1, or — when the build keys are known to lie in one residue class mod g (the key column of a shuffle result, the
 // placement column of a sharded scan: Column::mod_g) — stride = g, so that a rank's share of a dense id range is dense again.
 //
+// What the probe reads is the COMPACT form, 8 bytes per 4 keys {~start of the group's first key, 4 x u8 row counts}: 2 bytes
+// per key, so the 10^7-key table of BASELINE configs[1] is 20 MB and stays L2-resident next to the streamed columns.
 // Build, sorted build side (a scan in index order — every rhs of a left-deep BGP fold can be one):
-//   k_dense_heads     offs[key - kmin] = row, written once per distinct key at the head of its run
-//   k_suffix_min_u32  absent keys take the next present key's start (in-place suffix-min scan, decoupled look-back)
+//   k_dense_heads_compact   one pass over the keys writes the compact table directly (atomicMax + one byte per distinct key);
+//                           groups holding a key with >= 255 rows are resolved by binary search over the sorted keys
+//   (a probe side 16x smaller than the sorted build side skips the table altogether: two binary searches per probe row)
 // Build, unsorted build side: counting sort of the build rows by key
 //   k_dense_count (RED.ADD per row) -> exclusive scan -> k_dense_fill (cursor per key, payload columns written in key order)
+//   -> k_dense_compress (offs[] -> compact form; offs[] stays the fallback when a key has more than 255 rows)
 // Probe + expand (k_lookup_join): one pass, same output stage as the merge join — per tile of probe rows: coalesced key
 // loads, table look-ups (4 rows x 16 B in flight per thread), block scan of the match counts, decoupled look-back for the
 // tile's output offset, max-scan expansion with coalesced stores.  Output rows come out in probe order.
@@ -74,114 +78,6 @@ k_key_min_max(const uint32_t* __restrict__ k, uint64_t n, unsigned int* __restri
   }
 }
 
-// ---------------- sorted build side: run heads + suffix-min ----------------
-__global__ void __launch_bounds__(256)
-k_dense_heads(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t kstride, uint32_t range,
-              uint32_t* __restrict__ offs) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0) offs[range] = (uint32_t)nb;
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  for (; i < nb; i += stride) {
-    const uint32_t k = __ldg(bk + i);
-    if (k != 0 && (i == 0 || __ldg(bk + i - 1) != k)) offs[(k - kmin) / kstride] = (uint32_t)i;
-  }
-}
-
-constexpr int kSmThreads = 256;
-constexpr int kSmItems = 16;
-constexpr int kSmTile = kSmThreads * kSmItems;
-
-// a[i] = min(a[i], a[i+1], ..., a[n-1]) in place.  Tile b covers the b-th tile counted from the END of the array, so that
-// a tile only waits on lower-numbered blocks (status word: [63:62] flag, [31:0] value; identity = UINT32_MAX).
-__global__ void __launch_bounds__(kSmThreads)
-k_suffix_min_u32(uint32_t* __restrict__ a, uint64_t n, unsigned long long* __restrict__ status) {
-  __shared__ uint32_t s_warp[kSmThreads / 32];
-  __shared__ uint32_t s_excl;
-  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t tile = blockIdx.x;
-  // item j of this thread (j = 0 is the RIGHTMOST): index n - 1 - (tile * kSmTile + tid * kSmItems + j)
-  const uint64_t r0 = (uint64_t)tile * kSmTile + (uint64_t)tid * kSmItems;
-  uint32_t v[kSmItems];
-  // the thread's items are the 16 consecutive words ending at index n - 1 - r0: four 16-byte accesses when they are all
-  // inside the array and the run is 16-byte aligned (a is 256-byte aligned, so that is n % 4 == 0)
-  const bool vec = r0 + kSmItems <= n && (n & 3) == 0;
-  if (vec) {
-    const uint4* p = reinterpret_cast<const uint4*>(a + (n - r0 - kSmItems));
-#pragma unroll
-    for (int q = 0; q < kSmItems / 4; q++) {
-      const uint4 x = p[q];  // words n-r0-16+4q .. +3  =  items j = 15-4q, 14-4q, 13-4q, 12-4q
-      v[kSmItems - 1 - 4 * q] = x.x;
-      v[kSmItems - 2 - 4 * q] = x.y;
-      v[kSmItems - 3 - 4 * q] = x.z;
-      v[kSmItems - 4 - 4 * q] = x.w;
-    }
-  } else {
-#pragma unroll
-    for (int j = 0; j < kSmItems; j++) v[j] = r0 + j < n ? a[n - 1 - (r0 + j)] : 0xFFFFFFFFu;
-  }
-#pragma unroll
-  for (int j = 1; j < kSmItems; j++) v[j] = min(v[j], v[j - 1]);  // inclusive, right to left
-  const uint32_t tmin = v[kSmItems - 1];
-  uint32_t incl = tmin;  // inclusive over the threads to the right (lower tid)
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-    if ((int)lane >= o) incl = min(incl, t);
-  }
-  if (lane == 31) s_warp[warp] = incl;
-  uint32_t texcl = __shfl_up_sync(0xFFFFFFFFu, incl, 1);
-  if (lane == 0) texcl = 0xFFFFFFFFu;
-  __syncthreads();
-  uint32_t wexcl = 0xFFFFFFFFu, bmin = 0xFFFFFFFFu;
-#pragma unroll
-  for (int w = 0; w < kSmThreads / 32; w++) {
-    const uint32_t x = s_warp[w];
-    if (w < (int)warp) wexcl = min(wexcl, x);
-    bmin = min(bmin, x);
-  }
-  if (warp == 0) {
-    if (lane == 0) dev::st_status(status + tile, (tile == 0 ? dev::kFlagP : dev::kFlagA) | bmin);
-    uint32_t excl = 0xFFFFFFFFu;
-    if (tile != 0) {
-      int64_t look = (int64_t)tile - 1;
-      while (true) {
-        const int64_t idx = look - lane;
-        const unsigned long long s = idx >= 0 ? dev::ld_status(status + idx) : (dev::kFlagP | 0xFFFFFFFFull);
-        const uint32_t flag = (uint32_t)(s >> 62);
-        const uint32_t pmask = __ballot_sync(0xFFFFFFFFu, flag == 2);
-        const uint32_t invalid = __ballot_sync(0xFFFFFFFFu, flag == 0);
-        const int firstP = pmask ? (__ffs(pmask) - 1) : 32;
-        const uint32_t need = firstP == 32 ? 0xFFFFFFFFu : ((2u << firstP) - 1u);
-        if (invalid & need) {
-          __nanosleep(64);
-          continue;
-        }
-        uint32_t val = ((int)lane <= firstP) ? (uint32_t)(s & 0xFFFFFFFFull) : 0xFFFFFFFFu;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) val = min(val, __shfl_xor_sync(0xFFFFFFFFu, val, o));
-        excl = min(excl, val);
-        if (pmask) break;
-        look -= 32;
-      }
-      if (lane == 0) dev::st_status(status + tile, dev::kFlagP | min(excl, bmin));
-    }
-    if (lane == 0) s_excl = excl;
-  }
-  __syncthreads();
-  const uint32_t base = min(s_excl, min(wexcl, texcl));
-  if (vec) {
-    uint4* p = reinterpret_cast<uint4*>(a + (n - r0 - kSmItems));
-#pragma unroll
-    for (int q = 0; q < kSmItems / 4; q++)
-      p[q] = make_uint4(min(v[kSmItems - 1 - 4 * q], base), min(v[kSmItems - 2 - 4 * q], base),
-                        min(v[kSmItems - 3 - 4 * q], base), min(v[kSmItems - 4 - 4 * q], base));
-  } else {
-#pragma unroll
-    for (int j = 0; j < kSmItems; j++)
-      if (r0 + j < n) a[n - 1 - (r0 + j)] = min(v[j], base);
-  }
-}
-
 // ---------------- unsorted build side: counting sort by key ----------------
 __global__ void __launch_bounds__(256)
 k_dense_count(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t kstride, uint32_t* __restrict__ cnt) {
@@ -215,7 +111,45 @@ k_dense_fill(const __grid_constant__ DenseFillArgs A) {
   }
 }
 
-// ---------------- compact table: {u32 start; u8 count[4]} per 4 consecutive keys ----------------
+// ---------------- compact table built directly from a SORTED build side ----------------
+// tab2[g] = {~(start of the group's first present key), 4 x u8 row counts} for the 4 keys of group g, zero-initialised by
+// the host: the head of every key run publishes its start with one atomicMax on the complemented value (the smallest start
+// of the group wins) and stores its count byte; a run of 255 rows or more stores 255, which marks the whole group "heavy" —
+// the probe resolves keys of heavy groups by binary search over the sorted keys instead (k_lookup_join, mode 2).
+__global__ void __launch_bounds__(256)
+k_dense_heads_compact(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t kstride, uint2* __restrict__ tab2) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < nb; i += stride) {
+    const uint32_t k = __ldg(bk + i);
+    if (k == 0 || (i != 0 && __ldg(bk + i - 1) == k)) continue;
+    uint32_t cnt = 1;
+    while (cnt < 255u && i + cnt < nb && __ldg(bk + i + cnt) == k) cnt++;
+    const uint32_t slot = (k - kmin) / kstride;
+    uint2* g = tab2 + (slot >> 2);
+    atomicMax(&g->x, ~(uint32_t)i);
+    reinterpret_cast<uint8_t*>(&g->y)[slot & 3u] = (uint8_t)cnt;
+  }
+}
+
+// [first, first + count) of `key` in the ascending array bk[0 .. nb)
+__device__ __forceinline__ void sorted_group(const uint32_t* __restrict__ bk, uint32_t nb, uint32_t key, uint32_t* first,
+                                             uint32_t* count) {
+  uint32_t lo = 0, hi = nb;
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (__ldg(bk + mid) < key) lo = mid + 1; else hi = mid;
+  }
+  uint32_t lo2 = lo, hi2 = nb;
+  while (lo2 < hi2) {
+    const uint32_t mid = (lo2 + hi2) >> 1;
+    if (__ldg(bk + mid) <= key) lo2 = mid + 1; else hi2 = mid;
+  }
+  *first = lo;
+  *count = lo2 - lo;
+}
+
+// ---------------- compact table: {u32 ~start; u8 count[4]} per 4 consecutive keys ----------------
 __global__ void __launch_bounds__(256)
 k_dense_compress(const uint32_t* __restrict__ offs, uint32_t range, uint2* __restrict__ tab2, uint32_t* __restrict__ overflow) {
   const uint32_t groups = (range + 3) >> 2;
@@ -232,7 +166,7 @@ k_dense_compress(const uint32_t* __restrict__ offs, uint32_t range, uint2* __res
       over |= c > 255u;
       packed |= (c & 255u) << (8 * j);
     }
-    tab2[g] = make_uint2(o[0], packed);
+    tab2[g] = make_uint2(~o[0], packed);  // the start is stored complemented (see k_dense_heads_compact)
   }
   if (over) atomicOr(overflow, 1u);
 }
@@ -260,6 +194,13 @@ struct LookupArgs {
   // *overflow != 0: some key has more than 255 build rows and the kernel reads offs[] instead.
   const uint2* tab2;
   const uint32_t* overflow;
+  // mode 0: table from an unsorted build side (offs[] + its compact copy tab2; *overflow selects the wide one)
+  // mode 1: search — no table at all: the build keys are sorted and the probe side is tiny next to them, so each probe row
+  //         finds its group with two binary searches over the (L2-resident) key column
+  // mode 2: compact table built directly from a sorted build side (k_dense_heads_compact); heavy groups by binary search
+  int32_t mode;
+  const uint32_t* bk_sorted;
+  uint32_t nb_sorted, search_steps;  // search_steps = ceil(log2(nb + 1))
   int32_t left;  // probe side preserved (OPTIONAL): unmatched probe rows emit one padded row
   uint32_t n_tiles;
   unsigned long long* status;  // look-back words [n_tiles]
@@ -295,8 +236,46 @@ k_lookup_join(const __grid_constant__ LookupArgs A) {
   const uint64_t keep = dev::l2_policy_evict_last(), strm = dev::l2_policy_evict_first();
 
   // ---- keys (coalesced, striped) and table look-ups ----
-  const bool wide = A.tab2 == nullptr || __ldg(A.overflow) != 0;  // uniform over the grid
-  if (!wide) {  // compact table: all 8 rows of the thread in flight, 8 bytes each
+  const bool wide = A.mode == 0 && __ldg(A.overflow) != 0;  // uniform over the grid
+  if (A.mode == 1) {  // search mode: lower_bound(key) and upper_bound(key), 4 rows' searches in lockstep
+#pragma unroll 1
+    for (int h = 0; h < 2; h++) {
+      uint32_t key[4], lo[4], hi[4], lo2[4], hi2[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const uint32_t i = tid + (h * 4 + k) * kLThreads;
+        key[k] = i < rows ? dev::ld_hint_u32(A.pk + row0 + i, strm) : 0u;
+        lo[k] = lo2[k] = 0;
+        hi[k] = hi2[k] = key[k] != 0 ? A.nb_sorted : 0u;  // NULL never matches
+      }
+      for (uint32_t st = 0; st < A.search_steps; st++) {
+        uint32_t v[4], v2[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          v[k] = lo[k] < hi[k] ? dev::ld_hint_u32(A.bk_sorted + ((lo[k] + hi[k]) >> 1), keep) : 0u;
+          v2[k] = lo2[k] < hi2[k] ? dev::ld_hint_u32(A.bk_sorted + ((lo2[k] + hi2[k]) >> 1), keep) : 0u;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          if (lo[k] < hi[k]) {
+            const uint32_t mid = (lo[k] + hi[k]) >> 1;
+            if (v[k] < key[k]) lo[k] = mid + 1; else hi[k] = mid;
+          }
+          if (lo2[k] < hi2[k]) {
+            const uint32_t mid = (lo2[k] + hi2[k]) >> 1;
+            if (v2[k] <= key[k]) lo2[k] = mid + 1; else hi2[k] = mid;
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const uint32_t i = tid + (h * 4 + k) * kLThreads;
+        const uint32_t cnt = lo2[k] - lo[k];
+        S.gs[i] = cnt ? lo[k] : kNone;
+        S.off[i] = i < rows ? (cnt ? cnt : leftpad) : 0u;
+      }
+    }
+  } else if (!wide) {  // compact table: all 8 rows of the thread in flight, 8 bytes each
     uint32_t key[8];
 #pragma unroll
     for (int k = 0; k < 8; k++) {
@@ -315,8 +294,11 @@ k_lookup_join(const __grid_constant__ LookupArgs A) {
     for (int k = 0; k < 8; k++) {
       const uint32_t i = tid + k * kLThreads;
       const uint32_t sh = (slot[k] & 3u) * 8u;
-      const uint32_t cnt = (w[k].y >> sh) & 255u;
-      const uint32_t o0 = w[k].x + __dp4a(w[k].y & ((1u << sh) - 1u), 0x01010101u, 0u);  // + counts of the keys before it
+      uint32_t cnt = (w[k].y >> sh) & 255u;
+      uint32_t o0 = ~w[k].x + __dp4a(w[k].y & ((1u << sh) - 1u), 0x01010101u, 0u);  // + counts of the keys before it
+      // mode 2: a count byte of 255 anywhere in the group = "255 rows or more": exact bounds from the sorted keys
+      if (A.mode == 2 && slot[k] < A.range && ((w[k].y & 0x7F7F7F7Fu) + 0x01010101u & w[k].y & 0x80808080u) != 0)
+        sorted_group(A.bk_sorted, A.nb_sorted, key[k], &o0, &cnt);
       S.gs[i] = cnt ? o0 : kNone;
       S.off[i] = i < rows ? (cnt ? cnt : leftpad) : 0u;
     }

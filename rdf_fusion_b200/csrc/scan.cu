@@ -10,6 +10,7 @@
 //   1b. a 128-bit coalesced copy of the bound columns of [from,to) (or a zero-copy view, like the reference's Arc slices);
 //   2.  the fused predicate + compaction kernel (filter.cu) when predicates remain that pruning cannot absorb.
 #include <algorithm>
+#include <mutex>
 
 #include "rf_common.hpp"
 #include "rf_device.cuh"
@@ -391,11 +392,17 @@ static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t
       uint32_t bx = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(nvec, (uint64_t)kGatherThreads * kGatherUnroll),
                                                                       (uint64_t)ctx->core->num_sms * 8));
       if (R * 4 >= (1u << 20)) {
-        static bool attr_set = false;
+        // the attribute is per DEVICE: one flag per device, set under a lock
+        static std::mutex attr_mu;
+        static bool attr_set[64] = {};
         const int smem = kTmaChunk * kTmaStages;
-        if (!attr_set) {
-          RF_CUDA(cudaFuncSetAttribute(k_gather_range_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-          attr_set = true;
+        {
+          std::lock_guard<std::mutex> g(attr_mu);
+          const int dev = ctx->core->device & 63;
+          if (!attr_set[dev]) {
+            RF_CUDA(cudaFuncSetAttribute(k_gather_range_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            attr_set[dev] = true;
+          }
         }
         uint64_t chunks = ((R * 4 + kTmaChunk - 1) / kTmaChunk) * oc.size();
         uint32_t grid = (uint32_t)std::min<uint64_t>(chunks, (uint64_t)ctx->core->num_sms * 3);

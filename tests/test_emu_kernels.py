@@ -431,8 +431,8 @@ def test_lookup_join_dense_keys(emu, oracle, jt):
     (counting sort), the fused probe + expansion kernel over several tiles, heavy keys, keys outside the build range, and the
     same joins with the option off (open-addressing hash table)"""
     rng = np.random.default_rng(77 + jt)
-    shapes = some([(1, 1, 1, 0), (5000, 3000, 900, 100), (2600, 9000, 40, 7), (1500, 1200, 50000, 3), (9000, 20, 6, 0), (700, 2400, 4, 2)],
-                  [(2300, 1400, 500, 60), (1100, 2600, 30, 5), (700, 2400, 4, 2)])
+    shapes = some([(1, 1, 1, 0), (5000, 3000, 900, 100), (2600, 9000, 40, 7), (1500, 1200, 50000, 3), (9000, 20, 6, 0), (700, 2400, 4, 2), (40, 3000, 500, 10), (3, 9000, 100000, 1)],
+                  [(2300, 1400, 500, 60), (1100, 2600, 30, 5), (700, 2400, 4, 2), (40, 3000, 500, 10)])
     for nl_, nr_, hi, base in shapes:
         ln, rn = ["a", "k", "c"], ["k", "z"]
         lc = [rng.integers(1, 1000, nl_).astype(np.uint32), rng.integers(1, hi + 40, nl_).astype(np.uint32) + base,
@@ -452,7 +452,8 @@ def test_lookup_join_dense_keys(emu, oracle, jt):
                 _ok(emu, emu.rfgpu_sparql_join(emu.ctx, L, R, jt, C.byref(out)))
                 phys = emu.rfgpu_last_join_phys(emu.ctx)
                 dense = hi + 40 <= 8 * (nl_ + nr_) + 65536
-                assert phys == (F.PHYS_LOOKUP if lookup and dense else F.PHYS_HASH), (phys, nl_, nr_, hi)
+                search = r_sorted and nl_ * 16 <= nr_  # tiny probe side, sorted build side: binary searches, no table
+                assert phys == (F.PHYS_LOOKUP if lookup and (dense or search) else F.PHYS_HASH), (phys, nl_, nr_, hi)
                 names, _, cols = _take(emu, out)
                 a = oracle.canonical_rows(cols)
                 assert names == exp.names and a.shape == b.shape and np.array_equal(a, b), (nl_, nr_, hi, r_sorted, lookup)

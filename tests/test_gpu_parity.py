@@ -157,8 +157,8 @@ def test_equi_join_three_and_four_keys(ctx, oracle, jt):
         got, algo = _check_join(ctx, oracle, lc, [False] * len(lc), rc, [False] * len(rc), jt, impl="hash")
         assert algo == F.ALGO_EQUI
     # MINUS / EXISTS / NOT EXISTS on three shared variables
-    lc = _rand_table(rng, 5000, ["k1", "a", "k2", "k3"], [False] * 4, 0, 6)
-    rc = _rand_table(rng, 3000, ["k3", "k2", "z", "k1"], [False] * 4, 0, 6)
+    lc = _rand_table(rng, 5000, ["k1", "a", "k2", "k3"], [False] * 4, 0, 14)  # 14^3 key tuples: about a third has no partner
+    rc = _rand_table(rng, 3000, ["k3", "k2", "z", "k1"], [False] * 4, 0, 14)
     L, R = ctx.import_table(lc), ctx.import_table(rc)
     OL = oracle.OTable(list(lc), [False] * 4, list(lc.values()))
     OR = oracle.OTable(list(rc), [False] * 4, list(rc.values()))
