@@ -1057,7 +1057,27 @@ rfgpu_table* semi_anti_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_ta
     KernelScope ks(ctx, "k_mark_entries");
     k_mark_entries<<<grid_for(ctx, n), 256, 0, ctx->stream()>>>(m_row, n, hid, flag->as<uint32_t>());
   };
-  if (!any_nullable && nk == 1 && ctx->opt_sort_semi) {
+  DenseRange SD;
+  if (!any_nullable && nk == 1 && !ctx->opt_sort_semi)
+    SD = dense_range(ctx, R->cols[rk[0]].data, R->rows, R->sorted_col == rk[0], L->rows, R->cols[rk[0]].mod_g);
+  if (SD.ok) {
+    // one dense key: existence is one bit per possible key (identity hash, as in lookup_join.cuh) — mark the rhs keys,
+    // test the lhs keys; no table of keys, no row lists
+    ctx->last_join_phys = RFGPU_JOIN_PHYS_LOOKUP;
+    const uint64_t words = ((uint64_t)SD.range + 31) / 32 + 1;
+    BufRef bits = ctx->alloc(words * 4);
+    RF_CUDA(cudaMemsetAsync(bits->ptr, 0, words * 4, ctx->stream()));
+    if (SD.range) {
+      {
+        KernelScope ks(ctx, "k_dense_mark", 4ull * R->rows);
+        k_dense_mark<<<grid_for(ctx, R->rows, 256), 256, 0, ctx->stream()>>>(R->cols[rk[0]].data, R->rows, SD.kmin, SD.stride,
+                                                                              SD.range, bits->as<uint32_t>());
+      }
+      KernelScope ks(ctx, "k_dense_contains", 4ull * L->rows);
+      k_dense_contains<<<grid_for(ctx, L->rows, 256), 256, 0, ctx->stream()>>>(L->cols[lk[0]].data, L->rows, bits->as<uint32_t>(),
+                                                                                SD.kmin, SD.stride, SD.range, flag->as<uint32_t>());
+    }
+  } else if (!any_nullable && nk == 1 && ctx->opt_sort_semi) {
     // existence only: the rhs keys as one ascending list (the column itself when the rhs is sorted on it), and a
     // lower-bound search per lhs row; no table, no row lists
     ctx->last_join_phys = RFGPU_JOIN_PHYS_SORT_MERGE;

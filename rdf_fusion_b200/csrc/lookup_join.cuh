@@ -149,6 +149,42 @@ __device__ __forceinline__ void sorted_group(const uint32_t* __restrict__ bk, ui
   *count = lo2 - lo;
 }
 
+// slot of a probe key, or 0xFFFFFFFF when it can have no partner: NULL (0), below kmin, beyond the table, or (stride > 1)
+// not in the residue class of the build keys
+__device__ __forceinline__ uint32_t key_slot(uint32_t key, uint32_t kmin, uint32_t stride, uint32_t range) {
+  if (key < kmin || key == 0) return 0xFFFFFFFFu;
+  const uint32_t d = key - kmin;
+  if (stride == 1) return d < range ? d : 0xFFFFFFFFu;
+  const uint32_t q = d / stride;
+  return (q * stride == d && q < range) ? q : 0xFFFFFFFFu;
+}
+
+// ---------------- existence over the same key space (MINUS, FILTER [NOT] EXISTS on one dense key) ----------------
+// bits[slot / 32] bit (slot % 32) = some rhs row has the key of that slot: 1 bit per possible key (1.5 MB for 10^7 keys)
+__global__ void __launch_bounds__(256)
+k_dense_mark(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t kstride, uint32_t range,
+             uint32_t* __restrict__ bits) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < nb; i += stride) {
+    const uint32_t k = __ldg(bk + i);
+    if (k == 0) continue;  // NULL never matches
+    const uint32_t slot = (k - kmin) / kstride;
+    if (slot < range) atomicOr(bits + (slot >> 5), 1u << (slot & 31u));
+  }
+}
+// flag[i] = 1 where the probe key of row i is marked (flag is left alone elsewhere)
+__global__ void __launch_bounds__(256)
+k_dense_contains(const uint32_t* __restrict__ pk, uint64_t np, const uint32_t* __restrict__ bits, uint32_t kmin,
+                 uint32_t kstride, uint32_t range, uint32_t* __restrict__ flag) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < np; i += stride) {
+    const uint32_t slot = key_slot(__ldg(pk + i), kmin, kstride, range);
+    if (slot != 0xFFFFFFFFu && ((__ldg(bits + (slot >> 5)) >> (slot & 31u)) & 1u)) flag[i] = 1u;
+  }
+}
+
 // ---------------- compact table: {u32 ~start; u8 count[4]} per 4 consecutive keys ----------------
 __global__ void __launch_bounds__(256)
 k_dense_compress(const uint32_t* __restrict__ offs, uint32_t range, uint2* __restrict__ tab2, uint32_t* __restrict__ overflow) {
@@ -169,16 +205,6 @@ k_dense_compress(const uint32_t* __restrict__ offs, uint32_t range, uint2* __res
     tab2[g] = make_uint2(~o[0], packed);  // the start is stored complemented (see k_dense_heads_compact)
   }
   if (over) atomicOr(overflow, 1u);
-}
-
-// slot of a probe key, or 0xFFFFFFFF when it can have no partner: NULL (0), below kmin, beyond the table, or (stride > 1)
-// not in the residue class of the build keys
-__device__ __forceinline__ uint32_t key_slot(uint32_t key, uint32_t kmin, uint32_t stride, uint32_t range) {
-  if (key < kmin || key == 0) return 0xFFFFFFFFu;
-  const uint32_t d = key - kmin;
-  if (stride == 1) return d < range ? d : 0xFFFFFFFFu;
-  const uint32_t q = d / stride;
-  return (q * stride == d && q < range) ? q : 0xFFFFFFFFu;
 }
 
 // ---------------- probe + expand ----------------

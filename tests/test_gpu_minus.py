@@ -11,6 +11,15 @@ from helpers import GpuBackend, check_w3c_case
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["dense", "hash"])
+def semi_join_path(ctx, request):
+    """every test runs twice: with the direct-address existence bitmap for single dense keys (default) and with the
+    open-addressing hash table (RFGPU_OPT_LOOKUP_JOIN = 0)"""
+    ctx.set_option(F.OPT_LOOKUP_JOIN, 1 if request.param == "dense" else 0)
+    yield request.param
+    ctx.set_option(F.OPT_LOOKUP_JOIN, 1)
+
+
 FIRST_BATCH = ("negation/full-minuend", "negation/part-minuend", "negation/subsetByExcl01", "negation/subsetByExcl02",
                "negation/exists-01", "negation/exists-02")
 
