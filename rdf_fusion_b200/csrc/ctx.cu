@@ -162,7 +162,7 @@ int32_t rfgpu_ctx_create(int32_t device, rfgpu_ctx** out) {
     RF_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
     uint64_t thr = UINT64_MAX;
     RF_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
-    RF_CUDA(cudaHostAlloc((void**)&ctx->h_scratch, 256 * sizeof(uint64_t), cudaHostAllocDefault));
+    RF_CUDA(cudaHostAlloc((void**)&ctx->h_scratch, 512 * sizeof(uint64_t), cudaHostAllocDefault));
     RF_CUDA(cudaEventCreate(&ctx->t0));
     RF_CUDA(cudaEventCreate(&ctx->t1));
     rf::filter_noalloc_setup(device);  // once per device, this device current; never fails the context

@@ -414,6 +414,9 @@ extern "C" int32_t rfgpu_filter(rfgpu_ctx* ctx, const rfgpu_table* in, const rfg
   std::unique_ptr<rfgpu_table> t(new_table());
   t->rows = kept;
   t->sorted_col = in->sorted_col;  // order-preserving compaction
+  t->has_bounds = in->has_bounds;  // a filter only drops rows: the bounds stay valid
+  t->sorted_min = in->sorted_min;
+  t->sorted_max = in->sorted_max;
   for (int c = 0; c < nc; c++) {
     Column col;
     col.name = in->cols[c].name;

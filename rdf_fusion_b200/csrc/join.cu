@@ -95,13 +95,22 @@ struct DenseRange {
 
 // Bounds of the non-NULL build keys and whether a table of one u32 per possible key is worth it: at most 8 slots per
 // input row (memset + scan of the table stay below the cost of streaming the inputs) and at most 2^28 slots.
-DenseRange dense_range(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, bool sorted, uint64_t np, uint32_t stride) {
+DenseRange dense_range(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, bool sorted, uint64_t np, uint32_t stride,
+                       const rfgpu_table* bounds_of = nullptr, uint32_t residue = 0) {
   DenseRange D;
   D.stride = std::max<uint32_t>(stride, 1);
   if (!ctx->opt_lookup_join || nb == 0 || nb >= 0xFFFFFFFFull) return D;
   uint32_t* h = reinterpret_cast<uint32_t*>(ctx->h_scratch + 12);
   bool have = false;
-  if (sorted) {  // ascending, NULL (0) first: the ends are the bounds unless NULLs lead
+  if (sorted && bounds_of && bounds_of->has_bounds) {
+    // the scan that produced the build side already reported the bounds of its sort column (with the range, in one hand-off)
+    h[0] = bounds_of->sorted_min;
+    h[1] = bounds_of->sorted_max;
+    // the table base must lie in the keys' residue class (the reported minimum is conservative when NULLs lead the range)
+    if (D.stride > 1) h[0] += (residue + D.stride - h[0] % D.stride) % D.stride;
+    have = h[1] >= h[0];
+  }
+  if (!have && sorted) {  // ascending, NULL (0) first: the ends are the bounds unless NULLs lead
     RF_CUDA(cudaMemcpyAsync(h, bk, 4, cudaMemcpyDeviceToHost, ctx->stream()));
     RF_CUDA(cudaMemcpyAsync(h + 1, bk + nb - 1, 4, cudaMemcpyDeviceToHost, ctx->stream()));
     ctx->sync();
@@ -827,7 +836,7 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
         D.ok = true;
         D.range = 0xFFFFFFFFu;
       } else {
-        D = dense_range(ctx, kc(Bt, 0), Bt->rows, bsorted, Pt->rows, Bt->cols[bkey].mod_g);
+        D = dense_range(ctx, kc(Bt, 0), Bt->rows, bsorted, Pt->rows, Bt->cols[bkey].mod_g, Bt, Bt->cols[bkey].mod_r);
       }
       if (D.ok) {
         std::vector<BufRef> bufs;

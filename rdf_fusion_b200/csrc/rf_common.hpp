@@ -84,6 +84,11 @@ struct rfgpu_table {
   std::vector<rf::Column> cols;
   uint64_t rows = 0;
   int sorted_col = -1;  // rows ascend by this column (NULL = 0 first); -1 unknown
+  // Known bounds of the non-NULL values of sorted_col (has_bounds): a superset interval is fine.  A scan gets them from the
+  // range look-up in the same host hand-off as the range, so a join that sizes its direct-address table from the build keys'
+  // bounds needs no device read of its own.
+  bool has_bounds = false;
+  uint32_t sorted_min = 0, sorted_max = 0;
 };
 
 struct rfgpu_index_t {
@@ -125,7 +130,7 @@ struct rfgpu_ctx {
   int last_shuffle_path = 0;
   uint64_t last_from = 0, last_to = 0;
   // pinned host scratch for small device→host results (ranges, counts)
-  uint64_t* h_scratch = nullptr;  // 256 x u64: [0,16) scalars, [16,80) partition counts, [128,160) batched ranges
+  uint64_t* h_scratch = nullptr;  // 512 x u64: [0,16) scalars ([0..3] single range look-up), [16,80) partition counts, [96,128) hash chunks, [160,170) sort / dict, [256,320) batched range look-ups
   // profiling
   bool profiling = false;
   std::vector<std::pair<std::string, rf::KernelStat>> kstats;

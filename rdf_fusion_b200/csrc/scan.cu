@@ -23,7 +23,15 @@ struct SearchArgs {
   uint64_t n;
   uint32_t key[2][4];  // [0] lower tuple, [1] upper tuple
   int32_t depth;       // number of leading columns compared
+  int32_t sort_level;  // level the rows of the range ascend by (-1: none): its values at both ends are reported too
 };
+
+// value of the sort level at the found end of the range (the first row for the lower bound, the last for the upper one)
+__device__ __forceinline__ unsigned long long end_value(const SearchArgs& A, int which, uint64_t pos) {
+  if (A.sort_level < 0) return 0ull;
+  if (which == 0) return pos < A.n ? (unsigned long long)__ldg(A.col[A.sort_level] + pos) : 0ull;
+  return pos > 0 ? (unsigned long long)__ldg(A.col[A.sort_level] + pos - 1) : 0ull;
+}
 
 // true ⇔ row tuple >= key (which = 0, lower_bound) / row tuple > key (which = 1, upper_bound)
 __device__ __forceinline__ bool tuple_cmp(const SearchArgs& A, int which, uint64_t row) {
@@ -64,7 +72,10 @@ k_range_search(const __grid_constant__ SearchArgs A, unsigned long long* __restr
     lo = min(nlo, hi);
     hi = max(nhi, lo);
   }
-  if (threadIdx.x == 0) result[which] = lo;
+  if (threadIdx.x == 0) {
+    result[which] = lo;
+    result[2 + which] = end_value(A, which, lo);
+  }
 }
 
 // Batched form: Q look-ups per launch (grid = 2Q CTAs) — the "vectorised" range lookup for callers that hold several
@@ -95,7 +106,10 @@ k_range_search_many(const __grid_constant__ SearchBatch B, unsigned long long* _
     lo = min(nlo, hi);
     hi = max(nhi, lo);
   }
-  if (threadIdx.x == 0) result[blockIdx.x] = lo;
+  if (threadIdx.x == 0) {
+    result[blockIdx.x] = lo;
+    result[2 * kMaxBatch + blockIdx.x] = end_value(A, which, lo);
+  }
 }
 
 // ---- 1b: column gather ----
@@ -225,10 +239,14 @@ static int search_args_for(const rfgpu_index_t* ix, const ScanInstrs& ins, Searc
   }
   S->depth = depth;
   for (int l = 0; l < 4; l++) S->col[l] = ix->col[l]->as<uint32_t>();
+  S->sort_level = -1;
+  const std::string sv = ins.sorted_var();
+  for (int l = 0; l < 4 && !sv.empty(); l++)
+    if (ins.at[l].scan && ins.at[l].var == sv) S->sort_level = l;
   return depth;
 }
 
-// `range` != nullptr: [from, to) already known (batched look-up)
+// `range` != nullptr: [from, to) already known (batched look-up), followed by the sort level's values at both ends
 static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t flags, rfgpu_table** out,
                               const uint64_t* range) {
   const rfgpu_index_t* ix = find_index(p->store, p->perm);
@@ -288,9 +306,14 @@ static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t
   SearchArgs S;
   const int depth = search_args_for(ix, ins, &S);
   uint64_t from = 0, to = ix->rows;
+  uint64_t end_lo = 0, end_hi = 0;
+  bool have_ends = false;
   if (range) {
     from = range[0];
     to = std::max(range[0], range[1]);
+    end_lo = range[2];
+    end_hi = range[3];
+    have_ends = true;
   } else if (depth > 0) {
     {
       KernelScope ks(ctx, "k_range_search");
@@ -299,6 +322,9 @@ static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t
     ctx->sync();
     from = ctx->h_scratch[0];
     to = ctx->h_scratch[1];
+    end_lo = ctx->h_scratch[2];
+    end_hi = ctx->h_scratch[3];
+    have_ends = true;
     if (to < from) to = from;
   }
   ctx->last_from = from;
@@ -358,6 +384,13 @@ static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t
 
   std::unique_ptr<rfgpu_table> t(new_table());
   t->sorted_col = sorted_out;
+  if (have_ends && sorted_out >= 0 && S.sort_level >= 0 && R > 0 && end_hi >= end_lo && end_hi != 0) {
+    // the rows ascend by the sort level inside the range: its first and last values bound the column (a residual predicate
+    // only removes rows).  NULL (0) can lead the range: the lower bound is then conservative, which is all that is asked.
+    t->has_bounds = true;
+    t->sorted_min = (uint32_t)std::max<uint64_t>(end_lo, 1);
+    t->sorted_max = (uint32_t)end_hi;
+  }
   if (residual.empty()) {
     t->rows = R;
     if (flags & RFGPU_SCAN_ALLOW_VIEW) {
@@ -474,15 +507,16 @@ int32_t rfgpu_scan_execute_many(rfgpu_ctx* ctx, const rfgpu_scan_plan* const* pl
         RF_REQUIRE(ix, RFGPU_E_EXEC, "Index must exist");
         search_args_for(ix, p->gspo.reorder(p->perm), &B.q[i]);  // depth 0 → [0, n) falls out of the search itself
       }
-      uint64_t* res = ctx->h_scratch + 128;
+      uint64_t* res = ctx->h_scratch + 256;  // [256, 288) ranges, [288, 320) the sort level's end values
       {
         KernelScope ks(ctx, "k_range_search_many");
         k_range_search_many<<<2 * q, kSearchThreads, 0, ctx->stream()>>>(B, (unsigned long long*)res);
       }
       ctx->sync();
-      uint64_t ranges[2 * kMaxBatch];
-      for (int i = 0; i < 2 * q; i++) ranges[i] = res[i];
-      for (int i = 0; i < q; i++) scan_execute_impl(ctx, plans[base + i], flags, &out[base + i], &ranges[2 * i]);
+      for (int i = 0; i < q; i++) {
+        const uint64_t r4[4] = {res[2 * i], res[2 * i + 1], res[2 * kMaxBatch + 2 * i], res[2 * kMaxBatch + 2 * i + 1]};
+        scan_execute_impl(ctx, plans[base + i], flags, &out[base + i], r4);
+      }
     }
   } catch (...) {
     for (int i = 0; i < n; i++) {

@@ -87,7 +87,7 @@ void rfgpu_store_release(rfgpu_store* s) {
 rfgpu_ctx* emu_ctx_create() {
   auto* c = new rfgpu_ctx();
   c->core = std::make_shared<rf::Core>();
-  c->h_scratch = (uint64_t*)std::calloc(256, 8);
+  c->h_scratch = (uint64_t*)std::calloc(512, 8);
   return c;
 }
 void emu_ctx_destroy(rfgpu_ctx* c) {
