@@ -69,6 +69,12 @@ def parse_args():
                     help="with --hash-join: the build side (p2) is scanned in ?s order (GPSO), the probe side stays unsorted")
     ap.add_argument("--no-lookup-join", action="store_true",
                     help="dense keys: open-addressing hash table instead of the direct-address table")
+    ap.add_argument("--timeline", default=None, metavar="FILE",
+                    help="diagnostic: start / end of every kernel launch of one more step, written to FILE")
+    ap.add_argument("--host-profile", default=None, metavar="FILE",
+                    help="diagnostic: cProfile of 20 more device-resident steps (host side only), top functions written to FILE")
+    ap.add_argument("--no-lazy-rows", action="store_true",
+                    help="every join / filter waits for its output row count (RFGPU_OPT_LAZY_ROWS off)")
     return ap.parse_args()
 
 
@@ -268,6 +274,8 @@ def run_ours(a):
         ctx.set_option(F.OPT_MERGE_THREADS, a.merge_threads)
     if a.no_lookup_join:
         ctx.set_option(F.OPT_LOOKUP_JOIN, 0)
+    if a.no_lazy_rows:
+        ctx.set_option(F.OPT_LAZY_ROWS, 0)
     if a.nccl_shuffle:
         ctx.set_option(F.OPT_SHUFFLE_P2P, 0)
     if world > 1:
@@ -299,6 +307,7 @@ def run_ours(a):
     join_bytes = {}  # physical operator -> algorithmic bytes 4 (cb Nb + cp Np + co No) of the joins that used it
     plan_cache = {}
     prefetched, chain_keys = {}, []
+    deferred = []  # accounting that needs the row count of a join / filter result: run once the whole step is queued
 
     class Ops:  # the engine adapter of dist.fold_bgp
         @staticmethod
@@ -320,7 +329,7 @@ def run_ours(a):
             out = t.shuffle(key)
             if cnt["time_shuffles"]:
                 cnt["shuffle_ms"] += ctx.timer_stop()
-            cnt["sent"] += t.num_rows
+            cnt["sent"] += t.num_rows  # the exchange has read the count already (its own host hand-off)
             cnt["sent_bytes"] += 4 * len(t.names) * t.num_rows
             cnt["shuffles"] += 1
             return out
@@ -328,9 +337,13 @@ def run_ours(a):
         @staticmethod
         def join(l, r, jt):
             out = l.join(r, jt)
-            cnt["rows"] += l.num_rows + r.num_rows
-            b = 4 * (len(l.names) * l.num_rows + len(r.names) * r.num_rows + len(out.names) * out.num_rows)
-            join_bytes[out.last_join_phys] = join_bytes.get(out.last_join_phys, 0) + b
+            phys = out.last_join_phys
+
+            def account():  # row counts of join results are read lazily (rfgpu_table_num_rows): not in the middle of the step
+                cnt["rows"] += l.num_rows + r.num_rows
+                b = 4 * (len(l.names) * l.num_rows + len(r.names) * r.num_rows + len(out.names) * out.num_rows)
+                join_bytes[phys] = join_bytes.get(phys, 0) + b
+            deferred.append(account)
             return out
         names = staticmethod(lambda t: t.names)
         nullable = staticmethod(lambda t: t.nullable)
@@ -340,10 +353,15 @@ def run_ours(a):
         cnt["rows"] += sum(t.num_rows for t in ts)
         return ts
 
+    def out_rows(t):
+        def account():
+            cnt["out"] += t.num_rows
+        deferred.append(account)
+
     def part_filter(t):
         f = t.filter(ne_filter)
         cnt["rows"] += t.num_rows
-        cnt["out"] += f.num_rows
+        out_rows(f)
         return f
 
     def part_star():
@@ -354,7 +372,7 @@ def run_ours(a):
         if star_pk[1] != "s":
             tb = Ops.shuffle(tb, "s")
         tj = Ops.join(ta, tb, F.JOIN_INNER)
-        cnt["out"] += tj.num_rows
+        out_rows(tj)
         return tj
 
     def part_chain():
@@ -366,7 +384,7 @@ def run_ours(a):
         t, _, _ = fold_bgp(Ops, chain, F.JOIN_INNER)
         if not chain_keys:
             chain_keys.extend(k for k in plan_cache if k[0] in chain)
-        cnt["out"] += t.num_rows
+        out_rows(t)
         return t
 
     def step_device():
@@ -380,7 +398,16 @@ def run_ours(a):
             res.append(part_star())
         if "chain" in parts:
             res.append(part_chain())
+        # everything is queued: reading the last result's row count is the step's one wait for the device (the stream is in
+        # order, so every earlier result is complete by then); the bookkeeping runs after the timed region (flush_deferred)
+        if res:
+            res[-1].num_rows
         return res
+
+    def flush_deferred():
+        for account in deferred:
+            account()
+        deferred.clear()
 
     # ---- e2e: host buffers in and out, through the C ABI
     def pinned(n):
@@ -388,6 +415,7 @@ def run_ours(a):
     e2e_state = {}
     if not a.no_e2e:
         probe = step_device()  # sizes of every final result
+        flush_deferred()
         e2e_state["bufs"] = [[pinned(t.num_rows) for _ in t.names] for t in probe]
         d2h = sum(4 * len(t.names) * t.num_rows for t in probe)
         h2d = 0
@@ -454,10 +482,12 @@ def run_ours(a):
     def timed(fn, steps, warmup, profile=False):
         for _ in range(warmup):
             fn()
+            flush_deferred()
         ctx.metrics_reset()
         ctx.profile_enable(profile)
         reset_counters()
         barrier()
+        syncs0, redos0 = ctx.host_syncs, ctx.lazy_redos
         ms = 0.0
         for _ in range(steps):
             ctx.flush_l2()  # write 256 MB (> 126 MB L2) between timed iterations, outside the timed region
@@ -467,10 +497,14 @@ def run_ours(a):
             ctx.timer_start()
             fn()
             ms += ctx.timer_stop()
+            flush_deferred()
+        host_syncs = (ctx.host_syncs - syncs0 - steps) / steps  # minus the ctx.synchronize() before every timed step
+        redos = ctx.lazy_redos - redos0
         barrier()
         prof = ctx.profile() if profile else {}
         ctx.profile_enable(False)
         m = ctx.metrics()
+        m["host_syncs_per_step"], m["lazy_redos"] = host_syncs, redos
         c = dict(cnt)
         jb_ = dict(join_bytes)
         if world > 1:
@@ -487,6 +521,45 @@ def run_ours(a):
     c, ms, prof, met, jbytes = timed(step_device, a.steps, max(a.warmup, 3), profile=True)
     clocks = sampler.stop()
     rows, out = c["rows"], c["out"]
+    if a.timeline and rank == 0:  # diagnostic: one step's launches on a time axis (not part of any reported number)
+        ctx.profile_enable(True)
+        ctx.flush_l2()
+        ctx.synchronize()
+        ctx.timeline(True)
+        t0 = time.perf_counter()
+        step_device()
+        wall_us = (time.perf_counter() - t0) * 1e6
+        flush_deferred()
+        recs = ctx.timeline_records()
+        ctx.timeline(False)
+        ctx.profile_enable(False)
+        with open(a.timeline, "w") as f:
+            f.write("# one device-resident step after an L2 flush; host wall clock %.1f us; kernel, start_us, end_us, duration_us, "
+                    "idle_before_us (since the latest end so far)\n" % wall_us)
+            latest = 0.0
+            for name, s_us, e_us in recs:
+                f.write("%-28s %9.1f %9.1f %8.1f %8.1f\n" % (name, s_us, e_us, e_us - s_us, max(0.0, s_us - latest)))
+                latest = max(latest, e_us)
+    if a.host_profile and rank == 0:
+        import cProfile
+        import io
+        import pstats
+        t0 = time.perf_counter()
+        for _ in range(20):
+            step_device()
+            flush_deferred()
+        wall = (time.perf_counter() - t0) / 20
+        pr = cProfile.Profile()
+        pr.enable()
+        for _ in range(20):
+            step_device()
+            flush_deferred()
+        pr.disable()
+        buf = io.StringIO()
+        pstats.Stats(pr, stream=buf).sort_stats("cumulative").print_stats(45)
+        with open(a.host_profile, "w") as f:
+            f.write("wall clock per step without the profiler, L2 not flushed: %.1f us\n" % (wall * 1e6))
+            f.write(buf.getvalue())
 
     # ---- phases (a second, separately timed pass; not part of `value`): where the step's time goes, whole-shuffle time
     phases = {}
@@ -498,8 +571,10 @@ def run_ours(a):
         for _ in range(3):
             barrier()
             ctx.timer_start()
-            fn()
+            r = fn()
+            (r[-1] if isinstance(r, list) else r).num_rows  # the phase ends when its last result is there
             acc += ctx.timer_stop()
+            flush_deferred()
         phases[name + "_ms"] = acc / 3
     nvlink = None
     if world > 1:
@@ -511,6 +586,7 @@ def run_ours(a):
                 part_star()
             if "chain" in parts:
                 part_chain()
+            flush_deferred()
         cnt["time_shuffles"] = False
         t = torch.tensor([cnt["shuffle_ms"] / 3], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -556,7 +632,8 @@ def run_ours(a):
         for k, v in sorted(kern.items(), key=lambda kv: -kv[1]["ms"]):
             gbs = v["bytes"] / (v["ms"] / 1e3) / 1e9 if v["bytes"] else None
             breakdown[k] = {"launches": v["launches"], "ms_per_launch": v["ms"] / v["launches"],
-                            "share": v["ms"] / tot, "alg_GBps": gbs, "frac": gbs / peak if gbs else None}
+                            "share": v["ms"] / tot, "alg_GBps": gbs, "frac": gbs / peak if gbs else None,
+                            "gap_before_us_per_step": 1e3 * v.get("gap_ms", 0.0) / a.steps}
         # the dominant kernel among those that move data (the range search is latency: O(log N) bytes)
         top = max((k for k in kern if kern[k]["bytes"]), key=lambda k: kern[k]["ms"], default=max(kern, key=lambda k: kern[k]["ms"]))
         v = kern[top]
@@ -601,6 +678,7 @@ def run_ours(a):
                                      "in between), summed over the steps, max over ranks",
                            "setup_s": round(setup_s, 1), "phases_ms": phases, "kernels": breakdown},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(met["kernel_launches"]),
+                "host_syncs_per_step": met["host_syncs_per_step"], "lazy_redos": met["lazy_redos"],
                 "roofline": roof, "roofline_hash": roof_hash, "roofline_merge": roof_merge, "nvlink": nvlink,
                 "cpu_baseline": cb}
         emit(line)

@@ -192,7 +192,21 @@ int32_t rfgpu_scan_plan_order_by(rfgpu_ctx* ctx, rfgpu_scan_plan* p, const char*
 /* ---- tables (solution mappings on the device) ---- */
 rfgpu_table* rfgpu_table_retain(rfgpu_table* t);
 void rfgpu_table_release(rfgpu_table* t);
+/* Row counts are LAZY (RFGPU_OPT_LAZY_ROWS, default on): a join or filter whose output size is only known on the device
+ * returns without waiting for it, so that a chain of operators is queued back to back the way the reference streams record
+ * batches from operator to operator (lib/storage/src/memory/storage/scan.rs:101-213 — no barrier between operators there).
+ * The count is read the first time the host needs it: rfgpu_table_num_rows, any export, or an operator that has to know
+ * its input size on the host.  That first read synchronises the ctx stream once (not at all if it was synchronised since)
+ * and, if the operator's optimistic output capacity turned out too small, runs it a second time at the exact size — the
+ * caller never sees the difference.  rfgpu_table_num_rows has no error channel (0 on failure, message in
+ * rfgpu_last_error); rfgpu_table_settle is the same read with a status code.  rfgpu_table_is_pending: 1 while the count
+ * has not been read.  rfgpu_ctx_host_syncs / rfgpu_ctx_lazy_redos: how often this ctx waited for its stream / re-ran an
+ * operator because its capacity guess was too small. */
 uint64_t rfgpu_table_num_rows(const rfgpu_table* t);
+int32_t rfgpu_table_settle(rfgpu_ctx* ctx, const rfgpu_table* t);
+int32_t rfgpu_table_is_pending(const rfgpu_table* t);
+uint64_t rfgpu_ctx_host_syncs(const rfgpu_ctx* ctx);
+uint64_t rfgpu_ctx_lazy_redos(const rfgpu_ctx* ctx);
 int32_t rfgpu_table_num_cols(const rfgpu_table* t);
 const char* rfgpu_table_col_name(const rfgpu_table* t, int32_t col);
 int32_t rfgpu_table_col_nullable(const rfgpu_table* t, int32_t col);
@@ -461,6 +475,8 @@ typedef enum {
   RFGPU_OPT_LOOKUP_JOIN = 11,    /* 1 (default): single-key equi joins, MINUS / EXISTS and GROUP BY whose (build) keys span a
                                     range of at most 8 slots per input row use a direct-address table (slot = id - min id)
                                     instead of the open-addressing hash table; 0: always hash */
+  RFGPU_OPT_LAZY_ROWS = 12,      /* 1 (default): joins and filters return before their output row count has reached the host
+                                    (see rfgpu_table_num_rows); 0: every operator waits for its count */
   RFGPU_OPT_SHUFFLE_ARENA_BYTES = 7 /* size of this rank's receive arena (two halves, used alternately); read by
                                        rfgpu_comm_init, default 1 GiB.  A shuffle whose rows do not fit one half on some
                                        rank falls back to the NCCL exchange on every rank */
@@ -509,6 +525,15 @@ int32_t rfgpu_profile_enable(rfgpu_ctx* ctx, int32_t on);
 int32_t rfgpu_profile_num_kernels(rfgpu_ctx* ctx);
 int32_t rfgpu_profile_get(rfgpu_ctx* ctx, int32_t i, const char** name, uint64_t* launches,
                           double* total_ms, uint64_t* algorithmic_bytes);
+/* stream time that passed between the end of the previously profiled kernel and the start of kernel i's launches, summed
+ * over its launches: host hand-offs, memsets and copies in between — where a step's time goes besides the kernels */
+int32_t rfgpu_profile_gap_ms(rfgpu_ctx* ctx, int32_t i, double* gap_ms);
+/* launch timeline (with profiling enabled): rfgpu_profile_timeline(ctx, 1) sets the origin of the time axis on the ctx stream
+ * and starts recording the start / end of every kernel launch in microseconds; _len / _get read the records back in launch
+ * order (kernels of the range look-up stream overlap those of the ctx stream); rfgpu_profile_timeline(ctx, 0) stops */
+int32_t rfgpu_profile_timeline(rfgpu_ctx* ctx, int32_t on);
+int32_t rfgpu_profile_timeline_len(rfgpu_ctx* ctx);
+int32_t rfgpu_profile_timeline_get(rfgpu_ctx* ctx, int32_t i, const char** name, double* start_us, double* end_us);
 /* stream-ordered stopwatch on the ctx stream (bench.py times steps with it) */
 int32_t rfgpu_timer_start(rfgpu_ctx* ctx);
 int32_t rfgpu_timer_stop(rfgpu_ctx* ctx, double* elapsed_ms);

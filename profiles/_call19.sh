@@ -1,0 +1,4 @@
+set -x
+timeout 1800 python -m pytest tests -m gpu -x -q 2>&1 | tail -8 > gpurun_out/r2s_tests.txt
+timeout 600 python bench.py --steps 10 --no-e2e --no-cpu-baseline > gpurun_out/r2s_bench_n1.json 2> gpurun_out/r2s_bench_n1.err
+timeout 600 python bench.py --steps 10 --no-e2e --no-cpu-baseline --no-lazy-rows > gpurun_out/r2s_bench_n1_nolazy.json 2> gpurun_out/r2s_bench_n1_nolazy.err

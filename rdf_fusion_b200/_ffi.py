@@ -45,6 +45,7 @@ OPT_SORT_MERGE_JOIN = 8
 OPT_SORT_SEMI = 9
 OPT_SORT_AGG = 10
 OPT_LOOKUP_JOIN = 11
+OPT_LAZY_ROWS = 12
 SHUFFLE_LOCAL, SHUFFLE_NCCL, SHUFFLE_P2P = 0, 1, 2
 UNIQUE_ID_BYTES = 128
 
@@ -131,6 +132,10 @@ SIGNATURES = {
     "rfgpu_table_release": (None, [C.c_void_p]),
     "rfgpu_table_num_rows": (C.c_uint64, [C.c_void_p]),
     "rfgpu_table_num_cols": (C.c_int32, [C.c_void_p]),
+    "rfgpu_table_settle": (C.c_int32, [C.c_void_p, C.c_void_p]),
+    "rfgpu_table_is_pending": (C.c_int32, [C.c_void_p]),
+    "rfgpu_ctx_host_syncs": (C.c_uint64, [C.c_void_p]),
+    "rfgpu_ctx_lazy_redos": (C.c_uint64, [C.c_void_p]),
     "rfgpu_table_col_name": (C.c_char_p, [C.c_void_p, C.c_int32]),
     "rfgpu_table_col_nullable": (C.c_int32, [C.c_void_p, C.c_int32]),
     "rfgpu_table_col_device_ptr": (C.c_void_p, [C.c_void_p, C.c_int32]),
@@ -173,6 +178,10 @@ SIGNATURES = {
     "rfgpu_profile_enable": (C.c_int32, [C.c_void_p, C.c_int32]),
     "rfgpu_profile_num_kernels": (C.c_int32, [C.c_void_p]),
     "rfgpu_profile_get": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), u64p, C.POINTER(C.c_double), u64p]),
+    "rfgpu_profile_gap_ms": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_double)]),
+    "rfgpu_profile_timeline": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "rfgpu_profile_timeline_len": (C.c_int32, [C.c_void_p]),
+    "rfgpu_profile_timeline_get": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "rfgpu_timer_start": (C.c_int32, [C.c_void_p]),
     "rfgpu_timer_stop": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
     "rfgpu_flush_l2": (C.c_int32, [C.c_void_p]),

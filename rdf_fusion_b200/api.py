@@ -147,6 +147,15 @@ class Context:
     def synchronize(self):
         self.check(self.lib.rfgpu_ctx_synchronize(self.h))
 
+    @property
+    def host_syncs(self) -> int:
+        """How often this ctx has waited for its stream so far."""
+        return int(self.lib.rfgpu_ctx_host_syncs(self.h))
+
+    @property
+    def lazy_redos(self) -> int:
+        return int(self.lib.rfgpu_ctx_lazy_redos(self.h))
+
     def set_option(self, option: int, value: int):
         self.check(self.lib.rfgpu_ctx_set_option(self.h, option, value))
 
@@ -239,7 +248,22 @@ class Context:
             launches, nbytes = C.c_uint64(), C.c_uint64()
             ms = C.c_double()
             self.lib.rfgpu_profile_get(self.h, i, C.byref(name), C.byref(launches), C.byref(ms), C.byref(nbytes))
-            out[name.value.decode()] = {"launches": launches.value, "ms": ms.value, "bytes": nbytes.value}
+            gap = C.c_double()
+            self.lib.rfgpu_profile_gap_ms(self.h, i, C.byref(gap))
+            out[name.value.decode()] = {"launches": launches.value, "ms": ms.value, "bytes": nbytes.value, "gap_ms": gap.value}
+        return out
+
+    def timeline(self, on=True):
+        """start (on=True: time zero is now, on the ctx stream) or stop recording the launch timeline; needs profile_enable"""
+        self.check(self.lib.rfgpu_profile_timeline(self.h, 1 if on else 0))
+
+    def timeline_records(self):
+        """[(kernel name, start_us, end_us)] in launch order since timeline(True)"""
+        out = []
+        for i in range(self.lib.rfgpu_profile_timeline_len(self.h)):
+            name, a, b = C.c_char_p(), C.c_double(), C.c_double()
+            self.check(self.lib.rfgpu_profile_timeline_get(self.h, i, C.byref(name), C.byref(a), C.byref(b)))
+            out.append((name.value.decode(), a.value, b.value))
         return out
 
     def timer_start(self):
@@ -464,6 +488,8 @@ class Table:
     def __init__(self, ctx: Context, h):
         self.ctx = ctx
         self.h = h
+        self._names = None
+        self._nullable = None
 
     def __del__(self):
         try:
@@ -475,21 +501,34 @@ class Table:
 
     @property
     def num_rows(self) -> int:
+        """Exact row count.  The count of a join / filter result is read lazily (include/rfgpu.h, rfgpu_table_num_rows): the
+        first read waits for the device."""
+        if self.ctx.lib.rfgpu_table_is_pending(self.h):
+            self.ctx.check(self.ctx.lib.rfgpu_table_settle(self.ctx.h, self.h))
         return int(self.ctx.lib.rfgpu_table_num_rows(self.h))
 
     @property
+    def is_pending(self) -> bool:
+        return bool(self.ctx.lib.rfgpu_table_is_pending(self.h))
+
+    @property
     def names(self) -> List[str]:
-        return [self.ctx.lib.rfgpu_table_col_name(self.h, i).decode()
-                for i in range(self.ctx.lib.rfgpu_table_num_cols(self.h))]
+        if self._names is None:  # a table's schema never changes: read it through the C ABI once
+            self._names = [self.ctx.lib.rfgpu_table_col_name(self.h, i).decode()
+                           for i in range(self.ctx.lib.rfgpu_table_num_cols(self.h))]
+        return list(self._names)
 
     @property
     def nullable(self) -> List[bool]:
-        return [bool(self.ctx.lib.rfgpu_table_col_nullable(self.h, i))
-                for i in range(self.ctx.lib.rfgpu_table_num_cols(self.h))]
+        if self._nullable is None:
+            self._nullable = [bool(self.ctx.lib.rfgpu_table_col_nullable(self.h, i))
+                              for i in range(self.ctx.lib.rfgpu_table_num_cols(self.h))]
+        return list(self._nullable)
 
     def set_nullable(self, col, nullable=True):
         i = self.names.index(col) if isinstance(col, str) else col
         self.ctx.check(self.ctx.lib.rfgpu_table_set_nullable(self.h, i, 1 if nullable else 0))
+        self._nullable = None
         return self
 
     def to_numpy(self, row_off=0, n_rows=None, out: Optional[List[np.ndarray]] = None,

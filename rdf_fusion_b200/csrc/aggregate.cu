@@ -206,6 +206,7 @@ int32_t rfgpu_group_count(rfgpu_ctx* ctx, const rfgpu_table* in, const int32_t* 
                           int32_t counted_col, const char* count_name, rfgpu_table** out) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && in && key_cols && out && count_name, RFGPU_E_INVALID, "NULL argument");
+  rf::settle(in);  // lazy row count (rf_common.hpp)
   RF_CUDA(cudaSetDevice(ctx->core->device));
   std::vector<int> keys(key_cols, key_cols + std::max(n_keys, 0));
   *out = rf::group_by(ctx, in, keys, counted_col, count_name);
@@ -215,6 +216,7 @@ int32_t rfgpu_group_count(rfgpu_ctx* ctx, const rfgpu_table* in, const int32_t* 
 int32_t rfgpu_distinct(rfgpu_ctx* ctx, const rfgpu_table* in, rfgpu_table** out) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && in && out, RFGPU_E_INVALID, "NULL argument");
+  rf::settle(in);  // lazy row count (rf_common.hpp)
   RF_CUDA(cudaSetDevice(ctx->core->device));
   std::vector<int> keys;
   for (size_t c = 0; c < in->cols.size(); c++) keys.push_back((int)c);

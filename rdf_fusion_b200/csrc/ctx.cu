@@ -34,7 +34,8 @@ DevBuf::~DevBuf() {
   }
 }
 
-KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes) : ctx(c) {
+KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes, cudaStream_t on)
+    : ctx(c), stream(on ? on : c->stream()) {
   ctx->m.kernel_launches++;
   idx = ctx->kstat_index(name);
   ctx->kstats[idx].second.launches++;
@@ -50,14 +51,14 @@ KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes) : ctx(c
     };
     take(&a);
     take(&b);
-    RF_CUDA(cudaEventRecord(a, ctx->stream()));
+    RF_CUDA(cudaEventRecord(a, stream));
   }
 }
 
 KernelScope::~KernelScope() noexcept(false) {
   cudaError_t e = cudaGetLastError();
   if (a) {
-    cudaEventRecord(b, ctx->stream());
+    cudaEventRecord(b, stream);
     ctx->pending.push_back({idx, a, b});
   }
   if (e != cudaSuccess && !std::uncaught_exceptions())
@@ -66,6 +67,18 @@ KernelScope::~KernelScope() noexcept(false) {
 }
 
 rfgpu_table* new_table() { return new rfgpu_table(); }
+}  // namespace rf
+
+cudaStream_t rfgpu_ctx::lookup_stream() {
+  if (!lookup_stream_) {
+    int lo = 0, hi = 0;  // numerically lower = higher priority
+    RF_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    RF_CUDA(cudaStreamCreateWithPriority(&lookup_stream_, cudaStreamNonBlocking, hi));
+  }
+  return lookup_stream_;
+}
+
+namespace rf {
 
 BufRef alloc_col(rfgpu_ctx* ctx, uint64_t rows) { return ctx->alloc(rows * sizeof(uint32_t)); }
 
@@ -87,10 +100,24 @@ int rfgpu_ctx::kstat_index(const char* name) {
 void rfgpu_ctx::collect_profile() {
   if (pending.empty()) return;
   RF_CUDA(cudaStreamSynchronize(core->stream));
-  for (auto& p : pending) {
+  for (size_t i = 0; i < pending.size(); i++) {
+    auto& p = pending[i];
     float ms = 0;
     cudaEventElapsedTime(&ms, p.a, p.b);
     kstats[p.idx].second.ms += ms;
+    if (timeline_on && timeline_t0) {
+      float s_ms = 0, e_ms = 0;
+      cudaEventElapsedTime(&s_ms, timeline_t0, p.a);
+      cudaEventElapsedTime(&e_ms, timeline_t0, p.b);
+      timeline.push_back({p.idx, s_ms * 1e3f, e_ms * 1e3f});
+    }
+    if (i > 0) {  // stream time between the previous kernel's end and this one's start: host hand-offs, memsets, copies
+      float gap = 0;
+      cudaEventElapsedTime(&gap, pending[i - 1].b, p.a);
+      if (gap > 0) kstats[p.idx].second.gap_ms += gap;  // kernels on the look-up stream overlap the main stream's
+    }
+  }
+  for (auto& p : pending) {
     event_pool.push_back(p.a);
     event_pool.push_back(p.b);
   }
@@ -163,6 +190,19 @@ int32_t rfgpu_ctx_create(int32_t device, rfgpu_ctx** out) {
     uint64_t thr = UINT64_MAX;
     RF_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
     RF_CUDA(cudaHostAlloc((void**)&ctx->h_scratch, 512 * sizeof(uint64_t), cudaHostAllocDefault));
+    {  // lazy row counts: device words and their pinned mirrors (rf_common.hpp, struct LazyRows)
+      auto pool = std::make_shared<rf::LazyPool>();
+      pool->release = [](rf::LazyPool* p) {
+        if (p->d) cudaFree(p->d);
+        if (p->h) cudaFreeHost(p->h);
+      };
+      RF_CUDA(cudaMalloc((void**)&pool->d, rf::kLazySlots * 8));
+      RF_CUDA(cudaHostAlloc((void**)&pool->h, rf::kLazySlots * 8, cudaHostAllocDefault));
+      for (int i = rf::kLazySlots - 1; i >= 0; i--) pool->free.push_back(i);
+      ctx->lazy_pool = pool;
+      ctx->lazy_d = pool->d;
+      ctx->lazy_h = pool->h;
+    }
     RF_CUDA(cudaEventCreate(&ctx->t0));
     RF_CUDA(cudaEventCreate(&ctx->t1));
     rf::filter_noalloc_setup(device);  // once per device, this device current; never fails the context
@@ -194,15 +234,23 @@ void rfgpu_ctx_destroy(rfgpu_ctx* ctx) {
     cudaEventDestroy(p.b);
   }
   for (auto e : ctx->event_pool) cudaEventDestroy(e);
+  if (ctx->timeline_t0) cudaEventDestroy(ctx->timeline_t0);
   if (ctx->t0) cudaEventDestroy(ctx->t0);
   if (ctx->t1) cudaEventDestroy(ctx->t1);
   if (ctx->h_scratch) cudaFreeHost(ctx->h_scratch);
+  if (ctx->lookup_stream_) {
+    cudaStreamSynchronize(ctx->lookup_stream_);
+    cudaStreamDestroy(ctx->lookup_stream_);
+  }
   if (ctx->flush_buf) cudaFree(ctx->flush_buf);
   ctx->comm.reset();
   delete ctx;
 }
 
 void* rfgpu_ctx_stream(rfgpu_ctx* ctx) { return ctx ? (void*)ctx->core->stream : nullptr; }
+
+uint64_t rfgpu_ctx_host_syncs(const rfgpu_ctx* ctx) { return ctx ? ctx->m_host_syncs : 0; }
+uint64_t rfgpu_ctx_lazy_redos(const rfgpu_ctx* ctx) { return ctx ? ctx->m_lazy_redos : 0; }
 
 int32_t rfgpu_ctx_synchronize(rfgpu_ctx* ctx) {
   RF_API_BEGIN
@@ -366,6 +414,43 @@ int32_t rfgpu_profile_get(rfgpu_ctx* ctx, int32_t i, const char** name, uint64_t
   if (launches) *launches = ctx->kstats[i].second.launches;
   if (total_ms) *total_ms = ctx->kstats[i].second.ms;
   if (algorithmic_bytes) *algorithmic_bytes = ctx->kstats[i].second.bytes;
+  return RFGPU_OK;
+}
+
+int32_t rfgpu_profile_timeline(rfgpu_ctx* ctx, int32_t on) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx, RFGPU_E_INVALID, "ctx is NULL");
+  ctx->collect_profile();
+  ctx->timeline.clear();
+  ctx->timeline_on = on != 0;
+  if (on) {  // the origin of the time axis: now, on the ctx stream
+    if (!ctx->timeline_t0) RF_CUDA(cudaEventCreate(&ctx->timeline_t0));
+    RF_CUDA(cudaEventRecord(ctx->timeline_t0, ctx->stream()));
+  }
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_profile_timeline_len(rfgpu_ctx* ctx) {
+  if (!ctx) return 0;
+  try {
+    ctx->collect_profile();
+  } catch (...) {
+    return 0;
+  }
+  return (int32_t)ctx->timeline.size();
+}
+
+int32_t rfgpu_profile_timeline_get(rfgpu_ctx* ctx, int32_t i, const char** name, double* start_us, double* end_us) {
+  if (!ctx || i < 0 || i >= (int32_t)ctx->timeline.size() || !name || !start_us || !end_us) return RFGPU_E_INVALID;
+  *name = ctx->kstats[ctx->timeline[i].idx].first.c_str();
+  *start_us = ctx->timeline[i].start_us;
+  *end_us = ctx->timeline[i].end_us;
+  return RFGPU_OK;
+}
+
+int32_t rfgpu_profile_gap_ms(rfgpu_ctx* ctx, int32_t i, double* gap_ms) {
+  if (!ctx || !gap_ms || i < 0 || i >= (int32_t)ctx->kstats.size()) return RFGPU_E_INVALID;
+  *gap_ms = ctx->kstats[i].second.gap_ms;
   return RFGPU_OK;
 }
 

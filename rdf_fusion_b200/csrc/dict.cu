@@ -206,6 +206,7 @@ int32_t rfgpu_dict_decode(rfgpu_ctx* ctx, const rfgpu_dict* d, const rfgpu_table
   RF_API_BEGIN
   using namespace rf;
   RF_REQUIRE(ctx && d && t && out, RFGPU_E_INVALID, "NULL argument");
+  rf::settle(t);  // lazy row count (rf_common.hpp)
   RF_REQUIRE(col >= 0 && col < (int32_t)t->cols.size(), RFGPU_E_INVALID, "column index out of range");
   RF_REQUIRE(row_off <= t->rows && n_rows <= t->rows - row_off, RFGPU_E_INVALID, "row range out of bounds");
   RF_REQUIRE(n_rows < 0x7FFFFFFFull, RFGPU_E_UNSUPPORTED, "an Arrow Utf8 batch holds at most 2^31-2 rows");
@@ -271,6 +272,7 @@ int32_t rfgpu_table_lookup(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t col, co
   RF_API_BEGIN
   using namespace rf;
   RF_REQUIRE(ctx && t && out && name && (table || n_table == 0), RFGPU_E_INVALID, "NULL argument");
+  rf::settle(t);  // lazy row count (rf_common.hpp)
   RF_REQUIRE(col >= 0 && col < (int32_t)t->cols.size(), RFGPU_E_INVALID, "column index out of range");
   RF_REQUIRE(find_col(t, name) < 0, RFGPU_E_INVALID, std::string("duplicate column name ") + name);
   RF_REQUIRE(t->cols.size() < (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 columns");

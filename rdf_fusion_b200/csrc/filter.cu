@@ -146,7 +146,7 @@ k_filter_compact(const __grid_constant__ FilterArgs A, unsigned long long* __res
 }
 
 uint64_t filter_compact(rfgpu_ctx* ctx, const std::vector<DevPred>& preds, const std::vector<const uint32_t*>& src,
-                        uint64_t n, std::vector<BufRef>* out, const char* kernel_name, uint64_t bytes_in) {
+                        uint64_t n, std::vector<BufRef>* out, const char* kernel_name, uint64_t bytes_in, int* lazy_slot) {
   RF_REQUIRE(preds.size() <= (size_t)kMaxPreds, RFGPU_E_UNSUPPORTED, "more than 8 conjuncts in one filter");
   RF_REQUIRE(src.size() <= (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 columns in one filter");
   out->clear();
@@ -168,9 +168,17 @@ uint64_t filter_compact(rfgpu_ctx* ctx, const std::vector<DevPred>& preds, const
   auto status = ctx->alloc((uint64_t)tiles * 8 + 8);
   RF_CUDA(cudaMemsetAsync(status->ptr, 0, (uint64_t)tiles * 8 + 8, ctx->stream()));
   unsigned long long* d_total = status->as<unsigned long long>() + tiles;
+  // lazy row count (rf_common.hpp, LazyRows): the kept count goes to a device word the caller attaches to its table; the
+  // buffers hold n rows, which a filter cannot exceed
+  const int slot = (lazy_slot && ctx->lazy_enabled()) ? ctx->lazy_take() : -1;
+  if (slot >= 0) d_total = ctx->lazy_d + slot;
   {
     KernelScope ks(ctx, kernel_name, bytes_in);
     k_filter_compact<<<tiles, kFThreads, 0, ctx->stream()>>>(A, status->as<unsigned long long>(), d_total);
+  }
+  if (slot >= 0) {
+    *lazy_slot = slot;
+    return n;
   }
   RF_CUDA(cudaMemcpyAsync(ctx->h_scratch, d_total, 8, cudaMemcpyDeviceToHost, ctx->stream()));
   ctx->sync();
@@ -367,6 +375,7 @@ extern "C" int32_t rfgpu_filter(rfgpu_ctx* ctx, const rfgpu_table* in, const rfg
   RF_API_BEGIN
   using namespace rf;
   RF_REQUIRE(ctx && in && out && n >= 0 && (preds || n == 0), RFGPU_E_INVALID, "NULL / negative argument");
+  rf::settle(in);  // lazy row count (rf_common.hpp)
   RF_CUDA(cudaSetDevice(ctx->core->device));
   int nc = (int)in->cols.size();
   std::vector<DevPred> dp;
@@ -410,9 +419,15 @@ extern "C" int32_t rfgpu_filter(rfgpu_ctx* ctx, const rfgpu_table* in, const rfg
   // algorithmic bytes: predicate columns once + remaining output columns once (+ output, added later)
   uint64_t bytes_in = 4ull * in->rows * (uint64_t)std::max<int>(nc, __builtin_popcountll(pred_cols_mask));
   std::vector<BufRef> bufs;
-  uint64_t kept = filter_compact(ctx, dp, src, in->rows, &bufs, "k_filter_compact", bytes_in);
+  int slot = -1;
+  uint64_t kept = filter_compact(ctx, dp, src, in->rows, &bufs, "k_filter_compact", bytes_in, &slot);
   std::unique_ptr<rfgpu_table> t(new_table());
   t->rows = kept;
+  if (slot >= 0)  // `kept` is the capacity (= the input's rows): never too small, so there is nothing to run again
+    attach_lazy(
+        ctx, t.get(), slot, kept, {},
+        []() -> rfgpu_table* { throw Error(RFGPU_E_EXEC, "a filter result cannot exceed its input"); },
+        [ctx, nc](uint64_t n) { ctx->kstats[ctx->kstat_index("k_filter_compact")].second.bytes += 4ull * nc * n; });
   t->sorted_col = in->sorted_col;  // order-preserving compaction
   t->has_bounds = in->has_bounds;  // a filter only drops rows: the bounds stay valid
   t->sorted_min = in->sorted_min;

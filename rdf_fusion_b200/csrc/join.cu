@@ -18,9 +18,28 @@ namespace rf {
 
 namespace {
 
+// Set by a join kernel launch that did not wait for its row count (rf_common.hpp, LazyRows): the count lands in
+// ctx->lazy_d[slot]; the function returned the capacity `cap` of the buffers instead.  An unclaimed slot goes back.
+struct LazyOut {
+  rfgpu_ctx* ctx;
+  int slot = -1;
+  uint64_t cap = 0;
+  std::function<void(uint64_t)> account;  // the part of the kernel's byte accounting that needs the exact output count
+  explicit LazyOut(rfgpu_ctx* c) : ctx(c) {}
+  ~LazyOut() {
+    if (slot >= 0) ctx->lazy_pool->free.push_back(slot);
+  }
+  int claim() {
+    int s = slot;
+    slot = -1;
+    return s;
+  }
+};
+
 // streaming merge join of two inputs sorted on their single key column; returns the output row count and fills `bufs`
+// (`lz` non-NULL and lazy row counts enabled: returns the capacity at once, see LazyOut)
 uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint32_t* bk, uint64_t nb, bool left,
-                    const std::vector<OutColSpec>& specs, std::vector<BufRef>* bufs) {
+                    const std::vector<OutColSpec>& specs, std::vector<BufRef>* bufs, LazyOut* lz = nullptr) {
   bufs->clear();
   if (np == 0) {
     for (size_t c = 0; c < specs.size(); c++) bufs->push_back(alloc_col(ctx, 0));
@@ -61,6 +80,8 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
     }
     A.cap = cap;
     RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_tiles * 8, ctx->stream()));  // look-back words
+    const int slot = (lz && attempt == 0 && ctx->lazy_enabled()) ? ctx->lazy_take() : -1;
+    if (slot >= 0) A.total = ctx->lazy_d + slot;
     {
       KernelScope ks(ctx, "k_merge_join", 4ull * (np + nb));  // keys; payload + output bytes are added below
       switch (threads) {
@@ -68,6 +89,15 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
         case 128: k_merge_join<128><<<n_tiles, 128, 0, ctx->stream()>>>(A); break;
         default: k_merge_join<256><<<n_tiles, 256, 0, ctx->stream()>>>(A); break;
       }
+    }
+    if (slot >= 0) {  // the caller attaches the pending count to the output table
+      lz->slot = slot;
+      lz->cap = cap;
+      const uint64_t fixed = 4ull * (in_cols_p * np + in_cols_b * nb), per_row = 4ull * specs.size();
+      lz->account = [ctx, fixed, per_row](uint64_t n) {
+        ctx->kstats[ctx->kstat_index("k_merge_join")].second.bytes += fixed + per_row * n;
+      };
+      return cap;
     }
     RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 10, A.total, 8, cudaMemcpyDeviceToHost, ctx->stream()));
     ctx->sync();
@@ -176,8 +206,11 @@ BufRef dense_table_unsorted(rfgpu_ctx* ctx, const uint32_t* bk, uint64_t nb, con
 
 // Equi join through the direct-address table; `specs` as for merge_join (probe columns by probe row, build columns by
 // build row).  Returns the output row count and fills `bufs`.
+// `np_dev` non-NULL: the probe side's row count is still on the device — np is its capacity (k_lookup_join, kPersist).
 uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint32_t* bk, uint64_t nb, bool build_sorted,
-                     bool left, const DenseRange& D, std::vector<OutColSpec> specs, std::vector<BufRef>* bufs) {
+                     bool left, const DenseRange& D, std::vector<OutColSpec> specs, std::vector<BufRef>* bufs,
+                     LazyOut* lz = nullptr, const unsigned long long* np_dev = nullptr,
+                     const rfgpu_table* probe_table = nullptr /* of np_dev: its exact rows, once settled, for the accounting */) {
   bufs->clear();
   if (np == 0) {
     for (size_t c = 0; c < specs.size(); c++) bufs->push_back(alloc_col(ctx, 0));
@@ -218,6 +251,7 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
   LookupArgs A{};
   A.pk = pk;
   A.np = np;
+  A.np_dev = np_dev;
   A.offs = offs;
   A.kmin = D.kmin;
   A.range = D.range;
@@ -238,7 +272,8 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
   if (mode == 2) {
     RF_CUDA(cudaMemsetAsync(tab2->ptr, 0, (uint64_t)groups * 8 + 16, ctx->stream()));
     KernelScope ks(ctx, "k_dense_heads_compact", 4ull * nb + 2ull * D.range);
-    k_dense_heads_compact<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(bk, nb, D.kmin, D.stride, tab2->as<uint2>());
+    k_dense_heads_compact<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(bk, nb, D.kmin, D.stride, tab2->as<uint2>(),
+                                                                             np_dev, np);
   } else {
     RF_CUDA(cudaMemsetAsync(d_over, 0, 16, ctx->stream()));
     if (groups) {
@@ -257,7 +292,8 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
     in_cols_p += specs[c].probe != nullptr && specs[c].probe != pk;
   }
   const uint64_t kLimit = 0xFFFFFFFEull;
-  uint64_t cap = std::min<uint64_t>(kLimit, 2 * std::max(np, nb) + 1024);  // optimistic, as in merge_join()
+  // optimistic, as in merge_join(); a probe side that is itself an optimistic capacity is not doubled again
+  uint64_t cap = std::min<uint64_t>(kLimit, (np_dev ? std::max(np, nb) : 2 * std::max(np, nb)) + 1024);
   uint64_t n_out = 0;
   for (int attempt = 0;; attempt++) {
     bufs->clear();
@@ -267,9 +303,37 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
     }
     A.cap = cap;
     RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_tiles * 8, ctx->stream()));
+    const int slot = (lz && attempt == 0 && ctx->lazy_enabled()) ? ctx->lazy_take() : -1;
+    if (slot >= 0) A.total = ctx->lazy_d + slot;
+    RF_REQUIRE(!np_dev || slot >= 0, RFGPU_E_EXEC, "a pending probe side needs a lazy output");  // sparql_join settles otherwise
     {
-      KernelScope ks(ctx, "k_lookup_join", 4ull * np);
-      k_lookup_join<128><<<n_tiles, 128, 0, ctx->stream()>>>(A);
+      KernelScope ks(ctx, "k_lookup_join", np_dev ? 0 : 4ull * np);
+      if (!np_dev) {
+        k_lookup_join<128, false><<<n_tiles, 128, 0, ctx->stream()>>>(A);
+      } else {
+        uint32_t grid = n_tiles;  // host build (tests/emu): CTAs run one after the other, one tile each
+#ifdef __CUDACC__
+        // every CTA co-resident: the look-back of a striding CTA waits on tiles of running CTAs only
+        static int per_sm_of[64] = {};  // per device; the answer does not change
+        int& per_sm = per_sm_of[ctx->core->device & 63];
+        if (per_sm == 0) RF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_lookup_join<128, true>, 128, 0));
+        RF_REQUIRE(per_sm > 0, RFGPU_E_EXEC, "lookup join kernel cannot be resident");
+        grid = std::min<uint32_t>(n_tiles, (uint32_t)(ctx->core->num_sms * per_sm));
+#endif
+        k_lookup_join<128, true><<<grid, 128, 0, ctx->stream()>>>(A);
+      }
+    }
+    if (slot >= 0) {
+      lz->slot = slot;
+      lz->cap = cap;
+      const uint64_t build_bytes = 4ull * (build_sorted ? (1 + in_cols_b) * nb : 0), per_row = 4ull * specs.size();
+      const uint64_t np_known = np_dev ? 0 : np;
+      lz->account = [ctx, build_bytes, per_row, in_cols_p, np_known, probe_table](uint64_t n) {
+        const uint64_t np_exact = probe_table ? probe_table->rows : np_known;  // settled before this runs (a retained input)
+        ctx->kstats[ctx->kstat_index("k_lookup_join")].second.bytes +=
+            4ull * in_cols_p * np_exact + (probe_table ? 4ull * np_exact : 0) + build_bytes + per_row * n;
+      };
+      return cap;
     }
     RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 10, A.total, 8, cudaMemcpyDeviceToHost, ctx->stream()));
     ctx->sync();
@@ -647,7 +711,9 @@ static rfgpu_table* drop_hidden(const rfgpu_table* t, const char* drop = nullptr
   return o.release();
 }
 
-rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table* R, int join_type) {
+// allow_lazy (the C entry point only): the result of a single-key equi join may come back with its row count still on the
+// device, and a probe side in that state is consumed as it is (rf_common.hpp, LazyRows)
+rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table* R, int join_type, bool allow_lazy = false) {
   RF_REQUIRE(join_type == RFGPU_JOIN_INNER || join_type == RFGPU_JOIN_LEFT, RFGPU_E_INVALID, "bad join type");
   const bool left = join_type == RFGPU_JOIN_LEFT;
   // join keys: shared variable names, sorted (join/rewrite.rs:95-99)
@@ -664,6 +730,14 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
   const int algo = keys.empty() ? RFGPU_JOIN_ALGO_CROSS : (any_nullable ? RFGPU_JOIN_ALGO_COMPATIBLE : RFGPU_JOIN_ALGO_EQUI);
   ctx->last_join_algo = algo;
   ctx->last_join_phys = RFGPU_JOIN_PHYS_NONE;
+  // Only the merge join and the direct-address join below leave their output pending or read a pending probe side; every
+  // other path needs exact input sizes on the host now.
+  const bool lazy_path = allow_lazy && ctx->lazy_enabled() && algo == RFGPU_JOIN_ALGO_EQUI && keys.size() == 1 &&
+                         !ctx->opt_sort_merge_join && !ctx->opt_radix_join;
+  if (!lazy_path) {
+    settle(L);
+    settle(R);
+  }
 
   // output schema: lhs fields, then rhs-only fields (join/logical.rs:251-279)
   std::vector<int> rhs_only;
@@ -696,12 +770,17 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
     c.mod_r = R->cols[j].mod_r;
     T->cols.push_back(c);
   }
-  auto finish = [&](std::vector<BufRef>& bufs, uint64_t rows) {
+  auto finish = [&](std::vector<BufRef>& bufs, uint64_t rows, LazyOut* lz = nullptr) {
     for (size_t c = 0; c < nout; c++) {
       T->cols[c].owner = bufs[c];
       T->cols[c].data = bufs[c]->as<uint32_t>();
     }
     T->rows = rows;
+    if (lz && lz->slot >= 0) {  // `rows` is the capacity; the inputs stay alive for a second run should it be too small
+      const uint64_t cap = lz->cap;
+      attach_lazy(ctx, T.get(), lz->claim(), cap, {L, R},
+                  [ctx, L, R, join_type]() { return sparql_join(ctx, L, R, join_type, false); }, std::move(lz->account));
+    }
     ctx->m.join_rows_out += rows;
     ctx->m.algorithmic_bytes += 4ull * (nl * L->rows + R->cols.size() * R->rows + nout * rows);
     return T.release();
@@ -796,13 +875,22 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
       ctx->last_join_phys = RFGPU_JOIN_PHYS_SORT_MERGE;
       return out;
     }
+    if (lazy_path) {
+      settle(Bt);
+      const bool merge_path = ctx->opt_merge_join && L->sorted_col == keys[0].l && R->sorted_col == keys[0].r;
+      if (Pt->lazy && (merge_path || !ctx->opt_lookup_join || ctx->lazy_pool->free.empty())) settle(Pt);
+    }
     ctx->m.join_probe_rows += Pt->rows;
     ctx->m.join_build_rows += Bt->rows;
-    std::vector<OutColSpec> specs;
-    for (size_t i = 0; i < nl; i++)
-      specs.push_back(probe_is_l ? OutColSpec{L->cols[i].data, nullptr} : OutColSpec{nullptr, L->cols[i].data});
-    for (int j : rhs_only)
-      specs.push_back(probe_is_l ? OutColSpec{nullptr, R->cols[j].data} : OutColSpec{R->cols[j].data, nullptr});
+    auto make_specs = [&]() {  // column pointers: taken again after a settle() that may have recomputed an input
+      std::vector<OutColSpec> sp;
+      for (size_t i = 0; i < nl; i++)
+        sp.push_back(probe_is_l ? OutColSpec{L->cols[i].data, nullptr} : OutColSpec{nullptr, L->cols[i].data});
+      for (int j : rhs_only)
+        sp.push_back(probe_is_l ? OutColSpec{nullptr, R->cols[j].data} : OutColSpec{R->cols[j].data, nullptr});
+      return sp;
+    };
+    std::vector<OutColSpec> specs = make_specs();
     // output rows come out in probe order: a sorted probe side keeps the result sorted on the same variable
     int out_sorted = -1;
     if (Pt->sorted_col >= 0) {
@@ -819,10 +907,11 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
     if (ctx->opt_merge_join && keys.size() == 1 && L->sorted_col == keys[0].l && R->sorted_col == keys[0].r &&
         Pt->rows > 0) {
       std::vector<BufRef> bufs;
-      uint64_t n_out = merge_join(ctx, kc(Pt, 0), Pt->rows, kc(Bt, 0), Bt->rows, left, specs, &bufs);
+      LazyOut lz(ctx);
+      uint64_t n_out = merge_join(ctx, kc(Pt, 0), Pt->rows, kc(Bt, 0), Bt->rows, left, specs, &bufs, lazy_path ? &lz : nullptr);
       ctx->last_join_phys = RFGPU_JOIN_PHYS_MERGE;
       T->sorted_col = keys[0].l;
-      return finish(bufs, n_out);
+      return finish(bufs, n_out, &lz);
     }
     // dense build keys (object ids are dictionary ids): identity-hash table, one u32 per possible key, probe = one 16-byte
     // load from an L2-resident table; a build side sorted on the key needs no counting sort
@@ -840,11 +929,18 @@ rfgpu_table* sparql_join(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgpu_table
       }
       if (D.ok) {
         std::vector<BufRef> bufs;
-        const uint64_t n_out = lookup_join(ctx, kc(Pt, 0), Pt->rows, kc(Bt, 0), Bt->rows, bsorted, left, D, specs, &bufs);
+        LazyOut lz(ctx);
+        const unsigned long long* np_dev = Pt->lazy ? ctx->lazy_d + Pt->lazy->slot : nullptr;
+        const uint64_t n_out = lookup_join(ctx, kc(Pt, 0), Pt->rows, kc(Bt, 0), Bt->rows, bsorted, left, D, specs, &bufs,
+                                           lazy_path ? &lz : nullptr, np_dev, np_dev ? Pt : nullptr);
         ctx->last_join_phys = RFGPU_JOIN_PHYS_LOOKUP;
         T->sorted_col = out_sorted;
-        return finish(bufs, n_out);
+        return finish(bufs, n_out, &lz);
       }
+    }
+    if (Pt->lazy) {  // the hash paths below size their buffers from exact counts
+      settle(Pt);
+      specs = make_specs();
     }
     if (ctx->opt_radix_join && Bt->rows >= (uint64_t)ctx->opt_radix_min_rows) {
       std::vector<BufRef> bufs;
@@ -1184,6 +1280,7 @@ rfgpu_table* sparql_join_filter(rfgpu_ctx* ctx, const rfgpu_table* L, const rfgp
                                 const rfgpu_filter_pred* preds, int n_preds) {
   RF_REQUIRE(join_type == RFGPU_JOIN_INNER || join_type == RFGPU_JOIN_LEFT, RFGPU_E_INVALID, "bad join type");
   if (n_preds == 0) return sparql_join(ctx, L, R, join_type);
+  LazyOff lazy_off(ctx);  // this composition (and its callers in this file) read row counts of intermediate results on the host
   const bool left = join_type == RFGPU_JOIN_LEFT;
   const size_t nl = L->cols.size();
   static const char* kRid = "\x01rid";  // not a SPARQL variable name
@@ -1269,7 +1366,7 @@ int32_t rfgpu_sparql_join(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_ta
   RF_API_BEGIN
   RF_REQUIRE(ctx && lhs && rhs && out, RFGPU_E_INVALID, "NULL argument");
   RF_CUDA(cudaSetDevice(ctx->core->device));
-  *out = rf::sparql_join(ctx, lhs, rhs, join_type);
+  *out = rf::sparql_join(ctx, lhs, rhs, join_type, /*allow_lazy=*/true);
   RF_API_END(ctx)
 }
 
@@ -1277,6 +1374,8 @@ int32_t rfgpu_sparql_join_filter(rfgpu_ctx* ctx, const rfgpu_table* lhs, const r
                                  const rfgpu_filter_pred* preds, int32_t n_preds, rfgpu_table** out) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && lhs && rhs && out && n_preds >= 0 && (preds || n_preds == 0), RFGPU_E_INVALID, "NULL / negative argument");
+  rf::settle(lhs);  // lazy row count (rf_common.hpp)
+  rf::settle(rhs);  // lazy row count (rf_common.hpp)
   RF_CUDA(cudaSetDevice(ctx->core->device));
   *out = rf::sparql_join_filter(ctx, lhs, rhs, join_type, preds, n_preds);
   RF_API_END(ctx)
@@ -1285,6 +1384,8 @@ int32_t rfgpu_sparql_join_filter(rfgpu_ctx* ctx, const rfgpu_table* lhs, const r
 int32_t rfgpu_sparql_minus(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_table* rhs, rfgpu_table** out) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && lhs && rhs && out, RFGPU_E_INVALID, "NULL argument");
+  rf::settle(lhs);  // lazy row count (rf_common.hpp)
+  rf::settle(rhs);  // lazy row count (rf_common.hpp)
   RF_CUDA(cudaSetDevice(ctx->core->device));
   *out = rf::semi_anti_join(ctx, lhs, rhs, rf::SemiMode::kMinus);
   RF_API_END(ctx)
@@ -1294,6 +1395,8 @@ int32_t rfgpu_sparql_exists(rfgpu_ctx* ctx, const rfgpu_table* lhs, const rfgpu_
                             rfgpu_table** out) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && lhs && rhs && out, RFGPU_E_INVALID, "NULL argument");
+  rf::settle(lhs);  // lazy row count (rf_common.hpp)
+  rf::settle(rhs);  // lazy row count (rf_common.hpp)
   RF_CUDA(cudaSetDevice(ctx->core->device));
   *out = rf::semi_anti_join(ctx, lhs, rhs, negated ? rf::SemiMode::kNotExists : rf::SemiMode::kExists);
   RF_API_END(ctx)
@@ -1308,6 +1411,7 @@ int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value) {
   switch (option) {
     case RFGPU_OPT_MERGE_JOIN: ctx->opt_merge_join = value != 0; break;
     case RFGPU_OPT_LOOKUP_JOIN: ctx->opt_lookup_join = value != 0; break;
+    case RFGPU_OPT_LAZY_ROWS: ctx->opt_lazy_rows = value != 0; break;
     case RFGPU_OPT_SORT_MERGE_JOIN: ctx->opt_sort_merge_join = value != 0; break;
     case RFGPU_OPT_SORT_SEMI: ctx->opt_sort_semi = value != 0; break;
     case RFGPU_OPT_SORT_AGG: ctx->opt_sort_agg = value != 0; break;

@@ -116,8 +116,14 @@ k_dense_fill(const __grid_constant__ DenseFillArgs A) {
 // the host: the head of every key run publishes its start with one atomicMax on the complemented value (the smallest start
 // of the group wins) and stores its count byte; a run of 255 rows or more stores 255, which marks the whole group "heavy" —
 // the probe resolves keys of heavy groups by binary search over the sorted keys instead (k_lookup_join, mode 2).
+// np_dev non-NULL (pending probe side, k_lookup_join<kPersist>): when the probe side turns out tiny next to the build side the
+// probe kernel searches the sorted keys instead (lookup_searches() — both kernels evaluate the same test) and no table is needed.
+__device__ __forceinline__ bool lookup_searches(uint64_t np, uint64_t nb) { return np * 16 <= nb; }
+
 __global__ void __launch_bounds__(256)
-k_dense_heads_compact(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t kstride, uint2* __restrict__ tab2) {
+k_dense_heads_compact(const uint32_t* __restrict__ bk, uint64_t nb, uint32_t kmin, uint32_t kstride, uint2* __restrict__ tab2,
+                      const unsigned long long* __restrict__ np_dev, uint64_t np_cap) {
+  if (np_dev && lookup_searches(min((uint64_t)*np_dev, np_cap), nb)) return;
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (; i < nb; i += stride) {
@@ -211,6 +217,7 @@ k_dense_compress(const uint32_t* __restrict__ offs, uint32_t range, uint2* __res
 struct LookupArgs {
   const uint32_t* pk;  // probe keys (any order, 0 = NULL never matches)
   uint64_t np;
+  const unsigned long long* np_dev;  // non-NULL (kPersist): the probe row count is min(np, *np_dev)
   const uint32_t* offs;  // [range + 1], any 4-byte alignment; the 16-byte look-up reads the enclosing aligned granule, so the
                          // allocation has >= 3 readable words on either side
   uint32_t kmin, range;
@@ -248,22 +255,22 @@ struct LookupSmem {
   uint32_t wmax[kLThreads / 32];
 };
 
+// one tile of probe rows; `np` / `n_tiles` are the EFFECTIVE probe row count and tile count (see k_lookup_join)
 template <int kLThreads>
-__global__ void __launch_bounds__(kLThreads, kLThreads == 128 ? 12 : 1)
-k_lookup_join(const __grid_constant__ LookupArgs A) {
+__device__ __forceinline__ void lookup_tile(const LookupArgs& A, LookupSmem<kLThreads>& S, const uint32_t tile,
+                                            const uint64_t np, const uint32_t n_tiles, const int mode) {
   constexpr int kTile = kLThreads * 8, kChunk = kTile;
-  __shared__ LookupSmem<kLThreads> S;
-  const uint32_t tile = blockIdx.x, tid = threadIdx.x;
+  const uint32_t tid = threadIdx.x;
   const uint32_t lane = tid & 31, warp = tid >> 5;
   const uint64_t row0 = (uint64_t)tile * kTile;
-  const uint32_t rows = (uint32_t)min((uint64_t)kTile, A.np - row0);
+  const uint32_t rows = row0 < np ? (uint32_t)min((uint64_t)kTile, np - row0) : 0u;
   const uint32_t leftpad = A.left ? 1u : 0u;
   // the table is probed at random by every tile and should stay in L2; keys, probe payload and output only stream through
   const uint64_t keep = dev::l2_policy_evict_last(), strm = dev::l2_policy_evict_first();
 
   // ---- keys (coalesced, striped) and table look-ups ----
-  const bool wide = A.mode == 0 && __ldg(A.overflow) != 0;  // uniform over the grid
-  if (A.mode == 1) {  // search mode: lower_bound(key) and upper_bound(key), 4 rows' searches in lockstep
+  const bool wide = mode == 0 && __ldg(A.overflow) != 0;  // uniform over the grid
+  if (mode == 1) {  // search mode: lower_bound(key) and upper_bound(key), 4 rows' searches in lockstep
 #pragma unroll 1
     for (int h = 0; h < 2; h++) {
       uint32_t key[4], lo[4], hi[4], lo2[4], hi2[4];
@@ -323,7 +330,7 @@ k_lookup_join(const __grid_constant__ LookupArgs A) {
       uint32_t cnt = (w[k].y >> sh) & 255u;
       uint32_t o0 = ~w[k].x + __dp4a(w[k].y & ((1u << sh) - 1u), 0x01010101u, 0u);  // + counts of the keys before it
       // mode 2: a count byte of 255 anywhere in the group = "255 rows or more": exact bounds from the sorted keys
-      if (A.mode == 2 && slot[k] < A.range && ((w[k].y & 0x7F7F7F7Fu) + 0x01010101u & w[k].y & 0x80808080u) != 0)
+      if (mode == 2 && slot[k] < A.range && ((w[k].y & 0x7F7F7F7Fu) + 0x01010101u & w[k].y & 0x80808080u) != 0)
         sorted_group(A.bk_sorted, A.nb_sorted, key[k], &o0, &cnt);
       S.gs[i] = cnt ? o0 : kNone;
       S.off[i] = i < rows ? (cnt ? cnt : leftpad) : 0u;
@@ -403,7 +410,7 @@ k_lookup_join(const __grid_constant__ LookupArgs A) {
       const unsigned long long excl = dev::lookback_resolve(A.status, tile, tot);
       if (lane == 0) {
         S.base = excl;
-        if (tile == A.n_tiles - 1) *A.total = excl + tot;
+        if (tile == n_tiles - 1) *A.total = excl + tot;
       }
     }
   };
@@ -499,6 +506,28 @@ k_lookup_join(const __grid_constant__ LookupArgs A) {
       }
     }
     __syncthreads();
+  }
+}
+
+// kPersist = false: one tile per CTA (the host knows the probe row count).  kPersist = true: the probe side is a table whose
+// row count is still on the device (rf_common.hpp, LazyRows): A.np is its capacity, *A.np_dev the count; a grid of co-resident
+// CTAs strides over the tiles that exist (static assignment in tile order, so the look-back never waits on a CTA that is not
+// running) instead of launching one CTA per tile of the capacity.
+template <int kLThreads, bool kPersist>
+__global__ void __launch_bounds__(kLThreads, kLThreads == 128 ? 12 : 1)
+k_lookup_join(const __grid_constant__ LookupArgs A) {
+  __shared__ LookupSmem<kLThreads> S;
+  if (!kPersist) {
+    lookup_tile<kLThreads>(A, S, blockIdx.x, A.np, A.n_tiles, A.mode);
+  } else {
+    const uint64_t np = min(A.np, (uint64_t)*A.np_dev);
+    const uint32_t n_tiles = max(1u, (uint32_t)((np + kLThreads * 8 - 1) / (kLThreads * 8)));  // tile 0 reports an empty input
+    // a sorted build side that dwarfs the probe side: search it (k_dense_heads_compact made the same test and built nothing)
+    const int mode = (A.mode == 2 && lookup_searches(np, A.nb_sorted)) ? 1 : A.mode;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      lookup_tile<kLThreads>(A, S, tile, np, n_tiles, mode);
+      __syncthreads();  // the shared tile state is reused
+    }
   }
 }
 

@@ -5,6 +5,7 @@
 
 #include <atomic>
 #include <cstdint>
+#include <functional>
 #include <map>
 #include <memory>
 #include <stdexcept>
@@ -72,10 +73,41 @@ struct Column {
 struct KernelStat {
   uint64_t launches = 0;
   double ms = 0;
+  double gap_ms = 0;  // stream time between the previous profiled kernel's end and this kernel's start
   uint64_t bytes = 0;
 };
 
 struct Comm;  // NCCL communicator wrapper (shuffle.cu)
+
+// A row count the host has not read yet.  An operator whose output size is only known on the device (join, filter) can
+// return at once: its table's `rows` is then the CAPACITY it allocated, the exact count sits in a device word
+// (ctx->lazy_d[slot], read by consumer kernels that take their row count from the device) and is copied to its pinned
+// mirror (ctx->lazy_h[slot]) in stream order.  rf::settle() turns such a table into an ordinary one the first time the host
+// needs the count: one stream synchronisation — none if the stream was synchronised since — and, when the producer's
+// optimistic capacity was too small (count > cap: the kernel wrote nothing beyond cap), a second, exactly sized run of the
+// producer from its retained inputs (`redo`), after settling those first.  The reference streams record batches between
+// operators without a barrier of this kind at all (scan.rs:101-213).
+struct LazyPool {  // shared by the ctx and the pending tables (a table may be released after its ctx)
+  unsigned long long* d = nullptr;  // device words
+  uint64_t* h = nullptr;            // pinned mirrors
+  std::vector<int> free;
+  void (*release)(LazyPool*) = nullptr;  // frees d and h (ctx.cu; tests/emu has its own)
+  ~LazyPool() {
+    if (release) release(this);
+  }
+};
+struct LazyRows {
+  rfgpu_ctx* ctx = nullptr;
+  std::shared_ptr<LazyPool> pool;
+  int slot = -1;
+  uint64_t cap = 0;
+  uint64_t epoch = 0;                     // ctx->sync_epoch when the producer was queued
+  std::vector<rfgpu_table*> deps;         // retained inputs
+  std::function<rfgpu_table*()> redo;     // synchronous re-execution (lazy outputs off)
+  std::function<void(uint64_t)> account;  // byte accounting that needs the exact count (rfgpu_ctx_profile), run by settle()
+  ~LazyRows();
+};
+constexpr int kLazySlots = 512;
 
 }  // namespace rf
 
@@ -89,6 +121,7 @@ struct rfgpu_table {
   // bounds needs no device read of its own.
   bool has_bounds = false;
   uint32_t sorted_min = 0, sorted_max = 0;
+  std::unique_ptr<rf::LazyRows> lazy;  // non-null: `rows` is a capacity, the count is still on the device (rf::settle)
 };
 
 struct rfgpu_index_t {
@@ -136,6 +169,11 @@ struct rfgpu_ctx {
   std::vector<std::pair<std::string, rf::KernelStat>> kstats;
   struct Pending { int idx; cudaEvent_t a, b; };
   std::vector<Pending> pending;
+  // optional launch timeline (rfgpu_profile_timeline): start / end of every profiled launch, microseconds since the first
+  struct Launch { int idx; float start_us, end_us; };
+  bool timeline_on = false;
+  cudaEvent_t timeline_t0 = nullptr;
+  std::vector<Launch> timeline;
   std::vector<cudaEvent_t> event_pool;
   cudaEvent_t t0 = nullptr, t1 = nullptr;
   void* flush_buf = nullptr;
@@ -147,9 +185,39 @@ struct rfgpu_ctx {
   cudaEvent_t copy_event = nullptr;
   std::vector<rfgpu_table*> pending_exports;
 
+  // lazy row counts (rf::LazyRows): device words + pinned mirrors, a free list of slots, the number of host syncs so far
+  bool opt_lazy_rows = true;
+  std::shared_ptr<rf::LazyPool> lazy_pool;
+  unsigned long long* lazy_d = nullptr;  // = lazy_pool->d
+  uint64_t* lazy_h = nullptr;            // = lazy_pool->h
+  uint64_t sync_epoch = 0;
+  int lazy_off = 0;  // > 0 while a redo runs (its inner operators must finish synchronously)
+
   rf::BufRef alloc(size_t bytes) { return std::make_shared<rf::DevBuf>(core, bytes); }
   cudaStream_t stream() const { return core->stream; }
-  void sync() { RF_CUDA(cudaStreamSynchronize(core->stream)); }
+  void sync() {
+    RF_CUDA(cudaStreamSynchronize(core->stream));
+    sync_epoch++;
+    m_host_syncs++;
+  }
+  uint64_t m_host_syncs = 0, m_lazy_redos = 0;
+  // Range look-ups run on a stream of their own (highest priority): they read nothing but the immutable index (complete on
+  // the device when rfgpu_store_add_index returns), and the host waits for THEM, not for whatever the main stream still has
+  // queued — the next query's ranges arrive while the previous query's joins are running, and its kernels are queued behind
+  // them without the device going idle.
+  cudaStream_t lookup_stream_ = nullptr;
+  cudaStream_t lookup_stream();  // ctx.cu (tests/emu: the main stream)
+  void sync_lookup() {
+    RF_CUDA(cudaStreamSynchronize(lookup_stream()));
+    m_host_syncs++;
+  }
+  bool lazy_enabled() const { return opt_lazy_rows && lazy_off == 0 && lazy_d; }
+  int lazy_take() {  // -1: none free (the caller stays synchronous)
+    if (!lazy_pool || lazy_pool->free.empty()) return -1;
+    int s = lazy_pool->free.back();
+    lazy_pool->free.pop_back();
+    return s;
+  }
   // kernel launch accounting: KernelScope ks(ctx, "name", bytes); kernel<<<..., ctx->stream()>>>(...); (dtor closes)
   int kstat_index(const char* name);
   void collect_profile();
@@ -161,13 +229,26 @@ struct KernelScope {
   rfgpu_ctx* ctx;
   int idx = -1;
   cudaEvent_t a = nullptr, b = nullptr;
-  KernelScope(rfgpu_ctx* c, const char* name, uint64_t algorithmic_bytes = 0);
+  cudaStream_t stream = nullptr;
+  KernelScope(rfgpu_ctx* c, const char* name, uint64_t algorithmic_bytes = 0, cudaStream_t on = nullptr /* ctx stream */);
   ~KernelScope() noexcept(false);
 };
 
 inline uint32_t div_up(uint64_t a, uint64_t b) { return (uint32_t)((a + b - 1) / b); }
 
 rfgpu_table* new_table();
+// table.cu — lazy row counts (struct LazyRows above)
+// Makes `t` an ordinary table (exact `rows`); true when its contents were recomputed (pointers changed).
+bool settle(const rfgpu_table* t);
+// Queues the copy of ctx->lazy_d[slot] to its pinned mirror and marks `t` (whose buffers hold `cap` rows) as pending.
+// `deps` are retained; `redo` must produce the same table synchronously.
+void attach_lazy(rfgpu_ctx* ctx, rfgpu_table* t, int slot, uint64_t cap, std::vector<const rfgpu_table*> deps,
+                 std::function<rfgpu_table*()> redo, std::function<void(uint64_t)> account = nullptr);
+struct LazyOff {  // scope in which operators finish synchronously
+  rfgpu_ctx* c;
+  explicit LazyOff(rfgpu_ctx* ctx) : c(ctx) { c->lazy_off++; }
+  ~LazyOff() { c->lazy_off--; }
+};
 int placement_level(uint32_t perm, int mode);  // ctx.cu: level whose ids decide a quad's rank (-1: none)
 BufRef alloc_col(rfgpu_ctx* ctx, uint64_t rows);  // uint32_t[rows] (+pad)
 int find_col(const rfgpu_table* t, const std::string& name);
@@ -202,7 +283,8 @@ constexpr int kMaxCols = 16;
 // Evaluates preds over rows [0,n) and compacts `n_cols` source columns into freshly allocated outputs.
 // Returns the number of rows kept.
 uint64_t filter_compact(rfgpu_ctx* ctx, const std::vector<DevPred>& preds, const std::vector<const uint32_t*>& src,
-                        uint64_t n, std::vector<BufRef>* out, const char* kernel_name, uint64_t algorithmic_bytes_in);
+                        uint64_t n, std::vector<BufRef>* out, const char* kernel_name, uint64_t algorithmic_bytes_in,
+                        int* lazy_slot = nullptr);  // lazy_slot: see LazyRows — returns n and the slot the count goes to
 
 }  // namespace rf
 
@@ -223,3 +305,59 @@ uint64_t filter_compact(rfgpu_ctx* ctx, const std::vector<DevPred>& preds, const
 namespace rf {
 void set_error(const rfgpu_ctx* ctx, const std::string& msg);
 }
+
+// ---- lazy row counts (struct LazyRows): header-inline so that every build of these sources (library, tests/emu) has them ----
+namespace rf {
+
+inline LazyRows::~LazyRows() {
+  for (auto* d : deps) rfgpu_table_release(d);
+  if (pool && slot >= 0) pool->free.push_back(slot);
+}
+
+inline void attach_lazy(rfgpu_ctx* ctx, rfgpu_table* t, int slot, uint64_t cap, std::vector<const rfgpu_table*> deps,
+                        std::function<rfgpu_table*()> redo, std::function<void(uint64_t)> account) {
+  RF_CUDA(cudaMemcpyAsync(ctx->lazy_h + slot, ctx->lazy_d + slot, 8, cudaMemcpyDeviceToHost, ctx->stream()));
+  std::unique_ptr<LazyRows> z(new LazyRows());
+  z->ctx = ctx;
+  z->pool = ctx->lazy_pool;
+  z->slot = slot;
+  z->cap = cap;
+  z->epoch = ctx->sync_epoch;
+  for (auto* d : deps) z->deps.push_back(rfgpu_table_retain(const_cast<rfgpu_table*>(d)));
+  z->redo = std::move(redo);
+  z->account = std::move(account);
+  t->rows = cap;
+  t->lazy = std::move(z);
+}
+
+inline bool settle(const rfgpu_table* ct) {
+  rfgpu_table* t = const_cast<rfgpu_table*>(ct);
+  if (!t || !t->lazy) return false;
+  std::unique_ptr<LazyRows> z = std::move(t->lazy);  // t is an ordinary table from here on, whatever happens below
+  rfgpu_ctx* ctx = z->ctx;
+  bool changed = false;
+  for (auto* d : z->deps) changed |= settle(d);
+  if (!changed) {
+    if (z->epoch == ctx->sync_epoch) ctx->sync();
+    const uint64_t total = ctx->lazy_h[z->slot];
+    if (total <= z->cap) {
+      t->rows = total;
+      if (z->account) z->account(total);
+      return false;
+    }
+  }
+  // the optimistic capacity was too small, or an input was recomputed: run the producer again, synchronously
+  t->rows = 0;
+  LazyOff off(ctx);
+  std::unique_ptr<rfgpu_table> n(z->redo());
+  t->cols = std::move(n->cols);
+  t->rows = n->rows;
+  t->sorted_col = n->sorted_col;
+  t->has_bounds = n->has_bounds;
+  t->sorted_min = n->sorted_min;
+  t->sorted_max = n->sorted_max;
+  ctx->m_lazy_redos++;
+  return true;
+}
+
+}  // namespace rf

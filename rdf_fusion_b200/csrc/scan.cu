@@ -316,10 +316,10 @@ static void scan_execute_impl(rfgpu_ctx* ctx, const rfgpu_scan_plan* p, uint32_t
     have_ends = true;
   } else if (depth > 0) {
     {
-      KernelScope ks(ctx, "k_range_search");
-      k_range_search<<<2, kSearchThreads, 0, ctx->stream()>>>(S, (unsigned long long*)ctx->h_scratch);
+      KernelScope ks(ctx, "k_range_search", 0, ctx->lookup_stream());
+      k_range_search<<<2, kSearchThreads, 0, ctx->lookup_stream()>>>(S, (unsigned long long*)ctx->h_scratch);
     }
-    ctx->sync();
+    ctx->sync_lookup();  // waits for the look-up only, not for the main stream (rf_common.hpp)
     from = ctx->h_scratch[0];
     to = ctx->h_scratch[1];
     end_lo = ctx->h_scratch[2];
@@ -509,10 +509,10 @@ int32_t rfgpu_scan_execute_many(rfgpu_ctx* ctx, const rfgpu_scan_plan* const* pl
       }
       uint64_t* res = ctx->h_scratch + 256;  // [256, 288) ranges, [288, 320) the sort level's end values
       {
-        KernelScope ks(ctx, "k_range_search_many");
-        k_range_search_many<<<2 * q, kSearchThreads, 0, ctx->stream()>>>(B, (unsigned long long*)res);
+        KernelScope ks(ctx, "k_range_search_many", 0, ctx->lookup_stream());
+        k_range_search_many<<<2 * q, kSearchThreads, 0, ctx->lookup_stream()>>>(B, (unsigned long long*)res);
       }
-      ctx->sync();
+      ctx->sync_lookup();  // waits for the look-ups only, not for the main stream (rf_common.hpp)
       for (int i = 0; i < q; i++) {
         const uint64_t r4[4] = {res[2 * i], res[2 * i + 1], res[2 * kMaxBatch + 2 * i], res[2 * kMaxBatch + 2 * i + 1]};
         scan_execute_impl(ctx, plans[base + i], flags, &out[base + i], r4);

@@ -84,6 +84,7 @@ struct Comm {
   size_t arena_bytes = 0;
   bool p2p = false;
   uint64_t epoch = 0;  // shuffles done through the arenas; parity selects the half
+  uint64_t* h_counts = nullptr;  // pinned: the gathered (sent counts + stale flag) matrix of one shuffle
   void drop_arenas() {
     for (int r = 0; r < size; r++) {
       if (!arena[r]) continue;
@@ -95,6 +96,7 @@ struct Comm {
   }
   ~Comm() {
     drop_arenas();
+    if (h_counts) cudaFreeHost(h_counts);
     if (comm) nccl().CommDestroy(comm);
   }
 };
@@ -225,6 +227,7 @@ static std::vector<BufRef> partition(rfgpu_ctx* ctx, const rfgpu_table* in, int 
 struct P2pArgs {
   const uint32_t* key;
   uint64_t n;
+  const unsigned long long* n_dev;  // non-NULL: the row count is min(n, *n_dev)
   uint32_t n_parts;
   int32_t n_cols;
   uint64_t cap;                 // rows per column one arena half holds
@@ -307,28 +310,31 @@ k_shuffle_p2p(const __grid_constant__ P2pArgs A) {
     S.cnt[0][tid] = 0;
   }
   uint32_t nk[kP2pRows], v[kP2pRows], pk[kP2pRows], pn[kP2pRows];
-  uint64_t row0 = (uint64_t)blockIdx.x * kP2pTile;  // < n: the grid has at most one CTA per tile
+  uint64_t row0 = (uint64_t)blockIdx.x * kP2pTile;  // < A.n: the grid has at most one CTA per tile
+  // a table whose row count is still on the device (rf_common.hpp, LazyRows): A.n is its capacity
+  const uint64_t n = A.n_dev ? min(A.n, (uint64_t)*A.n_dev) : A.n;
+  if (row0 >= n) return;  // uniform over the CTA, before the first barrier
 #pragma unroll
   for (int k = 0; k < kP2pRows; k++) {
     const uint64_t i = row0 + k * kP2pThreads + tid;
-    nk[k] = i < A.n ? __ldg(A.key + i) : 0;
-    v[k] = i < A.n ? __ldg(A.src[0] + i) : 0;
+    nk[k] = i < n ? __ldg(A.key + i) : 0;
+    v[k] = i < n ? __ldg(A.src[0] + i) : 0;
   }
   __syncthreads();
-  p2p_ticket<kPow2>(nk, (uint32_t)min((uint64_t)kP2pTile, A.n - row0), A.n_parts, S.cnt[0], pk);
+  p2p_ticket<kPow2>(nk, (uint32_t)min((uint64_t)kP2pTile, n - row0), A.n_parts, S.cnt[0], pk);
 #pragma unroll
   for (int k = 0; k < kP2pRows; k++) {
     const uint64_t i = row0 + step + k * kP2pThreads + tid;
-    nk[k] = i < A.n ? __ldg(A.key + i) : 0;
+    nk[k] = i < n ? __ldg(A.key + i) : 0;
   }
   __syncthreads();
   unsigned long long base = 0;
   uint32_t cnt = 0;
   p2p_reserve(A, S, 0, base, cnt);
-  for (int b = 0; row0 < A.n; row0 += step, b ^= 1) {
-    const uint32_t rows = (uint32_t)min((uint64_t)kP2pTile, A.n - row0);
+  for (int b = 0; row0 < n; row0 += step, b ^= 1) {
+    const uint32_t rows = (uint32_t)min((uint64_t)kP2pTile, n - row0);
     const uint64_t next0 = row0 + step;
-    const uint32_t rows_next = next0 < A.n ? (uint32_t)min((uint64_t)kP2pTile, A.n - next0) : 0;
+    const uint32_t rows_next = next0 < n ? (uint32_t)min((uint64_t)kP2pTile, n - next0) : 0;
     if (tid < kMaxParts) S.cnt[b ^ 1][tid] = 0;
     __syncthreads();  // start[b] visible; the previous tile's write-out is over
     if (tid < A.n_parts)  // a run that does not fit the arena is dropped whole: the host sees the overflow and falls back
@@ -346,7 +352,7 @@ k_shuffle_p2p(const __grid_constant__ P2pArgs A) {
 #pragma unroll
     for (int k = 0; k < kP2pRows; k++) {
       const uint64_t i = next0 + step + k * kP2pThreads + tid;
-      nk[k] = i < A.n ? __ldg(A.key + i) : 0;
+      nk[k] = i < n ? __ldg(A.key + i) : 0;
     }
     __syncthreads();  // cnt[b^1] final; ptr / dest of this tile visible
     p2p_reserve(A, S, b ^ 1, base, cnt);
@@ -361,7 +367,7 @@ k_shuffle_p2p(const __grid_constant__ P2pArgs A) {
 #pragma unroll
         for (int k = 0; k < kP2pRows; k++) {
           const uint64_t i = r0 + k * kP2pThreads + tid;
-          v[k] = i < A.n ? __ldg(src + i) : 0;
+          v[k] = i < n ? __ldg(src + i) : 0;
         }
       }
       __syncthreads();
@@ -447,7 +453,18 @@ static void setup_arenas(rfgpu_ctx* ctx, Comm& c) {
 // Why no barrier before the kernel: shuffle k writes half k&1.  A peer's kernel of shuffle k starts after ITS all-gather of
 // shuffle k-1 completed, which needs MY all-gather of shuffle k-1 to have started, which in my stream follows my
 // copy-out and cursor reset of shuffle k-2 — the last use of half k&1.
-static bool shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col, rfgpu_table* t) {
+// flag[0] = 1 when the producer of a pending table wanted more rows than its buffers hold (the table is then garbage)
+__global__ void k_lazy_overflow(const unsigned long long* __restrict__ total, uint64_t cap, unsigned long long* __restrict__ flag) {
+  flag[0] = *total > cap ? 1ull : 0ull;
+}
+
+enum P2pResult { kP2pDone = 0, kP2pNoFit = 1, kP2pStaleInput = 2 };
+
+// A pending input (rf_common.hpp, LazyRows) is consumed as it is: the kernel takes the row count from the device, and whether
+// the table was valid at all (its producer's capacity guess held) travels with the sent counts, so that every rank learns it
+// in the same host hand-off and all of them repeat the exchange together after the affected ranks have recomputed their
+// input (kP2pStaleInput) — a rank must never decide alone to run a collective again.
+static P2pResult shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col, rfgpu_table* t) {
   Comm& cm = *ctx->comm;
   const int g = cm.size, me = cm.rank;
   const size_t C = in->cols.size();
@@ -455,13 +472,16 @@ static bool shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col, rfgp
   const uint64_t cap = ((half - kArenaCtrl) / (4 * C)) & ~31ull;
   const size_t off = (cm.epoch++ & 1) * half;
   const uint64_t n = in->rows;
-  BufRef d_cnt = ctx->alloc((uint64_t)(g + 1) * g * 8);
-  unsigned long long* d_sent = d_cnt->as<unsigned long long>() + (uint64_t)g * g;
-  RF_CUDA(cudaMemsetAsync(d_sent, 0, g * 8, ctx->stream()));
+  const int W = g + 1;  // words per rank in the gathered matrix: g sent counts + the stale-input flag
+  BufRef d_cnt = ctx->alloc((uint64_t)(g + 1) * W * 8);
+  unsigned long long* d_sent = d_cnt->as<unsigned long long>() + (uint64_t)g * W;
+  RF_CUDA(cudaMemsetAsync(d_sent, 0, W * 8, ctx->stream()));
+  const unsigned long long* n_dev = in->lazy ? ctx->lazy_d + in->lazy->slot : nullptr;
   if (n) {
     P2pArgs A{};
     A.key = in->cols[key_col].data;
     A.n = n;
+    A.n_dev = n_dev;
     A.n_parts = (uint32_t)g;
     A.n_cols = (int32_t)C;
     A.cap = cap;
@@ -475,22 +495,25 @@ static bool shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col, rfgp
   }
   // completion barrier + size exchange: a rank contributes only after its kernel (stream order), so when the gather
   // completes here every peer's stores into this arena are done
-  RF_NCCL(nccl().AllGather(d_sent, d_cnt->ptr, g, ncclUint64, cm.comm, ctx->stream()));
-  std::vector<uint64_t> all((size_t)g * g);
-  RF_CUDA(cudaMemcpyAsync(all.data(), d_cnt->ptr, (uint64_t)g * g * 8, cudaMemcpyDeviceToHost, ctx->stream()));
+  if (n_dev) k_lazy_overflow<<<1, 1, 0, ctx->stream()>>>(n_dev, in->lazy->cap, d_sent + g);
+  RF_NCCL(nccl().AllGather(d_sent, d_cnt->ptr, W, ncclUint64, cm.comm, ctx->stream()));
+  uint64_t* all = cm.h_counts;  // pinned: the copy is asynchronous and the sync below is the only wait
+  RF_CUDA(cudaMemcpyAsync(all, d_cnt->ptr, (uint64_t)g * W * 8, cudaMemcpyDeviceToHost, ctx->stream()));
   ctx->sync();
   uint64_t mine = 0;
-  bool fits = true;
+  bool fits = true, stale = false;
   for (int r = 0; r < g; r++) {
     uint64_t tot = 0;
-    for (int s = 0; s < g; s++) tot += all[(size_t)s * g + r];
+    for (int s = 0; s < g; s++) tot += all[(size_t)s * W + r];
     fits = fits && tot <= cap;
+    stale = stale || all[(size_t)r * W + g] != 0;
     if (r == me) mine = tot;
   }
   uint8_t* local = cm.arena[me] + off;
   // cursor back to 0 for shuffle k+2 — queued before anything below can throw: an error on this rank must not leave the
   // arena half unusable for the peers (the copy-out below only reads rows, the cursor word is not part of them)
   RF_CUDA(cudaMemsetAsync(local, 0, 8, ctx->stream()));
+  if (stale) return kP2pStaleInput;
   if (fits) {
     RF_REQUIRE(mine < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "shuffle result exceeds 2^32-2 rows on one GPU");
     t->rows = mine;
@@ -508,10 +531,10 @@ static bool shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col, rfgp
     }
     uint64_t link_rows = 0;
     for (int r = 0; r < g; r++)
-      if (r != me) link_rows += all[(size_t)me * g + r];
+      if (r != me) link_rows += all[(size_t)me * W + r];
     ctx->m.algorithmic_bytes += link_rows * 4 * C;
   }
-  return fits;
+  return fits ? kP2pDone : kP2pNoFit;
 }
 
 }  // namespace rf
@@ -540,6 +563,7 @@ int32_t rfgpu_comm_init(rfgpu_ctx* ctx, int32_t rank, int32_t n_ranks, const uin
   RF_NCCL(rf::nccl().CommInitRank(&c->comm, n_ranks, u, rank));
   c->rank = rank;
   c->size = n_ranks;
+  RF_CUDA(cudaHostAlloc((void**)&c->h_counts, (size_t)(rf::kMaxParts + 1) * rf::kMaxParts * 8, cudaHostAllocDefault));
   rf::setup_arenas(ctx, *c);
   ctx->comm = c;
   RF_API_END(ctx)
@@ -553,6 +577,7 @@ int32_t rfgpu_partition(rfgpu_ctx* ctx, const rfgpu_table* in, int32_t key_col, 
                         uint64_t* counts) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && in && out && counts, RFGPU_E_INVALID, "NULL argument");
+  rf::settle(in);  // lazy row count (rf_common.hpp)
   RF_CUDA(cudaSetDevice(ctx->core->device));
   auto bufs = rf::partition(ctx, in, key_col, n_parts, counts);
   std::unique_ptr<rfgpu_table> t(rf::new_table());
@@ -578,13 +603,22 @@ int32_t rfgpu_shuffle(rfgpu_ctx* ctx, const rfgpu_table* in, int32_t key_col, rf
   RF_REQUIRE(in->cols.size() <= (size_t)kMaxCols, RFGPU_E_UNSUPPORTED, "more than 16 columns");
   std::unique_ptr<rfgpu_table> t(new_table());
   if (g > 1 && ctx->comm->p2p && ctx->opt_shuffle_p2p) {
-    if (shuffle_p2p(ctx, in, key_col, t.get())) {
+    P2pResult r = shuffle_p2p(ctx, in, key_col, t.get());
+    if (r == kP2pStaleInput) {  // some rank's pending input was invalid: every rank settles its own and all exchange again
+      settle(in);
+      t.reset(new_table());
+      r = shuffle_p2p(ctx, in, key_col, t.get());
+      RF_REQUIRE(r != kP2pStaleInput, RFGPU_E_EXEC, "shuffle input still pending after it was settled");
+    }
+    if (r == kP2pDone) {
+      settle(in);  // free: the stream was synchronised after the producer's count reached its pinned mirror
       ctx->last_shuffle_path = RFGPU_SHUFFLE_P2P;
       *out = t.release();
       return RFGPU_OK;
     }
     t.reset(new_table());
   }
+  settle(in);  // the paths below partition with host-side counts
   ctx->last_shuffle_path = g > 1 ? RFGPU_SHUFFLE_NCCL : RFGPU_SHUFFLE_LOCAL;
   uint64_t send_counts[kMaxParts] = {0};
   auto parts = partition(ctx, in, key_col, (uint32_t)g, send_counts);

@@ -501,6 +501,7 @@ extern "C" {
 int32_t rfgpu_table_sort(rfgpu_ctx* ctx, const rfgpu_table* t, const int32_t* key_cols, int32_t n_keys, rfgpu_table** out) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && t && key_cols && out && n_keys > 0, RFGPU_E_INVALID, "NULL argument / no sort column");
+  rf::settle(t);  // lazy row count (rf_common.hpp)
   RF_CUDA(cudaSetDevice(ctx->core->device));
   std::vector<int> keys(key_cols, key_cols + n_keys);
   *out = rf::sort_table(ctx, t, keys);

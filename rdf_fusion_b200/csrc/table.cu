@@ -92,7 +92,30 @@ void rfgpu_table_release(rfgpu_table* t) {
   if (t && --t->refs == 0) delete t;
 }
 
-uint64_t rfgpu_table_num_rows(const rfgpu_table* t) { return t ? t->rows : 0; }
+uint64_t rfgpu_table_num_rows(const rfgpu_table* t) {
+  if (!t) return 0;
+  if (t->lazy) {  // the count is still on the device: wait for it (rfgpu_table_settle reports errors; here they read as 0 rows)
+    rfgpu_ctx* ctx = t->lazy->ctx;
+    try {
+      cudaSetDevice(ctx->core->device);
+      rf::settle(t);
+    } catch (const std::exception& e) {
+      rf::set_error(ctx, e.what());
+      return 0;
+    }
+  }
+  return t->rows;
+}
+
+int32_t rfgpu_table_settle(rfgpu_ctx* ctx, const rfgpu_table* t) {
+  RF_API_BEGIN
+  RF_REQUIRE(ctx && t, RFGPU_E_INVALID, "NULL argument");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  rf::settle(t);
+  RF_API_END(ctx)
+}
+
+int32_t rfgpu_table_is_pending(const rfgpu_table* t) { return t && t->lazy ? 1 : 0; }
 int32_t rfgpu_table_num_cols(const rfgpu_table* t) { return t ? (int32_t)t->cols.size() : 0; }
 const char* rfgpu_table_col_name(const rfgpu_table* t, int32_t c) {
   return t && c >= 0 && c < (int32_t)t->cols.size() ? t->cols[c].name.c_str() : nullptr;
@@ -101,6 +124,7 @@ int32_t rfgpu_table_col_nullable(const rfgpu_table* t, int32_t c) {
   return t && c >= 0 && c < (int32_t)t->cols.size() ? (int32_t)t->cols[c].nullable : -1;
 }
 const uint32_t* rfgpu_table_col_device_ptr(const rfgpu_table* t, int32_t c) {
+  if (t && t->lazy) rfgpu_table_num_rows(t);  // a pending table may still be recomputed: settle it before handing out pointers
   return t && c >= 0 && c < (int32_t)t->cols.size() ? t->cols[c].data : nullptr;
 }
 
@@ -109,6 +133,7 @@ int32_t rfgpu_table_sorted_col(const rfgpu_table* t) { return t ? t->sorted_col 
 int32_t rfgpu_table_set_sorted_col(rfgpu_ctx* ctx, rfgpu_table* t, int32_t col) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && t, RFGPU_E_INVALID, "NULL argument");
+  rf::settle(t);  // lazy row count (rf_common.hpp)
   RF_REQUIRE(col >= -1 && col < (int32_t)t->cols.size(), RFGPU_E_INVALID, "column index out of range");
   if (col >= 0 && t->rows > 1) {
     RF_CUDA(cudaSetDevice(ctx->core->device));
@@ -176,6 +201,7 @@ int32_t rfgpu_table_export(rfgpu_ctx* ctx, const rfgpu_table* t, uint64_t row_of
                            uint32_t* const* values, uint8_t* const* validity, uint64_t* null_counts) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && t, RFGPU_E_INVALID, "NULL argument");
+  rf::settle(t);  // lazy row count (rf_common.hpp)
   RF_REQUIRE(row_off <= t->rows && n_rows <= t->rows - row_off, RFGPU_E_INVALID, "row range out of bounds");
   RF_CUDA(cudaSetDevice(ctx->core->device));
   size_t nc = t->cols.size();
@@ -224,6 +250,7 @@ int32_t rfgpu_table_export_async(rfgpu_ctx* ctx, rfgpu_table* t, uint64_t row_of
                                  uint32_t* const* values) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && t, RFGPU_E_INVALID, "NULL argument");
+  rf::settle(t);  // lazy row count (rf_common.hpp)
   RF_REQUIRE(row_off <= t->rows && n_rows <= t->rows - row_off, RFGPU_E_INVALID, "row range out of bounds");
   RF_CUDA(cudaSetDevice(ctx->core->device));
   const size_t nc = t->cols.size();
@@ -248,6 +275,7 @@ int32_t rfgpu_table_col_min_max(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t co
                                 uint64_t* non_null) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && t && min_out && max_out, RFGPU_E_INVALID, "NULL argument");
+  rf::settle(t);  // lazy row count (rf_common.hpp)
   RF_REQUIRE(col >= 0 && col < (int32_t)t->cols.size(), RFGPU_E_INVALID, "column index out of range");
   RF_CUDA(cudaSetDevice(ctx->core->device));
   *min_out = 0xFFFFFFFFu;
@@ -277,6 +305,7 @@ int32_t rfgpu_table_project(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t n_cols
                             const char* const* new_names, rfgpu_table** out) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && t && out && n_cols >= 0 && (cols || n_cols == 0), RFGPU_E_INVALID, "NULL / negative argument");
+  rf::settle(t);  // lazy row count (rf_common.hpp)
   std::unique_ptr<rfgpu_table> r(rf::new_table());
   r->rows = t->rows;
   for (int i = 0; i < n_cols; i++) {
@@ -403,6 +432,7 @@ int32_t rfgpu_table_export_arrow(rfgpu_ctx* ctx, const rfgpu_table* t, uint64_t 
                                  struct ArrowArray* out_array, struct ArrowSchema* out_schema) {
   RF_API_BEGIN
   RF_REQUIRE(ctx && t && out_array && out_schema, RFGPU_E_INVALID, "NULL argument");
+  rf::settle(t);  // lazy row count (rf_common.hpp)
   size_t nc = t->cols.size();
   std::unique_ptr<ExportPriv> p(new ExportPriv);
   std::vector<uint32_t*> values(nc);

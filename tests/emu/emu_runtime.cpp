@@ -18,7 +18,7 @@ DevBuf::DevBuf(std::shared_ptr<Core> c, size_t n) : core(std::move(c)), bytes(n)
   std::memset(ptr, 0xA5, n);  // uninitialised device memory is not zero
 }
 DevBuf::~DevBuf() { std::free(ptr); }
-KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes) : ctx(c) {
+KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes, cudaStream_t) : ctx(c) {
   ctx->m.kernel_launches++;
   idx = ctx->kstat_index(name);
   ctx->kstats[idx].second.launches++;
@@ -46,6 +46,7 @@ int rfgpu_ctx::kstat_index(const char* name) {
   return (int)kstats.size() - 1;
 }
 void rfgpu_ctx::collect_profile() {}
+cudaStream_t rfgpu_ctx::lookup_stream() { return core->stream; }
 
 extern "C" {
 
@@ -84,12 +85,38 @@ void rfgpu_store_release(rfgpu_store* s) {
   if (s && --s->refs == 0) delete s;
 }
 
+rfgpu_table* rfgpu_table_retain(rfgpu_table* t) {
+  if (t) t->refs++;
+  return t;
+}
 rfgpu_ctx* emu_ctx_create() {
   auto* c = new rfgpu_ctx();
   c->core = std::make_shared<rf::Core>();
   c->h_scratch = (uint64_t*)std::calloc(512, 8);
+  // lazy row counts (rf_common.hpp, LazyRows): "device" words and "pinned" mirrors are two host arrays here
+  auto pool = std::make_shared<rf::LazyPool>();
+  pool->d = (unsigned long long*)std::calloc(rf::kLazySlots, 8);
+  pool->h = (uint64_t*)std::calloc(rf::kLazySlots, 8);
+  pool->release = [](rf::LazyPool* p) {
+    std::free(p->d);
+    std::free(p->h);
+  };
+  for (int i = rf::kLazySlots - 1; i >= 0; i--) pool->free.push_back(i);
+  c->lazy_pool = pool;
+  c->lazy_d = pool->d;
+  c->lazy_h = pool->h;
   return c;
 }
+void emu_set_lazy_rows(rfgpu_ctx* c, int32_t on) { c->opt_lazy_rows = on != 0; }
+int32_t emu_table_is_pending(const rfgpu_table* t) { return t->lazy ? 1 : 0; }
+uint64_t emu_host_syncs(const rfgpu_ctx* c) { return c->m_host_syncs; }
+uint64_t emu_lazy_redos(const rfgpu_ctx* c) { return c->m_lazy_redos; }
+void emu_table_set_bounds(rfgpu_table* t, uint32_t mn, uint32_t mx) {  // what a scan reports for its sort column
+  t->has_bounds = true;
+  t->sorted_min = mn;
+  t->sorted_max = mx;
+}
+uint64_t emu_table_capacity(const rfgpu_table* t) { return t->rows; }  // of a pending table: no settle
 void emu_ctx_destroy(rfgpu_ctx* c) {
   std::free(c->h_scratch);
   delete c;
@@ -123,10 +150,16 @@ rfgpu_table* emu_table_create(rfgpu_ctx* ctx, int32_t n_cols, const uint32_t* co
   }
   return t;
 }
-uint64_t emu_table_rows(const rfgpu_table* t) { return t->rows; }
+uint64_t emu_table_rows(const rfgpu_table* t) {
+  rf::settle(t);
+  return t->rows;
+}
 int32_t emu_table_cols(const rfgpu_table* t) { return (int32_t)t->cols.size(); }
 int32_t emu_table_sorted_col(const rfgpu_table* t) { return t->sorted_col; }
-const uint32_t* emu_table_col(const rfgpu_table* t, int32_t c) { return t->cols[c].data; }
+const uint32_t* emu_table_col(const rfgpu_table* t, int32_t c) {
+  rf::settle(t);
+  return t->cols[c].data;
+}
 void emu_table_release(rfgpu_table* t) { rfgpu_table_release(t); }
 rfgpu_store* emu_store_create() { return new rfgpu_store(); }
 void emu_store_release(rfgpu_store* s) { rfgpu_store_release(s); }

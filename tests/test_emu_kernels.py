@@ -657,3 +657,133 @@ def test_w3c_cases_on_host_threads(emu, bgp_golden, pattern_golden, join_golden,
             check_w3c_case(EmuBackend(emu, case["quads"]), case)
             n += 1
     assert n >= some(90, 20)
+
+
+def _lazy_sigs(lib):
+    for name, (res, args) in {"emu_set_lazy_rows": (None, [vp, C.c_int32]), "emu_table_is_pending": (C.c_int32, [vp]),
+                              "emu_host_syncs": (C.c_uint64, [vp]), "emu_lazy_redos": (C.c_uint64, [vp]),
+                              "emu_table_capacity": (C.c_uint64, [vp]),
+                              "emu_table_set_bounds": (None, [vp, C.c_uint32, C.c_uint32])}.items():
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+
+
+@pytest.mark.parametrize("fanout", [1, 3])
+def test_lazy_row_counts_chain(emu, oracle, fanout):
+    """rf_common.hpp LazyRows: a merge join, two direct-address joins that take their probe row count from the device
+    (k_lookup_join, kPersist) and a filter are queued without one host synchronisation; the counts are read at the end.
+    fanout = 3 makes every join outgrow its optimistic capacity: the results the later joins computed from truncated inputs
+    are thrown away and the chain is run again from the first join (settle() walks the retained inputs)."""
+    _lazy_sigs(emu)
+    rng = np.random.default_rng(17 + fanout)
+    n = 2000
+    # ?a p1 ?b . ?b p2 ?c . ?c p3 ?d . ?d p4 ?e   — every scan sorted on its subject (what the index order gives)
+    def scan(names, n_rows, key_hi):
+        k = np.sort(rng.integers(1, key_hi + 1, n_rows).astype(np.uint32))
+        v = rng.integers(1, key_hi + 1, n_rows).astype(np.uint32)
+        return list(names), [k, v]
+    hi = n // fanout
+    s1n, s1 = scan("ba", n, hi)          # sorted on ?b (object order of p1)
+    s2n, s2 = scan("bc", n, hi)
+    s3n, s3 = scan("cd", n, hi)
+    s4n, s4 = scan("de", n, hi)
+    T = [_named(emu, nm, [False, False], cols, 0) for nm, cols in ((s1n, s1), (s2n, s2), (s3n, s3), (s4n, s4))]
+    O = [oracle.OTable(nm, [False, False], cols) for nm, cols in ((s1n, s1), (s2n, s2), (s3n, s3), (s4n, s4))]
+    for t, (_, cols) in zip(T, ((s1n, s1), (s2n, s2), (s3n, s3), (s4n, s4))):
+        emu.emu_table_set_bounds(t, int(cols[0][0]), int(cols[0][-1]))  # a scan reports them with its range
+    want = O[0]
+    for o in O[1:]:
+        want = oracle.sparql_join(want, o, F.JOIN_INNER, "hash")[0]
+    for lazy in (1, 0):
+        emu.emu_set_lazy_rows(emu.ctx, lazy)
+        syncs0, redos0 = emu.emu_host_syncs(emu.ctx), emu.emu_lazy_redos(emu.ctx)
+        cur, made = T[0], []
+        for k, t in enumerate(T[1:]):
+            out = vp()
+            _ok(emu, emu.rfgpu_sparql_join(emu.ctx, cur, t, F.JOIN_INNER, C.byref(out)))
+            assert emu.rfgpu_last_join_phys(emu.ctx) == (F.PHYS_MERGE if k == 0 else F.PHYS_LOOKUP)
+            assert emu.emu_table_is_pending(out) == lazy
+            made.append(out)
+            cur = out
+        if lazy:
+            assert emu.emu_host_syncs(emu.ctx) == syncs0, "a lazy chain must not wait for the device"
+        names, _, cols = _take(emu, cur)  # settles: the only wait
+        made.pop()
+        if lazy:
+            assert emu.emu_host_syncs(emu.ctx) - syncs0 >= 1
+            assert (emu.emu_lazy_redos(emu.ctx) - redos0 > 0) == (fanout > 1), "capacity guess: 2 max(np, nb) + 1024"
+        assert names == want.names
+        a, b = oracle.canonical_rows(cols), oracle.canonical_rows(want.cols)
+        assert a.shape == b.shape and np.array_equal(a, b), (fanout, lazy, a.shape, b.shape)
+        for m in made:  # intermediate results stay valid tables of their own
+            assert emu.emu_table_rows(m) > 0 and not emu.emu_table_is_pending(m)
+            emu.emu_table_release(m)
+    emu.emu_set_lazy_rows(emu.ctx, 1)
+    for t in T:
+        emu.emu_table_release(t)
+
+
+def test_lazy_row_counts_filter_and_release(emu, oracle):
+    """a filter result is pending with the input's row count as capacity; releasing a pending table without reading it gives
+    its slot back; with every slot taken the operators fall back to waiting"""
+    import rdf_fusion_b200 as rf
+    _lazy_sigs(emu)
+    rng = np.random.default_rng(3)
+    cols = [rng.integers(1, 50, 300).astype(np.uint32), rng.integers(1, 50, 300).astype(np.uint32)]
+    t = _named(emu, "xy", [False, False], cols)
+    arr, keep = rf.make_filter_preds([rf.FPred(F.F_NE_COL, 0, col2=1)])
+    held = []
+    for i in range(530):  # more than kLazySlots
+        out = vp()
+        _ok(emu, emu.rfgpu_filter(emu.ctx, t, arr, 1, C.byref(out)))
+        if i < 512:
+            assert emu.emu_table_is_pending(out) and emu.emu_table_capacity(out) == 300
+        else:
+            assert not emu.emu_table_is_pending(out)
+        held.append(out)
+    keep_mask = cols[0] != cols[1]
+    for out in held[:3] + held[-3:]:
+        got = _cols(emu, out)
+        assert np.array_equal(got[0], cols[0][keep_mask]) and np.array_equal(got[1], cols[1][keep_mask])
+    for out in held:
+        emu.emu_table_release(out)
+    out = vp()
+    _ok(emu, emu.rfgpu_filter(emu.ctx, t, arr, 1, C.byref(out)))
+    assert emu.emu_table_is_pending(out), "released tables return their slots"
+    emu.emu_table_release(out)
+    emu.emu_table_release(t)
+
+
+def test_lazy_probe_switches_to_search_on_device(emu, oracle):
+    """a pending probe side whose capacity says "table" but whose real row count is tiny next to the sorted build side:
+    k_dense_heads_compact and k_lookup_join<kPersist> both read the count from the device and agree on the binary-search
+    mode (no table is written); same rows as the oracle, also for a Left join"""
+    _lazy_sigs(emu)
+    rng = np.random.default_rng(91)
+    nb = 30000
+    a = {"b": np.sort(rng.integers(1, 40, 2500).astype(np.uint32)), "a": rng.integers(1, 99, 2500).astype(np.uint32)}
+    b = {"b": np.sort(rng.integers(35, 3000, 2500).astype(np.uint32)), "c": rng.integers(1, nb // 3, 2500).astype(np.uint32)}
+    c = {"c": np.sort(rng.integers(1, nb // 3, nb).astype(np.uint32)), "d": rng.integers(1, 99, nb).astype(np.uint32)}
+    T, O = [], []
+    for tb in (a, b, c):
+        t = _named(emu, list(tb), [False, False], list(tb.values()), 0)
+        emu.emu_table_set_bounds(t, int(list(tb.values())[0][0]), int(list(tb.values())[0][-1]))
+        T.append(t)
+        O.append(oracle.OTable(list(tb), [False, False], list(tb.values())))
+    for jt in (F.JOIN_INNER, F.JOIN_LEFT):
+        j1 = vp()
+        _ok(emu, emu.rfgpu_sparql_join(emu.ctx, T[0], T[1], F.JOIN_INNER, C.byref(j1)))  # keys 35..39 only: a few hundred rows
+        assert emu.emu_table_is_pending(j1) and emu.emu_table_capacity(j1) * 16 > nb  # the host would build a table
+        j2 = vp()
+        _ok(emu, emu.rfgpu_sparql_join(emu.ctx, j1, T[2], jt, C.byref(j2)))
+        assert emu.rfgpu_last_join_phys(emu.ctx) == F.PHYS_LOOKUP and emu.emu_table_is_pending(j2)
+        w1 = oracle.sparql_join(O[0], O[1], F.JOIN_INNER, "hash")[0]
+        assert 0 < w1.num_rows * 16 <= nb
+        want = oracle.sparql_join(w1, O[2], jt, "hash")[0]
+        names, _, cols = _take(emu, j2)
+        assert names == want.names
+        x, y = oracle.canonical_rows(cols), oracle.canonical_rows(want.cols)
+        assert x.shape == y.shape and np.array_equal(x, y), (jt, x.shape, y.shape)
+        emu.emu_table_release(j1)
+    for t in T:
+        emu.emu_table_release(t)

@@ -717,3 +717,85 @@ def test_dynamic_filter_bounds_from_build_side(ctx, oracle):
         assert_same_table(got.names, got.to_numpy(), exp.names, exp.cols)
     empty = ctx.import_table({"a": np.zeros(5, np.uint32)}, {"a": True})
     assert empty.min_max("a") == (0xFFFFFFFF, 0, 0)
+
+
+@pytest.mark.gpu
+def test_lazy_row_counts_chain(ctx, oracle):
+    """Row counts of join / filter results are read lazily (include/rfgpu.h, rfgpu_table_num_rows): a chain
+    ?a p1 ?b . ?b p2 ?c . ?c p3 ?d . ?d p4 ?e is queued — merge join, then direct-address joins that take their probe row
+    count from the device — without the host waiting once after the range look-ups; the result equals the oracle's and the
+    one computed with RFGPU_OPT_LAZY_ROWS off."""
+    g = rf.generate_graph(200000, n_predicates=24, s=0.3, seed=21, s_o=0.6)
+    quads = g.quads()
+    perms = [F.GSPO, F.GPOS, F.GOSP, F.GPSO]
+    st = _gpu_store(ctx, quads, perms)
+    ost = oracle.OracleStore(8192, perms).load_quads(quads)
+    names = "abcde"
+
+    def plans(store):
+        return [store.plan([rf.traverse(0), rf.scan(names[i]), rf.traverse(g.pred_id(i + 1)), rf.scan(names[i + 1])])
+                for i in range(4)]
+    want = None
+    for pl in plans(ost):
+        t = pl.execute()
+        want = t if want is None else oracle.sparql_join(want, t, F.JOIN_INNER, "hash")[0]
+    assert want.num_rows > 100
+    gp = plans(st)
+    assert gp[0].order_by("b") and all(gp[i].order_by(names[i]) for i in range(1, 4))
+    results = {}
+    for lazy in (1, 0):
+        ctx.set_option(F.OPT_LAZY_ROWS, lazy)
+        try:
+            ts = rf.execute_many(gp, allow_view=True)
+            syncs0, redos0 = ctx.host_syncs, ctx.lazy_redos
+            cur, physes = ts[0], []
+            for t in ts[1:]:
+                cur = cur.join(t, F.JOIN_INNER)
+                physes.append(cur.last_join_phys)
+                assert cur.is_pending == bool(lazy)
+            assert physes[0] == F.PHYS_MERGE and set(physes[1:]) == {F.PHYS_LOOKUP}, physes
+            if lazy:
+                assert ctx.host_syncs == syncs0, "the joins of a lazy chain must not wait for the device"
+            f = cur.filter([rf.FPred(F.F_NE_COL, 0, col2=4)])  # needs its input's row count: the one wait
+            assert f.is_pending == bool(lazy)
+            n = f.num_rows
+            if lazy and ctx.lazy_redos == redos0:
+                assert 1 <= ctx.host_syncs - syncs0 <= 2
+            assert cur.num_rows == want.num_rows and not cur.is_pending
+            assert_same_table(cur.names, cur.to_numpy(), want.names, want.cols)
+            cols = cur.to_numpy()
+            assert n == int(np.count_nonzero(cols[0] != cols[4]))
+            results[lazy] = n
+        finally:
+            ctx.set_option(F.OPT_LAZY_ROWS, 1)
+    assert results[0] == results[1]
+
+
+@pytest.mark.gpu
+def test_lazy_row_counts_capacity_exceeded(ctx, oracle):
+    """every join of the chain has fan-out 3 and outgrows its optimistic output capacity: the later joins have consumed
+    truncated inputs by the time the host reads the first count; settling the last table recomputes the chain from the first
+    join on (retained inputs), and the intermediate tables are valid tables of their own afterwards"""
+    rng = np.random.default_rng(20)
+    n, fan = 20000, 3
+    hi = n // fan
+
+    def scan(names):
+        k = np.sort(rng.integers(1, hi + 1, n).astype(np.uint32))
+        return {names[0]: k, names[1]: rng.integers(1, hi + 1, n).astype(np.uint32)}
+    tabs = [scan(nm) for nm in ("ba", "bc", "cd", "de")]
+    want = None
+    for tb in tabs:
+        o = oracle.OTable(list(tb), [False, False], list(tb.values()))
+        want = o if want is None else oracle.sparql_join(want, o, F.JOIN_INNER, "hash")[0]
+    T = [ctx.import_table(tb).set_sorted(list(tb)[0]) for tb in tabs]
+    redos0 = ctx.lazy_redos
+    cur, made = T[0], []
+    for t in T[1:]:
+        cur = cur.join(t, F.JOIN_INNER)
+        assert cur.is_pending
+        made.append(cur)
+    assert cur.num_rows == want.num_rows
+    assert ctx.lazy_redos - redos0 >= 3, "each of the three joins wanted more rows than 2 max(np, nb) + 1024"
+    assert_same_table(cur.names, cur.to_numpy(), want.names, want.cols)
+    assert [m.is_pending for m in made] == [False] * 3 and made[0].num_rows < made[1].num_rows < made[2].num_rows
