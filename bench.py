@@ -518,7 +518,11 @@ def run_ours(a):
 
     sampler = ClockSampler(local)
     sampler.start()
-    c, ms, prof, met, jbytes = timed(step_device, a.steps, max(a.warmup, 3), profile=True)
+    c, ms, _, met, jbytes = timed(step_device, a.steps, max(a.warmup, 3))
+    # the same steps once more with a pair of CUDA events around every kernel launch (rfgpu_profile_*): per-kernel times and
+    # algorithmic bytes for `roofline` / `config.kernels`; the events cost a few microseconds per launch, so `value` is not
+    # taken from this pass
+    _, ms_profiled, prof, _, _ = timed(step_device, a.steps, 1, profile=True)
     clocks = sampler.stop()
     rows, out = c["rows"], c["out"]
     if a.timeline and rank == 0:  # diagnostic: one step's launches on a time axis (not part of any reported number)
@@ -676,7 +680,8 @@ def run_ours(a):
                                         "subject": "every permutation holds the quads whose subject hashes to the rank"}[a.layout],
                            "timing": "CUDA events on the ctx stream around each step (kernels, NCCL calls and host hand-offs "
                                      "in between), summed over the steps, max over ranks",
-                           "setup_s": round(setup_s, 1), "phases_ms": phases, "kernels": breakdown},
+                           "setup_s": round(setup_s, 1), "phases_ms": phases,
+                           "ms_per_step_with_launch_events": ms_profiled / a.steps, "kernels": breakdown},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(met["kernel_launches"]),
                 "host_syncs_per_step": met["host_syncs_per_step"], "lazy_redos": met["lazy_redos"],
                 "roofline": roof, "roofline_hash": roof_hash, "roofline_merge": roof_merge, "nvlink": nvlink,

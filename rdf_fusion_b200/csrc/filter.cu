@@ -27,6 +27,7 @@ struct FilterArgs {
   const uint32_t* src[kMaxCols];
   uint32_t* dst[kMaxCols];
   uint64_t n;
+  unsigned long long* total_host;  // optional: the kept count also goes here (mapped pinned memory; lazy row counts)
 };
 
 // membership of v (non-NULL) in the conjunct's IN list: up to 8 ids inline, longer lists sorted in global memory
@@ -123,7 +124,10 @@ k_filter_compact(const __grid_constant__ FilterArgs A, unsigned long long* __res
     unsigned long long excl = dev::lookback_exclusive(status, tile, btotal);
     if (lane == 0) {
       s_base = excl;
-      if (tile == gridDim.x - 1) *total = excl + btotal;
+      if (tile == gridDim.x - 1) {
+        *total = excl + btotal;
+        if (A.total_host) *A.total_host = excl + btotal;  // pinned mirror of a lazy row count
+      }
     }
   }
   if (btotal == 0) return;  // uniform over the CTA; warp 0 has published its aggregate above
@@ -171,7 +175,10 @@ uint64_t filter_compact(rfgpu_ctx* ctx, const std::vector<DevPred>& preds, const
   // lazy row count (rf_common.hpp, LazyRows): the kept count goes to a device word the caller attaches to its table; the
   // buffers hold n rows, which a filter cannot exceed
   const int slot = (lazy_slot && ctx->lazy_enabled()) ? ctx->lazy_take() : -1;
-  if (slot >= 0) d_total = ctx->lazy_d + slot;
+  if (slot >= 0) {
+    d_total = ctx->lazy_d + slot;
+    A.total_host = reinterpret_cast<unsigned long long*>(ctx->lazy_h + slot);
+  }
   {
     KernelScope ks(ctx, kernel_name, bytes_in);
     k_filter_compact<<<tiles, kFThreads, 0, ctx->stream()>>>(A, status->as<unsigned long long>(), d_total);

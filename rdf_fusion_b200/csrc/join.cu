@@ -81,7 +81,10 @@ uint64_t merge_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint3
     A.cap = cap;
     RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_tiles * 8, ctx->stream()));  // look-back words
     const int slot = (lz && attempt == 0 && ctx->lazy_enabled()) ? ctx->lazy_take() : -1;
-    if (slot >= 0) A.total = ctx->lazy_d + slot;
+    if (slot >= 0) {
+      A.total = ctx->lazy_d + slot;
+      A.total_host = reinterpret_cast<unsigned long long*>(ctx->lazy_h + slot);
+    }
     {
       KernelScope ks(ctx, "k_merge_join", 4ull * (np + nb));  // keys; payload + output bytes are added below
       switch (threads) {
@@ -247,7 +250,6 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
   }
   const int threads = 128;
   const uint32_t n_tiles = div_up(np, (uint64_t)threads * 8);
-  BufRef scratch = ctx->alloc((uint64_t)n_tiles * 8 + 16);
   LookupArgs A{};
   A.pk = pk;
   A.np = np;
@@ -265,17 +267,20 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
   // the compact table (2 bytes per key) is what the probe reads: built directly from a sorted build side, or compressed from
   // the wide table of the counting sort (which stays the fallback when a key has more than 255 build rows)
   const uint32_t groups = search ? 0 : (D.range + 3) / 4;
-  BufRef tab2 = ctx->alloc((uint64_t)groups * 8 + 16);
-  uint32_t* d_over = reinterpret_cast<uint32_t*>(tab2->as<uint8_t>() + (uint64_t)groups * 8);
+  // one allocation [table | overflow flag | look-back words | total] so that one memset zeroes whatever has to be zero
+  const uint64_t tab_bytes = (uint64_t)groups * 8, words_bytes = 16 + (uint64_t)n_tiles * 8 + 16;
+  BufRef tab2 = ctx->alloc(tab_bytes + words_bytes);
+  uint32_t* d_over = reinterpret_cast<uint32_t*>(tab2->as<uint8_t>() + tab_bytes);
+  unsigned long long* d_status = reinterpret_cast<unsigned long long*>(tab2->as<uint8_t>() + tab_bytes + 16);
   A.tab2 = tab2->as<uint2>();
   A.overflow = d_over;
   if (mode == 2) {
-    RF_CUDA(cudaMemsetAsync(tab2->ptr, 0, (uint64_t)groups * 8 + 16, ctx->stream()));
+    RF_CUDA(cudaMemsetAsync(tab2->ptr, 0, tab_bytes + words_bytes, ctx->stream()));
     KernelScope ks(ctx, "k_dense_heads_compact", 4ull * nb + 2ull * D.range);
     k_dense_heads_compact<<<grid_for(ctx, nb, 256), 256, 0, ctx->stream()>>>(bk, nb, D.kmin, D.stride, tab2->as<uint2>(),
                                                                              np_dev, np);
   } else {
-    RF_CUDA(cudaMemsetAsync(d_over, 0, 16, ctx->stream()));
+    RF_CUDA(cudaMemsetAsync(d_over, 0, words_bytes, ctx->stream()));
     if (groups) {
       KernelScope ks(ctx, "k_dense_compress", 6ull * D.range);
       k_dense_compress<<<grid_for(ctx, groups, 256), 256, 0, ctx->stream()>>>(offs, D.range, tab2->as<uint2>(), d_over);
@@ -283,7 +288,7 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
   }
   A.left = left ? 1 : 0;
   A.n_tiles = n_tiles;
-  A.status = scratch->as<unsigned long long>();
+  A.status = d_status;
   A.total = A.status + n_tiles;
   A.n_cols = (int32_t)specs.size();
   uint64_t in_cols_p = 0;
@@ -302,9 +307,12 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
       A.dst[c] = (*bufs)[c]->as<uint32_t>();
     }
     A.cap = cap;
-    RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_tiles * 8, ctx->stream()));
+    if (attempt > 0) RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_tiles * 8, ctx->stream()));  // (zeroed above the first time)
     const int slot = (lz && attempt == 0 && ctx->lazy_enabled()) ? ctx->lazy_take() : -1;
-    if (slot >= 0) A.total = ctx->lazy_d + slot;
+    if (slot >= 0) {
+      A.total = ctx->lazy_d + slot;
+      A.total_host = reinterpret_cast<unsigned long long*>(ctx->lazy_h + slot);
+    }
     RF_REQUIRE(!np_dev || slot >= 0, RFGPU_E_EXEC, "a pending probe side needs a lazy output");  // sparql_join settles otherwise
     {
       KernelScope ks(ctx, "k_lookup_join", np_dev ? 0 : 4ull * np);

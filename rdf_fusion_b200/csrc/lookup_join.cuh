@@ -238,6 +238,7 @@ struct LookupArgs {
   uint32_t n_tiles;
   unsigned long long* status;  // look-back words [n_tiles]
   unsigned long long* total;   // out: exact number of output rows
+  unsigned long long* total_host;  // optional second copy in mapped pinned host memory (lazy row counts)
   uint64_t cap;                // rows the dst columns can hold
   OutColSpec cols[kMaxCols];   // probe: indexed by probe row; build: indexed by build POSITION (key order)
   uint32_t* dst[kMaxCols];
@@ -410,7 +411,10 @@ __device__ __forceinline__ void lookup_tile(const LookupArgs& A, LookupSmem<kLTh
       const unsigned long long excl = dev::lookback_resolve(A.status, tile, tot);
       if (lane == 0) {
         S.base = excl;
-        if (tile == n_tiles - 1) *A.total = excl + tot;
+        if (tile == n_tiles - 1) {
+          *A.total = excl + tot;
+          if (A.total_host) *A.total_host = excl + tot;
+        }
       }
     }
   };

@@ -48,6 +48,7 @@ struct MergeArgs {
   uint32_t n_tiles;
   unsigned long long* status;  // look-back words [n_tiles]
   unsigned long long* total;   // out: exact number of output rows
+  unsigned long long* total_host;  // optional second copy in mapped pinned host memory (lazy row counts)
   uint64_t cap;                // rows the dst columns can hold
   OutColSpec cols[kMaxCols];
   uint32_t* dst[kMaxCols];
@@ -357,7 +358,10 @@ k_merge_join(const __grid_constant__ MergeArgs A) {
       const unsigned long long excl = dev::lookback_resolve(A.status, tile, tot);
       if (lane == 0) {
         S.base = excl;
-        if (tile == A.n_tiles - 1) *A.total = excl + tot;
+        if (tile == A.n_tiles - 1) {
+          *A.total = excl + tot;
+          if (A.total_host) *A.total_host = excl + tot;  // pinned mirror of a lazy row count (rf_common.hpp)
+        }
       }
     }
   };

@@ -81,8 +81,8 @@ struct Comm;  // NCCL communicator wrapper (shuffle.cu)
 
 // A row count the host has not read yet.  An operator whose output size is only known on the device (join, filter) can
 // return at once: its table's `rows` is then the CAPACITY it allocated, the exact count sits in a device word
-// (ctx->lazy_d[slot], read by consumer kernels that take their row count from the device) and is copied to its pinned
-// mirror (ctx->lazy_h[slot]) in stream order.  rf::settle() turns such a table into an ordinary one the first time the host
+// (ctx->lazy_d[slot], read by consumer kernels that take their row count from the device) and in its pinned mirror
+// (ctx->lazy_h[slot], written by the same kernel).  rf::settle() turns such a table into an ordinary one the first time the host
 // needs the count: one stream synchronisation — none if the stream was synchronised since — and, when the producer's
 // optimistic capacity was too small (count > cap: the kernel wrote nothing beyond cap), a second, exactly sized run of the
 // producer from its retained inputs (`redo`), after settling those first.  The reference streams record batches between
@@ -240,7 +240,8 @@ rfgpu_table* new_table();
 // table.cu — lazy row counts (struct LazyRows above)
 // Makes `t` an ordinary table (exact `rows`); true when its contents were recomputed (pointers changed).
 bool settle(const rfgpu_table* t);
-// Queues the copy of ctx->lazy_d[slot] to its pinned mirror and marks `t` (whose buffers hold `cap` rows) as pending.
+// Marks `t` (whose buffers hold `cap` rows) as pending; its producer kernel writes the count to ctx->lazy_d[slot] AND to the
+// pinned mirror ctx->lazy_h[slot] (mapped host memory: no copy operation in the stream).
 // `deps` are retained; `redo` must produce the same table synchronously.
 void attach_lazy(rfgpu_ctx* ctx, rfgpu_table* t, int slot, uint64_t cap, std::vector<const rfgpu_table*> deps,
                  std::function<rfgpu_table*()> redo, std::function<void(uint64_t)> account = nullptr);
@@ -316,7 +317,6 @@ inline LazyRows::~LazyRows() {
 
 inline void attach_lazy(rfgpu_ctx* ctx, rfgpu_table* t, int slot, uint64_t cap, std::vector<const rfgpu_table*> deps,
                         std::function<rfgpu_table*()> redo, std::function<void(uint64_t)> account) {
-  RF_CUDA(cudaMemcpyAsync(ctx->lazy_h + slot, ctx->lazy_d + slot, 8, cudaMemcpyDeviceToHost, ctx->stream()));
   std::unique_ptr<LazyRows> z(new LazyRows());
   z->ctx = ctx;
   z->pool = ctx->lazy_pool;
