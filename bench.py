@@ -19,6 +19,7 @@ rows per step = rows returned by every scan + rows entering the filter + build a
            Rust crate cannot be built here) on the host cores, on a bounded sample of the same workload.
 """
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -486,6 +487,8 @@ def run_ours(a):
         ctx.metrics_reset()
         ctx.profile_enable(profile)
         reset_counters()
+        gc.collect()
+        gc.disable()  # the host side is CPython here (Rust in the reference): no collector pause inside a timed step
         barrier()
         syncs0, redos0 = ctx.host_syncs, ctx.lazy_redos
         ms = 0.0
@@ -500,6 +503,7 @@ def run_ours(a):
             flush_deferred()
         host_syncs = (ctx.host_syncs - syncs0 - steps) / steps  # minus the ctx.synchronize() before every timed step
         redos = ctx.lazy_redos - redos0
+        gc.enable()
         barrier()
         prof = ctx.profile() if profile else {}
         ctx.profile_enable(False)
@@ -525,26 +529,36 @@ def run_ours(a):
     _, ms_profiled, prof, _, _ = timed(step_device, a.steps, 1, profile=True)
     clocks = sampler.stop()
     rows, out = c["rows"], c["out"]
-    if a.timeline and rank == 0:  # diagnostic: one step's launches on a time axis (not part of any reported number)
+    if a.timeline:  # diagnostic: one step's launches on a time axis (not part of any reported number); every rank runs the
+        # step (it holds collectives), rank 0 writes the file
         ctx.profile_enable(True)
         ctx.flush_l2()
         ctx.synchronize()
+        gc.collect()
+        gc.disable()
+        if world > 1:
+            dist.barrier()
         ctx.timeline(True)
+        ctx.alloc_stats(reset=True)
         t0 = time.perf_counter()
         step_device()
         wall_us = (time.perf_counter() - t0) * 1e6
+        al = ctx.alloc_stats()
         flush_deferred()
+        gc.enable()
         recs = ctx.timeline_records()
         ctx.timeline(False)
         ctx.profile_enable(False)
-        with open(a.timeline, "w") as f:
+        with open(a.timeline if rank == 0 else os.devnull, "w") as f:
             f.write("# one device-resident step after an L2 flush; host wall clock %.1f us; kernel, start_us, end_us, duration_us, "
-                    "idle_before_us (since the latest end so far)\n" % wall_us)
+                    "idle_before_us (since the latest end so far), queued_us (host clock when the launch call returned)\n"
+                    "# device allocations in this step: %d calls, %.1f us in cudaMallocAsync, longest %.1f us, %d over 20 us\n"
+                    % (wall_us, al["calls"], al["us"], al["max_us"], al["slow"]))
             latest = 0.0
-            for name, s_us, e_us in recs:
-                f.write("%-28s %9.1f %9.1f %8.1f %8.1f\n" % (name, s_us, e_us, e_us - s_us, max(0.0, s_us - latest)))
+            for name, s_us, e_us, q_us in recs:
+                f.write("%-28s %9.1f %9.1f %8.1f %8.1f %9.1f\n" % (name, s_us, e_us, e_us - s_us, max(0.0, s_us - latest), q_us))
                 latest = max(latest, e_us)
-    if a.host_profile and rank == 0:
+    if a.host_profile:
         import cProfile
         import io
         import pstats
@@ -561,7 +575,7 @@ def run_ours(a):
         pr.disable()
         buf = io.StringIO()
         pstats.Stats(pr, stream=buf).sort_stats("cumulative").print_stats(45)
-        with open(a.host_profile, "w") as f:
+        with open(a.host_profile if rank == 0 else os.devnull, "w") as f:
             f.write("wall clock per step without the profiler, L2 not flushed: %.1f us\n" % (wall * 1e6))
             f.write(buf.getvalue())
 

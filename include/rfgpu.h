@@ -206,6 +206,9 @@ uint64_t rfgpu_table_num_rows(const rfgpu_table* t);
 int32_t rfgpu_table_settle(rfgpu_ctx* ctx, const rfgpu_table* t);
 int32_t rfgpu_table_is_pending(const rfgpu_table* t);
 uint64_t rfgpu_ctx_host_syncs(const rfgpu_ctx* ctx);
+/* device allocations of this ctx since the last reset: out = {calls, host microseconds inside cudaMallocAsync, the longest call,
+ * calls that took more than 20 us (the stream-ordered pool could not reuse a block and went to the driver)} */
+int32_t rfgpu_ctx_alloc_stats(rfgpu_ctx* ctx, double out[4], int32_t reset);
 uint64_t rfgpu_ctx_lazy_redos(const rfgpu_ctx* ctx);
 int32_t rfgpu_table_num_cols(const rfgpu_table* t);
 const char* rfgpu_table_col_name(const rfgpu_table* t, int32_t col);
@@ -533,7 +536,8 @@ int32_t rfgpu_profile_gap_ms(rfgpu_ctx* ctx, int32_t i, double* gap_ms);
  * order (kernels of the range look-up stream overlap those of the ctx stream); rfgpu_profile_timeline(ctx, 0) stops */
 int32_t rfgpu_profile_timeline(rfgpu_ctx* ctx, int32_t on);
 int32_t rfgpu_profile_timeline_len(rfgpu_ctx* ctx);
-int32_t rfgpu_profile_timeline_get(rfgpu_ctx* ctx, int32_t i, const char** name, double* start_us, double* end_us);
+int32_t rfgpu_profile_timeline_get(rfgpu_ctx* ctx, int32_t i, const char** name, double* start_us, double* end_us,
+                                   double* queued_us /* optional: host clock when the launch returned, same origin */);
 /* stream-ordered stopwatch on the ctx stream (bench.py times steps with it) */
 int32_t rfgpu_timer_start(rfgpu_ctx* ctx);
 int32_t rfgpu_timer_stop(rfgpu_ctx* ctx, double* elapsed_ms);

@@ -135,6 +135,7 @@ SIGNATURES = {
     "rfgpu_table_settle": (C.c_int32, [C.c_void_p, C.c_void_p]),
     "rfgpu_table_is_pending": (C.c_int32, [C.c_void_p]),
     "rfgpu_ctx_host_syncs": (C.c_uint64, [C.c_void_p]),
+    "rfgpu_ctx_alloc_stats": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double), C.c_int32]),
     "rfgpu_ctx_lazy_redos": (C.c_uint64, [C.c_void_p]),
     "rfgpu_table_col_name": (C.c_char_p, [C.c_void_p, C.c_int32]),
     "rfgpu_table_col_nullable": (C.c_int32, [C.c_void_p, C.c_int32]),
@@ -181,7 +182,8 @@ SIGNATURES = {
     "rfgpu_profile_gap_ms": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_double)]),
     "rfgpu_profile_timeline": (C.c_int32, [C.c_void_p, C.c_int32]),
     "rfgpu_profile_timeline_len": (C.c_int32, [C.c_void_p]),
-    "rfgpu_profile_timeline_get": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "rfgpu_profile_timeline_get": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                                C.POINTER(C.c_double)]),
     "rfgpu_timer_start": (C.c_int32, [C.c_void_p]),
     "rfgpu_timer_stop": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
     "rfgpu_flush_l2": (C.c_int32, [C.c_void_p]),

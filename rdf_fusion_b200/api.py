@@ -152,6 +152,12 @@ class Context:
         """How often this ctx has waited for its stream so far."""
         return int(self.lib.rfgpu_ctx_host_syncs(self.h))
 
+    def alloc_stats(self, reset=False):
+        """{calls, us, max_us, slow}: host time inside the device allocator since the last reset (include/rfgpu.h)"""
+        out = (C.c_double * 4)()
+        self.check(self.lib.rfgpu_ctx_alloc_stats(self.h, out, 1 if reset else 0))
+        return {"calls": int(out[0]), "us": out[1], "max_us": out[2], "slow": int(out[3])}
+
     @property
     def lazy_redos(self) -> int:
         return int(self.lib.rfgpu_ctx_lazy_redos(self.h))
@@ -258,12 +264,13 @@ class Context:
         self.check(self.lib.rfgpu_profile_timeline(self.h, 1 if on else 0))
 
     def timeline_records(self):
-        """[(kernel name, start_us, end_us)] in launch order since timeline(True)"""
+        """[(kernel name, start_us, end_us, queued_us)] in launch order since timeline(True); queued_us = host clock when the
+        launch call returned"""
         out = []
         for i in range(self.lib.rfgpu_profile_timeline_len(self.h)):
-            name, a, b = C.c_char_p(), C.c_double(), C.c_double()
-            self.check(self.lib.rfgpu_profile_timeline_get(self.h, i, C.byref(name), C.byref(a), C.byref(b)))
-            out.append((name.value.decode(), a.value, b.value))
+            name, a, b, q = C.c_char_p(), C.c_double(), C.c_double(), C.c_double()
+            self.check(self.lib.rfgpu_profile_timeline_get(self.h, i, C.byref(name), C.byref(a), C.byref(b), C.byref(q)))
+            out.append((name.value.decode(), a.value, b.value, q.value))
         return out
 
     def timer_start(self):

@@ -24,7 +24,13 @@ Core::~Core() {
 DevBuf::DevBuf(std::shared_ptr<Core> c, size_t n) : core(std::move(c)), bytes(n) {
   size_t padded = ((n + kPad - 1) / kPad) * kPad + kPad;
   RF_CUDA(cudaSetDevice(core->device));
+  const double t0 = host_now_us();
   RF_CUDA(cudaMallocAsync(&ptr, padded, core->stream));
+  const double dt = host_now_us() - t0;
+  core->alloc_calls++;
+  core->alloc_us += dt;
+  core->alloc_max_us = std::max(core->alloc_max_us, dt);
+  core->alloc_slow += dt > 20.0;
 }
 
 DevBuf::~DevBuf() {
@@ -34,9 +40,9 @@ DevBuf::~DevBuf() {
   }
 }
 
-KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes, cudaStream_t on)
+KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes, cudaStream_t on, bool is_kernel)
     : ctx(c), stream(on ? on : c->stream()) {
-  ctx->m.kernel_launches++;
+  if (is_kernel) ctx->m.kernel_launches++;
   idx = ctx->kstat_index(name);
   ctx->kstats[idx].second.launches++;
   ctx->kstats[idx].second.bytes += bytes;
@@ -59,7 +65,7 @@ KernelScope::~KernelScope() noexcept(false) {
   cudaError_t e = cudaGetLastError();
   if (a) {
     cudaEventRecord(b, stream);
-    ctx->pending.push_back({idx, a, b});
+    ctx->pending.push_back({idx, a, b, ctx->timeline_on ? host_now_us() - ctx->timeline_host_t0 : 0.0});
   }
   if (e != cudaSuccess && !std::uncaught_exceptions())
     throw Error(RFGPU_E_CUDA, std::string("kernel launch failed: ") + ctx->kstats[idx].first + ": " +
@@ -109,7 +115,7 @@ void rfgpu_ctx::collect_profile() {
       float s_ms = 0, e_ms = 0;
       cudaEventElapsedTime(&s_ms, timeline_t0, p.a);
       cudaEventElapsedTime(&e_ms, timeline_t0, p.b);
-      timeline.push_back({p.idx, s_ms * 1e3f, e_ms * 1e3f});
+      timeline.push_back({p.idx, s_ms * 1e3f, e_ms * 1e3f, (float)p.host_us});
     }
     if (i > 0) {  // stream time between the previous kernel's end and this one's start: host hand-offs, memsets, copies
       float gap = 0;
@@ -248,6 +254,17 @@ void rfgpu_ctx_destroy(rfgpu_ctx* ctx) {
 }
 
 void* rfgpu_ctx_stream(rfgpu_ctx* ctx) { return ctx ? (void*)ctx->core->stream : nullptr; }
+
+int32_t rfgpu_ctx_alloc_stats(rfgpu_ctx* ctx, double out[4], int32_t reset) {
+  if (!ctx || !out) return RFGPU_E_INVALID;
+  rf::Core& c = *ctx->core;
+  out[0] = (double)c.alloc_calls;
+  out[1] = c.alloc_us;
+  out[2] = c.alloc_max_us;
+  out[3] = (double)c.alloc_slow;
+  if (reset) c.alloc_calls = c.alloc_slow = 0, c.alloc_us = c.alloc_max_us = 0;
+  return RFGPU_OK;
+}
 
 uint64_t rfgpu_ctx_host_syncs(const rfgpu_ctx* ctx) { return ctx ? ctx->m_host_syncs : 0; }
 uint64_t rfgpu_ctx_lazy_redos(const rfgpu_ctx* ctx) { return ctx ? ctx->m_lazy_redos : 0; }
@@ -426,6 +443,7 @@ int32_t rfgpu_profile_timeline(rfgpu_ctx* ctx, int32_t on) {
   if (on) {  // the origin of the time axis: now, on the ctx stream
     if (!ctx->timeline_t0) RF_CUDA(cudaEventCreate(&ctx->timeline_t0));
     RF_CUDA(cudaEventRecord(ctx->timeline_t0, ctx->stream()));
+    ctx->timeline_host_t0 = rf::host_now_us();
   }
   RF_API_END(ctx)
 }
@@ -440,11 +458,13 @@ int32_t rfgpu_profile_timeline_len(rfgpu_ctx* ctx) {
   return (int32_t)ctx->timeline.size();
 }
 
-int32_t rfgpu_profile_timeline_get(rfgpu_ctx* ctx, int32_t i, const char** name, double* start_us, double* end_us) {
+int32_t rfgpu_profile_timeline_get(rfgpu_ctx* ctx, int32_t i, const char** name, double* start_us, double* end_us,
+                                   double* queued_us) {
   if (!ctx || i < 0 || i >= (int32_t)ctx->timeline.size() || !name || !start_us || !end_us) return RFGPU_E_INVALID;
   *name = ctx->kstats[ctx->timeline[i].idx].first.c_str();
   *start_us = ctx->timeline[i].start_us;
   *end_us = ctx->timeline[i].end_us;
+  if (queued_us) *queued_us = ctx->timeline[i].host_us;
   return RFGPU_OK;
 }
 

@@ -58,6 +58,16 @@ k_filter_compact(const __grid_constant__ FilterArgs A, unsigned long long* __res
   const uint32_t tile = blockIdx.x;
   const uint64_t warp_row0 = (uint64_t)tile * kFTile + (uint64_t)warp * (32 * kFItems);
 
+#ifndef RF_FILTER_NO_PREFETCH
+  // every column's slice of this tile is asked into L2 now: the copy-out loop below reads column after column only once the
+  // tile's output offset is known, and would otherwise pay a DRAM round trip per column at the end of the latency chain
+  if (tid < (uint32_t)A.n_cols) {
+    const uint64_t r0 = (uint64_t)tile * kFTile, r1 = min(A.n, r0 + (uint64_t)kFTile);
+    const uintptr_t a0 = (uintptr_t)(A.src[tid] + r0) & ~(uintptr_t)15;
+    const uintptr_t a1 = ((uintptr_t)(A.src[tid] + r1) + 15) & ~(uintptr_t)15;
+    dev::bulk_prefetch_l2((const void*)a0, (uint32_t)(a1 - a0));
+  }
+#endif
   // Conjunct by conjunct, the thread's 16 values of the conjunct's column(s) are loaded together (16 independent loads
   // in flight; evaluating row by row would chain 16 memory round trips behind the ballots).  sel bit k = row k still
   // passes; a row that failed an earlier conjunct is not loaded again.

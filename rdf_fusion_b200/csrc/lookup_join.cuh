@@ -422,7 +422,11 @@ __device__ __forceinline__ void lookup_tile(const LookupArgs& A, LookupSmem<kLTh
     resolve();
     return;
   }
-  __syncthreads();
+  // no probe row emits more than one row: the scatter below is the slot -> row map already (merge_join.cuh)
+  bool multi_t = false;
+#pragma unroll
+  for (int r = 0; r < 8; r++) multi_t |= e[r] > 1u;
+  const bool multi = __syncthreads_or(multi_t) != 0;
 
   // ---- expansion, kChunk output rows per round (as in merge_join.cuh) ----
   uint32_t* H = S.H;
@@ -431,9 +435,11 @@ __device__ __forceinline__ void lookup_tile(const LookupArgs& A, LookupSmem<kLTh
   uint32_t carry = 0;  // (row + 1) covering the last slot of the previous round
   for (uint32_t c0 = 0; c0 < tot32; c0 += kChunk) {
     const uint32_t n = min((uint32_t)kChunk, tot32 - c0);
+    if (multi) {
 #pragma unroll
-    for (int k = 0; k < 8; k++) H[tid * 9 + k] = 0;
-    __syncthreads();
+      for (int k = 0; k < 8; k++) H[tid * 9 + k] = 0;
+      __syncthreads();
+    }
 #pragma unroll
     for (int k = 0; k < 8; k++) {
       const uint32_t i = tid + k * kLThreads;
@@ -442,6 +448,7 @@ __device__ __forceinline__ void lookup_tile(const LookupArgs& A, LookupSmem<kLTh
       if (S.off[i + 1] != o && rel < (uint32_t)kChunk) H[hpad(rel)] = i + 1;
     }
     __syncthreads();
+    if (multi) {
     uint32_t v[8];
 #pragma unroll
     for (int k = 0; k < 8; k++) v[k] = H[tid * 9 + k];
@@ -465,6 +472,7 @@ __device__ __forceinline__ void lookup_tile(const LookupArgs& A, LookupSmem<kLTh
     for (int k = 0; k < 8; k++) H[tid * 9 + k] = max(v[k], m);
     __syncthreads();
     carry = H[hpad(kChunk - 1)];
+    }
     // slot -> (probe row, build position); slots of one thread are kLThreads apart so every store is coalesced
     uint32_t prow[8], brow[8];
 #pragma unroll

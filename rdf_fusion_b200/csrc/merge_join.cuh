@@ -369,7 +369,13 @@ k_merge_join(const __grid_constant__ MergeArgs A) {
     resolve();
     return;
   }
-  __syncthreads();
+  // No probe row of the tile emits more than one row (unique build keys): every output slot then has exactly one source
+  // row, the scatter below already IS the slot -> row map, and the zero fill and the max-scan that spread multi-row groups
+  // over their slots are skipped (two barriers and most of the expansion's instructions).
+  bool multi_t = false;
+#pragma unroll
+  for (int r = 0; r < 8; r++) multi_t |= e[r] > 1u;
+  const bool multi = __syncthreads_or(multi_t) != 0;
 
   // ---- expansion, kMChunk output rows per round ----
   uint32_t* H = S.bk;
@@ -378,9 +384,11 @@ k_merge_join(const __grid_constant__ MergeArgs A) {
   uint32_t carry = 0;  // (row + 1) covering the last slot of the previous round
   for (uint32_t c0 = 0; c0 < tot32; c0 += kMChunk) {
     const uint32_t n = min((uint32_t)kMChunk, tot32 - c0);
+    if (multi) {
 #pragma unroll
-    for (int k = 0; k < kMChunkItems; k++) H[tid * 9 + k] = 0;
-    __syncthreads();
+      for (int k = 0; k < kMChunkItems; k++) H[tid * 9 + k] = 0;
+      __syncthreads();
+    }
 #pragma unroll
     for (int k = 0; k < kMTile / kMThreads; k++) {
       const uint32_t i = tid + k * kMThreads;
@@ -389,6 +397,7 @@ k_merge_join(const __grid_constant__ MergeArgs A) {
       if (S.off[i + 1] != o && rel < (uint32_t)kMChunk) H[hpad(rel)] = i + 1;
     }
     __syncthreads();
+    if (multi) {
     uint32_t v[kMChunkItems];
 #pragma unroll
     for (int k = 0; k < kMChunkItems; k++) v[k] = H[tid * 9 + k];
@@ -412,6 +421,7 @@ k_merge_join(const __grid_constant__ MergeArgs A) {
     for (int k = 0; k < kMChunkItems; k++) H[tid * 9 + k] = max(v[k], m);
     __syncthreads();
     carry = H[hpad(kMChunk - 1)];
+    }
     // slot → (probe row, build row); slots of one thread are kMThreads apart so every store is coalesced
     uint32_t prow[kMChunkItems], brow[kMChunkItems];
 #pragma unroll

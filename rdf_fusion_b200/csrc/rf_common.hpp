@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <chrono>
 #include <cstdint>
 #include <functional>
 #include <map>
@@ -43,6 +44,9 @@ struct Core {
   int device = 0;
   cudaStream_t stream = nullptr;
   int num_sms = kNumSMsB200;
+  // host time spent inside cudaMallocAsync (a pool that cannot reuse a block goes to the driver: ~100 us instead of ~1)
+  uint64_t alloc_calls = 0, alloc_slow = 0;
+  double alloc_us = 0, alloc_max_us = 0;
   ~Core();
 };
 
@@ -167,10 +171,11 @@ struct rfgpu_ctx {
   // profiling
   bool profiling = false;
   std::vector<std::pair<std::string, rf::KernelStat>> kstats;
-  struct Pending { int idx; cudaEvent_t a, b; };
+  struct Pending { int idx; cudaEvent_t a, b; double host_us; };  // host_us: when the host queued the launch (timeline only)
   std::vector<Pending> pending;
   // optional launch timeline (rfgpu_profile_timeline): start / end of every profiled launch, microseconds since the first
-  struct Launch { int idx; float start_us, end_us; };
+  struct Launch { int idx; float start_us, end_us, host_us; };
+  double timeline_host_t0 = 0;  // host clock (microseconds) when the origin event was recorded
   bool timeline_on = false;
   cudaEvent_t timeline_t0 = nullptr;
   std::vector<Launch> timeline;
@@ -230,10 +235,15 @@ struct KernelScope {
   int idx = -1;
   cudaEvent_t a = nullptr, b = nullptr;
   cudaStream_t stream = nullptr;
-  KernelScope(rfgpu_ctx* c, const char* name, uint64_t algorithmic_bytes = 0, cudaStream_t on = nullptr /* ctx stream */);
+  // is_kernel = false: a library call or copy timed like a kernel in the profile (NCCL collective, copy-out), not counted as one of ours
+  KernelScope(rfgpu_ctx* c, const char* name, uint64_t algorithmic_bytes = 0, cudaStream_t on = nullptr /* ctx stream */,
+              bool is_kernel = true);
   ~KernelScope() noexcept(false);
 };
 
+inline double host_now_us() {
+  return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 inline uint32_t div_up(uint64_t a, uint64_t b) { return (uint32_t)((a + b - 1) / b); }
 
 rfgpu_table* new_table();

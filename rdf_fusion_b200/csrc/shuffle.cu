@@ -84,7 +84,8 @@ struct Comm {
   size_t arena_bytes = 0;
   bool p2p = false;
   uint64_t epoch = 0;  // shuffles done through the arenas; parity selects the half
-  uint64_t* h_counts = nullptr;  // pinned: the gathered (sent counts + stale flag) matrix of one shuffle
+  uint64_t* h_counts = nullptr;  // pinned: the gathered (sent counts + flags) matrix of one shuffle
+  unsigned long long* d_counts = nullptr;  // device: the same matrix + this rank's contribution ((g + 1) x (g + 2) words)
   void drop_arenas() {
     for (int r = 0; r < size; r++) {
       if (!arena[r]) continue;
@@ -97,6 +98,7 @@ struct Comm {
   ~Comm() {
     drop_arenas();
     if (h_counts) cudaFreeHost(h_counts);
+    if (d_counts) cudaFree(d_counts);
     if (comm) nccl().CommDestroy(comm);
   }
 };
@@ -453,6 +455,35 @@ static void setup_arenas(rfgpu_ctx* ctx, Comm& c) {
 // Why no barrier before the kernel: shuffle k writes half k&1.  A peer's kernel of shuffle k starts after ITS all-gather of
 // shuffle k-1 completed, which needs MY all-gather of shuffle k-1 to have started, which in my stream follows my
 // copy-out and cursor reset of shuffle k-2 — the last use of half k&1.
+// Copy-out of one arena half: every column's received rows to the table's own buffers, one launch for all columns (a
+// cudaMemcpyAsync per column ran at ~1 TB/s of traffic with a launch gap between the columns; this streams 16-byte words
+// through every SM).  Sources are 128-byte aligned (control block 256 B, cap a multiple of 32 rows), destinations 256-byte.
+struct CopyOutArgs {
+  const uint4* src[kMaxCols];
+  uint4* dst[kMaxCols];
+  uint32_t n_cols;
+  uint64_t vec;  // 16-byte words per column (rows rounded up to 4; both buffers are padded)
+};
+__global__ void __launch_bounds__(256)
+k_copy_out(const __grid_constant__ CopyOutArgs A) {
+  const uint64_t total = A.vec * A.n_cols, stride = (uint64_t)gridDim.x * blockDim.x;
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < total; i += 4 * stride) {  // four independent 16-byte loads in flight per thread
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const uint64_t j = i + u * stride;
+      v[u] = A.src[j / A.vec][j % A.vec];
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const uint64_t j = i + u * stride;
+      A.dst[j / A.vec][j % A.vec] = v[u];
+    }
+  }
+  for (; i < total; i += stride) A.dst[i / A.vec][i % A.vec] = A.src[i / A.vec][i % A.vec];
+}
+
 // flag[0] = 1 when the producer of a pending table wanted more rows than its buffers hold (the table is then garbage)
 __global__ void k_lazy_overflow(const unsigned long long* __restrict__ total, uint64_t cap, unsigned long long* __restrict__ flag) {
   flag[0] = *total > cap ? 1ull : 0ull;
@@ -472,11 +503,17 @@ static P2pResult shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col,
   const uint64_t cap = ((half - kArenaCtrl) / (4 * C)) & ~31ull;
   const size_t off = (cm.epoch++ & 1) * half;
   const uint64_t n = in->rows;
-  const int W = g + 1;  // words per rank in the gathered matrix: g sent counts + the stale-input flag
-  BufRef d_cnt = ctx->alloc((uint64_t)(g + 1) * W * 8);
-  unsigned long long* d_sent = d_cnt->as<unsigned long long>() + (uint64_t)g * W;
-  RF_CUDA(cudaMemsetAsync(d_sent, 0, W * 8, ctx->stream()));
+  // words per rank in the gathered matrix: g sent counts, the stale-input flag, the failure flag.  The matrix lives in a
+  // buffer allocated with the communicator: nothing between here and the all-gather allocates, and whatever does fail on
+  // this rank before the all-gather is reported THROUGH it, so that the peers do not wait for a rank that has already
+  // thrown (they all throw after the gather instead).
+  const int W = g + 2;
+  unsigned long long* d_all = cm.d_counts;
+  unsigned long long* d_sent = d_all + (uint64_t)g * W;
   const unsigned long long* n_dev = in->lazy ? ctx->lazy_d + in->lazy->slot : nullptr;
+  std::string local_error;
+  try {
+  RF_CUDA(cudaMemsetAsync(d_sent, 0, W * 8, ctx->stream()));
   if (n) {
     P2pArgs A{};
     A.key = in->cols[key_col].data;
@@ -496,27 +533,43 @@ static P2pResult shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col,
   // completion barrier + size exchange: a rank contributes only after its kernel (stream order), so when the gather
   // completes here every peer's stores into this arena are done
   if (n_dev) k_lazy_overflow<<<1, 1, 0, ctx->stream()>>>(n_dev, in->lazy->cap, d_sent + g);
-  RF_NCCL(nccl().AllGather(d_sent, d_cnt->ptr, W, ncclUint64, cm.comm, ctx->stream()));
+  } catch (const std::exception& e) {
+    local_error = e.what();
+    cudaGetLastError();
+    cudaMemsetAsync(d_sent + g + 1, 0xFF, 8, ctx->stream());  // the failure flag
+  }
+  {
+    KernelScope ks(ctx, "ncclAllGather(sent counts)", 0, nullptr, false);
+    RF_NCCL(nccl().AllGather(d_sent, d_all, W, ncclUint64, cm.comm, ctx->stream()));
+  }
   uint64_t* all = cm.h_counts;  // pinned: the copy is asynchronous and the sync below is the only wait
-  RF_CUDA(cudaMemcpyAsync(all, d_cnt->ptr, (uint64_t)g * W * 8, cudaMemcpyDeviceToHost, ctx->stream()));
+  RF_CUDA(cudaMemcpyAsync(all, d_all, (uint64_t)g * W * 8, cudaMemcpyDeviceToHost, ctx->stream()));
   ctx->sync();
   uint64_t mine = 0;
   bool fits = true, stale = false;
+  int failed_rank = -1;
   for (int r = 0; r < g; r++) {
     uint64_t tot = 0;
     for (int s = 0; s < g; s++) tot += all[(size_t)s * W + r];
     fits = fits && tot <= cap;
     stale = stale || all[(size_t)r * W + g] != 0;
+    if (all[(size_t)r * W + g + 1] != 0 && failed_rank < 0) failed_rank = r;
     if (r == me) mine = tot;
   }
   uint8_t* local = cm.arena[me] + off;
   // cursor back to 0 for shuffle k+2 — queued before anything below can throw: an error on this rank must not leave the
   // arena half unusable for the peers (the copy-out below only reads rows, the cursor word is not part of them)
   RF_CUDA(cudaMemsetAsync(local, 0, 8, ctx->stream()));
+  RF_REQUIRE(failed_rank < 0, RFGPU_E_EXEC,
+             failed_rank == me ? "shuffle failed on this rank: " + local_error
+                               : "shuffle failed on rank " + std::to_string(failed_rank) + " (every rank gives up together)");
   if (stale) return kP2pStaleInput;
   if (fits) {
     RF_REQUIRE(mine < 0xFFFFFFFFull, RFGPU_E_UNSUPPORTED, "shuffle result exceeds 2^32-2 rows on one GPU");
     t->rows = mine;
+    CopyOutArgs O{};
+    O.n_cols = (uint32_t)C;
+    O.vec = (mine + 3) / 4;
     for (size_t c = 0; c < C; c++) {
       Column col = in->cols[c];
       // rows arrive from every rank: only the key column has a known residue class now (dest = id mod g)
@@ -524,10 +577,14 @@ static P2pResult shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col,
       col.mod_r = (int)c == key_col ? (uint32_t)me : 0u;
       col.owner = alloc_col(ctx, mine);
       col.data = col.owner->as<uint32_t>();
-      if (mine)
-        RF_CUDA(cudaMemcpyAsync(col.owner->ptr, local + kArenaCtrl + c * cap * 4, mine * 4, cudaMemcpyDeviceToDevice,
-                                ctx->stream()));
+      O.src[c] = reinterpret_cast<const uint4*>(local + kArenaCtrl + c * cap * 4);
+      O.dst[c] = col.owner->as<uint4>();
       t->cols.push_back(std::move(col));
+    }
+    if (mine) {
+      KernelScope ks(ctx, "k_copy_out", 8ull * C * mine);
+      const uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(O.vec * C, 256 * 4), (uint64_t)ctx->core->num_sms * 8));
+      k_copy_out<<<grid, 256, 0, ctx->stream()>>>(O);
     }
     uint64_t link_rows = 0;
     for (int r = 0; r < g; r++)
@@ -563,7 +620,8 @@ int32_t rfgpu_comm_init(rfgpu_ctx* ctx, int32_t rank, int32_t n_ranks, const uin
   RF_NCCL(rf::nccl().CommInitRank(&c->comm, n_ranks, u, rank));
   c->rank = rank;
   c->size = n_ranks;
-  RF_CUDA(cudaHostAlloc((void**)&c->h_counts, (size_t)(rf::kMaxParts + 1) * rf::kMaxParts * 8, cudaHostAllocDefault));
+  RF_CUDA(cudaHostAlloc((void**)&c->h_counts, (size_t)(rf::kMaxParts + 2) * (rf::kMaxParts + 1) * 8, cudaHostAllocDefault));
+  RF_CUDA(cudaMalloc((void**)&c->d_counts, (size_t)(rf::kMaxParts + 2) * (rf::kMaxParts + 1) * 8));
   rf::setup_arenas(ctx, *c);
   ctx->comm = c;
   RF_API_END(ctx)

@@ -89,6 +89,7 @@ inline int __syncthreads_count(int pred) {
   __syncthreads();
   return r;
 }
+inline int __syncthreads_or(int pred) { return __syncthreads_count(pred) != 0; }
 inline void __syncwarp(unsigned = 0xFFFFFFFFu) { emu::g_cta->warp[threadIdx.x >> 5]->arrive_and_wait(); }
 namespace emu {
 // every lane deposits v, all lanes see all 32 values; the second barrier lets the buffer be reused

@@ -18,7 +18,7 @@ DevBuf::DevBuf(std::shared_ptr<Core> c, size_t n) : core(std::move(c)), bytes(n)
   std::memset(ptr, 0xA5, n);  // uninitialised device memory is not zero
 }
 DevBuf::~DevBuf() { std::free(ptr); }
-KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes, cudaStream_t) : ctx(c) {
+KernelScope::KernelScope(rfgpu_ctx* c, const char* name, uint64_t bytes, cudaStream_t, bool) : ctx(c) {
   ctx->m.kernel_launches++;
   idx = ctx->kstat_index(name);
   ctx->kstats[idx].second.launches++;
