@@ -74,6 +74,8 @@ def parse_args():
                     help="diagnostic: start / end of every kernel launch of one more step, written to FILE")
     ap.add_argument("--host-profile", default=None, metavar="FILE",
                     help="diagnostic: cProfile of 20 more device-resident steps (host side only), top functions written to FILE")
+    ap.add_argument("--no-bulk-shuffle", action="store_true",
+                    help="fused shuffle kernel with one store per row and thread instead of bulk copies (RFGPU_OPT_SHUFFLE_BULK off)")
     ap.add_argument("--no-lazy-rows", action="store_true",
                     help="every join / filter waits for its output row count (RFGPU_OPT_LAZY_ROWS off)")
     return ap.parse_args()
@@ -277,6 +279,8 @@ def run_ours(a):
         ctx.set_option(F.OPT_LOOKUP_JOIN, 0)
     if a.no_lazy_rows:
         ctx.set_option(F.OPT_LAZY_ROWS, 0)
+    if a.no_bulk_shuffle:
+        ctx.set_option(F.OPT_SHUFFLE_BULK, 0)
     if a.nccl_shuffle:
         ctx.set_option(F.OPT_SHUFFLE_P2P, 0)
     if world > 1:

@@ -478,6 +478,8 @@ typedef enum {
   RFGPU_OPT_LOOKUP_JOIN = 11,    /* 1 (default): single-key equi joins, MINUS / EXISTS and GROUP BY whose (build) keys span a
                                     range of at most 8 slots per input row use a direct-address table (slot = id - min id)
                                     instead of the open-addressing hash table; 0: always hash */
+  RFGPU_OPT_SHUFFLE_BULK = 13,   /* 1 (default): the fused shuffle kernel writes each destination's run with bulk copies (copy engine,
+                                    shared -> peer memory); 0: one 4-byte store per row and thread */
   RFGPU_OPT_LAZY_ROWS = 12,      /* 1 (default): joins and filters return before their output row count has reached the host
                                     (see rfgpu_table_num_rows); 0: every operator waits for its count */
   RFGPU_OPT_SHUFFLE_ARENA_BYTES = 7 /* size of this rank's receive arena (two halves, used alternately); read by

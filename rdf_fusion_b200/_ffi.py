@@ -46,6 +46,7 @@ OPT_SORT_SEMI = 9
 OPT_SORT_AGG = 10
 OPT_LOOKUP_JOIN = 11
 OPT_LAZY_ROWS = 12
+OPT_SHUFFLE_BULK = 13
 SHUFFLE_LOCAL, SHUFFLE_NCCL, SHUFFLE_P2P = 0, 1, 2
 UNIQUE_ID_BYTES = 128
 

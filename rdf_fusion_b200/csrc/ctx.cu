@@ -130,6 +130,18 @@ void rfgpu_ctx::collect_profile() {
   pending.clear();
 }
 
+// top[l * top_n + k] = col[l][k << shift]: the sampled top level of the range look-up (rfgpu_index_t::top)
+__global__ void k_build_top(const uint32_t* c0, const uint32_t* c1, const uint32_t* c2, const uint32_t* c3, uint32_t top_n,
+                            uint32_t shift, uint32_t* __restrict__ top) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= top_n) return;
+  const uint64_t row = (uint64_t)k << shift;
+  top[k] = c0[row];
+  top[top_n + k] = c1[row];
+  top[2 * top_n + k] = c2[row];
+  top[3 * top_n + k] = c3[row];
+}
+
 __global__ void k_check_residue(const uint32_t* __restrict__ v, uint64_t n, uint32_t g, uint32_t r,
                                 unsigned long long* __restrict__ first_bad) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -365,6 +377,18 @@ int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm, con
                                            std::to_string(s->place_r) + " of " + std::to_string(s->place_g) +
                                            " under the declared placement");
   }
+  if (n_rows > (1u << 17)) {  // smaller indexes: the first cooperative step already lands in one page
+    uint32_t shift = 17;
+    while (((n_rows - 1) >> shift) + 1 > 1024) shift++;  // one sampled tuple per search thread at most
+    ix.top_shift = shift;
+    ix.top_n = (uint32_t)(((n_rows - 1) >> shift) + 1);
+    ix.top = ctx->alloc((uint64_t)ix.top_n * 16);
+    rf::KernelScope ks(ctx, "k_build_top");
+    k_build_top<<<rf::div_up(ix.top_n, 256), 256, 0, ctx->stream()>>>(ix.col[0]->as<uint32_t>(), ix.col[1]->as<uint32_t>(),
+                                                                       ix.col[2]->as<uint32_t>(), ix.col[3]->as<uint32_t>(),
+                                                                       ix.top_n, shift, ix.top->as<uint32_t>());
+  }
+  ctx->sync();  // the index (and its top level) is complete on the device before any look-up stream reads it
   s->indexes.push_back(std::move(ix));
   RF_API_END(ctx)
 }

@@ -1437,6 +1437,7 @@ int32_t rfgpu_ctx_set_option(rfgpu_ctx* ctx, int32_t option, int64_t value) {
       ctx->opt_merge_threads = (int)value;
       break;
     case RFGPU_OPT_SHUFFLE_P2P: ctx->opt_shuffle_p2p = value != 0; break;
+    case RFGPU_OPT_SHUFFLE_BULK: ctx->opt_shuffle_bulk = value != 0; break;
     case RFGPU_OPT_SHUFFLE_ARENA_BYTES:
       RF_REQUIRE(value >= (1 << 20), RFGPU_E_INVALID, "shuffle arena must be >= 1 MiB");
       ctx->opt_shuffle_arena_bytes = value;

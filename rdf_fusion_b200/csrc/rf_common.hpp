@@ -132,6 +132,11 @@ struct rfgpu_index_t {
   uint32_t perm = 0;
   uint64_t rows = 0;
   rf::BufRef col[4];  // level i column, uint32_t[rows]
+  // top level of the range look-up: the tuples of every 2^top_shift-th row, 4 x top_n ids in one small allocation (level-major).
+  // The first search step reads this (one page, L2-resident) instead of 1024 pivots spread over the whole index, each on a
+  // page of its own; the remaining steps stay inside one 2^top_shift-row window.  top_n = 0: not built.
+  rf::BufRef top;
+  uint32_t top_n = 0, top_shift = 0;
 };
 
 struct rfgpu_store {
@@ -156,6 +161,7 @@ struct rfgpu_ctx {
   int64_t opt_hash_l2_bytes = 1ll << 40;   // table bytes one pass of the hash join may hold; > this ⇒ multi-pass L2 blocking
                                            // (opt-in: measured no faster yet)
   int opt_merge_threads = 128;  // CTA size of k_merge_join (tile = 8 rows per thread)
+  bool opt_shuffle_bulk = true;  // k_shuffle_p2p writes its runs with bulk copies (shared -> peer memory) instead of per-row stores
   bool opt_shuffle_p2p = true;  // rfgpu_shuffle: fused partition + peer-memory scatter when the IPC arenas are mapped
   int64_t opt_shuffle_arena_bytes = 1ll << 30;  // receive arena of this rank (read by rfgpu_comm_init)
   // sort-based operators (sort.cu); opt-in until measured on a device

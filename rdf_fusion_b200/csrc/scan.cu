@@ -24,6 +24,8 @@ struct SearchArgs {
   uint32_t key[2][4];  // [0] lower tuple, [1] upper tuple
   int32_t depth;       // number of leading columns compared
   int32_t sort_level;  // level the rows of the range ascend by (-1: none): its values at both ends are reported too
+  const uint32_t* top;  // rfgpu_index_t::top (level-major, top_n ids per level) or NULL
+  uint32_t top_n, top_shift;
 };
 
 // value of the sort level at the found end of the range (the first row for the lower bound, the last for the upper one)
@@ -50,11 +52,37 @@ __device__ __forceinline__ bool tuple_cmp(const SearchArgs& A, int which, uint64
 
 constexpr int kSearchThreads = 1024;
 
+// first step of a look-up over the index' sampled top level (rows k << top_shift): narrows [lo, hi] to one window
+__device__ __forceinline__ void search_top(const SearchArgs& A, int which, uint64_t& lo, uint64_t& hi) {
+  if (A.top_n == 0) return;
+  bool below = false;
+  if (threadIdx.x < A.top_n) {
+    uint32_t v[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) v[j] = j < A.depth ? __ldg(A.top + (uint64_t)j * A.top_n + threadIdx.x) : 0u;
+    bool ge = which == 0;  // tuple_cmp on the sampled tuple
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      if (j >= A.depth) break;
+      const uint32_t k = A.key[which][j];
+      if (v[j] != k) {
+        ge = v[j] > k;
+        break;
+      }
+    }
+    below = !ge;
+  }
+  const uint64_t c = __syncthreads_count(below);  // monotone: sampled rows 0 .. c-1 are below the key, row c << shift is not
+  lo = c ? ((c - 1) << A.top_shift) + 1 : 0;
+  hi = min(A.n, c << A.top_shift);
+}
+
 // grid = 2 CTAs: blockIdx.x = 0 → lower bound of key[0]; 1 → upper bound of key[1].  result[] is pinned host memory.
 __global__ void __launch_bounds__(kSearchThreads)
 k_range_search(const __grid_constant__ SearchArgs A, unsigned long long* __restrict__ result) {
   const int which = blockIdx.x;
   uint64_t lo = 0, hi = A.n;  // answer in [lo, hi]
+  search_top(A, which, lo, hi);
   while (hi > lo) {
     uint64_t width = hi - lo;
     if (width <= kSearchThreads) {
@@ -89,6 +117,7 @@ k_range_search_many(const __grid_constant__ SearchBatch B, unsigned long long* _
   const SearchArgs& A = B.q[blockIdx.x >> 1];
   const int which = blockIdx.x & 1;
   uint64_t lo = 0, hi = A.n;
+  search_top(A, which, lo, hi);
   while (hi > lo) {
     uint64_t width = hi - lo;
     if (width <= kSearchThreads) {
@@ -239,6 +268,11 @@ static int search_args_for(const rfgpu_index_t* ix, const ScanInstrs& ins, Searc
   }
   S->depth = depth;
   for (int l = 0; l < 4; l++) S->col[l] = ix->col[l]->as<uint32_t>();
+  if (ix->top_n) {
+    S->top = ix->top->as<uint32_t>();
+    S->top_n = ix->top_n;
+    S->top_shift = ix->top_shift;
+  }
   S->sort_level = -1;
   const std::string sv = ins.sorted_var();
   for (int l = 0; l < 4 && !sv.empty(); l++)

@@ -247,8 +247,11 @@ struct P2pSmem {
   uint32_t start[2][kMaxParts];  // exclusive prefix of cnt: where the destination's run starts in the tile
   uint32_t sent[kMaxParts];      // per-CTA total over its tiles
   uint32_t* ptr[kMaxParts];      // ptr[d][j] = slot of the tile's staged row j in d's arena, column 0
-  uint32_t val[kP2pTile];        // one column of the tile, ordered by destination
-  uint8_t dest[kP2pTile];
+  // one column of the tile, ordered by destination.  Bulk variant: run d starts at a slot congruent (mod 4) to its first row
+  // in d's arena, so that 16-byte aligned pieces of the run are 16-byte aligned at the destination too (at most 6 slots of
+  // padding per destination: up to 3 in front of the run, up to 3 behind it)
+  __align__(16) uint32_t val[2][kP2pTile + 6 * kMaxParts];  // two buffers: the copy engine reads one while the next column is staged
+  uint8_t dest[kP2pTile + 6 * kMaxParts];
 };
 
 // destinations + tickets of one tile: out[k] = ticket (low 16 bits) | destination << 16; every thread calls it
@@ -271,7 +274,11 @@ __device__ __forceinline__ void p2p_reserve(const P2pArgs& A, P2pSmem& S, int b,
   const uint32_t tid = threadIdx.x, lane = tid & 31;
   if (tid < A.n_parts) {
     cnt = S.cnt[b][tid];
+#ifdef RF_SHUFFLE_DIAG_LOCALATOMIC  // timing diagnostic only (results are wrong): the reservation does not cross NVLink
+    base = cnt ? atomicAdd(A.sent + 8 + tid, (unsigned long long)cnt) : 0ull;
+#else
     base = cnt ? atomicAdd_system(reinterpret_cast<unsigned long long*>(A.arena[tid]), (unsigned long long)cnt) : 0ull;
+#endif
     S.sent[tid] += cnt;
   }
   if (tid < 32) {
@@ -301,7 +308,12 @@ __device__ __forceinline__ void p2p_reserve(const P2pArgs& A, P2pSmem& S, int b,
 // at 4 GPUs for 80 MB.  The time follows the bytes that cross NVLink (~355 GB/s per direction in every variant), not the
 // latency chain, the instruction count or the number of remote atomics: what bounds it is the rate at which 128-B
 // SM-issued peer stores drain into the link (next step there: 16-B aligned runs + bulk stores).
-template <bool kPow2>
+// kBulk: the runs are written with cp.async.bulk (shared -> peer global memory, one copy per destination, column and tile,
+// issued by one lane) instead of one 4-byte store per row and thread.  Measured with every destination redirected to the
+// local arena the kernel takes 46 us for a 4.2 M-row x 3-column table at 2 GPUs, 88 us with half of the rows crossing
+// NVLink: with thread-issued stores the link time ADDS to the processing time (the warps stall on the store queue while the
+// link drains); the copy engine takes the runs off the warps' hands, so the two overlap.
+template <bool kPow2, bool kBulk>
 __global__ void __launch_bounds__(kP2pThreads, 3)
 k_shuffle_p2p(const __grid_constant__ P2pArgs A) {
   __shared__ P2pSmem S;
@@ -332,6 +344,7 @@ k_shuffle_p2p(const __grid_constant__ P2pArgs A) {
   __syncthreads();
   unsigned long long base = 0;
   uint32_t cnt = 0;
+  uint32_t colno = 0;  // columns written so far (bulk variant: selects the staging buffer)
   p2p_reserve(A, S, 0, base, cnt);
   for (int b = 0; row0 < n; row0 += step, b ^= 1) {
     const uint32_t rows = (uint32_t)min((uint64_t)kP2pTile, n - row0);
@@ -339,6 +352,24 @@ k_shuffle_p2p(const __grid_constant__ P2pArgs A) {
     const uint32_t rows_next = next0 < n ? (uint32_t)min((uint64_t)kP2pTile, n - next0) : 0;
     if (tid < kMaxParts) S.cnt[b ^ 1][tid] = 0;
     __syncthreads();  // start[b] visible; the previous tile's write-out is over
+    if (kBulk) {
+      // re-place the runs: region d = [R_d, R_d + len_d) with len_d = (base_d mod 4) + cnt_d rounded up to 4 slots,
+      // run d starts at R_d + (base_d mod 4).  base_d (the reservation's result) has arrived by now.  (The host selects this
+      // variant for at most 32 ranks: one warp scans the regions.)
+      if (tid < 32) {
+        const uint32_t lane = tid;
+        const uint32_t b0 = (uint32_t)base & 3u;  // thread d holds destination d's reservation
+        uint32_t l0 = lane < A.n_parts ? (b0 + cnt + 3u) & ~3u : 0u;
+        uint32_t i0 = l0;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const uint32_t u0 = __shfl_up_sync(0xFFFFFFFFu, i0, d);
+          if (lane >= (uint32_t)d) i0 += u0;
+        }
+        if (lane < A.n_parts) S.start[b][lane] = i0 - l0 + b0;
+      }
+      __syncthreads();
+    }
     if (tid < A.n_parts)  // a run that does not fit the arena is dropped whole: the host sees the overflow and falls back
       S.ptr[tid] = base + cnt <= A.cap ? reinterpret_cast<uint32_t*>(A.arena[tid] + kArenaCtrl) + base - S.start[b][tid]
                                         : nullptr;
@@ -359,9 +390,10 @@ k_shuffle_p2p(const __grid_constant__ P2pArgs A) {
     __syncthreads();  // cnt[b^1] final; ptr / dest of this tile visible
     p2p_reserve(A, S, b ^ 1, base, cnt);
     for (int c = 0; c < A.n_cols; c++) {
+      uint32_t* const sval = S.val[kBulk ? (colno++ & 1u) : 0];
 #pragma unroll
       for (int k = 0; k < kP2pRows; k++)
-        if ((pk[k] >> 16) < kMaxParts) S.val[pk[k] & 0xFFFFu] = v[k];
+        if ((pk[k] >> 16) < kMaxParts) sval[pk[k] & 0xFFFFu] = v[k];
       {  // next column of this tile, or the first column of the next tile
         const bool last = c + 1 == A.n_cols;
         const uint32_t* const src = A.src[last ? 0 : c + 1];
@@ -372,15 +404,38 @@ k_shuffle_p2p(const __grid_constant__ P2pArgs A) {
           v[k] = i < n ? __ldg(src + i) : 0;
         }
       }
+      if (kBulk) dev::fence_proxy_async();  // the staged values are read by the copy engine (async proxy)
       __syncthreads();
-      // consecutive threads → consecutive rows of one destination's run → 128-B peer stores
       const uint64_t col_off = (uint64_t)c * A.cap;
+      if (!kBulk) {
+        // consecutive threads → consecutive rows of one destination's run → 128-B peer stores
 #pragma unroll
-      for (int k = 0; k < kP2pRows; k++) {
-        const uint32_t j = k * kP2pThreads + tid;
-        if (j < rows) {
-          uint32_t* const p = S.ptr[S.dest[j]];
-          if (p) __stcg(p + col_off + j, S.val[j]);
+        for (int k = 0; k < kP2pRows; k++) {
+          const uint32_t j = k * kP2pThreads + tid;
+          if (j < rows) {
+            uint32_t* const p = S.ptr[S.dest[j]];
+            if (p) __stcg(p + col_off + j, sval[j]);
+          }
+        }
+      } else {
+        // warp w writes the runs of destinations w, w + 8, ...: the 16-byte aligned middle of a run as ONE bulk copy issued
+        // by lane 0, the (at most 3 + 3) rows around it with ordinary stores
+        const uint32_t lane = tid & 31, warp = tid >> 5;
+        for (uint32_t d = warp; d < A.n_parts; d += kP2pThreads / 32) {
+          uint32_t* const p = S.ptr[d];
+          const uint32_t s0 = S.start[b][d], e0 = s0 + S.cnt[b][d];
+          if (!p || e0 == s0) continue;
+          const uint32_t a = min(e0, (s0 + 3u) & ~3u), z = max(a, e0 & ~3u);
+          if (lane < a - s0) __stcg(p + col_off + s0 + lane, sval[s0 + lane]);
+          if (lane >= 4 && lane - 4 < e0 - z) __stcg(p + col_off + z + lane - 4, sval[z + lane - 4]);
+          if (lane == 0 && z > a) dev::bulk_s2g(p + col_off + a, &sval[a], (z - a) * 4);
+        }
+        if (lane == 0) {
+          // one group per column and issuing lane (empty if it had no run).  The NEXT column is staged into the other
+          // buffer, last read by the previous column's group: wait until the engine has READ that one (all but the newest
+          // group) — not for this column's copy, and never for the remote writes.
+          dev::bulk_commit();
+          dev::bulk_wait_read<1>();
         }
       }
       __syncthreads();
@@ -388,6 +443,7 @@ k_shuffle_p2p(const __grid_constant__ P2pArgs A) {
 #pragma unroll
     for (int k = 0; k < kP2pRows; k++) pk[k] = pn[k];
   }
+  if (kBulk) dev::bulk_wait<0>();  // every copy this thread issued is complete before the CTA retires
   __syncthreads();
   if (tid < A.n_parts && S.sent[tid]) atomicAdd(A.sent + tid, (unsigned long long)S.sent[tid]);
 }
@@ -513,7 +569,11 @@ static P2pResult shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col,
   const unsigned long long* n_dev = in->lazy ? ctx->lazy_d + in->lazy->slot : nullptr;
   std::string local_error;
   try {
+#ifdef RF_SHUFFLE_DIAG_LOCALATOMIC
+  RF_CUDA(cudaMemsetAsync(d_sent, 0, (W + 16) * 8, ctx->stream()));
+#else
   RF_CUDA(cudaMemsetAsync(d_sent, 0, W * 8, ctx->stream()));
+#endif
   if (n) {
     P2pArgs A{};
     A.key = in->cols[key_col].data;
@@ -524,11 +584,20 @@ static P2pResult shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col,
     A.cap = cap;
     for (size_t c = 0; c < C; c++) A.src[c] = in->cols[c].data;
     for (int r = 0; r < g; r++) A.arena[r] = cm.arena[r] + off;
+#ifdef RF_SHUFFLE_DIAG_LOCAL  // timing diagnostic only (results are wrong): every destination is this rank's own arena — no NVLink
+    for (int r = 0; r < g; r++) A.arena[r] = cm.arena[me] + off;
+#endif
     A.sent = d_sent;
     const uint32_t grid = (uint32_t)std::min<uint64_t>(div_up(n, kP2pTile), (uint64_t)ctx->core->num_sms * 3);
     KernelScope ks(ctx, "k_shuffle_p2p", 8ull * C * n);
-    if ((g & (g - 1)) == 0) k_shuffle_p2p<true><<<grid, kP2pThreads, 0, ctx->stream()>>>(A);
-    else k_shuffle_p2p<false><<<grid, kP2pThreads, 0, ctx->stream()>>>(A);
+    const bool pow2 = (g & (g - 1)) == 0;
+    if (ctx->opt_shuffle_bulk && g <= 32) {
+      if (pow2) k_shuffle_p2p<true, true><<<grid, kP2pThreads, 0, ctx->stream()>>>(A);
+      else k_shuffle_p2p<false, true><<<grid, kP2pThreads, 0, ctx->stream()>>>(A);
+    } else {
+      if (pow2) k_shuffle_p2p<true, false><<<grid, kP2pThreads, 0, ctx->stream()>>>(A);
+      else k_shuffle_p2p<false, false><<<grid, kP2pThreads, 0, ctx->stream()>>>(A);
+    }
   }
   // completion barrier + size exchange: a rank contributes only after its kernel (stream order), so when the gather
   // completes here every peer's stores into this arena are done

@@ -69,6 +69,16 @@ int32_t rfgpu_store_add_index(rfgpu_ctx* ctx, rfgpu_store* s, uint32_t perm, con
                "index columns are not strictly sorted in permutation order at row " + std::to_string(r));
   }
   if (!s->indexes.empty()) RF_REQUIRE(s->indexes[0].rows == n_rows, RFGPU_E_INVALID, "all permutations must hold the same quads");
+  if (n_rows > 64) {  // the sampled top level of the range look-up (ctx.cu: k_build_top), at a small shift so that tests reach it
+    uint32_t shift = 3;
+    while (((n_rows - 1) >> shift) + 1 > 1024) shift++;
+    ix.top_shift = shift;
+    ix.top_n = (uint32_t)(((n_rows - 1) >> shift) + 1);
+    ix.top = ctx->alloc((uint64_t)ix.top_n * 16);
+    uint32_t* top = ix.top->as<uint32_t>();
+    for (uint32_t k = 0; k < ix.top_n; k++)
+      for (int l = 0; l < 4; l++) top[(uint64_t)l * ix.top_n + k] = cols[l][(uint64_t)k << shift];
+  }
   s->indexes.push_back(std::move(ix));
   RF_API_END(ctx)
 }
