@@ -313,8 +313,11 @@ __device__ __forceinline__ void p2p_reserve(const P2pArgs& A, P2pSmem& S, int b,
 // local arena the kernel takes 46 us for a 4.2 M-row x 3-column table at 2 GPUs, 88 us with half of the rows crossing
 // NVLink: with thread-issued stores the link time ADDS to the processing time (the warps stall on the store queue while the
 // link drains); the copy engine takes the runs off the warps' hands, so the two overlap.
+#ifndef RF_SHUFFLE_MIN_CTAS
+#define RF_SHUFFLE_MIN_CTAS 3
+#endif
 template <bool kPow2, bool kBulk>
-__global__ void __launch_bounds__(kP2pThreads, 3)
+__global__ void __launch_bounds__(kP2pThreads, RF_SHUFFLE_MIN_CTAS)
 k_shuffle_p2p(const __grid_constant__ P2pArgs A) {
   __shared__ P2pSmem S;
   const uint32_t tid = threadIdx.x;
@@ -588,7 +591,7 @@ static P2pResult shuffle_p2p(rfgpu_ctx* ctx, const rfgpu_table* in, int key_col,
     for (int r = 0; r < g; r++) A.arena[r] = cm.arena[me] + off;
 #endif
     A.sent = d_sent;
-    const uint32_t grid = (uint32_t)std::min<uint64_t>(div_up(n, kP2pTile), (uint64_t)ctx->core->num_sms * 3);
+    const uint32_t grid = (uint32_t)std::min<uint64_t>(div_up(n, kP2pTile), (uint64_t)ctx->core->num_sms * RF_SHUFFLE_MIN_CTAS);
     KernelScope ks(ctx, "k_shuffle_p2p", 8ull * C * n);
     const bool pow2 = (g & (g - 1)) == 0;
     if (ctx->opt_shuffle_bulk && g <= 32) {
