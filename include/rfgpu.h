@@ -404,6 +404,130 @@ int32_t rfgpu_plain_terms_export(rfgpu_ctx* ctx, const rfgpu_plain_terms* p, uin
 int32_t rfgpu_table_lookup(rfgpu_ctx* ctx, const rfgpu_table* t, int32_t col, const uint32_t* table, uint32_t n_table,
                            int32_t on_device, const char* name, rfgpu_table** out);
 
+/* ---- object id -> typed value: ENC_TV (the rest of SURVEY §8f-2) ---- */
+/* Replaces MemObjectIdMapping::decode_array_to_typed_value (lib/storage/src/memory/object_id_mapping.rs:376-402) behind
+ * ENC_TV (lib/functions/src/builtin/encoding/with_typed_value_encoding.rs:63-84), and the comparison operators evaluated
+ * on its result (lib/functions/src/scalar/comparison/{equal,less_than,less_or_equal,greater_than,greater_or_equal}.rs over
+ * TypedValueRef::partial_cmp, lib/model/src/typed_value.rs:162-262).
+ *
+ * The reference keeps an EncodedTypedValue per object id (lib/storage/src/memory/encoding/typed_value.rs:9-25), parsed once
+ * from the term's lexical form when the term is interned (TypedValueRef::try_from, lib/model/src/typed_value.rs:337-410).
+ * The device twin is a table of one 32-byte record per id — one sector per gathered id — holding the fixed-width part of
+ * that value; the strings of the string-valued variants stay in the rfgpu_dict the table is created over.  Parsing stays
+ * with the reference's own parsers on the host: the Rust binding fills rfgpu_tv_value from EncodedTypedValue. */
+typedef struct rfgpu_tv_table rfgpu_tv_table;
+typedef struct rfgpu_typed_values rfgpu_typed_values;
+
+/* TypedValueEncodingField = the type ids of the dense union (lib/encoding/src/typed_value/encoding.rs:241-262, :343-362) */
+typedef enum {
+  RFGPU_TV_NULL = 0,        /* unbound, or a literal whose lexical form is not in its datatype's lexical space (Invalid) */
+  RFGPU_TV_NAMED_NODE = 1,  /* Utf8: the dictionary's value */
+  RFGPU_TV_BLANK_NODE = 2,  /* Utf8 */
+  RFGPU_TV_STRING = 3,      /* Struct{value: Utf8, language: Utf8 nullable}: simple literals / xsd:string and language-tagged strings */
+  RFGPU_TV_BOOLEAN = 4,     /* Boolean: lo = 0 / 1 */
+  RFGPU_TV_FLOAT = 5,       /* Float32: lo = the f32 bits */
+  RFGPU_TV_DOUBLE = 6,      /* Float64: lo = the f64 bits */
+  RFGPU_TV_DECIMAL = 7,     /* Decimal128: (hi, lo) = the i128 of lib/model/src/xsd/decimal.rs (value * 10^18);
+                               aux = the f64 bits of Double::from(decimal) (decimal.rs:445-462), used when it meets a float / double */
+  RFGPU_TV_INT = 8,         /* Int32: lo = the value, sign-extended to 64 bits */
+  RFGPU_TV_INTEGER = 9,     /* Int64: lo */
+  RFGPU_TV_DATE_TIME = 10,  /* Struct{value: Decimal128, offset: Int16 nullable}: (hi, lo) = Timestamp::value(), */
+  RFGPU_TV_TIME = 11,       /*   aux = the timezone offset in minutes when RFGPU_TV_HAS_AUX is set */
+  RFGPU_TV_DATE = 12,       /*   (lib/encoding/src/typed_value/element_builder.rs:385-398) */
+  RFGPU_TV_DURATION = 13,   /* Struct{months: Int64 nullable, seconds: Decimal128 nullable}: aux = months when RFGPU_TV_HAS_AUX,
+                               (hi, lo) = seconds when RFGPU_TV_HAS_VALUE (xsd:duration both, yearMonthDuration / dayTimeDuration one) */
+  RFGPU_TV_OTHER_LITERAL = 14 /* Struct{value: Utf8, datatype: Utf8} */
+} rfgpu_tv_field;
+#define RFGPU_TV_N_FIELDS 15
+#define RFGPU_TV_HAS_AUX 1
+#define RFGPU_TV_HAS_VALUE 2
+
+/* One typed value in its fixed-width form (32 bytes, no implicit padding). */
+typedef struct {
+  uint64_t lo, hi;
+  int64_t aux;
+  uint8_t field;  /* rfgpu_tv_field */
+  uint8_t flags;  /* RFGPU_TV_HAS_AUX | RFGPU_TV_HAS_VALUE */
+  uint8_t reserved[6];
+} rfgpu_tv_value;
+
+/* values[0 .. n_ids]: indexed by object id, entry 0 unused; n_ids must equal rfgpu_dict_len(d).  `d` is retained.  The field
+ * of a string-valued entry must agree with the dictionary's term type (named node / blank node / literal): RFGPU_E_INVALID. */
+int32_t rfgpu_tv_table_create(rfgpu_ctx* ctx, rfgpu_dict* d, const rfgpu_tv_value* values, uint32_t n_ids,
+                              rfgpu_tv_table** out);
+rfgpu_tv_table* rfgpu_tv_table_retain(rfgpu_tv_table* tv);
+void rfgpu_tv_table_release(rfgpu_tv_table* tv);
+
+/* ENC_TV(col): rows [row_off, row_off + n_rows) of column `col` as the dense union array of the TypedValue encoding, device
+ * resident: type_ids, offsets, and every child compacted in row order (TypedValueArrayElementBuilder,
+ * lib/encoding/src/typed_value/element_builder.rs:83-398).  NULL ids and Invalid values land in the null child.  An id beyond
+ * the dictionary is RFGPU_E_INVALID (the reference panics: "Missing EncodedObjectId"). */
+int32_t rfgpu_tv_decode(rfgpu_ctx* ctx, const rfgpu_tv_table* tv, const rfgpu_table* t, int32_t col, uint64_t row_off,
+                        uint64_t n_rows, rfgpu_typed_values** out);
+void rfgpu_typed_values_release(rfgpu_typed_values* v);
+/* rows and the length of each of the 15 children */
+int32_t rfgpu_typed_values_sizes(const rfgpu_typed_values* v, uint64_t* rows, uint64_t counts[RFGPU_TV_N_FIELDS]);
+/* The strings of a string-valued child (field 1, 2, 3 or 14) in PlainTerm form, one row per child element (borrowed: valid
+ * until `v` is released; NULL for an empty child or another field): named / blank node = its `value` child; string = value +
+ * language_tag; other literal = value + data_type.  Read them with rfgpu_plain_terms_sizes / _export. */
+const rfgpu_plain_terms* rfgpu_typed_values_strings(const rfgpu_typed_values* v, int32_t field);
+/* Host destinations of the fixed-width buffers; a NULL member is skipped.  Decimal128 values are 16 bytes each, little endian
+ * (Arrow's layout); validity bitmaps are LSB-first, (count + 7) / 8 bytes. */
+typedef struct {
+  int8_t* type_ids;            /* [rows] */
+  int32_t* offsets;            /* [rows] */
+  uint8_t* boolean_bits;       /* (counts[4] + 7) / 8 bytes */
+  float* floats;               /* [counts[5]] */
+  double* doubles;             /* [counts[6]] */
+  uint8_t* decimals;           /* [counts[7]] x 16 B */
+  int32_t* ints;               /* [counts[8]] */
+  int64_t* integers;           /* [counts[9]] */
+  uint8_t* ts_value[3];        /* date_time, time, date: [counts[10 + k]] x 16 B */
+  int16_t* ts_offset[3];       /* [counts[10 + k]] */
+  uint8_t* ts_offset_valid[3];
+  int64_t* dur_months;         /* [counts[13]] */
+  uint8_t* dur_months_valid;
+  uint8_t* dur_seconds;        /* [counts[13]] x 16 B */
+  uint8_t* dur_seconds_valid;
+} rfgpu_tv_export;
+int32_t rfgpu_typed_values_export(rfgpu_ctx* ctx, const rfgpu_typed_values* v, const rfgpu_tv_export* dst);
+
+/* A value FILTER evaluated where the ids are: a postfix program over typed values whose result is the effective boolean
+ * value of the expression per row.  Comparisons push one truth value (SPARQL's three-valued logic: true / false / error),
+ * AND / OR / NOT combine the top of the stack as SPARQL 1.1 §17.2 defines (error || true = true, error && false = false).
+ * The output is the input table plus the nullable column `name`: 1 = true, 2 = false, NULL = error — so FILTER(e) is
+ * RFGPU_F_EQ_CONST(name, 1) for rfgpu_filter / rfgpu_sparql_join_filter and FILTER(!e) is RFGPU_F_EQ_CONST(name, 2).
+ * A comparison whose operand is NULL or Invalid is an error (dispatch/binary.rs: error_op), as is every pair partial_cmp
+ * leaves unordered.  Duration-against-duration comparisons (calendar arithmetic on four reference dates,
+ * lib/model/src/xsd/duration.rs:271-308) are not evaluated on the device: RFGPU_E_UNSUPPORTED if a row needs one. */
+typedef enum {
+  RFGPU_TV_EQ = 0,  /* partial_cmp == Equal   (equal.rs:57) */
+  RFGPU_TV_LT = 1,  /* == Less                (less_than.rs:55) */
+  RFGPU_TV_LE = 2,  /* Equal or Less          (less_or_equal.rs:55) */
+  RFGPU_TV_GT = 3,  /* == Greater             (greater_than.rs:55) */
+  RFGPU_TV_GE = 4,  /* Equal or Greater       (greater_or_equal.rs:55) */
+  RFGPU_TV_AND = 5, /* pops two, pushes one */
+  RFGPU_TV_OR = 6,
+  RFGPU_TV_NOT = 7, /* pops one, pushes one */
+  RFGPU_TV_BOUND = 8 /* BOUND(lhs column): true / false, never an error */
+} rfgpu_tv_op;
+typedef struct {
+  int32_t op;        /* rfgpu_tv_op */
+  int32_t lhs, rhs;  /* comparison operands: >= 0 a column of the table, < 0 the constant -(k + 1) */
+} rfgpu_tv_instr;
+typedef struct {
+  rfgpu_tv_value v;
+  const uint8_t* str;   /* string-valued fields: the value bytes (host memory) */
+  uint32_t str_len;
+  const uint8_t* str2;  /* STRING with RFGPU_TV_HAS_AUX: the language tag; OTHER_LITERAL: the datatype IRI */
+  uint32_t str2_len;
+} rfgpu_tv_const;
+#define RFGPU_TV_MAX_INSTRS 16
+#define RFGPU_TV_MAX_CONSTS 8
+#define RFGPU_TV_MAX_CONST_BYTES 1024 /* all constant strings of one program together */
+int32_t rfgpu_tv_eval(rfgpu_ctx* ctx, const rfgpu_tv_table* tv, const rfgpu_table* t, const rfgpu_tv_instr* prog,
+                      int32_t n_instr, const rfgpu_tv_const* consts, int32_t n_consts, const char* name, rfgpu_table** out);
+
 /* physical operator of the last rfgpu_group_count / rfgpu_distinct */
 typedef enum {
   RFGPU_AGG_PHYS_NONE = 0,

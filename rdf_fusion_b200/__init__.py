@@ -8,5 +8,6 @@ from ._ffi import (ALGO_COMPATIBLE, ALGO_CROSS, ALGO_EQUI, F_BETWEEN, F_EQ_COL, 
                    F_IS_NOT_NULL, F_IS_NULL, F_NE_COL, F_NE_CONST, GOPS, GOSP, GPOS, GPSO, GSOP, GSPO, JOIN_INNER,
                    JOIN_LEFT, OP_EQ, OP_GT, OP_GTEQ, OP_LT, OP_LTEQ, PERM_NAMES)
 from .api import (FALSE, Between, Context, Dictionary, EqualTo, FPred, In, Instr, Pred, RfgpuError, ScanPlan, Store,  # noqa: F401
-                  Table, execute_many, make_filter_preds, make_instructions, numeric_rank_table, pack_terms, scan, traverse)
+                  Table, TV_VALUE_DTYPE, TypedValueTable, execute_many, make_filter_preds, make_instructions, numeric_rank_table,
+                  pack_terms, scan, traverse, typed_values_to_arrow)
 from .synth import BsbmLikeGraph, SynthGraph, generate_bsbm_like, generate_graph  # noqa: F401

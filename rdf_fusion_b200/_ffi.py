@@ -92,6 +92,35 @@ PLACE_NONE, PLACE_JOINED_COMPONENT, PLACE_SUBJECT = 0, 1, 2
 SYNTH_KEEP_ALL, SYNTH_KEEP_HASH_SUBJECT, SYNTH_KEEP_RANGE, SYNTH_KEEP_HASH_OBJECT = 0, 1, 2, 3
 
 
+# typed values (ENC_TV): rfgpu_tv_field / rfgpu_tv_op and the structs of include/rfgpu.h
+(TV_NULL, TV_NAMED_NODE, TV_BLANK_NODE, TV_STRING, TV_BOOLEAN, TV_FLOAT, TV_DOUBLE, TV_DECIMAL, TV_INT, TV_INTEGER, TV_DATE_TIME,
+ TV_TIME, TV_DATE, TV_DURATION, TV_OTHER_LITERAL) = range(15)
+TV_N_FIELDS = 15
+TV_HAS_AUX, TV_HAS_VALUE = 1, 2
+TV_EQ, TV_LT, TV_LE, TV_GT, TV_GE, TV_AND, TV_OR, TV_NOT, TV_BOUND = range(9)
+
+
+class TvValue(C.Structure):
+    _fields_ = [("lo", C.c_uint64), ("hi", C.c_uint64), ("aux", C.c_int64), ("field", C.c_uint8), ("flags", C.c_uint8),
+                ("reserved", C.c_uint8 * 6)]
+
+
+class TvInstr(C.Structure):
+    _fields_ = [("op", C.c_int32), ("lhs", C.c_int32), ("rhs", C.c_int32)]
+
+
+class TvConst(C.Structure):
+    _fields_ = [("v", TvValue), ("str", C.c_char_p), ("str_len", C.c_uint32), ("str2", C.c_char_p), ("str2_len", C.c_uint32)]
+
+
+class TvExport(C.Structure):
+    _fields_ = [("type_ids", C.c_void_p), ("offsets", C.c_void_p), ("boolean_bits", C.c_void_p), ("floats", C.c_void_p),
+                ("doubles", C.c_void_p), ("decimals", C.c_void_p), ("ints", C.c_void_p), ("integers", C.c_void_p),
+                ("ts_value", C.c_void_p * 3), ("ts_offset", C.c_void_p * 3), ("ts_offset_valid", C.c_void_p * 3),
+                ("dur_months", C.c_void_p), ("dur_months_valid", C.c_void_p), ("dur_seconds", C.c_void_p),
+                ("dur_seconds_valid", C.c_void_p)]
+
+
 class Metrics(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "kernel_launches", "h2d_bytes", "d2h_bytes", "scan_rows_in", "scan_rows_out", "filter_rows_in",
@@ -204,6 +233,17 @@ SIGNATURES = {
     "rfgpu_plain_terms_sizes": (C.c_int32, [C.c_void_p, u64p, u64p, u64p]),
     "rfgpu_plain_terms_export": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                              C.POINTER(C.c_void_p)]),
+    "rfgpu_tv_table_create": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "rfgpu_tv_table_retain": (C.c_void_p, [C.c_void_p]),
+    "rfgpu_tv_table_release": (None, [C.c_void_p]),
+    "rfgpu_tv_decode": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_uint64, C.c_uint64,
+                                    C.POINTER(C.c_void_p)]),
+    "rfgpu_typed_values_release": (None, [C.c_void_p]),
+    "rfgpu_typed_values_sizes": (C.c_int32, [C.c_void_p, u64p, u64p]),
+    "rfgpu_typed_values_strings": (C.c_void_p, [C.c_void_p, C.c_int32]),
+    "rfgpu_typed_values_export": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(TvExport)]),
+    "rfgpu_tv_eval": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(TvInstr), C.c_int32, C.POINTER(TvConst),
+                                  C.c_int32, C.c_char_p, C.POINTER(C.c_void_p)]),
     "rfgpu_table_sort": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_void_p)]),
     "rfgpu_store_build": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.c_uint64, C.c_int32, u32p,
                                       C.c_int32]),

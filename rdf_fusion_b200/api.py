@@ -800,20 +800,24 @@ class Dictionary:
         out = C.c_void_p()
         self.ctx.check(self.ctx.lib.rfgpu_dict_decode(self.ctx.h, self.h, table.h, i, row_off, n, C.byref(out)))
         try:
-            rows = C.c_uint64()
-            sizes, nulls = (C.c_uint64 * 3)(), (C.c_uint64 * 3)()
-            self.ctx.check(self.ctx.lib.rfgpu_plain_terms_sizes(out, C.byref(rows), sizes, nulls))
-            n = int(rows.value)
-            term_type = np.zeros(max(n, 1), np.uint8)
-            valid = [np.zeros((n + 7) // 8 + 1, np.uint8) for _ in range(3)]
-            offs = [np.zeros(n + 1, np.int32) for _ in range(3)]
-            data = [np.zeros(max(int(sizes[k]), 1), np.uint8) for k in range(3)]
-            arr = lambda xs: (C.c_void_p * 3)(*[x.ctypes.data for x in xs])  # noqa: E731
-            self.ctx.check(self.ctx.lib.rfgpu_plain_terms_export(self.ctx.h, out, term_type.ctypes.data, arr(valid), arr(offs),
-                                                                 arr(data)))
+            return _plain_terms_to_arrow_from_handle(self.ctx, out)
         finally:
             self.ctx.lib.rfgpu_plain_terms_release(out)
-        return plain_terms_to_arrow(n, term_type, valid, offs, data, [int(x) for x in sizes], [int(x) for x in nulls])
+
+
+def _plain_terms_to_arrow_from_handle(ctx: Context, h):
+    """rfgpu_plain_terms (device) -> pyarrow StructArray: sizes, one export, no per-row work on the host"""
+    rows = C.c_uint64()
+    sizes, nulls = (C.c_uint64 * 3)(), (C.c_uint64 * 3)()
+    ctx.check(ctx.lib.rfgpu_plain_terms_sizes(h, C.byref(rows), sizes, nulls))
+    n = int(rows.value)
+    term_type = np.zeros(max(n, 1), np.uint8)
+    valid = [np.zeros((n + 7) // 8 + 1, np.uint8) for _ in range(3)]
+    offs = [np.zeros(n + 1, np.int32) for _ in range(3)]
+    data = [np.zeros(max(int(sizes[k]), 1), np.uint8) for k in range(3)]
+    arr = lambda xs: (C.c_void_p * 3)(*[x.ctypes.data for x in xs])  # noqa: E731
+    ctx.check(ctx.lib.rfgpu_plain_terms_export(ctx.h, h, term_type.ctypes.data, arr(valid), arr(offs), arr(data)))
+    return plain_terms_to_arrow(n, term_type, valid, offs, data, [int(x) for x in sizes], [int(x) for x in nulls])
 
 
 def plain_terms_to_arrow(n, term_type, valid, offs, data, sizes, nulls):
@@ -830,3 +834,147 @@ def plain_terms_to_arrow(n, term_type, valid, offs, data, sizes, nulls):
               pa.field("data_type", pa.utf8(), True), pa.field("language_tag", pa.utf8(), True)]
     null_struct = ~np.unpackbits(np.frombuffer(vb[0], np.uint8), bitorder="little")[:n].astype(bool) if n else None
     return pa.StructArray.from_arrays(kids, fields=fields, mask=pa.array(null_struct, pa.bool_()) if n else None)
+
+
+# ---- object id -> typed value (ENC_TV) and value comparisons on ids (second half) ----
+TV_VALUE_DTYPE = np.dtype([("lo", "<u8"), ("hi", "<u8"), ("aux", "<i8"), ("field", "u1"), ("flags", "u1"), ("reserved", "u1", 6)])
+TV_FIELD_NAMES = ["null", "named_node", "blank_node", "string", "boolean", "float", "double", "decimal", "int", "integer",
+                  "date_time", "time", "date", "duration", "other_literal"]  # encoding.rs:264-282
+
+
+class TypedValueTable:
+    """Device twin of the per-id EncodedTypedValue (rfgpu_tv_table): one 32-byte record per object id over a Dictionary.
+    `records` is a TV_VALUE_DTYPE array indexed by id (entry 0 unused) — the caller parses the lexical forms (the reference
+    does that once per interned term with its own xsd parsers; this library never parses)."""
+
+    def __init__(self, ctx: Context, dictionary: Dictionary, records: np.ndarray):
+        self.ctx, self.dictionary = ctx, dictionary
+        rec = np.ascontiguousarray(records, TV_VALUE_DTYPE)
+        h = C.c_void_p()
+        ctx.check(ctx.lib.rfgpu_tv_table_create(ctx.h, dictionary.h, rec.ctypes.data, len(rec) - 1, C.byref(h)))
+        self.h = h
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.ctx.lib.rfgpu_tv_table_release(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def eval(self, table: "Table", prog: Sequence[tuple], consts: Sequence[tuple] = (), name: str = "ebv") -> "Table":
+        return Table(self.ctx, self.eval_handle(table, prog, consts, name))
+
+    def eval_handle(self, table, prog: Sequence[tuple], consts: Sequence[tuple] = (), name: str = "ebv"):
+        """`table` plus the nullable column `name` = EBV of the postfix program per row: 1 true, 2 false, NULL error
+        (rfgpu_tv_eval).  prog = [(op, lhs, rhs)]: comparison operands are column names / indexes, or ("const", k);
+        consts[k] = (record, value_bytes, lang_or_datatype_bytes)."""
+        names = table.names
+
+        def ref(x):
+            if isinstance(x, tuple):
+                return -(int(x[1]) + 1)
+            return names.index(x) if isinstance(x, str) else int(x)
+        ins = (F.TvInstr * max(1, len(prog)))()
+        for k, (op, lhs, rhs) in enumerate(prog):
+            ins[k].op = op
+            ins[k].lhs = ref(lhs) if lhs is not None else 0
+            ins[k].rhs = ref(rhs) if rhs is not None else 0
+        cs = (F.TvConst * max(1, len(consts)))()
+        keep = []
+        for k, (rec, s1, s2) in enumerate(consts):
+            r = np.zeros((), TV_VALUE_DTYPE)
+            r[...] = rec
+            C.memmove(C.byref(cs[k].v), r.tobytes(), 32)
+            s1, s2 = bytes(s1 or b""), bytes(s2 or b"")
+            keep += [s1, s2]
+            cs[k].str, cs[k].str_len, cs[k].str2, cs[k].str2_len = s1, len(s1), s2, len(s2)
+        out = C.c_void_p()
+        self.ctx.check(self.ctx.lib.rfgpu_tv_eval(self.ctx.h, self.h, table.h, ins, len(prog), cs, len(consts), name.encode(),
+                                                  C.byref(out)))
+        return out
+
+    def decode(self, table: "Table", col, row_off: int = 0, n_rows: Optional[int] = None):
+        """ENC_TV(col) -> the buffers of the dense union (rfgpu_tv_decode), as exported: {"rows", "counts", "type_ids",
+        "offsets", "boolean_bits", "floats", "doubles", "decimals", "ints", "integers", "ts_value", "ts_offset",
+        "ts_offset_valid", "dur_months", "dur_months_valid", "dur_seconds", "dur_seconds_valid", "strings": {field: StructArray}}.
+        typed_values_to_arrow() wraps them into the pyarrow UnionArray of the TypedValue encoding."""
+        i = table.names.index(col) if isinstance(col, str) else int(col)
+        n = table.num_rows - row_off if n_rows is None else n_rows
+        out = C.c_void_p()
+        lib = self.ctx.lib
+        self.ctx.check(lib.rfgpu_tv_decode(self.ctx.h, self.h, table.h, i, row_off, n, C.byref(out)))
+        try:
+            rows = C.c_uint64()
+            counts = (C.c_uint64 * F.TV_N_FIELDS)()
+            self.ctx.check(lib.rfgpu_typed_values_sizes(out, C.byref(rows), counts))
+            n = int(rows.value)
+            c = [int(x) for x in counts]
+            z = lambda k, dt: np.zeros(max(k, 1), dt)  # noqa: E731
+            bits = lambda k: np.zeros((k + 7) // 8 + 1, np.uint8)  # noqa: E731
+            r = {"rows": n, "counts": c, "type_ids": z(n, np.int8), "offsets": z(n, np.int32),
+                 "boolean_bits": bits(c[F.TV_BOOLEAN]), "floats": z(c[F.TV_FLOAT], np.float32),
+                 "doubles": z(c[F.TV_DOUBLE], np.float64), "decimals": z(16 * c[F.TV_DECIMAL], np.uint8),
+                 "ints": z(c[F.TV_INT], np.int32), "integers": z(c[F.TV_INTEGER], np.int64),
+                 "ts_value": [z(16 * c[F.TV_DATE_TIME + k], np.uint8) for k in range(3)],
+                 "ts_offset": [z(c[F.TV_DATE_TIME + k], np.int16) for k in range(3)],
+                 "ts_offset_valid": [bits(c[F.TV_DATE_TIME + k]) for k in range(3)],
+                 "dur_months": z(c[F.TV_DURATION], np.int64), "dur_months_valid": bits(c[F.TV_DURATION]),
+                 "dur_seconds": z(16 * c[F.TV_DURATION], np.uint8), "dur_seconds_valid": bits(c[F.TV_DURATION])}
+            e = F.TvExport()
+            for k in ("type_ids", "offsets", "boolean_bits", "floats", "doubles", "decimals", "ints", "integers", "dur_months",
+                      "dur_months_valid", "dur_seconds", "dur_seconds_valid"):
+                setattr(e, k, r[k].ctypes.data)
+            for k in ("ts_value", "ts_offset", "ts_offset_valid"):
+                setattr(e, k, (C.c_void_p * 3)(*[a.ctypes.data for a in r[k]]))
+            self.ctx.check(lib.rfgpu_typed_values_export(self.ctx.h, out, C.byref(e)))
+            r["type_ids"], r["offsets"] = r["type_ids"][:n], r["offsets"][:n]
+            r["strings"] = {}
+            for f in (F.TV_NAMED_NODE, F.TV_BLANK_NODE, F.TV_STRING, F.TV_OTHER_LITERAL):
+                h = lib.rfgpu_typed_values_strings(out, f)
+                if h:
+                    r["strings"][f] = _plain_terms_to_arrow_from_handle(self.ctx, C.c_void_p(h))
+        finally:
+            lib.rfgpu_typed_values_release(out)
+        return r
+
+
+def typed_values_to_arrow(r):
+    """The exported buffers of TypedValueTable.decode -> the pyarrow dense UnionArray of the reference's TypedValue encoding
+    (lib/encoding/src/typed_value/encoding.rs:16-137: same children, names, types and order).  No per-row work: the fixed-width
+    buffers ARE the Arrow buffers; the Utf8 children are the value / data_type / language_tag arrays of the decoded strings."""
+    import pyarrow as pa
+    c = r["counts"]
+    dec = pa.decimal128(36, 16)  # Decimal::PRECISION / SCALE (lib/model/src/xsd/decimal.rs:26-27)
+    buf = lambda a, nbytes: pa.py_buffer(a.tobytes()[:nbytes])  # noqa: E731
+
+    def fixed(t, a, k, width):
+        return pa.Array.from_buffers(t, k, [None, buf(a, k * width)])
+
+    def utf8(f, child):
+        if c[f] == 0:
+            return pa.array([], pa.utf8())
+        return r["strings"][f].field(child)
+
+    def ts(k):
+        n = c[F.TV_DATE_TIME + k]
+        value = fixed(dec, r["ts_value"][k], n, 16)
+        off = pa.Array.from_buffers(pa.int16(), n, [buf(r["ts_offset_valid"][k], (n + 7) // 8), buf(r["ts_offset"][k], 2 * n)])
+        return pa.StructArray.from_arrays([value, off], fields=[pa.field("value", dec, False), pa.field("offset", pa.int16(), True)])
+    nd = c[F.TV_DURATION]
+    dur = pa.StructArray.from_arrays(
+        [pa.Array.from_buffers(pa.int64(), nd, [buf(r["dur_months_valid"], (nd + 7) // 8), buf(r["dur_months"], 8 * nd)]),
+         pa.Array.from_buffers(dec, nd, [buf(r["dur_seconds_valid"], (nd + 7) // 8), buf(r["dur_seconds"], 16 * nd)])],
+        fields=[pa.field("months", pa.int64(), True), pa.field("seconds", dec, True)])
+    string = pa.StructArray.from_arrays([utf8(F.TV_STRING, "value"), utf8(F.TV_STRING, "language_tag")],
+                                        fields=[pa.field("value", pa.utf8(), False), pa.field("language", pa.utf8(), True)])
+    other = pa.StructArray.from_arrays([utf8(F.TV_OTHER_LITERAL, "value"), utf8(F.TV_OTHER_LITERAL, "data_type")],
+                                       fields=[pa.field("value", pa.utf8(), False), pa.field("datatype", pa.utf8(), False)])
+    nb = c[F.TV_BOOLEAN]
+    kids = [pa.nulls(c[F.TV_NULL]), utf8(F.TV_NAMED_NODE, "value"), utf8(F.TV_BLANK_NODE, "value"), string,
+            pa.Array.from_buffers(pa.bool_(), nb, [None, buf(r["boolean_bits"], (nb + 7) // 8)]),
+            fixed(pa.float32(), r["floats"], c[F.TV_FLOAT], 4), fixed(pa.float64(), r["doubles"], c[F.TV_DOUBLE], 8),
+            fixed(dec, r["decimals"], c[F.TV_DECIMAL], 16), fixed(pa.int32(), r["ints"], c[F.TV_INT], 4),
+            fixed(pa.int64(), r["integers"], c[F.TV_INTEGER], 8), ts(0), ts(1), ts(2), dur, other]
+    return pa.UnionArray.from_dense(pa.array(r["type_ids"], pa.int8()), pa.array(r["offsets"], pa.int32()), kids,
+                                    field_names=TV_FIELD_NAMES, type_codes=list(range(15)))

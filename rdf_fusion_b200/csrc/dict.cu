@@ -11,43 +11,10 @@
 // The encode direction (term → id: string hashing into the DashMap, :309-329) stays on the host.
 #include <algorithm>
 
-#include "rf_common.hpp"
-
-struct rfgpu_dict {
-  std::atomic<int> refs{1};
-  uint32_t n_ids = 0, n_aux = 0;
-  rf::BufRef term_type;    // u8[n_ids + 1], indexed by id (entry 0 unused)
-  rf::BufRef value_off;    // u64[n_ids + 2]: value of id = value_bytes[value_off[id] .. value_off[id + 1])
-  rf::BufRef value_bytes;
-  rf::BufRef datatype;     // u32[n_ids + 1]: index into the string table, 0 = none (named / blank nodes)
-  rf::BufRef language;     // u32[n_ids + 1]: index into the string table, 0 = none
-  rf::BufRef aux_off;      // u32[n_aux + 2]: string a = aux_bytes[aux_off[a] .. aux_off[a + 1]), a in 1..n_aux
-  rf::BufRef aux_bytes;
-};
-
-struct rfgpu_plain_terms {
-  uint64_t rows = 0;
-  uint64_t bytes[3] = {0, 0, 0};  // value, data_type, language_tag
-  uint64_t nulls[3] = {0, 0, 0};  // struct, data_type, language_tag
-  rf::BufRef term_type;           // u8[rows]
-  rf::BufRef valid[3];            // Arrow validity bitmaps (LSB first) as u32 words
-  rf::BufRef off[3];              // u32[rows + 1]
-  rf::BufRef data[3];
-};
+#include "dict.hpp"
 
 namespace rf {
 namespace {
-
-struct DictDev {
-  const uint8_t* term_type;
-  const unsigned long long* value_off;
-  const uint8_t* value_bytes;
-  const uint32_t* datatype;
-  const uint32_t* language;
-  const uint32_t* aux_off;
-  const uint8_t* aux_bytes;
-  uint32_t n_ids;
-};
 
 struct DecodeArgs {
   DictDev D;
@@ -153,6 +120,66 @@ BufRef upload(rfgpu_ctx* ctx, const void* host, size_t bytes) {
 }  // namespace
 }  // namespace rf
 
+namespace rf {
+
+rfgpu_plain_terms* decode_ids(rfgpu_ctx* ctx, const rfgpu_dict* d, const uint32_t* ids, uint64_t n_rows) {
+  RF_REQUIRE(n_rows < 0x7FFFFFFFull, RFGPU_E_UNSUPPORTED, "an Arrow Utf8 batch holds at most 2^31-2 rows");
+  RF_CUDA(cudaSetDevice(ctx->core->device));
+  std::unique_ptr<rfgpu_plain_terms> P(new rfgpu_plain_terms());
+  P->rows = n_rows;
+  const uint64_t n = n_rows, words = (n + 31) / 32;
+  DecodeArgs A{};
+  A.D = dict_dev(d);
+  A.ids = ids;
+  A.n = n;
+  P->term_type = ctx->alloc(n);
+  A.term_type = P->term_type->as<uint8_t>();
+  for (int k = 0; k < 3; k++) {
+    P->valid[k] = ctx->alloc(words * 4);
+    P->off[k] = alloc_col(ctx, n + 1);
+    A.valid[k] = P->valid[k]->as<uint32_t>();
+    A.off[k] = P->off[k]->as<uint32_t>();
+    RF_CUDA(cudaMemsetAsync(A.off[k] + n, 0, 4, ctx->stream()));  // the scan's last entry becomes the total
+  }
+  BufRef misc = ctx->alloc(32);  // [0] bad id, [1..3] null counts (u64 at byte 8)
+  RF_CUDA(cudaMemsetAsync(misc->ptr, 0, 32, ctx->stream()));
+  A.bad = misc->as<unsigned int>();
+  A.null_cnt = misc->as<unsigned long long>() + 1;
+  if (n) {
+    {
+      KernelScope ks(ctx, "k_dict_lengths", 4ull * n);
+      uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(n, 256), (uint64_t)ctx->core->num_sms * 16));
+      k_dict_lengths<<<grid, 256, 0, ctx->stream()>>>(A);
+    }
+    for (int k = 0; k < 3; k++) exclusive_scan_u32(ctx, A.off[k], A.off[k], n + 1, ctx->h_scratch + 162 + k);
+  } else {
+    for (int k = 0; k < 3; k++) ctx->h_scratch[162 + k] = 0;
+  }
+  RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 166, misc->ptr, 32, cudaMemcpyDeviceToHost, ctx->stream()));
+  ctx->sync();
+  const uint32_t bad = *reinterpret_cast<const uint32_t*>(ctx->h_scratch + 166);
+  RF_REQUIRE(bad == 0, RFGPU_E_INVALID,
+             "object id " + std::to_string(bad) + " is not in the dictionary (ids 1.." + std::to_string(d->n_ids) + ")");
+  for (int k = 0; k < 3; k++) {
+    P->bytes[k] = ctx->h_scratch[162 + k];
+    P->nulls[k] = ctx->h_scratch[167 + k];
+    RF_REQUIRE(P->bytes[k] < 0x7FFFFFFFull, RFGPU_E_UNSUPPORTED,
+               "decoded strings exceed 2^31-2 bytes: Utf8 offsets are i32, decode a smaller row range");
+    P->data[k] = ctx->alloc(P->bytes[k]);
+    A.data[k] = P->data[k]->as<uint8_t>();
+  }
+  if (n) {
+    KernelScope ks(ctx, "k_dict_copy", 4ull * n + 2 * (P->bytes[0] + P->bytes[1] + P->bytes[2]));
+    uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(n, 8), (uint64_t)ctx->core->num_sms * 16));
+    k_dict_copy<<<grid, 256, 0, ctx->stream()>>>(A);
+  }
+  ctx->m.algorithmic_bytes += 4ull * n + 2 * (P->bytes[0] + P->bytes[1] + P->bytes[2]) + 13ull * n;
+  ctx->sync();
+  return P.release();
+}
+
+}  // namespace rf
+
 extern "C" {
 
 int32_t rfgpu_dict_create(rfgpu_ctx* ctx, uint32_t n_ids, const uint8_t* term_type, const uint64_t* value_off,
@@ -209,61 +236,7 @@ int32_t rfgpu_dict_decode(rfgpu_ctx* ctx, const rfgpu_dict* d, const rfgpu_table
   rf::settle(t);  // lazy row count (rf_common.hpp)
   RF_REQUIRE(col >= 0 && col < (int32_t)t->cols.size(), RFGPU_E_INVALID, "column index out of range");
   RF_REQUIRE(row_off <= t->rows && n_rows <= t->rows - row_off, RFGPU_E_INVALID, "row range out of bounds");
-  RF_REQUIRE(n_rows < 0x7FFFFFFFull, RFGPU_E_UNSUPPORTED, "an Arrow Utf8 batch holds at most 2^31-2 rows");
-  RF_CUDA(cudaSetDevice(ctx->core->device));
-  std::unique_ptr<rfgpu_plain_terms> P(new rfgpu_plain_terms());
-  P->rows = n_rows;
-  const uint64_t n = n_rows, words = (n + 31) / 32;
-  DecodeArgs A{};
-  A.D = DictDev{d->term_type->as<uint8_t>(), d->value_off->as<unsigned long long>(), d->value_bytes->as<uint8_t>(),
-                d->datatype->as<uint32_t>(), d->language->as<uint32_t>(), d->aux_off->as<uint32_t>(),
-                d->aux_bytes->as<uint8_t>(), d->n_ids};
-  A.ids = t->cols[col].data + row_off;
-  A.n = n;
-  P->term_type = ctx->alloc(n);
-  A.term_type = P->term_type->as<uint8_t>();
-  for (int k = 0; k < 3; k++) {
-    P->valid[k] = ctx->alloc(words * 4);
-    P->off[k] = alloc_col(ctx, n + 1);
-    A.valid[k] = P->valid[k]->as<uint32_t>();
-    A.off[k] = P->off[k]->as<uint32_t>();
-    RF_CUDA(cudaMemsetAsync(A.off[k] + n, 0, 4, ctx->stream()));  // the scan's last entry becomes the total
-  }
-  BufRef misc = ctx->alloc(32);  // [0] bad id, [1..3] null counts (u64 at byte 8)
-  RF_CUDA(cudaMemsetAsync(misc->ptr, 0, 32, ctx->stream()));
-  A.bad = misc->as<unsigned int>();
-  A.null_cnt = misc->as<unsigned long long>() + 1;
-  if (n) {
-    {
-      KernelScope ks(ctx, "k_dict_lengths", 4ull * n);
-      uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(n, 256), (uint64_t)ctx->core->num_sms * 16));
-      k_dict_lengths<<<grid, 256, 0, ctx->stream()>>>(A);
-    }
-    for (int k = 0; k < 3; k++) exclusive_scan_u32(ctx, A.off[k], A.off[k], n + 1, ctx->h_scratch + 162 + k);
-  } else {
-    for (int k = 0; k < 3; k++) ctx->h_scratch[162 + k] = 0;
-  }
-  RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 166, misc->ptr, 32, cudaMemcpyDeviceToHost, ctx->stream()));
-  ctx->sync();
-  const uint32_t bad = *reinterpret_cast<const uint32_t*>(ctx->h_scratch + 166);
-  RF_REQUIRE(bad == 0, RFGPU_E_INVALID,
-             "object id " + std::to_string(bad) + " is not in the dictionary (ids 1.." + std::to_string(d->n_ids) + ")");
-  for (int k = 0; k < 3; k++) {
-    P->bytes[k] = ctx->h_scratch[162 + k];
-    P->nulls[k] = ctx->h_scratch[167 + k];
-    RF_REQUIRE(P->bytes[k] < 0x7FFFFFFFull, RFGPU_E_UNSUPPORTED,
-               "decoded strings exceed 2^31-2 bytes: Utf8 offsets are i32, decode a smaller row range");
-    P->data[k] = ctx->alloc(P->bytes[k]);
-    A.data[k] = P->data[k]->as<uint8_t>();
-  }
-  if (n) {
-    KernelScope ks(ctx, "k_dict_copy", 4ull * n + 2 * (P->bytes[0] + P->bytes[1] + P->bytes[2]));
-    uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(n, 8), (uint64_t)ctx->core->num_sms * 16));
-    k_dict_copy<<<grid, 256, 0, ctx->stream()>>>(A);
-  }
-  ctx->m.algorithmic_bytes += 4ull * n + 2 * (P->bytes[0] + P->bytes[1] + P->bytes[2]) + 13ull * n;
-  ctx->sync();
-  *out = P.release();
+  *out = decode_ids(ctx, d, t->cols[col].data + row_off, n_rows);
   RF_API_END(ctx)
 }
 

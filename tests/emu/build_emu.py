@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "rdf_fusion_b200", "csrc")
 BUILD = os.path.join(HERE, "_build")
-SOURCES = ["sort.cu", "dict.cu", "filter.cu", "aggregate.cu", "join.cu", "scan.cu", "scan_plan.cpp"]
+SOURCES = ["sort.cu", "dict.cu", "typed_value.cu", "filter.cu", "aggregate.cu", "join.cu", "scan.cu", "scan_plan.cpp"]
 
 
 def _balanced(s, i, open_, close):
@@ -89,7 +89,7 @@ def build(asan=False, tsan=False):
         if not os.path.exists(dst) or open(dst).read() != text:
             open(dst, "w").write(text)
         newest = max(newest, os.path.getmtime(dst))
-    for h in ("rf_common.hpp", "rf_device.cuh"):
+    for h in ("rf_common.hpp", "rf_device.cuh", "dict.hpp"):
         newest = max(newest, os.path.getmtime(os.path.join(CSRC, h)))
     newest = max(newest, os.path.getmtime(os.path.join(HERE, "emu_device.inl")))
     so = os.path.join(BUILD, "librfemu_asan.so" if asan else "librfemu_tsan.so" if tsan else "librfemu.so")

@@ -159,6 +159,26 @@ class OracleBackend:
         return r.names, r.nullable, r.cols
 
 
+    def tv_filter(self, t, prog, consts):
+        """rows whose program evaluates to true (oracle/typed_value.py); self.terms = the dictionary of the case"""
+        from oracle import typed_value as tvo
+        names, nullable, cols = t
+        tvs = [None] + [tvo.typed_value(tuple(x)) for x in self.terms]
+        ctv = [tvo.typed_value(c) for c in consts]
+        ref = lambda x: None if x is None else ("const", x["const"]) if "const" in x else names.index(x["var"])  # noqa: E731
+        p = [(op, ref(l), ref(r)) for op, l, r in prog]
+        n = len(cols[0]) if cols else 0
+        keep = np.zeros(n, bool)
+        for i in range(n):
+            def operand(r, bound=False):
+                if isinstance(r, tuple):
+                    return ctv[r[1]]
+                v = int(cols[r][i])
+                return (v != 0) if bound else (tvs[v] if v else None)
+            keep[i] = tvo.eval_program(p, operand) == tvo.TRUE
+        return names, nullable, [c[keep] for c in cols]
+
+
 class GpuBackend:
     """Drives the CUDA path through the C ABI; intermediates cross the host only for UNION (a host operator)."""
 
@@ -200,6 +220,25 @@ class GpuBackend:
 
     def filter(self, t, preds):
         return self._out(self.make(*t).filter(preds))
+
+    def tv_filter(self, t, prog, consts):
+        """rfgpu_tv_eval appends the EBV column, rfgpu_filter keeps the rows where it is 1 (true).  The typed-value records of
+        the dictionary and of the constants come from the oracle's parser: the product never parses lexical forms (the Rust
+        binding fills them from the reference's EncodedTypedValue)."""
+        from oracle import typed_value as tvo
+        import tv_support
+        names, nullable, cols = t
+        if not (cols and len(cols[0])):
+            return t
+        if getattr(self, "_tv", None) is None:
+            terms = [tuple(x) for x in self.terms]
+            self._tv = rf.TypedValueTable(self.ctx, rf.Dictionary(self.ctx, terms), tvo.records(terms))
+        ref = lambda x: None if x is None else ("const", x["const"]) if "const" in x else x["var"]  # noqa: E731
+        T = self._tv.eval(self.make(names, nullable, cols), [(op, ref(l), ref(r)) for op, l, r in prog],
+                          [tv_support.const_of(c, tvo) for c in consts], "__ebv")
+        out = T.filter([rf.FPred(F.F_EQ_CONST, len(names), value=1)])
+        on, onl, oc = self._out(out)
+        return on[:-1], onl[:-1], oc[:-1]
 
     def join_filtered(self, l, r, jt, preds):
         return self._out(self.make(*l).join(self.make(*r), jt, filter=preds))
@@ -307,6 +346,9 @@ def eval_plan(be, node):
     if op == "filter":
         t = eval_plan(be, node["in"])
         return be.filter(t, _resolve_preds(node["preds"], t[0]))
+    if op == "tv_filter":  # FILTER over typed values: EBV(program over ENC_TV(columns) and constants) is true
+        t = eval_plan(be, node["in"])
+        return be.tv_filter(t, node["prog"], [tuple(c) for c in node["consts"]])
     if op == "filter_any_bound":  # FILTER(bound(a) || bound(b) ..): a disjunction stays a host FilterExec
         names, nullable, cols = eval_plan(be, node["in"])
         keep = np.zeros(len(cols[0]) if cols else 0, dtype=bool)
