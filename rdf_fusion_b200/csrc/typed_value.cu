@@ -28,6 +28,7 @@ struct rfgpu_tv_table {
   uint32_t n_ids = 0;
   rfgpu_dict* dict = nullptr;  // retained
   rf::BufRef values;           // rfgpu_tv_value[n_ids + 1]
+  rf::BufRef fields;           // u8[n_ids + 1]: the records' field alone (1 B per id stays L2-resident where 32 B does not)
   ~rfgpu_tv_table() { rfgpu_dict_release(dict); }
 };
 
@@ -222,6 +223,9 @@ struct EvalArgs {
   const uint8_t* const_bytes;  // device copy of the constants' strings
   uint32_t* out;
   unsigned int* flags;  // [0] a duration pair was met, [1] largest id beyond the dictionary
+  // per-id mode (the truth table of a program over ONE column and constants): "row" i is object id i, the result a byte
+  int32_t identity_col;  // -1: rows of a table
+  uint8_t* out8;
 };
 
 __device__ __forceinline__ bool is_stringy(uint32_t f) {
@@ -243,7 +247,7 @@ __device__ __forceinline__ bool load_operand(const EvalArgs& A, int32_t ref, uin
     o.s2len = c.s2_len;
     return o.field != RFGPU_TV_NULL;
   }
-  const uint32_t id = __ldg(A.cols[ref] + i);
+  const uint32_t id = ref == A.identity_col ? (uint32_t)i : __ldg(A.cols[ref] + i);
   if (id == 0) return false;
   if (id > A.D.n_ids) {
     atomicMax(A.flags + 1, id);
@@ -308,7 +312,8 @@ __global__ void __launch_bounds__(256) k_tv_eval(const __grid_constant__ EvalArg
         }
         stack = (stack << 2) | r;
       } else if (in.op == RFGPU_TV_BOUND) {
-        stack = (stack << 2) | (__ldg(A.cols[in.lhs] + i) != 0 ? kTrue : kFalse);
+        const uint32_t id = in.lhs == A.identity_col ? (uint32_t)i : __ldg(A.cols[in.lhs] + i);
+        stack = (stack << 2) | (id != 0 ? kTrue : kFalse);
       } else if (in.op == RFGPU_TV_NOT) {
         const uint32_t x = stack & 3;
         stack = (stack & ~3u) | (x == kTrue ? kFalse : x == kFalse ? kTrue : kError);
@@ -322,13 +327,34 @@ __global__ void __launch_bounds__(256) k_tv_eval(const __grid_constant__ EvalArg
         stack = ((stack >> 4) << 2) | r;
       }
     }
-    A.out[i] = stack & 3;
+    if (A.out8)
+      A.out8[i] = (uint8_t)(stack & 3);
+    else
+      A.out[i] = stack & 3;
+  }
+}
+
+// out[i] = truth[ids[i]]: the per-id truth table of a single-column program applied to the rows (the table is 1 B per id:
+// L2-resident, so the rows stream at the speed of their own 8 bytes)
+__global__ void __launch_bounds__(256) k_tv_apply(const uint32_t* __restrict__ ids, uint64_t n, const uint8_t* __restrict__ truth,
+                                                  uint32_t n_ids, uint32_t* __restrict__ out, unsigned int* flags) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const uint32_t id = __ldg(ids + i);
+    uint32_t v = 0;
+    if (id <= n_ids)
+      v = __ldg(truth + id);
+    else
+      atomicMax(flags + 1, id);
+    out[i] = v;
   }
 }
 
 // ---------------------------------------------------------------- decode into the dense union
 struct DecodeTvArgs {
   const rfgpu_tv_value* values;
+  const uint8_t* fields;  // u8[n_ids + 1]
   uint32_t n_ids;
   const uint32_t* ids;
   uint64_t n;
@@ -360,7 +386,7 @@ __device__ __forceinline__ uint32_t tv_field_of(const DecodeTvArgs& A, uint32_t 
     atomicMax(A.bad, id);
     return RFGPU_TV_NULL;
   }
-  return __ldg(&A.values[id].field);
+  return __ldg(A.fields + id);
 }
 
 __global__ void __launch_bounds__(kTvThreads) k_tv_count(const __grid_constant__ DecodeTvArgs A) {
@@ -509,6 +535,10 @@ int32_t rfgpu_tv_table_create(rfgpu_ctx* ctx, rfgpu_dict* d, const rfgpu_tv_valu
   RF_CUDA(cudaMemcpyAsync(tv->values->ptr, values, ((size_t)n_ids + 1) * sizeof(rfgpu_tv_value), cudaMemcpyHostToDevice,
                           ctx->stream()));
   RF_CUDA(cudaMemsetAsync(tv->values->ptr, 0, sizeof(rfgpu_tv_value), ctx->stream()));  // entry 0 = NULL whatever was passed
+  std::vector<uint8_t> fields((size_t)n_ids + 1, 0);
+  for (uint32_t id = 1; id <= n_ids; id++) fields[id] = values[id].field;
+  tv->fields = ctx->alloc(fields.size());
+  RF_CUDA(cudaMemcpyAsync(tv->fields->ptr, fields.data(), fields.size(), cudaMemcpyHostToDevice, ctx->stream()));
   ctx->m.h2d_bytes += ((size_t)n_ids + 1) * sizeof(rfgpu_tv_value);
   ctx->sync();
   tv->dict = rfgpu_dict_retain(d);
@@ -604,15 +634,57 @@ int32_t rfgpu_tv_eval(rfgpu_ctx* ctx, const rfgpu_tv_table* tv, const rfgpu_tabl
   c.owner = alloc_col(ctx, t->rows);
   c.data = c.owner->as<uint32_t>();
   A.out = c.owner->as<uint32_t>();
+  A.identity_col = -1;
+  A.out8 = nullptr;
+  // A program whose comparisons all pit ONE column against constants is a function of that column's id alone: evaluate it
+  // once per dictionary id (sequential reads of the records) and gather the rows' answers from the 1-byte truth table —
+  // 8 B of streaming per row instead of a random 32-B sector.  Pays as soon as the table is not much longer than the rows.
+  int32_t one_col = -1;
+  bool per_id = true;
+  for (int32_t k = 0; k < n_instr && per_id; k++) {
+    const rfgpu_tv_instr& in = prog[k];
+    int32_t c0 = -1;
+    if (in.op <= RFGPU_TV_GE) {
+      if ((in.lhs >= 0) == (in.rhs >= 0)) per_id = false;  // column against column, or constant against constant
+      c0 = in.lhs >= 0 ? in.lhs : in.rhs;
+    } else if (in.op == RFGPU_TV_BOUND) {
+      c0 = in.lhs;
+    } else {
+      continue;
+    }
+    if (one_col >= 0 && c0 != one_col) per_id = false;
+    one_col = c0;
+  }
+  per_id = per_id && one_col >= 0 && t->rows >= (uint64_t)tv->n_ids / 2;
   if (t->rows) {
-    // per row: 4 B per operand id + one 32-B record per operand, 4 B out (string bytes not counted)
     uint64_t ops = 0;
     for (int32_t k = 0; k < n_instr; k++)
       if (prog[k].op <= RFGPU_TV_GE) ops += (prog[k].lhs >= 0) + (prog[k].rhs >= 0);
-    KernelScope ks(ctx, "k_tv_eval", t->rows * (36 * ops + 4));
-    uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(t->rows, 256), (uint64_t)ctx->core->num_sms * 16));
-    k_tv_eval<<<grid, 256, 0, ctx->stream()>>>(A);
-    ctx->m.algorithmic_bytes += t->rows * (36 * ops + 4);
+    if (per_id) {
+      const uint64_t n_tab = (uint64_t)tv->n_ids + 1;
+      BufRef truth = ctx->alloc(n_tab);
+      EvalArgs B = A;
+      B.identity_col = one_col;
+      B.out8 = truth->as<uint8_t>();
+      B.n = n_tab;
+      {
+        KernelScope ks(ctx, "k_tv_eval", n_tab * (32 * ops + 1));
+        uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(n_tab, 256), (uint64_t)ctx->core->num_sms * 16));
+        k_tv_eval<<<grid, 256, 0, ctx->stream()>>>(B);
+      }
+      {
+        KernelScope ks(ctx, "k_tv_apply", t->rows * 9);
+        uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(t->rows, 256), (uint64_t)ctx->core->num_sms * 16));
+        k_tv_apply<<<grid, 256, 0, ctx->stream()>>>(t->cols[one_col].data, t->rows, truth->as<uint8_t>(), tv->n_ids, A.out, A.flags);
+      }
+      ctx->m.algorithmic_bytes += n_tab * (32 * ops + 1) + t->rows * 9;
+    } else {
+      // per row: 4 B per operand id + one 32-B record per operand, 4 B out (string bytes not counted)
+      KernelScope ks(ctx, "k_tv_eval", t->rows * (36 * ops + 4));
+      uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(t->rows, 256), (uint64_t)ctx->core->num_sms * 16));
+      k_tv_eval<<<grid, 256, 0, ctx->stream()>>>(A);
+      ctx->m.algorithmic_bytes += t->rows * (36 * ops + 4);
+    }
   }
   RF_CUDA(cudaMemcpyAsync(ctx->h_scratch + 170, misc->ptr, 8, cudaMemcpyDeviceToHost, ctx->stream()));
   ctx->sync();
@@ -641,6 +713,7 @@ int32_t rfgpu_tv_decode(rfgpu_ctx* ctx, const rfgpu_tv_table* tv, const rfgpu_ta
   V->rows = n;
   DecodeTvArgs A{};
   A.values = tv->values->as<rfgpu_tv_value>();
+  A.fields = tv->fields->as<uint8_t>();
   A.n_ids = tv->n_ids;
   A.ids = t->cols[col].data + row_off;
   A.n = n;

@@ -143,7 +143,7 @@ def emu():
     sig = {"emu_ctx_create": (vp, []), "emu_ctx_destroy": (None, [vp]),
            "emu_table_create": (vp, [vp, C.c_int32, C.POINTER(vp), C.c_uint64, C.c_int32]), "emu_table_rows": (C.c_uint64, [vp]),
            "emu_table_cols": (C.c_int32, [vp]), "emu_table_col": (u32p, [vp, C.c_int32]), "emu_table_release": (None, [vp]),
-           "rfgpu_last_error": (C.c_char_p, [vp])}
+           "rfgpu_last_error": (C.c_char_p, [vp]), "emu_kernel_launches": (C.c_uint64, [vp, C.c_char_p])}
     for name in ("rfgpu_dict_create", "rfgpu_dict_release", "rfgpu_plain_terms_sizes", "rfgpu_plain_terms_export",
                  "rfgpu_tv_table_create", "rfgpu_tv_table_release", "rfgpu_tv_decode", "rfgpu_typed_values_release",
                  "rfgpu_typed_values_sizes", "rfgpu_typed_values_strings", "rfgpu_typed_values_export", "rfgpu_tv_eval"):
@@ -231,9 +231,22 @@ def test_comparison_programs_on_host_threads(emu, tvo, seed):
              [(F.TV_BOUND, 0, None), (F.TV_LT, 0, ("const", 2)), (F.TV_NOT, None, None), (F.TV_AND, None, None)],
              [(F.TV_EQ, 0, 1), (F.TV_EQ, 1, ("const", 0)), (F.TV_OR, None, None), (F.TV_BOUND, 1, None), (F.TV_AND, None, None)]]
     for prog in progs:
+        applied = emu.emu_kernel_launches(emu.ctx, b"k_tv_apply")
         got = _emu_eval(emu, tv, t, prog, consts)
         want = S.oracle_eval(prog, [a, b], ctv, tvs, tvo)
         assert np.array_equal(got, want), (prog, np.nonzero(got != want)[0][:5])
+        # one column against constants: the per-id truth table (k_tv_eval over the dictionary, k_tv_apply over the rows)
+        used = {l for op, l, r in prog if op == F.TV_BOUND} | {x for op, l, r in prog if op <= F.TV_GE for x in (l, r) if isinstance(x, int)}
+        one_col = len(used) == 1 and all(isinstance(l, int) != isinstance(r, int) for op, l, r in prog if op <= F.TV_GE)
+        assert emu.emu_kernel_launches(emu.ctx, b"k_tv_apply") - applied == (1 if one_col else 0), prog
+    # the same single-column programs on fewer rows than half the dictionary: evaluated per row
+    few = _EmuTable(emu, [a[:50], b[:50]], ["a", "b"])
+    for prog in progs[3:6]:
+        applied = emu.emu_kernel_launches(emu.ctx, b"k_tv_apply")
+        got = _emu_eval(emu, tv, few, prog, consts)
+        assert np.array_equal(got, S.oracle_eval(prog, [a[:50], b[:50]], ctv, tvs, tvo))
+        assert emu.emu_kernel_launches(emu.ctx, b"k_tv_apply") == applied
+    few.close()
     t.close()
 
 
