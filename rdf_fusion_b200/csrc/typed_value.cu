@@ -432,17 +432,15 @@ __global__ void __launch_bounds__(kTvThreads) k_tv_scatter(const __grid_constant
     if (in) {
       A.type_ids[i] = (int8_t)f;
       A.offsets[i] = (int32_t)off;
-      if (f != RFGPU_TV_NULL) {
+      if (f == RFGPU_TV_NAMED_NODE || f == RFGPU_TV_BLANK_NODE || f == RFGPU_TV_STRING || f == RFGPU_TV_OTHER_LITERAL) {
+        A.id_list[f][off] = id;  // the strings stay in the dictionary: no record to read
+      } else if (f != RFGPU_TV_NULL) {
         const uint4* rec = reinterpret_cast<const uint4*>(A.values + id);
         const uint4 r0 = __ldg(rec), r1 = __ldg(rec + 1);
         const uint64_t lo = (uint64_t)r0.x | ((uint64_t)r0.y << 32), hi = (uint64_t)r0.z | ((uint64_t)r0.w << 32);
         const int64_t aux = (int64_t)((uint64_t)r1.x | ((uint64_t)r1.y << 32));
         const uint32_t flags = (r1.z >> 8) & 0xFF;
         switch (f) {
-          case RFGPU_TV_NAMED_NODE:
-          case RFGPU_TV_BLANK_NODE:
-          case RFGPU_TV_STRING:
-          case RFGPU_TV_OTHER_LITERAL: A.id_list[f][off] = id; break;
           case RFGPU_TV_BOOLEAN: A.bool_bytes[off] = (uint8_t)(lo & 1); break;
           case RFGPU_TV_FLOAT: A.floats[off] = (uint32_t)lo; break;
           case RFGPU_TV_DOUBLE: A.doubles[off] = lo; break;
