@@ -50,7 +50,7 @@ __device__ __forceinline__ bool in_list(const DevPred& p, uint32_t v) {
 __global__ void __launch_bounds__(kFThreads, 5)
 k_filter_compact(const __grid_constant__ FilterArgs A, unsigned long long* __restrict__ status,
                  unsigned long long* __restrict__ total) {
-  __shared__ uint32_t s_stage[kFTile];
+  __shared__ uint32_t s_stage[2 * kFTile];  // two output columns are staged per round
   __shared__ uint32_t s_warp[kFThreads / 32 + 1];
   __shared__ unsigned long long s_base;
 
@@ -130,32 +130,50 @@ k_filter_compact(const __grid_constant__ FilterArgs A, unsigned long long* __res
   }
   const uint32_t btotal = __shfl_sync(0xFFFFFFFFu, incl, kFThreads / 32 - 1);
   const uint32_t woff = __shfl_sync(0xFFFFFFFFu, incl - v, warp);  // exclusive offset of this warp in the tile
-  if (warp == 0) {
-    unsigned long long excl = dev::lookback_exclusive(status, tile, btotal);
-    if (lane == 0) {
-      s_base = excl;
-      if (tile == gridDim.x - 1) {
-        *total = excl + btotal;
-        if (A.total_host) *A.total_host = excl + btotal;  // pinned mirror of a lazy row count
+  // The tile's aggregate is published NOW and the look-back resolved only after the first two output columns have been
+  // staged: without the wait for the predecessors the kernel takes 54 us instead of 86 (profiles/r4d_filter_nolookback.json) —
+  // tiles in flight on other SMs reach this point at different times and every later tile inherits the slowest one's delay —
+  // so the wait is spent loading, not idling.
+  if (warp == 0) dev::lookback_publish(status, tile, btotal);
+  auto resolve = [&]() {
+    if (warp == 0) {
+      const unsigned long long excl = dev::lookback_resolve(status, tile, btotal);
+      if (lane == 0) {
+        s_base = excl;
+        if (tile == gridDim.x - 1) {
+          *total = excl + btotal;
+          if (A.total_host) *A.total_host = excl + btotal;  // pinned mirror of a lazy row count
+        }
       }
     }
+  };
+  if (btotal == 0) {  // uniform over the CTA; the successors still need this tile's inclusive prefix
+    resolve();
+    return;
   }
-  if (btotal == 0) return;  // uniform over the CTA; warp 0 has published its aggregate above
   const uint32_t lt = (1u << lane) - 1u;
-
-  for (int c = 0; c < A.n_cols; c++) {
+  auto stage = [&](int c, uint32_t* buf) {
     const uint32_t* __restrict__ src = A.src[c];
     uint32_t o = woff;
 #pragma unroll
     for (int k = 0; k < kFItems; k++) {
       uint32_t b = ballots[k];
-      if ((b >> lane) & 1u) s_stage[o + __popc(b & lt)] = __ldg(src + warp_row0 + k * 32 + lane);
+      if ((b >> lane) & 1u) buf[o + __popc(b & lt)] = __ldg(src + warp_row0 + k * 32 + lane);
       o += __popc(b);
     }
-    __syncthreads();  // for column 0 this also publishes s_base
+  };
+  auto write = [&](int c, const uint32_t* buf) {
     uint32_t* __restrict__ dst = A.dst[c] + s_base;
-    for (uint32_t i = tid; i < btotal; i += kFThreads) dst[i] = s_stage[i];
-    __syncthreads();
+    for (uint32_t i = tid; i < btotal; i += kFThreads) dst[i] = buf[i];
+  };
+  for (int c0 = 0; c0 < A.n_cols || c0 == 0; c0 += 2) {
+    if (c0 < A.n_cols) stage(c0, s_stage);
+    if (c0 + 1 < A.n_cols) stage(c0 + 1, s_stage + kFTile);
+    if (c0 == 0) resolve();
+    __syncthreads();  // the staged survivors (and, in the first round, s_base) are visible
+    if (c0 < A.n_cols) write(c0, s_stage);
+    if (c0 + 1 < A.n_cols) write(c0 + 1, s_stage + kFTile);
+    if (c0 + 2 < A.n_cols) __syncthreads();  // the buffers are free again
   }
 }
 

@@ -289,9 +289,10 @@ def test_filter_entry_point(emu, oracle):
     import rdf_fusion_b200 as rf
     rng = np.random.default_rng(77)
     for n in some((0, 1, 33, 4096, 4097, 9000), (0, 33, 4097)):
-        cols = [np.where(rng.random(n) < 0.2, 0, rng.integers(1, 9, n)).astype(np.uint32) for _ in range(3)]
+        # five columns: the kernel stages two output columns per round (rounds of 2, 2 and 1)
+        cols = [np.where(rng.random(n) < 0.2, 0, rng.integers(1, 9, n)).astype(np.uint32) for _ in range(5)]
         t = _table(emu, cols)
-        O = oracle.OTable(["c0", "c1", "c2"], [True] * 3, cols)
+        O = oracle.OTable(["c0", "c1", "c2", "c3", "c4"], [True] * 5, cols)
         for preds in ([rf.FPred(F.F_NE_CONST, 0, value=3)], [rf.FPred(F.F_EQ_COL, 0, col2=1), rf.FPred(F.F_IS_NOT_NULL, 2)],
                       [rf.FPred(F.F_IN, 1, ids=[1, 2, 5, 7, 8, 3, 4, 6, 9, 10, 11])], [rf.FPred(F.F_IS_NULL, 2)]):
             arr, keep = rf.make_filter_preds(preds)
