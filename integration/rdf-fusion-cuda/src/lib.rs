@@ -5,6 +5,7 @@ pub mod ffi;
 pub mod join_exec;
 pub mod optimizer;
 pub mod planner;
+pub mod typed_value;
 
 use arrow::array::{Array, RecordBatch, StructArray};
 use arrow::datatypes::SchemaRef;

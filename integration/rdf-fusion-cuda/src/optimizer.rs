@@ -61,7 +61,8 @@ pub(crate) fn as_column_cmp_u32(e: &Arc<dyn PhysicalExpr>) -> Option<(String, i3
 }
 
 /// An ID-level conjunct as rfgpu_filter_pred (`col = c`, `col != c`, `col_i = col_j`, `col_i != col_j`, IS [NOT] NULL);
-/// None for value-level expressions (EBV(GT(ENC_TV(..))): they stay on DataFusion or go through rfgpu_table_lookup ranks).
+/// None for value-level expressions (EBV(GT(ENC_TV(..))): comparisons of ENC_TV(column) with constants or columns, joined by
+/// AND / OR / NOT, compile to a typed_value::GpuTypedValues::eval program; anything else stays on DataFusion).
 fn as_id_pred(e: &Arc<dyn PhysicalExpr>) -> Option<ffi::rfgpu_filter_pred> {
     let mut p = ffi::rfgpu_filter_pred { op: 0, col: 0, col2: 0, value: 0, hi: 0, ids: std::ptr::null(), n_ids: 0 };
     if let Some(n) = e.as_any().downcast_ref::<IsNullExpr>() {
