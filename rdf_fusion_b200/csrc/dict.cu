@@ -5,9 +5,10 @@
 // resident in HBM (term type, value bytes, data type / language tag as indexes into a small string table) and a batch of
 // ids becomes the four child arrays of the PlainTerm struct (term_type: UInt8, value / data_type / language_tag: Utf8 with
 // i32 offsets, struct-level and child validity bitmaps) in three steps:
-//   k_dict_lengths  per row the three string lengths, the term type and (by ballot) the validity words
+//   k_dict_lengths  per row the three string lengths, the term type and (by ballot) the validity words — one gather of the
+//                   id's 32-byte record (DictRec, dict.hpp) instead of five gathers from five arrays
 //   exclusive scan  lengths → Arrow offsets (filter.cu)
-//   k_dict_copy     one warp per row copies the value bytes and the two short strings, coalesced along the bytes
+//   k_dict_copy     eight lanes per row (four rows of a warp in flight) copy the value bytes and the two short strings
 // The encode direction (term → id: string hashing into the DashMap, :309-329) stays on the host.
 #include <algorithm>
 
@@ -28,6 +29,20 @@ struct DecodeArgs {
   unsigned long long* null_cnt;   // [3]
 };
 
+__device__ __forceinline__ DictRec load_rec(const DictRec* p) {  // 32 B: two 16-byte loads of one sector
+  const uint4* q = reinterpret_cast<const uint4*>(p);
+  const uint4 a = __ldg(q), b = __ldg(q + 1);
+  DictRec r;
+  r.value_off = (unsigned long long)a.x | ((unsigned long long)a.y << 32);
+  r.value_len = a.z;
+  r.dt = a.w;
+  r.lang = b.x;
+  r.dt_len = b.y;
+  r.lang_len = b.z;
+  r.term_type = b.w;
+  return r;
+}
+
 __global__ void __launch_bounds__(256) k_dict_lengths(const __grid_constant__ DecodeArgs A) {
   const uint64_t n_pad = (A.n + 31) & ~31ull;  // whole warps reach the ballots
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -38,25 +53,17 @@ __global__ void __launch_bounds__(256) k_dict_lengths(const __grid_constant__ De
     const uint32_t id = in ? __ldg(A.ids + i) : 0;
     const bool ok = id != 0 && id <= A.D.n_ids;
     if (id > A.D.n_ids) atomicMax(A.bad, id);
-    uint32_t vlen = 0, dlen = 0, llen = 0, dt = 0, lg = 0;
-    uint8_t tt = 0;
-    if (ok) {
-      vlen = (uint32_t)(__ldg(A.D.value_off + id + 1) - __ldg(A.D.value_off + id));
-      dt = __ldg(A.D.datatype + id);
-      lg = __ldg(A.D.language + id);
-      if (dt) dlen = __ldg(A.D.aux_off + dt + 1) - __ldg(A.D.aux_off + dt);
-      if (lg) llen = __ldg(A.D.aux_off + lg + 1) - __ldg(A.D.aux_off + lg);
-      tt = __ldg(A.D.term_type + id);
-    }
+    DictRec r{};
+    if (ok) r = load_rec(A.D.rec + id);
     if (in) {
-      A.off[0][i] = vlen;
-      A.off[1][i] = dlen;
-      A.off[2][i] = llen;
-      A.term_type[i] = tt;
+      A.off[0][i] = r.value_len;
+      A.off[1][i] = r.dt_len;
+      A.off[2][i] = r.lang_len;
+      A.term_type[i] = (uint8_t)r.term_type;
     }
     const uint32_t b0 = __ballot_sync(0xFFFFFFFFu, ok);
-    const uint32_t b1 = __ballot_sync(0xFFFFFFFFu, ok && dt != 0);
-    const uint32_t b2 = __ballot_sync(0xFFFFFFFFu, ok && lg != 0);
+    const uint32_t b1 = __ballot_sync(0xFFFFFFFFu, ok && r.dt != 0);
+    const uint32_t b2 = __ballot_sync(0xFFFFFFFFu, ok && r.lang != 0);
     if (lane == 0) {
       const uint32_t live = (uint32_t)min((uint64_t)32, A.n - i);  // rows of this word that exist
       A.valid[0][i >> 5] = b0;
@@ -69,31 +76,25 @@ __global__ void __launch_bounds__(256) k_dict_lengths(const __grid_constant__ De
   }
 }
 
-__device__ __forceinline__ void warp_copy_bytes(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, uint32_t len,
-                                                uint32_t lane) {
-  for (uint32_t j = lane; j < len; j += 32) dst[j] = __ldg(src + j);
+// Eight lanes per row, four rows per warp in flight: terms are short (an IRI is a few dozen bytes), so a whole warp per row
+// left most lanes idle behind one dependent chain id -> record -> bytes (373 us for 2.5e6 IRIs, profiles/r4b_tv_microbench.json).
+constexpr uint32_t kCopyLanes = 8;
+__device__ __forceinline__ void group_copy_bytes(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, uint32_t len,
+                                                 uint32_t sub) {
+  for (uint32_t j = sub; j < len; j += kCopyLanes) dst[j] = __ldg(src + j);
 }
 
 __global__ void __launch_bounds__(256) k_dict_copy(const __grid_constant__ DecodeArgs A) {
-  const uint32_t lane = threadIdx.x & 31;
-  uint64_t row = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const uint64_t n_warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-  for (; row < A.n; row += n_warps) {
+  const uint32_t sub = threadIdx.x & (kCopyLanes - 1);
+  uint64_t row = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / kCopyLanes;
+  const uint64_t n_groups = ((uint64_t)gridDim.x * blockDim.x) / kCopyLanes;
+  for (; row < A.n; row += n_groups) {
     const uint32_t id = __ldg(A.ids + row);
     if (id == 0 || id > A.D.n_ids) continue;
-    {
-      const uint32_t o = A.off[0][row], len = A.off[0][row + 1] - o;
-      warp_copy_bytes(A.data[0] + o, A.D.value_bytes + __ldg(A.D.value_off + id), len, lane);
-    }
-    const uint32_t dt = __ldg(A.D.datatype + id), lg = __ldg(A.D.language + id);
-    if (dt) {
-      const uint32_t o = A.off[1][row], len = A.off[1][row + 1] - o;
-      warp_copy_bytes(A.data[1] + o, A.D.aux_bytes + __ldg(A.D.aux_off + dt), len, lane);
-    }
-    if (lg) {
-      const uint32_t o = A.off[2][row], len = A.off[2][row + 1] - o;
-      warp_copy_bytes(A.data[2] + o, A.D.aux_bytes + __ldg(A.D.aux_off + lg), len, lane);
-    }
+    const DictRec r = load_rec(A.D.rec + id);
+    group_copy_bytes(A.data[0] + A.off[0][row], A.D.value_bytes + r.value_off, r.value_len, sub);
+    if (r.dt) group_copy_bytes(A.data[1] + A.off[1][row], A.D.aux_bytes + __ldg(A.D.aux_off + r.dt), r.dt_len, sub);
+    if (r.lang) group_copy_bytes(A.data[2] + A.off[2][row], A.D.aux_bytes + __ldg(A.D.aux_off + r.lang), r.lang_len, sub);
   }
 }
 
@@ -170,7 +171,7 @@ rfgpu_plain_terms* decode_ids(rfgpu_ctx* ctx, const rfgpu_dict* d, const uint32_
   }
   if (n) {
     KernelScope ks(ctx, "k_dict_copy", 4ull * n + 2 * (P->bytes[0] + P->bytes[1] + P->bytes[2]));
-    uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(n, 8), (uint64_t)ctx->core->num_sms * 16));
+    uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(div_up(n, 256 / kCopyLanes), (uint64_t)ctx->core->num_sms * 16));
     k_dict_copy<<<grid, 256, 0, ctx->stream()>>>(A);
   }
   ctx->m.algorithmic_bytes += 4ull * n + 2 * (P->bytes[0] + P->bytes[1] + P->bytes[2]) + 13ull * n;
@@ -214,6 +215,18 @@ int32_t rfgpu_dict_create(rfgpu_ctx* ctx, uint32_t n_ids, const uint8_t* term_ty
   d->language = upload(ctx, language, ((size_t)n_ids + 1) * 4);
   d->aux_off = upload(ctx, aux_off, ((size_t)n_aux + 2) * 4);
   d->aux_bytes = upload(ctx, aux_bytes, aux_off[n_aux + 1]);
+  std::vector<DictRec> rec((size_t)n_ids + 1);
+  for (uint32_t i = 1; i <= n_ids; i++) {
+    DictRec& r = rec[i];
+    r.value_off = value_off[i];
+    r.value_len = (uint32_t)(value_off[i + 1] - value_off[i]);
+    r.dt = datatype[i];
+    r.lang = language[i];
+    r.dt_len = r.dt ? aux_off[r.dt + 1] - aux_off[r.dt] : 0;
+    r.lang_len = r.lang ? aux_off[r.lang + 1] - aux_off[r.lang] : 0;
+    r.term_type = term_type[i];
+  }
+  d->rec = upload(ctx, rec.data(), rec.size() * sizeof(DictRec));
   ctx->sync();
   *out = d.release();
   RF_API_END(ctx)

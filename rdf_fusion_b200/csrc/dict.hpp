@@ -12,6 +12,7 @@ struct rfgpu_dict {
   rf::BufRef language;     // u32[n_ids + 1]: index into the string table, 0 = none
   rf::BufRef aux_off;      // u32[n_aux + 2]: string a = aux_bytes[aux_off[a] .. aux_off[a + 1]), a in 1..n_aux
   rf::BufRef aux_bytes;
+  rf::BufRef rec;          // DictRec[n_ids + 1]: everything the decode needs to know about an id in ONE 32-byte sector
 };
 
 struct rfgpu_plain_terms {
@@ -26,6 +27,16 @@ struct rfgpu_plain_terms {
 
 namespace rf {
 
+// One gather per decoded row instead of five (value offsets, data type, language, their lengths, term type).
+struct DictRec {
+  unsigned long long value_off;
+  uint32_t value_len;
+  uint32_t dt, lang;          // indexes into the string table (0 = none)
+  uint32_t dt_len, lang_len;
+  uint32_t term_type;
+};
+static_assert(sizeof(DictRec) == 32, "one record = one 32-byte sector");
+
 struct DictDev {
   const uint8_t* term_type;
   const unsigned long long* value_off;
@@ -35,12 +46,13 @@ struct DictDev {
   const uint32_t* aux_off;
   const uint8_t* aux_bytes;
   uint32_t n_ids;
+  const DictRec* rec;
 };
 
 inline DictDev dict_dev(const rfgpu_dict* d) {
   return DictDev{d->term_type->as<uint8_t>(), d->value_off->as<unsigned long long>(), d->value_bytes->as<uint8_t>(),
                  d->datatype->as<uint32_t>(), d->language->as<uint32_t>(), d->aux_off->as<uint32_t>(),
-                 d->aux_bytes->as<uint8_t>(), d->n_ids};
+                 d->aux_bytes->as<uint8_t>(), d->n_ids, d->rec->as<DictRec>()};
 }
 
 // dict.cu — decodes the device id list ids[0..n) into the four children of the PlainTerm struct array (the body of
