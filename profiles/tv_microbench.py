@@ -73,6 +73,14 @@ def main():
     m = min(n, 20000000)
     out.append(measure(ctx, "ENC_TV decode into the union, %d rows" % m, lambda: tv.decode(T, "price", 0, m)["rows"],
                        m * (4 + 4 + 32 + 5 + 8), reps=2))
+    # ENC_PT of the same column (the ProjectionExec at the top of every plan): every row is a string here
+    k = min(n, 10000000)
+    d = tv.dictionary
+    lens = np.array([len(t[1]) for t in terms], np.int64)
+    dt_len = np.array([0 if t[0] == "nn" else len(t[2]) for t in terms], np.int64)
+    pt_bytes = int(lens[ids[:k] - 1].sum() + dt_len[ids[:k] - 1].sum())
+    out.append(measure(ctx, "ENC_PT decode (rfgpu_dict_decode), %d rows" % k, lambda: len(d.decode(T, "price", 0, k)),
+                       k * (4 + 32 + 13) + 2 * pt_bytes, reps=2))
     print(json.dumps({"hbm_peak_GBps": PEAK, "results": out}, indent=1))
 
 
