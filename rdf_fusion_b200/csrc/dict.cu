@@ -48,6 +48,7 @@ __global__ void __launch_bounds__(256) k_dict_lengths(const __grid_constant__ De
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   const uint32_t lane = threadIdx.x & 31;
+  unsigned long long nulls0 = 0, nulls1 = 0, nulls2 = 0;  // lane 0: NULL rows of the words this warp wrote
   for (; i < n_pad; i += stride) {
     const bool in = i < A.n;
     const uint32_t id = in ? __ldg(A.ids + i) : 0;
@@ -69,10 +70,17 @@ __global__ void __launch_bounds__(256) k_dict_lengths(const __grid_constant__ De
       A.valid[0][i >> 5] = b0;
       A.valid[1][i >> 5] = b1;
       A.valid[2][i >> 5] = b2;
-      atomicAdd(A.null_cnt + 0, (unsigned long long)(live - __popc(b0)));
-      atomicAdd(A.null_cnt + 1, (unsigned long long)(live - __popc(b1)));
-      atomicAdd(A.null_cnt + 2, (unsigned long long)(live - __popc(b2)));
+      nulls0 += live - __popc(b0);
+      nulls1 += live - __popc(b1);
+      nulls2 += live - __popc(b2);
     }
+  }
+  // one atomic per warp and counter at the END: three atomics per 32 rows on the same three words bound the kernel at the
+  // rate L2 serves one address (70 ns per row whatever the gathers cost, profiles/r4f_tv_microbench.json)
+  if (lane == 0) {
+    if (nulls0) atomicAdd(A.null_cnt + 0, nulls0);
+    if (nulls1) atomicAdd(A.null_cnt + 1, nulls1);
+    if (nulls2) atomicAdd(A.null_cnt + 2, nulls2);
   }
 }
 
