@@ -249,7 +249,10 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
         }
   }
   const int threads = 128;
-  const uint32_t n_tiles = div_up(np, (uint64_t)threads * 8);
+  // tiles of the launch; search-mode tiles hold a quarter of the rows (lookup_join.cuh), and a pending probe side may switch
+  // to search mode on the device: the look-back words are sized for that
+  const uint32_t n_tiles = div_up(np, (uint64_t)lookup_tile_rows(mode, threads * 8));
+  const uint32_t n_words = div_up(np, (uint64_t)threads * 8 / kSearchTileDiv);
   LookupArgs A{};
   A.pk = pk;
   A.np = np;
@@ -268,7 +271,7 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
   // the wide table of the counting sort (which stays the fallback when a key has more than 255 build rows)
   const uint32_t groups = search ? 0 : (D.range + 3) / 4;
   // one allocation [table | overflow flag | look-back words | total] so that one memset zeroes whatever has to be zero
-  const uint64_t tab_bytes = (uint64_t)groups * 8, words_bytes = 16 + (uint64_t)n_tiles * 8 + 16;
+  const uint64_t tab_bytes = (uint64_t)groups * 8, words_bytes = 16 + (uint64_t)n_words * 8 + 16;
   BufRef tab2 = ctx->alloc(tab_bytes + words_bytes);
   uint32_t* d_over = reinterpret_cast<uint32_t*>(tab2->as<uint8_t>() + tab_bytes);
   unsigned long long* d_status = reinterpret_cast<unsigned long long*>(tab2->as<uint8_t>() + tab_bytes + 16);
@@ -289,7 +292,7 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
   A.left = left ? 1 : 0;
   A.n_tiles = n_tiles;
   A.status = d_status;
-  A.total = A.status + n_tiles;
+  A.total = A.status + n_words;
   A.n_cols = (int32_t)specs.size();
   uint64_t in_cols_p = 0;
   for (size_t c = 0; c < specs.size(); c++) {
@@ -307,7 +310,7 @@ uint64_t lookup_join(rfgpu_ctx* ctx, const uint32_t* pk, uint64_t np, const uint
       A.dst[c] = (*bufs)[c]->as<uint32_t>();
     }
     A.cap = cap;
-    if (attempt > 0) RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_tiles * 8, ctx->stream()));  // (zeroed above the first time)
+    if (attempt > 0) RF_CUDA(cudaMemsetAsync(A.status, 0, (uint64_t)n_words * 8, ctx->stream()));  // (zeroed above the first time)
     const int slot = (lz && attempt == 0 && ctx->lazy_enabled()) ? ctx->lazy_take() : -1;
     if (slot >= 0) {
       A.total = ctx->lazy_d + slot;

@@ -257,14 +257,24 @@ struct LookupSmem {
 };
 
 // one tile of probe rows; `np` / `n_tiles` are the EFFECTIVE probe row count and tile count (see k_lookup_join)
+// Search mode (mode 1) is pure latency: ceil(log2 nb) dependent loads per probe row and a probe side that is tiny by
+// definition (16x smaller than the build side), so full tiles leave most of the GPU empty — 2e5 probe rows are 195 tiles of
+// 1024 rows, each thread walking 8 rows in two passes of 22 steps: 39 us at 8 % of the warp slots (profiles/r2o_ncu_summary.txt).
+// Its tiles therefore hold a quarter of the rows: four times the CTAs, one pass of two rows per thread.
+constexpr uint32_t kSearchTileDiv = 4;
+__host__ __device__ __forceinline__ uint32_t lookup_tile_rows(int mode, uint32_t full_tile) {
+  return mode == 1 ? full_tile / kSearchTileDiv : full_tile;
+}
+
 template <int kLThreads>
 __device__ __forceinline__ void lookup_tile(const LookupArgs& A, LookupSmem<kLThreads>& S, const uint32_t tile,
                                             const uint64_t np, const uint32_t n_tiles, const int mode) {
   constexpr int kTile = kLThreads * 8, kChunk = kTile;
   const uint32_t tid = threadIdx.x;
   const uint32_t lane = tid & 31, warp = tid >> 5;
-  const uint64_t row0 = (uint64_t)tile * kTile;
-  const uint32_t rows = row0 < np ? (uint32_t)min((uint64_t)kTile, np - row0) : 0u;
+  const uint32_t tile_rows = lookup_tile_rows(mode, (uint32_t)kTile);
+  const uint64_t row0 = (uint64_t)tile * tile_rows;
+  const uint32_t rows = row0 < np ? (uint32_t)min((uint64_t)tile_rows, np - row0) : 0u;
   const uint32_t leftpad = A.left ? 1u : 0u;
   // the table is probed at random by every tile and should stay in L2; keys, probe payload and output only stream through
   const uint64_t keep = dev::l2_policy_evict_last(), strm = dev::l2_policy_evict_first();
@@ -274,6 +284,14 @@ __device__ __forceinline__ void lookup_tile(const LookupArgs& A, LookupSmem<kLTh
   if (mode == 1) {  // search mode: lower_bound(key) and upper_bound(key), 4 rows' searches in lockstep
 #pragma unroll 1
     for (int h = 0; h < 2; h++) {
+      if ((uint32_t)(h * 4 * kLThreads) >= rows) {  // no row of this pass exists (uniform over the CTA)
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          S.gs[tid + (h * 4 + k) * kLThreads] = kNone;
+          S.off[tid + (h * 4 + k) * kLThreads] = 0u;
+        }
+        continue;
+      }
       uint32_t key[4], lo[4], hi[4], lo2[4], hi2[4];
 #pragma unroll
       for (int k = 0; k < 4; k++) {
@@ -533,9 +551,10 @@ k_lookup_join(const __grid_constant__ LookupArgs A) {
     lookup_tile<kLThreads>(A, S, blockIdx.x, A.np, A.n_tiles, A.mode);
   } else {
     const uint64_t np = min(A.np, (uint64_t)*A.np_dev);
-    const uint32_t n_tiles = max(1u, (uint32_t)((np + kLThreads * 8 - 1) / (kLThreads * 8)));  // tile 0 reports an empty input
     // a sorted build side that dwarfs the probe side: search it (k_dense_heads_compact made the same test and built nothing)
     const int mode = (A.mode == 2 && lookup_searches(np, A.nb_sorted)) ? 1 : A.mode;
+    const uint32_t tile_rows = lookup_tile_rows(mode, (uint32_t)kLThreads * 8);
+    const uint32_t n_tiles = max(1u, (uint32_t)((np + tile_rows - 1) / tile_rows));  // tile 0 reports an empty input
     for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
       lookup_tile<kLThreads>(A, S, tile, np, n_tiles, mode);
       __syncthreads();  // the shared tile state is reused

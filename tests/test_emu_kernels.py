@@ -432,8 +432,8 @@ def test_lookup_join_dense_keys(emu, oracle, jt):
     (counting sort), the fused probe + expansion kernel over several tiles, heavy keys, keys outside the build range, and the
     same joins with the option off (open-addressing hash table)"""
     rng = np.random.default_rng(77 + jt)
-    shapes = some([(1, 1, 1, 0), (5000, 3000, 900, 100), (2600, 9000, 40, 7), (1500, 1200, 50000, 3), (9000, 20, 6, 0), (700, 2400, 4, 2), (40, 3000, 500, 10), (3, 9000, 100000, 1)],
-                  [(2300, 1400, 500, 60), (1100, 2600, 30, 5), (700, 2400, 4, 2), (40, 3000, 500, 10)])
+    shapes = some([(1, 1, 1, 0), (5000, 3000, 900, 100), (2600, 9000, 40, 7), (1500, 1200, 50000, 3), (9000, 20, 6, 0), (700, 2400, 4, 2), (40, 3000, 500, 10), (3, 9000, 100000, 1), (600, 12000, 3000, 5)],
+                  [(2300, 1400, 500, 60), (1100, 2600, 30, 5), (700, 2400, 4, 2), (40, 3000, 500, 10), (600, 12000, 3000, 5)])  # the last: search mode over several quarter tiles
     for nl_, nr_, hi, base in shapes:
         ln, rn = ["a", "k", "c"], ["k", "z"]
         lc = [rng.integers(1, 1000, nl_).astype(np.uint32), rng.integers(1, hi + 40, nl_).astype(np.uint32) + base,

@@ -772,6 +772,38 @@ def test_lazy_row_counts_chain(ctx, oracle):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("jt", [F.JOIN_INNER, F.JOIN_LEFT])
+def test_lookup_join_search_mode_tiles(ctx, oracle, jt):
+    """a probe side 16x smaller than a sorted build side: no table, two binary searches per probe row (lookup_join.cuh mode 1),
+    whose tiles hold a quarter of the rows — several quarter tiles with a partial last one, chosen by the host (row count
+    known) and by the device (pending probe side whose capacity says "table")"""
+    rng = np.random.default_rng(123 + jt)
+    nb = 200000
+    build = {"k": np.sort(rng.integers(1, nb // 3, nb).astype(np.uint32)), "z": rng.integers(1, 999, nb).astype(np.uint32)}
+    OB = oracle.OTable(list(build), [False, False], list(build.values()))
+    B = ctx.import_table(build).set_sorted("k")
+    for n_probe in (1, 255, 256, 257, 5000):
+        probe = {"a": rng.integers(1, 999, n_probe).astype(np.uint32), "k": rng.integers(1, nb // 3 + 50, n_probe).astype(np.uint32)}
+        want = oracle.sparql_join(oracle.OTable(list(probe), [False, False], list(probe.values())), OB, jt, "hash")[0]
+        got = ctx.import_table(probe).join(B, jt)
+        assert got.last_join_phys == F.PHYS_LOOKUP
+        assert got.num_rows == want.num_rows
+        assert_same_table(got.names, got.to_numpy(), want.names, want.cols)
+    # decided on the device: j1 is pending with a capacity of thousands of rows, but holds a few hundred
+    a = {"b": np.sort(rng.integers(1, 40, 2500).astype(np.uint32)), "a": rng.integers(1, 99, 2500).astype(np.uint32)}
+    b = {"b": np.sort(rng.integers(35, 600, 2500).astype(np.uint32)), "k": rng.integers(1, nb // 3, 2500).astype(np.uint32)}
+    j1 = ctx.import_table(a).set_sorted("b").join(ctx.import_table(b).set_sorted("b"), F.JOIN_INNER)
+    j2 = j1.join(B, jt)
+    assert j2.last_join_phys == F.PHYS_LOOKUP
+    w1 = oracle.sparql_join(oracle.OTable(list(a), [False, False], list(a.values())),
+                            oracle.OTable(list(b), [False, False], list(b.values())), F.JOIN_INNER, "hash")[0]
+    assert 256 < w1.num_rows and w1.num_rows * 16 <= nb
+    want = oracle.sparql_join(w1, OB, jt, "hash")[0]
+    assert j2.num_rows == want.num_rows
+    assert_same_table(j2.names, j2.to_numpy(), want.names, want.cols)
+
+
+@pytest.mark.gpu
 def test_lazy_row_counts_capacity_exceeded(ctx, oracle):
     """every join of the chain has fan-out 3 and outgrows its optimistic output capacity: the later joins have consumed
     truncated inputs by the time the host reads the first count; settling the last table recomputes the chain from the first
