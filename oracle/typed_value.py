@@ -18,8 +18,9 @@ Restates, with the reference lines each function follows (root = /root/reference
     EncodedTypedValue (lib/storage/src/memory/encoding/typed_value.rs:9-25).
 
 Pinned on the W3C evaluation tests the reference itself runs (testsuite/tests/sparql.rs:16-34): sparql10/expr-equals and
-sparql10/open-world, tests/golden/tv_golden.json (tests/golden/make_tv_golden.py); duration ORDER comparisons are restated
-only for the cases that need no calendar arithmetic (see compare()).
+sparql10/open-world, tests/golden/tv_golden.json (tests/golden/make_tv_golden.py), and on the reference's unit-test vectors
+(date_time.rs:2697-2812, decimal.rs:702-735, duration.rs:1028-1176).  Duration order (calendar arithmetic on four reference
+dates, duration.rs:271-308) is restated here too; the DEVICE refuses it (RFGPU_E_UNSUPPORTED).
 
 Terms are the tuples of rdf_fusion_b200.api.pack_terms: ("nn", iri) | ("bn", label) | ("lit", value, datatype) |
 ("lang", value, tag).  A typed value is a tuple (field, payload...), field = TypedValueEncodingField
@@ -467,7 +468,78 @@ def _ts_cmp(a, b):  # date_time.rs:1617-1654
 
 
 class Unsupported(Exception):
-    """a pair whose order the reference finds by calendar arithmetic (duration.rs:271-308); not restated"""
+    """kept for callers that want to refuse duration order as the device does (rfgpu_tv_eval: RFGPU_E_UNSUPPORTED)"""
+
+
+def _tdiv(a, b):  # Rust's integer division truncates toward zero
+    q = abs(a) // abs(b)
+    return q if (a < 0) == (b < 0) else -q
+
+
+def _trem(a, b):
+    return a - b * _tdiv(a, b)
+
+
+def _u8(v):
+    if not (0 <= v <= 255):
+        raise ParseError("u8")
+    return v
+
+
+def _normalize_month(yr, mo):  # date_time.rs:1933-1950
+    if mo >= 0:
+        return _i64(yr + _tdiv(mo - 1, 12)), _u8(abs(_trem(mo - 1, 12)) + 1)
+    return _i64(yr + _tdiv(mo - 1, 12) - 1), _u8(12 + _trem(mo - 1, 12) + 1)
+
+
+def _normalize_day(yr, mo, da):  # date_time.rs:1953-1970
+    yr, mo = _normalize_month(yr, mo)
+    while True:
+        if da <= 0:
+            yr, mo = _normalize_month(yr, mo - 1)
+            da += _days_in_month(yr, mo)
+        elif da > _days_in_month(yr, mo):
+            da -= _days_in_month(yr, mo)
+            yr, mo = _normalize_month(yr, mo + 1)
+        else:
+            return yr, mo, _u8(da)
+
+
+def _date_time_plus_duration(months, seconds, ymd):
+    """DateTime::checked_add_duration (date_time.rs:188-200) of the date `ymd` at 00:00:00 without a timezone -> its
+    timeline value, or None where the reference returns Err.  months / seconds: Duration::all_months / all_seconds."""
+    y, m, d = ymd
+    try:
+        if months == 0:  # DayTimeDuration::try_from(duration) succeeds: the seconds are added to the timestamp
+            return _chk_i128(_time_on_timeline(y, m, d, 0, 0, 0, None) + seconds)
+        # dateTimePlusDuration (date_time.rs:2023-2052)
+        yr, mo = _normalize_month(y, _i64(m + months))
+        da = min(d, _days_in_month(yr, mo))
+        se = _chk_i128(seconds)
+        # normalizeSecond / normalizeMinute (date_time.rs:1973-2001)
+        mi = _i64(_tdiv(_tdiv(se, DEC_POW), 60))
+        se = _trem(se, 60 * DEC_POW)
+        hr = _tdiv(mi, 60)
+        mi = _trem(mi, 60)
+        da = da + _tdiv(hr, 24)
+        hr = _trem(hr, 24)
+        yr, mo, da = _normalize_day(yr, mo, da)
+        return _time_on_timeline(yr, mo, da, _u8(hr), _u8(mi), se, None)
+    except ParseError:
+        return None
+
+
+def _duration_cmp(a, b):
+    """Duration::partial_cmp (duration.rs:271-308): both durations are added to four reference dates; ordered only if the four
+    comparisons agree.  a, b = (DURATION, months or None, seconds or None)."""
+    res = []
+    for ymd in ((1969, 9, 1), (1697, 2, 1), (1903, 3, 1), (1903, 7, 1)):
+        ta = _date_time_plus_duration(a[1] or 0, a[2] or 0, ymd)
+        tb = _date_time_plus_duration(b[1] or 0, b[2] or 0, ymd)
+        if ta is None or tb is None:
+            return None
+        res.append(_cmp(ta, tb))
+    return res[0] if res.count(res[0]) == 4 else None
 
 
 def compare(a, b):
@@ -491,10 +563,8 @@ def compare(a, b):
         return _num_cmp(a, b) if fb in (FLOAT, DOUBLE, DECIMAL, INT, INTEGER) else None
     if fa in (DATE_TIME, TIME, DATE):
         return _ts_cmp(a, b) if fb == fa else None
-    if fa == DURATION:
-        if fb != DURATION:
-            return None
-        raise Unsupported("duration order")
+    if fa == DURATION:  # Duration, YearMonthDuration and DayTimeDuration compare with each other (typed_value.rs:232-249)
+        return _duration_cmp(a, b) if fb == DURATION else None
     if fa == OTHER:
         if fb != OTHER or a[2] != b[2]:
             return None

@@ -55,6 +55,33 @@ def test_oracle_decimal_vectors(tvo):
     assert tvo.typed_value(S.lit("-170141183460469231731.687303715884105728", "decimal"))[1] == -2 ** 127
 
 
+def test_oracle_duration_vectors(tvo):
+    """duration.rs:1028-1230: the lexical mapping (months, seconds) and Duration::partial_cmp over the four reference dates"""
+    for dt, lex, months, seconds in S.REF_DURATION_PARSE:
+        tv = tvo.typed_value(S.lit(lex, dt))
+        assert tv is not None and tv[0] == tvo.DURATION, (dt, lex)
+        want_s = None if seconds is None else Fraction(str(seconds))
+        got_m, got_s = tv[1], None if tv[2] is None else Fraction(tv[2], tvo.DEC_POW)
+        if dt == S.D:  # xsd:duration always carries both parts (Duration::new), a missing one is zero
+            assert (got_m, got_s) == (months or 0, want_s or 0), (dt, lex, tv)
+        else:
+            assert (got_m, got_s) == (months, want_s), (dt, lex, tv)
+    for (ta, la), (tb, lb), want in S.REF_DURATION_VECTORS:
+        a, b = tvo.typed_value(S.lit(la, ta)), tvo.typed_value(S.lit(lb, tb))
+        c = tvo.compare(a, b)
+        if want == "not equal":
+            assert c != 0, (la, lb, c)
+        else:
+            assert c == want, (la, lb, c)
+            assert tvo.compare(b, a) == -want
+    # the component types reject the other type's fields; opposite signs are no duration; a negative time part next to months
+    # makes an hour count the reference cannot hold in a u8: unordered
+    assert tvo.typed_value(S.lit("P1D", S.YM)) is None and tvo.typed_value(S.lit("P1M", S.DT)) is None
+    assert tvo.typed_value(S.lit("P1Y-1M", S.D)) is None and tvo.typed_value(S.lit("P", S.D)) is None
+    assert tvo.compare(tvo.typed_value(S.lit("-P1YT1H", S.D)), tvo.typed_value(S.lit("P1Y", S.D))) is None
+    assert tvo.compare(tvo.typed_value(S.lit("P1Y", S.D)), tvo.typed_value(S.lit("1", "integer"))) is None
+
+
 def test_oracle_timeline_against_the_calendar(tvo):
     """timeOnTimeline (date_time.rs:2055-2082) against Python's proleptic Gregorian calendar: seconds since 0001-01-01"""
     import datetime

@@ -49,6 +49,29 @@ REF_DECIMAL_INVALID = ["", "+", "-", ".", "+.", "-.", "a", ".a", "0.000000000000
 REF_DECIMAL_EQUAL = [("+100000.00", "100000"), ("0.1220", "0.122"), (".12200", "0.122"), ("1.", "1"), ("1.0", "1"),
                      ("01.0", "1"), ("-0", "0"), ("0.100000000000000000000000000", "0.1")]
 
+# lib/model/src/xsd/duration.rs:1114-1176 (fn equals, fn cmp): (datatype, lexical) pairs and the ordering partial_cmp must give.
+# `equals` there is the derived PartialEq (same months and seconds): for those pairs partial_cmp is Equal as well; the pairs it
+# declares unequal (P1Y / P365D, P1M / P30D) are unordered under partial_cmp (the four reference dates disagree), never Equal.
+D, YM, DT = "duration", "yearMonthDuration", "dayTimeDuration"
+REF_DURATION_VECTORS = [
+    ((YM, "P1Y"), (YM, "P12M"), 0), ((YM, "P1Y"), (D, "P12M"), 0), ((D, "P1Y"), (YM, "P12M"), 0), ((D, "P1Y"), (D, "P12M"), 0),
+    ((DT, "PT24H"), (DT, "P1D"), 0), ((DT, "PT24H"), (D, "P1D"), 0), ((D, "PT24H"), (DT, "P1D"), 0), ((D, "PT24H"), (D, "P1D"), 0),
+    ((D, "P0Y"), (D, "P0D"), 0), ((D, "P2Y"), (D, "P24M"), 0), ((D, "P10D"), (D, "PT240H"), 0),
+    ((D, "P2Y0M0DT0H0M0S"), (D, "P24M"), 0), ((D, "P0Y0M10D"), (D, "PT240H"), 0),
+    ((D, "P1Y"), (D, "P365D"), "not equal"), ((D, "P1M"), (D, "P30D"), "not equal"),
+    ((D, "P1Y1D"), (D, "P13MT25H"), -1), ((YM, "P1Y"), (YM, "P13M"), -1), ((D, "P1Y"), (YM, "P13M"), -1), ((YM, "P1Y"), (D, "P13M"), -1),
+    ((DT, "P1D"), (DT, "PT25H"), -1), ((DT, "PT1H"), (DT, "PT61M"), -1), ((DT, "PT1M"), (DT, "PT61S"), -1),
+    ((D, "PT1H"), (DT, "PT61M"), -1), ((DT, "PT1H"), (D, "PT61M"), -1), ((YM, "P1M"), (DT, "P40D"), -1), ((DT, "P25D"), (YM, "P1M"), -1),
+]
+# duration.rs:1028-1065 (fn from_str) and :1178-1230 (years / months / days / hours / minutes / seconds): lexical form -> (months, seconds)
+REF_DURATION_PARSE = [
+    (D, "P1Y", 12, None), (YM, "P1M", 1, None), (DT, "P1D", None, 86400), (D, "PT1H", None, 3600), (DT, "PT1M", None, 60),
+    (D, "PT1.1S", None, "1.1"), (YM, "-P1Y", -12, None), (D, "-P1M", -1, None), (DT, "-P1D", None, -86400), (D, "-PT1.1S", None, "-1.1"),
+    (D, "PT0H", None, 0), (D, "-PT0H", None, 0), (YM, "P0Y", 0, None), (D, "P20Y15M", 255, None), (D, "-P20Y18M", -258, None),
+    (D, "P3DT55H", None, 3 * 86400 + 55 * 3600), (D, "P3DT12H32M12S", None, 3 * 86400 + 12 * 3600 + 32 * 60 + 12),
+    (D, "P3DT10H12.5S", None, "295212.5"), (D, "-PT256S", None, -256), (D, "-P5DT12H30M", None, -(5 * 86400 + 12 * 3600 + 30 * 60)),
+]
+
 OPS = {"=": F.TV_EQ, "<": F.TV_LT, "<=": F.TV_LE, ">": F.TV_GT, ">=": F.TV_GE}
 
 
