@@ -82,6 +82,33 @@ def test_oracle_duration_vectors(tvo):
     assert tvo.compare(tvo.typed_value(S.lit("P1Y", S.D)), tvo.typed_value(S.lit("1", "integer"))) is None
 
 
+def test_oracle_number_vectors(tvo):
+    """float.rs:298-316, double.rs:320-344, integer.rs:333-340, int.rs:282-289 (fn from_str): lexical form -> value"""
+    import math
+    for t, np_t in (("float", np.float32), ("double", np.float64)):
+        val = lambda s: tvo.typed_value(S.lit(s, t))[1]  # noqa: E731
+        assert math.isnan(val("NaN"))
+        assert val("INF") == val("+INF") == math.inf and val("-INF") == -math.inf
+        assert val("0.0E0") == 0 and math.copysign(1, float(val("0.0E0"))) == 1
+        assert val("-0.0E0") == 0 and math.copysign(1, float(val("-0.0E0"))) == -1
+        for s, v in (("0.1e1", 1), ("-0.1e1", -1), ("1.e1", 10), ("-1.e1", -10), ("1", 1), ("-1", -1), ("1.", 1), ("-1.", -1)):
+            assert val(s) == v, (t, s)
+        for v in (np.finfo(np_t).min, np.finfo(np_t).max):  # MIN / MAX round trip through their decimal forms
+            assert val(repr(float(v))) == v
+        assert tvo.typed_value(S.lit("1e", t)) is None and tvo.typed_value(S.lit(" 1", t)) is None
+    for t in ("int", "integer"):
+        val = lambda s: tvo.typed_value(S.lit(s, t))  # noqa: E731
+        assert val("0")[1] == 0 and val("-0")[1] == 0 and val("123")[1] == 123 and val("-123")[1] == -123
+        assert val("123456789123456789123456789123456789123456789") is None
+    assert tvo.typed_value(S.lit("2147483648", "int")) is None and tvo.typed_value(S.lit("2147483648", "integer"))[1] == 2 ** 31
+    # f32::from_str rounds the decimal form ONCE: 16777217 = 2^24 + 1 ties to even, and a value whose f64 rounding would
+    # land on a tie of the f32 grid must not be rounded twice
+    assert tvo.typed_value(S.lit("16777217", "float"))[1] == np.float32(16777216)
+    # 1 + 2.5 ulp plus a hair: correctly rounded it is 1 + 3 ulp; through f64 it would first become the exact tie and then go to even
+    assert tvo.typed_value(S.lit("1.00000029802322387695312500001", "float"))[1] == np.float32(1 + 3 * 2.0 ** -23)
+    assert np.float32(float("1.00000029802322387695312500001")) == np.float32(1 + 2 * 2.0 ** -23)  # what double rounding gives
+
+
 def test_oracle_timeline_against_the_calendar(tvo):
     """timeOnTimeline (date_time.rs:2055-2082) against Python's proleptic Gregorian calendar: seconds since 0001-01-01"""
     import datetime
